@@ -1,0 +1,369 @@
+#!/usr/bin/env python
+"""bench.py -- output MP/s of the 9x12MP vertical stitch (BASELINE.json configs[1]) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg2_yuv|cfg1|cfg3]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one stitch job (layout + fused resample/compose of all 9 images into the
+canvas) with the decoded RGBA bitmaps already resident in HBM.  `value` = output
+megapixels of all ranks / device time (CUDA events on the launch stream, max over
+ranks).  `e2e` = the same job through the public C ABI with pinned HOST buffers
+(H2D of the 9 bitmaps + D2H of the canvas inside the timed region).
+`roofline` = algorithmic bytes (sum of source bytes + canvas bytes) per
+launch / average launch duration vs the measured HBM copy peak.
+`cpu_baseline` = the C restatement of the same path (oracle/raster_ref.c, fp32, OpenMP)
+timed on this box's host cores on a bounded sample.  --impl reference times that CPU
+path alone: the reference itself (a WeChat mini-program) cannot run outside WeChat.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+MIXED = [(4032, 3024), (3024, 4032), (1920, 1080), (1080, 1920), (4000, 3000), (3000, 4000), (2048, 2048),
+         (6000, 4000), (1280, 720)]
+WORKLOADS = {
+    # name: (dims, direction, mode, platform, output, description)
+    "cfg2": ([(4032, 3024)] * 9, "vertical", "min", "ios", "rgba",
+             "9x 4032x3024 RGBA vertical stitch, iOS canvas clamp -> 1820x12288 (BASELINE configs[1])"),
+    "cfg2_yuv": ([(4032, 3024)] * 9, "vertical", "min", "ios", "yuv420",
+                 "9x 4032x3024 vertical stitch with fused RGBA->YUV420 epilogue (BASELINE configs[3])"),
+    "cfg1": ([(1080, 1920)] * 2, "vertical", "min", "ios", "rgba",
+             "2x 1080x1920 vertical stitch, 2.2x supersampled canvas 2376x8448 (BASELINE configs[0])"),
+    "cfg3": (MIXED, "horizontal", "max", "ios", "rgba",
+             "9 mixed-aspect images horizontal 'max' -> 12288x1139 (BASELINE configs[2])"),
+}
+SEED = 0x5717C4
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            d = json.load(open(p))
+            return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period: float = 0.01):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.max_mhz = None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def sample(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        try:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+            try:
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+            except Exception:
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+            names = {
+                0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x100: "display_clock_setting",
+                0x10: "sync_boost",
+            }
+            for bit, name in names.items():
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            self.sample()
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=2)
+        self.sample()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+def cpu_reference_run(workload: str, steps: int, warmup: int, threads: int | None = None):
+    """Times the C restatement (fp32, OpenMP) of the path on the host cores: one full job per step."""
+    import numpy as np
+
+    from oracle import layout_ref as LR
+    from oracle import raster_c as RC
+    from tests import util as U
+
+    dims, direction, mode, platform, output, _ = WORKLOADS[workload]
+    cores = threads or os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    bitmaps = []
+    cache = {}
+    for i, (w, h) in enumerate(dims):
+        key = (w, h)
+        if key not in cache:                      # content does not affect CPU timing; reuse per shape
+            cache[key] = U.synth_image(w, h, SEED + i, 0)
+        bitmaps.append(cache[key])
+    lay = LR.compute_layout(U.recs(dims), direction, mode, 0, U.profile_of(platform))
+    mp = lay.canvasW * lay.canvasH / 1e6
+    want_yuv = output != "rgba"
+
+    def one():
+        lay2 = LR.compute_layout(U.recs(dims), direction, mode, 0, U.profile_of(platform))
+        RC.render(lay2, bitmaps, [1] * len(dims), want_rgba=not want_yuv or output == "both", want_yuv=want_yuv,
+                  precision="f32")
+
+    for _ in range(warmup):
+        one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = time.perf_counter() - t0
+    return mp * steps / dt, dt / steps * 1e3, cores, mp
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--slots", type=int, default=3, help="distinct resident job slots rotated between steps")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (min(steps, 10))")
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    dims, direction, mode, platform, output, desc = WORKLOADS[args.workload]
+    W = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        steps = max(1, args.steps)
+        val, ms, cores, mp = cpu_reference_run(args.workload, steps, min(args.warmup, 2))
+        line = {
+            "impl": "reference", "metric": "output MP/s, 9x12MP vertical stitch", "value": val, "unit": "MP/s",
+            "n_gpus": args.gpus, "steps": steps, "warmup": min(args.warmup, 2), "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "name": args.workload},
+            "cpu_baseline": {"value": val, "unit": "MP/s", "cores": cores, "kind": "port",
+                             "sample": f"{steps} full job(s) of the workload, C restatement (oracle/raster_ref.c fp32, OpenMP)"},
+            "e2e": {"value": val, "unit": "MP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "the reference (WeChat mini-program, closed Canvas2D runtime) cannot run here; this times the CPU restatement of its path",
+        }
+        print(json.dumps(line))
+        return 0
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from imagestitching_b200 import DeviceBitmap, StitchContext
+    from imagestitching_b200 import _lib as L
+    from imagestitching_b200.stitch import _profile_struct
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl ours needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    stream = torch.cuda.Stream()
+    ctx = StitchContext(local_rank, stream.cuda_stream)
+    lib = ctx.lib
+    profile = _profile_struct(platform)
+
+    # ---- resident job slots (bitmaps generated on device by K0) ----
+    slots = []
+    n = len(dims)
+    with torch.cuda.stream(stream):
+        for s in range(max(1, args.slots)):
+            imgs, keep = [], []
+            for i, (w, h) in enumerate(dims):
+                pitch = (w * 4 + 15) & ~15
+                t = torch.empty(h * pitch, dtype=torch.uint8, device="cuda")
+                st = lib.stitch_generate_image(ctx.handle, t.data_ptr(), w, h, pitch, SEED + 1000 * rank + 16 * s + i, 0)
+                assert st == 0
+                keep.append(t)
+                imgs.append({"naturalWidth": w, "naturalHeight": h, "width": w, "height": h, "orientation": 1,
+                             "fileSize": 0, "bitmap": DeviceBitmap(t.data_ptr(), w, h, pitch)})
+            slots.append((imgs, keep))
+    # layout (for sizes)
+    from imagestitching_b200 import compute_layout
+    lay = compute_layout(slots[0][0], direction, mode, 0, platform)
+    cw, ch = int(lay["canvasW"]), int(lay["canvasH"])
+    mp = cw * ch / 1e6
+    rgba_bytes = cw * ch * 4
+    yuv_bytes = cw * ch + 2 * ((cw + 1) // 2) * ((ch + 1) // 2)
+    src_bytes = sum(w * h * 4 for (w, h) in dims)
+    out_bytes = (rgba_bytes if output in ("rgba", "both") else 0) + (yuv_bytes if output in ("yuv420", "both") else 0)
+    algo_bytes = src_bytes + out_bytes
+
+    jobs = []
+    for (imgs, keep) in slots:
+        o_rgba = torch.empty(rgba_bytes, dtype=torch.uint8, device="cuda") if output in ("rgba", "both") else None
+        o_yuv = torch.empty(yuv_bytes, dtype=torch.uint8, device="cuda") if output in ("yuv420", "both") else None
+        job, keep2 = ctx.build_job(imgs, direction, mode, 0, profile, output, True,
+                                   o_rgba.data_ptr() if o_rgba is not None else 0,
+                                   o_yuv.data_ptr() if o_yuv is not None else 0, rgba_bytes, yuv_bytes)
+        jobs.append((job, keep2, o_rgba, o_yuv))
+    res = L.StitchResult()
+
+    def step(i):
+        job = jobs[i % len(jobs)][0]
+        t = C.c_uint64()
+        st = lib.stitch_submit(ctx.handle, C.byref(job), C.byref(res), C.byref(t))
+        if st != 0:
+            raise RuntimeError(f"stitch_submit failed: {st} {lib.stitch_last_error(ctx.handle)}")
+        return t.value
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    # ---- device-resident timing ----
+    last = 0
+    for i in range(W):
+        last = step(i)
+    lib.stitch_wait(ctx.handle, last)
+    torch.cuda.synchronize()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    launches0 = ctx.kernel_launches
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    sampler.start()
+    ev0.record(stream)
+    for i in range(args.steps):
+        last = step(i)
+    ev1.record(stream)
+    sampler.sample()
+    lib.stitch_wait(ctx.handle, last)
+    torch.cuda.synchronize()
+    sampler.stop()
+    barrier()
+    elapsed_ms = ev0.elapsed_time(ev1)
+    launches = ctx.kernel_launches - launches0
+    if world > 1:
+        t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    value = mp * args.steps * world / (elapsed_ms / 1e3)
+    ms_per_step = elapsed_ms / args.steps
+
+    # ---- end-to-end through the C ABI with pinned host buffers ----
+    e2e_steps = args.e2e_steps or max(3, min(args.steps, 10))
+    host_imgs, host_keep = [], []
+    for i, (w, h) in enumerate(dims):
+        p = C.c_void_p()
+        assert lib.stitch_host_alloc(w * h * 4, C.byref(p)) == 0
+        arr = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(h, w, 4))
+        # fill from the device-generated bitmap of slot 0 (row pitch == w*4 for these widths or copy row-wise)
+        t = slots[0][1][i]
+        pitch = (w * 4 + 15) & ~15
+        arr[:] = t.view(h, pitch)[:, : w * 4].reshape(h, w, 4).cpu().numpy()
+        host_keep.append(p)
+        host_imgs.append({"naturalWidth": w, "naturalHeight": h, "width": w, "height": h, "orientation": 1,
+                          "fileSize": 0, "bitmap": arr})
+    ho_rgba, ho_yuv = C.c_void_p(), C.c_void_p()
+    if output in ("rgba", "both"):
+        assert lib.stitch_host_alloc(rgba_bytes, C.byref(ho_rgba)) == 0
+    if output in ("yuv420", "both"):
+        assert lib.stitch_host_alloc(yuv_bytes, C.byref(ho_yuv)) == 0
+    hjob, hkeep = ctx.build_job(host_imgs, direction, mode, 0, profile, output, False, ho_rgba.value or 0,
+                                ho_yuv.value or 0, rgba_bytes, yuv_bytes)
+    hres = L.StitchResult()
+    for _ in range(2):
+        assert lib.stitch_run(ctx.handle, C.byref(hjob), C.byref(hres)) == 0
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        st = lib.stitch_run(ctx.handle, C.byref(hjob), C.byref(hres))
+        assert st == 0
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    e2e_value = mp * e2e_steps * world / e2e_s
+
+    peak, peak_src = _peaks()
+    achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9   # one compose launch per step
+    line = {
+        "metric": "output MP/s, 9x12MP vertical stitch" if args.workload.startswith("cfg2") else "output MP/s",
+        "value": value, "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": W,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8 in/out, f32 accumulate", "data": "synthetic",
+        "config": {"workload": desc, "name": args.workload, "canvas": [cw, ch], "output_mp_per_step": mp,
+                   "inputs": "device-resident RGBA8, generated on device (seed 0x5717C4)",
+                   "l2": f"{len(jobs)} job slots rotated; each job reads {src_bytes/1e6:.0f} MB (> 126 MB L2)",
+                   "parallelism": f"{world} independent job stream(s), no collective"},
+        "gpu_launches": int(launches),
+        "clocks": sampler.summary(),
+        "e2e": {"value": e2e_value, "unit": "MP/s", "h2d_bytes_per_step": src_bytes, "d2h_bytes_per_step": out_bytes,
+                "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": algo_bytes,
+                     "frac_of_8TBps_nominal": achieved / 8000.0,
+                     "launches_per_step": launches / max(1, args.steps)},
+    }
+    prof_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof_path):
+        try:
+            line["roofline"]["traffic"] = json.load(open(prof_path)).get(args.workload)
+        except Exception:
+            pass
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            val, ms, cores, _ = cpu_reference_run(args.workload, max(1, args.cpu_steps), 1)
+            line["cpu_baseline"] = {"value": val, "unit": "MP/s", "cores": cores, "kind": "port",
+                                    "sample": f"{max(1, args.cpu_steps)} full job(s), C restatement fp32 + OpenMP ({ms:.0f} ms/job)"}
+        except Exception as e:  # the baseline is a report, never a blocker
+            line["cpu_baseline"] = {"value": None, "unit": "MP/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
+    if rank == 0:
+        print(json.dumps(line))
+    for p in host_keep + [ho_rgba, ho_yuv]:
+        if p:
+            lib.stitch_host_free(p)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

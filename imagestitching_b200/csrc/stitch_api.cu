@@ -1,0 +1,401 @@
+// libstitch.so: context, job planning and kernel launch behind the C ABI (include/stitch.h).
+//
+// Replaces, for the stitch path only (reference paths under
+// /root/reference/miniprogram-stitch/miniprogram/, P = pages/index/index.js, U = utils/canvas.js):
+//   P:1186-1633 onStitch()            -> stitch_run / stitch_submit + stitch_wait
+//   U:131-150   safeCreateOffscreenCanvas -> caller/ctx-owned device canvas
+//   U:153-202   drawWithOrientation   -> ImgParam placement + kernels
+//   U:205-242   safeCanvasToTempFilePath  -> RGBA / I420 export into the caller's buffer
+// There is no CPU pixel path in this library.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <string>
+#include <vector>
+
+#include "gather_kernel.cuh"
+#include "stitch.h"
+#include "stitch_plan.h"
+#include "stream_kernel.cuh"
+
+struct PendingJob {
+  uint64_t ticket;
+  cudaEvent_t done;
+  int32_t n;
+};
+
+struct StitchCtx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  StitchProgressFn progress = nullptr;
+  void* progress_user = nullptr;
+  std::string last_error;
+  // grow-only device staging for host-resident inputs / outputs
+  std::vector<void*> in_stage;
+  std::vector<size_t> in_stage_cap;
+  void* out_stage = nullptr;
+  size_t out_stage_cap = 0;
+  int64_t launches = 0;
+  uint64_t next_ticket = 1;
+  std::deque<PendingJob> pending;
+  bool busy = false;
+  int sm_count = 148;
+  stitch::StreamScratch scratch;
+};
+
+namespace {
+
+int fail(StitchCtx* ctx, int code, const std::string& msg) {
+  if (ctx) ctx->last_error = msg;
+  return code;
+}
+
+#define CUDA_TRY(ctx, expr)                                                                  \
+  do {                                                                                       \
+    cudaError_t e__ = (expr);                                                                \
+    if (e__ != cudaSuccess) {                                                                \
+      return fail(ctx, STITCH_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(e__)); \
+    }                                                                                        \
+  } while (0)
+
+void emit(StitchCtx* ctx, int pct) {
+  if (ctx->progress) ctx->progress(ctx->progress_user, pct);
+}
+
+// Resolve one drawWithOrientation call (U:153-202) + ctx.scale(ss,ss) (P:1426-1428).
+void make_placement(const StitchRect& r, int orientation, double ss, int bw, int bh, int cw, int ch, ImgParam* p) {
+  double dx = r.dx, dy = r.dy;
+  const double dw = r.dw, dh = r.dh;
+  bool transpose = false, flip_u = false, flip_v = false;  // bitmap-axis flips
+  switch (orientation) {
+    case 2: flip_u = true; break;                                   // U:161-165
+    case 3: flip_u = true; flip_v = true; break;                    // U:166-170
+    case 4: flip_v = true; break;                                   // U:171-175
+    case 5: transpose = true; break;                                // U:176-181
+    case 6: transpose = true; flip_v = true; break;                 // U:182-186
+    case 7: transpose = true; flip_u = true; flip_v = true; dy = dy - dh; break;  // U:187-192 (lands above the rect)
+    case 8: transpose = true; flip_u = true; break;                 // U:193-197
+    default: break;                                                 // U:155-159,198-199
+  }
+  p->X0 = dx * ss;
+  p->Y0 = dy * ss;
+  p->W = dw * ss;
+  p->H = dh * ss;
+  p->bw = bw;
+  p->bh = bh;
+  p->transpose = transpose ? 1 : 0;
+  if (transpose) {  // device x runs along bitmap y
+    p->sx_len = bh;
+    p->sy_len = bw;
+    p->flip_x = flip_v;
+    p->flip_y = flip_u;
+  } else {
+    p->sx_len = bw;
+    p->sy_len = bh;
+    p->flip_x = flip_u;
+    p->flip_y = flip_v;
+  }
+  auto lo = [](double v, int hi) { double f = std::floor(v); return (int)std::fmin(std::fmax(f, 0.0), (double)hi); };
+  auto hi = [](double v, int hi_) { double c = std::ceil(v); return (int)std::fmin(std::fmax(c, 0.0), (double)hi_); };
+  p->x_lo = lo(p->X0, cw);
+  p->x_hi = hi(p->X0 + p->W, cw);
+  p->y_lo = lo(p->Y0, ch);
+  p->y_hi = hi(p->Y0 + p->H, ch);
+  if (!(p->W > 0) || !(p->H > 0)) p->x_hi = p->x_lo;  // empty
+  p->pad = 0;
+}
+
+int ensure_stage(StitchCtx* ctx, size_t idx, size_t bytes) {
+  if (ctx->in_stage.size() <= idx) {
+    ctx->in_stage.resize(idx + 1, nullptr);
+    ctx->in_stage_cap.resize(idx + 1, 0);
+  }
+  if (ctx->in_stage_cap[idx] < bytes) {
+    if (ctx->in_stage[idx]) CUDA_TRY(ctx, cudaFree(ctx->in_stage[idx]));
+    ctx->in_stage[idx] = nullptr;
+    ctx->in_stage_cap[idx] = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->in_stage[idx], bytes));
+    ctx->in_stage_cap[idx] = bytes;
+  }
+  return STITCH_OK;
+}
+
+int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
+  if (!ctx || !job || !res) return fail(ctx, STITCH_E_BAD_ARG, "null argument");
+  if (job->n <= 0) return fail(ctx, STITCH_E_EMPTY, "empty image list");  // P:1189
+  if (!job->images) return fail(ctx, STITCH_E_BAD_ARG, "images == NULL");
+  if (job->n > STITCH_MAX_IMAGES) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int n = job->n;
+  std::memset(res, 0, sizeof(*res));
+
+  emit(ctx, 1);  // P:1193
+  int32_t seq[2 * STITCH_MAX_IMAGES + 4];
+  stitch_progress_sequence(n, seq, 2 * STITCH_MAX_IMAGES + 4);
+
+  // [1] per-image prepare check (P:1225-1249): here only the record normalisation survives.
+  StitchImageDesc descs[STITCH_MAX_IMAGES];
+  for (int i = 0; i < n; ++i) {
+    descs[i] = job->images[i].desc;
+    emit(ctx, seq[1 + i]);
+  }
+  // [2] layout (P:1251-1386)
+  int st = stitch_layout(descs, n, &job->params, &res->layout);
+  if (st != STITCH_OK) return fail(ctx, st, stitch_strerror(st));
+  emit(ctx, 30);  // P:1358
+  const StitchLayout& L = res->layout;
+  const int cw = (int)L.canvas_w, ch = (int)L.canvas_h;
+  res->canvas_w = cw;
+  res->canvas_h = ch;
+  stitch_output_size(&L, &res->rgba_bytes, &res->yuv_bytes);
+
+  int flags = job->output_flags ? job->output_flags : STITCH_OUT_RGBA;
+  const bool want_rgba = (flags & STITCH_OUT_RGBA) != 0, want_yuv = (flags & STITCH_OUT_YUV420) != 0;
+  // [3] surface (U:131-150, P:1388-1413): the caller's buffer is the canvas.
+  const int64_t rgba_pitch = job->out_rgba_pitch ? job->out_rgba_pitch : (int64_t)cw * 4;
+  if (want_rgba) {
+    if (!job->out_rgba || rgba_pitch < (int64_t)cw * 4 || (rgba_pitch & 3) ||
+        job->out_capacity_rgba < rgba_pitch * (int64_t)(ch - 1) + (int64_t)cw * 4)
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (RGBA output buffer missing or too small)");
+  }
+  if (want_yuv) {
+    if (!job->out_yuv || job->out_capacity_yuv < res->yuv_bytes)
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (YUV output buffer missing or too small)");
+  }
+
+  // bitmaps (P:1512-1514)
+  for (int i = 0; i < n; ++i) {
+    const StitchImage& im = job->images[i];
+    if (!im.data || im.bmp_width <= 0 || im.bmp_height <= 0) {
+      char buf[64];
+      std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
+      return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+    }
+    const int64_t pitch = im.pitch_bytes ? im.pitch_bytes : (int64_t)im.bmp_width * 4;
+    if (pitch < (int64_t)im.bmp_width * 4 || (pitch & 3)) return fail(ctx, STITCH_E_BAD_ARG, "bad bitmap pitch");
+  }
+
+  JobParam P;
+  std::memset(&P, 0, sizeof P);
+  P.n = n;
+  P.cw = cw;
+  P.ch = ch;
+  const double ss = (L.super_sample != 1.0) ? L.super_sample : 1.0;  // P:1426
+
+  // stage inputs
+  for (int i = 0; i < n; ++i) {
+    const StitchImage& im = job->images[i];
+    int64_t pitch = im.pitch_bytes ? im.pitch_bytes : (int64_t)im.bmp_width * 4;
+    const uint8_t* dptr = nullptr;
+    if (im.mem_kind == STITCH_MEM_DEVICE) {
+      dptr = (const uint8_t*)im.data;
+    } else {
+      // Host bitmap: stage with a 16B-aligned pitch so the streaming kernel's 128-bit loads apply.
+      const int64_t dpitch = ((int64_t)im.bmp_width * 4 + 15) & ~15LL;
+      st = ensure_stage(ctx, i, (size_t)(dpitch * im.bmp_height));
+      if (st != STITCH_OK) return st;
+      CUDA_TRY(ctx, cudaMemcpy2DAsync(ctx->in_stage[i], dpitch, im.data, pitch, (size_t)im.bmp_width * 4, im.bmp_height,
+                                      cudaMemcpyHostToDevice, ctx->stream));
+      dptr = (const uint8_t*)ctx->in_stage[i];
+      pitch = dpitch;
+    }
+    P.img[i].data = dptr;
+    P.img[i].pitch = pitch;
+    make_placement(L.rects[i], im.desc.orientation, ss, im.bmp_width, im.bmp_height, cw, ch, &P.img[i]);
+  }
+
+  // outputs
+  uint8_t* d_rgba = nullptr;
+  uint8_t* d_yuv = nullptr;
+  int64_t d_rgba_pitch = rgba_pitch;
+  const bool out_host = job->out_mem_kind != STITCH_MEM_DEVICE;
+  if (out_host) {
+    d_rgba_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
+    const size_t need_rgba = want_rgba ? (size_t)(d_rgba_pitch * ch) : 0;
+    const size_t need = need_rgba + (want_yuv ? (size_t)res->yuv_bytes : 0) + 256;
+    if (ctx->out_stage_cap < need) {
+      if (ctx->out_stage) CUDA_TRY(ctx, cudaFree(ctx->out_stage));
+      ctx->out_stage = nullptr;
+      ctx->out_stage_cap = 0;
+      cudaError_t e = cudaMalloc(&ctx->out_stage, need);
+      if (e != cudaSuccess) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (device canvas allocation failed)");
+      ctx->out_stage_cap = need;
+    }
+    if (want_rgba) d_rgba = (uint8_t*)ctx->out_stage;
+    if (want_yuv) d_yuv = (uint8_t*)ctx->out_stage + ((need_rgba + 255) & ~(size_t)255);
+  } else {
+    if (want_rgba) d_rgba = (uint8_t*)job->out_rgba;
+    if (want_yuv) d_yuv = (uint8_t*)job->out_yuv;
+  }
+  P.out_rgba = d_rgba;
+  P.out_pitch = d_rgba_pitch;
+  if (want_yuv) {
+    const int64_t cwh = (cw + 1) / 2, chh = (ch + 1) / 2;
+    P.out_y = d_yuv;
+    P.out_cb = d_yuv + (int64_t)cw * ch;
+    P.out_cr = P.out_cb + cwh * chh;
+  }
+
+  // [4] the draw loop (P:1439-1572) as fused launches
+  int launches = 0;
+  st = stitch::launch_job(P, want_yuv, ctx->sm_count, ctx->scratch, ctx->stream, &launches);
+  if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
+  ctx->launches += launches;
+  res->kernel_launches = launches;
+  for (int i = 0; i < n; ++i) emit(ctx, seq[2 + n + i]);  // P:1556-1557 (one fused launch covers all images)
+
+  // [5] export (U:205-242): the canvas is copied out whole, unscaled (P:1577-1579)
+  if (out_host) {
+    if (want_rgba)
+      CUDA_TRY(ctx, cudaMemcpy2DAsync(job->out_rgba, rgba_pitch, d_rgba, d_rgba_pitch, (size_t)cw * 4, ch,
+                                      cudaMemcpyDeviceToHost, ctx->stream));
+    if (want_yuv)
+      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  return STITCH_OK;
+}
+
+}  // namespace
+
+extern "C" int stitch_ctx_create(int32_t device, void* stream, StitchCtx** out) {
+  if (!out) return STITCH_E_BAD_ARG;
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || device < 0 || device >= count) return STITCH_E_CUDA;
+  if (cudaSetDevice(device) != cudaSuccess) return STITCH_E_CUDA;
+  StitchCtx* ctx = new StitchCtx();
+  ctx->device = device;
+  if (stream) {
+    ctx->stream = (cudaStream_t)stream;
+  } else {
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+      delete ctx;
+      return STITCH_E_CUDA;
+    }
+    ctx->own_stream = true;
+  }
+  cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+  *out = ctx;
+  return STITCH_OK;
+}
+
+extern "C" int stitch_ctx_destroy(StitchCtx* ctx) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto& p : ctx->pending) cudaEventDestroy(p.done);
+  for (void* p : ctx->in_stage)
+    if (p) cudaFree(p);
+  if (ctx->out_stage) cudaFree(ctx->out_stage);
+  stitch::free_scratch(ctx->scratch);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return STITCH_OK;
+}
+
+extern "C" void* stitch_ctx_stream(StitchCtx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+extern "C" int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  ctx->progress = fn;
+  ctx->progress_user = user;
+  return STITCH_OK;
+}
+
+extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "stitch already in progress");  // P:772,781
+  ctx->busy = true;
+  int st = enqueue_job(ctx, job, result);
+  if (st == STITCH_OK) {
+    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) st = fail(ctx, STITCH_E_CUDA, std::string("stream sync: ") + cudaGetErrorString(e));
+  }
+  if (st == STITCH_OK) {
+    emit(ctx, 96);   // P:1581
+    emit(ctx, 100);  // P:1611
+  } else if (st != STITCH_E_EMPTY) {
+    emit(ctx, 0);  // P:1622
+  }
+  ctx->busy = false;
+  return st;
+}
+
+extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {
+  if (!ctx || !ticket) return STITCH_E_BAD_ARG;
+  int st = enqueue_job(ctx, job, result);
+  if (st != STITCH_OK) return st;
+  PendingJob pj;
+  pj.ticket = ctx->next_ticket++;
+  pj.n = job->n;
+  CUDA_TRY(ctx, cudaEventCreateWithFlags(&pj.done, cudaEventDisableTiming));
+  CUDA_TRY(ctx, cudaEventRecord(pj.done, ctx->stream));
+  ctx->pending.push_back(pj);
+  *ticket = pj.ticket;
+  return STITCH_OK;
+}
+
+extern "C" int stitch_wait(StitchCtx* ctx, uint64_t ticket) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  // tickets complete in stream order: waiting for ticket T retires every earlier one too
+  while (!ctx->pending.empty() && ctx->pending.front().ticket <= ticket) {
+    PendingJob pj = ctx->pending.front();
+    ctx->pending.pop_front();
+    cudaError_t e = cudaEventSynchronize(pj.done);
+    cudaEventDestroy(pj.done);
+    if (e != cudaSuccess) return fail(ctx, STITCH_E_CUDA, std::string("event sync: ") + cudaGetErrorString(e));
+    emit(ctx, 96);
+    emit(ctx, 100);
+  }
+  return STITCH_OK;
+}
+
+extern "C" int stitch_host_alloc(size_t bytes, void** out) {
+  if (!out) return STITCH_E_BAD_ARG;
+  return cudaMallocHost(out, bytes) == cudaSuccess ? STITCH_OK : STITCH_E_CUDA;
+}
+extern "C" int stitch_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? STITCH_OK : STITCH_E_CUDA; }
+
+extern "C" int stitch_device_alloc(StitchCtx* ctx, size_t bytes, void** out) {
+  if (!ctx || !out) return STITCH_E_BAD_ARG;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaMalloc(out, bytes));
+  return STITCH_OK;
+}
+extern "C" int stitch_device_free(StitchCtx* ctx, void* p) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaFree(p));
+  return STITCH_OK;
+}
+extern "C" int stitch_memcpy_h2d(StitchCtx* ctx, void* dst, const void* src, size_t bytes) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return STITCH_OK;
+}
+extern "C" int stitch_memcpy_d2h(StitchCtx* ctx, void* dst, const void* src, size_t bytes) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return STITCH_OK;
+}
+
+extern "C" int stitch_generate_image(StitchCtx* ctx, void* dev_dst, int32_t width, int32_t height, int64_t pitch_bytes,
+                                     uint64_t seed, int32_t pattern) {
+  if (!ctx || !dev_dst || width <= 0 || height <= 0) return STITCH_E_BAD_ARG;
+  if (pitch_bytes == 0) pitch_bytes = (int64_t)width * 4;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  cudaError_t e = stitch::launch_generate((uint8_t*)dev_dst, width, height, pitch_bytes, seed, pattern, ctx->stream);
+  if (e != cudaSuccess) return fail(ctx, STITCH_E_CUDA, cudaGetErrorString(e));
+  ctx->launches += 1;
+  return STITCH_OK;
+}
+
+extern "C" const char* stitch_last_error(StitchCtx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+extern "C" int64_t stitch_kernel_launch_count(StitchCtx* ctx) { return ctx ? ctx->launches : 0; }

@@ -1,0 +1,363 @@
+"""Host-side mirror of the reference's stitch interface, on top of the C ABI.
+
+The reference (a WeChat Page, pages/index/index.js under
+/root/reference/miniprogram-stitch/miniprogram/) exposes the stitch path as page
+state + one method:
+    in : data.images[] ({naturalWidth,naturalHeight,width,height,orientation,fileSize,...},
+         index.js:724-739), data.direction ('vertical'|'horizontal', :16),
+         data.gap (:17), data.verticalStitchMode / horizontalStitchMode (:19-20),
+         platform + deviceMaxCanvasSize / deviceMaxCanvasPixels (:126-156)
+    out: data.stitchedTempPath, data.stitchProgress, data.isStitching (:1611)
+    fn : onStitchVertical / onStitchHorizontal -> onStitch (:771-788, :1186-1633)
+``StitchPage`` keeps those names, argument meanings and error behaviour;
+``stitch()`` / ``compute_layout()`` are the functional form the TypeScript facade
+(imagestitching_b200/ts/stitch.ts) also exposes.  Pixels come only from libstitch.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Any, Callable, Dict, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib as L
+
+_DIRECTIONS = {"vertical": L.VERTICAL, "horizontal": L.HORIZONTAL}
+_MODES = {"min": L.MODE_MIN, "max": L.MODE_MAX, "original": L.MODE_ORIGINAL}
+_PLATFORMS = {"ios": L.IOS, "android": L.ANDROID}
+
+# reference Error messages by status (index.js:1254,1320,1412,1513)
+_MESSAGES = {
+    L.E_BAD_DIMS: "图片尺寸不可用",
+    L.E_BAD_OUT: "输出尺寸计算失败",
+    L.E_NO_SURFACE: "无法获取绘图上下文",
+}
+
+
+class StitchError(Exception):
+    def __init__(self, status: int, message: str):
+        super().__init__(message)
+        self.status = status
+        self.message = message
+
+
+@dataclass
+class DeviceBitmap:
+    """An RGBA8 bitmap already resident in GPU memory (e.g. a torch tensor's data_ptr())."""
+    ptr: int
+    width: int
+    height: int
+    pitch: int = 0
+    keepalive: Any = None
+
+
+@dataclass
+class StitchOutput:
+    width: int
+    height: int
+    layout: Dict[str, Any]
+    rgba: Any = None          # numpy [h,w,4] (host) or device pointer int
+    y: Any = None
+    cb: Any = None
+    cr: Any = None
+    kernel_launches: int = 0
+    progress: List[int] = field(default_factory=list)
+
+
+def _profile_struct(platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
+                    deviceMaxCanvasPixels: Optional[int] = None, fallback: bool = True) -> L.StitchProfile:
+    """Profile as the page holds it after onLoad (index.js:342): stored values or the fallback."""
+    lib = L.load()
+    p = L.StitchProfile()
+    plat = _PLATFORMS.get(platform, L.OTHER)
+    if fallback:
+        lib.stitch_profile_preset(plat, C.byref(p))
+    p.platform = plat
+    if deviceMaxCanvasSize:
+        p.max_canvas_size = int(deviceMaxCanvasSize)
+        if not deviceMaxCanvasPixels and fallback:
+            # applyFallback() derives pixels from the stored size (index.js:131-137)
+            side = p.max_canvas_size
+            cap = side * min(side, 4096) if plat == L.ANDROID else side * min(side, 12288)
+            p.max_canvas_pixels = max(cap, 4096 * 2048)
+    if deviceMaxCanvasPixels:
+        p.max_canvas_pixels = int(deviceMaxCanvasPixels)
+    return p
+
+
+def _orientation_value(o: Any) -> int:
+    # utils/canvas.js:155-199: strict === against numbers 1..8; strings like 'up' draw plain
+    if isinstance(o, bool) or not isinstance(o, (int, float)):
+        return 0
+    return int(o) if float(o).is_integer() and 1 <= o <= 8 else 0
+
+
+def _desc(img: Dict[str, Any]) -> L.StitchImageDesc:
+    d = L.StitchImageDesc()
+    d.natural_width = int(img.get("naturalWidth") or 0)
+    d.natural_height = int(img.get("naturalHeight") or 0)
+    d.width = int(img.get("width") or 0)
+    d.height = int(img.get("height") or 0)
+    d.orientation = _orientation_value(img.get("orientation"))
+    d.file_size = int(img.get("fileSize") or 0)
+    return d
+
+
+def _params(direction: str, mode: Optional[str], gap, profile: L.StitchProfile) -> L.StitchParams:
+    p = L.StitchParams()
+    if direction not in _DIRECTIONS:
+        # index.js:1261: anything that is not 'vertical' takes the horizontal branch
+        p.direction = L.HORIZONTAL
+    else:
+        p.direction = _DIRECTIONS[direction]
+    mode = mode or "min"                       # index.js:1257
+    p.mode = _MODES.get(mode, L.MODE_OTHER)
+    try:
+        p.gap = float(gap or 0)                # index.js:1256
+    except (TypeError, ValueError):
+        p.gap = 0.0
+    p.profile = profile
+    return p
+
+
+def _layout_dict(lay: L.StitchLayout) -> Dict[str, Any]:
+    n = lay.n
+    return {
+        "n": n, "bigTask": bool(lay.big_task), "maxSide": lay.max_side, "maxPixels": lay.max_pixels,
+        "preW": lay.pre_w, "preH": lay.pre_h, "scaleDown": lay.scale_down,
+        "targetW": lay.target_w, "targetH": lay.target_h, "superSample": lay.super_sample,
+        "canvasW": lay.canvas_w, "canvasH": lay.canvas_h, "scaledGap": lay.scaled_gap,
+        "rects": [[lay.rects[i].dx, lay.rects[i].dy, lay.rects[i].dw, lay.rects[i].dh] for i in range(n)],
+        "natural": [[lay.natural_w[i], lay.natural_h[i]] for i in range(n)],
+    }
+
+
+def _raise(status: int, ctx=None):
+    lib = L.load()
+    msg = ""
+    if ctx:
+        msg = (lib.stitch_last_error(ctx) or b"").decode("utf-8", "replace")
+    if not msg:
+        msg = _MESSAGES.get(status) or (lib.stitch_strerror(status) or b"").decode("utf-8", "replace")
+    raise StitchError(status, msg)
+
+
+def compute_layout(images: Sequence[Dict[str, Any]], direction: str, mode: Optional[str] = "min", gap=0,
+                   platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
+                   deviceMaxCanvasPixels: Optional[int] = None) -> Dict[str, Any]:
+    """Exact twin of index.js:1251-1386 + 1522-1554 (CPU only; no GPU needed)."""
+    lib = L.load()
+    n = len(images)
+    descs = (L.StitchImageDesc * max(n, 1))(*[_desc(i) for i in images])
+    prm = _params(direction, mode, gap, _profile_struct(platform, deviceMaxCanvasSize, deviceMaxCanvasPixels))
+    lay = L.StitchLayout()
+    st = lib.stitch_layout(descs, n, C.byref(prm), C.byref(lay))
+    if st != L.OK:
+        _raise(st)
+    d = _layout_dict(lay)
+    seq = (C.c_int32 * 32)()
+    k = lib.stitch_progress_sequence(n, seq, 32)
+    d["progress"] = [seq[i] for i in range(k)]
+    return d
+
+
+class StitchContext:
+    """One per GPU: owns a StitchCtx (stream, staging).  Not thread-safe."""
+
+    def __init__(self, device: int = 0, stream: int = 0):
+        self.lib = L.load()
+        h = C.c_void_p()
+        st = self.lib.stitch_ctx_create(device, C.c_void_p(stream or None), C.byref(h))
+        if st != L.OK:
+            raise StitchError(st, "stitch_ctx_create failed (no usable CUDA device; there is no CPU fallback)")
+        self.handle = h
+        self.device = device
+        self._cb = None
+
+    def close(self):
+        if self.handle:
+            self.lib.stitch_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.stitch_ctx_stream(self.handle) or 0)
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.stitch_kernel_launch_count(self.handle))
+
+    # -- job construction ----------------------------------------------------
+    def build_job(self, images: Sequence[Dict[str, Any]], direction: str, mode: Optional[str], gap,
+                  profile: L.StitchProfile, output: str, out_device: bool = False, out_rgba_ptr: int = 0,
+                  out_yuv_ptr: int = 0, out_rgba_capacity: int = 0, out_yuv_capacity: int = 0):
+        n = len(images)
+        arr = (L.StitchImage * max(n, 1))()
+        keep = []
+        for i, img in enumerate(images):
+            arr[i].desc = _desc(img)
+            bmp = img.get("bitmap")
+            if isinstance(bmp, DeviceBitmap):
+                arr[i].data = bmp.ptr
+                arr[i].bmp_width, arr[i].bmp_height = bmp.width, bmp.height
+                arr[i].pitch_bytes = bmp.pitch
+                arr[i].mem_kind = L.MEM_DEVICE
+                keep.append(bmp)
+            elif bmp is not None:
+                a = np.asarray(bmp)
+                if a.dtype != np.uint8 or a.ndim != 3 or a.shape[2] != 4:
+                    raise StitchError(L.E_BAD_ARG, f"bitmap {i} must be uint8 [h,w,4] RGBA")
+                if a.strides[2] != 1 or a.strides[1] != 4:
+                    a = np.ascontiguousarray(a)
+                arr[i].data = a.ctypes.data if a.size else None
+                arr[i].bmp_height, arr[i].bmp_width = a.shape[0], a.shape[1]
+                arr[i].pitch_bytes = a.strides[0] if a.shape[0] > 1 else a.shape[1] * 4
+                arr[i].mem_kind = L.MEM_HOST
+                keep.append(a)
+        job = L.StitchJob()
+        job.images = arr
+        job.n = n
+        job.params = _params(direction, mode, gap, profile)
+        job.output_flags = {"rgba": L.OUT_RGBA, "yuv420": L.OUT_YUV420, "both": L.OUT_RGBA | L.OUT_YUV420}[output]
+        job.out_mem_kind = L.MEM_DEVICE if out_device else L.MEM_HOST
+        job.out_rgba = out_rgba_ptr or None
+        job.out_yuv = out_yuv_ptr or None
+        job.out_capacity_rgba = out_rgba_capacity
+        job.out_capacity_yuv = out_yuv_capacity
+        return job, (arr, keep)
+
+    def run(self, images: Sequence[Dict[str, Any]], direction: str, *, mode: Optional[str] = "min", gap=0,
+            platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
+            deviceMaxCanvasPixels: Optional[int] = None, output: str = "rgba",
+            on_progress: Optional[Callable[[int], None]] = None) -> Optional[StitchOutput]:
+        """Synchronous stitch with host outputs (numpy).  Returns None for an empty list (index.js:1189)."""
+        lib = self.lib
+        if not images:
+            return None
+        profile = _profile_struct(platform, deviceMaxCanvasSize, deviceMaxCanvasPixels)
+        # size the host output from the layout twin
+        descs = (L.StitchImageDesc * len(images))(*[_desc(i) for i in images])
+        prm = _params(direction, mode, gap, profile)
+        lay = L.StitchLayout()
+        st = lib.stitch_layout(descs, len(images), C.byref(prm), C.byref(lay))
+        if st != L.OK:
+            _raise(st)
+        rb, yb = C.c_int64(), C.c_int64()
+        lib.stitch_output_size(C.byref(lay), C.byref(rb), C.byref(yb))
+        cw, ch = int(lay.canvas_w), int(lay.canvas_h)
+        rgba = np.empty((ch, cw, 4), dtype=np.uint8) if output in ("rgba", "both") else None
+        yuv = np.empty(yb.value, dtype=np.uint8) if output in ("yuv420", "both") else None
+        job, keep = self.build_job(images, direction, mode, gap, profile, output, False,
+                                   rgba.ctypes.data if rgba is not None else 0,
+                                   yuv.ctypes.data if yuv is not None else 0,
+                                   rgba.nbytes if rgba is not None else 0, yuv.nbytes if yuv is not None else 0)
+        progress: List[int] = []
+
+        def _cb(_user, pct):
+            progress.append(int(pct))
+            if on_progress:
+                on_progress(int(pct))
+
+        cb = L.PROGRESS_FN(_cb)
+        lib.stitch_set_progress_cb(self.handle, cb, None)
+        res = L.StitchResult()
+        try:
+            st = lib.stitch_run(self.handle, C.byref(job), C.byref(res))
+        finally:
+            lib.stitch_set_progress_cb(self.handle, C.cast(None, L.PROGRESS_FN), None)
+        if st != L.OK:
+            _raise(st, self.handle)
+        out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, progress=progress)
+        out.rgba = rgba
+        if yuv is not None:
+            cwh, chh = (cw + 1) // 2, (ch + 1) // 2
+            out.y = yuv[: cw * ch].reshape(ch, cw)
+            out.cb = yuv[cw * ch: cw * ch + cwh * chh].reshape(chh, cwh)
+            out.cr = yuv[cw * ch + cwh * chh:].reshape(chh, cwh)
+        return out
+
+
+_default_ctx: Dict[int, StitchContext] = {}
+
+
+def stitch(images: Sequence[Dict[str, Any]], direction: str, *, device: int = 0, **kw) -> Optional[StitchOutput]:
+    """Functional entry: ordered image list + 'vertical'/'horizontal' in, exported buffer out."""
+    ctx = _default_ctx.get(device)
+    if ctx is None:
+        ctx = _default_ctx[device] = StitchContext(device)
+    return ctx.run(images, direction, **kw)
+
+
+class StitchPage:
+    """The stitch-relevant slice of the reference's Page object, same field and method names."""
+
+    MAX_IMAGES = 9  # index.js:311
+
+    def __init__(self, device: int = 0, platform: str = "ios", output: str = "rgba"):
+        self.data: Dict[str, Any] = {
+            "images": [], "direction": "vertical", "gap": 0,
+            "verticalStitchMode": "min", "horizontalStitchMode": "min",
+            "stitchedTempPath": "", "isStitching": False, "stitchProgress": 0,
+        }
+        self.platform = platform                     # wx.getSystemInfoSync().platform
+        self.deviceMaxCanvasSize: Optional[int] = None
+        self.deviceMaxCanvasPixels: Optional[int] = None
+        self.output = output
+        self.progressLog: List[int] = []
+        self.lastToast = ""
+        self.result: Optional[StitchOutput] = None
+        self._device = device
+        self._ctx: Optional[StitchContext] = None
+
+    def setData(self, d: Dict[str, Any]):
+        self.data.update(d)
+        if "stitchProgress" in d:
+            self.progressLog.append(d["stitchProgress"])
+
+    def onStitchVertical(self):                      # index.js:771-779
+        if self.data["isStitching"]:
+            return
+        if not self.data["images"]:
+            self.lastToast = "请先添加图片"
+            return
+        self.setData({"direction": "vertical"})
+        self.onStitch()
+
+    def onStitchHorizontal(self):                    # index.js:780-788
+        if self.data["isStitching"]:
+            return
+        if not self.data["images"]:
+            self.lastToast = "请先添加图片"
+            return
+        self.setData({"direction": "horizontal"})
+        self.onStitch()
+
+    def onStitch(self):                              # index.js:1186-1633
+        images = [dict(it) for it in (self.data["images"] or [])]
+        if not images:
+            return                                   # :1189
+        direction, gap = self.data["direction"], self.data["gap"]
+        self.progressLog = []
+        self.data.update({"isStitching": True, "stitchedTempPath": ""})
+        mode = (self.data["verticalStitchMode"] if direction == "vertical" else self.data["horizontalStitchMode"]) or "min"
+        try:
+            if self._ctx is None:
+                self._ctx = StitchContext(self._device)
+            out = self._ctx.run(images[: self.MAX_IMAGES] if len(images) <= self.MAX_IMAGES else images, direction,
+                                mode=mode, gap=gap, platform=self.platform,
+                                deviceMaxCanvasSize=self.deviceMaxCanvasSize,
+                                deviceMaxCanvasPixels=self.deviceMaxCanvasPixels, output=self.output,
+                                on_progress=lambda p: self.setData({"stitchProgress": p}) if p not in (100,) else None)
+            self.result = out
+            self.setData({"stitchedTempPath": f"mem://stitch/{id(out):x}", "stitchProgress": 100, "isStitching": False})  # :1611
+        except StitchError as err:                   # :1618-1624
+            self.lastToast = "拼图失败：" + err.message if err.message else "拼图失败"
+            self.progressLog = [p for p in self.progressLog if p != 0]
+            self.setData({"isStitching": False, "stitchProgress": 0})

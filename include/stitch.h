@@ -1,0 +1,180 @@
+/*
+ * libstitch.so -- C ABI of the B200-native stitch path.
+ *
+ * This is the drop-in boundary for ONE path of Iamctb/ImageStitching: the
+ * `onStitch()` pipeline of the WeChat page (layout -> per-image drawImage loop
+ * -> export).  The reference has no FFI of its own (it is a single JS Page), so
+ * every entry point cites the reference lines it replaces.  Reference paths are
+ * relative to /root/reference/miniprogram-stitch/miniprogram/ :
+ *     P = pages/index/index.js      U = utils/canvas.js
+ *
+ * Rules of the ABI: extern "C", plain pointers and sizes, caller owns every
+ * buffer it passes in, the library never frees caller memory, nothing throws
+ * across the boundary (all functions return a StitchStatus), a StitchCtx is
+ * bound to one GPU and is NOT thread-safe (use one ctx per thread/GPU).
+ * There is no CPU fallback: every pixel is produced by sm_100a kernels.
+ */
+#ifndef STITCH_H_
+#define STITCH_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define STITCH_ABI_VERSION 1
+#define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
+
+/* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
+typedef enum StitchStatus {
+  STITCH_OK = 0,
+  STITCH_E_EMPTY = 1,      /* P:1189  empty list -> silent return upstream          */
+  STITCH_E_BAD_DIMS = 2,   /* P:1254  '图片尺寸不可用'                               */
+  STITCH_E_BAD_OUT = 3,    /* P:1320  '输出尺寸计算失败'                             */
+  STITCH_E_NO_SURFACE = 4, /* P:1412  '无法获取绘图上下文' == canvas alloc failure    */
+  STITCH_E_BAD_IMAGE = 5,  /* P:1513  '图片${idx}解码异常' == null/zero-size bitmap   */
+  STITCH_E_TOO_MANY = 6,   /* P:1081-1091 intake caps the list at MAX_IMAGES        */
+  STITCH_E_BAD_ARG = 7,    /* null pointer / unknown enum value at the ABI itself   */
+  STITCH_E_CUDA = 8,       /* CUDA runtime error; text via stitch_last_error()      */
+  STITCH_E_BUSY = 9        /* P:772,781 isStitching re-entrancy guard               */
+} StitchStatus;
+
+typedef enum StitchDirection { STITCH_VERTICAL = 0, STITCH_HORIZONTAL = 1 } StitchDirection; /* P:16,777,786 */
+/* P:19-20; any string other than 'min'/'max' behaves as STITCH_MODE_OTHER (P:1280,1307 vs P:1527,1541) */
+typedef enum StitchMode { STITCH_MODE_MIN = 0, STITCH_MODE_MAX = 1, STITCH_MODE_ORIGINAL = 2, STITCH_MODE_OTHER = 3 } StitchMode;
+typedef enum StitchPlatform { STITCH_IOS = 0, STITCH_ANDROID = 1, STITCH_OTHER = 2 } StitchPlatform; /* wx.getSystemInfoSync().platform, P:1324 */
+
+/* Device canvas-limit profile: this.deviceMaxCanvasSize / deviceMaxCanvasPixels (P:126-156).
+ * 0 means "unset" (JS falsy) and takes the reference's `||` fallbacks (P:1325-1336). */
+typedef struct StitchProfile {
+  int32_t platform;           /* StitchPlatform */
+  int32_t max_canvas_size;    /* 0 = unset */
+  int64_t max_canvas_pixels;  /* 0 = unset */
+} StitchProfile;
+
+/* Fills the reference's fallback profile for a platform (P:128-138). */
+int stitch_profile_preset(int32_t platform, StitchProfile* out);
+
+/* The fields of the prepared-image record the layout reads (P:724-739). 0 = missing (JS falsy). */
+typedef struct StitchImageDesc {
+  int32_t natural_width, natural_height; /* naturalWidth / naturalHeight */
+  int32_t width, height;                 /* width / height (fallbacks, P:1243-1244) */
+  int32_t orientation;                   /* numeric EXIF 1..8; anything else draws plain (U:155,198) */
+  int32_t reserved;
+  int64_t file_size;                     /* fileSize, feeds bigTask (P:1211-1212) */
+} StitchImageDesc;
+
+typedef struct StitchParams {
+  int32_t direction;     /* StitchDirection */
+  int32_t mode;          /* StitchMode: verticalStitchMode / horizontalStitchMode (P:1257) */
+  double gap;            /* this.data.gap (P:1187,1256); UI clamps to 0..20 (P:825,852) */
+  StitchProfile profile;
+} StitchParams;
+
+typedef struct StitchRect { double dx, dy, dw, dh; } StitchRect; /* user-space drawImage dest rect (P:1526-1554) */
+
+/* Everything P:1251-1386 + P:1432-1554 computes, as IEEE doubles exactly as the JS holds them. */
+typedef struct StitchLayout {
+  int32_t n;
+  int32_t big_task;                 /* P:1212 */
+  double max_side, max_pixels;      /* MAX_CANVAS_SIDE, MAX_TOTAL_PIXELS (P:1325-1336) */
+  double pre_w, pre_h;              /* outW/outH after Math.round, before clamp (P:1318-1319) */
+  double scale_down;                /* P:1337-1349 */
+  double target_w, target_h;        /* P:1352-1353,1360-1361 */
+  double super_sample;              /* P:1364-1383 */
+  double canvas_w, canvas_h;        /* canvasOutW/H (P:1373-1383) */
+  double scaled_gap;                /* P:1432 */
+  StitchRect rects[STITCH_MAX_IMAGES];
+  int32_t natural_w[STITCH_MAX_IMAGES], natural_h[STITCH_MAX_IMAGES]; /* P:1522-1523 */
+} StitchLayout;
+
+/* Pure CPU, no CUDA: bit-exact twin of P:1211-1213,1243-1386,1432-1433,1522-1554. */
+int stitch_layout(const StitchImageDesc* images, int32_t n, const StitchParams* params, StitchLayout* out);
+
+/* stitchProgress values of a successful run (P:1193,1247,1358,1556-1557,1581,1611).
+ * Writes up to cap values, returns how many the sequence has (2n+4). */
+int stitch_progress_sequence(int32_t n, int32_t* out, int32_t cap);
+
+/* ---- execution ---- */
+typedef struct StitchCtx StitchCtx;
+
+/* One ctx per GPU (replaces the page's canvas node + OffscreenCanvas, U:131-150).
+ * `stream` is a cudaStream_t the ctx should launch on, or NULL to create its own. */
+int stitch_ctx_create(int32_t device, void* stream, StitchCtx** out);
+int stitch_ctx_destroy(StitchCtx* ctx);
+void* stitch_ctx_stream(StitchCtx* ctx); /* the cudaStream_t kernels are launched on */
+
+/* Progress callback == this.setData({stitchProgress}) (values of stitch_progress_sequence);
+ * invoked on the calling thread inside stitch_run/stitch_wait. */
+typedef void (*StitchProgressFn)(void* user, int32_t percent);
+int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
+
+typedef enum StitchMemKind { STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1 } StitchMemKind;
+typedef enum StitchOutputFlags { STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2 } StitchOutputFlags;
+
+/* A decoded bitmap (what loadImageFrom hands to drawWithOrientation, P:1445-1463,1532):
+ * RGBA8, straight (non-premultiplied) alpha, row pitch in bytes (>= 4*bmp_width). */
+typedef struct StitchImage {
+  StitchImageDesc desc;
+  const void* data;       /* NULL -> STITCH_E_BAD_IMAGE (P:1512-1514) */
+  int32_t bmp_width, bmp_height; /* bmp.width / bmp.height; 0 -> STITCH_E_BAD_IMAGE */
+  int64_t pitch_bytes;    /* 0 = tightly packed */
+  int32_t mem_kind;       /* StitchMemKind */
+  int32_t reserved;
+} StitchImage;
+
+typedef struct StitchJob {
+  const StitchImage* images;
+  int32_t n;
+  StitchParams params;
+  int32_t output_flags;   /* StitchOutputFlags bitmask; 0 == STITCH_OUT_RGBA */
+  int32_t out_mem_kind;   /* where out_rgba / out_yuv live */
+  void* out_rgba;         /* canvas_w*canvas_h*4 bytes (pitch = out_rgba_pitch or 4*canvas_w); may be NULL if not requested */
+  int64_t out_rgba_pitch;
+  void* out_yuv;          /* planar I420: Y[h][w], Cb[ceil(h/2)][ceil(w/2)], Cr[...]; tightly packed */
+  int64_t out_capacity_rgba, out_capacity_yuv; /* bytes available; too small -> STITCH_E_NO_SURFACE */
+} StitchJob;
+
+typedef struct StitchResult {
+  StitchLayout layout;
+  int32_t canvas_w, canvas_h;
+  int64_t rgba_bytes, yuv_bytes;
+  int32_t kernel_launches;    /* kernels launched for this job */
+  int32_t reserved;
+} StitchResult;
+
+/* Required output sizes for a layout (export region == whole canvas, U:206-209, P:1577-1579). */
+int stitch_output_size(const StitchLayout* layout, int64_t* rgba_bytes, int64_t* yuv_bytes);
+
+/* Synchronous onStitch(): layout -> draw all images -> export into the caller's buffer. (P:1186-1633) */
+int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
+
+/* Asynchronous form for job-level sharding: enqueue on the ctx stream, wait later.
+ * Buffers must stay valid until stitch_wait(ticket) returns. */
+int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket);
+int stitch_wait(StitchCtx* ctx, uint64_t ticket);
+
+/* Pinned host / device buffers for callers without a CUDA runtime of their own (e.g. the N-API shim). */
+int stitch_host_alloc(size_t bytes, void** out);
+int stitch_host_free(void* p);
+int stitch_device_alloc(StitchCtx* ctx, size_t bytes, void** out);
+int stitch_device_free(StitchCtx* ctx, void* p);
+int stitch_memcpy_h2d(StitchCtx* ctx, void* dst, const void* src, size_t bytes); /* synchronous */
+int stitch_memcpy_d2h(StitchCtx* ctx, void* dst, const void* src, size_t bytes); /* synchronous */
+
+/* On-device synthetic bitmap generator (test/bench helper K0). */
+int stitch_generate_image(StitchCtx* ctx, void* dev_dst, int32_t width, int32_t height, int64_t pitch_bytes,
+                          uint64_t seed, int32_t pattern);
+
+const char* stitch_strerror(int status);
+const char* stitch_last_error(StitchCtx* ctx);
+int stitch_abi_version(void);
+/* Number of CUDA kernels this ctx has launched since creation (for bench accounting). */
+int64_t stitch_kernel_launch_count(StitchCtx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STITCH_H_ */
