@@ -58,7 +58,7 @@ class StitchJob(C.Structure):
 
 class StitchResult(C.Structure):
     _fields_ = [("layout", StitchLayout), ("canvas_w", C.c_int32), ("canvas_h", C.c_int32), ("rgba_bytes", C.c_int64),
-                ("yuv_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("reserved", C.c_int32)]
+                ("yuv_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("path_info", C.c_int32)]
 
 
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
@@ -89,7 +89,7 @@ SIGNATURES = {
     "stitch_kernel_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstitch.so")
+LIB_PATH = os.environ.get("STITCH_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstitch.so")
 _lib = None
 
 

@@ -1,0 +1,168 @@
+// Host side of the draw loop: partition the canvas into regions (stitch_plan.h) and launch.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <vector>
+
+#include "compose_kernel.cuh"
+#include "gather_kernel.cuh"
+#include "stitch_plan.h"
+
+namespace stitch {
+
+struct StreamScratch {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+inline void free_scratch(StreamScratch& s) {
+  if (s.p) cudaFree(s.p);
+  s.p = nullptr;
+  s.cap = 0;
+}
+
+inline bool is_int(double v) { return std::floor(v) == v && std::fabs(v) < 1e9; }
+
+inline bool stream_eligible(const ImgParam& im) {
+  if (im.transpose) return false;
+  const int64_t dw = (int64_t)im.W, dh = (int64_t)im.H;
+  if (!(im.sx_len > dw && im.sy_len > dh)) return false;       // area filter on both axes
+  if ((int64_t)im.sx_len > 4 * dw) return false;               // one-hop neighbour exchange needs ratio_x <= 4
+  if (((uintptr_t)im.data & 15) || (im.pitch & 15)) return false;  // 128-bit row loads
+  if ((int64_t)im.sx_len * dw >= (1LL << 40) || (int64_t)im.sy_len * dh >= (1LL << 40)) return false;
+  // at least one output row must fit the per-warp row table
+  if (im.sy_len / dh + 4 > STREAM_TAB_MAX) return false;
+  return true;
+}
+
+// Returns true and fills `plan` when the fused compose launch applies to this job: every device
+// rect integer-aligned (superSample == 1 and gap*scaleDown integral, true for BASELINE configs 2-5)
+// and the clipped rects pairwise disjoint, so painter's-order source-over degenerates to each
+// pixel belonging to at most one image.
+inline bool build_plan(const JobParam& P, Plan* plan) {
+  struct Box { int x0, y0, x1, y1, img; };
+  std::vector<Box> boxes;
+  for (int k = 0; k < P.n; ++k) {
+    const ImgParam& im = P.img[k];
+    if (!is_int(im.X0) || !is_int(im.Y0) || !is_int(im.W) || !is_int(im.H)) return false;
+    if (im.x_hi <= im.x_lo || im.y_hi <= im.y_lo) continue;  // nothing visible
+    boxes.push_back({im.x_lo, im.y_lo, im.x_hi, im.y_hi, k});
+  }
+  for (size_t a = 0; a < boxes.size(); ++a)
+    for (size_t b = a + 1; b < boxes.size(); ++b)
+      if (boxes[a].x0 < boxes[b].x1 && boxes[b].x0 < boxes[a].x1 && boxes[a].y0 < boxes[b].y1 && boxes[b].y0 < boxes[a].y1)
+        return false;
+
+  std::vector<Region> regs;
+  // heavy first: streaming regions, then gather, then fill
+  for (int pass = 0; pass < 2; ++pass) {
+    for (const Box& bx : boxes) {
+      const ImgParam& im = P.img[bx.img];
+      const bool se = stream_eligible(im);
+      if ((pass == 0) != se) continue;
+      Region r{};
+      r.img = bx.img;
+      if (se) {
+        const int dw = (int)im.W, dh = (int)im.H, X0 = (int)im.X0, Y0 = (int)im.Y0;
+        int rx0 = bx.x0 - X0, rx1 = bx.x1 - X0, ry0 = bx.y0 - Y0, ry1 = bx.y1 - Y0;  // device-relative
+        if (im.flip_x) { int t = dw - rx1; rx1 = dw - rx0; rx0 = t; }
+        if (im.flip_y) { int t = dh - ry1; ry1 = dh - ry0; ry0 = t; }
+        r.kind = REGION_STREAM;
+        r.x0 = rx0; r.x1 = rx1; r.y0 = ry0; r.y1 = ry1;
+        int tw = (int)((124LL * dw) / im.sx_len);
+        if (tw < 1) tw = 1;
+        const int nx = (rx1 - rx0 + tw - 1) / tw;
+        r.tile_w = (rx1 - rx0 + nx - 1) / nx;     // balance the last column
+        int th = (int)(((int64_t)(STREAM_TAB_MAX - 4) * dh) / im.sy_len);
+        th = std::max(1, std::min(th, 48));
+        r.tile_h = th;
+        r.maxo = (int)((4LL * dw + im.sx_len - 1) / im.sx_len);
+        r.maxo = std::max(2, std::min(r.maxo, 4));
+      } else {
+        r.kind = REGION_GATHER;
+        r.x0 = bx.x0; r.x1 = bx.x1; r.y0 = bx.y0; r.y1 = bx.y1;
+        r.tile_w = 32;
+        r.tile_h = 8;
+      }
+      regs.push_back(r);
+    }
+  }
+  // white background = complement of the boxes: sweep horizontal bands between all y edges
+  std::vector<int> ys{0, P.ch};
+  for (const Box& b : boxes) { ys.push_back(b.y0); ys.push_back(b.y1); }
+  std::sort(ys.begin(), ys.end());
+  ys.erase(std::unique(ys.begin(), ys.end()), ys.end());
+  std::vector<Region> fills;
+  for (size_t i = 0; i + 1 < ys.size(); ++i) {
+    const int ya = ys[i], yb = ys[i + 1];
+    if (ya < 0 || yb > P.ch || ya >= yb) continue;
+    std::vector<std::pair<int, int>> spans;
+    for (const Box& b : boxes)
+      if (b.y0 <= ya && b.y1 >= yb) spans.push_back({b.x0, b.x1});
+    std::sort(spans.begin(), spans.end());
+    int x = 0;
+    auto add = [&](int xa, int xb) {
+      if (xa >= xb) return;
+      // merge with a fill of identical x-range that ends where this band starts
+      for (Region& f : fills)
+        if (f.x0 == xa && f.x1 == xb && f.y1 == ya) { f.y1 = yb; return; }
+      Region r{};
+      r.kind = REGION_FILL; r.img = -1;
+      r.x0 = xa; r.x1 = xb; r.y0 = ya; r.y1 = yb;
+      r.tile_w = 256; r.tile_h = 8;
+      fills.push_back(r);
+    };
+    for (auto& s : spans) { add(x, s.first); x = std::max(x, s.second); }
+    add(x, P.cw);
+  }
+  for (Region& f : fills) regs.push_back(f);
+  if (regs.size() > STITCH_MAX_REGIONS) return false;
+  int unit = 0;
+  plan->n_regions = (int)regs.size();
+  for (size_t i = 0; i < regs.size(); ++i) {
+    Region& r = regs[i];
+    r.tiles_x = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
+    r.tiles_y = (r.y1 - r.y0 + r.tile_h - 1) / r.tile_h;
+    r.first_unit = unit;
+    unit += r.tiles_x * r.tiles_y;
+    plan->r[i] = r;
+  }
+  plan->n_units = unit;
+  return unit > 0;
+}
+
+inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScratch& scratch, cudaStream_t stream,
+                      int* launches, int* path_info) {
+  (void)sm_count;
+  (void)scratch;
+  *launches = 0;
+  *path_info = 1 << 24;
+  if (want_yuv) {
+    dim3 grid(((P.cw + 1) / 2 + 31) / 32, ((P.ch + 1) / 2 + 7) / 8);
+    gather_yuv_kernel<<<grid, 256, 0, stream>>>(P);
+    *launches = 1;
+    return (int)cudaGetLastError();
+  }
+  Plan plan;
+  if (build_plan(P, &plan)) {
+    const int grid = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
+    int maxo = 2, cnt[3] = {0, 0, 0};
+    for (int i = 0; i < plan.n_regions; ++i) {
+      if (plan.r[i].kind == REGION_STREAM) maxo = std::max(maxo, plan.r[i].maxo);
+      cnt[plan.r[i].kind]++;
+    }
+    *path_info = cnt[REGION_STREAM] | (cnt[REGION_GATHER] << 8) | (cnt[REGION_FILL] << 16);
+    if (maxo <= 2) compose_kernel<2><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan);
+    else if (maxo == 3) compose_kernel<3><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan);
+    else compose_kernel<4><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan);
+  } else {
+    dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
+    gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
+  }
+  *launches = 1;
+  return (int)cudaGetLastError();
+}
+
+}  // namespace stitch

@@ -19,7 +19,8 @@
 #include "gather_kernel.cuh"
 #include "stitch.h"
 #include "stitch_plan.h"
-#include "stream_kernel.cuh"
+#include "launch.cuh"
+#include "synth.cuh"
 
 struct PendingJob {
   uint64_t ticket;
@@ -242,7 +243,9 @@ int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
 
   // [4] the draw loop (P:1439-1572) as fused launches
   int launches = 0;
-  st = stitch::launch_job(P, want_yuv, ctx->sm_count, ctx->scratch, ctx->stream, &launches);
+  int path_info = 0;
+  st = stitch::launch_job(P, want_yuv, ctx->sm_count, ctx->scratch, ctx->stream, &launches, &path_info);
+  res->path_info = path_info;
   if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
   ctx->launches += launches;
   res->kernel_launches = launches;

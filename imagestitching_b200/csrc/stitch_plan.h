@@ -30,3 +30,31 @@ struct JobParam {
   uint8_t* out_cb;
   uint8_t* out_cr;
 };
+
+// ---- fused compose launch: the canvas is partitioned into regions, each region into warp units ----
+enum RegionKind : int32_t {
+  REGION_STREAM = 0,  // integer-aligned area downscale of one image: streaming kernel
+  REGION_FILL = 1,    // white background (P:1423-1424) where no image lands
+  REGION_GATHER = 2   // anything else inside one image's bounding box: per-pixel gather
+};
+
+struct Region {
+  int32_t kind, img;
+  // STREAM: source-order output index ranges [x0,x1) x [y0,y1) inside the image's device rect
+  // FILL/GATHER: device pixel rect
+  int32_t x0, y0, x1, y1;
+  int32_t tile_w, tile_h;    // warp-unit size (output pixels)
+  int32_t tiles_x, tiles_y;  // warp-unit grid
+  int32_t first_unit;
+  int32_t maxo;              // STREAM: max outputs starting inside one 4-pixel source group
+};
+
+#define STITCH_MAX_REGIONS 64
+#define STREAM_TAB_MAX 288   // row-table entries per warp
+#define STREAM_WARPS 8
+
+struct Plan {
+  Region r[STITCH_MAX_REGIONS];
+  int32_t n_regions;
+  int32_t n_units;
+};

@@ -1,23 +1,11 @@
-// Job launcher + synthetic-bitmap generator.  (Streaming downscale kernel: see below.)
+// K0: on-device synthetic bitmaps (test / bench helper).  Integer-only so the
+// tests can reproduce it exactly on the CPU (tests/util.py synth_image).
 #pragma once
 #include <cuda_runtime.h>
 
 #include <cstdint>
 
-#include "gather_kernel.cuh"
-#include "stitch_plan.h"
-
 namespace stitch {
-
-struct StreamScratch {
-  void* p = nullptr;
-  size_t cap = 0;
-};
-inline void free_scratch(StreamScratch& s) {
-  if (s.p) cudaFree(s.p);
-  s.p = nullptr;
-  s.cap = 0;
-}
 
 // ---- K0: on-device synthetic bitmaps (integer-only so tests/oracle can reproduce it exactly) ----
 __host__ __device__ inline uint64_t splitmix64(uint64_t x) {
@@ -72,23 +60,6 @@ inline cudaError_t launch_generate(uint8_t* dst, int width, int height, int64_t 
   dim3 grid((width + 255) / 256, height);
   generate_kernel<<<grid, 256, 0, stream>>>(dst, width, height, pitch, seed, pattern);
   return cudaGetLastError();
-}
-
-// ---- job launch ----
-inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScratch& scratch, cudaStream_t stream,
-                      int* launches) {
-  (void)sm_count;
-  (void)scratch;
-  *launches = 0;
-  if (want_yuv) {
-    dim3 grid(((P.cw + 1) / 2 + 31) / 32, ((P.ch + 1) / 2 + 7) / 8);
-    gather_yuv_kernel<<<grid, 256, 0, stream>>>(P);
-  } else {
-    dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
-    gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
-  }
-  *launches = 1;
-  return (int)cudaGetLastError();
 }
 
 }  // namespace stitch

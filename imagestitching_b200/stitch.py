@@ -62,6 +62,7 @@ class StitchOutput:
     cb: Any = None
     cr: Any = None
     kernel_launches: int = 0
+    path_info: int = 0
     progress: List[int] = field(default_factory=list)
 
 
@@ -274,7 +275,7 @@ class StitchContext:
             lib.stitch_set_progress_cb(self.handle, C.cast(None, L.PROGRESS_FN), None)
         if st != L.OK:
             _raise(st, self.handle)
-        out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, progress=progress)
+        out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, path_info=res.path_info, progress=progress)
         out.rgba = rgba
         if yuv is not None:
             cwh, chh = (cw + 1) // 2, (ch + 1) // 2

@@ -142,7 +142,8 @@ typedef struct StitchResult {
   int32_t canvas_w, canvas_h;
   int64_t rgba_bytes, yuv_bytes;
   int32_t kernel_launches;    /* kernels launched for this job */
-  int32_t reserved;
+  int32_t path_info;          /* diagnostics: bits 0-7 streaming regions, 8-15 gather regions, 16-23 fill
+                                 regions of the fused compose launch; bit 24 = whole-canvas gather launch */
 } StitchResult;
 
 /* Required output sizes for a layout (export region == whole canvas, U:206-209, P:1577-1579). */

@@ -33,7 +33,7 @@ def _run_and_check(ctx, dims, bitmaps, direction, mode, gap, platform="ios", siz
                    output="rgba", use_numpy=False, file_sizes=None):
     prof = U.profile_of(platform, size, pixels)
     lay, want = U.oracle_render(dims, bitmaps, direction, mode, gap, prof, orientations, yuv=(output != "rgba"),
-                                use_numpy=use_numpy)
+                                use_numpy=use_numpy, file_sizes=file_sizes)
     got = ctx.run(U.page_images(dims, bitmaps, orientations, file_sizes), direction, mode=mode, gap=gap,
                   platform=platform, deviceMaxCanvasSize=size or None, deviceMaxCanvasPixels=pixels or None,
                   output=output)

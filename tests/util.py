@@ -75,9 +75,10 @@ def profile_of(platform="ios", size=0, pixels=0) -> LR.Profile:
     return LR.Profile(platform, size or 0, pixels or 0).with_fallback()
 
 
-def oracle_render(dims, bitmaps, direction, mode, gap, profile, orientations=None, yuv=False, use_numpy=False):
+def oracle_render(dims, bitmaps, direction, mode, gap, profile, orientations=None, yuv=False, use_numpy=False,
+                  file_sizes=None):
     orientations = orientations or [1] * len(dims)
-    L = LR.compute_layout(recs(dims, orientations), direction, mode, gap, profile)
+    L = LR.compute_layout(recs(dims, orientations, file_sizes), direction, mode, gap, profile)
     if use_numpy:
         out = {"rgba": RR.render_rgba(L, bitmaps, orientations)}
         if yuv:
