@@ -1,22 +1,26 @@
 // Fused resample + compose kernel (K1): ONE launch draws every image of a job into the canvas.
 //
 // Replaces the per-image ctx.drawImage loop (P:1439-1572 -> U:153-202) and the canvas
-// pre-fill (P:1423-1424).  The canvas is partitioned on the host (plan.h) into regions,
-// every region into warp-sized units; each warp of the grid executes one unit:
+// pre-fill (P:1423-1424).  The canvas is partitioned on the host (launch.cuh) into regions,
+// every region into warp-sized units; a persistent grid of warps pulls units from an atomic
+// counter (heavy units first) until none are left:
 //
 //   REGION_STREAM  integer-aligned area downscale (1 < ratio_x <= 4, ratio_y > 1), EXIF 1-4.
-//       The bandwidth path.  A warp owns a band of <=31 source groups (4 px = 16 B each) and
-//       streams DOWN the source rows with one coalesced 128-bit load per lane per row
-//       (register prefetch ring, no shared-memory staging of pixels).  Vertical area weights
-//       are warp-uniform (row table in smem); the horizontal pass runs in registers when an
-//       output row completes: each lane reduces its 4 columns into the <=MAXO outputs that
-//       start in its group plus the tail of its left neighbour's last output, which travels
-//       by one shuffle.  Every source byte is loaded exactly once per warp.
-//       Arithmetic: a byte b is expanded with ONE PRMT to the float 1 + b*2^-15
-//       (0x3F80bb00); because the filter weights sum to 1 the accumulators stay in that
-//       form, and one FFMA.RM against 2^23 - 2^15 + 0.5 leaves floor(value + 0.5) in the
-//       low mantissa byte.  Resolution of the form is 2^-8 LSB per rounding.
-//       Pixels whose filtered alpha is not 255 fall back to the exact gather path.
+//       The bandwidth path.  A warp owns a band of <=32 source groups (4 px = 16 B each) and
+//       streams DOWN the source rows.  Row segments (<=512 B) are staged into a per-warp
+//       shared-memory ring by the bulk-copy engine (cp.async.bulk + mbarrier complete_tx, one
+//       elected lane issues), STREAM_NST rows deep, so the bytes in flight do not cost
+//       registers; each lane then reads its own 16 B (conflict-free LDS.128).
+//       Vertical area weights are warp-uniform (row table in smem); the horizontal pass runs in
+//       registers when an output row completes: each lane reduces its 4 columns into the
+//       <=MAXO outputs that start in its group plus the tail of its left neighbour's last
+//       output, which travels by one shuffle.  Every source byte is fetched once per warp.
+//       Arithmetic: a byte b is expanded with ONE PRMT to the float 1 + b*2^-15 (0x3F80bb00);
+//       because the filter weights sum to 1 the accumulators stay in that form, and one
+//       FFMA.RM against 2^23 - 2^15 + 0.5 leaves floor(value + 0.5) in the low mantissa byte.
+//       Resolution of the form is 2^-8 LSB per rounding.  Alpha is not filtered: the pixels are
+//       ANDed together and a unit that saw any alpha != 255 is redone by the exact
+//       premultiplied gather path (photos are opaque, so this is the rare case).
 //   REGION_FILL    white.
 //   REGION_GATHER  per-pixel evaluation (gather_kernel.cuh shade()) for upscale / EXIF 5-8 /
 //       ratios outside the streaming range.
@@ -30,19 +34,47 @@
 
 namespace stitch {
 
-#ifndef STREAM_NPF
-#define STREAM_NPF 4  // rows of prefetch per lane
+#ifndef STREAM_NST
+#define STREAM_NST 8  // ring depth: source rows in flight per warp
 #endif
 #ifndef STREAM_MINB
-#define STREAM_MINB 2  // resident CTAs per SM the register allocation targets
+#define STREAM_MINB 3  // resident CTAs per SM the register allocation targets
 #endif
+#define STREAM_STAGE_BYTES 512
 
-__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
-  uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(p));
-  return r;
+struct WarpSmem {
+  alignas(128) uint8_t ring[STREAM_NST][STREAM_STAGE_BYTES];
+  alignas(8) unsigned long long bar[STREAM_NST];
+  alignas(8) float2 tab[STREAM_TAB_MAX];
+};
+static constexpr int kComposeSmemBytes = (int)sizeof(WarpSmem) * STREAM_WARPS;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy (TMA engine, UBLKCP); completion is signalled on the mbarrier.
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
 }
 
 // byte ch of px -> float 1 + b * 2^-15
@@ -59,10 +91,21 @@ __device__ __noinline__ uint32_t shade_px(const JobParam& P, int x, int y) {
   return q8(Rr) | (q8(Gg) << 8) | (q8(Bb) << 16) | 0xff000000u;
 }
 
-__device__ __forceinline__ int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+// floor(n / d) for 0 <= n < 2^52, d > 0: one fp64 divide plus an exact fix-up (cheaper than the
+// 64-bit integer division sequence).
+__device__ __forceinline__ int64_t floor_div(int64_t n, int64_t d) {
+  int64_t q = (int64_t)floor((double)n / (double)d);
+  if (q * d > n) --q;
+  if ((q + 1) * d <= n) ++q;
+  return q;
+}
+__device__ __forceinline__ int64_t ceil_div(int64_t n, int64_t d) { return floor_div(n + d - 1, d); }
 
+// `it` counts the rows this warp has pushed through its ring since kernel start (stage = it % NST,
+// mbarrier parity = (it / NST) & 1), so the ring carries over from unit to unit.
 template <int MAXO>
-__device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, int tx, int ty, float2* tab, int lane) {
+__device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, int tx, int ty, WarpSmem& ws, int lane,
+                                            uint32_t& it) {
   const ImgParam& im = P.img[R.img];
   const int sw = im.sx_len, sh = im.sy_len;
   const int dw = (int)im.W, dh = (int)im.H;
@@ -72,36 +115,36 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   const float inv_sw = 1.0f / (float)sw, inv_sh = 1.0f / (float)sh;
 
   // ---- vertical: source rows [rs, re) and the warp's row table ----
-  const int rs = (int)(((int64_t)oy0 * sh) / dh);
-  const int re = (int)min((int64_t)sh, ceil_div64((int64_t)oy1 * sh, dh));
+  const int rs = (int)floor_div((int64_t)oy0 * sh, dh);
+  const int re = (int)min((int64_t)sh, ceil_div((int64_t)oy1 * sh, dh));
   const int nrows = re - rs;
+  float2* tab = ws.tab;
   for (int k = lane; k < nrows; k += 32) {
     const int64_t i = rs + k;
-    const int64_t lo = i * dh, hi = lo + dh;          // row i in units of 1/dh ... scaled by dh*sh
-    const int64_t Ya = lo / sh;                        // output row containing the start of row i
+    const int64_t lo = i * dh, hi = lo + dh;           // row i, in source units scaled by dh
+    const int64_t Ya = floor_div(lo, sh);              // output row containing the start of row i
     const int64_t E = (Ya + 1) * sh;                   // where output row Ya ends
     float wc, wn;
     if (E >= hi) {                                     // row entirely inside output Ya
       wc = (float)dh * inv_sh;
-      wn = (E == hi) ? 0.f : -1.f;                     // exact boundary at the row end: emit, next starts clean
+      wn = (E == hi) ? 0.f : -1.f;                     // boundary exactly at the row end: emit, next starts clean
     } else {
       wc = (float)(E - lo) * inv_sh;
       wn = (float)(hi - E) * inv_sh;
     }
-    if (Ya < oy0) {                                    // contribution to the previous unit's row is dropped
+    if (Ya < oy0) {                                    // the part that belongs to the previous unit's row is dropped
       wc = (wn > 0.f) ? wn : 0.f;
       wn = -1.f;
     }
     tab[k] = make_float2(wc, wn);
   }
-  __syncwarp();
 
   // ---- horizontal: this lane's 4-pixel source group and the outputs that start in it ----
-  const int g0 = (int)((((int64_t)ox0 * sw) / dw) >> 2);
+  const int g0 = (int)(floor_div((int64_t)ox0 * sw, dw) >> 2);
   const int g = g0 + lane;
-  const int64_t c0 = (int64_t)4 * g * dw;              // group start in scaled units
-  const int Xfirst = (int)ceil_div64(c0, sw);
-  const int Xnext = (int)ceil_div64(c0 + (int64_t)4 * dw, sw);
+  const int64_t c0 = (int64_t)4 * g * dw;              // group start, in source units scaled by dw
+  const int Xfirst = (int)ceil_div(c0, sw);
+  const int Xnext = (int)ceil_div(c0 + (int64_t)4 * dw, sw);
   const int cnt = min(Xnext - Xfirst, MAXO);
   float w[MAXO][4], wprev[4];
 #pragma unroll
@@ -119,91 +162,102 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
       w[o][c] = (ov > 0 && Xfirst + o < dw) ? (float)ov * inv_sw : 0.f;
     }
   }
-  const bool active = ((int64_t)4 * g * dw < (int64_t)ox1 * sw) && (4 * g < sw);
+  // groups the warp needs: up to the end of the tile's last output, inside the bitmap
+  const int g_end = (int)min(ceil_div((int64_t)ox1 * sw, (int64_t)4 * dw), (int64_t)((sw + 3) >> 2));
+  const int nact = min(32, g_end - g0);
+  const bool active = lane < nact;
+  const uint32_t row_bytes = (uint32_t)nact * 16u;
   bool st_ok[MAXO];
-  int xdev[MAXO];
+  float last[MAXO];  // 1 for the last output that starts in this group: it takes the right neighbour's tail
 #pragma unroll
   for (int o = 0; o < MAXO; ++o) {
     const int X = Xfirst + o;
     st_ok[o] = active && (o < cnt) && (X >= ox0) && (X < ox1);
-    xdev[o] = X0 + (im.flip_x ? dw - 1 - X : X);
+    last[o] = (o == cnt - 1 && lane != 31) ? 1.f : 0.f;
+  }
+  // columns past the bitmap edge (row padding) must not trip the alpha check
+  const uint32_t m0 = (4 * g + 0 >= sw) ? 0xff000000u : 0u, m1 = (4 * g + 1 >= sw) ? 0xff000000u : 0u,
+                 m2 = (4 * g + 2 >= sw) ? 0xff000000u : 0u, m3 = (4 * g + 3 >= sw) ? 0xff000000u : 0u;
+  // output pointer walks with the rows: device position of this lane's output 0, +-4 bytes per output
+  const int xstep = im.flip_x ? -4 : 4;
+  const int64_t ystep = im.flip_y ? -P.out_pitch : P.out_pitch;
+  uint8_t* optr = P.out_rgba + (int64_t)(Y0 + (im.flip_y ? dh - 1 - oy0 : oy0)) * P.out_pitch +
+                  (int64_t)(X0 + (im.flip_x ? dw - 1 - Xfirst : Xfirst)) * 4;
+
+  const uint8_t* src = im.data + (int64_t)rs * im.pitch + (int64_t)g0 * 16;
+  __syncwarp();  // row table visible; every lane is done with the previous unit's ring reads
+  if (lane == 0) {
+    const int pre = min(nrows, STREAM_NST);
+    for (int u = 0; u < pre; ++u) {
+      const uint32_t s = (it + u) % STREAM_NST;
+      mbar_expect_tx(&ws.bar[s], row_bytes);
+      bulk_g2s(ws.ring[s], src + (int64_t)u * im.pitch, row_bytes, &ws.bar[s]);
+    }
   }
 
-  const uint8_t* base = im.data + (int64_t)rs * im.pitch + (int64_t)g * 16;
-  uint4 ring[STREAM_NPF];
+  float acc[12];
 #pragma unroll
-  for (int u = 0; u < STREAM_NPF; ++u) {
-    ring[u] = make_uint4(0, 0, 0, 0);
-    if (active && u < nrows) ring[u] = ldg_stream(reinterpret_cast<const uint4*>(base + (int64_t)u * im.pitch));
-  }
-  float acc[16];
-#pragma unroll
-  for (int k = 0; k < 16; ++k) acc[k] = 0.f;
-  int Y = oy0;
-  bool need_fix = false;
+  for (int k = 0; k < 12; ++k) acc[k] = 0.f;
+  uint32_t and_acc = 0xffffffffu;
 
-  for (int i = 0; i < nrows; i += STREAM_NPF) {
+  for (int i = 0; i < nrows; ++i) {
+    const uint32_t s = it % STREAM_NST;
+    mbar_wait(&ws.bar[s], (it / STREAM_NST) & 1u);
+    const uint4 px = *reinterpret_cast<const uint4*>(&ws.ring[s][lane * 16]);
+    const float2 t = tab[i];
+    __syncwarp();  // all lanes hold their 16 B: the stage can be refilled
+    if (lane == 0 && i + STREAM_NST < nrows) {
+      mbar_expect_tx(&ws.bar[s], row_bytes);
+      bulk_g2s(ws.ring[s], src + (int64_t)(i + STREAM_NST) * im.pitch, row_bytes, &ws.bar[s]);
+    }
+    ++it;
+    and_acc &= (px.x | m0);
+    and_acc &= (px.y | m1);
+    and_acc &= (px.z | m2);
+    and_acc &= (px.w | m3);
+    float f[12];
+    f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x);
+    f[3] = expand<0>(px.y); f[4] = expand<1>(px.y); f[5] = expand<2>(px.y);
+    f[6] = expand<0>(px.z); f[7] = expand<1>(px.z); f[8] = expand<2>(px.z);
+    f[9] = expand<0>(px.w); f[10] = expand<1>(px.w); f[11] = expand<2>(px.w);
 #pragma unroll
-    for (int u = 0; u < STREAM_NPF; ++u) {
-      const int ii = i + u;
-      if (ii < nrows) {
-        const uint4 px = ring[u];
-        if (active && ii + STREAM_NPF < nrows)
-          ring[u] = ldg_stream(reinterpret_cast<const uint4*>(base + (int64_t)(ii + STREAM_NPF) * im.pitch));
-        const float2 t = tab[ii];
-        float f[16];
-        f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x); f[3] = expand<3>(px.x);
-        f[4] = expand<0>(px.y); f[5] = expand<1>(px.y); f[6] = expand<2>(px.y); f[7] = expand<3>(px.y);
-        f[8] = expand<0>(px.z); f[9] = expand<1>(px.z); f[10] = expand<2>(px.z); f[11] = expand<3>(px.z);
-        f[12] = expand<0>(px.w); f[13] = expand<1>(px.w); f[14] = expand<2>(px.w); f[15] = expand<3>(px.w);
+    for (int k = 0; k < 12; ++k) acc[k] = fmaf(t.x, f[k], acc[k]);
+    if (t.y >= 0.f) {
+      // ---- an output row is complete: horizontal pass in registers ----
+      float out[MAXO][3];
 #pragma unroll
-        for (int k = 0; k < 16; ++k) acc[k] = fmaf(t.x, f[k], acc[k]);
-        if (t.y >= 0.f) {
-          // ---- output row Y complete: horizontal pass in registers ----
-          float prev[4], out[MAXO][4];
+      for (int ch = 0; ch < 3; ++ch) {
+        float prev = wprev[0] * acc[ch];
 #pragma unroll
-          for (int ch = 0; ch < 4; ++ch) {
-            prev[ch] = wprev[0] * acc[ch];
+        for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], acc[c * 3 + ch], prev);
 #pragma unroll
-            for (int c = 1; c < 4; ++c) prev[ch] = fmaf(wprev[c], acc[c * 4 + ch], prev[ch]);
+        for (int o = 0; o < MAXO; ++o) {
+          out[o][ch] = w[o][0] * acc[ch];
 #pragma unroll
-            for (int o = 0; o < MAXO; ++o) {
-              out[o][ch] = w[o][0] * acc[ch];
+          for (int c = 1; c < 4; ++c) out[o][ch] = fmaf(w[o][c], acc[c * 3 + ch], out[o][ch]);
+        }
+        const float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
 #pragma unroll
-              for (int c = 1; c < 4; ++c) out[o][ch] = fmaf(w[o][c], acc[c * 4 + ch], out[o][ch]);
-            }
-          }
-          const int ydev = Y0 + (im.flip_y ? dh - 1 - Y : Y);
-          uint8_t* orow = P.out_rgba + (int64_t)ydev * P.out_pitch;
+        for (int o = 0; o < MAXO; ++o) out[o][ch] = fmaf(last[o], rcv, out[o][ch]);
+      }
 #pragma unroll
-          for (int ch = 0; ch < 4; ++ch) {
-            float rcv = __shfl_down_sync(0xffffffffu, prev[ch], 1);
-            if (lane == 31) rcv = 0.f;
-#pragma unroll
-            for (int o = 0; o < MAXO; ++o)
-              if (o == cnt - 1) out[o][ch] += rcv;
-          }
-#pragma unroll
-          for (int o = 0; o < MAXO; ++o) {
-            if (st_ok[o]) {
-              // filtered alpha must be 255 for the plain (non-premultiplied) average to be exact
-              need_fix |= !(fmaf(out[o][3], 32768.f, -32768.f) > 254.95f);
-              const uint32_t r = __float_as_uint(__fmaf_rd(out[o][0], 32768.f, 8355840.5f));
-              const uint32_t gg = __float_as_uint(__fmaf_rd(out[o][1], 32768.f, 8355840.5f));
-              const uint32_t b = __float_as_uint(__fmaf_rd(out[o][2], 32768.f, 8355840.5f));
-              const uint32_t v = __byte_perm(__byte_perm(r, gg, 0x0040u), b, 0x0410u) | 0xff000000u;
-              *reinterpret_cast<uint32_t*>(orow + (int64_t)xdev[o] * 4) = v;
-            }
-          }
-          ++Y;
-#pragma unroll
-          for (int k = 0; k < 16; ++k) acc[k] = t.y * f[k];
+      for (int o = 0; o < MAXO; ++o) {
+        if (st_ok[o]) {
+          const uint32_t r = __float_as_uint(__fmaf_rd(out[o][0], 32768.f, 8355840.5f));
+          const uint32_t gg = __float_as_uint(__fmaf_rd(out[o][1], 32768.f, 8355840.5f));
+          const uint32_t b = __float_as_uint(__fmaf_rd(out[o][2], 32768.f, 8355840.5f));
+          *reinterpret_cast<uint32_t*>(optr + o * xstep) =
+              __byte_perm(__byte_perm(r, gg, 0x0040u), b, 0x0410u) | 0xff000000u;
         }
       }
+      optr += ystep;
+#pragma unroll
+      for (int k = 0; k < 12; ++k) acc[k] = t.y * f[k];
     }
   }
   // Translucent bitmaps (rare: photos are opaque): the unit is redone with the exact premultiplied
   // source-over evaluation.  Outside the hot loop so it costs the streaming path no registers.
+  const bool need_fix = active && ((and_acc >> 24) != 0xffu);
   if (__any_sync(0xffffffffu, need_fix)) {
     const int ax = im.flip_x ? dw - ox1 : ox0, bx = im.flip_x ? dw - ox0 : ox1;
     const int ay = im.flip_y ? dh - oy1 : oy0, by = im.flip_y ? dh - oy0 : oy1;
@@ -228,32 +282,53 @@ __device__ __forceinline__ void gather_unit(const JobParam& P, const Region& R, 
   const int y0 = R.y0 + ty * R.tile_h, y1 = min(y0 + R.tile_h, R.y1);
   for (int y = y0; y < y1; ++y) {
     uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
-    for (int x = x0 + lane; x < x1; x += 32) {
-      row[x] = shade_px(P, x, y);
-    }
+    for (int x = x0 + lane; x < x1; x += 32) row[x] = shade_px(P, x, y);
   }
 }
 
+// sched[0] = next unit to hand out, sched[1] = warps that have left the kernel; the last warp out
+// resets both, so back-to-back launches on one stream need no memset in between.
+//
 // MAXO = max over the job's streaming regions of ceil(4 / ratio_x): 2 for ratio > 2 (the 9x12MP
 // config), 3 for ratio > 4/3, 4 for ratio > 1.
 template <int MAXO>
 __global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
-compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan) {
-  __shared__ float2 tabs[STREAM_WARPS][STREAM_TAB_MAX];
+compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int unit = blockIdx.x * STREAM_WARPS + warp;
-  if (unit >= plan.n_units) return;
-  int ri = 0;
-  while (ri + 1 < plan.n_regions && unit >= plan.r[ri + 1].first_unit) ++ri;
-  const Region& R = plan.r[ri];
-  const int local = unit - R.first_unit;
-  const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
-  if (R.kind == REGION_STREAM) {
-    stream_unit<MAXO>(P, R, tx, ty, tabs[warp], lane);
-  } else if (R.kind == REGION_FILL) {
-    fill_unit(P, R, tx, ty, lane);
-  } else {
-    gather_unit(P, R, tx, ty, lane);
+  WarpSmem& ws = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
+  if (lane == 0) {
+    for (int s = 0; s < STREAM_NST; ++s) mbar_init(&ws.bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncwarp();
+  uint32_t it = 0;
+  for (;;) {
+    unsigned int unit = 0;
+    if (lane == 0) unit = atomicAdd(&sched[0], 1u);
+    unit = __shfl_sync(0xffffffffu, unit, 0);
+    if (unit >= (unsigned int)plan.n_units) break;
+    int ri = 0;
+    while (ri + 1 < plan.n_regions && (int)unit >= plan.r[ri + 1].first_unit) ++ri;
+    const Region& R = plan.r[ri];
+    const int local = (int)unit - R.first_unit;
+    const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
+    if (R.kind == REGION_STREAM) {
+      stream_unit<MAXO>(P, R, tx, ty, ws, lane, it);
+    } else if (R.kind == REGION_FILL) {
+      fill_unit(P, R, tx, ty, lane);
+    } else {
+      gather_unit(P, R, tx, ty, lane);
+    }
+  }
+  if (lane == 0) {
+    __threadfence();
+    const unsigned int total = gridDim.x * STREAM_WARPS;
+    if (atomicAdd(&sched[1], 1u) == total - 1) {
+      sched[0] = 0;
+      sched[1] = 0;
+      __threadfence();
+    }
   }
 }
 

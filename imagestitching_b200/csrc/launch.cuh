@@ -133,10 +133,31 @@ inline bool build_plan(const JobParam& P, Plan* plan) {
   return unit > 0;
 }
 
+template <int MAXO>
+inline cudaError_t launch_compose(const JobParam& P, const Plan& plan, int sm_count, unsigned int* sched,
+                                  cudaStream_t stream) {
+  static bool configured = false;   // per MAXO instantiation
+  static int ctas_per_sm = 1;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kComposeSmemBytes);
+    if (e != cudaSuccess) return e;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, compose_kernel<MAXO>, STREAM_WARPS * 32,
+                                                      kComposeSmemBytes);
+    if (e != cudaSuccess) return e;
+    if (ctas_per_sm < 1) ctas_per_sm = 1;
+    configured = true;
+  }
+  // persistent grid: every resident warp slot of the chip, capped by the number of units
+  int grid = sm_count * ctas_per_sm;
+  const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
+  if (grid > need) grid = need;
+  compose_kernel<MAXO><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
+  return cudaGetLastError();
+}
+
 inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScratch& scratch, cudaStream_t stream,
                       int* launches, int* path_info) {
-  (void)sm_count;
-  (void)scratch;
   *launches = 0;
   *path_info = 1 << 24;
   if (want_yuv) {
@@ -147,20 +168,29 @@ inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScra
   }
   Plan plan;
   if (build_plan(P, &plan)) {
-    const int grid = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
+    if (!scratch.p) {  // unit scheduler counters {next unit, warps retired}; the kernel leaves them at zero
+      cudaError_t e = cudaMalloc(&scratch.p, 256);
+      if (e != cudaSuccess) return (int)e;
+      scratch.cap = 256;
+      e = cudaMemsetAsync(scratch.p, 0, 256, stream);
+      if (e != cudaSuccess) return (int)e;
+    }
     int maxo = 2, cnt[3] = {0, 0, 0};
     for (int i = 0; i < plan.n_regions; ++i) {
       if (plan.r[i].kind == REGION_STREAM) maxo = std::max(maxo, plan.r[i].maxo);
       cnt[plan.r[i].kind]++;
     }
     *path_info = cnt[REGION_STREAM] | (cnt[REGION_GATHER] << 8) | (cnt[REGION_FILL] << 16);
-    if (maxo <= 2) compose_kernel<2><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan);
-    else if (maxo == 3) compose_kernel<3><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan);
-    else compose_kernel<4><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan);
-  } else {
-    dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
-    gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
+    unsigned int* sched = (unsigned int*)scratch.p;
+    cudaError_t e;
+    if (maxo <= 2) e = launch_compose<2>(P, plan, sm_count, sched, stream);
+    else if (maxo == 3) e = launch_compose<3>(P, plan, sm_count, sched, stream);
+    else e = launch_compose<4>(P, plan, sm_count, sched, stream);
+    *launches = 1;
+    return (int)e;
   }
+  dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
+  gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
   *launches = 1;
   return (int)cudaGetLastError();
 }
