@@ -40,6 +40,9 @@ namespace stitch {
 #ifndef STREAM_MINB
 #define STREAM_MINB 3  // resident CTAs per SM the register allocation targets
 #endif
+#ifndef STREAM_USE_BULK
+#define STREAM_USE_BULK 0  // 1: cp.async.bulk + mbarrier ring (one elected lane); 0: per-lane cp.async ring
+#endif
 #define STREAM_STAGE_BYTES 512
 
 struct WarpSmem {
@@ -75,6 +78,18 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
+}
+
+// Per-lane 16-byte async copy global -> shared (LDGSTS).  A lane only ever refills the slot it has
+// itself just read with LDS; both go through the lane's LSU queue in program order and the copy's
+// shared-memory write lands a global-memory latency later, so no barrier is needed.
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global.L2::128B [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
 // byte ch of px -> float 1 + b * 2^-15
@@ -186,6 +201,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
 
   const uint8_t* src = im.data + (int64_t)rs * im.pitch + (int64_t)g0 * 16;
   __syncwarp();  // row table visible; every lane is done with the previous unit's ring reads
+#if STREAM_USE_BULK
   if (lane == 0) {
     const int pre = min(nrows, STREAM_NST);
     for (int u = 0; u < pre; ++u) {
@@ -194,6 +210,18 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
       bulk_g2s(ws.ring[s], src + (int64_t)u * im.pitch, row_bytes, &ws.bar[s]);
     }
   }
+#else
+  // each lane stages its own 16 B per row: STREAM_NST rows in flight, one commit group per row
+  const uint8_t* lsrc = src + lane * 16;
+  uint8_t* lring = &ws.ring[0][lane * 16];
+  uint32_t stage = 0;
+#pragma unroll
+  for (int u = 0; u < STREAM_NST; ++u) {
+    if (active && u < nrows) cp_async16(lring + u * STREAM_STAGE_BYTES, lsrc);
+    lsrc += im.pitch;
+    cp_async_commit();
+  }
+#endif
 
   float acc[12];
 #pragma unroll
@@ -201,6 +229,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   uint32_t and_acc = 0xffffffffu;
 
   for (int i = 0; i < nrows; ++i) {
+#if STREAM_USE_BULK
     const uint32_t s = it % STREAM_NST;
     mbar_wait(&ws.bar[s], (it / STREAM_NST) & 1u);
     const uint4 px = *reinterpret_cast<const uint4*>(&ws.ring[s][lane * 16]);
@@ -211,6 +240,16 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
       bulk_g2s(ws.ring[s], src + (int64_t)(i + STREAM_NST) * im.pitch, row_bytes, &ws.bar[s]);
     }
     ++it;
+#else
+    cp_async_wait<STREAM_NST - 1>();   // row i has landed (this lane's own copy; no cross-lane hazard)
+    uint8_t* slot = lring + stage * STREAM_STAGE_BYTES;
+    const uint4 px = *reinterpret_cast<const uint4*>(slot);
+    const float2 t = tab[i];
+    if (active && i + STREAM_NST < nrows) cp_async16(slot, lsrc);
+    lsrc += im.pitch;
+    cp_async_commit();
+    stage = (stage + 1 == STREAM_NST) ? 0u : stage + 1;
+#endif
     and_acc &= (px.x | m0);
     and_acc &= (px.y | m1);
     and_acc &= (px.z | m2);
