@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <vector>
 
 #include "compose_kernel.cuh"
@@ -32,16 +33,29 @@ inline bool stream_eligible(const ImgParam& im) {
   if ((int64_t)im.sx_len > 4 * dw) return false;               // one-hop neighbour exchange needs ratio_x <= 4
   if (((uintptr_t)im.data & 15) || (im.pitch & 15)) return false;  // 128-bit row loads
   if ((int64_t)im.sx_len * dw >= (1LL << 40) || (int64_t)im.sy_len * dh >= (1LL << 40)) return false;
-  // at least one output row must fit the per-warp row table
-  if (im.sy_len / dh + 4 > STREAM_TAB_MAX) return false;
+  // at least one output row (plus unroll padding) must fit the per-warp row table
+  if (im.sy_len / dh + 4 + STREAM_NST > STREAM_TAB_MAX) return false;
   return true;
+}
+
+// 32-bit geometry suffices when every scaled coordinate the kernel forms stays below 2^31.
+inline bool needs_wide(const ImgParam& im) {
+  const int64_t dw = (int64_t)im.W, dh = (int64_t)im.H;
+  return ((int64_t)im.sx_len + 512) * (dw + 1) >= (1LL << 31) || ((int64_t)im.sy_len + 8) * (dh + 1) >= (1LL << 31);
+}
+
+// Largest tile_h (output rows per unit) whose source rows fit the row table.
+inline int stream_max_tile_h(const ImgParam& im) {
+  const int64_t dh = (int64_t)im.H;
+  int64_t th = ((int64_t)(STREAM_TAB_MAX - 4 - STREAM_NST) * dh) / im.sy_len;
+  return (int)std::max<int64_t>(1, std::min<int64_t>(th, 1 << 20));
 }
 
 // Returns true and fills `plan` when the fused compose launch applies to this job: every device
 // rect integer-aligned (superSample == 1 and gap*scaleDown integral, true for BASELINE configs 2-5)
 // and the clipped rects pairwise disjoint, so painter's-order source-over degenerates to each
 // pixel belonging to at most one image.
-inline bool build_plan(const JobParam& P, Plan* plan) {
+inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   struct Box { int x0, y0, x1, y1, img; };
   std::vector<Box> boxes;
   for (int k = 0; k < P.n; ++k) {
@@ -75,9 +89,7 @@ inline bool build_plan(const JobParam& P, Plan* plan) {
         if (tw < 1) tw = 1;
         const int nx = (rx1 - rx0 + tw - 1) / tw;
         r.tile_w = (rx1 - rx0 + nx - 1) / nx;     // balance the last column
-        int th = (int)(((int64_t)(STREAM_TAB_MAX - 4) * dh) / im.sy_len);
-        th = std::max(1, std::min(th, 48));
-        r.tile_h = th;
+        r.tile_h = stream_max_tile_h(im);   // refined below for load balance
         r.maxo = (int)((4LL * dw + im.sx_len - 1) / im.sx_len);
         r.maxo = std::max(2, std::min(r.maxo, 4));
       } else {
@@ -119,6 +131,47 @@ inline bool build_plan(const JobParam& P, Plan* plan) {
   }
   for (Region& f : fills) regs.push_back(f);
   if (regs.size() > STITCH_MAX_REGIONS) return false;
+
+  // Unit height of the streaming regions.  Units are handed out dynamically to `resident_warps`
+  // persistent warps, so the makespan is ceil(units / warps) unit-times: pick the number of source
+  // rows per unit (equal work per unit across regions) so that the unit count lands just under a
+  // small multiple k of the warp count.  k = 2 keeps the per-unit setup (row table, lane weights)
+  // amortised over the most rows; larger k only when the row table caps the unit height.
+  auto count_units = [&](int src_rows) {
+    int64_t n = 0;
+    for (Region& r : regs) {
+      int tw = r.tile_w, th = r.tile_h;
+      if (r.kind == REGION_STREAM) {
+        const ImgParam& im = P.img[r.img];
+        int64_t h = ((int64_t)src_rows * (int64_t)im.H) / im.sy_len;
+        th = (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+      }
+      n += (int64_t)((r.x1 - r.x0 + tw - 1) / tw) * ((r.y1 - r.y0 + th - 1) / th);
+    }
+    return n;
+  };
+  const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_NST;
+  int best_rows = max_src_rows;
+  if (resident_warps > 0 && count_units(max_src_rows) < 8LL * resident_warps) {
+    for (int k = 2; k <= 8; ++k) {
+      // smallest src_rows with units <= k * warps (units is non-increasing in src_rows)
+      int lo = 1, hi = max_src_rows;
+      if (count_units(hi) > (int64_t)k * resident_warps) continue;   // cannot get that few units: try larger k
+      while (lo < hi) {
+        const int mid = (lo + hi) / 2;
+        if (count_units(mid) <= (int64_t)k * resident_warps) hi = mid; else lo = mid + 1;
+      }
+      best_rows = lo;
+      break;
+    }
+    if (count_units(max_src_rows) <= resident_warps) best_rows = std::min(best_rows, 64);  // small job: spread it
+  }
+  for (Region& r : regs) {
+    if (r.kind != REGION_STREAM) continue;
+    const ImgParam& im = P.img[r.img];
+    int64_t h = ((int64_t)best_rows * (int64_t)im.H) / im.sy_len;
+    r.tile_h = (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+  }
   int unit = 0;
   plan->n_regions = (int)regs.size();
   for (size_t i = 0; i < regs.size(); ++i) {
@@ -133,28 +186,28 @@ inline bool build_plan(const JobParam& P, Plan* plan) {
   return unit > 0;
 }
 
-template <int MAXO>
-inline cudaError_t launch_compose(const JobParam& P, const Plan& plan, int sm_count, unsigned int* sched,
-                                  cudaStream_t stream) {
-  static bool configured = false;   // per MAXO instantiation
-  static int ctas_per_sm = 1;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         kComposeSmemBytes);
-    if (e != cudaSuccess) return e;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, compose_kernel<MAXO>, STREAM_WARPS * 32,
-                                                      kComposeSmemBytes);
-    if (e != cudaSuccess) return e;
-    if (ctas_per_sm < 1) ctas_per_sm = 1;
-    configured = true;
+template <int MAXO, bool WIDE>
+struct ComposeLaunch {
+  // resident CTAs per SM of this instantiation (queried once), 0 on error
+  static int ctas_per_sm(cudaError_t* err) {
+    static int value = -1;
+    if (value < 0) {
+      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           kComposeSmemBytes);
+      int n = 0;
+      if (e == cudaSuccess)
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, WIDE>, STREAM_WARPS * 32,
+                                                          kComposeSmemBytes);
+      if (e != cudaSuccess) { *err = e; return 0; }
+      value = n < 1 ? 1 : n;
+    }
+    return value;
   }
-  // persistent grid: every resident warp slot of the chip, capped by the number of units
-  int grid = sm_count * ctas_per_sm;
-  const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
-  if (grid > need) grid = need;
-  compose_kernel<MAXO><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
-  return cudaGetLastError();
-}
+  static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
+    compose_kernel<MAXO, WIDE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
+    return cudaGetLastError();
+  }
+};
 
 inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScratch& scratch, cudaStream_t stream,
                       int* launches, int* path_info) {
@@ -166,8 +219,30 @@ inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScra
     *launches = 1;
     return (int)cudaGetLastError();
   }
+  // kernel variant: decided by the images alone (before the unit grid is chosen)
+  int maxo = 2;
+  static const bool force_wide = std::getenv("STITCH_FORCE_WIDE") != nullptr;   // test hook: 64-bit geometry path
+  bool wide = force_wide;
+  for (int k = 0; k < P.n; ++k) {
+    const ImgParam& im = P.img[k];
+    if (!is_int(im.W) || !is_int(im.H) || im.W < 1 || im.H < 1 || !stream_eligible(im)) continue;
+    const int64_t dw = (int64_t)im.W;
+    maxo = std::max(maxo, (int)std::min<int64_t>(4, (4 * dw + im.sx_len - 1) / im.sx_len));
+    wide = wide || needs_wide(im);
+  }
+  cudaError_t err = cudaSuccess;
+  int per_sm = 0;
+#define STITCH_DISPATCH(M, Wd, expr) \
+  if (maxo == M && wide == Wd) { using K = ComposeLaunch<M, Wd>; expr; }
+#define STITCH_ALL(expr)                                                                                        \
+  STITCH_DISPATCH(2, false, expr) STITCH_DISPATCH(3, false, expr) STITCH_DISPATCH(4, false, expr) \
+  STITCH_DISPATCH(2, true, expr) STITCH_DISPATCH(3, true, expr) STITCH_DISPATCH(4, true, expr)
+  STITCH_ALL(per_sm = K::ctas_per_sm(&err))
+  if (err != cudaSuccess) return (int)err;
+  const int resident_warps = sm_count * per_sm * STREAM_WARPS;
+
   Plan plan;
-  if (build_plan(P, &plan)) {
+  if (build_plan(P, resident_warps, &plan)) {
     if (!scratch.p) {  // unit scheduler counters {next unit, warps retired}; the kernel leaves them at zero
       cudaError_t e = cudaMalloc(&scratch.p, 256);
       if (e != cudaSuccess) return (int)e;
@@ -175,20 +250,20 @@ inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScra
       e = cudaMemsetAsync(scratch.p, 0, 256, stream);
       if (e != cudaSuccess) return (int)e;
     }
-    int maxo = 2, cnt[3] = {0, 0, 0};
-    for (int i = 0; i < plan.n_regions; ++i) {
-      if (plan.r[i].kind == REGION_STREAM) maxo = std::max(maxo, plan.r[i].maxo);
-      cnt[plan.r[i].kind]++;
-    }
+    int cnt[3] = {0, 0, 0};
+    for (int i = 0; i < plan.n_regions; ++i) cnt[plan.r[i].kind]++;
     *path_info = cnt[REGION_STREAM] | (cnt[REGION_GATHER] << 8) | (cnt[REGION_FILL] << 16);
+    // persistent grid: every resident warp slot of the chip, capped by the number of units
+    int grid = sm_count * per_sm;
+    const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
+    if (grid > need) grid = need;
     unsigned int* sched = (unsigned int*)scratch.p;
-    cudaError_t e;
-    if (maxo <= 2) e = launch_compose<2>(P, plan, sm_count, sched, stream);
-    else if (maxo == 3) e = launch_compose<3>(P, plan, sm_count, sched, stream);
-    else e = launch_compose<4>(P, plan, sm_count, sched, stream);
+    STITCH_ALL(err = K::launch(P, plan, grid, sched, stream))
     *launches = 1;
-    return (int)e;
+    return (int)err;
   }
+#undef STITCH_ALL
+#undef STITCH_DISPATCH
   dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
   gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
   *launches = 1;
