@@ -1,0 +1,62 @@
+// TypeScript facade of the stitch path: keeps the page's interface (ordered image list +
+// 'vertical' | 'horizontal' in, exported RGBA / I420 buffer out; pages/index/index.js:14-21,1186-1633)
+// and calls libstitch.so through the N-API addon in ./napi/stitch_napi.cc.
+//
+// NOT EXECUTED IN THIS REPO'S CI: the build image has no node/tsc (DESIGN.md section 1).  The Python
+// mirror (imagestitching_b200/stitch.py) is the executed equivalent and shares the golden vectors.
+import { computeLayout, fallbackProfile, Direction, ImageRecord, Layout, Platform } from './layout';
+
+// eslint-disable-next-line @typescript-eslint/no-var-requires
+const native = require('./build/Release/stitch_napi.node') as {
+  createContext(device: number): unknown;
+  destroyContext(ctx: unknown): void;
+  run(ctx: unknown, job: NativeJob, onProgress?: (pct: number) => void): Promise<NativeResult>;
+};
+
+export interface StitchImage extends ImageRecord {
+  /** decoded RGBA8 bitmap, straight alpha (what loadImageFrom hands to drawWithOrientation) */
+  data: Uint8Array;
+  bmpWidth: number; bmpHeight: number; pitchBytes?: number;
+}
+export interface StitchOptions {
+  gap?: number; mode?: 'min' | 'max' | 'original' | string;
+  platform?: Platform; deviceMaxCanvasSize?: number; deviceMaxCanvasPixels?: number;
+  output?: 'rgba' | 'yuv420' | 'both'; device?: number; onProgress?: (pct: number) => void;
+}
+export interface StitchResult { width: number; height: number; layout: Layout; rgba?: Uint8Array; yuv?: Uint8Array; }
+interface NativeJob {
+  images: StitchImage[]; direction: number; mode: number; gap: number;
+  platform: number; maxCanvasSize: number; maxCanvasPixels: number; output: number;
+}
+interface NativeResult { width: number; height: number; rgba?: Uint8Array; yuv?: Uint8Array; status: number; message: string; }
+
+const MODES: Record<string, number> = { min: 0, max: 1, original: 2 };
+const PLATFORMS: Record<string, number> = { ios: 0, android: 1 };
+const contexts = new Map<number, unknown>();
+
+export class StitchError extends Error {
+  constructor(public status: number, message: string) { super(message); }
+}
+
+export { computeLayout, fallbackProfile };
+
+/** onStitch(): resolves to undefined for an empty list (index.js:1189), rejects with the reference's messages. */
+export async function stitch(images: StitchImage[], direction: Direction, opts: StitchOptions = {}): Promise<StitchResult | undefined> {
+  if (!images.length) return undefined;
+  const platform = opts.platform || 'ios';
+  const profile = fallbackProfile(platform, opts.deviceMaxCanvasSize, opts.deviceMaxCanvasPixels);
+  const mode = opts.mode || 'min';
+  const layout = computeLayout(images, direction, mode, opts.gap, profile);      // twin; the native side recomputes it
+  const device = opts.device || 0;
+  let ctx = contexts.get(device);
+  if (!ctx) { ctx = native.createContext(device); contexts.set(device, ctx); }
+  const res = await native.run(ctx, {
+    images, direction: direction === 'vertical' ? 0 : 1, mode: mode in MODES ? MODES[mode] : 3, gap: opts.gap || 0,
+    platform: platform in PLATFORMS ? PLATFORMS[platform] : 2,
+    maxCanvasSize: profile.deviceMaxCanvasSize || 0, maxCanvasPixels: profile.deviceMaxCanvasPixels || 0,
+    output: { rgba: 1, yuv420: 2, both: 3 }[opts.output || 'rgba'],
+  }, opts.onProgress);
+  if (res.status !== 0) throw new StitchError(res.status, res.message);
+  if (res.width !== layout.canvasW || res.height !== layout.canvasH) throw new StitchError(-1, 'layout twin mismatch');
+  return { width: res.width, height: res.height, layout, rgba: res.rgba, yuv: res.yuv };
+}
