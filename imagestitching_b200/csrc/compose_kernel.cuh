@@ -77,9 +77,9 @@ __device__ __forceinline__ void gather_unit(const JobParam& P, const Region& R, 
 // sched[0] = next unit to hand out, sched[1] = warps that have left the kernel; the last warp out
 // resets both, so back-to-back launches on one stream need no memset in between.
 //
-// MAXO = max over the job's streaming regions of ceil(4 / ratio_x); WIDE = 64-bit geometry
-// (only when sx_len*W or sy_len*H does not fit 31 bits).
-template <int MAXO, bool WIDE>
+// MAXO = max over the job's streaming regions of ceil(4 / ratio_x); PARTIAL = some streamed bitmap's
+// width is not a multiple of 4 (stream_unit.cuh).
+template <int MAXO, bool PARTIAL>
 __global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
 compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -102,8 +102,7 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
     const int local = (int)unit - R.first_unit;
     const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
     if (R.kind == REGION_STREAM) {
-      if (WIDE) stream_unit<MAXO, int64_t>(P, R, tx, ty, ws, lane);
-      else stream_unit<MAXO, int32_t>(P, R, tx, ty, ws, lane);
+      stream_unit<MAXO, PARTIAL>(P, R, tx, ty, ws, lane);
     } else if (R.kind == REGION_FILL) {
       fill_unit(P, R, tx, ty, lane);
     } else {

@@ -32,16 +32,12 @@ inline bool stream_eligible(const ImgParam& im) {
   if (!(im.sx_len > dw && im.sy_len > dh)) return false;       // area filter on both axes
   if ((int64_t)im.sx_len > 4 * dw) return false;               // one-hop neighbour exchange needs ratio_x <= 4
   if (((uintptr_t)im.data & 15) || (im.pitch & 15)) return false;  // 128-bit row loads
-  if ((int64_t)im.sx_len * dw >= (1LL << 40) || (int64_t)im.sy_len * dh >= (1LL << 40)) return false;
+  // the kernel's geometry is unsigned 32-bit: every scaled coordinate it forms must stay below 2^31
+  if (((int64_t)im.sx_len + 512) * (dw + 1) >= (1LL << 31) || ((int64_t)im.sy_len + 8) * (dh + 1) >= (1LL << 31)) return false;
+  if (im.pitch * (int64_t)STREAM_TAB_MAX >= (1LL << 31)) return false;  // 32-bit row offsets inside a unit
   // at least one output row (plus unroll padding) must fit the per-warp row table
   if (im.sy_len / dh + 4 + STREAM_NST > STREAM_TAB_MAX) return false;
   return true;
-}
-
-// 32-bit geometry suffices when every scaled coordinate the kernel forms stays below 2^31.
-inline bool needs_wide(const ImgParam& im) {
-  const int64_t dw = (int64_t)im.W, dh = (int64_t)im.H;
-  return ((int64_t)im.sx_len + 512) * (dw + 1) >= (1LL << 31) || ((int64_t)im.sy_len + 8) * (dh + 1) >= (1LL << 31);
 }
 
 // Largest tile_h (output rows per unit) whose source rows fit the row table.
@@ -85,13 +81,13 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
         if (im.flip_y) { int t = dh - ry1; ry1 = dh - ry0; ry0 = t; }
         r.kind = REGION_STREAM;
         r.x0 = rx0; r.x1 = rx1; r.y0 = ry0; r.y1 = ry1;
-        int tw = (int)((124LL * dw) / im.sx_len);
-        if (tw < 1) tw = 1;
-        const int nx = (rx1 - rx0 + tw - 1) / tw;
-        r.tile_w = (rx1 - rx0 + nx - 1) / nx;     // balance the last column
+        // bands in group space: unit tx stores the outputs that start in groups g_base + 31*tx ... + 30
+        const int64_t sw = im.sx_len;
+        r.g_base = (int)((((int64_t)rx0 * sw) / dw) >> 2);
+        const int g_end = (int)std::min<int64_t>(((int64_t)rx1 * sw + 4 * dw - 1) / (4 * dw), (sw + 3) >> 2);
+        r.tile_w = 0;
+        r.tiles_x = std::max(1, (g_end - r.g_base + STREAM_STRIDE - 1) / STREAM_STRIDE);
         r.tile_h = stream_max_tile_h(im);   // refined below for load balance
-        r.maxo = (int)((4LL * dw + im.sx_len - 1) / im.sx_len);
-        r.maxo = std::max(2, std::min(r.maxo, 4));
       } else {
         r.kind = REGION_GATHER;
         r.x0 = bx.x0; r.x1 = bx.x1; r.y0 = bx.y0; r.y1 = bx.y1;
@@ -140,13 +136,17 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   auto count_units = [&](int src_rows) {
     int64_t n = 0;
     for (Region& r : regs) {
-      int tw = r.tile_w, th = r.tile_h;
+      int th = r.tile_h;
+      int64_t nx;
       if (r.kind == REGION_STREAM) {
         const ImgParam& im = P.img[r.img];
         int64_t h = ((int64_t)src_rows * (int64_t)im.H) / im.sy_len;
         th = (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+        nx = r.tiles_x;
+      } else {
+        nx = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
       }
-      n += (int64_t)((r.x1 - r.x0 + tw - 1) / tw) * ((r.y1 - r.y0 + th - 1) / th);
+      n += nx * ((r.y1 - r.y0 + th - 1) / th);
     }
     return n;
   };
@@ -176,7 +176,7 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   plan->n_regions = (int)regs.size();
   for (size_t i = 0; i < regs.size(); ++i) {
     Region& r = regs[i];
-    r.tiles_x = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
+    if (r.kind != REGION_STREAM) r.tiles_x = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
     r.tiles_y = (r.y1 - r.y0 + r.tile_h - 1) / r.tile_h;
     r.first_unit = unit;
     unit += r.tiles_x * r.tiles_y;
@@ -186,17 +186,17 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   return unit > 0;
 }
 
-template <int MAXO, bool WIDE>
+template <int MAXO, bool PARTIAL>
 struct ComposeLaunch {
   // resident CTAs per SM of this instantiation (queried once), 0 on error
   static int ctas_per_sm(cudaError_t* err) {
     static int value = -1;
     if (value < 0) {
-      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, PARTIAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            kComposeSmemBytes);
       int n = 0;
       if (e == cudaSuccess)
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, WIDE>, STREAM_WARPS * 32,
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, PARTIAL>, STREAM_WARPS * 32,
                                                           kComposeSmemBytes);
       if (e != cudaSuccess) { *err = e; return 0; }
       value = n < 1 ? 1 : n;
@@ -204,7 +204,7 @@ struct ComposeLaunch {
     return value;
   }
   static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
-    compose_kernel<MAXO, WIDE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
+    compose_kernel<MAXO, PARTIAL><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
     return cudaGetLastError();
   }
 };
@@ -221,19 +221,18 @@ inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScra
   }
   // kernel variant: decided by the images alone (before the unit grid is chosen)
   int maxo = 2;
-  static const bool force_wide = std::getenv("STITCH_FORCE_WIDE") != nullptr;   // test hook: 64-bit geometry path
-  bool wide = force_wide;
+  bool partial = false;
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
     if (!is_int(im.W) || !is_int(im.H) || im.W < 1 || im.H < 1 || !stream_eligible(im)) continue;
     const int64_t dw = (int64_t)im.W;
     maxo = std::max(maxo, (int)std::min<int64_t>(4, (4 * dw + im.sx_len - 1) / im.sx_len));
-    wide = wide || needs_wide(im);
+    partial = partial || (im.sx_len & 3) != 0;
   }
   cudaError_t err = cudaSuccess;
   int per_sm = 0;
-#define STITCH_DISPATCH(M, Wd, expr) \
-  if (maxo == M && wide == Wd) { using K = ComposeLaunch<M, Wd>; expr; }
+#define STITCH_DISPATCH(M, Pt, expr) \
+  if (maxo == M && partial == Pt) { using K = ComposeLaunch<M, Pt>; expr; }
 #define STITCH_ALL(expr)                                                                                        \
   STITCH_DISPATCH(2, false, expr) STITCH_DISPATCH(3, false, expr) STITCH_DISPATCH(4, false, expr) \
   STITCH_DISPATCH(2, true, expr) STITCH_DISPATCH(3, true, expr) STITCH_DISPATCH(4, true, expr)

@@ -43,10 +43,10 @@ struct Region {
   // STREAM: source-order output index ranges [x0,x1) x [y0,y1) inside the image's device rect
   // FILL/GATHER: device pixel rect
   int32_t x0, y0, x1, y1;
-  int32_t tile_w, tile_h;    // warp-unit size (output pixels)
+  int32_t tile_w, tile_h;    // warp-unit size (output pixels); STREAM uses tile_h only (bands are 31 groups wide)
   int32_t tiles_x, tiles_y;  // warp-unit grid
   int32_t first_unit;
-  int32_t maxo;              // STREAM: max outputs starting inside one 4-pixel source group
+  int32_t g_base;            // STREAM: first 4-pixel source group of the region; unit tx owns groups g_base + 31*tx ...
 };
 
 #define STITCH_MAX_REGIONS 64
