@@ -36,14 +36,14 @@ inline bool stream_eligible(const ImgParam& im) {
   if (((int64_t)im.sx_len + 512) * (dw + 1) >= (1LL << 31) || ((int64_t)im.sy_len + 8) * (dh + 1) >= (1LL << 31)) return false;
   if (im.pitch * (int64_t)STREAM_TAB_MAX >= (1LL << 31)) return false;  // 32-bit row offsets inside a unit
   // at least one output row (plus unroll padding) must fit the per-warp row table
-  if (im.sy_len / dh + 4 + STREAM_NST > STREAM_TAB_MAX) return false;
+  if (im.sy_len / dh + 4 + STREAM_UNR > STREAM_TAB_MAX) return false;
   return true;
 }
 
 // Largest tile_h (output rows per unit) whose source rows fit the row table.
 inline int stream_max_tile_h(const ImgParam& im) {
   const int64_t dh = (int64_t)im.H;
-  int64_t th = ((int64_t)(STREAM_TAB_MAX - 4 - STREAM_NST) * dh) / im.sy_len;
+  int64_t th = ((int64_t)(STREAM_TAB_MAX - 4 - STREAM_UNR) * dh) / im.sy_len;
   return (int)std::max<int64_t>(1, std::min<int64_t>(th, 1 << 20));
 }
 
@@ -128,49 +128,74 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   for (Region& f : fills) regs.push_back(f);
   if (regs.size() > STITCH_MAX_REGIONS) return false;
 
-  // Unit height of the streaming regions.  Units are handed out dynamically to `resident_warps`
-  // persistent warps, so the makespan is ceil(units / warps) unit-times: pick the number of source
-  // rows per unit (equal work per unit across regions) so that the unit count lands just under a
-  // small multiple k of the warp count.  k = 2 keeps the per-unit setup (row table, lane weights)
-  // amortised over the most rows; larger k only when the row table caps the unit height.
-  auto count_units = [&](int src_rows) {
+  // Unit heights of the streaming regions -- a "guided" schedule.  Units are handed out in order to
+  // `resident_warps` persistent warps.  Each image's rows are split into a BODY of large units
+  // (about one per warp, so the per-unit setup -- row table, lane weights -- is amortised over the
+  // most rows) followed by a TAIL of small units that even out the different speeds of the SMs
+  // (near / far L2 and HBM); all tails are queued after all bodies.  With equal-sized units only,
+  // ncu showed the SMs 14 % idle on average while the slowest ones finished.
+  static const double body_frac = [] { const char* e = std::getenv("STITCH_BODY_FRAC"); return e ? atof(e) : 0.75; }();
+  static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? atoi(e) : 32; }();
+  const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_UNR;
+  auto tile_h_for = [&](const Region& r, int src_rows) {
+    const ImgParam& im = P.img[r.img];
+    const int64_t h = ((int64_t)src_rows * (int64_t)im.H) / im.sy_len;
+    return (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+  };
+  auto body_rows_of = [&](const Region& r, int th) {   // output rows of the region that go to whole body units
+    const int64_t H = r.y1 - r.y0;
+    return (int)((int64_t)(body_frac * (double)H) / th * th);
+  };
+  auto count_body = [&](int src_rows) {
     int64_t n = 0;
-    for (Region& r : regs) {
-      int th = r.tile_h;
-      int64_t nx;
+    for (const Region& r : regs)
       if (r.kind == REGION_STREAM) {
-        const ImgParam& im = P.img[r.img];
-        int64_t h = ((int64_t)src_rows * (int64_t)im.H) / im.sy_len;
-        th = (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
-        nx = r.tiles_x;
-      } else {
-        nx = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
+        const int th = tile_h_for(r, src_rows);
+        n += (int64_t)r.tiles_x * (body_rows_of(r, th) / th);
       }
-      n += nx * ((r.y1 - r.y0 + th - 1) / th);
-    }
     return n;
   };
-  const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_NST;
-  int best_rows = max_src_rows;
-  if (resident_warps > 0 && count_units(max_src_rows) < 8LL * resident_warps) {
-    for (int k = 2; k <= 8; ++k) {
-      // smallest src_rows with units <= k * warps (units is non-increasing in src_rows)
+  int body_src_rows = max_src_rows;
+  if (resident_warps > 0) {
+    for (int k = 1; k <= 8; ++k) {
+      // smallest src_rows with body units <= k * warps (non-increasing in src_rows up to rounding)
+      if (count_body(max_src_rows) > (int64_t)k * resident_warps) continue;  // table caps the height: more units per warp
       int lo = 1, hi = max_src_rows;
-      if (count_units(hi) > (int64_t)k * resident_warps) continue;   // cannot get that few units: try larger k
       while (lo < hi) {
         const int mid = (lo + hi) / 2;
-        if (count_units(mid) <= (int64_t)k * resident_warps) hi = mid; else lo = mid + 1;
+        if (count_body(mid) <= (int64_t)k * resident_warps) hi = mid; else lo = mid + 1;
       }
-      best_rows = lo;
+      body_src_rows = lo;
       break;
     }
-    if (count_units(max_src_rows) <= resident_warps) best_rows = std::min(best_rows, 64);  // small job: spread it
   }
-  for (Region& r : regs) {
-    if (r.kind != REGION_STREAM) continue;
-    const ImgParam& im = P.img[r.img];
-    int64_t h = ((int64_t)best_rows * (int64_t)im.H) / im.sy_len;
-    r.tile_h = (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+  {
+    std::vector<Region> bodies, tails, others;
+    for (const Region& r0 : regs) {
+      if (r0.kind != REGION_STREAM) { others.push_back(r0); continue; }
+      const int th_b = tile_h_for(r0, body_src_rows);
+      const int th_t = tile_h_for(r0, std::min(tail_rows, body_src_rows));
+      const int hb = (th_b > th_t) ? body_rows_of(r0, th_b) : 0;   // no point in a body of tail-sized units
+      if (hb > 0) {
+        Region b = r0;
+        b.y1 = r0.y0 + hb;
+        b.tile_h = th_b;
+        bodies.push_back(b);
+      }
+      if (r0.y0 + hb < r0.y1) {
+        Region t = r0;
+        t.y0 = r0.y0 + hb;
+        t.tile_h = th_t;
+        tails.push_back(t);
+      }
+    }
+    regs.clear();
+    // order = hand-out order: bodies, then the per-pixel gather regions, then the small units
+    for (const Region& r : bodies) regs.push_back(r);
+    for (const Region& r : others) if (r.kind == REGION_GATHER) regs.push_back(r);
+    for (const Region& r : tails) regs.push_back(r);
+    for (const Region& r : others) if (r.kind != REGION_GATHER) regs.push_back(r);
+    if (regs.size() > STITCH_MAX_REGIONS) return false;
   }
   int unit = 0;
   plan->n_regions = (int)regs.size();

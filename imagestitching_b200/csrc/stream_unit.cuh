@@ -17,12 +17,13 @@
 namespace stitch {
 
 #ifndef STREAM_NST
-#define STREAM_NST 4  // ring depth == row-loop unroll: source rows in flight per lane
+#define STREAM_NST 8  // ring depth: source rows in flight per lane (power of two, multiple of STREAM_UNR)
 #endif
+#define STREAM_UNR 4  // rows per iteration of the unrolled row loop
 #define STREAM_STAGE_BYTES 512
 #define STREAM_STRIDE 31  // groups whose outputs a unit stores
 
-static_assert(STREAM_NST % 2 == 0, "the row table is read two rows at a time");
+static_assert(STREAM_NST % STREAM_UNR == 0 && (STREAM_NST & (STREAM_NST - 1)) == 0 && STREAM_UNR % 2 == 0, "ring layout");
 
 struct WarpSmem {
   alignas(128) uint8_t ring[STREAM_NST][STREAM_STAGE_BYTES];
@@ -162,7 +163,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   const uint32_t rs = (oy0 * sh) / dh;
   const uint32_t re = min(sh, udiv_ceil(oy1 * sh, dh));
   const int nrows = (int)(re - rs);
-  const int nrows_pad = (nrows + STREAM_NST - 1) / STREAM_NST * STREAM_NST;
+  const int nrows_pad = (nrows + STREAM_UNR - 1) / STREAM_UNR * STREAM_UNR;
   __syncwarp();  // every lane is done reading the previous unit's table
   build_row_table(ws.tab, lane, rs, nrows, nrows_pad, sh, dh, oy0, inv_sh);
 
@@ -209,20 +210,20 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   uint8_t* optr = P.out_rgba + (int64_t)(Y0 + (im.flip_y ? (int)(dh - 1 - oy0) : (int)oy0)) * P.out_pitch +
                   (int64_t)(X0 + (im.flip_x ? (int)dw - 1 - Xfirst : Xfirst)) * 4;
 
-  // ---- ring prologue: each lane stages its own 16 B per row, one commit group per row.  Rows are
-  // addressed by a 32-bit offset clamped to the unit's last row, so the refills need no predicate:
-  // past the end (and in lanes past the bitmap's last group) they re-read bytes that are then
-  // weighted with zero. ----
+  // ---- ring prologue: each lane stages its own 16 B per row; rows travel in pairs (one commit group
+  // per pair, STREAM_NST rows deep).  Rows are addressed by a 32-bit offset clamped to the unit's last
+  // row, so the refills need no predicate: past the end (and in lanes past the bitmap's last group)
+  // they re-read bytes that are then weighted with zero. ----
   const uint32_t pitch = (uint32_t)im.pitch;
   const uint8_t* lbase = im.data + (int64_t)rs * im.pitch + (int64_t)min(g, g_last) * 16;
   const uint32_t off_max = (uint32_t)(nrows - 1) * pitch;
   uint32_t off = 0;
   const uint32_t lring = smem_u32(&ws.ring[0][lane * 16]);
 #pragma unroll
-  for (int u = 0; u < STREAM_NST - 1; ++u) {
+  for (int u = 0; u < STREAM_NST; ++u) {
     cp_async16(lring + u * STREAM_STAGE_BYTES, lbase + off);
     off = min(off + pitch, off_max);
-    cp_async_commit();
+    if (u & 1) cp_async_commit();
   }
   __syncwarp();  // row table complete
 
@@ -231,74 +232,90 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   for (int k = 0; k < 12; ++k) acc[k] = 0.f;
   uint32_t and_acc = 0xffffffffu;
   const uint32_t tab_s = smem_u32(ws.tab);
+  uint32_t hoff = 0;  // byte offset of the ring part the current STREAM_UNR rows live in
 
-  for (int i = 0; i < nrows_pad; i += STREAM_NST) {
-    float4 t2;
+  // One source row: vertical accumulate; when the row completes an output row (EMIT), the horizontal
+  // pass runs in registers and the accumulators restart with the row's share of the next output row.
+  auto row_step = [&](const uint4& px, const float wc, const float wn, const bool emit) {
+    if (PARTIAL) {
+      and_acc &= px.x;
+      and_acc &= (px.y | m1);
+      and_acc &= (px.z | m2);
+      and_acc &= (px.w | m3);
+    } else {
+      and_acc &= px.x & px.y;
+      and_acc &= px.z & px.w;
+    }
+    float f[12];
+    f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x);
+    f[3] = expand<0>(px.y); f[4] = expand<1>(px.y); f[5] = expand<2>(px.y);
+    f[6] = expand<0>(px.z); f[7] = expand<1>(px.z); f[8] = expand<2>(px.z);
+    f[9] = expand<0>(px.w); f[10] = expand<1>(px.w); f[11] = expand<2>(px.w);
 #pragma unroll
-    for (int u = 0; u < STREAM_NST; ++u) {
-      if ((u & 1) == 0) t2 = lds128f(tab_s + (uint32_t)(i + u) * 8u);  // table entries of rows i+u, i+u+1
-      const float wc = (u & 1) ? t2.z : t2.x, wn = (u & 1) ? t2.w : t2.y;
-      // refill the slot that was read one step ago (its pixels are in registers by now) with row
-      // i+u+NST-1, then wait for row i+u: NST-1 copies stay in flight per lane
-      cp_async16(lring + ((u + STREAM_NST - 1) % STREAM_NST) * STREAM_STAGE_BYTES, lbase + off);
-      off = min(off + pitch, off_max);
-      cp_async_commit();
-      cp_async_wait<STREAM_NST - 1>();  // row i+u has landed (this lane's own copy)
-      const uint4 px = lds128(lring + u * STREAM_STAGE_BYTES);
-      if (PARTIAL) {
-        and_acc &= px.x;
-        and_acc &= (px.y | m1);
-        and_acc &= (px.z | m2);
-        and_acc &= (px.w | m3);
-      } else {
-        and_acc &= px.x & px.y;
-        and_acc &= px.z & px.w;
-      }
-      float f[12];
-      f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x);
-      f[3] = expand<0>(px.y); f[4] = expand<1>(px.y); f[5] = expand<2>(px.y);
-      f[6] = expand<0>(px.z); f[7] = expand<1>(px.z); f[8] = expand<2>(px.z);
-      f[9] = expand<0>(px.w); f[10] = expand<1>(px.w); f[11] = expand<2>(px.w);
+    for (int k = 0; k < 12; k += 2) fma2_s(acc[k], acc[k + 1], f[k], f[k + 1], wc);
+    if (emit) {
+      uint32_t q[MAXO][3];
 #pragma unroll
-      for (int k = 0; k < 12; k += 2) fma2_s(acc[k], acc[k + 1], f[k], f[k + 1], wc);
-      if (wn >= 0.f) {
-        // ---- an output row is complete: horizontal pass in registers ----
-        uint32_t q[MAXO][3];
+      for (int ch = 0; ch < 3; ++ch) {
+        float prev = wprev[0] * acc[ch];
 #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-          float prev = wprev[0] * acc[ch];
+        for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], acc[c * 3 + ch], prev);
+        const float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
+        float out[MAXO];
+        // outputs in pairs: (out[o], out[o+1]) = sum_c (w[o][c], w[o+1][c]) * acc[c]
 #pragma unroll
-          for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], acc[c * 3 + ch], prev);
-          const float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
-          float out[MAXO];
-          // outputs in pairs: (out[o], out[o+1]) = sum_c (w[o][c], w[o+1][c]) * acc[c]
+        for (int o = 0; o + 1 < MAXO; o += 2) {
+          mul2_s(out[o], out[o + 1], w[o][0], w[o + 1][0], acc[ch]);
 #pragma unroll
-          for (int o = 0; o + 1 < MAXO; o += 2) {
-            mul2_s(out[o], out[o + 1], w[o][0], w[o + 1][0], acc[ch]);
-#pragma unroll
-            for (int c = 1; c < 4; ++c) fma2_s(out[o], out[o + 1], w[o][c], w[o + 1][c], acc[c * 3 + ch]);
-            fma2_s(out[o], out[o + 1], last[o], last[o + 1], rcv);
-            if (ch == 2) quant2_neg(q[o][ch], q[o + 1][ch], out[o], out[o + 1]);
-            else quant2(q[o][ch], q[o + 1][ch], out[o], out[o + 1]);
-          }
-          if (MAXO & 1) {
-            const int o = MAXO - 1;
-            out[o] = w[o][0] * acc[ch];
-#pragma unroll
-            for (int c = 1; c < 4; ++c) out[o] = fmaf(w[o][c], acc[c * 3 + ch], out[o]);
-            out[o] = fmaf(last[o], rcv, out[o]);
-            q[o][ch] = (ch == 2) ? quant_bits_neg(out[o]) : quant_bits(out[o]);
-          }
+          for (int c = 1; c < 4; ++c) fma2_s(out[o], out[o + 1], w[o][c], w[o + 1][c], acc[c * 3 + ch]);
+          fma2_s(out[o], out[o + 1], last[o], last[o + 1], rcv);
+          if (ch == 2) quant2_neg(q[o][ch], q[o + 1][ch], out[o], out[o + 1]);
+          else quant2(q[o][ch], q[o + 1][ch], out[o], out[o + 1]);
         }
+        if (MAXO & 1) {
+          const int o = MAXO - 1;
+          out[o] = w[o][0] * acc[ch];
 #pragma unroll
-        for (int o = 0; o < MAXO; ++o) {
-          const uint32_t v = pack_rgb(q[o][0], q[o][1], q[o][2]);
-          if (st_ok[o]) *reinterpret_cast<uint32_t*>(optr + o * xstep) = v;
+          for (int c = 1; c < 4; ++c) out[o] = fmaf(w[o][c], acc[c * 3 + ch], out[o]);
+          out[o] = fmaf(last[o], rcv, out[o]);
+          q[o][ch] = (ch == 2) ? quant_bits_neg(out[o]) : quant_bits(out[o]);
         }
-        optr += ystep;
-#pragma unroll
-        for (int k = 0; k < 12; k += 2) mul2_s(acc[k], acc[k + 1], f[k], f[k + 1], wn);
       }
+#pragma unroll
+      for (int o = 0; o < MAXO; ++o) {
+        const uint32_t v = pack_rgb(q[o][0], q[o][1], q[o][2]);
+        if (st_ok[o]) *reinterpret_cast<uint32_t*>(optr + o * xstep) = v;
+      }
+      optr += ystep;
+#pragma unroll
+      for (int k = 0; k < 12; k += 2) mul2_s(acc[k], acc[k + 1], f[k], f[k + 1], wn);
+    }
+  };
+
+  for (int i0 = 0; i0 < nrows_pad; i0 += 32) {
+    // which of the next 32 rows complete an output row: one ballot, so the per-row branch below is on
+    // a warp-uniform mask and needs no reconvergence scaffolding around the shuffles
+    const bool fl = (i0 + lane < nrows_pad) && (ws.tab[i0 + lane].y >= 0.f);
+    uint32_t mask = __ballot_sync(0xffffffffu, fl);
+    const int i1 = min(i0 + 32, nrows_pad);
+    for (int i = i0; i < i1; i += STREAM_UNR) {
+      const uint32_t ring_h = lring + hoff;
+#pragma unroll
+      for (int u = 0; u < STREAM_UNR; u += 2) {
+        const float4 t2 = lds128f(tab_s + (uint32_t)(i + u) * 8u);  // table entries of rows i+u, i+u+1
+        cp_async_wait<STREAM_NST / 2 - 1>();  // rows i+u, i+u+1 have landed (this lane's own copies)
+        const uint4 pa = lds128(ring_h + u * STREAM_STAGE_BYTES);
+        const uint4 pb = lds128(ring_h + (u + 1) * STREAM_STAGE_BYTES);
+        cp_async16(ring_h + u * STREAM_STAGE_BYTES, lbase + off);  // rows i+u+NST, i+u+1+NST
+        off = min(off + pitch, off_max);
+        cp_async16(ring_h + (u + 1) * STREAM_STAGE_BYTES, lbase + off);
+        off = min(off + pitch, off_max);
+        cp_async_commit();
+        row_step(pa, t2.x, t2.y, (mask >> u) & 1u);
+        row_step(pb, t2.z, t2.w, (mask >> (u + 1)) & 1u);
+      }
+      mask >>= STREAM_UNR;
+      hoff = (hoff + STREAM_UNR * STREAM_STAGE_BYTES) & (STREAM_NST * STREAM_STAGE_BYTES - 1);
     }
   }
   // Translucent bitmaps (rare: photos are opaque): the unit is redone with the exact premultiplied
