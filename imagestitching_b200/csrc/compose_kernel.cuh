@@ -37,15 +37,71 @@
 namespace stitch {
 
 #ifndef STREAM_MINB
-#define STREAM_MINB 3  // resident CTAs per SM the register allocation targets
+#define STREAM_MINB 2  // resident CTAs per SM the register allocation targets (measured: 2 x 8 warps with 128 registers beats 3 x 8 with 80)
 #endif
 
 // Exact (gather) evaluation of one canvas pixel, kept out of line so the rare slow path does not
 // inflate the streaming loop's register allocation.
-__device__ __noinline__ uint32_t shade_px(const JobParam& P, int x, int y) {
-  float Rr, Gg, Bb;
-  shade(P, x, y, Rr, Gg, Bb);
-  return q8(Rr) | (q8(Gg) << 8) | (q8(Bb) << 16) | 0xff000000u;
+__device__ __noinline__ void shade_rgb(const JobParam& P, int x, int y, float* rgb) {
+  shade(P, x, y, rgb[0], rgb[1], rgb[2]);
+}
+__device__ __forceinline__ uint32_t shade_px(const JobParam& P, int x, int y) {
+  float c[3];
+  shade_rgb(P, x, y, c);
+  return q8(c[0]) | (q8(c[1]) << 8) | (q8(c[2]) << 16) | 0xff000000u;
+}
+
+// One 2x2 chroma block (bx, by) of the canvas, evaluated exactly: optional RGBA and Y for the
+// block's pixels inside [x0,x1) x [y0,y1), and Cb/Cr with edge replication.
+template <bool RGBA, bool LUMA, bool CHROMA>
+__device__ __forceinline__ void shade_block(const JobParam& P, int bx, int by, int x0, int y0, int x1, int y1) {
+  float cb = 0.f, cr = 0.f;
+#pragma unroll
+  for (int dy = 0; dy < 2; ++dy) {
+#pragma unroll
+    for (int dx = 0; dx < 2; ++dx) {
+      const int xx = bx * 2 + dx, yy = by * 2 + dy;
+      const int x = min(xx, P.cw - 1), y = min(yy, P.ch - 1);  // edge replication for odd sizes
+      const bool inside = xx >= x0 && xx < x1 && yy >= y0 && yy < y1;
+      if (!CHROMA && !inside) continue;
+      float c[3];
+      shade_rgb(P, x, y, c);
+      if (inside) {
+        if (LUMA) P.out_y[(int64_t)y * P.cw + x] = (uint8_t)q8(0.299f * c[0] + 0.587f * c[1] + 0.114f * c[2]);
+        if (RGBA)
+          *reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch + (int64_t)x * 4) =
+              q8(c[0]) | (q8(c[1]) << 8) | (q8(c[2]) << 16) | 0xff000000u;
+      }
+      cb += 128.f - 0.168736f * c[0] - 0.331264f * c[1] + 0.5f * c[2];
+      cr += 128.f + 0.5f * c[0] - 0.418688f * c[1] - 0.081312f * c[2];
+    }
+  }
+  if (CHROMA) {
+    const int cwh = (P.cw + 1) >> 1;
+    P.out_cb[(int64_t)by * cwh + bx] = (uint8_t)q8(cb * 0.25f);
+    P.out_cr[(int64_t)by * cwh + bx] = (uint8_t)q8(cr * 0.25f);
+  }
+}
+
+// Exact re-evaluation of the canvas rect [x0,x1) x [y0,y1) by one warp (a streaming unit that met
+// translucent pixels).  With chroma output y0/y1 are even and the unit owns the chroma blocks whose
+// first pixel in source order -- even canvas x, odd when the image is mirrored -- lies in [x0,x1).
+template <int MODE>
+__device__ __noinline__ void redo_rect(const JobParam& P, int x0, int y0, int x1, int y1, int lane, int key_odd) {
+  if (MODE == 0) {
+    for (int y = y0; y < y1; ++y) {
+      uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
+      for (int x = x0 + lane; x < x1; x += 32) row[x] = shade_px(P, x, y);
+    }
+  } else {
+    const int bx0 = (x0 - key_odd) >> 1, bx1 = (x1 - 1) >> 1;   // blocks that touch the rect
+    for (int by = y0 >> 1; by < (y1 + 1) >> 1; ++by)
+      for (int bx = bx0 + lane; bx <= bx1; bx += 32) {
+        const int key = 2 * bx + key_odd;
+        if (key >= x0 && key < x1) shade_block<MODE == 2, true, true>(P, bx, by, x0, y0, x1, y1);
+        else shade_block<MODE == 2, true, false>(P, bx, by, x0, y0, x1, y1);
+      }
+  }
 }
 
 }  // namespace stitch
@@ -56,30 +112,56 @@ namespace stitch {
 
 static constexpr int kComposeSmemBytes = (int)sizeof(WarpSmem) * STREAM_WARPS;
 
+// FILL / GATHER units.  MODE 0: the region is a device pixel rect.  With chroma output (MODE 1, 2)
+// the region is a rect of 2x2 chroma BLOCKS, so no block is ever split between two units.
+template <int MODE>
 __device__ __forceinline__ void fill_unit(const JobParam& P, const Region& R, int tx, int ty, int lane) {
   const int x0 = R.x0 + tx * R.tile_w, x1 = min(x0 + R.tile_w, R.x1);
   const int y0 = R.y0 + ty * R.tile_h, y1 = min(y0 + R.tile_h, R.y1);
-  for (int y = y0; y < y1; ++y) {
-    uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
-    for (int x = x0 + lane; x < x1; x += 32) row[x] = 0xffffffffu;
+  if (MODE == 0) {
+    for (int y = y0; y < y1; ++y) {
+      uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
+      for (int x = x0 + lane; x < x1; x += 32) row[x] = 0xffffffffu;
+    }
+  } else {
+    const int cwh = (P.cw + 1) >> 1;
+    for (int by = y0; by < y1; ++by)
+      for (int bx = x0 + lane; bx < x1; bx += 32) {
+        P.out_cb[(int64_t)by * cwh + bx] = 128;
+        P.out_cr[(int64_t)by * cwh + bx] = 128;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) {
+          const int x = 2 * bx + (d & 1), y = 2 * by + (d >> 1);
+          if (x < P.cw && y < P.ch) {
+            P.out_y[(int64_t)y * P.cw + x] = 255;
+            if (MODE == 2) *reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch + (int64_t)x * 4) = 0xffffffffu;
+          }
+        }
+      }
   }
 }
 
+template <int MODE>
 __device__ __forceinline__ void gather_unit(const JobParam& P, const Region& R, int tx, int ty, int lane) {
   const int x0 = R.x0 + tx * R.tile_w, x1 = min(x0 + R.tile_w, R.x1);
   const int y0 = R.y0 + ty * R.tile_h, y1 = min(y0 + R.tile_h, R.y1);
-  for (int y = y0; y < y1; ++y) {
-    uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
-    for (int x = x0 + lane; x < x1; x += 32) row[x] = shade_px(P, x, y);
+  if (MODE == 0) {
+    for (int y = y0; y < y1; ++y) {
+      uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
+      for (int x = x0 + lane; x < x1; x += 32) row[x] = shade_px(P, x, y);
+    }
+  } else {
+    for (int by = y0; by < y1; ++by)
+      for (int bx = x0 + lane; bx < x1; bx += 32) shade_block<MODE == 2, true, true>(P, bx, by, 0, 0, P.cw, P.ch);
   }
 }
 
 // sched[0] = next unit to hand out, sched[1] = warps that have left the kernel; the last warp out
 // resets both, so back-to-back launches on one stream need no memset in between.
 //
-// MAXO = max over the job's streaming regions of ceil(4 / ratio_x); PARTIAL = some streamed bitmap's
-// width is not a multiple of 4 (stream_unit.cuh).
-template <int MAXO, bool PARTIAL>
+// MAXO = max over the job's streaming regions of ceil(4 / ratio_x); MODE = STREAM_MODE_* (RGBA
+// canvas, I420 planes, or both).
+template <int MAXO, int MODE>
 __global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
 compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -102,11 +184,11 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
     const int local = (int)unit - R.first_unit;
     const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
     if (R.kind == REGION_STREAM) {
-      stream_unit<MAXO, PARTIAL>(P, R, tx, ty, ws, lane);
+      stream_unit<MAXO, MODE>(P, R, tx, ty, ws, lane);
     } else if (R.kind == REGION_FILL) {
-      fill_unit(P, R, tx, ty, lane);
+      fill_unit<MODE>(P, R, tx, ty, lane);
     } else {
-      gather_unit(P, R, tx, ty, lane);
+      gather_unit<MODE>(P, R, tx, ty, lane);
     }
   }
   if (lane == 0) {

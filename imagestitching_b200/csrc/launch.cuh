@@ -51,14 +51,27 @@ inline int stream_max_tile_h(const ImgParam& im) {
 // rect integer-aligned (superSample == 1 and gap*scaleDown integral, true for BASELINE configs 2-5)
 // and the clipped rects pairwise disjoint, so painter's-order source-over degenerates to each
 // pixel belonging to at most one image.
-inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
-  struct Box { int x0, y0, x1, y1, img; };
+//
+// mode = STREAM_MODE_*.  With chroma output the partition is made on the grid of 2x2 chroma blocks
+// (cell size 2): a streamed image keeps the largest block-aligned box inside its rect and the odd
+// rows / columns along its edges -- blocks shared with a neighbour or the background -- go to
+// per-block GATHER regions, so no chroma block is ever split between two units.
+inline bool build_plan(const JobParam& P, int mode, int resident_warps, Plan* plan) {
+  const int cs = (mode == STREAM_MODE_RGBA) ? 1 : 2;                  // cell size in pixels
+  const int stride = STREAM_STRIDE_OF(mode);
+  const int ccw = (P.cw + cs - 1) / cs, cch = (P.ch + cs - 1) / cs;   // canvas in cells
+  struct Box { int x0, y0, x1, y1, img; bool stream; int ix0, iy0, ix1, iy1, ox0, oy0, ox1, oy1; };
   std::vector<Box> boxes;
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
     if (!is_int(im.X0) || !is_int(im.Y0) || !is_int(im.W) || !is_int(im.H)) return false;
     if (im.x_hi <= im.x_lo || im.y_hi <= im.y_lo) continue;  // nothing visible
-    boxes.push_back({im.x_lo, im.y_lo, im.x_hi, im.y_hi, k});
+    Box b{};
+    b.x0 = im.x_lo; b.y0 = im.y_lo; b.x1 = im.x_hi; b.y1 = im.y_hi; b.img = k;
+    b.ix0 = (b.x0 + cs - 1) / cs; b.iy0 = (b.y0 + cs - 1) / cs; b.ix1 = b.x1 / cs; b.iy1 = b.y1 / cs;   // inner, in cells
+    b.ox0 = b.x0 / cs; b.oy0 = b.y0 / cs; b.ox1 = (b.x1 + cs - 1) / cs; b.oy1 = (b.y1 + cs - 1) / cs;   // outer, in cells
+    b.stream = stream_eligible(im) && b.ix0 < b.ix1 && b.iy0 < b.iy1 && (cs == 1 || stream_max_tile_h(im) >= 2);
+    boxes.push_back(b);
   }
   for (size_t a = 0; a < boxes.size(); ++a)
     for (size_t b = a + 1; b < boxes.size(); ++b)
@@ -66,66 +79,70 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
         return false;
 
   std::vector<Region> regs;
-  // heavy first: streaming regions, then gather, then fill
-  for (int pass = 0; pass < 2; ++pass) {
-    for (const Box& bx : boxes) {
-      const ImgParam& im = P.img[bx.img];
-      const bool se = stream_eligible(im);
-      if ((pass == 0) != se) continue;
-      Region r{};
-      r.img = bx.img;
-      if (se) {
-        const int dw = (int)im.W, dh = (int)im.H, X0 = (int)im.X0, Y0 = (int)im.Y0;
-        int rx0 = bx.x0 - X0, rx1 = bx.x1 - X0, ry0 = bx.y0 - Y0, ry1 = bx.y1 - Y0;  // device-relative
-        if (im.flip_x) { int t = dw - rx1; rx1 = dw - rx0; rx0 = t; }
-        if (im.flip_y) { int t = dh - ry1; ry1 = dh - ry0; ry0 = t; }
-        r.kind = REGION_STREAM;
-        r.x0 = rx0; r.x1 = rx1; r.y0 = ry0; r.y1 = ry1;
-        // bands in group space: unit tx stores the outputs that start in groups g_base + 31*tx ... + 30
-        const int64_t sw = im.sx_len;
-        r.g_base = (int)((((int64_t)rx0 * sw) / dw) >> 2);
-        const int g_end = (int)std::min<int64_t>(((int64_t)rx1 * sw + 4 * dw - 1) / (4 * dw), (sw + 3) >> 2);
-        r.tile_w = 0;
-        r.tiles_x = std::max(1, (g_end - r.g_base + STREAM_STRIDE - 1) / STREAM_STRIDE);
-        r.tile_h = stream_max_tile_h(im);   // refined below for load balance
-      } else {
-        r.kind = REGION_GATHER;
-        r.x0 = bx.x0; r.x1 = bx.x1; r.y0 = bx.y0; r.y1 = bx.y1;
-        r.tile_w = 32;
-        r.tile_h = 8;
-      }
-      regs.push_back(r);
-    }
+  // streaming regions: the inner box of every eligible image
+  for (const Box& bx : boxes) {
+    if (!bx.stream) continue;
+    const ImgParam& im = P.img[bx.img];
+    Region r{};
+    r.img = bx.img;
+    const int dw = (int)im.W, dh = (int)im.H, X0 = (int)im.X0, Y0 = (int)im.Y0;
+    int rx0 = bx.ix0 * cs - X0, rx1 = bx.ix1 * cs - X0, ry0 = bx.iy0 * cs - Y0, ry1 = bx.iy1 * cs - Y0;  // device-relative
+    if (im.flip_x) { int t = dw - rx1; rx1 = dw - rx0; rx0 = t; }
+    if (im.flip_y) { int t = dh - ry1; ry1 = dh - ry0; ry0 = t; }
+    r.kind = REGION_STREAM;
+    r.x0 = rx0; r.x1 = rx1; r.y0 = ry0; r.y1 = ry1;
+    // bands in group space: unit tx stores the outputs that start in groups g_base + stride*tx ...
+    const int64_t sw = im.sx_len;
+    r.g_base = (int)((((int64_t)rx0 * sw) / dw) >> 2);
+    const int g_end = (int)std::min<int64_t>(((int64_t)rx1 * sw + 4 * dw - 1) / (4 * dw), (sw + 3) >> 2);
+    r.tile_w = 0;
+    r.tiles_x = std::max(1, (g_end - r.g_base + stride - 1) / stride);
+    r.tile_h = stream_max_tile_h(im);   // refined below for load balance
+    regs.push_back(r);
   }
-  // white background = complement of the boxes: sweep horizontal bands between all y edges
-  std::vector<int> ys{0, P.ch};
-  for (const Box& b : boxes) { ys.push_back(b.y0); ys.push_back(b.y1); }
+  // the rest of the canvas, in cells: sweep the bands between all y edges; inside a band cut at all x
+  // edges; a piece is GATHER when some image's rect reaches into it, FILL (white, P:1423-1424) otherwise
+  std::vector<int> ys{0, cch};
+  for (const Box& b : boxes) { ys.push_back(b.oy0); ys.push_back(b.oy1); ys.push_back(b.iy0); ys.push_back(b.iy1); }
   std::sort(ys.begin(), ys.end());
   ys.erase(std::unique(ys.begin(), ys.end()), ys.end());
-  std::vector<Region> fills;
+  std::vector<Region> rest;
   for (size_t i = 0; i + 1 < ys.size(); ++i) {
     const int ya = ys[i], yb = ys[i + 1];
-    if (ya < 0 || yb > P.ch || ya >= yb) continue;
-    std::vector<std::pair<int, int>> spans;
+    if (ya < 0 || yb > cch || ya >= yb) continue;
+    std::vector<int> xs{0, ccw};
     for (const Box& b : boxes)
-      if (b.y0 <= ya && b.y1 >= yb) spans.push_back({b.x0, b.x1});
-    std::sort(spans.begin(), spans.end());
-    int x = 0;
-    auto add = [&](int xa, int xb) {
-      if (xa >= xb) return;
-      // merge with a fill of identical x-range that ends where this band starts
-      for (Region& f : fills)
-        if (f.x0 == xa && f.x1 == xb && f.y1 == ya) { f.y1 = yb; return; }
+      if (b.oy0 < yb && b.oy1 > ya) { xs.push_back(b.ox0); xs.push_back(b.ox1); xs.push_back(b.ix0); xs.push_back(b.ix1); }
+    std::sort(xs.begin(), xs.end());
+    xs.erase(std::unique(xs.begin(), xs.end()), xs.end());
+    int run_kind = -1, run_x0 = 0, run_x1 = 0;
+    auto flush = [&]() {
+      if (run_kind < 0) return;
+      // merge with a region of the same kind and x-range that ends where this band starts
+      for (Region& f : rest)
+        if (f.kind == run_kind && f.x0 == run_x0 && f.x1 == run_x1 && f.y1 == ya) { f.y1 = yb; run_kind = -1; return; }
       Region r{};
-      r.kind = REGION_FILL; r.img = -1;
-      r.x0 = xa; r.x1 = xb; r.y0 = ya; r.y1 = yb;
-      r.tile_w = 256; r.tile_h = 8;
-      fills.push_back(r);
+      r.kind = run_kind; r.img = -1;
+      r.x0 = run_x0; r.x1 = run_x1; r.y0 = ya; r.y1 = yb;
+      if (run_kind == REGION_FILL) { r.tile_w = 256; r.tile_h = 8; }
+      else { r.tile_w = 32; r.tile_h = (cs == 1) ? 8 : 4; }
+      rest.push_back(r);
+      run_kind = -1;
     };
-    for (auto& s : spans) { add(x, s.first); x = std::max(x, s.second); }
-    add(x, P.cw);
+    for (size_t j = 0; j + 1 < xs.size(); ++j) {
+      const int xa = xs[j], xb = xs[j + 1];
+      if (xa < 0 || xb > ccw || xa >= xb) continue;
+      int kind = REGION_FILL;
+      for (const Box& b : boxes) {
+        if (b.stream && b.ix0 <= xa && b.ix1 >= xb && b.iy0 <= ya && b.iy1 >= yb) { kind = -1; break; }  // streamed
+        if (b.ox0 < xb && b.ox1 > xa && b.oy0 < yb && b.oy1 > ya) kind = REGION_GATHER;
+      }
+      if (kind != run_kind || xa != run_x1) { flush(); run_kind = kind; run_x0 = xa; }
+      run_x1 = xb;
+    }
+    flush();
   }
-  for (Region& f : fills) regs.push_back(f);
+  for (Region& f : rest) regs.push_back(f);
   if (regs.size() > STITCH_MAX_REGIONS) return false;
 
   // Unit heights of the streaming regions -- a "guided" schedule.  Units are handed out in order to
@@ -140,7 +157,8 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   auto tile_h_for = [&](const Region& r, int src_rows) {
     const ImgParam& im = P.img[r.img];
     const int64_t h = ((int64_t)src_rows * (int64_t)im.H) / im.sy_len;
-    return (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+    const int th = (int)std::max<int64_t>(1, std::min<int64_t>(h, stream_max_tile_h(im)));
+    return cs == 1 ? th : std::max(2, th & ~1);   // chroma rows come in pairs
   };
   auto body_rows_of = [&](const Region& r, int th) {   // output rows of the region that go to whole body units
     const int64_t H = r.y1 - r.y0;
@@ -211,17 +229,17 @@ inline bool build_plan(const JobParam& P, int resident_warps, Plan* plan) {
   return unit > 0;
 }
 
-template <int MAXO, bool PARTIAL>
+template <int MAXO, int MODE>
 struct ComposeLaunch {
   // resident CTAs per SM of this instantiation (queried once), 0 on error
   static int ctas_per_sm(cudaError_t* err) {
     static int value = -1;
     if (value < 0) {
-      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, PARTIAL>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            kComposeSmemBytes);
       int n = 0;
       if (e == cudaSuccess)
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, PARTIAL>, STREAM_WARPS * 32,
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, MODE>, STREAM_WARPS * 32,
                                                           kComposeSmemBytes);
       if (e != cudaSuccess) { *err = e; return 0; }
       value = n < 1 ? 1 : n;
@@ -229,44 +247,41 @@ struct ComposeLaunch {
     return value;
   }
   static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
-    compose_kernel<MAXO, PARTIAL><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
+    compose_kernel<MAXO, MODE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
     return cudaGetLastError();
   }
 };
 
-inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScratch& scratch, cudaStream_t stream,
-                      int* launches, int* path_info) {
+// The draw loop of one job as ONE launch.  path_info: streaming | gather << 8 | fill << 16 region
+// counts of the fused plan, or 1 << 24 when the whole canvas took the per-pixel gather kernel
+// (fractional device rects, overlapping images).
+inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_count, StreamScratch& scratch,
+                      cudaStream_t stream, int* launches, int* path_info) {
   *launches = 0;
   *path_info = 1 << 24;
-  if (want_yuv) {
-    dim3 grid(((P.cw + 1) / 2 + 31) / 32, ((P.ch + 1) / 2 + 7) / 8);
-    gather_yuv_kernel<<<grid, 256, 0, stream>>>(P);
-    *launches = 1;
-    return (int)cudaGetLastError();
-  }
+  const int mode = want_yuv ? (want_rgba ? STREAM_MODE_BOTH : STREAM_MODE_YUV) : STREAM_MODE_RGBA;
   // kernel variant: decided by the images alone (before the unit grid is chosen)
   int maxo = 2;
-  bool partial = false;
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
     if (!is_int(im.W) || !is_int(im.H) || im.W < 1 || im.H < 1 || !stream_eligible(im)) continue;
     const int64_t dw = (int64_t)im.W;
     maxo = std::max(maxo, (int)std::min<int64_t>(4, (4 * dw + im.sx_len - 1) / im.sx_len));
-    partial = partial || (im.sx_len & 3) != 0;
   }
   cudaError_t err = cudaSuccess;
   int per_sm = 0;
-#define STITCH_DISPATCH(M, Pt, expr) \
-  if (maxo == M && partial == Pt) { using K = ComposeLaunch<M, Pt>; expr; }
-#define STITCH_ALL(expr)                                                                                        \
-  STITCH_DISPATCH(2, false, expr) STITCH_DISPATCH(3, false, expr) STITCH_DISPATCH(4, false, expr) \
-  STITCH_DISPATCH(2, true, expr) STITCH_DISPATCH(3, true, expr) STITCH_DISPATCH(4, true, expr)
+#define STITCH_DISPATCH(M, Md, expr) \
+  if (maxo == M && mode == Md) { using K = ComposeLaunch<M, Md>; expr; }
+#define STITCH_ALL(expr)                                                                     \
+  STITCH_DISPATCH(2, 0, expr) STITCH_DISPATCH(3, 0, expr) STITCH_DISPATCH(4, 0, expr)        \
+  STITCH_DISPATCH(2, 1, expr) STITCH_DISPATCH(3, 1, expr) STITCH_DISPATCH(4, 1, expr)        \
+  STITCH_DISPATCH(2, 2, expr) STITCH_DISPATCH(3, 2, expr) STITCH_DISPATCH(4, 2, expr)
   STITCH_ALL(per_sm = K::ctas_per_sm(&err))
   if (err != cudaSuccess) return (int)err;
   const int resident_warps = sm_count * per_sm * STREAM_WARPS;
 
   Plan plan;
-  if (build_plan(P, resident_warps, &plan)) {
+  if (build_plan(P, mode, resident_warps, &plan)) {
     if (!scratch.p) {  // unit scheduler counters {next unit, warps retired}; the kernel leaves them at zero
       cudaError_t e = cudaMalloc(&scratch.p, 256);
       if (e != cudaSuccess) return (int)e;
@@ -276,7 +291,7 @@ inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScra
     }
     int cnt[3] = {0, 0, 0};
     for (int i = 0; i < plan.n_regions; ++i) cnt[plan.r[i].kind]++;
-    *path_info = cnt[REGION_STREAM] | (cnt[REGION_GATHER] << 8) | (cnt[REGION_FILL] << 16);
+    *path_info = std::min(cnt[REGION_STREAM], 255) | (std::min(cnt[REGION_GATHER], 255) << 8) | (std::min(cnt[REGION_FILL], 255) << 16);
     // persistent grid: every resident warp slot of the chip, capped by the number of units
     int grid = sm_count * per_sm;
     const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
@@ -288,8 +303,13 @@ inline int launch_job(const JobParam& P, bool want_yuv, int sm_count, StreamScra
   }
 #undef STITCH_ALL
 #undef STITCH_DISPATCH
-  dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
-  gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
+  if (want_yuv) {
+    dim3 grid(((P.cw + 1) / 2 + 31) / 32, ((P.ch + 1) / 2 + 7) / 8);
+    gather_yuv_kernel<<<grid, 256, 0, stream>>>(P);
+  } else {
+    dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
+    gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
+  }
   *launches = 1;
   return (int)cudaGetLastError();
 }

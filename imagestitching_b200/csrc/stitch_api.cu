@@ -244,7 +244,7 @@ int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
   // [4] the draw loop (P:1439-1572) as fused launches
   int launches = 0;
   int path_info = 0;
-  st = stitch::launch_job(P, want_yuv, ctx->sm_count, ctx->scratch, ctx->stream, &launches, &path_info);
+  st = stitch::launch_job(P, want_rgba, want_yuv, ctx->sm_count, ctx->scratch, ctx->stream, &launches, &path_info);
   res->path_info = path_info;
   if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
   ctx->launches += launches;

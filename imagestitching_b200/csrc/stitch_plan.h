@@ -49,7 +49,7 @@ struct Region {
   int32_t g_base;            // STREAM: first 4-pixel source group of the region; unit tx owns groups g_base + 31*tx ...
 };
 
-#define STITCH_MAX_REGIONS 64
+#define STITCH_MAX_REGIONS 128
 #define STREAM_TAB_MAX 288   // row-table entries per warp
 #define STREAM_WARPS 8
 

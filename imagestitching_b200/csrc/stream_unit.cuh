@@ -21,7 +21,13 @@ namespace stitch {
 #endif
 #define STREAM_UNR 4  // rows per iteration of the unrolled row loop
 #define STREAM_STAGE_BYTES 512
-#define STREAM_STRIDE 31  // groups whose outputs a unit stores
+// Output modes of the fused launch
+#define STREAM_MODE_RGBA 0  // RGBA8 canvas
+#define STREAM_MODE_YUV 1   // planar I420 only (U:205-242 export feeding a JPEG encoder)
+#define STREAM_MODE_BOTH 2  // RGBA8 canvas and I420
+// groups whose outputs a unit stores: 31 (lane 31 only supplies lane 30's tail); 30 when chroma is
+// produced, so that lane 30's outputs are complete too and can pair with lane 29's last output
+#define STREAM_STRIDE_OF(MODE) ((MODE) == STREAM_MODE_RGBA ? 31 : 30)
 
 static_assert(STREAM_NST % STREAM_UNR == 0 && (STREAM_NST & (STREAM_NST - 1)) == 0 && STREAM_UNR % 2 == 0, "ring layout");
 
@@ -37,7 +43,7 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 // the copy's shared-memory write lands a global-memory latency later, so no barrier is needed and
 // no other lane ever touches the slot.
 __device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
-  asm volatile("cp.async.cg.shared.global.L2::128B [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
+  asm volatile("cp.async.cg.shared.global.L2::256B [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -147,10 +153,10 @@ __device__ __forceinline__ void build_row_table(float2* tab, int lane, uint32_t 
 
 // MAXO = max number of outputs that can START inside one 4-pixel source group = ceil(4 / ratio_x):
 // 2 for ratio_x > 2 (the 9x12MP config), 3 for ratio_x > 4/3, 4 for ratio_x > 1.
-// PARTIAL = some streamed bitmap has a width that is not a multiple of 4: the columns of its last
-// group that lie in the row padding are masked out of the alpha check.
+// MODE = STREAM_MODE_*.  With chroma output the host aligns the region to even canvas coordinates and
+// makes tile_h even, so every 2x2 chroma block lies inside one unit (launch.cuh).
 // All geometry is unsigned 32-bit; launch.cuh only admits images whose scaled coordinates fit.
-template <int MAXO, bool PARTIAL>
+template <int MAXO, int MODE>
 __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, int tx, int ty, WarpSmem& ws, int lane) {
   const ImgParam& im = P.img[R.img];
   const uint32_t sw = (uint32_t)im.sx_len, sh = (uint32_t)im.sy_len;
@@ -168,7 +174,9 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   build_row_table(ws.tab, lane, rs, nrows, nrows_pad, sh, dh, oy0, inv_sh);
 
   // ---- horizontal: this lane's 4-pixel source group and the outputs that start in it ----
-  const uint32_t g = (uint32_t)(R.g_base + tx * STREAM_STRIDE + lane);
+  constexpr int STRIDE = STREAM_STRIDE_OF(MODE);
+  constexpr bool RGBA = MODE != STREAM_MODE_YUV, YUV = MODE != STREAM_MODE_RGBA;
+  const uint32_t g = (uint32_t)(R.g_base + tx * STRIDE + lane);
   const uint32_t g_last = (sw + 3) / 4 - 1;
   const uint32_t c0 = 4u * g * dw;  // group start, in source units scaled by dw
   const int Xfirst = (int)udiv_ceil(c0, sw);
@@ -195,20 +203,43 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
 #pragma unroll
   for (int o = 0; o < MAXO; ++o) {
     const int X = Xfirst + o;
-    st_ok[o] = (o < cnt) && (X >= R.x0) && (X < R.x1);
+    st_ok[o] = (lane < STRIDE) && (o < cnt) && (X >= R.x0) && (X < R.x1);
     last[o] = (o == cnt - 1) ? 1.f : 0.f;
   }
-  uint32_t m1 = 0, m2 = 0, m3 = 0;
-  if (PARTIAL) {  // columns past the bitmap edge (row padding) must not trip the alpha check
-    m1 = (4 * g + 1 >= sw) ? 0xff000000u : 0u;
-    m2 = (4 * g + 2 >= sw) ? 0xff000000u : 0u;
-    m3 = (4 * g + 3 >= sw) ? 0xff000000u : 0u;
-  }
-  // output pointer walks with the rows: device position of this lane's output 0, +-4 bytes per output
-  const int xstep = im.flip_x ? -4 : 4;
+  // columns past the bitmap edge (row padding) must not trip the alpha check
+  const uint32_t m1 = (4 * g + 1 >= sw) ? 0xff000000u : 0u, m2 = (4 * g + 2 >= sw) ? 0xff000000u : 0u,
+                 m3 = (4 * g + 3 >= sw) ? 0xff000000u : 0u;
+  // output pointers walk with the rows: device position of this lane's output 0, +-1 pixel per output
+  const int xdir = im.flip_x ? -1 : 1;
+  const int cx0 = X0 + (im.flip_x ? (int)dw - 1 - Xfirst : Xfirst);      // canvas x of output 0
+  const int cy0 = Y0 + (im.flip_y ? (int)(dh - 1 - oy0) : (int)oy0);      // canvas y of the unit's first output row
+  const int xstep = 4 * xdir;
   const int64_t ystep = im.flip_y ? -P.out_pitch : P.out_pitch;
-  uint8_t* optr = P.out_rgba + (int64_t)(Y0 + (im.flip_y ? (int)(dh - 1 - oy0) : (int)oy0)) * P.out_pitch +
-                  (int64_t)(X0 + (im.flip_x ? (int)dw - 1 - Xfirst : Xfirst)) * 4;
+  uint8_t* optr = RGBA ? P.out_rgba + (int64_t)cy0 * P.out_pitch + (int64_t)cx0 * 4 : nullptr;
+  // I420: Y walks like the canvas; chroma is finished on every second emitted row.  Output o is the
+  // FIRST (in source order) of its horizontal pair when its canvas x is even (odd when mirrored); the
+  // lane that owns the first element stores the pair's chroma, its partner is output o+1 -- the next
+  // one in this lane or the first one of the right neighbour.
+  uint8_t* yptr = nullptr;
+  uint8_t *cbptr = nullptr, *crptr = nullptr;
+  int64_t ystep_y = 0, cstep = 0;
+  bool c_own[MAXO];
+  float ccb[MAXO], ccr[MAXO];  // vertical sums of the un-rounded chroma of the current block row
+  bool second = false;          // the next emitted row completes a chroma row
+  if (YUV) {
+    const int cwh = (P.cw + 1) >> 1;
+    yptr = P.out_y + (int64_t)cy0 * P.cw + cx0;
+    ystep_y = im.flip_y ? -(int64_t)P.cw : (int64_t)P.cw;
+    cbptr = P.out_cb + (int64_t)(cy0 >> 1) * cwh + (cx0 >> 1);
+    crptr = P.out_cr + (int64_t)(cy0 >> 1) * cwh + (cx0 >> 1);
+    cstep = im.flip_y ? -(int64_t)cwh : (int64_t)cwh;
+#pragma unroll
+    for (int o = 0; o < MAXO; ++o) {
+      const int cx = cx0 + o * xdir;
+      c_own[o] = st_ok[o] && ((cx & 1) == (im.flip_x ? 1 : 0));
+      ccb[o] = ccr[o] = 0.f;
+    }
+  }
 
   // ---- ring prologue: each lane stages its own 16 B per row; rows travel in pairs (one commit group
   // per pair, STREAM_NST rows deep).  Rows are addressed by a 32-bit offset clamped to the unit's last
@@ -237,15 +268,10 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   // One source row: vertical accumulate; when the row completes an output row (EMIT), the horizontal
   // pass runs in registers and the accumulators restart with the row's share of the next output row.
   auto row_step = [&](const uint4& px, const float wc, const float wn, const bool emit) {
-    if (PARTIAL) {
-      and_acc &= px.x;
-      and_acc &= (px.y | m1);
-      and_acc &= (px.z | m2);
-      and_acc &= (px.w | m3);
-    } else {
-      and_acc &= px.x & px.y;
-      and_acc &= px.z & px.w;
-    }
+    and_acc &= px.x;
+    and_acc &= (px.y | m1);
+    and_acc &= (px.z | m2);
+    and_acc &= (px.w | m3);
     float f[12];
     f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x);
     f[3] = expand<0>(px.y); f[4] = expand<1>(px.y); f[5] = expand<2>(px.y);
@@ -254,39 +280,83 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
 #pragma unroll
     for (int k = 0; k < 12; k += 2) fma2_s(acc[k], acc[k + 1], f[k], f[k + 1], wc);
     if (emit) {
-      uint32_t q[MAXO][3];
+      float out[3][MAXO];  // un-rounded outputs, still in the 1 + v * 2^-15 form
 #pragma unroll
       for (int ch = 0; ch < 3; ++ch) {
         float prev = wprev[0] * acc[ch];
 #pragma unroll
         for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], acc[c * 3 + ch], prev);
         const float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
-        float out[MAXO];
         // outputs in pairs: (out[o], out[o+1]) = sum_c (w[o][c], w[o+1][c]) * acc[c]
 #pragma unroll
         for (int o = 0; o + 1 < MAXO; o += 2) {
-          mul2_s(out[o], out[o + 1], w[o][0], w[o + 1][0], acc[ch]);
+          mul2_s(out[ch][o], out[ch][o + 1], w[o][0], w[o + 1][0], acc[ch]);
 #pragma unroll
-          for (int c = 1; c < 4; ++c) fma2_s(out[o], out[o + 1], w[o][c], w[o + 1][c], acc[c * 3 + ch]);
-          fma2_s(out[o], out[o + 1], last[o], last[o + 1], rcv);
-          if (ch == 2) quant2_neg(q[o][ch], q[o + 1][ch], out[o], out[o + 1]);
-          else quant2(q[o][ch], q[o + 1][ch], out[o], out[o + 1]);
+          for (int c = 1; c < 4; ++c) fma2_s(out[ch][o], out[ch][o + 1], w[o][c], w[o + 1][c], acc[c * 3 + ch]);
+          fma2_s(out[ch][o], out[ch][o + 1], last[o], last[o + 1], rcv);
         }
         if (MAXO & 1) {
           const int o = MAXO - 1;
-          out[o] = w[o][0] * acc[ch];
+          out[ch][o] = w[o][0] * acc[ch];
 #pragma unroll
-          for (int c = 1; c < 4; ++c) out[o] = fmaf(w[o][c], acc[c * 3 + ch], out[o]);
-          out[o] = fmaf(last[o], rcv, out[o]);
-          q[o][ch] = (ch == 2) ? quant_bits_neg(out[o]) : quant_bits(out[o]);
+          for (int c = 1; c < 4; ++c) out[ch][o] = fmaf(w[o][c], acc[c * 3 + ch], out[ch][o]);
+          out[ch][o] = fmaf(last[o], rcv, out[ch][o]);
         }
       }
+      if (RGBA) {
+        uint32_t q[3][MAXO];
 #pragma unroll
-      for (int o = 0; o < MAXO; ++o) {
-        const uint32_t v = pack_rgb(q[o][0], q[o][1], q[o][2]);
-        if (st_ok[o]) *reinterpret_cast<uint32_t*>(optr + o * xstep) = v;
+        for (int ch = 0; ch < 3; ++ch) {
+#pragma unroll
+          for (int o = 0; o + 1 < MAXO; o += 2) {
+            if (ch == 2) quant2_neg(q[ch][o], q[ch][o + 1], out[ch][o], out[ch][o + 1]);
+            else quant2(q[ch][o], q[ch][o + 1], out[ch][o], out[ch][o + 1]);
+          }
+          if (MAXO & 1) q[ch][MAXO - 1] = (ch == 2) ? quant_bits_neg(out[ch][MAXO - 1]) : quant_bits(out[ch][MAXO - 1]);
+        }
+#pragma unroll
+        for (int o = 0; o < MAXO; ++o) {
+          const uint32_t v = pack_rgb(q[0][o], q[1][o], q[2][o]);
+          if (st_ok[o]) *reinterpret_cast<uint32_t*>(optr + o * xstep) = v;
+        }
+        optr += ystep;
       }
-      optr += ystep;
+      if (YUV) {
+        // JFIF full-range BT.601.  The luma weights sum to 1, so Y keeps the biased
+        // form; the chroma weights sum to 0, so the bias cancels and cb/cr are plain values * 2^-15.
+#pragma unroll
+        for (int o = 0; o < MAXO; ++o) {
+          const float R_ = out[0][o], G_ = out[1][o], B_ = out[2][o];
+          const float yv = fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_));
+          const uint32_t yq = quant_bits(yv);
+          if (st_ok[o]) yptr[o * xdir] = (uint8_t)yq;
+          ccb[o] += fmaf(-0.168736f, R_, fmaf(-0.331264f, G_, 0.5f * B_));
+          ccr[o] += fmaf(0.5f, R_, fmaf(-0.418688f, G_, -0.081312f * B_));
+        }
+        yptr += ystep_y;
+        if (second) {
+          const float nb_cb = __shfl_down_sync(0xffffffffu, ccb[0], 1);
+          const float nb_cr = __shfl_down_sync(0xffffffffu, ccr[0], 1);
+#pragma unroll
+          for (int o = 0; o < MAXO; ++o) {
+            float pcb = nb_cb, pcr = nb_cr;  // partner = output o+1
+            if (o + 1 < MAXO && o + 1 < cnt) { pcb = ccb[o + 1]; pcr = ccr[o + 1]; }
+            const float bias = 1.f + 128.f / 32768.f;
+            const uint32_t cbq = quant_bits(fmaf(0.25f, ccb[o] + pcb, bias));
+            const uint32_t crq = quant_bits(fmaf(0.25f, ccr[o] + pcr, bias));
+            const int co = ((cx0 + o * xdir) >> 1) - (cx0 >> 1);
+            if (c_own[o]) {
+              cbptr[co] = (uint8_t)cbq;
+              crptr[co] = (uint8_t)crq;
+            }
+          }
+#pragma unroll
+          for (int o = 0; o < MAXO; ++o) ccb[o] = ccr[o] = 0.f;
+          cbptr += cstep;
+          crptr += cstep;
+        }
+        second = !second;
+      }
 #pragma unroll
       for (int k = 0; k < 12; k += 2) mul2_s(acc[k], acc[k + 1], f[k], f[k + 1], wn);
     }
@@ -322,14 +392,11 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   // source-over evaluation.  Outside the hot loop so it costs the streaming path no registers.
   const bool need_fix = (and_acc >> 24) != 0xffu;
   if (__any_sync(0xffffffffu, need_fix)) {
-    const int xf0 = __shfl_sync(0xffffffffu, Xfirst, 0), xf1 = __shfl_sync(0xffffffffu, Xfirst, 31);
+    const int xf0 = __shfl_sync(0xffffffffu, Xfirst, 0), xf1 = __shfl_sync(0xffffffffu, Xfirst, STRIDE);
     const int ox0 = max(R.x0, xf0), ox1 = min(R.x1, xf1);
     const int ax = im.flip_x ? (int)dw - ox1 : ox0, bx = im.flip_x ? (int)dw - ox0 : ox1;
     const int ay = im.flip_y ? (int)(dh - oy1) : (int)oy0, by = im.flip_y ? (int)(dh - oy0) : (int)oy1;
-    for (int y = Y0 + ay; y < Y0 + by; ++y) {
-      uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
-      for (int x = X0 + ax + lane; x < X0 + bx; x += 32) row[x] = shade_px(P, x, y);
-    }
+    redo_rect<MODE>(P, X0 + ax, Y0 + ay, X0 + bx, Y0 + by, lane, im.flip_x ? 1 : 0);
   }
 }
 

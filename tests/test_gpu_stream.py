@@ -160,3 +160,74 @@ def test_stream_matches_gather_statistics(ctx):
     d = np.abs(got.rgba[:, :, :3].astype(np.int16) - want["rgba"][:, :, :3].astype(np.int16))
     assert d.max() <= 1
     assert (d != 0).mean() < 0.02, (d != 0).mean()
+
+
+# ---- fused I420 epilogue inside the streaming units (BASELINE configs[3]) ----
+
+def _go_yuv(ctx, dims, direction, mode, size, orientations=None, pattern=1, gap=0, seed=23, bitmaps=None, min_stream=1):
+    bitmaps = bitmaps or [U.synth_image(w, h, seed + i, pattern) for i, (w, h) in enumerate(dims)]
+    fs = [BIG] + [0] * (len(dims) - 1)
+    prof = U.profile_of("ios", size, 0)
+    lay, want = U.oracle_render(dims, bitmaps, direction, mode, gap, prof, orientations, file_sizes=fs, yuv=True)
+    tag = f"{dims} {direction}/{mode}/{size}/{orientations}"
+    outs = {}
+    for output in ("yuv420", "both"):
+        got = ctx.run(U.page_images(dims, bitmaps, orientations, fs), direction, mode=mode, gap=gap, platform="ios",
+                      deviceMaxCanvasSize=size or None, output=output)
+        assert (got.width, got.height) == (int(lay.canvasW), int(lay.canvasH))
+        assert not _whole_gather(got) and _n_stream(got) >= min_stream, hex(got.path_info)
+        U.check_pixels(got.y, want["y"], tag + " Y")
+        U.check_pixels(got.cb, want["cb"], tag + " Cb")
+        U.check_pixels(got.cr, want["cr"], tag + " Cr")
+        if output == "both":
+            U.check_pixels(got.rgba[:, :, :3], want["rgba"][:, :, :3], tag + " rgba")
+            assert (got.rgba[:, :, 3] == 255).all()
+        outs[output] = got
+    a, b = outs["yuv420"], outs["both"]
+    assert (a.y == b.y).all() and (a.cb == b.cb).all() and (a.cr == b.cr).all()
+    return outs["both"], lay
+
+
+@pytest.mark.parametrize("w,h,size", [
+    (403, 302, 384), (640, 480, 420), (806, 604, 364), (900, 600, 300), (1000, 750, 250), (1001, 333, 333),
+    (37, 29, 20), (9, 7, 4),
+])
+def test_yuv_stream_ratios(ctx, w, h, size):
+    _go_yuv(ctx, [(w, h)], "vertical", "min", size)
+    _go_yuv(ctx, [(h, w)], "horizontal", "min", size)
+
+
+def test_yuv_stream_odd_seams(ctx):
+    """Images whose scaled heights / widths are odd: chroma blocks straddle two images (gather strips)."""
+    dims = [(806, 603), (806, 605), (403, 303), (806, 601)]
+    got, lay = _go_yuv(ctx, dims, "vertical", "min", 1100, min_stream=3)
+    assert any(int(r[1]) % 2 == 1 for r in lay.rects)
+    assert _n_gather(got) >= 1
+    dims = [(603, 806), (605, 806), (607, 810)]
+    got, lay = _go_yuv(ctx, dims, "horizontal", "min", 600, min_stream=2)
+    assert any(int(r[0]) % 2 == 1 for r in lay.rects)
+
+
+@pytest.mark.parametrize("orientation", [2, 3, 4])
+def test_yuv_stream_flips(ctx, orientation):
+    dims = [(806, 604), (805, 603), (640, 481)]
+    _go_yuv(ctx, dims, "vertical", "min", 800, orientations=[orientation, 1, orientation], min_stream=2)
+    _go_yuv(ctx, dims, "horizontal", "min", 900, orientations=[1, orientation, orientation], min_stream=2)
+
+
+def test_yuv_stream_original_margins_and_mixed(ctx):
+    dims = [(w // 4, h // 4) for (w, h) in U.MIXED]
+    _go_yuv(ctx, dims, "vertical", "original", 2400)
+    _go_yuv(ctx, dims, "horizontal", "original", 2400)
+    _go_yuv(ctx, dims, "horizontal", "max", 3072, min_stream=1)        # upscales (gather) next to downscales (stream)
+    _go_yuv(ctx, dims, "vertical", "min", 0, orientations=[1, 6, 1, 8, 1, 5, 1, 1, 1][:len(dims)], min_stream=0)
+
+
+def test_yuv_stream_translucent(ctx):
+    dims = [(403, 302)] * 2
+    bm = [U.synth_image(w, h, 5 + i, 2) for i, (w, h) in enumerate(dims)]
+    _go_yuv(ctx, dims, "vertical", "min", 300, bitmaps=bm)
+    bm = [U.synth_image(w, h, 5 + i, 1) for i, (w, h) in enumerate(dims)]
+    bm[0][100, 200, 3] = 17
+    bm[1][301, 402, 3] = 254
+    _go_yuv(ctx, dims, "vertical", "min", 300, bitmaps=bm)
