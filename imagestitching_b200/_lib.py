@@ -71,6 +71,8 @@ SIGNATURES = {
     "stitch_ctx_create": (C.c_int, [C.c_int32, C.c_void_p, C.POINTER(C.c_void_p)]),
     "stitch_ctx_destroy": (C.c_int, [C.c_void_p]),
     "stitch_ctx_stream": (C.c_void_p, [C.c_void_p]),
+    "stitch_ctx_set_lanes": (C.c_int, [C.c_void_p, C.c_int32]),
+    "stitch_ctx_join": (C.c_int, [C.c_void_p]),
     "stitch_set_progress_cb": (C.c_int, [C.c_void_p, PROGRESS_FN, C.c_void_p]),
     "stitch_output_size": (C.c_int, [C.POINTER(StitchLayout), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "stitch_run": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult)]),

@@ -28,24 +28,31 @@ struct PendingJob {
   int32_t n;
 };
 
-struct StitchCtx {
-  int device = 0;
+// One job lane: a stream with its own unit-scheduler counters and its own staging, so that jobs
+// submitted to different lanes overlap -- the next job's blocks fill the SM slots the draining one
+// frees, and with host buffers lane A's device->host export runs against lane B's host->device upload.
+struct Lane {
   cudaStream_t stream = nullptr;
   bool own_stream = false;
-  StitchProgressFn progress = nullptr;
-  void* progress_user = nullptr;
-  std::string last_error;
+  stitch::StreamScratch scratch;
   // grow-only device staging for host-resident inputs / outputs
   std::vector<void*> in_stage;
   std::vector<size_t> in_stage_cap;
   void* out_stage = nullptr;
   size_t out_stage_cap = 0;
+};
+
+struct StitchCtx {
+  int device = 0;
+  std::vector<Lane> lanes;   // lanes[0] = the ctx stream (stitch_run); stitch_submit rotates over all
+  StitchProgressFn progress = nullptr;
+  void* progress_user = nullptr;
+  std::string last_error;
   int64_t launches = 0;
   uint64_t next_ticket = 1;
   std::deque<PendingJob> pending;
   bool busy = false;
   int sm_count = 148;
-  stitch::StreamScratch scratch;
 };
 
 namespace {
@@ -110,22 +117,34 @@ void make_placement(const StitchRect& r, int orientation, double ss, int bw, int
   p->pad = 0;
 }
 
-int ensure_stage(StitchCtx* ctx, size_t idx, size_t bytes) {
-  if (ctx->in_stage.size() <= idx) {
-    ctx->in_stage.resize(idx + 1, nullptr);
-    ctx->in_stage_cap.resize(idx + 1, 0);
+int ensure_stage(StitchCtx* ctx, Lane& ln, size_t idx, size_t bytes) {
+  if (ln.in_stage.size() <= idx) {
+    ln.in_stage.resize(idx + 1, nullptr);
+    ln.in_stage_cap.resize(idx + 1, 0);
   }
-  if (ctx->in_stage_cap[idx] < bytes) {
-    if (ctx->in_stage[idx]) CUDA_TRY(ctx, cudaFree(ctx->in_stage[idx]));
-    ctx->in_stage[idx] = nullptr;
-    ctx->in_stage_cap[idx] = 0;
-    CUDA_TRY(ctx, cudaMalloc(&ctx->in_stage[idx], bytes));
-    ctx->in_stage_cap[idx] = bytes;
+  if (ln.in_stage_cap[idx] < bytes) {
+    if (ln.in_stage[idx]) CUDA_TRY(ctx, cudaFree(ln.in_stage[idx]));
+    ln.in_stage[idx] = nullptr;
+    ln.in_stage_cap[idx] = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ln.in_stage[idx], bytes));
+    // row padding of staged bitmaps is read by the kernel's last 16-byte group: keep it opaque
+    CUDA_TRY(ctx, cudaMemsetAsync(ln.in_stage[idx], 0xff, bytes, ln.stream));
+    ln.in_stage_cap[idx] = bytes;
   }
   return STITCH_OK;
 }
 
-int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
+void free_lane(Lane& ln) {
+  if (ln.stream) cudaStreamSynchronize(ln.stream);
+  for (void* p : ln.in_stage)
+    if (p) cudaFree(p);
+  if (ln.out_stage) cudaFree(ln.out_stage);
+  stitch::free_scratch(ln.scratch);
+  if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
+  ln = Lane();
+}
+
+int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res) {
   if (!ctx || !job || !res) return fail(ctx, STITCH_E_BAD_ARG, "null argument");
   if (job->n <= 0) return fail(ctx, STITCH_E_EMPTY, "empty image list");  // P:1189
   if (!job->images) return fail(ctx, STITCH_E_BAD_ARG, "images == NULL");
@@ -197,11 +216,11 @@ int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
     } else {
       // Host bitmap: stage with a 16B-aligned pitch so the streaming kernel's 128-bit loads apply.
       const int64_t dpitch = ((int64_t)im.bmp_width * 4 + 15) & ~15LL;
-      st = ensure_stage(ctx, i, (size_t)(dpitch * im.bmp_height));
+      st = ensure_stage(ctx, ln, i, (size_t)(dpitch * im.bmp_height));
       if (st != STITCH_OK) return st;
-      CUDA_TRY(ctx, cudaMemcpy2DAsync(ctx->in_stage[i], dpitch, im.data, pitch, (size_t)im.bmp_width * 4, im.bmp_height,
-                                      cudaMemcpyHostToDevice, ctx->stream));
-      dptr = (const uint8_t*)ctx->in_stage[i];
+      CUDA_TRY(ctx, cudaMemcpy2DAsync(ln.in_stage[i], dpitch, im.data, pitch, (size_t)im.bmp_width * 4, im.bmp_height,
+                                      cudaMemcpyHostToDevice, ln.stream));
+      dptr = (const uint8_t*)ln.in_stage[i];
       pitch = dpitch;
     }
     P.img[i].data = dptr;
@@ -218,16 +237,16 @@ int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
     d_rgba_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
     const size_t need_rgba = want_rgba ? (size_t)(d_rgba_pitch * ch) : 0;
     const size_t need = need_rgba + (want_yuv ? (size_t)res->yuv_bytes : 0) + 256;
-    if (ctx->out_stage_cap < need) {
-      if (ctx->out_stage) CUDA_TRY(ctx, cudaFree(ctx->out_stage));
-      ctx->out_stage = nullptr;
-      ctx->out_stage_cap = 0;
-      cudaError_t e = cudaMalloc(&ctx->out_stage, need);
+    if (ln.out_stage_cap < need) {
+      if (ln.out_stage) CUDA_TRY(ctx, cudaFree(ln.out_stage));
+      ln.out_stage = nullptr;
+      ln.out_stage_cap = 0;
+      cudaError_t e = cudaMalloc(&ln.out_stage, need);
       if (e != cudaSuccess) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (device canvas allocation failed)");
-      ctx->out_stage_cap = need;
+      ln.out_stage_cap = need;
     }
-    if (want_rgba) d_rgba = (uint8_t*)ctx->out_stage;
-    if (want_yuv) d_yuv = (uint8_t*)ctx->out_stage + ((need_rgba + 255) & ~(size_t)255);
+    if (want_rgba) d_rgba = (uint8_t*)ln.out_stage;
+    if (want_yuv) d_yuv = (uint8_t*)ln.out_stage + ((need_rgba + 255) & ~(size_t)255);
   } else {
     if (want_rgba) d_rgba = (uint8_t*)job->out_rgba;
     if (want_yuv) d_yuv = (uint8_t*)job->out_yuv;
@@ -244,7 +263,7 @@ int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
   // [4] the draw loop (P:1439-1572) as fused launches
   int launches = 0;
   int path_info = 0;
-  st = stitch::launch_job(P, want_rgba, want_yuv, ctx->sm_count, ctx->scratch, ctx->stream, &launches, &path_info);
+  st = stitch::launch_job(P, want_rgba, want_yuv, ctx->sm_count, ln.scratch, ln.stream, &launches, &path_info);
   res->path_info = path_info;
   if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
   ctx->launches += launches;
@@ -255,9 +274,9 @@ int enqueue_job(StitchCtx* ctx, const StitchJob* job, StitchResult* res) {
   if (out_host) {
     if (want_rgba)
       CUDA_TRY(ctx, cudaMemcpy2DAsync(job->out_rgba, rgba_pitch, d_rgba, d_rgba_pitch, (size_t)cw * 4, ch,
-                                      cudaMemcpyDeviceToHost, ctx->stream));
+                                      cudaMemcpyDeviceToHost, ln.stream));
     if (want_yuv)
-      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ln.stream));
   }
   return STITCH_OK;
 }
@@ -273,14 +292,16 @@ extern "C" int stitch_ctx_create(int32_t device, void* stream, StitchCtx** out) 
   if (cudaSetDevice(device) != cudaSuccess) return STITCH_E_CUDA;
   StitchCtx* ctx = new StitchCtx();
   ctx->device = device;
+  ctx->lanes.resize(1);
+  Lane& l0 = ctx->lanes[0];
   if (stream) {
-    ctx->stream = (cudaStream_t)stream;
+    l0.stream = (cudaStream_t)stream;
   } else {
-    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    if (cudaStreamCreateWithFlags(&l0.stream, cudaStreamNonBlocking) != cudaSuccess) {
       delete ctx;
       return STITCH_E_CUDA;
     }
-    ctx->own_stream = true;
+    l0.own_stream = true;
   }
   cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
   *out = ctx;
@@ -290,18 +311,45 @@ extern "C" int stitch_ctx_create(int32_t device, void* stream, StitchCtx** out) 
 extern "C" int stitch_ctx_destroy(StitchCtx* ctx) {
   if (!ctx) return STITCH_E_BAD_ARG;
   cudaSetDevice(ctx->device);
-  cudaStreamSynchronize(ctx->stream);
+  for (Lane& ln : ctx->lanes)
+    if (ln.stream) cudaStreamSynchronize(ln.stream);
   for (auto& p : ctx->pending) cudaEventDestroy(p.done);
-  for (void* p : ctx->in_stage)
-    if (p) cudaFree(p);
-  if (ctx->out_stage) cudaFree(ctx->out_stage);
-  stitch::free_scratch(ctx->scratch);
-  if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+  for (Lane& ln : ctx->lanes) free_lane(ln);
   delete ctx;
   return STITCH_OK;
 }
 
-extern "C" void* stitch_ctx_stream(StitchCtx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" void* stitch_ctx_stream(StitchCtx* ctx) { return ctx ? (void*)ctx->lanes[0].stream : nullptr; }
+
+extern "C" int stitch_ctx_set_lanes(StitchCtx* ctx, int32_t n) {
+  if (!ctx || n < 1 || n > STITCH_MAX_LANES) return STITCH_E_BAD_ARG;
+  if (ctx->busy || !ctx->pending.empty()) return fail(ctx, STITCH_E_BUSY, "jobs in flight");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  while ((int)ctx->lanes.size() > n) {
+    free_lane(ctx->lanes.back());
+    ctx->lanes.pop_back();
+  }
+  while ((int)ctx->lanes.size() < n) {
+    Lane ln;
+    CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ln.stream, cudaStreamNonBlocking));
+    ln.own_stream = true;
+    ctx->lanes.push_back(ln);
+  }
+  return STITCH_OK;
+}
+
+extern "C" int stitch_ctx_join(StitchCtx* ctx) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  for (size_t k = 1; k < ctx->lanes.size(); ++k) {
+    cudaEvent_t ev;
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    CUDA_TRY(ctx, cudaEventRecord(ev, ctx->lanes[k].stream));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lanes[0].stream, ev, 0));
+    CUDA_TRY(ctx, cudaEventDestroy(ev));
+  }
+  return STITCH_OK;
+}
 
 extern "C" int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user) {
   if (!ctx) return STITCH_E_BAD_ARG;
@@ -314,9 +362,9 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
   if (!ctx) return STITCH_E_BAD_ARG;
   if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "stitch already in progress");  // P:772,781
   ctx->busy = true;
-  int st = enqueue_job(ctx, job, result);
+  int st = enqueue_job(ctx, ctx->lanes[0], job, result);
   if (st == STITCH_OK) {
-    cudaError_t e = cudaStreamSynchronize(ctx->stream);
+    cudaError_t e = cudaStreamSynchronize(ctx->lanes[0].stream);
     if (e != cudaSuccess) st = fail(ctx, STITCH_E_CUDA, std::string("stream sync: ") + cudaGetErrorString(e));
   }
   if (st == STITCH_OK) {
@@ -331,13 +379,14 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
 
 extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {
   if (!ctx || !ticket) return STITCH_E_BAD_ARG;
-  int st = enqueue_job(ctx, job, result);
+  Lane& ln = ctx->lanes[ctx->next_ticket % ctx->lanes.size()];  // jobs rotate over the lanes
+  int st = enqueue_job(ctx, ln, job, result);
   if (st != STITCH_OK) return st;
   PendingJob pj;
   pj.ticket = ctx->next_ticket++;
   pj.n = job->n;
   CUDA_TRY(ctx, cudaEventCreateWithFlags(&pj.done, cudaEventDisableTiming));
-  CUDA_TRY(ctx, cudaEventRecord(pj.done, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(pj.done, ln.stream));
   ctx->pending.push_back(pj);
   *ticket = pj.ticket;
   return STITCH_OK;
@@ -345,7 +394,7 @@ extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult*
 
 extern "C" int stitch_wait(StitchCtx* ctx, uint64_t ticket) {
   if (!ctx) return STITCH_E_BAD_ARG;
-  // tickets complete in stream order: waiting for ticket T retires every earlier one too
+  // waiting for ticket T retires every earlier one too (tickets of one lane complete in order)
   while (!ctx->pending.empty() && ctx->pending.front().ticket <= ticket) {
     PendingJob pj = ctx->pending.front();
     ctx->pending.pop_front();
@@ -378,14 +427,14 @@ extern "C" int stitch_device_free(StitchCtx* ctx, void* p) {
 }
 extern "C" int stitch_memcpy_h2d(StitchCtx* ctx, void* dst, const void* src, size_t bytes) {
   if (!ctx) return STITCH_E_BAD_ARG;
-  CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->lanes[0].stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->lanes[0].stream));
   return STITCH_OK;
 }
 extern "C" int stitch_memcpy_d2h(StitchCtx* ctx, void* dst, const void* src, size_t bytes) {
   if (!ctx) return STITCH_E_BAD_ARG;
-  CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->lanes[0].stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->lanes[0].stream));
   return STITCH_OK;
 }
 
@@ -394,7 +443,7 @@ extern "C" int stitch_generate_image(StitchCtx* ctx, void* dev_dst, int32_t widt
   if (!ctx || !dev_dst || width <= 0 || height <= 0) return STITCH_E_BAD_ARG;
   if (pitch_bytes == 0) pitch_bytes = (int64_t)width * 4;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  cudaError_t e = stitch::launch_generate((uint8_t*)dev_dst, width, height, pitch_bytes, seed, pattern, ctx->stream);
+  cudaError_t e = stitch::launch_generate((uint8_t*)dev_dst, width, height, pitch_bytes, seed, pattern, ctx->lanes[0].stream);
   if (e != cudaSuccess) return fail(ctx, STITCH_E_CUDA, cudaGetErrorString(e));
   ctx->launches += 1;
   return STITCH_OK;

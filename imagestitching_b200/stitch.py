@@ -191,6 +191,18 @@ class StitchContext:
     def stream(self) -> int:
         return int(self.lib.stitch_ctx_stream(self.handle) or 0)
 
+    def set_lanes(self, n: int) -> None:
+        """Number of job lanes stitch_submit rotates over (include/stitch.h: stitch_ctx_set_lanes)."""
+        st = self.lib.stitch_ctx_set_lanes(self.handle, int(n))
+        if st != L.OK:
+            raise StitchError(st, (self.lib.stitch_last_error(self.handle) or b"").decode("utf-8", "replace"))
+
+    def join(self) -> None:
+        """Make the ctx stream wait (device-side) for everything submitted on the other lanes."""
+        st = self.lib.stitch_ctx_join(self.handle)
+        if st != L.OK:
+            raise StitchError(st, (self.lib.stitch_last_error(self.handle) or b"").decode("utf-8", "replace"))
+
     @property
     def kernel_launches(self) -> int:
         return int(self.lib.stitch_kernel_launch_count(self.handle))

@@ -104,7 +104,18 @@ typedef struct StitchCtx StitchCtx;
  * `stream` is a cudaStream_t the ctx should launch on, or NULL to create its own. */
 int stitch_ctx_create(int32_t device, void* stream, StitchCtx** out);
 int stitch_ctx_destroy(StitchCtx* ctx);
-void* stitch_ctx_stream(StitchCtx* ctx); /* the cudaStream_t kernels are launched on */
+void* stitch_ctx_stream(StitchCtx* ctx); /* the cudaStream_t stitch_run launches on (lane 0) */
+
+/* Job lanes.  The reference draws one job at a time (isStitching, P:772,781); a batch of independent
+ * jobs (BASELINE configs[4]) is instead rotated by stitch_submit over `n` lanes -- streams with their
+ * own staging and unit-scheduler counters -- so the next job's blocks fill the SMs the finishing job
+ * frees and, with host buffers, one lane's export (D2H) overlaps another lane's upload (H2D).
+ * Lane 0 is the ctx stream; lanes 1..n-1 are streams the ctx creates.  Default 1.
+ * stitch_ctx_join makes lane 0's stream wait (on the device, without blocking the host) for everything
+ * submitted so far on the other lanes, so one event on the ctx stream brackets a whole batch. */
+#define STITCH_MAX_LANES 8
+int stitch_ctx_set_lanes(StitchCtx* ctx, int32_t n);
+int stitch_ctx_join(StitchCtx* ctx);
 
 /* Progress callback == this.setData({stitchProgress}) (values of stitch_progress_sequence);
  * invoked on the calling thread inside stitch_run/stitch_wait. */
@@ -152,7 +163,7 @@ int stitch_output_size(const StitchLayout* layout, int64_t* rgba_bytes, int64_t*
 /* Synchronous onStitch(): layout -> draw all images -> export into the caller's buffer. (P:1186-1633) */
 int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
 
-/* Asynchronous form for job-level sharding: enqueue on the ctx stream, wait later.
+/* Asynchronous form for job-level sharding: enqueue on the next lane, wait later.
  * Buffers must stay valid until stitch_wait(ticket) returns. */
 int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket);
 int stitch_wait(StitchCtx* ctx, uint64_t ticket);

@@ -223,6 +223,41 @@ def test_device_buffers_and_async(ctx):
         lib.stitch_device_free(ctx.handle, p)
 
 
+def test_job_lanes_batch(ctx):
+    """A batch of different host-buffer jobs rotated over 3 lanes (stitch_ctx_set_lanes): every job's export
+    equals the one-at-a-time result; tickets retire in order; lanes cannot change while jobs are in flight."""
+    import ctypes as C
+    from imagestitching_b200.stitch import _profile_struct
+    lib = ctx.lib
+    cases = []
+    for k in range(7):
+        dims = [(160 + 8 * k, 120 + k)] * (2 + k % 3)
+        bitmaps = [U.synth_image(w, h, 900 + 10 * k + i, 0) for i, (w, h) in enumerate(dims)]
+        ref = ctx.run(U.page_images(dims, bitmaps), "vertical", platform="ios", deviceMaxCanvasSize=170)
+        cases.append((dims, bitmaps, ref))
+    ctx.set_lanes(3)
+    try:
+        outs, jobs, ress, tickets = [], [], [], []
+        for dims, bitmaps, ref in cases:
+            out = np.zeros_like(ref.rgba)
+            job, keep = ctx.build_job(U.page_images(dims, bitmaps), "vertical", "min", 0, _profile_struct("ios", 170, None),
+                                      "rgba", False, out.ctypes.data, 0, out.nbytes, 0)
+            res = L.StitchResult()
+            t = C.c_uint64()
+            assert lib.stitch_submit(ctx.handle, C.byref(job), C.byref(res), C.byref(t)) == 0
+            outs.append(out); jobs.append((job, keep)); ress.append(res); tickets.append(t.value)
+        assert tickets == sorted(tickets)
+        assert lib.stitch_ctx_set_lanes(ctx.handle, 2) == L.E_BUSY        # jobs in flight
+        assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0
+        for out, (dims, bitmaps, ref) in zip(outs, cases):
+            assert (out == ref.rgba).all()
+        assert lib.stitch_ctx_join(ctx.handle) == 0
+    finally:
+        ctx.set_lanes(1)
+    assert lib.stitch_ctx_set_lanes(ctx.handle, 0) == L.E_BAD_ARG
+    assert lib.stitch_ctx_set_lanes(ctx.handle, 99) == L.E_BAD_ARG
+
+
 def test_generator_matches_cpu_twin(ctx):
     import ctypes as C
     lib = ctx.lib
