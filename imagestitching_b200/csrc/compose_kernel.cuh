@@ -159,9 +159,9 @@ __device__ __forceinline__ void gather_unit(const JobParam& P, const Region& R, 
 // sched[0] = next unit to hand out, sched[1] = warps that have left the kernel; the last warp out
 // resets both, so back-to-back launches on one stream need no memset in between.
 //
-// MAXO = max over the job's streaming regions of ceil(4 / ratio_x); MODE = STREAM_MODE_* (RGBA
-// canvas, I420 planes, or both).
-template <int MAXO, int MODE>
+// MAXO = max over the job's streaming regions of ceil(4 / ratio_x); HOPS = max of ceil(ratio_x / 4)
+// (1, 2 or 4); MODE = STREAM_MODE_* (RGBA canvas, I420 planes, or both).
+template <int MAXO, int HOPS, int MODE>
 __global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
 compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -184,7 +184,7 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
     const int local = (int)unit - R.first_unit;
     const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
     if (R.kind == REGION_STREAM) {
-      stream_unit<MAXO, MODE>(P, R, tx, ty, ws, lane);
+      stream_unit<MAXO, HOPS, MODE>(P, R, tx, ty, ws, lane);
     } else if (R.kind == REGION_FILL) {
       fill_unit<MODE>(P, R, tx, ty, lane);
     } else {

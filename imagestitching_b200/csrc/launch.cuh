@@ -30,7 +30,7 @@ inline bool stream_eligible(const ImgParam& im) {
   if (im.transpose) return false;
   const int64_t dw = (int64_t)im.W, dh = (int64_t)im.H;
   if (!(im.sx_len > dw && im.sy_len > dh)) return false;       // area filter on both axes
-  if ((int64_t)im.sx_len > 4 * dw) return false;               // one-hop neighbour exchange needs ratio_x <= 4
+  if ((int64_t)im.sx_len > 16 * dw) return false;              // tails are collected over at most 4 groups: ratio_x <= 16
   if (((uintptr_t)im.data & 15) || (im.pitch & 15)) return false;  // 128-bit row loads
   // the kernel's geometry is unsigned 32-bit: every scaled coordinate it forms must stay below 2^31
   if (((int64_t)im.sx_len + 512) * (dw + 1) >= (1LL << 31) || ((int64_t)im.sy_len + 8) * (dh + 1) >= (1LL << 31)) return false;
@@ -56,9 +56,9 @@ inline int stream_max_tile_h(const ImgParam& im) {
 // (cell size 2): a streamed image keeps the largest block-aligned box inside its rect and the odd
 // rows / columns along its edges -- blocks shared with a neighbour or the background -- go to
 // per-block GATHER regions, so no chroma block is ever split between two units.
-inline bool build_plan(const JobParam& P, int mode, int resident_warps, Plan* plan) {
+inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps, Plan* plan) {
   const int cs = (mode == STREAM_MODE_RGBA) ? 1 : 2;                  // cell size in pixels
-  const int stride = STREAM_STRIDE_OF(mode);
+  const int stride = STREAM_STRIDE_OF(mode, hops);
   const int ccw = (P.cw + cs - 1) / cs, cch = (P.ch + cs - 1) / cs;   // canvas in cells
   struct Box { int x0, y0, x1, y1, img; bool stream; int ix0, iy0, ix1, iy1, ox0, oy0, ox1, oy1; };
   std::vector<Box> boxes;
@@ -229,17 +229,17 @@ inline bool build_plan(const JobParam& P, int mode, int resident_warps, Plan* pl
   return unit > 0;
 }
 
-template <int MAXO, int MODE>
+template <int MAXO, int HOPS, int MODE>
 struct ComposeLaunch {
   // resident CTAs per SM of this instantiation (queried once), 0 on error
   static int ctas_per_sm(cudaError_t* err) {
     static int value = -1;
     if (value < 0) {
-      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, HOPS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            kComposeSmemBytes);
       int n = 0;
       if (e == cudaSuccess)
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, MODE>, STREAM_WARPS * 32,
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, HOPS, MODE>, STREAM_WARPS * 32,
                                                           kComposeSmemBytes);
       if (e != cudaSuccess) { *err = e; return 0; }
       value = n < 1 ? 1 : n;
@@ -247,7 +247,7 @@ struct ComposeLaunch {
     return value;
   }
   static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
-    compose_kernel<MAXO, MODE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
+    compose_kernel<MAXO, HOPS, MODE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
     return cudaGetLastError();
   }
 };
@@ -261,27 +261,33 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
   *path_info = 1 << 24;
   const int mode = want_yuv ? (want_rgba ? STREAM_MODE_BOTH : STREAM_MODE_YUV) : STREAM_MODE_RGBA;
   // kernel variant: decided by the images alone (before the unit grid is chosen)
-  int maxo = 2;
+  int maxo = 2, hops = 1;
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
-    if (!is_int(im.W) || !is_int(im.H) || im.W < 1 || im.H < 1 || !stream_eligible(im)) continue;
+    if (!is_int(im.X0) || !is_int(im.Y0) || !is_int(im.W) || !is_int(im.H) || im.W < 1 || im.H < 1 || !stream_eligible(im)) continue;
     const int64_t dw = (int64_t)im.W;
     maxo = std::max(maxo, (int)std::min<int64_t>(4, (4 * dw + im.sx_len - 1) / im.sx_len));
+    hops = std::max(hops, (int)((im.sx_len + 4 * dw - 1) / (4 * dw)));
+  }
+  // instantiated (MAXO, HOPS) shapes: (2|3|4, 1) for ratios <= 4, (2, 2) for 2 < ratio <= 8, (4, 4) for the rest
+  if (hops > 1) {
+    if (hops == 2 && maxo == 2) { /* (2, 2) */ }
+    else { maxo = 4; hops = 4; }
   }
   cudaError_t err = cudaSuccess;
   int per_sm = 0;
-#define STITCH_DISPATCH(M, Md, expr) \
-  if (maxo == M && mode == Md) { using K = ComposeLaunch<M, Md>; expr; }
-#define STITCH_ALL(expr)                                                                     \
-  STITCH_DISPATCH(2, 0, expr) STITCH_DISPATCH(3, 0, expr) STITCH_DISPATCH(4, 0, expr)        \
-  STITCH_DISPATCH(2, 1, expr) STITCH_DISPATCH(3, 1, expr) STITCH_DISPATCH(4, 1, expr)        \
-  STITCH_DISPATCH(2, 2, expr) STITCH_DISPATCH(3, 2, expr) STITCH_DISPATCH(4, 2, expr)
+#define STITCH_DISPATCH(M, H, Md, expr) \
+  if (maxo == M && hops == H && mode == Md) { using K = ComposeLaunch<M, H, Md>; expr; }
+#define STITCH_SHAPES(Md, expr)                                                               \
+  STITCH_DISPATCH(2, 1, Md, expr) STITCH_DISPATCH(3, 1, Md, expr) STITCH_DISPATCH(4, 1, Md, expr) \
+  STITCH_DISPATCH(2, 2, Md, expr) STITCH_DISPATCH(4, 4, Md, expr)
+#define STITCH_ALL(expr) STITCH_SHAPES(0, expr) STITCH_SHAPES(1, expr) STITCH_SHAPES(2, expr)
   STITCH_ALL(per_sm = K::ctas_per_sm(&err))
   if (err != cudaSuccess) return (int)err;
   const int resident_warps = sm_count * per_sm * STREAM_WARPS;
 
   Plan plan;
-  if (build_plan(P, mode, resident_warps, &plan)) {
+  if (build_plan(P, mode, hops, resident_warps, &plan)) {
     if (!scratch.p) {  // unit scheduler counters {next unit, warps retired}; the kernel leaves them at zero
       cudaError_t e = cudaMalloc(&scratch.p, 256);
       if (e != cudaSuccess) return (int)e;
@@ -302,6 +308,7 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
     return (int)err;
   }
 #undef STITCH_ALL
+#undef STITCH_SHAPES
 #undef STITCH_DISPATCH
   if (want_yuv) {
     dim3 grid(((P.cw + 1) / 2 + 31) / 32, ((P.ch + 1) / 2 + 7) / 8);

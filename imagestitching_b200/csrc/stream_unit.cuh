@@ -25,9 +25,10 @@ namespace stitch {
 #define STREAM_MODE_RGBA 0  // RGBA8 canvas
 #define STREAM_MODE_YUV 1   // planar I420 only (U:205-242 export feeding a JPEG encoder)
 #define STREAM_MODE_BOTH 2  // RGBA8 canvas and I420
-// groups whose outputs a unit stores: 31 (lane 31 only supplies lane 30's tail); 30 when chroma is
-// produced, so that lane 30's outputs are complete too and can pair with lane 29's last output
-#define STREAM_STRIDE_OF(MODE) ((MODE) == STREAM_MODE_RGBA ? 31 : 30)
+// HOPS = how many groups to the right an output can reach: 1 for ratio_x <= 4, 2 for <= 8, 4 for <= 16.
+// Groups whose outputs a unit stores: 32 - HOPS (the last HOPS lanes only supply tails); 32 - 2*HOPS
+// when chroma is produced, so that the chroma partner of the last stored output is complete too.
+#define STREAM_STRIDE_OF(MODE, HOPS) ((MODE) == STREAM_MODE_RGBA ? 32 - (HOPS) : 32 - 2 * (HOPS))
 
 static_assert(STREAM_NST % STREAM_UNR == 0 && (STREAM_NST & (STREAM_NST - 1)) == 0 && STREAM_UNR % 2 == 0, "ring layout");
 
@@ -153,10 +154,12 @@ __device__ __forceinline__ void build_row_table(float2* tab, int lane, uint32_t 
 
 // MAXO = max number of outputs that can START inside one 4-pixel source group = ceil(4 / ratio_x):
 // 2 for ratio_x > 2 (the 9x12MP config), 3 for ratio_x > 4/3, 4 for ratio_x > 1.
+// HOPS: see STREAM_STRIDE_OF; for ratio_x > 4 a group holds at most one output start and whole groups
+// can lie inside one output, whose owner then collects the `prev` sums of up to HOPS lanes to its right.
 // MODE = STREAM_MODE_*.  With chroma output the host aligns the region to even canvas coordinates and
 // makes tile_h even, so every 2x2 chroma block lies inside one unit (launch.cuh).
 // All geometry is unsigned 32-bit; launch.cuh only admits images whose scaled coordinates fit.
-template <int MAXO, int MODE>
+template <int MAXO, int HOPS, int MODE>
 __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, int tx, int ty, WarpSmem& ws, int lane) {
   const ImgParam& im = P.img[R.img];
   const uint32_t sw = (uint32_t)im.sx_len, sh = (uint32_t)im.sy_len;
@@ -174,15 +177,30 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   build_row_table(ws.tab, lane, rs, nrows, nrows_pad, sh, dh, oy0, inv_sh);
 
   // ---- horizontal: this lane's 4-pixel source group and the outputs that start in it ----
-  constexpr int STRIDE = STREAM_STRIDE_OF(MODE);
+  constexpr int STRIDE = STREAM_STRIDE_OF(MODE, HOPS);
   constexpr bool RGBA = MODE != STREAM_MODE_YUV, YUV = MODE != STREAM_MODE_RGBA;
   const uint32_t g = (uint32_t)(R.g_base + tx * STRIDE + lane);
   const uint32_t g_last = (sw + 3) / 4 - 1;
   const uint32_t c0 = 4u * g * dw;  // group start, in source units scaled by dw
   const int Xfirst = (int)udiv_ceil(c0, sw);
   int Xnext = __shfl_down_sync(0xffffffffu, Xfirst, 1);
-  if (lane == 31) Xnext = Xfirst;  // lane 31 only feeds lane 30's tail
+  if (lane == 31) Xnext = Xfirst;  // lane 31 only feeds tails
   const int cnt = min(Xnext - Xfirst, MAXO);
+  // hop[k] = 1 when the tail of this lane's last output reaches k+1 groups to the right: it always
+  // reaches the next group; it reaches further while the groups in between start no output
+  float hop[HOPS];
+  int nxt = 1;  // distance to the next lane that starts an output (chroma partner)
+  {
+    bool open = cnt > 0;
+    bool seek = true;
+#pragma unroll
+    for (int k = 0; k < HOPS; ++k) {
+      hop[k] = open ? 1.f : 0.f;
+      const int c_k = __shfl_down_sync(0xffffffffu, cnt, k + 1);
+      if (seek && c_k > 0) { nxt = k + 1; seek = false; }
+      open = open && (c_k == 0);
+    }
+  }
   float w[MAXO][4], wprev[4];
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
@@ -286,7 +304,9 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
         float prev = wprev[0] * acc[ch];
 #pragma unroll
         for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], acc[c * 3 + ch], prev);
-        const float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
+        float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
+#pragma unroll
+        for (int k = 1; k < HOPS; ++k) rcv = fmaf(hop[k], __shfl_down_sync(0xffffffffu, prev, k + 1), rcv);
         // outputs in pairs: (out[o], out[o+1]) = sum_c (w[o][c], w[o+1][c]) * acc[c]
 #pragma unroll
         for (int o = 0; o + 1 < MAXO; o += 2) {
@@ -335,8 +355,8 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
         }
         yptr += ystep_y;
         if (second) {
-          const float nb_cb = __shfl_down_sync(0xffffffffu, ccb[0], 1);
-          const float nb_cr = __shfl_down_sync(0xffffffffu, ccr[0], 1);
+          const float nb_cb = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccb[0], 1) : __shfl_sync(0xffffffffu, ccb[0], lane + nxt);
+          const float nb_cr = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccr[0], 1) : __shfl_sync(0xffffffffu, ccr[0], lane + nxt);
 #pragma unroll
           for (int o = 0; o < MAXO; ++o) {
             float pcb = nb_cb, pcr = nb_cr;  // partner = output o+1

@@ -58,9 +58,37 @@ def test_ratios_single_image(ctx, w, h, size):
     assert _n_stream(got) == 1
 
 
-def test_ratio_above_4_uses_gather(ctx):
-    got, _ = _go(ctx, [(1000, 750)], "vertical", "min", 240)
+@pytest.mark.parametrize("w,h,size", [
+    (1000, 750, 240),    # ratio 4.17: an output can reach two groups to the right (HOPS 2)
+    (1330, 1000, 200),   # ratio 6.65 (the Android preset of the 9x12MP config)
+    (1600, 1200, 200),   # ratio 8.0 exactly
+    (1601, 1203, 199),   # ratio 8.05 -> HOPS 4
+    (2400, 1800, 200),   # ratio 12
+    (3200, 2400, 200),   # ratio 16.0 exactly (upper limit)
+    (1333, 999, 111),    # ratio 12.0, odd everything
+])
+def test_ratios_above_4_stream(ctx, w, h, size):
+    got, lay = _go(ctx, [(w, h)], "vertical", "min", size)
+    assert _n_stream(got) == 1 and not _whole_gather(got)
+    got, lay = _go(ctx, [(h, w)], "horizontal", "min", size, orientations=[3])
+    assert _n_stream(got) == 1
+    _go_yuv(ctx, [(w, h)], "vertical", "min", size)
+
+
+def test_ratio_above_16_uses_gather(ctx):
+    got, _ = _go(ctx, [(3300, 2475)], "vertical", "min", 150)      # ratio 16.5
     assert _n_stream(got) == 0 and _n_gather(got) == 1
+
+
+def test_mixed_ratios_one_launch(ctx):
+    """Ratios from 1.5 to 5.6 and an identity copy in one job (BASELINE configs[2] in 'min' mode, quartered):
+    the launch takes the most general kernel shape (MAXO 4, HOPS 4) for all streamed images."""
+    dims = [(w // 4, h // 4) for (w, h) in U.MIXED]
+    got, lay = _go(ctx, dims, "horizontal", "min", 0)
+    assert _n_stream(got) == 8 and _n_gather(got) == 1
+    _go_yuv(ctx, dims, "horizontal", "min", 0, min_stream=8)
+    got, lay = _go(ctx, dims, "horizontal", "min", 1024)          # Android-like clamp: ratios 2.8 .. 10.5
+    assert _n_stream(got) == 9
 
 
 @pytest.mark.parametrize("orientation", [2, 3, 4])
