@@ -23,6 +23,8 @@
 //       (A cp.async.bulk + mbarrier ring fed by one elected lane was measured too: 0.164 ms vs
 //       0.127 ms per 9x12MP job -- the elect/R2UR/UBLKCP sequence costs ~25 issue slots per
 //       512-byte row, and the kernel is issue-bound, not latency-bound.  See DESIGN.md.)
+//   REGION_UPSCALE bilinear enlargement of the fully covered pixels of one image (upscale_unit.cuh):
+//       output-bound, 16-byte stores, source through L1.
 //   REGION_FILL    white.
 //   REGION_GATHER  per-pixel evaluation (gather_kernel.cuh shade()) for upscale / EXIF 5-8 /
 //       ratios outside the streaming range.
@@ -107,6 +109,7 @@ __device__ __noinline__ void redo_rect(const JobParam& P, int x0, int y0, int x1
 }  // namespace stitch
 
 #include "stream_unit.cuh"
+#include "upscale_unit.cuh"
 
 namespace stitch {
 
@@ -185,6 +188,8 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
     const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
     if (R.kind == REGION_STREAM) {
       stream_unit<MAXO, HOPS, MODE>(P, R, tx, ty, ws, lane);
+    } else if (R.kind == REGION_UPSCALE) {
+      upscale_unit<MODE>(P, R, tx, ty, lane);
     } else if (R.kind == REGION_FILL) {
       fill_unit<MODE>(P, R, tx, ty, lane);
     } else {

@@ -40,6 +40,15 @@ inline bool stream_eligible(const ImgParam& im) {
   return true;
 }
 
+// Bilinear on both axes (device rect at least as large as the bitmap), EXIF 1-4: upscale_unit.cuh.
+inline bool upscale_eligible(const ImgParam& im) {
+  if (im.transpose) return false;
+  if (!(im.W >= (double)im.sx_len && im.H >= (double)im.sy_len)) return false;
+  if (((uintptr_t)im.data & 3) || (im.pitch & 3)) return false;
+  if (!(std::fabs(im.X0) < 1e8 && std::fabs(im.Y0) < 1e8 && im.W < 1e8 && im.H < 1e8)) return false;
+  return true;
+}
+
 // Largest tile_h (output rows per unit) whose source rows fit the row table.
 inline int stream_max_tile_h(const ImgParam& im) {
   const int64_t dh = (int64_t)im.H;
@@ -60,28 +69,48 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
   const int cs = (mode == STREAM_MODE_RGBA) ? 1 : 2;                  // cell size in pixels
   const int stride = STREAM_STRIDE_OF(mode, hops);
   const int ccw = (P.cw + cs - 1) / cs, cch = (P.ch + cs - 1) / cs;   // canvas in cells
-  struct Box { int x0, y0, x1, y1, img; bool stream; int ix0, iy0, ix1, iy1, ox0, oy0, ox1, oy1; };
+  // Per image: the OUTER box (every pixel the device rect touches) and the FULL box (pixels it covers
+  // completely); both also on the cell grid.  A fast region (STREAM / UPSCALE) is the full box in whole
+  // cells; it needs the image to be alone there, i.e. no other image's outer box may reach into it --
+  // otherwise painter's-order compositing matters and the image is left to the gather pieces.
+  struct Box { int x0, y0, x1, y1, img; int kind; int ix0, iy0, ix1, iy1, ox0, oy0, ox1, oy1; };
   std::vector<Box> boxes;
+  bool any_fast = false;
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
-    if (!is_int(im.X0) || !is_int(im.Y0) || !is_int(im.W) || !is_int(im.H)) return false;
     if (im.x_hi <= im.x_lo || im.y_hi <= im.y_lo) continue;  // nothing visible
     Box b{};
     b.x0 = im.x_lo; b.y0 = im.y_lo; b.x1 = im.x_hi; b.y1 = im.y_hi; b.img = k;
-    b.ix0 = (b.x0 + cs - 1) / cs; b.iy0 = (b.y0 + cs - 1) / cs; b.ix1 = b.x1 / cs; b.iy1 = b.y1 / cs;   // inner, in cells
+    // fully covered pixels, clipped to the canvas
+    const int fx0 = (int)std::fmin(std::fmax(std::ceil(im.X0), 0.0), (double)P.cw);
+    const int fy0 = (int)std::fmin(std::fmax(std::ceil(im.Y0), 0.0), (double)P.ch);
+    const int fx1 = (int)std::fmin(std::fmax(std::floor(im.X0 + im.W), 0.0), (double)P.cw);
+    const int fy1 = (int)std::fmin(std::fmax(std::floor(im.Y0 + im.H), 0.0), (double)P.ch);
+    b.ix0 = (fx0 + cs - 1) / cs; b.iy0 = (fy0 + cs - 1) / cs; b.ix1 = fx1 / cs; b.iy1 = fy1 / cs;         // full, in cells
     b.ox0 = b.x0 / cs; b.oy0 = b.y0 / cs; b.ox1 = (b.x1 + cs - 1) / cs; b.oy1 = (b.y1 + cs - 1) / cs;   // outer, in cells
-    b.stream = stream_eligible(im) && b.ix0 < b.ix1 && b.iy0 < b.iy1 && (cs == 1 || stream_max_tile_h(im) >= 2);
+    const bool integral = is_int(im.X0) && is_int(im.Y0) && is_int(im.W) && is_int(im.H);
+    b.kind = REGION_GATHER;
+    if (b.ix0 < b.ix1 && b.iy0 < b.iy1) {
+      if (integral && stream_eligible(im) && (cs == 1 || stream_max_tile_h(im) >= 2)) b.kind = REGION_STREAM;
+      else if (upscale_eligible(im)) b.kind = REGION_UPSCALE;
+    }
     boxes.push_back(b);
   }
-  for (size_t a = 0; a < boxes.size(); ++a)
-    for (size_t b = a + 1; b < boxes.size(); ++b)
-      if (boxes[a].x0 < boxes[b].x1 && boxes[b].x0 < boxes[a].x1 && boxes[a].y0 < boxes[b].y1 && boxes[b].y0 < boxes[a].y1)
-        return false;
+  for (size_t a = 0; a < boxes.size(); ++a) {
+    if (boxes[a].kind == REGION_GATHER) continue;
+    for (size_t b = 0; b < boxes.size(); ++b) {
+      if (a == b) continue;
+      const Box &A = boxes[a], &B = boxes[b];
+      if (A.ix0 < B.ox1 && B.ox0 < A.ix1 && A.iy0 < B.oy1 && B.oy0 < A.iy1) { boxes[a].kind = REGION_GATHER; break; }
+    }
+  }
+  for (const Box& b : boxes) any_fast = any_fast || b.kind != REGION_GATHER;
+  if (!any_fast) return false;   // nothing to fuse: the whole-canvas gather kernel does the job
 
   std::vector<Region> regs;
   // streaming regions: the inner box of every eligible image
   for (const Box& bx : boxes) {
-    if (!bx.stream) continue;
+    if (bx.kind != REGION_STREAM) continue;
     const ImgParam& im = P.img[bx.img];
     Region r{};
     r.img = bx.img;
@@ -98,6 +127,18 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
     r.tile_w = 0;
     r.tiles_x = std::max(1, (g_end - r.g_base + stride - 1) / stride);
     r.tile_h = stream_max_tile_h(im);   // refined below for load balance
+    regs.push_back(r);
+  }
+  // enlarged images: the full box in device pixels, 32 aligned quads x UPSCALE_TILE_H rows per unit
+  for (const Box& bx : boxes) {
+    if (bx.kind != REGION_UPSCALE) continue;
+    Region r{};
+    r.kind = REGION_UPSCALE;
+    r.img = bx.img;
+    r.x0 = bx.ix0 * cs; r.x1 = bx.ix1 * cs; r.y0 = bx.iy0 * cs; r.y1 = bx.iy1 * cs;
+    r.tile_w = UPSCALE_TILE_W;
+    r.tile_h = UPSCALE_TILE_H;
+    r.tiles_x = (r.x1 - (r.x0 & ~3) + UPSCALE_TILE_W - 1) / UPSCALE_TILE_W;
     regs.push_back(r);
   }
   // the rest of the canvas, in cells: sweep the bands between all y edges; inside a band cut at all x
@@ -134,7 +175,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
       if (xa < 0 || xb > ccw || xa >= xb) continue;
       int kind = REGION_FILL;
       for (const Box& b : boxes) {
-        if (b.stream && b.ix0 <= xa && b.ix1 >= xb && b.iy0 <= ya && b.iy1 >= yb) { kind = -1; break; }  // streamed
+        if (b.kind != REGION_GATHER && b.ix0 <= xa && b.ix1 >= xb && b.iy0 <= ya && b.iy1 >= yb) { kind = -1; break; }  // fast region
         if (b.ox0 < xb && b.ox1 > xa && b.oy0 < yb && b.oy1 > ya) kind = REGION_GATHER;
       }
       if (kind != run_kind || xa != run_x1) { flush(); run_kind = kind; run_x0 = xa; }
@@ -210,16 +251,17 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
     regs.clear();
     // order = hand-out order: bodies, then the per-pixel gather regions, then the small units
     for (const Region& r : bodies) regs.push_back(r);
+    for (const Region& r : others) if (r.kind == REGION_UPSCALE) regs.push_back(r);
     for (const Region& r : others) if (r.kind == REGION_GATHER) regs.push_back(r);
     for (const Region& r : tails) regs.push_back(r);
-    for (const Region& r : others) if (r.kind != REGION_GATHER) regs.push_back(r);
+    for (const Region& r : others) if (r.kind == REGION_FILL) regs.push_back(r);
     if (regs.size() > STITCH_MAX_REGIONS) return false;
   }
   int unit = 0;
   plan->n_regions = (int)regs.size();
   for (size_t i = 0; i < regs.size(); ++i) {
     Region& r = regs[i];
-    if (r.kind != REGION_STREAM) r.tiles_x = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
+    if (r.kind == REGION_FILL || r.kind == REGION_GATHER) r.tiles_x = (r.x1 - r.x0 + r.tile_w - 1) / r.tile_w;
     r.tiles_y = (r.y1 - r.y0 + r.tile_h - 1) / r.tile_h;
     r.first_unit = unit;
     unit += r.tiles_x * r.tiles_y;
@@ -252,8 +294,8 @@ struct ComposeLaunch {
   }
 };
 
-// The draw loop of one job as ONE launch.  path_info: streaming | gather << 8 | fill << 16 region
-// counts of the fused plan, or 1 << 24 when the whole canvas took the per-pixel gather kernel
+// The draw loop of one job as ONE launch.  path_info: streaming | gather << 8 | fill << 16 |
+// upscale << 25 region counts of the fused plan, or 1 << 24 when the whole canvas took the per-pixel gather kernel
 // (fractional device rects, overlapping images).
 inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_count, StreamScratch& scratch,
                       cudaStream_t stream, int* launches, int* path_info) {
@@ -295,9 +337,10 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
       e = cudaMemsetAsync(scratch.p, 0, 256, stream);
       if (e != cudaSuccess) return (int)e;
     }
-    int cnt[3] = {0, 0, 0};
+    int cnt[4] = {0, 0, 0, 0};
     for (int i = 0; i < plan.n_regions; ++i) cnt[plan.r[i].kind]++;
-    *path_info = std::min(cnt[REGION_STREAM], 255) | (std::min(cnt[REGION_GATHER], 255) << 8) | (std::min(cnt[REGION_FILL], 255) << 16);
+    *path_info = std::min(cnt[REGION_STREAM], 255) | (std::min(cnt[REGION_GATHER], 255) << 8) |
+                 (std::min(cnt[REGION_FILL], 255) << 16) | (std::min(cnt[REGION_UPSCALE], 63) << 25);
     // persistent grid: every resident warp slot of the chip, capped by the number of units
     int grid = sm_count * per_sm;
     const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;

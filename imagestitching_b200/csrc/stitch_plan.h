@@ -35,13 +35,14 @@ struct JobParam {
 enum RegionKind : int32_t {
   REGION_STREAM = 0,  // integer-aligned area downscale of one image: streaming kernel
   REGION_FILL = 1,    // white background (P:1423-1424) where no image lands
-  REGION_GATHER = 2   // anything else inside one image's bounding box: per-pixel gather
+  REGION_GATHER = 2,  // anything else inside one image's bounding box: per-pixel gather
+  REGION_UPSCALE = 3  // fully covered pixels of one enlarged image (bilinear on both axes), EXIF 1-4
 };
 
 struct Region {
   int32_t kind, img;
   // STREAM: source-order output index ranges [x0,x1) x [y0,y1) inside the image's device rect
-  // FILL/GATHER: device pixel rect
+  // FILL/GATHER: device pixel rect (rect of 2x2 chroma blocks when chroma is produced); UPSCALE: device pixel rect
   int32_t x0, y0, x1, y1;
   int32_t tile_w, tile_h;    // warp-unit size (output pixels); STREAM uses tile_h only (bands are 31 groups wide)
   int32_t tiles_x, tiles_y;  // warp-unit grid

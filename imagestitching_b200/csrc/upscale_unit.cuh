@@ -1,0 +1,189 @@
+// The bilinear upscale unit of the fused compose kernel (see compose_kernel.cuh).
+//
+// Replaces ctx.drawImage (U:156-199) where the device rect is at least as large as the bitmap on both
+// axes -- BASELINE configs[0] (2.2x supersampled canvas, P:1360-1386 + ctx.scale(ss,ss) P:1426-1428) and
+// the enlarged images of configs[2] -- for EXIF 1-4.  The device rect may be fractional; the region
+// holds only canvas pixels the rect covers completely, so coverage is 1 and the filter is the plain
+// bilinear one of SURVEY App. C.4.  The fractional edge rows / columns are GATHER regions.
+//
+// One warp, one unit = 32 aligned quads of 4 output pixels (128 px) x tile_h output rows.  The work is
+// output-bound (one 16-byte store per lane and row); source pixels come through L1 with 32-bit loads:
+// a lane keeps, for the two source rows its output row blends, the horizontally interpolated values of
+// its 4 pixels in registers and reloads a row only when the output row moves on to the next one.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "stitch_plan.h"
+#include "stream_unit.cuh"
+
+namespace stitch {
+
+#define UPSCALE_TILE_W 128
+#define UPSCALE_TILE_H 32
+
+// fp64 tap position of device pixel j on one axis, exactly as gather_kernel.cuh::axis_taps evaluates it
+// for a fully covered pixel: u = ((j + 0.5) - d0) / s - 0.5 with s = dlen / slen.
+__device__ __forceinline__ void bilinear_tap(int j, double d0, double s, int slen, bool flip, int* ia, int* ib, float* t) {
+  const double a = (double)j, b = (double)j + 1.0;
+  const double u = ((a + b) * 0.5 - d0) / s - 0.5;
+  const double f = floor(u);
+  const int i0 = (int)f;
+  *t = (float)(u - f);
+  int i_a = min(max(i0, 0), slen - 1), i_b = min(max(i0 + 1, 0), slen - 1);
+  if (flip) {
+    i_a = slen - 1 - i_a;
+    i_b = slen - 1 - i_b;
+  }
+  *ia = i_a;
+  *ib = i_b;
+}
+
+template <int MODE>
+__device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R, int tx, int ty, int lane) {
+  constexpr bool RGBA = MODE != STREAM_MODE_YUV, YUV = MODE != STREAM_MODE_RGBA;
+  const ImgParam& im = P.img[R.img];
+  const double sx = im.W / (double)im.sx_len, sy = im.H / (double)im.sy_len;
+  const int y0 = R.y0 + ty * R.tile_h, y1 = min(y0 + R.tile_h, R.y1);
+  const int q = (R.x0 >> 2) + tx * 32 + lane;  // this lane's aligned quad of canvas pixels
+  const int xq = 4 * q;
+
+  // ---- column taps of the lane's 4 pixels (byte offsets inside a bitmap row) ----
+  int offA[4], offB[4];
+  float tcol[4];
+  bool ok[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int x = xq + k;
+    ok[k] = x >= R.x0 && x < R.x1;
+    int ia, ib;
+    bilinear_tap(min(max(x, R.x0), R.x1 - 1), im.X0, sx, im.sx_len, im.flip_x != 0, &ia, &ib, &tcol[k]);
+    offA[k] = ia * 4;
+    offB[k] = ib * 4;
+  }
+  // ---- row taps: lane r evaluates output row y0 + r once, the row loop fetches them by shuffle ----
+  int rowA, rowB;
+  float trow;
+  bilinear_tap(min(y0 + lane, y1 - 1), im.Y0, sy, im.sy_len, im.flip_y != 0, &rowA, &rowB, &trow);
+
+  float hA[12], hB[12];  // horizontally interpolated values of source rows curA / curB, 1 + v * 2^-15 form
+  int curA = -1, curB = -1;
+  uint32_t and_acc = 0xffffffffu;
+  auto load_row = [&](int row, float* h) {
+    const uint8_t* base = im.data + (int64_t)row * im.pitch;
+    uint32_t pa[4], pb[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      pa[k] = __ldg(reinterpret_cast<const uint32_t*>(base + offA[k]));
+      pb[k] = __ldg(reinterpret_cast<const uint32_t*>(base + offB[k]));
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      and_acc &= pa[k] & pb[k];
+      const float a0 = expand<0>(pa[k]), a1 = expand<1>(pa[k]), a2 = expand<2>(pa[k]);
+      h[k * 3 + 0] = fmaf(tcol[k], expand<0>(pb[k]) - a0, a0);
+      h[k * 3 + 1] = fmaf(tcol[k], expand<1>(pb[k]) - a1, a1);
+      h[k * 3 + 2] = fmaf(tcol[k], expand<2>(pb[k]) - a2, a2);
+    }
+  };
+
+  // output pointers
+  uint8_t* orow = RGBA ? P.out_rgba + (int64_t)y0 * P.out_pitch + (int64_t)xq * 4 : nullptr;
+  const bool vec_ok = RGBA && ok[0] && ok[3] && ((((uintptr_t)P.out_rgba) | (uintptr_t)P.out_pitch) & 15) == 0;
+  uint8_t* yrow = nullptr;
+  uint8_t *cbp = nullptr, *crp = nullptr;
+  float ccb[2] = {0.f, 0.f}, ccr[2] = {0.f, 0.f};
+  int cwh = 0;
+  if (YUV) {
+    cwh = (P.cw + 1) >> 1;
+    yrow = P.out_y + (int64_t)y0 * P.cw + xq;
+    cbp = P.out_cb + (int64_t)(y0 >> 1) * cwh + (xq >> 1);
+    crp = P.out_cr + (int64_t)(y0 >> 1) * cwh + (xq >> 1);
+  }
+
+  for (int y = y0; y < y1; ++y) {
+    const int ia = __shfl_sync(0xffffffffu, rowA, y - y0);
+    const int ib = __shfl_sync(0xffffffffu, rowB, y - y0);
+    const float tv = __shfl_sync(0xffffffffu, trow, y - y0);
+    if (ia != curA) {
+      if (ia == curB) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) { const float s = hA[k]; hA[k] = hB[k]; hB[k] = s; }
+        curB = curA;
+      } else {
+        load_row(ia, hA);
+      }
+      curA = ia;
+    }
+    if (ib != curB) {
+      if (ib == curA) {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) hB[k] = hA[k];
+      } else {
+        load_row(ib, hB);
+      }
+      curB = ib;
+    }
+    float v[12];
+    const float wa = 1.f - tv;
+#pragma unroll
+    for (int k = 0; k < 12; k += 2) {
+      mul2_s(v[k], v[k + 1], hA[k], hA[k + 1], wa);
+      fma2_s(v[k], v[k + 1], hB[k], hB[k + 1], tv);
+    }
+    if (RGBA) {
+      uint32_t px[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        px[k] = pack_rgb(quant_bits(v[k * 3]), quant_bits(v[k * 3 + 1]), quant_bits_neg(v[k * 3 + 2]));
+      if (vec_ok) {
+        *reinterpret_cast<uint4*>(orow) = make_uint4(px[0], px[1], px[2], px[3]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (ok[k]) reinterpret_cast<uint32_t*>(orow)[k] = px[k];
+      }
+      orow += P.out_pitch;
+    }
+    if (YUV) {
+      uint32_t yq[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float R_ = v[k * 3], G_ = v[k * 3 + 1], B_ = v[k * 3 + 2];
+        yq[k] = quant_bits(fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_))) & 0xffu;
+        ccb[k >> 1] += fmaf(-0.168736f, R_, fmaf(-0.331264f, G_, 0.5f * B_));
+        ccr[k >> 1] += fmaf(0.5f, R_, fmaf(-0.418688f, G_, -0.081312f * B_));
+      }
+      if (ok[0] && ok[3] && (((uintptr_t)yrow) & 3) == 0) {
+        *reinterpret_cast<uint32_t*>(yrow) = yq[0] | (yq[1] << 8) | (yq[2] << 16) | (yq[3] << 24);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (ok[k]) yrow[k] = (uint8_t)yq[k];
+      }
+      yrow += P.cw;
+      if ((y & 1) != 0) {  // second row of the chroma block row (y0 is even)
+        const float bias = 1.f + 128.f / 32768.f;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          if (ok[2 * c]) {   // the region is even-aligned: a pair is inside or outside as a whole
+            cbp[c] = (uint8_t)quant_bits(fmaf(0.25f, ccb[c], bias));
+            crp[c] = (uint8_t)quant_bits(fmaf(0.25f, ccr[c], bias));
+          }
+          ccb[c] = ccr[c] = 0.f;
+        }
+        cbp += cwh;
+        crp += cwh;
+      }
+    }
+  }
+  // translucent source pixels: redo the unit with the exact premultiplied source-over evaluation
+  const bool need_fix = (and_acc >> 24) != 0xffu;
+  if (__any_sync(0xffffffffu, need_fix)) {
+    const int xa = max(R.x0, 4 * ((R.x0 >> 2) + tx * 32)), xb = min(R.x1, 4 * ((R.x0 >> 2) + tx * 32 + 32));
+    redo_rect<MODE>(P, xa, y0, xb, y1, lane, 0);
+  }
+}
+
+}  // namespace stitch

@@ -22,6 +22,10 @@ def _whole_gather(got):
     return bool(got.path_info & (1 << 24))
 
 
+def _n_up(got):
+    return (got.path_info >> 25) & 0x3F
+
+
 def _go(ctx, dims, direction, mode, size, platform="ios", orientations=None, pattern=1, gap=0, seed=11, bitmaps=None):
     bitmaps = bitmaps or [U.synth_image(w, h, seed + i, pattern) for i, (w, h) in enumerate(dims)]
     fs = [BIG] + [0] * (len(dims) - 1)
@@ -77,7 +81,7 @@ def test_ratios_above_4_stream(ctx, w, h, size):
 
 def test_ratio_above_16_uses_gather(ctx):
     got, _ = _go(ctx, [(3300, 2475)], "vertical", "min", 150)      # ratio 16.5
-    assert _n_stream(got) == 0 and _n_gather(got) == 1
+    assert _n_stream(got) == 0 and _whole_gather(got)
 
 
 def test_mixed_ratios_one_launch(ctx):
@@ -85,7 +89,7 @@ def test_mixed_ratios_one_launch(ctx):
     the launch takes the most general kernel shape (MAXO 4, HOPS 4) for all streamed images."""
     dims = [(w // 4, h // 4) for (w, h) in U.MIXED]
     got, lay = _go(ctx, dims, "horizontal", "min", 0)
-    assert _n_stream(got) == 8 and _n_gather(got) == 1
+    assert _n_stream(got) == 8 and _n_up(got) == 1
     _go_yuv(ctx, dims, "horizontal", "min", 0, min_stream=8)
     got, lay = _go(ctx, dims, "horizontal", "min", 1024)          # Android-like clamp: ratios 2.8 .. 10.5
     assert _n_stream(got) == 9
@@ -109,17 +113,18 @@ def test_transposed_in_fused_launch(ctx, orientation):
 
 
 def test_orientation7_overlaps_previous_image(ctx):
-    """EXIF 7 lands above its rect (reference quirk) and overlaps the previous image -> whole-canvas path."""
+    """EXIF 7 lands above its rect (reference quirk) and overlaps the previous image: both are composited by
+    gather pieces in painter's order, the untouched third image still streams."""
     dims = [(403, 302), (302, 403), (640, 480)]
     got, _ = _go(ctx, dims, "vertical", "min", 500, orientations=[1, 7, 1])
-    assert _whole_gather(got)
+    assert not _whole_gather(got) and _n_stream(got) == 1 and _n_gather(got) >= 1
 
 
 def test_mixed_upscale_downscale_one_launch(ctx):
     """BASELINE configs[2] at 1/8 scale: 'max' mode upscales the small images (gather) and downscales the rest."""
     dims = [(w // 8, h // 8) for (w, h) in U.MIXED]
     got, lay = _go(ctx, dims, "horizontal", "max", 1536)
-    assert _n_stream(got) >= 1 and _n_gather(got) >= 1 and not _whole_gather(got)
+    assert _n_stream(got) >= 1 and _n_up(got) >= 1 and not _whole_gather(got)
     got, lay = _go(ctx, dims, "horizontal", "min", 0)
     got, lay = _go(ctx, dims, "vertical", "min", 1000)
 
@@ -148,12 +153,13 @@ def test_translucent_fixup(ctx):
 
 
 def test_gap_integer_scaled(ctx):
-    """gap*scaleDown integral keeps rects integer (fused path); fractional gaps take the whole-canvas path."""
+    """gap*scaleDown integral keeps rects integer (all stream); with a fractional cursor only the first image
+    (rect at 0) still streams, the others are gather pieces of the same launch."""
     dims = [(400, 300)] * 3
     got, lay = _go(ctx, dims, "vertical", "min", 0, gap=6)        # no clamp: scaleDown 1, gap 6
     assert not _whole_gather(got)
     got, lay = _go(ctx, dims, "vertical", "min", 451, gap=7)      # scaleDown < 1: fractional cursor
-    assert _whole_gather(got)
+    assert _n_stream(got) == 1 and _n_gather(got) >= 1 and not _whole_gather(got)
 
 
 def test_unaligned_device_pitch_falls_back(ctx):
@@ -172,7 +178,7 @@ def test_unaligned_device_pitch_falls_back(ctx):
     got = ctx.run([{"naturalWidth": w, "naturalHeight": h, "fileSize": BIG, "bitmap": DeviceBitmap(p.value, w, h, w * 4)}],
                   "vertical", platform="ios", deviceMaxCanvasSize=50)
     lib.stitch_device_free(ctx.handle, p)
-    assert _n_stream(got) == 0 and _n_gather(got) == 1
+    assert _n_stream(got) == 0 and _whole_gather(got)
     U.check_pixels(got.rgba[:, :, :3], want["rgba"][:, :, :3], "unaligned pitch")
 
 
@@ -259,3 +265,69 @@ def test_yuv_stream_translucent(ctx):
     bm[0][100, 200, 3] = 17
     bm[1][301, 402, 3] = 254
     _go_yuv(ctx, dims, "vertical", "min", 300, bitmaps=bm)
+
+
+# ---- bilinear upscale units (BASELINE configs[0]: supersampled canvas; configs[2]: 'max' mode) ----
+
+def _go_up(ctx, dims, direction, mode, platform="ios", size=0, orientations=None, pattern=1, gap=0, seed=31, bitmaps=None,
+           outputs=("rgba", "yuv420", "both")):
+    bitmaps = bitmaps or [U.synth_image(w, h, seed + i, pattern) for i, (w, h) in enumerate(dims)]
+    prof = U.profile_of(platform, size, 0)
+    lay, want = U.oracle_render(dims, bitmaps, direction, mode, gap, prof, orientations, yuv=True)
+    tag = f"{dims} {direction}/{mode}/{platform}/{size}/{orientations}"
+    got = None
+    for output in outputs:
+        got = ctx.run(U.page_images(dims, bitmaps, orientations), direction, mode=mode, gap=gap, platform=platform,
+                      deviceMaxCanvasSize=size or None, output=output)
+        assert (got.width, got.height) == (int(lay.canvasW), int(lay.canvasH))
+        if output != "yuv420":
+            U.check_pixels(got.rgba[:, :, :3], want["rgba"][:, :, :3], tag + " rgba")
+            assert (got.rgba[:, :, 3] == 255).all()
+        if output != "rgba":
+            U.check_pixels(got.y, want["y"], tag + " Y")
+            U.check_pixels(got.cb, want["cb"], tag + " Cb")
+            U.check_pixels(got.cr, want["cr"], tag + " Cr")
+    return got, lay
+
+
+def test_upscale_supersampled_canvas(ctx):
+    """configs[0] at 1/10 scale: ss = 2.2 makes every device rect fractional; the seam row is a gather piece."""
+    got, lay = _go_up(ctx, [(108, 192)] * 2, "vertical", "min")
+    assert lay.superSample == 2.2 and _n_up(got) == 2 and not _whole_gather(got)
+    got, lay = _go_up(ctx, [(108, 192)] * 2, "vertical", "min", platform="android")      # ss 2.6
+    assert _n_up(got) == 2
+    got, lay = _go_up(ctx, [(192, 108), (96, 54), (131, 77)], "horizontal", "max", gap=3)
+    assert _n_up(got) == 3
+
+
+@pytest.mark.parametrize("orientation", [2, 3, 4, 6])
+def test_upscale_orientations(ctx, orientation):
+    got, lay = _go_up(ctx, [(101, 67), (67, 101), (80, 80)], "vertical", "max", orientations=[orientation, 1, orientation])
+    assert _n_up(got) == (3 if orientation < 5 else 1)
+
+
+def test_upscale_wide_and_tiny(ctx):
+    """More than one 128-px tile per row, odd sizes, 1-pixel sources."""
+    _go_up(ctx, [(300, 40), (150, 20)], "vertical", "max")
+    _go_up(ctx, [(1, 1), (3, 2)], "vertical", "max", outputs=("rgba", "both"))
+    _go_up(ctx, [(7, 5)], "horizontal", "min")
+
+
+def test_upscale_translucent(ctx):
+    dims = [(90, 60)] * 2
+    bm = [U.synth_image(w, h, 5 + i, 2) for i, (w, h) in enumerate(dims)]
+    got, _ = _go_up(ctx, dims, "vertical", "min", bitmaps=bm)
+    assert _n_up(got) == 2
+    bm = [U.synth_image(w, h, 5 + i, 1) for i, (w, h) in enumerate(dims)]
+    bm[0][10, 20, 3] = 17
+    bm[1][59, 89, 3] = 254
+    _go_up(ctx, dims, "vertical", "min", bitmaps=bm)
+
+
+def test_identity_copy_takes_upscale_units_exactly(ctx):
+    dims = [(257, 131), (257, 90)]
+    bm = [U.synth_image(w, h, 70 + i, 1) for i, (w, h) in enumerate(dims)]
+    fs = [BIG, 0]
+    got = ctx.run(U.page_images(dims, bm, None, fs), "vertical", platform="ios")
+    assert _n_up(got) == 2 and got.height == 221
+    assert (got.rgba[:131] == bm[0]).all() and (got.rgba[131:] == bm[1]).all()
