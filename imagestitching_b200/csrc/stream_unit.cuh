@@ -4,9 +4,9 @@
 // one image.  Replaces ctx.drawImage (U:156-199) for integer-aligned downscales.
 //
 // Bands are laid out in GROUP space: unit tx owns the outputs that start inside groups
-// [g_base + 31*tx, g_base + 31*tx + 31); lane 31 holds the next band's first group only to supply
-// the tail of lane 30's last output, so adjacent bands overlap by exactly one group (3 % of the
-// lanes) whatever the scale ratio is.
+// [g_base + S*tx, g_base + S*tx + S), S = STREAM_STRIDE_OF(MODE, HOPS); the last 32 - S lanes hold the
+// next band's first groups only to supply the tails of the outputs that reach into them (for the RGBA
+// canvas and ratio_x <= 4: S = 31, one overlap group = 3 % of the lanes whatever the scale ratio is).
 #pragma once
 #include <cuda_runtime.h>
 
