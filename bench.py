@@ -124,8 +124,9 @@ def cpu_reference_run(workload: str, steps: int, warmup: int, threads: int | Non
     from tests import util as U
 
     dims, direction, mode, platform, output, _ = WORKLOADS[workload]
-    cores = threads or os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = threads or len(os.sched_getaffinity(0)) or os.cpu_count() or 1
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use every host core
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     bitmaps = []
     cache = {}
     for i, (w, h) in enumerate(dims):
