@@ -241,7 +241,8 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   uint8_t* yptr = nullptr;
   uint8_t *cbptr = nullptr, *crptr = nullptr;
   int64_t ystep_y = 0, cstep = 0;
-  bool c_own[MAXO];
+  bool c_own[MAXO], pair_local[MAXO];
+  int c_off[MAXO];
   float ccb[MAXO], ccr[MAXO];  // vertical sums of the un-rounded chroma of the current block row
   bool second = false;          // the next emitted row completes a chroma row
   if (YUV) {
@@ -255,6 +256,8 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
     for (int o = 0; o < MAXO; ++o) {
       const int cx = cx0 + o * xdir;
       c_own[o] = st_ok[o] && ((cx & 1) == (im.flip_x ? 1 : 0));
+      pair_local[o] = o + 1 < cnt;                 // the pair's second element is this lane's next output
+      c_off[o] = (cx >> 1) - (cx0 >> 1);
       ccb[o] = ccr[o] = 0.f;
     }
   }
@@ -344,31 +347,54 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
       if (YUV) {
         // JFIF full-range BT.601.  The luma weights sum to 1, so Y keeps the biased
         // form; the chroma weights sum to 0, so the bias cancels and cb/cr are plain values * 2^-15.
+        uint32_t yq[MAXO];
 #pragma unroll
-        for (int o = 0; o < MAXO; ++o) {
+        for (int o = 0; o + 1 < MAXO; o += 2) {
+          float y0_, y1_;
+          mul2_s(y0_, y1_, out[2][o], out[2][o + 1], 0.114f);
+          fma2_s(y0_, y1_, out[1][o], out[1][o + 1], 0.587f);
+          fma2_s(y0_, y1_, out[0][o], out[0][o + 1], 0.299f);
+          quant2(yq[o], yq[o + 1], y0_, y1_);
+          fma2_s(ccb[o], ccb[o + 1], out[2][o], out[2][o + 1], 0.5f);
+          fma2_s(ccb[o], ccb[o + 1], out[1][o], out[1][o + 1], -0.331264f);
+          fma2_s(ccb[o], ccb[o + 1], out[0][o], out[0][o + 1], -0.168736f);
+          fma2_s(ccr[o], ccr[o + 1], out[2][o], out[2][o + 1], -0.081312f);
+          fma2_s(ccr[o], ccr[o + 1], out[1][o], out[1][o + 1], -0.418688f);
+          fma2_s(ccr[o], ccr[o + 1], out[0][o], out[0][o + 1], 0.5f);
+        }
+        if (MAXO & 1) {
+          const int o = MAXO - 1;
           const float R_ = out[0][o], G_ = out[1][o], B_ = out[2][o];
-          const float yv = fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_));
-          const uint32_t yq = quant_bits(yv);
-          if (st_ok[o]) yptr[o * xdir] = (uint8_t)yq;
-          ccb[o] += fmaf(-0.168736f, R_, fmaf(-0.331264f, G_, 0.5f * B_));
-          ccr[o] += fmaf(0.5f, R_, fmaf(-0.418688f, G_, -0.081312f * B_));
+          yq[o] = quant_bits(fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_)));
+          ccb[o] = fmaf(-0.168736f, R_, fmaf(-0.331264f, G_, fmaf(0.5f, B_, ccb[o])));
+          ccr[o] = fmaf(0.5f, R_, fmaf(-0.418688f, G_, fmaf(-0.081312f, B_, ccr[o])));
+        }
+        {
+          uint8_t* const yq_ptr = yptr;
+#pragma unroll
+          for (int o = 0; o < MAXO; ++o) {
+            uint8_t* const p = yq_ptr + o * xdir;
+            if (st_ok[o]) *p = (uint8_t)yq[o];
+          }
         }
         yptr += ystep_y;
-        if (second) {
+        if (__any_sync(0xffffffffu, second)) {   // warp-uniform by construction; the vote tells the compiler
           const float nb_cb = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccb[0], 1) : __shfl_sync(0xffffffffu, ccb[0], lane + nxt);
           const float nb_cr = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccr[0], 1) : __shfl_sync(0xffffffffu, ccr[0], lane + nxt);
+          const float bias = 1.f + 128.f / 32768.f;
 #pragma unroll
           for (int o = 0; o < MAXO; ++o) {
             float pcb = nb_cb, pcr = nb_cr;  // partner = output o+1
-            if (o + 1 < MAXO && o + 1 < cnt) { pcb = ccb[o + 1]; pcr = ccr[o + 1]; }
-            const float bias = 1.f + 128.f / 32768.f;
+            if (o + 1 < MAXO) {
+              pcb = pair_local[o] ? ccb[o + 1] : nb_cb;
+              pcr = pair_local[o] ? ccr[o + 1] : nb_cr;
+            }
             const uint32_t cbq = quant_bits(fmaf(0.25f, ccb[o] + pcb, bias));
             const uint32_t crq = quant_bits(fmaf(0.25f, ccr[o] + pcr, bias));
-            const int co = ((cx0 + o * xdir) >> 1) - (cx0 >> 1);
-            if (c_own[o]) {
-              cbptr[co] = (uint8_t)cbq;
-              crptr[co] = (uint8_t)crq;
-            }
+            uint8_t* const pb = cbptr + c_off[o];
+            uint8_t* const pr = crptr + c_off[o];
+            if (c_own[o]) *pb = (uint8_t)cbq;
+            if (c_own[o]) *pr = (uint8_t)crq;
           }
 #pragma unroll
           for (int o = 0; o < MAXO; ++o) ccb[o] = ccr[o] = 0.f;
