@@ -16,6 +16,7 @@ from tests import util as U
 pytestmark = pytest.mark.gpu
 
 SMALL = [(40, 30), (31, 47), (64, 64)]
+BIG_FILE = 26 * 1024 * 1024   # makes a job a 'big task' (P:1212): superSample stays 1
 
 
 def _noise(dims, seed, alpha=False):
@@ -221,6 +222,30 @@ def test_device_buffers_and_async(ctx):
     assert (host == ref.rgba).all()
     for p in dptrs + [out]:
         lib.stitch_device_free(ctx.handle, p)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_randomized_jobs(ctx, seed):
+    """Random jobs (sizes, modes, gaps, clamps, EXIF, alpha, output formats): whatever mixture of stream / upscale /
+    gather / fill units the plan chooses, layout is bit-exact and every plane is within the parity bar."""
+    rng = np.random.default_rng(1000 + seed)
+    for case in range(10):
+        n = int(rng.integers(1, 10))
+        dims = [(int(rng.integers(3, 420)), int(rng.integers(3, 420))) for _ in range(n)]
+        direction = ["vertical", "horizontal"][int(rng.integers(0, 2))]
+        mode = ["min", "max", "original"][int(rng.integers(0, 3))]
+        gap = [0, 0, 3, 7.5, 20][int(rng.integers(0, 5))]
+        platform = ["ios", "android", "other"][int(rng.integers(0, 3))]
+        size = [0, 0, int(rng.integers(60, 900))][int(rng.integers(0, 3))]
+        orientations = [int(rng.integers(1, 9)) if rng.random() < 0.25 else 1 for _ in range(n)]
+        fs = [BIG_FILE if (i == 0 and rng.random() < 0.6) else 0 for i in range(n)]
+        output = ["rgba", "yuv420", "both"][int(rng.integers(0, 3))]
+        bitmaps = []
+        for i, (w, h) in enumerate(dims):
+            pat = 2 if rng.random() < 0.1 else int(rng.integers(0, 2))      # 10 % translucent noise
+            bitmaps.append(U.synth_image(w, h, 5000 + 100 * seed + 10 * case + i, pat))
+        _run_and_check(ctx, dims, bitmaps, direction, mode, gap, platform, size, 0, orientations, output=output,
+                       file_sizes=fs)
 
 
 def test_job_lanes_batch(ctx):
