@@ -16,7 +16,7 @@ VERTICAL, HORIZONTAL = 0, 1
 MODE_MIN, MODE_MAX, MODE_ORIGINAL, MODE_OTHER = 0, 1, 2, 3
 IOS, ANDROID, OTHER = 0, 1, 2
 MEM_HOST, MEM_DEVICE = 0, 1
-OUT_RGBA, OUT_YUV420 = 1, 2
+OUT_RGBA, OUT_YUV420, OUT_JPEG = 1, 2, 4
 
 
 class StitchProfile(C.Structure):
@@ -53,12 +53,14 @@ class StitchJob(C.Structure):
     _fields_ = [("images", C.POINTER(StitchImage)), ("n", C.c_int32), ("params", StitchParams),
                 ("output_flags", C.c_int32), ("out_mem_kind", C.c_int32), ("out_rgba", C.c_void_p),
                 ("out_rgba_pitch", C.c_int64), ("out_yuv", C.c_void_p), ("out_capacity_rgba", C.c_int64),
-                ("out_capacity_yuv", C.c_int64)]
+                ("out_capacity_yuv", C.c_int64), ("out_jpeg", C.c_void_p), ("out_capacity_jpeg", C.c_int64),
+                ("jpeg_quality", C.c_int32), ("jpeg_restart_interval", C.c_int32)]
 
 
 class StitchResult(C.Structure):
     _fields_ = [("layout", StitchLayout), ("canvas_w", C.c_int32), ("canvas_h", C.c_int32), ("rgba_bytes", C.c_int64),
-                ("yuv_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("path_info", C.c_int32)]
+                ("yuv_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("path_info", C.c_int32),
+                ("jpeg_bytes", C.c_int64)]
 
 
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
@@ -75,6 +77,7 @@ SIGNATURES = {
     "stitch_ctx_join": (C.c_int, [C.c_void_p]),
     "stitch_set_progress_cb": (C.c_int, [C.c_void_p, PROGRESS_FN, C.c_void_p]),
     "stitch_output_size": (C.c_int, [C.POINTER(StitchLayout), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "stitch_jpeg_capacity": (C.c_int64, [C.POINTER(StitchLayout), C.c_int32]),
     "stitch_run": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult)]),
     "stitch_submit": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult), C.POINTER(C.c_uint64)]),
     "stitch_wait": (C.c_int, [C.c_void_p, C.c_uint64]),

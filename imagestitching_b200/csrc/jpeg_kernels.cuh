@@ -1,0 +1,358 @@
+// Baseline JPEG export of the stitched canvas on the GPU.
+//
+// Replaces the encoder behind safeCanvasToTempFilePath (U:205-242, wx.canvasToTempFilePath with fileType
+// 'jpg', quality 1) for the I420 planes the compose kernel writes.  Format: ITU-T T.81 baseline, 4:2:0,
+// Annex K tables, JFIF container, restart markers every `ri` MCUs -- the restart interval is what makes
+// the entropy coder parallel: every segment starts byte-aligned with its DC predictors at zero.
+//
+//   J1 jpeg_dct_kernel      one thread per 8x8 block: level shift, integer LL&M forward DCT in registers,
+//                           quantise, zig-zag -> int16 coefficients in MCU order (Y00 Y01 Y10 Y11 Cb Cr)
+//   J2 jpeg_entropy_kernel  one WARP per restart segment: a lane owns two zig-zag positions of the block;
+//                           zero runs come from two ballots, code lengths from a warp prefix sum, the bits
+//                           are ORed into a per-warp shared-memory window and flushed as bytes with 0xFF
+//                           stuffing into the segment's slot of the scratch stream
+//   J3 jpeg_offsets_kernel  exclusive scan of the segment lengths (+2 per restart marker) and the header
+//      jpeg_gather_kernel   one warp per segment copies it to its final place and appends RSTn / EOI
+//
+// All arithmetic is int32, so the CPU checker of the test suite reproduces the file bit for bit.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "jpeg_tables.h"
+
+namespace stitch {
+namespace jpeg {
+
+struct HeaderBytes {
+  uint8_t b[704];
+  int32_t n;
+};
+
+// worst case of one entropy-coded block: DC 9 + 11 bits, 63 x (16 + 10) bits = 1658 bits = 208 bytes, every
+// byte stuffed
+#define JPEG_BLOCK_MAX_BYTES 432
+#define JPEG_WIN_WORDS 64  // per-warp bit window: 256 bytes >= 208 + 1 carried byte
+
+#define JDESCALE(x, n) (((x) + (1 << ((n)-1))) >> (n))
+
+// one 8-point pass of the LL&M integer DCT (13-bit constants); FIRST = row pass (results scaled up by 4)
+template <bool FIRST>
+__device__ __forceinline__ void fdct8(int32_t& d0, int32_t& d1, int32_t& d2, int32_t& d3, int32_t& d4, int32_t& d5,
+                                      int32_t& d6, int32_t& d7) {
+  int32_t t0 = d0 + d7, t7 = d0 - d7, t1 = d1 + d6, t6 = d1 - d6;
+  int32_t t2 = d2 + d5, t5 = d2 - d5, t3 = d3 + d4, t4 = d3 - d4;
+  const int32_t t10 = t0 + t3, t13 = t0 - t3, t11 = t1 + t2, t12 = t1 - t2;
+  constexpr int SH = FIRST ? 11 : 15;
+  if (FIRST) {
+    d0 = (t10 + t11) << 2;
+    d4 = (t10 - t11) << 2;
+  } else {
+    d0 = JDESCALE(t10 + t11, 2);
+    d4 = JDESCALE(t10 - t11, 2);
+  }
+  int32_t z1 = (t12 + t13) * 4433;
+  d2 = JDESCALE(z1 + t13 * 6270, SH);
+  d6 = JDESCALE(z1 - t12 * 15137, SH);
+  z1 = t4 + t7;
+  int32_t z2 = t5 + t6, z3 = t4 + t6, z4 = t5 + t7;
+  const int32_t z5 = (z3 + z4) * 9633;
+  t4 *= 2446;
+  t5 *= 16819;
+  t6 *= 25172;
+  t7 *= 12299;
+  z1 *= -7373;
+  z2 *= -20995;
+  z3 = z3 * -16069 + z5;
+  z4 = z4 * -3196 + z5;
+  d7 = JDESCALE(t4 + z1 + z3, SH);
+  d5 = JDESCALE(t5 + z2 + z4, SH);
+  d3 = JDESCALE(t6 + z2 + z3, SH);
+  d1 = JDESCALE(t7 + z1 + z4, SH);
+}
+
+__device__ __forceinline__ int32_t jquant(int32_t v, int32_t qv) {
+  const bool neg = v < 0;
+  v = (neg ? -v : v) + (qv >> 1);
+  v = v >= qv ? v / qv : 0;
+  return neg ? -v : v;
+}
+
+// J1.  Threads [0, 4M) are the luma blocks in raster order of the (2*mx) x (2*my) luma block grid (so a
+// warp reads 256 contiguous bytes of each pixel row), [4M, 5M) the Cb blocks, [5M, 6M) the Cr blocks.
+__global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t* __restrict__ py, const uint8_t* __restrict__ pcb,
+                                                       const uint8_t* __restrict__ pcr, int w, int h, int mx, int my,
+                                                       const __grid_constant__ Tables tab, int16_t* __restrict__ coef) {
+  const int M = mx * my;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 6 * M) return;
+  const uint8_t* plane;
+  int pw, ph, bx, by, slot, comp;
+  if (t < 4 * M) {
+    const int gx = t % (2 * mx), gy = t / (2 * mx);
+    plane = py; pw = w; ph = h; bx = gx; by = gy; comp = 0;
+    slot = ((gy >> 1) * mx + (gx >> 1)) * 6 + ((gy & 1) << 1) + (gx & 1);
+  } else {
+    const int c = (t - 4 * M) / M, m = (t - 4 * M) % M;
+    plane = c ? pcr : pcb; pw = (w + 1) >> 1; ph = (h + 1) >> 1; bx = m % mx; by = m / mx; comp = 1;
+    slot = m * 6 + 4 + c;
+  }
+  int32_t d[64];
+  const int x0 = bx * 8, y0 = by * 8;
+  const bool fast = (x0 + 8 <= pw) && (((pw | (int)(uintptr_t)plane) & 3) == 0);
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int yy = min(y0 + r, ph - 1);
+    const uint8_t* row = plane + (size_t)yy * pw;
+    if (fast) {
+      const uint32_t a = *reinterpret_cast<const uint32_t*>(row + x0), b = *reinterpret_cast<const uint32_t*>(row + x0 + 4);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        d[r * 8 + c] = (int32_t)((a >> (8 * c)) & 0xff) - 128;
+        d[r * 8 + 4 + c] = (int32_t)((b >> (8 * c)) & 0xff) - 128;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < 8; ++c) d[r * 8 + c] = (int32_t)row[min(x0 + c, pw - 1)] - 128;  // edge replication
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < 8; ++r)
+    fdct8<true>(d[r * 8], d[r * 8 + 1], d[r * 8 + 2], d[r * 8 + 3], d[r * 8 + 4], d[r * 8 + 5], d[r * 8 + 6], d[r * 8 + 7]);
+#pragma unroll
+  for (int c = 0; c < 8; ++c)
+    fdct8<false>(d[c], d[8 + c], d[16 + c], d[24 + c], d[32 + c], d[40 + c], d[48 + c], d[56 + c]);
+  constexpr uint8_t ZZ[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                              41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                              30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+  uint32_t packed[32];
+#pragma unroll
+  for (int k = 0; k < 64; k += 2) {
+    const int32_t a = jquant(d[ZZ[k]], tab.qdiv[comp][ZZ[k]]), b = jquant(d[ZZ[k + 1]], tab.qdiv[comp][ZZ[k + 1]]);
+    packed[k >> 1] = ((uint32_t)a & 0xffffu) | ((uint32_t)b << 16);
+  }
+  uint4* o = reinterpret_cast<uint4*>(coef + (size_t)slot * 64);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) o[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
+}
+
+// ---- J2: entropy coding, one warp per restart segment ----
+
+__device__ __forceinline__ int hibit(uint32_t x) { return 31 - __clz(x); }  // -1 for x == 0
+
+// value bits of a coefficient / DC difference of magnitude category s (T.81 F.1.2.1)
+__device__ __forceinline__ uint32_t vbits(int v, int s) { return (uint32_t)(v < 0 ? v - 1 : v) & ((1u << s) - 1u); }
+
+// ORs the low `len` (<= 64) bits of `val`, MSB first, into the bit window at bit position `pos`.  The item
+// is left-aligned in 64 bits and lands in up to three words; neighbouring items share a word, hence the atomics.
+__device__ __forceinline__ void win_put(uint32_t* win, int pos, uint64_t val, int len) {
+  if (len == 0) return;
+  const uint64_t x = val << (64 - len);
+  const int wi = pos >> 5, bo = pos & 31;
+  const uint32_t w0 = (uint32_t)(x >> (32 + bo));
+  const uint32_t w1 = (uint32_t)(x >> bo);
+  const uint32_t w2 = bo ? (uint32_t)(x << (32 - bo)) : 0u;
+  if (w0) atomicOr(&win[wi], w0);
+  if (w1) atomicOr(&win[wi + 1], w1);
+  if (w2) atomicOr(&win[wi + 2], w2);
+}
+
+// `seg_cap` bytes of scratch per segment; seg_len[s] receives the byte count (stuffing included).
+__global__ void __launch_bounds__(128) jpeg_entropy_kernel(const int16_t* __restrict__ coef, int n_mcu, int ri, int n_seg,
+                                                           const __grid_constant__ Tables tab, uint8_t* __restrict__ scratch,
+                                                           int64_t seg_cap, uint32_t* __restrict__ seg_len) {
+  __shared__ uint32_t s_huff[4][256];
+  __shared__ uint32_t s_win[4][JPEG_WIN_WORDS + 4];
+  for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) s_huff[i >> 8][i & 255] = tab.huff[i >> 8][i & 255];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  uint32_t* win = s_win[warp];
+  for (int i = lane; i < JPEG_WIN_WORDS + 4; i += 32) win[i] = 0;
+  __syncthreads();
+  const int seg = blockIdx.x * 4 + warp;
+  if (seg >= n_seg) return;
+  uint8_t* out = scratch + (int64_t)seg * seg_cap;
+  const uint32_t lt = (1u << lane) - 1u;
+  int outpos = 0;   // bytes written to the segment so far
+  int carry = 0;    // bits (< 8) waiting in the window
+  int pred0 = 0, pred1 = 0, pred2 = 0;   // DC predictors of Y, Cb, Cr: zero at every restart
+  const int m0 = seg * ri, m1 = min(m0 + ri, n_mcu);
+  const uint32_t* cw = reinterpret_cast<const uint32_t*>(coef) + (size_t)m0 * 6 * 32;
+  uint32_t next = cw[lane];
+  for (int m = m0; m < m1; ++m) {
+    for (int b = 0; b < 6; ++b) {
+      const uint32_t word = next;
+      cw += 32;
+      if (!(m == m1 - 1 && b == 5)) next = cw[lane];   // prefetch the next block's coefficients
+      const int comp = b < 4 ? 0 : b - 3;
+      const uint32_t* dc = s_huff[comp ? 1 : 0];
+      const uint32_t* ac = s_huff[comp ? 3 : 2];
+      const int c0 = (int16_t)(word & 0xffffu), c1 = (int16_t)(word >> 16);   // zig-zag positions 2*lane, 2*lane+1
+      // nonzero maps; position 0 (DC) is the anchor the first run is counted from
+      const uint32_t nz0 = __ballot_sync(0xffffffffu, c0 != 0) | 1u;   // bit l <-> k = 2l
+      const uint32_t nz1 = __ballot_sync(0xffffffffu, c1 != 0);        // bit l <-> k = 2l + 1
+      uint64_t v0 = 0, v1 = 0, v2 = 0;
+      int l0 = 0, l1 = 0, l2 = 0;
+      const uint32_t zrl = ac[0xf0];
+      auto ac_item = [&](int k, int v, int prev, uint64_t& val, int& len) {
+        const int run = k - prev - 1;
+        const int s = 32 - __clz((uint32_t)(v < 0 ? -v : v));
+        const uint32_t e = ac[((run & 15) << 4) | s];
+        uint64_t x = 0;
+        int n = 0;
+        for (int z = run >> 4; z > 0; --z) {
+          x = (x << (zrl >> 16)) | (zrl & 0xffffu);
+          n += zrl >> 16;
+        }
+        x = (x << (e >> 16)) | (e & 0xffffu);
+        x = (x << s) | vbits(v, s);
+        val = x;
+        len = n + (int)(e >> 16) + s;
+      };
+      if (lane == 0) {   // DC difference
+        const int diff = c0 - (comp == 0 ? pred0 : comp == 1 ? pred1 : pred2);
+        const int s = 32 - __clz((uint32_t)(diff < 0 ? -diff : diff));
+        const uint32_t e = dc[s];
+        v0 = ((uint64_t)(e & 0xffffu) << s) | vbits(diff, s);
+        l0 = (int)(e >> 16) + s;
+      } else if (c0 != 0) {
+        const int prev = max(2 * hibit(nz0 & lt), 2 * hibit(nz1 & lt) + 1);
+        ac_item(2 * lane, c0, prev, v0, l0);
+      }
+      if (c1 != 0) {
+        const int prev = max(2 * hibit(nz0 & (lt | (1u << lane))), 2 * hibit(nz1 & lt) + 1);
+        ac_item(2 * lane + 1, c1, prev, v1, l1);
+      }
+      if (lane == 31) {   // end of block unless position 63 is coded
+        if (c1 == 0) {
+          const uint32_t e = ac[0];
+          v2 = e & 0xffffu;
+          l2 = (int)(e >> 16);
+        }
+      }
+      {
+        const int dcv = __shfl_sync(0xffffffffu, c0, 0);
+        if (comp == 0) pred0 = dcv; else if (comp == 1) pred1 = dcv; else pred2 = dcv;
+      }
+      // bit offsets: exclusive prefix sum of the lanes' lengths
+      const int mine = l0 + l1 + l2;
+      int incl = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+      }
+      const int total = carry + __shfl_sync(0xffffffffu, incl, 31);
+      int pos = carry + incl - mine;
+      win_put(win, pos, v0, l0);
+      pos += l0;
+      win_put(win, pos, v1, l1);
+      pos += l1;
+      win_put(win, pos, v2, l2);
+      __syncwarp();
+      // flush the complete bytes with 0xFF stuffing
+      const int nbytes = total >> 3;
+      int extra = 0;
+      for (int j0 = 0; j0 < nbytes; j0 += 32) {
+        const int j = j0 + lane;
+        const bool valid = j < nbytes;
+        const uint32_t by = valid ? (win[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu : 0u;
+        const uint32_t ffm = __ballot_sync(0xffffffffu, valid && by == 0xffu);
+        if (valid) {
+          const int p = outpos + j + extra + __popc(ffm & lt);
+          out[p] = (uint8_t)by;
+          if (by == 0xffu) out[p + 1] = 0;
+        }
+        extra += __popc(ffm);
+      }
+      outpos += nbytes + extra;
+      // keep the partial byte, clear the rest of the window
+      carry = total & 7;
+      const uint32_t part = carry ? ((win[nbytes >> 2] >> (24 - 8 * (nbytes & 3))) & 0xffu) << 24 : 0u;
+      __syncwarp();
+      for (int i = lane; i <= (total >> 5) + 1; i += 32) win[i] = 0;
+      __syncwarp();
+      if (lane == 0) win[0] = part;
+      __syncwarp();
+    }
+  }
+  // pad the last byte with 1-bits (stuffed like any other byte)
+  if (lane == 0) {
+    if (carry) {
+      const uint32_t by = ((win[0] >> 24) & 0xffu) | ((1u << (8 - carry)) - 1u);
+      out[outpos++] = (uint8_t)by;
+      if (by == 0xffu) out[outpos++] = 0;
+    }
+    seg_len[seg] = (uint32_t)outpos;
+  }
+}
+
+// ---- J3: place the segments ----
+
+// One block: exclusive scan of (seg_len + 2 bytes of RSTn, none after the last segment) starting behind the
+// header; writes the header, the segment offsets and the total file size (EOI included).  info[0] = total
+// bytes, info[1] = 1 when the file does not fit `cap`.
+__global__ void __launch_bounds__(1024) jpeg_offsets_kernel(const uint32_t* __restrict__ seg_len, int n_seg,
+                                                            const __grid_constant__ HeaderBytes hdr, uint8_t* __restrict__ out,
+                                                            int64_t cap, uint64_t* __restrict__ seg_off, uint64_t* __restrict__ info) {
+  __shared__ uint64_t s_warp[32];
+  __shared__ uint64_t s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_carry = (uint64_t)hdr.n;
+  __syncthreads();
+  for (int base = 0; base < n_seg; base += 1024) {
+    const int i = base + tid;
+    const uint64_t mine = i < n_seg ? (uint64_t)seg_len[i] + (i + 1 < n_seg ? 2u : 0u) : 0u;
+    uint64_t incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint64_t up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      uint64_t v = s_warp[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint64_t up = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += up;
+      }
+      s_warp[lane] = v;
+    }
+    __syncthreads();
+    const uint64_t before = s_carry + (warp ? s_warp[warp - 1] : 0) + incl - mine;
+    if (i < n_seg) seg_off[i] = before;
+    __syncthreads();
+    if (tid == 1023) s_carry = before + mine;
+    __syncthreads();
+  }
+  const uint64_t total = s_carry + 2;   // EOI
+  if (tid == 0) {
+    info[0] = total;
+    info[1] = total > (uint64_t)cap ? 1u : 0u;
+  }
+  if (total <= (uint64_t)cap)
+    for (int i = tid; i < hdr.n; i += 1024) out[i] = hdr.b[i];
+}
+
+// One warp per segment: copy it behind its predecessors, then RSTn (n = segment index mod 8) or, after the
+// last one, EOI.
+__global__ void __launch_bounds__(256) jpeg_gather_kernel(const uint8_t* __restrict__ scratch, int64_t seg_cap,
+                                                          const uint32_t* __restrict__ seg_len,
+                                                          const uint64_t* __restrict__ seg_off, int n_seg,
+                                                          const uint64_t* __restrict__ info, uint8_t* __restrict__ out) {
+  const int seg = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (seg >= n_seg || info[1]) return;
+  const uint8_t* src = scratch + (int64_t)seg * seg_cap;
+  uint8_t* dst = out + seg_off[seg];
+  const uint32_t n = seg_len[seg];
+  for (uint32_t j = lane; j < n; j += 32) dst[j] = src[j];
+  if (lane == 0) {
+    dst[n] = 0xff;
+    dst[n + 1] = (uint8_t)(seg + 1 < n_seg ? 0xd0 + (seg & 7) : 0xd9);
+  }
+}
+
+}  // namespace jpeg
+}  // namespace stitch

@@ -241,6 +241,17 @@ extern "C" int stitch_output_size(const StitchLayout* layout, int64_t* rgba_byte
   return STITCH_OK;
 }
 
+extern "C" int64_t stitch_jpeg_capacity(const StitchLayout* layout, int32_t restart_interval) {
+  if (!layout) return 0;
+  const int64_t w = (int64_t)dmax(1, std::floor(layout->canvas_w));
+  const int64_t h = (int64_t)dmax(1, std::floor(layout->canvas_h));
+  const int64_t ri = restart_interval > 0 ? restart_interval : 8;
+  const int64_t mcus = ((w + 15) / 16) * ((h + 15) / 16);
+  const int64_t segs = (mcus + ri - 1) / ri;
+  // header < 1 KB; 6 blocks of at most 432 bytes per MCU; per segment one padded byte (stuffed) + RSTn
+  return 1024 + mcus * 6 * 432 + segs * 4 + 2;
+}
+
 extern "C" const char* stitch_strerror(int status) {
   switch (status) {
     case STITCH_OK: return "ok";

@@ -20,6 +20,7 @@
 #include "stitch.h"
 #include "stitch_plan.h"
 #include "launch.cuh"
+#include "jpeg_kernels.cuh"
 #include "synth.cuh"
 
 struct PendingJob {
@@ -40,6 +41,11 @@ struct Lane {
   std::vector<size_t> in_stage_cap;
   void* out_stage = nullptr;
   size_t out_stage_cap = 0;
+  // JPEG export: one grow-only device arena (I420 planes when the caller did not ask for them, coefficients,
+  // segment scratch, lengths / offsets / info, file staging for host outputs) and a pinned info word pair
+  void* jpeg_arena = nullptr;
+  size_t jpeg_arena_cap = 0;
+  uint64_t* jpeg_info_host = nullptr;
 };
 
 struct StitchCtx {
@@ -139,6 +145,8 @@ void free_lane(Lane& ln) {
   for (void* p : ln.in_stage)
     if (p) cudaFree(p);
   if (ln.out_stage) cudaFree(ln.out_stage);
+  if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
+  if (ln.jpeg_info_host) cudaFreeHost(ln.jpeg_info_host);
   stitch::free_scratch(ln.scratch);
   if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
   ln = Lane();
@@ -175,6 +183,10 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
 
   int flags = job->output_flags ? job->output_flags : STITCH_OUT_RGBA;
   const bool want_rgba = (flags & STITCH_OUT_RGBA) != 0, want_yuv = (flags & STITCH_OUT_YUV420) != 0;
+  const bool want_jpeg = (flags & STITCH_OUT_JPEG) != 0;
+  if (want_jpeg && (!job->out_jpeg || job->out_capacity_jpeg < 1024))
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer missing or too small)");
+  if (want_jpeg && (cw > 65535 || ch > 65535)) return fail(ctx, STITCH_E_BAD_ARG, "JPEG export: canvas side above 65535");
   // [3] surface (U:131-150, P:1388-1413): the caller's buffer is the canvas.
   const int64_t rgba_pitch = job->out_rgba_pitch ? job->out_rgba_pitch : (int64_t)cw * 4;
   if (want_rgba) {
@@ -251,10 +263,57 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     if (want_rgba) d_rgba = (uint8_t*)job->out_rgba;
     if (want_yuv) d_yuv = (uint8_t*)job->out_yuv;
   }
+  // JPEG export: carve the lane's arena.  The encoder reads the I420 planes of this launch: the caller's
+  // when STITCH_OUT_YUV420 is set too, planes inside the arena otherwise.
+  const int64_t cwh = (cw + 1) / 2, chh = (ch + 1) / 2;
+  const int jpeg_ri = job->jpeg_restart_interval > 0 ? job->jpeg_restart_interval : 8;
+  const int jpeg_q = job->jpeg_quality > 0 ? (job->jpeg_quality > 100 ? 100 : job->jpeg_quality) : 100;
+  const int mcu_x = (cw + 15) / 16, mcu_y = (ch + 15) / 16, n_mcu = mcu_x * mcu_y;
+  const int n_seg = (n_mcu + jpeg_ri - 1) / jpeg_ri;
+  const int64_t seg_cap = (int64_t)jpeg_ri * 6 * JPEG_BLOCK_MAX_BYTES + 16;
+  uint8_t* j_file = nullptr;
+  int16_t* j_coef = nullptr;
+  uint8_t* j_scratch = nullptr;
+  uint32_t* j_len = nullptr;
+  uint64_t *j_off = nullptr, *j_info = nullptr;
+  int64_t j_cap = 0;
+  if (want_jpeg) {
+    if (jpeg_ri > 65535) return fail(ctx, STITCH_E_BAD_ARG, "JPEG restart interval above 65535");
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const int64_t worst = 1024 + (int64_t)n_mcu * 6 * JPEG_BLOCK_MAX_BYTES + (int64_t)n_seg * 4 + 2;
+    j_cap = job->out_capacity_jpeg < worst ? job->out_capacity_jpeg : worst;
+    const size_t b_yuv = want_yuv ? 0 : up((size_t)res->yuv_bytes);
+    const size_t b_coef = up((size_t)n_mcu * 6 * 64 * sizeof(int16_t));
+    const size_t b_scr = up((size_t)n_seg * (size_t)seg_cap);
+    const size_t b_len = up((size_t)n_seg * 4), b_off = up((size_t)n_seg * 8), b_info = 256;
+    const size_t b_file = out_host ? up((size_t)j_cap) : 0;
+    const size_t need = b_yuv + b_coef + b_scr + b_len + b_off + b_info + b_file;
+    if (ln.jpeg_arena_cap < need) {
+      if (ln.jpeg_arena) {
+        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+        CUDA_TRY(ctx, cudaFree(ln.jpeg_arena));
+      }
+      ln.jpeg_arena = nullptr;
+      ln.jpeg_arena_cap = 0;
+      if (cudaMalloc(&ln.jpeg_arena, need) != cudaSuccess)
+        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG work buffers allocation failed)");
+      ln.jpeg_arena_cap = need;
+    }
+    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+    uint8_t* a = (uint8_t*)ln.jpeg_arena;
+    if (!want_yuv) d_yuv = a;
+    a += b_yuv;
+    j_coef = (int16_t*)a; a += b_coef;
+    j_scratch = a; a += b_scr;
+    j_len = (uint32_t*)a; a += b_len;
+    j_off = (uint64_t*)a; a += b_off;
+    j_info = (uint64_t*)a; a += b_info;
+    j_file = out_host ? a : (uint8_t*)job->out_jpeg;
+  }
+  const bool planes = want_yuv || want_jpeg;
   P.out_rgba = d_rgba;
   P.out_pitch = d_rgba_pitch;
-  if (want_yuv) {
-    const int64_t cwh = (cw + 1) / 2, chh = (ch + 1) / 2;
+  if (planes) {
     P.out_y = d_yuv;
     P.out_cb = d_yuv + (int64_t)cw * ch;
     P.out_cr = P.out_cb + cwh * chh;
@@ -263,7 +322,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   // [4] the draw loop (P:1439-1572) as fused launches
   int launches = 0;
   int path_info = 0;
-  st = stitch::launch_job(P, want_rgba, want_yuv, ctx->sm_count, ln.scratch, ln.stream, &launches, &path_info);
+  st = stitch::launch_job(P, want_rgba, planes, ctx->sm_count, ln.scratch, ln.stream, &launches, &path_info);
   res->path_info = path_info;
   if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
   ctx->launches += launches;
@@ -277,6 +336,35 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
                                       cudaMemcpyDeviceToHost, ln.stream));
     if (want_yuv)
       CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ln.stream));
+  }
+  // [5b] export as a JPEG file (U:211-221 with fileType 'jpg'): DCT + quantise, entropy-code one restart
+  // segment per warp, scan the segment sizes, gather.  The file size must reach the host before the call
+  // returns, so a JPEG job is complete when this function returns (also under stitch_submit).
+  if (want_jpeg) {
+    stitch::jpeg::Tables tab;
+    stitch::jpeg::build_tables(jpeg_q, &tab);
+    stitch::jpeg::HeaderBytes hdr;
+    const std::vector<uint8_t> hv = stitch::jpeg::header(cw, ch, jpeg_q, jpeg_ri);
+    if (hv.size() > sizeof hdr.b) return fail(ctx, STITCH_E_BAD_ARG, "JPEG header too long");
+    std::memcpy(hdr.b, hv.data(), hv.size());
+    hdr.n = (int32_t)hv.size();
+    const int n_blocks = n_mcu * 6;
+    stitch::jpeg::jpeg_dct_kernel<<<(n_blocks + 127) / 128, 128, 0, ln.stream>>>(P.out_y, P.out_cb, P.out_cr, cw, ch, mcu_x,
+                                                                              mcu_y, tab, j_coef);
+    stitch::jpeg::jpeg_entropy_kernel<<<(n_seg + 3) / 4, 128, 0, ln.stream>>>(j_coef, n_mcu, jpeg_ri, n_seg, tab, j_scratch,
+                                                                             seg_cap, j_len);
+    stitch::jpeg::jpeg_offsets_kernel<<<1, 1024, 0, ln.stream>>>(j_len, n_seg, hdr, j_file, j_cap, j_off, j_info);
+    stitch::jpeg::jpeg_gather_kernel<<<(n_seg + 7) / 8, 256, 0, ln.stream>>>(j_scratch, seg_cap, j_len, j_off, n_seg, j_info,
+                                                                            j_file);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches += 4;
+    res->kernel_launches += 4;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, j_info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    res->jpeg_bytes = (int64_t)ln.jpeg_info_host[0];
+    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer too small; see jpeg_bytes)");
+    if (out_host)
+      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_jpeg, j_file, (size_t)res->jpeg_bytes, cudaMemcpyDeviceToHost, ln.stream));
   }
   return STITCH_OK;
 }

@@ -61,9 +61,17 @@ class StitchOutput:
     y: Any = None
     cb: Any = None
     cr: Any = None
+    jpeg: Optional[bytes] = None   # the exported JFIF file (output "...+jpeg" / "jpeg")
     kernel_launches: int = 0
     path_info: int = 0
     progress: List[int] = field(default_factory=list)
+
+
+def _output_flags(output: str) -> int:
+    flags = 0
+    for part in output.split("+"):
+        flags |= {"rgba": L.OUT_RGBA, "yuv420": L.OUT_YUV420, "both": L.OUT_RGBA | L.OUT_YUV420, "jpeg": L.OUT_JPEG}[part]
+    return flags
 
 
 def _profile_struct(platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
@@ -210,7 +218,8 @@ class StitchContext:
     # -- job construction ----------------------------------------------------
     def build_job(self, images: Sequence[Dict[str, Any]], direction: str, mode: Optional[str], gap,
                   profile: L.StitchProfile, output: str, out_device: bool = False, out_rgba_ptr: int = 0,
-                  out_yuv_ptr: int = 0, out_rgba_capacity: int = 0, out_yuv_capacity: int = 0):
+                  out_yuv_ptr: int = 0, out_rgba_capacity: int = 0, out_yuv_capacity: int = 0, out_jpeg_ptr: int = 0,
+                  out_jpeg_capacity: int = 0, jpeg_quality: int = 0, jpeg_restart_interval: int = 0):
         n = len(images)
         arr = (L.StitchImage * max(n, 1))()
         keep = []
@@ -238,19 +247,25 @@ class StitchContext:
         job.images = arr
         job.n = n
         job.params = _params(direction, mode, gap, profile)
-        job.output_flags = {"rgba": L.OUT_RGBA, "yuv420": L.OUT_YUV420, "both": L.OUT_RGBA | L.OUT_YUV420}[output]
+        job.output_flags = _output_flags(output)
         job.out_mem_kind = L.MEM_DEVICE if out_device else L.MEM_HOST
         job.out_rgba = out_rgba_ptr or None
         job.out_yuv = out_yuv_ptr or None
         job.out_capacity_rgba = out_rgba_capacity
         job.out_capacity_yuv = out_yuv_capacity
+        job.out_jpeg = out_jpeg_ptr or None
+        job.out_capacity_jpeg = out_jpeg_capacity
+        job.jpeg_quality = jpeg_quality
+        job.jpeg_restart_interval = jpeg_restart_interval
         return job, (arr, keep)
 
     def run(self, images: Sequence[Dict[str, Any]], direction: str, *, mode: Optional[str] = "min", gap=0,
             platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
             deviceMaxCanvasPixels: Optional[int] = None, output: str = "rgba",
-            on_progress: Optional[Callable[[int], None]] = None) -> Optional[StitchOutput]:
-        """Synchronous stitch with host outputs (numpy).  Returns None for an empty list (index.js:1189)."""
+            on_progress: Optional[Callable[[int], None]] = None, jpeg_quality: int = 0,
+            jpeg_restart_interval: int = 0, jpeg_capacity: int = 0) -> Optional[StitchOutput]:
+        """Synchronous stitch with host outputs (numpy).  Returns None for an empty list (index.js:1189).
+        `output`: "rgba" | "yuv420" | "both", optionally "+jpeg", or "jpeg" alone (the exported file)."""
         lib = self.lib
         if not images:
             return None
@@ -265,12 +280,18 @@ class StitchContext:
         rb, yb = C.c_int64(), C.c_int64()
         lib.stitch_output_size(C.byref(lay), C.byref(rb), C.byref(yb))
         cw, ch = int(lay.canvas_w), int(lay.canvas_h)
-        rgba = np.empty((ch, cw, 4), dtype=np.uint8) if output in ("rgba", "both") else None
-        yuv = np.empty(yb.value, dtype=np.uint8) if output in ("yuv420", "both") else None
+        flags = _output_flags(output)
+        rgba = np.empty((ch, cw, 4), dtype=np.uint8) if flags & L.OUT_RGBA else None
+        yuv = np.empty(yb.value, dtype=np.uint8) if flags & L.OUT_YUV420 else None
+        jpg = None
+        if flags & L.OUT_JPEG:
+            jpg = np.empty(jpeg_capacity or int(lib.stitch_jpeg_capacity(C.byref(lay), jpeg_restart_interval)), dtype=np.uint8)
         job, keep = self.build_job(images, direction, mode, gap, profile, output, False,
                                    rgba.ctypes.data if rgba is not None else 0,
                                    yuv.ctypes.data if yuv is not None else 0,
-                                   rgba.nbytes if rgba is not None else 0, yuv.nbytes if yuv is not None else 0)
+                                   rgba.nbytes if rgba is not None else 0, yuv.nbytes if yuv is not None else 0,
+                                   jpg.ctypes.data if jpg is not None else 0, jpg.nbytes if jpg is not None else 0,
+                                   jpeg_quality, jpeg_restart_interval)
         progress: List[int] = []
 
         def _cb(_user, pct):
@@ -286,9 +307,13 @@ class StitchContext:
         finally:
             lib.stitch_set_progress_cb(self.handle, C.cast(None, L.PROGRESS_FN), None)
         if st != L.OK:
+            if st == L.E_NO_SURFACE and res.jpeg_bytes:
+                raise StitchError(st, f"JPEG output buffer too small: {res.jpeg_bytes} bytes needed")
             _raise(st, self.handle)
         out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, path_info=res.path_info, progress=progress)
         out.rgba = rgba
+        if jpg is not None:
+            out.jpeg = jpg[: res.jpeg_bytes].tobytes()
         if yuv is not None:
             cwh, chh = (cw + 1) // 2, (ch + 1) // 2
             out.y = yuv[: cw * ch].reshape(ch, cw)

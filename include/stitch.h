@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 1
+#define STITCH_ABI_VERSION 2
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -123,7 +123,7 @@ typedef void (*StitchProgressFn)(void* user, int32_t percent);
 int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 
 typedef enum StitchMemKind { STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1 } StitchMemKind;
-typedef enum StitchOutputFlags { STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2 } StitchOutputFlags;
+typedef enum StitchOutputFlags { STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4 } StitchOutputFlags;
 
 /* A decoded bitmap (what loadImageFrom hands to drawWithOrientation, P:1445-1463,1532):
  * RGBA8, straight (non-premultiplied) alpha, row pitch in bytes (>= 4*bmp_width). */
@@ -146,6 +146,12 @@ typedef struct StitchJob {
   int64_t out_rgba_pitch;
   void* out_yuv;          /* planar I420: Y[h][w], Cb[ceil(h/2)][ceil(w/2)], Cr[...]; tightly packed */
   int64_t out_capacity_rgba, out_capacity_yuv; /* bytes available; too small -> STITCH_E_NO_SURFACE */
+  /* STITCH_OUT_JPEG: the export file itself (U:205-242 with fileType 'jpg'): baseline JFIF, YCbCr 4:2:0,
+   * encoded on the GPU from the I420 planes of the same launch.  Lives where out_mem_kind says. */
+  void* out_jpeg;
+  int64_t out_capacity_jpeg;      /* bytes available; stitch_jpeg_capacity() is always enough */
+  int32_t jpeg_quality;           /* 1..100 (IJG scale); 0 = 100, the reference's `quality: 1` */
+  int32_t jpeg_restart_interval;  /* MCUs between restart markers; 0 = default (8) */
 } StitchJob;
 
 typedef struct StitchResult {
@@ -154,11 +160,17 @@ typedef struct StitchResult {
   int64_t rgba_bytes, yuv_bytes;
   int32_t kernel_launches;    /* kernels launched for this job */
   int32_t path_info;          /* diagnostics: bits 0-7 streaming regions, 8-15 gather regions, 16-23 fill
-                                 regions of the fused compose launch; bit 24 = whole-canvas gather launch */
+                                 regions of the fused compose launch; bit 24 = whole-canvas gather launch;
+                                 bits 25-30 upscale regions */
+  int64_t jpeg_bytes;         /* size of the JPEG file written to out_jpeg (or needed, on STITCH_E_NO_SURFACE) */
 } StitchResult;
 
 /* Required output sizes for a layout (export region == whole canvas, U:206-209, P:1577-1579). */
 int stitch_output_size(const StitchLayout* layout, int64_t* rgba_bytes, int64_t* yuv_bytes);
+/* Worst-case size of the JPEG export of this layout (every coefficient coded at full length, every byte
+ * stuffed): a capacity that can never be too small.  Real files are a fraction of it; a smaller capacity
+ * is accepted and reported through STITCH_E_NO_SURFACE + result.jpeg_bytes (the size needed) if exceeded. */
+int64_t stitch_jpeg_capacity(const StitchLayout* layout, int32_t restart_interval);
 
 /* Synchronous onStitch(): layout -> draw all images -> export into the caller's buffer. (P:1186-1633) */
 int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
