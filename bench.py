@@ -37,6 +37,8 @@ WORKLOADS = {
              "9x 4032x3024 RGBA vertical stitch, iOS canvas clamp -> 1820x12288 (BASELINE configs[1])"),
     "cfg2_yuv": ([(4032, 3024)] * 9, "vertical", "min", "ios", "yuv420",
                  "9x 4032x3024 vertical stitch with fused RGBA->YUV420 epilogue (BASELINE configs[3])"),
+    "cfg2_jpeg": ([(4032, 3024)] * 9, "vertical", "min", "ios", "jpeg",
+                  "9x 4032x3024 vertical stitch exported as a baseline JPEG file (quality 90, GPU encoder; SURVEY 8f rank 1)"),
     "cfg1": ([(1080, 1920)] * 2, "vertical", "min", "ios", "rgba",
              "2x 1080x1920 vertical stitch, 2.2x supersampled canvas 2376x8448 (BASELINE configs[0])"),
     "cfg3": (MIXED, "horizontal", "max", "ios", "rgba",
@@ -233,6 +235,8 @@ def main():
     rgba_bytes = cw * ch * 4
     yuv_bytes = cw * ch + 2 * ((cw + 1) // 2) * ((ch + 1) // 2)
     src_bytes = sum(w * h * 4 for (w, h) in dims)
+    has_jpeg = output == "jpeg"
+    jpeg_cap = 64 << 20 if has_jpeg else 0        # quality 90: the 22 MP canvas compresses to a few MB
     out_bytes = (rgba_bytes if output in ("rgba", "both") else 0) + (yuv_bytes if output in ("yuv420", "both") else 0)
     algo_bytes = src_bytes + out_bytes
 
@@ -240,10 +244,12 @@ def main():
     for (imgs, keep) in slots:
         o_rgba = torch.empty(rgba_bytes, dtype=torch.uint8, device="cuda") if output in ("rgba", "both") else None
         o_yuv = torch.empty(yuv_bytes, dtype=torch.uint8, device="cuda") if output in ("yuv420", "both") else None
+        o_jpeg = torch.empty(jpeg_cap, dtype=torch.uint8, device="cuda") if has_jpeg else None
         job, keep2 = ctx.build_job(imgs, direction, mode, 0, profile, output, True,
                                    o_rgba.data_ptr() if o_rgba is not None else 0,
-                                   o_yuv.data_ptr() if o_yuv is not None else 0, rgba_bytes, yuv_bytes)
-        jobs.append((job, keep2, o_rgba, o_yuv))
+                                   o_yuv.data_ptr() if o_yuv is not None else 0, rgba_bytes, yuv_bytes,
+                                   o_jpeg.data_ptr() if has_jpeg else 0, jpeg_cap, 90 if has_jpeg else 0, 0)
+        jobs.append((job, keep2, o_rgba, o_yuv, o_jpeg))
     res = L.StitchResult()
 
     def step(i):
@@ -319,8 +325,13 @@ def main():
         if output in ("yuv420", "both"):
             assert lib.stitch_host_alloc(yuv_bytes, C.byref(ho_yuv)) == 0
         host_outs += [ho_rgba, ho_yuv]
+        ho_jpeg = C.c_void_p()
+        if has_jpeg:
+            assert lib.stitch_host_alloc(jpeg_cap, C.byref(ho_jpeg)) == 0
+            host_outs.append(ho_jpeg)
         hjobs.append(ctx.build_job(host_imgs, direction, mode, 0, profile, output, False, ho_rgba.value or 0,
-                                   ho_yuv.value or 0, rgba_bytes, yuv_bytes))
+                                   ho_yuv.value or 0, rgba_bytes, yuv_bytes, ho_jpeg.value or 0, jpeg_cap,
+                                   90 if has_jpeg else 0, 0))
     hres = L.StitchResult()
 
     def e2e_loop(nsteps):
@@ -352,6 +363,9 @@ def main():
         e2e_s = float(t.item())
     e2e_value = mp * e2e_steps * world / e2e_s
 
+    if has_jpeg:
+        out_bytes = int(hres.jpeg_bytes)          # d2h of the e2e step = the file
+        algo_bytes = src_bytes + out_bytes
     peak, peak_src = _peaks()
     achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9   # one compose launch per step
     line = {

@@ -33,7 +33,8 @@ struct HeaderBytes {
 // worst case of one entropy-coded block: DC 9 + 11 bits, 63 x (16 + 10) bits = 1658 bits = 208 bytes, every
 // byte stuffed
 #define JPEG_BLOCK_MAX_BYTES 432
-#define JPEG_WIN_WORDS 64  // per-warp bit window: 256 bytes >= 208 + 1 carried byte
+#define JPEG_WIN_WORDS 128      // per-warp bit window: 512 bytes
+#define JPEG_FLUSH_BITS 2048     // flush once this much is waiting: 2047 + 1665 (worst block) bits still fit
 
 #define JDESCALE(x, n) (((x) + (1 << ((n)-1))) >> (n))
 
@@ -72,11 +73,13 @@ __device__ __forceinline__ void fdct8(int32_t& d0, int32_t& d1, int32_t& d2, int
   d1 = JDESCALE(t7 + z1 + z4, SH);
 }
 
-__device__ __forceinline__ int32_t jquant(int32_t v, int32_t qv) {
+// round-half-up division of the magnitude by qv = q * 8; the quotient comes from a multiply-high with
+// ceil(2^32 / qv), exact for every numerator an 8-bit block can produce (< 2^16)
+__device__ __forceinline__ int32_t jquant(int32_t v, int32_t qv, uint32_t magic) {
   const bool neg = v < 0;
-  v = (neg ? -v : v) + (qv >> 1);
-  v = v >= qv ? v / qv : 0;
-  return neg ? -v : v;
+  const uint32_t n = (uint32_t)(neg ? -v : v) + (uint32_t)(qv >> 1);
+  const int32_t r = (int32_t)__umulhi(n, magic);
+  return neg ? -r : r;
 }
 
 // J1.  Threads [0, 4M) are the luma blocks in raster order of the (2*mx) x (2*my) luma block grid (so a
@@ -129,7 +132,8 @@ __global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t* __restrict
   uint32_t packed[32];
 #pragma unroll
   for (int k = 0; k < 64; k += 2) {
-    const int32_t a = jquant(d[ZZ[k]], tab.qdiv[comp][ZZ[k]]), b = jquant(d[ZZ[k + 1]], tab.qdiv[comp][ZZ[k + 1]]);
+    const int32_t a = jquant(d[ZZ[k]], tab.qdiv[comp][ZZ[k]], tab.qmagic[comp][ZZ[k]]);
+    const int32_t b = jquant(d[ZZ[k + 1]], tab.qdiv[comp][ZZ[k + 1]], tab.qmagic[comp][ZZ[k + 1]]);
     packed[k >> 1] = ((uint32_t)a & 0xffffu) | ((uint32_t)b << 16);
   }
   uint4* o = reinterpret_cast<uint4*>(coef + (size_t)slot * 64);
@@ -174,7 +178,7 @@ __global__ void __launch_bounds__(128) jpeg_entropy_kernel(const int16_t* __rest
   uint8_t* out = scratch + (int64_t)seg * seg_cap;
   const uint32_t lt = (1u << lane) - 1u;
   int outpos = 0;   // bytes written to the segment so far
-  int carry = 0;    // bits (< 8) waiting in the window
+  int carry = 0;    // bits waiting in the window (< JPEG_FLUSH_BITS between blocks)
   int pred0 = 0, pred1 = 0, pred2 = 0;   // DC predictors of Y, Cb, Cr: zero at every restart
   const int m0 = seg * ri, m1 = min(m0 + ri, n_mcu);
   const uint32_t* cw = reinterpret_cast<const uint32_t*>(coef) + (size_t)m0 * 6 * 32;
@@ -250,30 +254,33 @@ __global__ void __launch_bounds__(128) jpeg_entropy_kernel(const int16_t* __rest
       pos += l1;
       win_put(win, pos, v2, l2);
       __syncwarp();
-      // flush the complete bytes with 0xFF stuffing
-      const int nbytes = total >> 3;
-      int extra = 0;
-      for (int j0 = 0; j0 < nbytes; j0 += 32) {
-        const int j = j0 + lane;
-        const bool valid = j < nbytes;
-        const uint32_t by = valid ? (win[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu : 0u;
-        const uint32_t ffm = __ballot_sync(0xffffffffu, valid && by == 0xffu);
-        if (valid) {
-          const int p = outpos + j + extra + __popc(ffm & lt);
-          out[p] = (uint8_t)by;
-          if (by == 0xffu) out[p + 1] = 0;
+      carry = total;
+      // flush the complete bytes with 0xFF stuffing once enough of them wait (and at the segment's end)
+      if (total >= JPEG_FLUSH_BITS || (m == m1 - 1 && b == 5)) {
+        const int nbytes = total >> 3;
+        int extra = 0;
+        for (int j0 = 0; j0 < nbytes; j0 += 32) {
+          const int j = j0 + lane;
+          const bool valid = j < nbytes;
+          const uint32_t by = valid ? (win[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu : 0u;
+          const uint32_t ffm = __ballot_sync(0xffffffffu, valid && by == 0xffu);
+          if (valid) {
+            const int p = outpos + j + extra + __popc(ffm & lt);
+            out[p] = (uint8_t)by;
+            if (by == 0xffu) out[p + 1] = 0;
+          }
+          extra += __popc(ffm);
         }
-        extra += __popc(ffm);
+        outpos += nbytes + extra;
+        // keep the partial byte, clear the rest of the window
+        carry = total & 7;
+        const uint32_t part = carry ? ((win[nbytes >> 2] >> (24 - 8 * (nbytes & 3))) & 0xffu) << 24 : 0u;
+        __syncwarp();
+        for (int i = lane; i <= (total >> 5) + 1; i += 32) win[i] = 0;
+        __syncwarp();
+        if (lane == 0) win[0] = part;
+        __syncwarp();
       }
-      outpos += nbytes + extra;
-      // keep the partial byte, clear the rest of the window
-      carry = total & 7;
-      const uint32_t part = carry ? ((win[nbytes >> 2] >> (24 - 8 * (nbytes & 3))) & 0xffu) << 24 : 0u;
-      __syncwarp();
-      for (int i = lane; i <= (total >> 5) + 1; i += 32) win[i] = 0;
-      __syncwarp();
-      if (lane == 0) win[0] = part;
-      __syncwarp();
     }
   }
   // pad the last byte with 1-bits (stuffed like any other byte)

@@ -70,7 +70,8 @@ inline void huff_table(const uint8_t* bits, const uint8_t* val, uint32_t* out256
 
 // Device-side constants of one encode: quantisation divisors (q * 8, natural order) and the four code tables.
 struct Tables {
-  uint16_t qdiv[2][64];       // [luma, chroma][natural index]
+  uint16_t qdiv[2][64];       // [luma, chroma][natural index]: divisor q * 8 (the DCT output is scaled by 8)
+  uint32_t qmagic[2][64];     // ceil(2^32 / qdiv): floor(n / qdiv) == umulhi(n, qmagic) for n < 2^21
   uint32_t huff[4][256];      // DC luma, DC chroma, AC luma, AC chroma: code | len << 16
 };
 
@@ -78,7 +79,10 @@ inline void build_tables(int quality, Tables* t) {
   uint8_t q[64];
   for (int c = 0; c < 2; ++c) {
     quant_table(c != 0, quality, q);
-    for (int i = 0; i < 64; ++i) t->qdiv[c][i] = (uint16_t)(q[i] * 8);
+    for (int i = 0; i < 64; ++i) {
+      t->qdiv[c][i] = (uint16_t)(q[i] * 8);
+      t->qmagic[c][i] = (uint32_t)(((1ull << 32) + t->qdiv[c][i] - 1) / t->qdiv[c][i]);
+    }
   }
   huff_table(JDC_LUMA_BITS, JDC_LUMA_VAL, t->huff[0]);
   huff_table(JDC_CHROMA_BITS, JDC_CHROMA_VAL, t->huff[1]);

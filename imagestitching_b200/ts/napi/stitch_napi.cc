@@ -21,7 +21,7 @@ struct RunData {
   std::vector<napi_ref> keep;          // the Uint8Arrays stay alive until completion
   StitchJob job{};
   StitchResult result{};
-  std::vector<uint8_t> rgba, yuv;
+  std::vector<uint8_t> rgba, yuv, jpeg;
   int status = 0;
   std::string message;
   napi_deferred deferred = nullptr;
@@ -86,7 +86,9 @@ void complete(napi_env env, napi_status, void* p) {
     napi_create_typedarray(env, napi_uint8_array, buf.size(), ab, 0, &ta);
     napi_set_named_property(env, out, key, ta);
   };
-  if (d->status == STITCH_OK) { attach("rgba", d->rgba); attach("yuv", d->yuv); }
+  if (d->status == STITCH_OK) { attach("rgba", d->rgba); attach("yuv", d->yuv);
+    d->jpeg.resize((size_t)d->result.jpeg_bytes);   // the file is the first jpeg_bytes of the capacity buffer
+    attach("jpeg", d->jpeg); }
   for (napi_ref r : d->keep) napi_delete_reference(env, r);
   if (d->tsfn) napi_release_threadsafe_function(d->tsfn, napi_tsfn_release);
   napi_resolve_deferred(env, d->deferred, out);
@@ -165,11 +167,18 @@ napi_value Run(napi_env env, napi_callback_info info) {
   // size the outputs with the layout twin
   std::vector<StitchImageDesc> descs(n);
   for (uint32_t i = 0; i < n; ++i) descs[i] = d->images[i].desc;
-  StitchLayout lay;
+  StitchLayout lay{};
   int64_t rb = 0, yb = 0;
   if (stitch_layout(descs.data(), (int32_t)n, &d->job.params, &lay) == STITCH_OK) stitch_output_size(&lay, &rb, &yb);
   if (d->job.output_flags & STITCH_OUT_RGBA) d->rgba.resize((size_t)rb);
   if (d->job.output_flags & STITCH_OUT_YUV420) d->yuv.resize((size_t)yb);
+  if (d->job.output_flags & STITCH_OUT_JPEG) {
+    d->job.jpeg_quality = get_i32(env, job, "jpegQuality", 0);
+    d->job.jpeg_restart_interval = get_i32(env, job, "jpegRestartInterval", 0);
+    d->jpeg.resize((size_t)stitch_jpeg_capacity(&lay, d->job.jpeg_restart_interval));
+    d->job.out_jpeg = d->jpeg.data();
+    d->job.out_capacity_jpeg = (int64_t)d->jpeg.size();
+  }
   d->job.out_rgba = d->rgba.empty() ? nullptr : d->rgba.data();
   d->job.out_yuv = d->yuv.empty() ? nullptr : d->yuv.data();
   d->job.out_capacity_rgba = (int64_t)d->rgba.size();
