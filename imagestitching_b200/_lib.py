@@ -63,6 +63,11 @@ class StitchResult(C.Structure):
                 ("jpeg_bytes", C.c_int64)]
 
 
+class StitchPreviewLayout(C.Structure):
+    _fields_ = [("canvas_w", C.c_int32), ("canvas_h", C.c_int32), ("pv_w", C.c_int32), ("pv_h", C.c_int32),
+                ("scale_fit", C.c_double), ("dx", C.c_double), ("dy", C.c_double), ("dpr", C.c_double)]
+
+
 PROGRESS_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int32)
 
 # name -> (restype, argtypes); every symbol include/stitch.h declares
@@ -81,6 +86,10 @@ SIGNATURES = {
     "stitch_run": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult)]),
     "stitch_submit": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult), C.POINTER(C.c_uint64)]),
     "stitch_wait": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "stitch_preview_layout": (C.c_int, [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
+                                        C.POINTER(StitchPreviewLayout)]),
+    "stitch_preview": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_double, C.c_double,
+                                 C.c_double, C.c_void_p, C.c_int64, C.c_int32, C.POINTER(StitchPreviewLayout)]),
     "stitch_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "stitch_host_free": (C.c_int, [C.c_void_p]),
     "stitch_device_alloc": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]),

@@ -44,13 +44,13 @@ namespace stitch {
 
 // Exact (gather) evaluation of one canvas pixel, kept out of line so the rare slow path does not
 // inflate the streaming loop's register allocation.
-__device__ __noinline__ void shade_rgb(const JobParam& P, int x, int y, float* rgb) {
-  shade(P, x, y, rgb[0], rgb[1], rgb[2]);
+__device__ __noinline__ void shade_rgb(const JobParam& P, int x, int y, float* rgba) {
+  shade(P, x, y, rgba[0], rgba[1], rgba[2], rgba[3]);
 }
 __device__ __forceinline__ uint32_t shade_px(const JobParam& P, int x, int y) {
-  float c[3];
+  float c[4];
   shade_rgb(P, x, y, c);
-  return q8(c[0]) | (q8(c[1]) << 8) | (q8(c[2]) << 16) | 0xff000000u;
+  return finish_px(P, c[0], c[1], c[2], c[3]);
 }
 
 // One 2x2 chroma block (bx, by) of the canvas, evaluated exactly: optional RGBA and Y for the
@@ -66,7 +66,7 @@ __device__ __forceinline__ void shade_block(const JobParam& P, int bx, int by, i
       const int x = min(xx, P.cw - 1), y = min(yy, P.ch - 1);  // edge replication for odd sizes
       const bool inside = xx >= x0 && xx < x1 && yy >= y0 && yy < y1;
       if (!CHROMA && !inside) continue;
-      float c[3];
+      float c[4];
       shade_rgb(P, x, y, c);
       if (inside) {
         if (LUMA) P.out_y[(int64_t)y * P.cw + x] = (uint8_t)q8(0.299f * c[0] + 0.587f * c[1] + 0.114f * c[2]);
@@ -122,9 +122,10 @@ __device__ __forceinline__ void fill_unit(const JobParam& P, const Region& R, in
   const int x0 = R.x0 + tx * R.tile_w, x1 = min(x0 + R.tile_w, R.x1);
   const int y0 = R.y0 + ty * R.tile_h, y1 = min(y0 + R.tile_h, R.y1);
   if (MODE == 0) {
+    const uint32_t bg = P.transparent ? 0u : 0xffffffffu;  // clearRect (P:1598) or '#ffffff' (P:1423-1424)
     for (int y = y0; y < y1; ++y) {
       uint32_t* row = reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch);
-      for (int x = x0 + lane; x < x1; x += 32) row[x] = 0xffffffffu;
+      for (int x = x0 + lane; x < x1; x += 32) row[x] = bg;
     }
   } else {
     const int cwh = (P.cw + 1) >> 1;

@@ -76,9 +76,10 @@ __device__ __forceinline__ float tap_weight(const AxisTaps& t, int k) {
   return fmaxf(hi - lo, 0.f) * t.inv_tot;
 }
 
-// Un-rounded composited RGB of canvas pixel (x, y).
-__device__ __forceinline__ void shade(const JobParam& P, int x, int y, float& R, float& G, float& B) {
-  R = G = B = 255.f;
+// Un-rounded composited colour of canvas pixel (x, y): premultiplied RGB and alpha, all on the 0..255
+// scale.  Over the opaque white canvas A stays 255 and R, G, B are the final colour.
+__device__ __forceinline__ void shade(const JobParam& P, int x, int y, float& R, float& G, float& B, float& A) {
+  R = G = B = A = P.transparent ? 0.f : 255.f;
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
     if (x < im.x_lo || x >= im.x_hi || y < im.y_lo || y >= im.y_hi) continue;
@@ -111,21 +112,35 @@ __device__ __forceinline__ void shade(const JobParam& P, int x, int y, float& R,
     R = fmaf(C, fr, keep * R);
     G = fmaf(C, fg, keep * G);
     B = fmaf(C, fb, keep * B);
+    A = fmaf(C, fa, keep * A);
   }
+}
+__device__ __forceinline__ void shade(const JobParam& P, int x, int y, float& R, float& G, float& B) {
+  float A;
+  shade(P, x, y, R, G, B, A);
 }
 
 __device__ __forceinline__ uint32_t q8(float v) {  // round half up, clamp (App. C.7)
   return (uint32_t)min(max(__float2int_rd(v + 0.5f), 0), 255);
 }
 
+// RGBA8 of a shaded pixel: opaque over white, or straight alpha over the cleared canvas (colour =
+// premultiplied / alpha before rounding; nothing where alpha rounds to 0).
+__device__ __forceinline__ uint32_t finish_px(const JobParam& P, float R, float G, float B, float A) {
+  if (!P.transparent) return q8(R) | (q8(G) << 8) | (q8(B) << 16) | 0xff000000u;
+  const uint32_t a8 = q8(A);
+  if (a8 == 0 || !(A > 0.f)) return 0u;
+  const float inv = 255.f / A;
+  return q8(R * inv) | (q8(G * inv) << 8) | (q8(B * inv) << 16) | (a8 << 24);
+}
+
 __global__ void __launch_bounds__(256) gather_rgba_kernel(const __grid_constant__ JobParam P) {
   const int x = blockIdx.x * 32 + (threadIdx.x & 31);
   const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
   if (x >= P.cw || y >= P.ch) return;
-  float R, G, B;
-  shade(P, x, y, R, G, B);
-  const uint32_t v = q8(R) | (q8(G) << 8) | (q8(B) << 16) | 0xff000000u;
-  *reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch + (int64_t)x * 4) = v;
+  float R, G, B, A;
+  shade(P, x, y, R, G, B, A);
+  *reinterpret_cast<uint32_t*>(P.out_rgba + (int64_t)y * P.out_pitch + (int64_t)x * 4) = finish_px(P, R, G, B, A);
 }
 
 // One thread per 2x2 block: RGBA (optional) + JFIF BT.601 full-range I420 (App. C.9).

@@ -252,6 +252,27 @@ extern "C" int64_t stitch_jpeg_capacity(const StitchLayout* layout, int32_t rest
   return 1024 + mcus * 6 * 432 + segs * 4 + 2;
 }
 
+// Preview geometry: U:17-24 (createHighResCanvas) + P:1599-1603.
+extern "C" int stitch_preview_layout(int32_t export_w, int32_t export_h, double view_w, double view_h, double dpr,
+                                     StitchPreviewLayout* out) {
+  if (!out) return STITCH_E_BAD_ARG;
+  std::memset(out, 0, sizeof(*out));
+  if (export_w <= 0 || export_h <= 0) return STITCH_E_BAD_DIMS;
+  if (!(dpr == dpr) || dpr == 0.0) dpr = 1.0;  // `info.pixelRatio || 1` (0 and NaN are falsy)
+  out->dpr = dpr;
+  const double cw = std::floor(view_w * dpr), ch = std::floor(view_h * dpr);  // U:19-20
+  if (!(cw >= 1.0) || !(ch >= 1.0) || cw > 2147483647.0 || ch > 2147483647.0) return STITCH_E_BAD_OUT;
+  out->canvas_w = (int32_t)cw;
+  out->canvas_h = (int32_t)ch;
+  const double fx = view_w / (double)export_w, fy = view_h / (double)export_h;
+  out->scale_fit = fx < fy ? fx : fy;                                   // P:1600
+  out->pv_w = (int32_t)js_round((double)export_w * out->scale_fit);     // P:1601
+  out->pv_h = (int32_t)js_round((double)export_h * out->scale_fit);     // P:1602
+  out->dx = (view_w - (double)out->pv_w) / 2;                           // P:1603
+  out->dy = (view_h - (double)out->pv_h) / 2;
+  return STITCH_OK;
+}
+
 extern "C" const char* stitch_strerror(int status) {
   switch (status) {
     case STITCH_OK: return "ok";

@@ -120,7 +120,6 @@ void make_placement(const StitchRect& r, int orientation, double ss, int bw, int
   p->y_lo = lo(p->Y0, ch);
   p->y_hi = hi(p->Y0 + p->H, ch);
   if (!(p->W > 0) || !(p->H > 0)) p->x_hi = p->x_lo;  // empty
-  p->pad = 0;
 }
 
 int ensure_stage(StitchCtx* ctx, Lane& ln, size_t idx, size_t bytes) {
@@ -463,6 +462,82 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
   }
   ctx->busy = false;
   return st;
+}
+
+// Preview draw (P:1593-1603): one image, cleared canvas, ctx.scale(dpr, dpr).  Reuses the fused compose
+// launch with JobParam.transparent set: fully covered opaque pixels take the streaming / upscale units
+// as in a stitch job, the fractional border and the empty margins become GATHER / FILL units.
+extern "C" int stitch_preview(StitchCtx* ctx, const void* src, int32_t src_mem_kind, int32_t export_w, int32_t export_h,
+                              int64_t src_pitch, double view_w, double view_h, double dpr, void* out_rgba,
+                              int64_t out_capacity, int32_t out_mem_kind, StitchPreviewLayout* layout_out) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "context is busy");
+  StitchPreviewLayout pl;
+  int st = stitch_preview_layout(export_w, export_h, view_w, view_h, dpr, &pl);
+  if (layout_out) *layout_out = pl;
+  if (st != STITCH_OK) return fail(ctx, st, stitch_strerror(st));
+  if (!src) return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常");
+  int64_t pitch = src_pitch ? src_pitch : (int64_t)export_w * 4;
+  if (pitch < (int64_t)export_w * 4 || (pitch & 3)) return fail(ctx, STITCH_E_BAD_ARG, "bad bitmap pitch");
+  const int cw = pl.canvas_w, ch = pl.canvas_h;
+  if (!out_rgba || out_capacity < (int64_t)cw * ch * 4)
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (preview output buffer missing or too small)");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Lane& ln = ctx->lanes[0];
+
+  JobParam P;
+  std::memset(&P, 0, sizeof P);
+  P.n = 1;
+  P.cw = cw;
+  P.ch = ch;
+  P.transparent = 1;  // clearRect, P:1598
+  const uint8_t* dptr = (const uint8_t*)src;
+  if (src_mem_kind != STITCH_MEM_DEVICE) {
+    const int64_t dpitch = ((int64_t)export_w * 4 + 15) & ~15LL;
+    st = ensure_stage(ctx, ln, 0, (size_t)(dpitch * export_h));
+    if (st != STITCH_OK) return st;
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(ln.in_stage[0], dpitch, src, pitch, (size_t)export_w * 4, export_h,
+                                    cudaMemcpyHostToDevice, ln.stream));
+    dptr = (const uint8_t*)ln.in_stage[0];
+    pitch = dpitch;
+  }
+  P.img[0].data = dptr;
+  P.img[0].pitch = pitch;
+  StitchRect r;
+  r.dx = pl.dx;
+  r.dy = pl.dy;
+  r.dw = (double)pl.pv_w;
+  r.dh = (double)pl.pv_h;
+  make_placement(r, 1, pl.dpr, export_w, export_h, cw, ch, &P.img[0]);
+
+  const bool out_host = out_mem_kind != STITCH_MEM_DEVICE;
+  int64_t d_pitch = (int64_t)cw * 4;
+  uint8_t* d_out = (uint8_t*)out_rgba;
+  if (out_host) {
+    d_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
+    const size_t need = (size_t)(d_pitch * ch) + 256;
+    if (ln.out_stage_cap < need) {
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+      if (ln.out_stage) CUDA_TRY(ctx, cudaFree(ln.out_stage));
+      ln.out_stage = nullptr;
+      ln.out_stage_cap = 0;
+      if (cudaMalloc(&ln.out_stage, need) != cudaSuccess)
+        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (device canvas allocation failed)");
+      ln.out_stage_cap = need;
+    }
+    d_out = (uint8_t*)ln.out_stage;
+  }
+  P.out_rgba = d_out;
+  P.out_pitch = d_pitch;
+  int launches = 0, path_info = 0;
+  st = stitch::launch_job(P, true, false, ctx->sm_count, ln.scratch, ln.stream, &launches, &path_info);
+  if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
+  ctx->launches += launches;
+  if (out_host)
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, (size_t)cw * 4, d_out, d_pitch, (size_t)cw * 4, ch, cudaMemcpyDeviceToHost,
+                                    ln.stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+  return STITCH_OK;
 }
 
 extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {

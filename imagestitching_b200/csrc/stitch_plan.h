@@ -23,7 +23,7 @@ struct JobParam {
   ImgParam img[STITCH_MAX_IMAGES];
   int32_t n;
   int32_t cw, ch;
-  int32_t pad;
+  int32_t transparent;  // 0: opaque white canvas (P:1423-1424); 1: cleared canvas, straight-alpha RGBA out (preview, P:1598)
   uint8_t* out_rgba;  // may be null
   int64_t out_pitch;
   uint8_t* out_y;     // may be null

@@ -50,7 +50,7 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
   const int xq = 4 * q;
 
   // ---- column taps of the lane's 4 pixels (byte offsets inside a bitmap row) ----
-  int offA[4], offB[4];
+  uint32_t offA[4], offB[4];
   float tcol[4];
   bool ok[4];
 #pragma unroll
@@ -59,32 +59,47 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
     ok[k] = x >= R.x0 && x < R.x1;
     int ia, ib;
     bilinear_tap(min(max(x, R.x0), R.x1 - 1), im.X0, sx, im.sx_len, im.flip_x != 0, &ia, &ib, &tcol[k]);
-    offA[k] = ia * 4;
-    offB[k] = ib * 4;
+    offA[k] = (uint32_t)ia * 4u;
+    offB[k] = (uint32_t)ib * 4u;
   }
-  // ---- row taps: lane r evaluates output row y0 + r once, the row loop fetches them by shuffle ----
-  int rowA, rowB;
+  // ---- row taps: lane r evaluates output row y0 + r once, the row loop fetches them by shuffle.
+  // k_r is the UNCLAMPED index of the upper tap (floor(u), may be -1); the device rect is at least as tall
+  // as the bitmap, so k advances by at most one per output row and the unit walks the source rows k, k+1, ...
+  // once: it holds rows k and k+1 (horizontally interpolated) in registers, emits every output row that
+  // blends them, then replaces the older one by row k+2 -- which has been in flight since the previous step.
+  int k_r;
   float trow;
-  bilinear_tap(min(y0 + lane, y1 - 1), im.Y0, sy, im.sy_len, im.flip_y != 0, &rowA, &rowB, &trow);
+  {
+    const int j = min(y0 + lane, y1 - 1);
+    const double u = (((double)j + ((double)j + 1.0)) * 0.5 - im.Y0) / sy - 0.5;   // == bilinear_tap's u
+    const double f = floor(u);
+    k_r = (int)f;
+    trow = (float)(u - f);
+  }
+  auto src_row = [&](int k) {  // clamp to edge, then the EXIF mirror
+    const int c = min(max(k, 0), im.sy_len - 1);
+    return im.flip_y ? im.sy_len - 1 - c : c;
+  };
 
-  float hA[12], hB[12];  // horizontally interpolated values of source rows curA / curB, 1 + v * 2^-15 form
-  int curA = -1, curB = -1;
   uint32_t and_acc = 0xffffffffu;
-  auto load_row = [&](int row, float* h) {
-    const uint8_t* base = im.data + (int64_t)row * im.pitch;
-    uint32_t pa[4], pb[4];
+  auto issue = [&](int k, uint32_t* raw) {
+    const uint8_t* base = im.data + (int64_t)src_row(k) * im.pitch;
+    asm("" : "+l"(base));  // keep ONE row pointer; otherwise the multiply is re-associated into every tap
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      pa[k] = __ldg(reinterpret_cast<const uint32_t*>(base + offA[k]));
-      pb[k] = __ldg(reinterpret_cast<const uint32_t*>(base + offB[k]));
+    for (int c = 0; c < 4; ++c) {
+      raw[c] = __ldg(reinterpret_cast<const uint32_t*>(base + (size_t)offA[c]));
+      raw[4 + c] = __ldg(reinterpret_cast<const uint32_t*>(base + (size_t)offB[c]));
     }
+  };
+  auto convert = [&](const uint32_t* raw, float* h) {  // 1 + v * 2^-15 form, interpolated along x
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      and_acc &= pa[k] & pb[k];
-      const float a0 = expand<0>(pa[k]), a1 = expand<1>(pa[k]), a2 = expand<2>(pa[k]);
-      h[k * 3 + 0] = fmaf(tcol[k], expand<0>(pb[k]) - a0, a0);
-      h[k * 3 + 1] = fmaf(tcol[k], expand<1>(pb[k]) - a1, a1);
-      h[k * 3 + 2] = fmaf(tcol[k], expand<2>(pb[k]) - a2, a2);
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t pa = raw[c], pb = raw[4 + c];
+      and_acc &= pa & pb;
+      const float a0 = expand<0>(pa), a1 = expand<1>(pa), a2 = expand<2>(pa);
+      h[c * 3 + 0] = fmaf(tcol[c], expand<0>(pb) - a0, a0);
+      h[c * 3 + 1] = fmaf(tcol[c], expand<1>(pb) - a1, a1);
+      h[c * 3 + 2] = fmaf(tcol[c], expand<2>(pb) - a2, a2);
     }
   };
 
@@ -102,35 +117,14 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
     crp = P.out_cr + (int64_t)(y0 >> 1) * cwh + (xq >> 1);
   }
 
-  for (int y = y0; y < y1; ++y) {
-    const int ia = __shfl_sync(0xffffffffu, rowA, y - y0);
-    const int ib = __shfl_sync(0xffffffffu, rowB, y - y0);
-    const float tv = __shfl_sync(0xffffffffu, trow, y - y0);
-    if (ia != curA) {
-      if (ia == curB) {
-#pragma unroll
-        for (int k = 0; k < 12; ++k) { const float s = hA[k]; hA[k] = hB[k]; hB[k] = s; }
-        curB = curA;
-      } else {
-        load_row(ia, hA);
-      }
-      curA = ia;
-    }
-    if (ib != curB) {
-      if (ib == curA) {
-#pragma unroll
-        for (int k = 0; k < 12; ++k) hB[k] = hA[k];
-      } else {
-        load_row(ib, hB);
-      }
-      curB = ib;
-    }
+  int y = y0;
+  auto emit = [&](const float* A, const float* B, float tv) {
     float v[12];
     const float wa = 1.f - tv;
 #pragma unroll
     for (int k = 0; k < 12; k += 2) {
-      mul2_s(v[k], v[k + 1], hA[k], hA[k + 1], wa);
-      fma2_s(v[k], v[k + 1], hB[k], hB[k + 1], tv);
+      mul2_s(v[k], v[k + 1], A[k], A[k + 1], wa);
+      fma2_s(v[k], v[k + 1], B[k], B[k + 1], tv);
     }
     if (RGBA) {
       uint32_t px[4];
@@ -177,6 +171,33 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
         crp += cwh;
       }
     }
+    ++y;
+  };
+
+  float hA[12], hB[12];
+  uint32_t raw[8];
+  int k = __shfl_sync(0xffffffffu, k_r, 0);
+  {
+    uint32_t raw2[8];
+    issue(k, raw);
+    issue(k + 1, raw2);
+    convert(raw, hA);
+    convert(raw2, hB);
+  }
+  issue(k + 2, raw);
+  for (;;) {
+    // rows k (hA) and k + 1 (hB)
+    while (y < y1 && __shfl_sync(0xffffffffu, k_r, y - y0) == k) emit(hA, hB, __shfl_sync(0xffffffffu, trow, y - y0));
+    if (y >= y1) break;
+    convert(raw, hA);
+    ++k;
+    issue(k + 2, raw);
+    // rows k (hB) and k + 1 (hA)
+    while (y < y1 && __shfl_sync(0xffffffffu, k_r, y - y0) == k) emit(hB, hA, __shfl_sync(0xffffffffu, trow, y - y0));
+    if (y >= y1) break;
+    convert(raw, hB);
+    ++k;
+    issue(k + 2, raw);
   }
   // translucent source pixels: redo the unit with the exact premultiplied source-over evaluation
   const bool need_fix = (and_acc >> 24) != 0xffu;

@@ -171,6 +171,16 @@ def compute_layout(images: Sequence[Dict[str, Any]], direction: str, mode: Optio
     return d
 
 
+def preview_layout(export_w: int, export_h: int, view_w: float, view_h: float, dpr=1) -> Dict[str, Any]:
+    """createHighResCanvas + the fit-scale of index.js:1599-1603 (pure CPU, no GPU needed)."""
+    pl = L.StitchPreviewLayout()
+    st = L.load().stitch_preview_layout(int(export_w), int(export_h), float(view_w), float(view_h), float(dpr or 0), C.byref(pl))
+    if st != L.OK:
+        _raise(st)
+    return {"canvasW": pl.canvas_w, "canvasH": pl.canvas_h, "scaleFit": pl.scale_fit, "pvW": pl.pv_w, "pvH": pl.pv_h,
+            "dx": pl.dx, "dy": pl.dy, "dpr": pl.dpr}
+
+
 class StitchContext:
     """One per GPU: owns a StitchCtx (stream, staging).  Not thread-safe."""
 
@@ -216,6 +226,26 @@ class StitchContext:
         return int(self.lib.stitch_kernel_launch_count(self.handle))
 
     # -- job construction ----------------------------------------------------
+    def preview(self, exported, view_w: float, view_h: float, dpr=1) -> np.ndarray:
+        """index.js:1593-1603: the exported canvas (uint8 [h, w, 4] array or DeviceBitmap) drawn fit-scaled and
+        centred on the cleared preview canvas.  Returns straight-alpha RGBA8 [canvasH, canvasW, 4]."""
+        lib = L.load()
+        if isinstance(exported, DeviceBitmap):
+            ptr, kind, w, h, pitch = exported.ptr, L.MEM_DEVICE, exported.width, exported.height, exported.pitch
+        else:
+            exported = np.ascontiguousarray(exported, dtype=np.uint8)
+            ptr, kind, (h, w), pitch = exported.ctypes.data, L.MEM_HOST, exported.shape[:2], exported.strides[0]
+        pl = L.StitchPreviewLayout()
+        st = lib.stitch_preview_layout(int(w), int(h), float(view_w), float(view_h), float(dpr or 0), C.byref(pl))
+        if st != L.OK:
+            _raise(st, self.handle)
+        out = np.empty((pl.canvas_h, pl.canvas_w, 4), dtype=np.uint8)
+        st = lib.stitch_preview(self.handle, ptr, kind, int(w), int(h), int(pitch), float(view_w), float(view_h),
+                                float(dpr or 0), out.ctypes.data, out.nbytes, L.MEM_HOST, C.byref(pl))
+        if st != L.OK:
+            _raise(st, self.handle)
+        return out
+
     def build_job(self, images: Sequence[Dict[str, Any]], direction: str, mode: Optional[str], gap,
                   profile: L.StitchProfile, output: str, out_device: bool = False, out_rgba_ptr: int = 0,
                   out_yuv_ptr: int = 0, out_rgba_capacity: int = 0, out_yuv_capacity: int = 0, out_jpeg_ptr: int = 0,

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 2
+#define STITCH_ABI_VERSION 3
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -179,6 +179,27 @@ int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
  * Buffers must stay valid until stitch_wait(ticket) returns. */
 int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket);
 int stitch_wait(StitchCtx* ctx, uint64_t ticket);
+
+/* ---- preview of the exported image on the page's <canvas> (P:1593-1603) ----
+ * createHighResCanvas(node, size.width, size.height) (U:17-24) restores the canvas to floor(size * dpr)
+ * device pixels under ctx.scale(dpr, dpr); clearRect leaves it transparent; the exported bitmap is drawn
+ * into the centred fit rect: scaleFit = min(sw/ew, sh/eh), pv = round(e * scaleFit), at ((s - pv) / 2). */
+typedef struct StitchPreviewLayout {
+  int32_t canvas_w, canvas_h;  /* floor(view * dpr), U:19-20 */
+  int32_t pv_w, pv_h;          /* CSS px, P:1601-1602 */
+  double scale_fit;            /* P:1600 */
+  double dx, dy;               /* CSS px, P:1603 */
+  double dpr;                  /* pixelRatio || 1, U:2-14 */
+} StitchPreviewLayout;
+/* Pure CPU.  STITCH_E_BAD_DIMS for a non-positive export size, STITCH_E_BAD_OUT when the canvas has no pixels. */
+int stitch_preview_layout(int32_t export_w, int32_t export_h, double view_w, double view_h, double dpr,
+                          StitchPreviewLayout* out);
+/* Draws the preview: `src` is the exported RGBA8 canvas (export_w x export_h, straight alpha, pitch 0 =
+ * packed), `out_rgba` receives canvas_w*canvas_h*4 bytes of STRAIGHT-alpha RGBA8 (transparent where the
+ * image does not reach, P:1598).  One fused compose launch on the ctx stream; synchronous. */
+int stitch_preview(StitchCtx* ctx, const void* src, int32_t src_mem_kind, int32_t export_w, int32_t export_h,
+                   int64_t src_pitch, double view_w, double view_h, double dpr, void* out_rgba, int64_t out_capacity,
+                   int32_t out_mem_kind, StitchPreviewLayout* layout_out);
 
 /* Pinned host / device buffers for callers without a CUDA runtime of their own (e.g. the N-API shim). */
 int stitch_host_alloc(size_t bytes, void** out);

@@ -332,3 +332,38 @@ def placement_for(rect, orientation, ss: float) -> Placement:
     p.W *= ss
     p.H *= ss
     return p
+
+
+# ---------------------------------------------------------------------------
+# Preview of the exported file on the page's <canvas> (index.js:1593-1603).
+# ---------------------------------------------------------------------------
+
+@dataclass
+class PreviewLayout:
+    canvasW: int = 0          # device pixels of the restored preview canvas (utils/canvas.js:19-20)
+    canvasH: int = 0
+    scaleFit: float = 0.0     # index.js:1600
+    pvW: int = 0              # index.js:1601-1602 (CSS px)
+    pvH: int = 0
+    dx: float = 0.0           # index.js:1603 (CSS px, may end in .5)
+    dy: float = 0.0
+    dpr: float = 1.0
+
+
+def preview_layout(export_w: int, export_h: int, view_w: float, view_h: float, dpr) -> PreviewLayout:
+    """createHighResCanvas(node, size.width, size.height) (utils/canvas.js:17-24: canvas = floor(size*dpr),
+    ctx.scale(dpr, dpr)) followed by the fit-scale draw of index.js:1599-1603."""
+    dpr = float(dpr) if dpr else 1.0                                   # `info.pixelRatio || 1`
+    pl = PreviewLayout(dpr=dpr)
+    pl.canvasW = int(math.floor(view_w * dpr))
+    pl.canvasH = int(math.floor(view_h * dpr))
+    pl.scaleFit = min(view_w / export_w, view_h / export_h)
+    pl.pvW = int(js_round(export_w * pl.scaleFit))
+    pl.pvH = int(js_round(export_h * pl.scaleFit))
+    pl.dx = (view_w - pl.pvW) / 2
+    pl.dy = (view_h - pl.pvH) / 2
+    return pl
+
+
+def preview_placement(pl: PreviewLayout) -> Placement:
+    return Placement(pl.dx * pl.dpr, pl.dy * pl.dpr, pl.pvW * pl.dpr, pl.pvH * pl.dpr)

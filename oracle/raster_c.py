@@ -43,7 +43,27 @@ def load():
             fn.restype = C.c_int
             fn.argtypes = [C.POINTER(OrImage), C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                            C.c_void_p, C.c_void_p]
+        for name in ("oracle_preview_f64", "oracle_preview_f32"):
+            fn = getattr(_lib, name)
+            fn.restype = C.c_int
+            fn.argtypes = [C.POINTER(OrImage), C.c_int, C.c_int, C.c_void_p, C.c_int64]
     return _lib
+
+
+def render_preview(bmp: np.ndarray, pl, precision: str = "f64") -> np.ndarray:
+    """C twin of raster_ref.render_preview: straight-alpha RGBA8 [canvasH, canvasW, 4]."""
+    from .layout_ref import preview_placement
+    lib = load()
+    a = np.ascontiguousarray(np.asarray(bmp))
+    p = preview_placement(pl)
+    im = OrImage()
+    im.data, im.pitch, im.bh, im.bw = a.ctypes.data, a.strides[0], a.shape[0], a.shape[1]
+    im.X0, im.Y0, im.W, im.H = p.X0, p.Y0, p.W, p.H
+    out = np.empty((int(pl.canvasH), int(pl.canvasW), 4), np.uint8)
+    fn = lib.oracle_preview_f64 if precision == "f64" else lib.oracle_preview_f32
+    if out.size and fn(C.byref(im), int(pl.canvasW), int(pl.canvasH), out.ctypes.data, 0) != 0:
+        raise MemoryError("oracle_preview failed")
+    return out
 
 
 def render(layout: Layout, bitmaps: Sequence[np.ndarray], orientations: Sequence[object], want_rgba: bool = True,

@@ -159,3 +159,33 @@ def psnr(a: np.ndarray, b: np.ndarray) -> float:
     d = a.astype(np.float64) - b.astype(np.float64)
     mse = float(np.mean(d * d))
     return float("inf") if mse == 0 else 10.0 * math.log10(255.0 * 255.0 / mse)
+
+
+def render_preview(bmp: np.ndarray, pl) -> np.ndarray:
+    """Preview draw (index.js:1597-1603): clearRect -> transparent canvas, one drawImage of the exported
+    bitmap into the centred fit rect under ctx.scale(dpr, dpr).  Same filter as draw_image; the canvas keeps
+    premultiplied colour + alpha, the result is STRAIGHT-alpha RGBA8 (colour = premultiplied / alpha before
+    rounding, alpha = round(255 * coverage * filtered alpha), colour 0 where alpha rounds to 0)."""
+    from .layout_ref import preview_placement
+    p = preview_placement(pl)
+    cw, ch = int(pl.canvasW), int(pl.canvasH)
+    out = np.zeros((ch, cw, 4), np.uint8)
+    src = np.asarray(bmp).astype(np.float64)
+    sh, sw = src.shape[:2]
+    Wx, cx = axis_weights(cw, p.X0, p.W, sw, False)
+    Wy, cy = axis_weights(ch, p.Y0, p.H, sh, False)
+    xs, ys = np.nonzero(cx)[0], np.nonzero(cy)[0]
+    if xs.size == 0 or ys.size == 0:
+        return out
+    x0, x1, y0, y1 = xs[0], xs[-1] + 1, ys[0], ys[-1] + 1
+    Wx, Wy = Wx[x0:x1], Wy[y0:y1]
+    alpha = src[:, :, 3] / 255.0
+    C = np.outer(cy[y0:y1], cx[x0:x1])
+    A = C * (Wx @ (Wy @ alpha).T).T                    # canvas alpha in 0..1
+    a8 = quantise(A * 255.0)
+    safe = np.where(A > 0, A, 1.0)
+    for c in range(3):
+        F = C * (Wx @ (Wy @ (src[:, :, c] * alpha)).T).T
+        out[y0:y1, x0:x1, c] = np.where(a8 > 0, quantise(F / safe), 0)
+    out[y0:y1, x0:x1, 3] = a8
+    return out
