@@ -194,6 +194,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
   // ncu showed the SMs 14 % idle on average while the slowest ones finished.
   static const double body_frac = [] { const char* e = std::getenv("STITCH_BODY_FRAC"); return e ? atof(e) : 0.75; }();
   static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? atoi(e) : 32; }();
+  static const double up_body_frac = [] { const char* e = std::getenv("STITCH_UP_BODY_FRAC"); return e ? atof(e) : 0.8; }();
   const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_UNR;
   auto tile_h_for = [&](const Region& r, int src_rows) {
     const ImgParam& im = P.img[r.img];
@@ -251,7 +252,23 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
     regs.clear();
     // order = hand-out order: bodies, then the per-pixel gather regions, then the small units
     for (const Region& r : bodies) regs.push_back(r);
-    for (const Region& r : others) if (r.kind == REGION_UPSCALE) regs.push_back(r);
+    // enlarged images get the same treatment: full-height units over the first rows, quarter-height
+    // units over the rest, so the last round of units is short (configs[0]: 2.1 full units per warp)
+    for (const Region& r : others) {
+      if (r.kind != REGION_UPSCALE) continue;
+      const int hb = (int)((int64_t)(up_body_frac * (double)(r.y1 - r.y0)) / UPSCALE_TILE_H * UPSCALE_TILE_H);
+      if (hb > 0) {
+        Region b = r;
+        b.y1 = r.y0 + hb;
+        regs.push_back(b);
+      }
+      if (r.y0 + hb < r.y1) {
+        Region t = r;
+        t.y0 = r.y0 + hb;
+        t.tile_h = UPSCALE_TAIL_H;
+        tails.push_back(t);
+      }
+    }
     for (const Region& r : others) if (r.kind == REGION_GATHER) regs.push_back(r);
     for (const Region& r : tails) regs.push_back(r);
     for (const Region& r : others) if (r.kind == REGION_FILL) regs.push_back(r);
@@ -338,7 +355,15 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
       if (e != cudaSuccess) return (int)e;
     }
     int cnt[4] = {0, 0, 0, 0};
-    for (int i = 0; i < plan.n_regions; ++i) cnt[plan.r[i].kind]++;
+    uint32_t up_seen = 0;
+    for (int i = 0; i < plan.n_regions; ++i) {
+      const Region& r = plan.r[i];
+      if (r.kind == REGION_UPSCALE) {  // body + tail of one enlarged image count once
+        if (up_seen >> r.img & 1u) continue;
+        up_seen |= 1u << r.img;
+      }
+      cnt[r.kind]++;
+    }
     *path_info = std::min(cnt[REGION_STREAM], 255) | (std::min(cnt[REGION_GATHER], 255) << 8) |
                  (std::min(cnt[REGION_FILL], 255) << 16) | (std::min(cnt[REGION_UPSCALE], 63) << 25);
     // persistent grid: every resident warp slot of the chip, capped by the number of units

@@ -22,6 +22,7 @@ namespace stitch {
 
 #define UPSCALE_TILE_W 128
 #define UPSCALE_TILE_H 32
+#define UPSCALE_TAIL_H 8   // unit height at the end of the hand-out order (launch.cuh)
 
 // fp64 tap position of device pixel j on one axis, exactly as gather_kernel.cuh::axis_taps evaluates it
 // for a fully covered pixel: u = ((j + 0.5) - d0) / s - 0.5 with s = dlen / slen.
@@ -177,6 +178,10 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
   float hA[12], hB[12];
   uint32_t raw[8];
   int k = __shfl_sync(0xffffffffu, k_r, 0);
+  // bit r: output row r starts a new source-row pair (k advances by exactly one there)
+  const int k_prev = __shfl_up_sync(0xffffffffu, k_r, 1);
+  const uint32_t step = __ballot_sync(0xffffffffu, lane > 0 && k_r != k_prev);
+  const int nrows = y1 - y0;
   {
     uint32_t raw2[8];
     issue(k, raw);
@@ -185,16 +190,28 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
     convert(raw2, hB);
   }
   issue(k + 2, raw);
+  int r = 0;
+  float tv = __shfl_sync(0xffffffffu, trow, 0);
   for (;;) {
-    // rows k (hA) and k + 1 (hB)
-    while (y < y1 && __shfl_sync(0xffffffffu, k_r, y - y0) == k) emit(hA, hB, __shfl_sync(0xffffffffu, trow, y - y0));
-    if (y >= y1) break;
+    // rows k (hA) and k + 1 (hB); the next row's weight is fetched one row ahead
+    do {
+      ++r;
+      const float tn = __shfl_sync(0xffffffffu, trow, r & 31);
+      emit(hA, hB, tv);
+      tv = tn;
+    } while (r < nrows && !((step >> r) & 1u));
+    if (r >= nrows) break;
     convert(raw, hA);
     ++k;
     issue(k + 2, raw);
     // rows k (hB) and k + 1 (hA)
-    while (y < y1 && __shfl_sync(0xffffffffu, k_r, y - y0) == k) emit(hB, hA, __shfl_sync(0xffffffffu, trow, y - y0));
-    if (y >= y1) break;
+    do {
+      ++r;
+      const float tn = __shfl_sync(0xffffffffu, trow, r & 31);
+      emit(hB, hA, tv);
+      tv = tn;
+    } while (r < nrows && !((step >> r) & 1u));
+    if (r >= nrows) break;
     convert(raw, hB);
     ++k;
     issue(k + 2, raw);
