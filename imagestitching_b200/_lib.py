@@ -63,6 +63,10 @@ class StitchResult(C.Structure):
                 ("jpeg_bytes", C.c_int64)]
 
 
+class StitchImageInfo(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("type", C.c_int32), ("orientation_exif", C.c_int32)]
+
+
 class StitchPreviewLayout(C.Structure):
     _fields_ = [("canvas_w", C.c_int32), ("canvas_h", C.c_int32), ("pv_w", C.c_int32), ("pv_h", C.c_int32),
                 ("scale_fit", C.c_double), ("dx", C.c_double), ("dy", C.c_double), ("dpr", C.c_double)]
@@ -86,6 +90,10 @@ SIGNATURES = {
     "stitch_run": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult)]),
     "stitch_submit": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult), C.POINTER(C.c_uint64)]),
     "stitch_wait": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "stitch_probe_image": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(StitchImageInfo)]),
+    "stitch_orientation_name": (C.c_char_p, [C.c_int32]),
+    "stitch_type_name": (C.c_char_p, [C.c_int32]),
+    "stitch_prepare_record": (C.c_int, [C.POINTER(StitchImageInfo), C.c_int64, C.POINTER(StitchImageDesc)]),
     "stitch_preview_layout": (C.c_int, [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double,
                                         C.POINTER(StitchPreviewLayout)]),
     "stitch_preview": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_double, C.c_double,

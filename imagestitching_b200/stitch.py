@@ -171,6 +171,37 @@ def compute_layout(images: Sequence[Dict[str, Any]], direction: str, mode: Optio
     return d
 
 
+def get_image_info(file_bytes: bytes) -> Dict[str, Any]:
+    """wx.getImageInfo for an in-memory file: {width, height, type, orientation} with WeChat's orientation string,
+    plus the numeric EXIF value as orientationExif."""
+    lib = L.load()
+    info = L.StitchImageInfo()
+    buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")
+    st = lib.stitch_probe_image(buf, len(file_bytes), C.byref(info))
+    if st != L.OK:
+        _raise(st)
+    return {"width": info.width, "height": info.height, "type": lib.stitch_type_name(info.type).decode(),
+            "orientation": lib.stitch_orientation_name(info.orientation_exif).decode(),
+            "orientationExif": info.orientation_exif}
+
+
+def prepare_image(file_bytes: bytes, **extra) -> Dict[str, Any]:
+    """_prepareSingleImage (index.js:678-741) for an in-memory file: the prepared record the stitch path reads."""
+    lib = L.load()
+    info = L.StitchImageInfo()
+    buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")
+    st = lib.stitch_probe_image(buf, len(file_bytes), C.byref(info))
+    if st != L.OK:
+        _raise(st)
+    d = L.StitchImageDesc()
+    lib.stitch_prepare_record(C.byref(info), len(file_bytes), C.byref(d))
+    rec = dict(extra)
+    rec.update({"naturalWidth": d.natural_width, "naturalHeight": d.natural_height, "width": d.width, "height": d.height,
+                "orientation": lib.stitch_orientation_name(info.orientation_exif).decode(), "fileSize": int(d.file_size),
+                "preparedType": lib.stitch_type_name(info.type).decode(), "prepared": True})
+    return rec
+
+
 def preview_layout(export_w: int, export_h: int, view_w: float, view_h: float, dpr=1) -> Dict[str, Any]:
     """createHighResCanvas + the fit-scale of index.js:1599-1603 (pure CPU, no GPU needed)."""
     pl = L.StitchPreviewLayout()

@@ -180,6 +180,28 @@ int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
 int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket);
 int stitch_wait(StitchCtx* ctx, uint64_t ticket);
 
+/* ---- intake: what wx.getImageInfo gives _prepareSingleImage (P:678-741) ----
+ * Reads width, height, container type and EXIF orientation from the first bytes of an image FILE
+ * (SUPPORTED_IMAGE_TYPES, P:4: jpg/jpeg, png, gif, bmp, webp).  Pure CPU. */
+typedef enum StitchImageType {
+  STITCH_TYPE_UNKNOWN = 0, STITCH_TYPE_JPEG = 1, STITCH_TYPE_PNG = 2, STITCH_TYPE_GIF = 3, STITCH_TYPE_BMP = 4,
+  STITCH_TYPE_WEBP = 5
+} StitchImageType;
+typedef struct StitchImageInfo {
+  int32_t width, height;     /* info.width / info.height (stored size, before any EXIF rotation) */
+  int32_t type;              /* StitchImageType; stitch_type_name() gives info.type */
+  int32_t orientation_exif;  /* EXIF tag 0x0112, 1..8; 1 when absent.  stitch_orientation_name() gives the
+                                string WeChat reports ('up', 'right', ...) */
+} StitchImageInfo;
+/* STITCH_E_BAD_IMAGE when the bytes are not a recognised image header (the page falls back to a transcode,
+ * P:684-694, then fails with the load error). */
+int stitch_probe_image(const void* file, size_t bytes, StitchImageInfo* out);
+const char* stitch_orientation_name(int32_t exif);
+const char* stitch_type_name(int32_t type);
+/* The prepared record of P:724-739 from a probe result and the file size.  orientation is 1: the page
+ * stores WeChat's orientation STRING, which drawWithOrientation's numeric switch (U:160-199) never matches. */
+int stitch_prepare_record(const StitchImageInfo* info, int64_t file_size, StitchImageDesc* out);
+
 /* ---- preview of the exported image on the page's <canvas> (P:1593-1603) ----
  * createHighResCanvas(node, size.width, size.height) (U:17-24) restores the canvas to floor(size * dpr)
  * device pixels under ctx.scale(dpr, dpr); clearRect leaves it transparent; the exported bitmap is drawn
