@@ -23,6 +23,12 @@ def _lib():
         lib.jpeg_ref_huff_tables.argtypes = [C.c_void_p, C.c_void_p]
         lib.jpeg_ref_block.restype = None
         lib.jpeg_ref_block.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        lib.jpeg_ref_info.restype = C.c_int
+        lib.jpeg_ref_info.argtypes = [C.c_void_p, C.c_size_t] + [C.POINTER(C.c_int)] * 5
+        lib.jpeg_ref_decode.restype = C.c_int
+        lib.jpeg_ref_decode.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64]
+        lib.jpeg_ref_coefficients.restype = C.c_int
+        lib.jpeg_ref_coefficients.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p]
         lib._jpeg_bound = True
     return lib
 
@@ -52,3 +58,38 @@ def huff_tables():
     length = np.empty((4, 256), np.uint8)
     _lib().jpeg_ref_huff_tables(code.ctypes.data, length.ctypes.data)
     return code, length
+
+
+def info(data: bytes):
+    """(width, height, components, luma h-sampling, luma v-sampling) of a baseline JPEG, or raises ValueError."""
+    lib = _lib()
+    v = [C.c_int() for _ in range(5)]
+    rc = lib.jpeg_ref_info(data, len(data), *[C.byref(x) for x in v])
+    if rc:
+        raise ValueError(f"oracle JPEG decoder: unsupported or corrupt file ({rc})")
+    return tuple(x.value for x in v)
+
+
+def decode(data: bytes) -> np.ndarray:
+    """oracle/jpeg_dec_ref.c: RGBA8 [h, w, 4] bitmap (alpha 255) of a baseline JPEG file."""
+    lib = _lib()
+    w, h, *_ = info(data)
+    out = np.empty((h, w, 4), np.uint8)
+    rc = lib.jpeg_ref_decode(data, len(data), out.ctypes.data, 0)
+    if rc:
+        raise ValueError(f"oracle JPEG decoder failed ({rc})")
+    return out
+
+
+def coefficients(data: bytes):
+    """Quantised coefficients per component: int16 [blocks_y, blocks_x, 64] over the MCU-padded planes."""
+    lib = _lib()
+    w, h, nc, hs, vs = info(data)
+    mcux, mcuy = -(-w // (8 * hs)), -(-h // (8 * vs))
+    shapes = [(mcuy * vs, mcux * hs, 64)] + [(mcuy, mcux, 64)] * (nc - 1)
+    arrs = [np.zeros(s, np.int16) for s in shapes]
+    ptrs = [a.ctypes.data for a in arrs] + [None] * (3 - nc)
+    rc = lib.jpeg_ref_coefficients(data, len(data), *ptrs)
+    if rc:
+        raise ValueError(f"oracle JPEG decoder failed ({rc})")
+    return arrs
