@@ -1,0 +1,674 @@
+// Baseline JPEG decoding on the GPU: replaces the bitmap decode inside loadImageFrom
+// (U:27-121, P:1441-1520) so a job can take the FILES instead of 48.8 MB RGBA bitmaps per image.
+//
+// Huffman-coded data has no random access, so the entropy decoder is the self-synchronising one
+// (Klein & Wiseman 2003; Weissenberger & Schmidt 2018): the scan is cut into subsequences of JDEC_SUB raw
+// bytes, one THREAD each.
+//   D1 first pass   every thread decodes its subsequence from its first bit as if a block started there and
+//                   records where it ended: (byte, bit, block-in-MCU, zig-zag index) -- the state the next
+//                   subsequence has to start from IF this one started right.
+//   D2 sync         repeated: a thread restarts from its predecessor's end state; when its own end state stops
+//                   changing the chain from the (known) start of the scan is consistent.  Huffman codes
+//                   re-synchronise after a few symbols, so this converges in a few rounds; restart markers
+//                   are hard synchronisation points.
+//   D3 offsets      exclusive scan of the number of blocks each subsequence starts.
+//   D4 write        decode once more from the true start states, coefficients into scan-order blocks.
+//   D5 dc           DC differences -> values: segmented scan over MCUs (segments = restart intervals).
+//   D6 idct         one thread per block: dequantise, integer LL&M inverse DCT (13-bit constants), planes.
+//   D7 colour       triangle-filter chroma upsampling + 16-bit fixed-point YCbCr -> RGB, RGBA8 out.
+// All arithmetic is integer and follows libjpeg's default pipeline; tests hold the bitmap byte-identical to
+// the sequential CPU decoder of the test tree, which is itself pinned to libjpeg.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "jpeg_parse.h"
+
+namespace stitch {
+namespace jpegdec {
+
+#define JDEC_SUB 128          // raw bytes per subsequence
+#define JDEC_THREADS 256
+#define JDEC_MAX_IMAGES 9
+
+struct DecImage {
+  const uint8_t* scan;        // entropy-coded segment (device)
+  const Tables* tab;          // device copy of the header tables
+  uint32_t scan_len;
+  int32_t w, h, ncomp, hs, vs, mcux, mcuy, ri, bpm;   // bpm = blocks per MCU
+  int32_t n_sub, n_blocks;
+  int32_t td[3], ta[3], tq[3];
+  uint4* state;               // [n_sub] end state {byte, bit | b << 8 | z << 16 | done << 24, blocks started, -}
+  uint32_t* prefix;           // [n_sub] exclusive scan of blocks started
+  int16_t* coef;              // [n_blocks][64] scan order, zig-zag order inside a block
+  uint8_t* plane[3];          // component planes, MCU-padded
+  int32_t pw[3], ph[3];
+  uint8_t* rgba;              // output bitmap
+  int64_t pitch;
+};
+struct DecBatch {
+  DecImage img[JDEC_MAX_IMAGES];
+  int32_t n;
+  uint32_t* changed;          // device flag raised by the sync kernel
+};
+
+// ---- Huffman tables in shared memory ----
+struct SmemTables {
+  uint16_t lut[4][256];       // first 8 bits -> (length << 8 | symbol), 0 = longer than 8 bits
+  int32_t maxcode[4][17];     // per length 1..16, -1 = no codes
+  int32_t mincode[4][17];
+  int32_t valptr[4][17];
+  uint8_t vals[4][256];
+};
+
+__device__ __forceinline__ void build_tables(const Tables* __restrict__ g, SmemTables& s) {
+  for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) {
+    s.vals[i >> 8][i & 255] = g->vals[i >> 8][i & 255];
+    s.lut[i >> 8][i & 255] = 0;
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    const int t = threadIdx.x;
+    int code = 0, k = 0;
+    for (int l = 1; l <= 16; ++l) {
+      const int nb = g->bits[t][l - 1];
+      s.valptr[t][l] = k;
+      s.mincode[t][l] = code;
+      if (l <= 8)
+        for (int j = 0; j < nb; ++j) {
+          const int first = (code + j) << (8 - l);
+          for (int f = 0; f < (1 << (8 - l)); ++f) s.lut[t][(first + f) & 255] = (uint16_t)(l << 8 | g->vals[t][(k + j) & 255]);
+        }
+      code += nb;
+      k += nb;
+      s.maxcode[t][l] = nb ? code - 1 : -1;
+      code <<= 1;
+    }
+  }
+  __syncthreads();
+}
+
+// ---- bit reader over the raw (byte-stuffed) scan ----
+struct Reader {
+  const uint8_t* p;
+  uint32_t n;      // scan length
+  uint32_t pos;    // next raw byte to fetch
+  uint64_t acc;    // unread bits, top aligned
+  int cnt;         // bits in acc (real + fake)
+  int fake;        // zero bits fed after a marker / the end of the data
+  bool mark;       // fetching has reached a marker (p[pos] == 0xFF, p[pos+1] != 0) or the end
+};
+
+__device__ __forceinline__ void rd_start(Reader& r, uint32_t byte, int bit) {
+  r.pos = byte;
+  r.acc = 0;
+  r.cnt = 0;
+  r.fake = 0;
+  r.mark = false;
+  (void)bit;
+}
+__device__ __forceinline__ void rd_fill(Reader& r) {
+  while (r.cnt <= 56) {
+    uint32_t v = 0;
+    if (!r.mark) {
+      if (r.pos < r.n) {
+        v = r.p[r.pos];
+        if (v == 0xFFu) {
+          const uint32_t nx = (r.pos + 1 < r.n) ? r.p[r.pos + 1] : 0xD9u;
+          if (nx == 0) r.pos += 2;               // stuffed zero
+          else { r.mark = true; v = 0; }         // marker: stay on it
+        } else {
+          r.pos += 1;
+        }
+      } else {
+        r.mark = true;
+      }
+    }
+    if (r.mark) r.fake += 8;
+    r.acc |= (uint64_t)v << (56 - r.cnt);
+    r.cnt += 8;
+  }
+}
+__device__ __forceinline__ void rd_skip(Reader& r, int nbits) {
+  r.acc <<= nbits;
+  r.cnt -= nbits;
+}
+// Raw byte index + bit offset of the next unread bit (the canonical form states are compared in).
+__device__ __forceinline__ void rd_where(const Reader& r, uint32_t* byte, int* bit) {
+  const int real = r.cnt - r.fake;               // unread real bits (>= 0 at symbol boundaries)
+  const int nb = (real + 7) >> 3;
+  uint32_t c = r.pos;
+  for (int k = 0; k < nb; ++k) {
+    --c;
+    if (r.p[c] == 0 && c > 0 && r.p[c - 1] == 0xFFu) --c;   // the data byte is the 0xFF of an FF 00 pair
+  }
+  *byte = c;
+  *bit = (8 - (real & 7)) & 7;
+}
+
+struct State {
+  uint32_t byte;
+  int bit, b, z;
+  bool done;       // reached the end of the scan (EOI or any non-RST marker, or the end of the data)
+};
+__device__ __forceinline__ uint32_t pack_state(const State& s) {
+  return (uint32_t)s.bit | (uint32_t)s.b << 8 | (uint32_t)s.z << 16 | (s.done ? 1u << 24 : 0u);
+}
+__device__ __forceinline__ State unpack_state(uint32_t byte, uint32_t v) {
+  State s;
+  s.byte = byte;
+  s.bit = v & 255;
+  s.b = (v >> 8) & 255;
+  s.z = (v >> 16) & 255;
+  s.done = (v >> 24) & 1;
+  return s;
+}
+
+__device__ __forceinline__ int huff_decode(const SmemTables& T, int t, Reader& r) {
+  const uint32_t v = (uint32_t)(r.acc >> 48);    // 16 bits
+  const uint32_t e = T.lut[t][v >> 8];
+  if (e) {
+    rd_skip(r, e >> 8);
+    return e & 255;
+  }
+  for (int l = 9; l <= 16; ++l) {
+    const int code = (int)(v >> (16 - l));
+    if (code <= T.maxcode[t][l] && code >= T.mincode[t][l]) {
+      rd_skip(r, l);
+      return T.vals[t][(T.valptr[t][l] + code - T.mincode[t][l]) & 255];
+    }
+  }
+  rd_skip(r, 16);                                // no such code (only on a wrong path or in a corrupt file)
+  return 0;
+}
+
+// Decodes the symbols whose first bit lies in raw bytes [.., end_byte), starting from `s`.  Returns the
+// state after the last of them and the number of blocks STARTED (DC symbols).  WRITE: also stores the
+// coefficients; blk is the scan-order index of the block in progress (or of the next one when s.z == 0).
+template <bool WRITE>
+__device__ __forceinline__ State decode_range(const DecImage& I, const SmemTables& T, State s, uint32_t end_byte,
+                                              uint32_t* started, int64_t blk) {
+  Reader r;
+  r.p = I.scan;
+  r.n = I.scan_len;
+  rd_start(r, s.byte, s.bit);
+  uint32_t count = 0;
+  const int ny = I.hs * I.vs;
+  bool first = true;
+  int b = s.b, z = s.z;
+  State out = s;
+  if (s.done) { *started = 0; return s; }
+  int16_t* cur = nullptr;
+  if (WRITE && z > 0) { --blk; cur = (blk >= 0 && blk < I.n_blocks) ? I.coef + blk * 64 : nullptr; ++blk; }
+  for (;;) {
+    rd_fill(r);
+    if (first) { rd_skip(r, s.bit); first = false; }
+    // Position of the next symbol.  With `real` unread bits in nb (possibly partial) data bytes the raw index c
+    // of its first byte lies in [pos - 2 nb, pos - nb] (stuffed zeros); only when the upper bound reaches the
+    // boundary is the exact index needed, and rd_where walks back over the last bytes to get it.
+    {
+      const int real = r.cnt - r.fake;
+      const uint32_t nb = (uint32_t)((real + 7) >> 3);
+      if (r.pos - nb >= end_byte) {
+        uint32_t c;
+        int cbit;
+        rd_where(r, &c, &cbit);
+        if (c >= end_byte) {
+          out.byte = c; out.bit = cbit; out.b = b; out.z = z; out.done = false;
+          break;
+        }
+      }
+    }
+    // ---- one symbol ----
+    const int comp = b < ny ? 0 : b - ny + 1;
+    int value = 0, zpos = z;
+    bool block_done = false, is_dc = (z == 0);
+    if (is_dc) {
+      const int sz = huff_decode(T, I.td[comp], r) & 15;
+      if (sz) {
+        const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
+        rd_skip(r, sz);
+        value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
+      }
+      z = 1;
+    } else {
+      const int rs = huff_decode(T, 2 + I.ta[comp], r);
+      const int run = rs >> 4, sz = rs & 15;
+      if (sz == 0) {
+        if (run == 15) { z += 16; zpos = -1; if (z > 63) block_done = true; }
+        else { block_done = true; zpos = -1; }
+      } else {
+        z += run;
+        const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
+        rd_skip(r, sz);
+        value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
+        zpos = z;
+        z += 1;
+        if (z > 63) block_done = true;
+      }
+    }
+    if (r.cnt < r.fake) {
+      // the symbol ran into a marker (it was padding) or past the end: drop it
+      const uint32_t mpos = r.pos;
+      const uint32_t m = (mpos + 1 < r.n) ? r.p[mpos + 1] : 0xD9u;
+      if (mpos + 1 < r.n && m >= 0xD0u && m <= 0xD7u) {   // RSTn: byte-aligned restart, predictors and position reset
+        b = 0;
+        z = 0;
+        rd_start(r, mpos + 2, 0);
+        if (mpos + 2 >= end_byte) {
+          out.byte = mpos + 2; out.bit = 0; out.b = 0; out.z = 0; out.done = false;
+          break;
+        }
+        continue;
+      }
+      out.byte = r.n; out.bit = 0; out.b = 0; out.z = 0; out.done = true;
+      break;
+    }
+    if (is_dc) {
+      ++count;
+      if (WRITE) {
+        cur = (blk >= 0 && blk < I.n_blocks) ? I.coef + blk * 64 : nullptr;
+        ++blk;
+        if (cur) cur[0] = (int16_t)value;
+      }
+    } else if (WRITE && zpos > 0 && zpos < 64 && cur) {
+      cur[zpos] = (int16_t)value;
+    }
+    if (block_done) {
+      z = 0;
+      b = (b + 1 == I.bpm) ? 0 : b + 1;
+    }
+  }
+  *started = count;
+  return out;
+}
+
+
+// Start state of subsequence i when nothing is known: the first data bit of raw byte i * JDEC_SUB, taken as
+// the DC symbol of the first block of an MCU.  (A stuffed zero or the second byte of an RSTn is stepped over.)
+__device__ __forceinline__ State guess_state(const DecImage& I, uint32_t i) {
+  State s;
+  s.byte = i * JDEC_SUB;
+  s.bit = 0;
+  s.b = 0;
+  s.z = 0;
+  s.done = false;
+  if (i > 0 && s.byte < I.scan_len && I.scan[s.byte - 1] == 0xFFu) {
+    const uint32_t v = I.scan[s.byte];
+    if (v == 0 || (v >= 0xD0u && v <= 0xD7u)) s.byte += 1;
+  }
+  return s;
+}
+
+// D1: first pass from guessed states.
+__global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ SmemTables T;
+  const DecImage& I = B.img[blockIdx.y];
+  if (blockIdx.x * JDEC_THREADS >= (unsigned)I.n_sub) return;
+  build_tables(I.tab, T);
+  const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
+  if (i >= (uint32_t)I.n_sub) return;
+  uint32_t started = 0;
+  const State e = decode_range<false>(I, T, guess_state(I, i), (i + 1) * JDEC_SUB, &started, 0);
+  I.state[i] = make_uint4(e.byte, pack_state(e), started, 0u);
+}
+
+// D2: one synchronisation round.  Inside a block the threads iterate until their chain is consistent with the
+// state their first thread got from the previous block (as it was when the kernel started); the host
+// relaunches until no end state changes any more.
+__global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ SmemTables T;
+  __shared__ uint2 sh_state[JDEC_THREADS + 1];   // [t + 1] = end state of thread t; [0] = predecessor block's last
+  __shared__ int sh_dirty[JDEC_THREADS + 1];     // [t + 1]: thread t's end state changed in the last iteration
+  const DecImage& I = B.img[blockIdx.y];
+  if (blockIdx.x * JDEC_THREADS >= (unsigned)I.n_sub) return;
+  build_tables(I.tab, T);
+  const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
+  const bool live = i < (uint32_t)I.n_sub;
+  const int t = threadIdx.x;
+  uint4 mine = live ? I.state[i] : make_uint4(0, 0, 0, 0);
+  sh_state[t + 1] = make_uint2(mine.x, mine.y);
+  sh_dirty[t + 1] = 1;   // first iteration: everybody re-decodes from the predecessor's state
+  if (t == 0) {
+    if (i == 0) {
+      sh_state[0] = make_uint2(0u, 0u);          // the scan starts at byte 0, bit 0, block 0, DC
+    } else {
+      const uint4 p = I.state[i - 1];
+      sh_state[0] = make_uint2(p.x, p.y);
+    }
+    sh_dirty[0] = 1;
+  }
+  __syncthreads();
+  bool changed_ever = false, settled = false;
+  for (int iter = 0; iter < JDEC_THREADS + 1; ++iter) {
+    const bool work = live && sh_dirty[t] != 0;
+    uint2 mine_new = make_uint2(mine.x, mine.y);
+    uint32_t started = mine.z;
+    if (work) {
+      const uint2 ps = sh_state[t];
+      const State e = decode_range<false>(I, T, unpack_state(ps.x, ps.y), (i + 1) * JDEC_SUB, &started, 0);
+      mine_new = make_uint2(e.byte, pack_state(e));
+    }
+    __syncthreads();
+    const bool changed = work && (mine_new.x != mine.x || mine_new.y != mine.y);
+    if (work) {
+      mine.x = mine_new.x;
+      mine.y = mine_new.y;
+      mine.z = started;
+      sh_state[t + 1] = mine_new;
+    }
+    sh_dirty[t + 1] = changed ? 1 : 0;
+    if (t == 0) sh_dirty[0] = 0;
+    changed_ever |= changed;
+    if (!__syncthreads_or(changed ? 1 : 0)) { settled = true; break; }
+  }
+  if (live) I.state[i] = mine;
+  if (!settled && t == 0) atomicOr(B.changed, 1u);   // ran out of iterations with changes pending
+  // the LAST thread's end state feeds the next block: if it moved, another round is needed
+  if (live && changed_ever && (t == JDEC_THREADS - 1 || i == (uint32_t)I.n_sub - 1) && i + 1 < (uint32_t)I.n_sub)
+    atomicOr(B.changed, 1u);
+}
+
+// D3: exclusive scan of the blocks-started counts (one block per image).
+__global__ void __launch_bounds__(1024) jdec_scan_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ uint32_t warp_sum[32];
+  __shared__ uint32_t carry_s;
+  const DecImage& I = B.img[blockIdx.x];
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  if (t == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < I.n_sub; base += 1024) {
+    const int i = base + t;
+    const uint32_t v = i < I.n_sub ? I.state[i].z : 0u;
+    uint32_t x = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    if (lane == 31) warp_sum[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      uint32_t s = warp_sum[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, s, d);
+        if (lane >= d) s += y;
+      }
+      warp_sum[lane] = s;
+    }
+    __syncthreads();
+    const uint32_t before = carry_s + (w ? warp_sum[w - 1] : 0u) + x - v;
+    if (i < I.n_sub) I.prefix[i] = before;
+    __syncthreads();
+    if (t == 1023) carry_s = before + v;
+    __syncthreads();
+  }
+}
+
+// D4: write pass from the synchronised states.
+__global__ void __launch_bounds__(JDEC_THREADS) jdec_write_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ SmemTables T;
+  const DecImage& I = B.img[blockIdx.y];
+  if (blockIdx.x * JDEC_THREADS >= (unsigned)I.n_sub) return;
+  build_tables(I.tab, T);
+  const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
+  if (i >= (uint32_t)I.n_sub) return;
+  State s;
+  if (i == 0) { s.byte = 0; s.bit = 0; s.b = 0; s.z = 0; s.done = false; }
+  else { const uint4 p = I.state[i - 1]; s = unpack_state(p.x, p.y); }
+  uint32_t started = 0;
+  decode_range<true>(I, T, s, (i + 1) * JDEC_SUB, &started, (int64_t)I.prefix[i]);
+}
+
+// D5: DC differences -> DC values.  One block per image walks the MCUs in chunks of 1024 with a running
+// carry per component; a restart interval boundary (MCU index multiple of ri) zeroes the predictors.
+__global__ void __launch_bounds__(1024) jdec_dc_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ int wsum[3][32];
+  __shared__ int wflag[32];
+  __shared__ int carry[3];
+  const DecImage& I = B.img[blockIdx.x];
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  const int n_mcu = I.mcux * I.mcuy, ny = I.hs * I.vs;
+  if (t < 3) carry[t] = 0;
+  __syncthreads();
+  for (int base = 0; base < n_mcu; base += 1024) {
+    const int m = base + t;
+    const bool live = m < n_mcu;
+    int sum[3] = {0, 0, 0};
+    int16_t* blk = I.coef + (int64_t)m * I.bpm * 64;
+    if (live) {
+      for (int b = 0; b < ny; ++b) sum[0] += blk[b * 64];
+      if (I.ncomp == 3) { sum[1] = blk[ny * 64]; sum[2] = blk[(ny + 1) * 64]; }
+    }
+    // segmented inclusive scan over MCUs: flag = this MCU starts a restart interval
+    int flag = (live && I.ri > 0 && (m % I.ri) == 0) ? 1 : 0;
+    int x[3] = {sum[0], sum[1], sum[2]}, f = flag;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int f2 = __shfl_up_sync(0xffffffffu, f, d);
+      int y[3];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) y[c] = __shfl_up_sync(0xffffffffu, x[c], d);
+      if (lane >= d) {
+        if (!f) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) x[c] += y[c];
+        }
+        f |= f2;
+      }
+    }
+    if (lane == 31) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) wsum[c][w] = x[c];
+      wflag[w] = f;
+    }
+    __syncthreads();
+    if (w == 0) {
+      int xs[3] = {wsum[0][lane], wsum[1][lane], wsum[2][lane]}, fs = wflag[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int f2 = __shfl_up_sync(0xffffffffu, fs, d);
+        int y[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) y[c] = __shfl_up_sync(0xffffffffu, xs[c], d);
+        if (lane >= d) {
+          if (!fs) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) xs[c] += y[c];
+          }
+          fs |= f2;
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 3; ++c) wsum[c][lane] = xs[c];
+      wflag[lane] = fs;
+    }
+    __syncthreads();
+    // prefix of everything before this MCU's warp + chunk carry, unless a flag intervened
+    int pre[3];
+    {
+      const bool cut_w = f != 0;                        // a restart inside my warp at or before me
+      const bool cut_b = w > 0 && wflag[w - 1] != 0;    // a restart in an earlier warp of this chunk
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        int v = x[c];                                   // inclusive within the warp (segmented)
+        if (!cut_w) {
+          if (w > 0) v += wsum[c][w - 1];
+          if (!cut_b) v += carry[c];
+        }
+        pre[c] = v - sum[c];                            // exclusive: predictor entering this MCU
+      }
+    }
+    if (live) {
+      if (flag) { pre[0] = pre[1] = pre[2] = 0; }
+      int p0 = pre[0];
+      for (int b = 0; b < ny; ++b) { p0 += blk[b * 64]; blk[b * 64] = (int16_t)p0; }
+      if (I.ncomp == 3) {
+        blk[ny * 64] = (int16_t)(pre[1] + sum[1]);
+        blk[(ny + 1) * 64] = (int16_t)(pre[2] + sum[2]);
+      }
+    }
+    __syncthreads();
+    if (t == 1023) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) carry[c] = pre[c] + sum[c];
+    }
+    __syncthreads();
+  }
+}
+
+// ---- D6: dequantise + inverse DCT (LL&M, 13-bit constants; same arithmetic as libjpeg's default) ----
+__device__ __forceinline__ void idct8(const int* in, int* out, int shift) {
+  int z2 = in[2], z3 = in[6];
+  int z1 = (z2 + z3) * 4433;
+  int tmp2 = z1 + z3 * (-15137), tmp3 = z1 + z2 * 6270;
+  z2 = in[0];
+  z3 = in[4];
+  int tmp0 = (z2 + z3) * 8192, tmp1 = (z2 - z3) * 8192;
+  const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+  tmp0 = in[7];
+  tmp1 = in[5];
+  tmp2 = in[3];
+  tmp3 = in[1];
+  z1 = tmp0 + tmp3;
+  z2 = tmp1 + tmp2;
+  z3 = tmp0 + tmp2;
+  int z4 = tmp1 + tmp3;
+  const int z5 = (z3 + z4) * 9633;
+  tmp0 *= 2446;
+  tmp1 *= 16819;
+  tmp2 *= 25172;
+  tmp3 *= 12299;
+  z1 *= -7373;
+  z2 *= -20995;
+  z3 *= -16069;
+  z4 *= -3196;
+  z3 += z5;
+  z4 += z5;
+  tmp0 += z1 + z3;
+  tmp1 += z2 + z4;
+  tmp2 += z2 + z3;
+  tmp3 += z1 + z4;
+  const int r = 1 << (shift - 1);
+  out[0] = (tmp10 + tmp3 + r) >> shift;
+  out[7] = (tmp10 - tmp3 + r) >> shift;
+  out[1] = (tmp11 + tmp2 + r) >> shift;
+  out[6] = (tmp11 - tmp2 + r) >> shift;
+  out[2] = (tmp12 + tmp1 + r) >> shift;
+  out[5] = (tmp12 - tmp1 + r) >> shift;
+  out[3] = (tmp13 + tmp0 + r) >> shift;
+  out[4] = (tmp13 - tmp0 + r) >> shift;
+}
+
+__global__ void __launch_bounds__(128) jdec_idct_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ uint16_t sq[4][64];     // zig-zag order
+  const DecImage& I = B.img[blockIdx.y];
+  if (blockIdx.x * 128 >= (unsigned)I.n_blocks) return;
+  constexpr uint8_t ZZ[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                              41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                              30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+  for (int k = threadIdx.x; k < 256; k += 128) sq[k >> 6][k & 63] = I.tab->q[k >> 6][k & 63];   // zig-zag order, as stored
+  __syncthreads();
+  const int blk = blockIdx.x * 128 + threadIdx.x;
+  if (blk >= I.n_blocks) return;
+  const int m = blk / I.bpm, b = blk - m * I.bpm, ny = I.hs * I.vs;
+  const int comp = b < ny ? 0 : b - ny + 1;
+  const int mx = m % I.mcux, my = m / I.mcux;
+  int bx, by;
+  if (comp == 0) { bx = mx * I.hs + (b % I.hs); by = my * I.vs + (b / I.hs); }
+  else { bx = mx; by = my; }
+  const uint16_t* q = sq[I.tq[comp]];
+  // load (zig-zag order, 128 contiguous bytes) and dequantise into natural order
+  int v[64];
+  const int4* src = reinterpret_cast<const int4*>(I.coef + (int64_t)blk * 64);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int4 a = src[j];
+    const int w4[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k0 = j * 8 + e * 2;
+      v[ZZ[k0]] = (int)(int16_t)(w4[e] & 0xffff) * (int)q[k0];
+      v[ZZ[k0 + 1]] = (int)(int16_t)(w4[e] >> 16) * (int)q[k0 + 1];
+    }
+  }
+  // columns, then rows
+  int ws[64];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    int in[8], o[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) in[r] = v[r * 8 + c];
+    idct8(in, o, 11);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) ws[r * 8 + c] = o[r];
+  }
+  uint8_t* dst = I.plane[comp] + (int64_t)by * 8 * I.pw[comp] + bx * 8;
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    int o[8];
+    idct8(&ws[r * 8], o, 18);
+    uint32_t lo = 0, hi = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      lo |= (uint32_t)min(max(o[c] + 128, 0), 255) << (8 * c);
+      hi |= (uint32_t)min(max(o[c + 4] + 128, 0), 255) << (8 * c);
+    }
+    *reinterpret_cast<uint2*>(dst + (int64_t)r * I.pw[comp]) = make_uint2(lo, hi);
+  }
+}
+
+// ---- D7: chroma upsampling (triangle filter, as libjpeg's "fancy" upsampling) + YCbCr -> RGB ----
+__global__ void __launch_bounds__(256) jdec_colour_kernel(const __grid_constant__ DecBatch B) {
+  const DecImage& I = B.img[blockIdx.z];
+  const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
+  if (x >= I.w || y >= I.h) return;
+  const int yy = I.plane[0][(int64_t)y * I.pw[0] + x];
+  uint32_t px;
+  if (I.ncomp == 1) {
+    px = (uint32_t)yy * 0x010101u | 0xff000000u;
+  } else {
+    const int cw = (I.w + I.hs - 1) / I.hs, chh = (I.h + I.vs - 1) / I.vs;
+    const bool fancy = I.hs == 2 && cw > 2;
+    int cv[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      const uint8_t* P = I.plane[c + 1];
+      const int stride = I.pw[c + 1];
+      int val;
+      if (I.hs == 1) {
+        val = P[(int64_t)y * stride + x];
+      } else if (I.vs == 1) {
+        const uint8_t* r0 = P + (int64_t)y * stride;
+        const int i = x >> 1;
+        if (!fancy) val = r0[i];
+        else if ((x & 1) == 0) val = i == 0 ? r0[0] : (r0[i] * 3 + r0[i - 1] + 1) >> 2;
+        else val = i == cw - 1 ? r0[i] : (r0[i] * 3 + r0[i + 1] + 2) >> 2;
+      } else {
+        const int r = y >> 1, i = x >> 1;
+        if (!fancy) {
+          val = P[(int64_t)r * stride + i];
+        } else {
+          const int rn = min(max((y & 1) ? r + 1 : r - 1, 0), chh - 1);
+          const uint8_t* r0 = P + (int64_t)r * stride;
+          const uint8_t* r1 = P + (int64_t)rn * stride;
+          const int cur = r0[i] * 3 + r1[i];
+          if ((x & 1) == 0) val = i == 0 ? (cur * 4 + 8) >> 4 : (cur * 3 + (r0[i - 1] * 3 + r1[i - 1]) + 8) >> 4;
+          else val = i == cw - 1 ? (cur * 4 + 7) >> 4 : (cur * 3 + (r0[i + 1] * 3 + r1[i + 1]) + 7) >> 4;
+        }
+      }
+      cv[c] = val - 128;
+    }
+    const int R = min(max(yy + ((91881 * cv[1] + 32768) >> 16), 0), 255);
+    const int G = min(max(yy + ((-22554 * cv[0] + 32768 - 46802 * cv[1]) >> 16), 0), 255);
+    const int Bc = min(max(yy + ((116130 * cv[0] + 32768) >> 16), 0), 255);
+    px = (uint32_t)R | (uint32_t)G << 8 | (uint32_t)Bc << 16 | 0xff000000u;
+  }
+  *reinterpret_cast<uint32_t*>(I.rgba + (int64_t)y * I.pitch + (int64_t)x * 4) = px;
+}
+
+}  // namespace jpegdec
+}  // namespace stitch

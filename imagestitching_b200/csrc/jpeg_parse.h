@@ -1,0 +1,127 @@
+// Host-side JPEG header parser of the GPU decoder (jpeg_decode.cuh): marker segments of ITU-T T.81 Annex B.
+//
+// Replaces the first half of loadImageFrom (U:27-121: canvas.createImage() + img.src = path); the entropy
+// decoding, IDCT, upsampling and colour conversion run on the GPU.  Supported: SOF0 / SOF1 (Huffman, 8 bit),
+// 1 or 3 components in one interleaved scan, luma sampling 1x1 / 2x1 / 2x2 with 1x1 chroma, DRI.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cstring>
+
+namespace stitch {
+namespace jpegdec {
+
+// zig-zag position k -> natural index (T.81 Figure A.6)
+static const uint8_t kZigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                                    41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                                    30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+// Everything the kernels need from the headers; uploaded once per image.
+struct Tables {
+  uint16_t q[4][64];      // quantisation tables in ZIG-ZAG order (as DQT stores them)
+  uint8_t bits[4][16];    // Huffman BITS, tables [class * 2 + id]
+  uint8_t vals[4][256];   // HUFFVAL
+};
+
+struct Header {
+  int w = 0, h = 0, ncomp = 0;
+  int hs = 1, vs = 1;          // luma sampling factors (chroma is 1x1)
+  int tq[3] = {0, 0, 0}, td[3] = {0, 0, 0}, ta[3] = {0, 0, 0};
+  int ri = 0;                  // restart interval in MCUs (0 = none)
+  int mcux = 0, mcuy = 0;
+  size_t scan_off = 0, scan_len = 0;
+  Tables tab;
+};
+
+enum ParseStatus { kOk = 0, kNotJpeg = 1, kCorrupt = 2, kUnsupported = 3 };
+
+inline ParseStatus parse(const uint8_t* p, size_t n, Header* H) {
+  std::memset(&H->tab, 0, sizeof(H->tab));
+  if (n < 4 || p[0] != 0xFF || p[1] != 0xD8) return kNotJpeg;
+  bool have_sof = false, have_h[4] = {false, false, false, false}, have_q[4] = {false, false, false, false};
+  size_t o = 2;
+  while (o + 4 <= n) {
+    if (p[o] != 0xFF) return kCorrupt;
+    const int m = p[o + 1];
+    if (m == 0xFF) { ++o; continue; }
+    if (m == 0x01 || (m >= 0xD0 && m <= 0xD7)) { o += 2; continue; }
+    const size_t len = ((size_t)p[o + 2] << 8) | p[o + 3];
+    if (len < 2 || o + 2 + len > n) return kCorrupt;
+    const uint8_t* s = p + o + 4;
+    const size_t sl = len - 2;
+    if (m == 0xDB) {
+      for (size_t i = 0; i < sl;) {
+        const int pq = s[i] >> 4, t = s[i] & 15;
+        if (pq != 0) return kUnsupported;  // 16-bit tables belong to 12-bit JPEG
+        if (t > 3 || i + 65 > sl) return kCorrupt;
+        for (int k = 0; k < 64; ++k) H->tab.q[t][k] = s[i + 1 + k];
+        have_q[t] = true;
+        i += 65;
+      }
+    } else if (m == 0xC0 || m == 0xC1) {
+      if (sl < 6) return kCorrupt;
+      if (s[0] != 8) return kUnsupported;
+      H->h = (s[1] << 8) | s[2];
+      H->w = (s[3] << 8) | s[4];
+      H->ncomp = s[5];
+      if (H->w == 0 || H->h == 0) return kCorrupt;
+      if (H->ncomp != 1 && H->ncomp != 3) return kUnsupported;
+      if (sl < (size_t)(6 + 3 * H->ncomp)) return kCorrupt;
+      int hs[3] = {1, 1, 1}, vs[3] = {1, 1, 1};
+      for (int c = 0; c < H->ncomp; ++c) {
+        hs[c] = s[7 + 3 * c] >> 4;
+        vs[c] = s[7 + 3 * c] & 15;
+        H->tq[c] = s[8 + 3 * c];
+        if (H->tq[c] > 3) return kCorrupt;
+      }
+      if (H->ncomp == 1) {
+        H->hs = H->vs = 1;
+      } else {
+        if (hs[1] != 1 || vs[1] != 1 || hs[2] != 1 || vs[2] != 1) return kUnsupported;
+        if (!((hs[0] == 1 && vs[0] == 1) || (hs[0] == 2 && vs[0] == 1) || (hs[0] == 2 && vs[0] == 2))) return kUnsupported;
+        H->hs = hs[0];
+        H->vs = vs[0];
+      }
+      H->mcux = (H->w + 8 * H->hs - 1) / (8 * H->hs);
+      H->mcuy = (H->h + 8 * H->vs - 1) / (8 * H->vs);
+      have_sof = true;
+    } else if (m >= 0xC2 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
+      return kUnsupported;  // progressive, lossless, arithmetic coding
+    } else if (m == 0xC4) {
+      for (size_t i = 0; i < sl;) {
+        if (i + 17 > sl) return kCorrupt;
+        const int tc = s[i] >> 4, th = s[i] & 15;
+        if (tc > 1 || th > 1) return kUnsupported;  // baseline: two tables per class
+        const int t = tc * 2 + th;
+        int cnt = 0;
+        for (int l = 0; l < 16; ++l) { H->tab.bits[t][l] = s[i + 1 + l]; cnt += s[i + 1 + l]; }
+        if (cnt > 256 || i + 17 + cnt > sl) return kCorrupt;
+        std::memset(H->tab.vals[t], 0, 256);
+        std::memcpy(H->tab.vals[t], s + i + 17, cnt);
+        have_h[t] = true;
+        i += 17 + cnt;
+      }
+    } else if (m == 0xDD) {
+      if (sl < 2) return kCorrupt;
+      H->ri = (s[0] << 8) | s[1];
+    } else if (m == 0xDA) {
+      if (!have_sof) return kCorrupt;
+      if (sl < 1 || s[0] != H->ncomp) return kUnsupported;  // non-interleaved scans
+      if (sl < (size_t)(1 + 2 * H->ncomp + 3)) return kCorrupt;
+      for (int c = 0; c < H->ncomp; ++c) {
+        H->td[c] = s[2 + 2 * c] >> 4;
+        H->ta[c] = s[2 + 2 * c] & 15;
+        if (H->td[c] > 1 || H->ta[c] > 1) return kUnsupported;
+        if (!have_h[H->td[c]] || !have_h[2 + H->ta[c]] || !have_q[H->tq[c]]) return kCorrupt;
+      }
+      H->scan_off = o + 2 + len;
+      H->scan_len = n - H->scan_off;
+      return kOk;
+    }
+    o += 2 + len;
+  }
+  return kCorrupt;
+}
+
+}  // namespace jpegdec
+}  // namespace stitch

@@ -21,6 +21,7 @@
 #include "stitch_plan.h"
 #include "launch.cuh"
 #include "jpeg_kernels.cuh"
+#include "jpeg_decode.cuh"
 #include "synth.cuh"
 
 struct PendingJob {
@@ -46,6 +47,9 @@ struct Lane {
   void* jpeg_arena = nullptr;
   size_t jpeg_arena_cap = 0;
   uint64_t* jpeg_info_host = nullptr;
+  // JPEG decode: grow-only arena (scan bytes, tables, subsequence states, coefficients, component planes)
+  void* dec_arena = nullptr;
+  size_t dec_arena_cap = 0;
 };
 
 struct StitchCtx {
@@ -145,10 +149,122 @@ void free_lane(Lane& ln) {
     if (p) cudaFree(p);
   if (ln.out_stage) cudaFree(ln.out_stage);
   if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
+  if (ln.dec_arena) cudaFree(ln.dec_arena);
   if (ln.jpeg_info_host) cudaFreeHost(ln.jpeg_info_host);
   stitch::free_scratch(ln.scratch);
   if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
   ln = Lane();
+}
+
+// One JPEG file to decode into a device bitmap.
+struct DecodeItem {
+  const uint8_t* file;
+  size_t bytes;
+  stitch::jpegdec::Header hdr;
+  uint8_t* rgba;     // device destination
+  int64_t pitch;
+};
+
+// GPU decode of up to 9 files in one batch of launches on the lane's stream (jpeg_decode.cuh).  Synchronises
+// the stream: the number of synchronisation rounds is data dependent.
+int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
+  namespace jd = stitch::jpegdec;
+  if (n <= 0) return STITCH_OK;
+  if (n > JDEC_MAX_IMAGES) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  jd::DecBatch B;
+  std::memset(&B, 0, sizeof B);
+  B.n = n;
+  size_t need = 256;  // the `changed` flag
+  struct Carve { size_t scan, tab, state, prefix, coef, plane[3]; } cv[JDEC_MAX_IMAGES];
+  int max_sub = 0, max_blocks = 0, max_w = 0, max_h = 0;
+  for (int i = 0; i < n; ++i) {
+    const jd::Header& H = items[i].hdr;
+    jd::DecImage& I = B.img[i];
+    if (H.scan_len >= (size_t)1 << 31) return fail(ctx, STITCH_E_BAD_IMAGE, "JPEG scan larger than 2 GiB");
+    I.scan_len = (uint32_t)H.scan_len;
+    I.w = H.w; I.h = H.h; I.ncomp = H.ncomp; I.hs = H.hs; I.vs = H.vs; I.mcux = H.mcux; I.mcuy = H.mcuy; I.ri = H.ri;
+    I.bpm = H.ncomp == 1 ? 1 : H.hs * H.vs + 2;
+    I.n_sub = (int)((H.scan_len + JDEC_SUB - 1) / JDEC_SUB);
+    if (I.n_sub < 1) I.n_sub = 1;
+    I.n_blocks = H.mcux * H.mcuy * I.bpm;
+    for (int c = 0; c < 3; ++c) { I.td[c] = H.td[c]; I.ta[c] = H.ta[c]; I.tq[c] = H.tq[c]; }
+    I.pw[0] = H.mcux * H.hs * 8; I.ph[0] = H.mcuy * H.vs * 8;
+    I.pw[1] = I.pw[2] = H.ncomp == 3 ? H.mcux * 8 : 0;
+    I.ph[1] = I.ph[2] = H.ncomp == 3 ? H.mcuy * 8 : 0;
+    I.rgba = items[i].rgba;
+    I.pitch = items[i].pitch;
+    Carve& c = cv[i];
+    c.scan = need; need += up(H.scan_len + 16);
+    c.tab = need; need += up(sizeof(jd::Tables));
+    c.state = need; need += up((size_t)I.n_sub * 16);
+    c.prefix = need; need += up((size_t)I.n_sub * 4);
+    c.coef = need; need += up((size_t)I.n_blocks * 128);
+    for (int k = 0; k < 3; ++k) { c.plane[k] = need; need += up((size_t)I.pw[k] * I.ph[k]); }
+    max_sub = std::max(max_sub, I.n_sub);
+    max_blocks = std::max(max_blocks, I.n_blocks);
+    max_w = std::max(max_w, H.w);
+    max_h = std::max(max_h, H.h);
+  }
+  if (ln.dec_arena_cap < need) {
+    if (ln.dec_arena) {
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+      CUDA_TRY(ctx, cudaFree(ln.dec_arena));
+    }
+    ln.dec_arena = nullptr;
+    ln.dec_arena_cap = 0;
+    if (cudaMalloc(&ln.dec_arena, need) != cudaSuccess)
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG decode buffers allocation failed)");
+    ln.dec_arena_cap = need;
+  }
+  if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+  uint8_t* A = (uint8_t*)ln.dec_arena;
+  B.changed = (uint32_t*)A;
+  for (int i = 0; i < n; ++i) {
+    jd::DecImage& I = B.img[i];
+    const Carve& c = cv[i];
+    const jd::Header& H = items[i].hdr;
+    I.scan = A + c.scan;
+    I.tab = (const jd::Tables*)(A + c.tab);
+    I.state = (uint4*)(A + c.state);
+    I.prefix = (uint32_t*)(A + c.prefix);
+    I.coef = (int16_t*)(A + c.coef);
+    for (int k = 0; k < 3; ++k) I.plane[k] = A + c.plane[k];
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + c.scan, items[i].file + H.scan_off, H.scan_len, cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + c.tab, &H.tab, sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(A + c.coef, 0, (size_t)I.n_blocks * 128, ln.stream));
+  }
+  const dim3 gsub((max_sub + JDEC_THREADS - 1) / JDEC_THREADS, n);
+  jd::jdec_first_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+  int launches = 1, rounds = 0;
+  for (;; ++rounds) {
+    if (rounds > 4096) return fail(ctx, STITCH_E_BAD_IMAGE, "JPEG entropy decoder did not synchronise");
+    CUDA_TRY(ctx, cudaMemsetAsync(B.changed, 0, 4, ln.stream));
+    jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+    ++launches;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, B.changed, 4, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    if (*(volatile uint32_t*)ln.jpeg_info_host == 0) break;
+  }
+  jd::jdec_scan_kernel<<<n, 1024, 0, ln.stream>>>(B);
+  jd::jdec_write_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+  jd::jdec_dc_kernel<<<n, 1024, 0, ln.stream>>>(B);
+  jd::jdec_idct_kernel<<<dim3((max_blocks + 127) / 128, n), 128, 0, ln.stream>>>(B);
+  jd::jdec_colour_kernel<<<dim3((max_w + 31) / 32, (max_h + 7) / 8, n), 256, 0, ln.stream>>>(B);
+  launches += 5;
+  CUDA_TRY(ctx, cudaGetLastError());
+  ctx->launches += launches;
+  return STITCH_OK;
+}
+
+int parse_jpeg(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::jpegdec::Header* H) {
+  const stitch::jpegdec::ParseStatus ps = stitch::jpegdec::parse((const uint8_t*)file, bytes, H);
+  if (ps == stitch::jpegdec::kOk) return STITCH_OK;
+  char buf[96];
+  std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
+                ps == stitch::jpegdec::kUnsupported ? "JPEG variant not supported: baseline Huffman, 4:4:4 / 4:2:2 / 4:2:0 / gray only"
+                : ps == stitch::jpegdec::kNotJpeg ? "not a JPEG file" : "corrupt JPEG headers");
+  return fail(ctx, STITCH_E_BAD_IMAGE, buf);
 }
 
 int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res) {
@@ -198,9 +314,29 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (YUV output buffer missing or too small)");
   }
 
-  // bitmaps (P:1512-1514)
+  // bitmaps (P:1512-1514); a STITCH_MEM_HOST_JPEG image is a FILE the GPU decodes (loadImageFrom, U:27-121)
+  int bw[STITCH_MAX_IMAGES], bh[STITCH_MAX_IMAGES];
+  DecodeItem dec[STITCH_MAX_IMAGES];
+  int n_dec = 0;
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
+    bw[i] = im.bmp_width;
+    bh[i] = im.bmp_height;
+    if (im.mem_kind == STITCH_MEM_HOST_JPEG) {
+      if (!im.data || im.pitch_bytes <= 0) {
+        char buf[64];
+        std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
+        return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+      }
+      DecodeItem& d = dec[n_dec++];
+      d.file = (const uint8_t*)im.data;
+      d.bytes = (size_t)im.pitch_bytes;
+      st = parse_jpeg(ctx, im.data, d.bytes, i, &d.hdr);
+      if (st != STITCH_OK) return st;
+      bw[i] = d.hdr.w;
+      bh[i] = d.hdr.h;
+      continue;
+    }
     if (!im.data || im.bmp_width <= 0 || im.bmp_height <= 0) {
       char buf[64];
       std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -218,11 +354,21 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   const double ss = (L.super_sample != 1.0) ? L.super_sample : 1.0;  // P:1426
 
   // stage inputs
+  int k_dec = 0;
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
     int64_t pitch = im.pitch_bytes ? im.pitch_bytes : (int64_t)im.bmp_width * 4;
     const uint8_t* dptr = nullptr;
-    if (im.mem_kind == STITCH_MEM_DEVICE) {
+    if (im.mem_kind == STITCH_MEM_HOST_JPEG) {
+      const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
+      st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
+      if (st != STITCH_OK) return st;
+      dec[k_dec].rgba = (uint8_t*)ln.in_stage[i];
+      dec[k_dec].pitch = dpitch;
+      ++k_dec;
+      dptr = (const uint8_t*)ln.in_stage[i];
+      pitch = dpitch;
+    } else if (im.mem_kind == STITCH_MEM_DEVICE) {
       dptr = (const uint8_t*)im.data;
     } else {
       // Host bitmap: stage with a 16B-aligned pitch so the streaming kernel's 128-bit loads apply.
@@ -236,7 +382,11 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     }
     P.img[i].data = dptr;
     P.img[i].pitch = pitch;
-    make_placement(L.rects[i], im.desc.orientation, ss, im.bmp_width, im.bmp_height, cw, ch, &P.img[i]);
+    make_placement(L.rects[i], im.desc.orientation, ss, bw[i], bh[i], cw, ch, &P.img[i]);
+  }
+  if (n_dec > 0) {
+    st = decode_batch(ctx, ln, dec, n_dec);
+    if (st != STITCH_OK) return st;
   }
 
   // outputs
@@ -536,6 +686,47 @@ extern "C" int stitch_preview(StitchCtx* ctx, const void* src, int32_t src_mem_k
   if (out_host)
     CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, (size_t)cw * 4, d_out, d_pitch, (size_t)cw * 4, ch, cudaMemcpyDeviceToHost,
                                     ln.stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+  return STITCH_OK;
+}
+
+// loadImageFrom (U:27-121) for one JPEG file: header parse on the host, everything else on the GPU.
+extern "C" int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                                  int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "context is busy");
+  if (!file) return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Lane& ln = ctx->lanes[0];
+  DecodeItem d;
+  d.file = (const uint8_t*)file;
+  d.bytes = bytes;
+  int st = parse_jpeg(ctx, file, bytes, 0, &d.hdr);
+  if (info) {
+    std::memset(info, 0, sizeof(*info));
+    StitchImageInfo probe;
+    if (stitch_probe_image(file, bytes, &probe) == STITCH_OK) *info = probe;
+  }
+  if (st != STITCH_OK) return st;
+  const int w = d.hdr.w, h = d.hdr.h;
+  const int64_t pitch = out_pitch ? out_pitch : (int64_t)w * 4;
+  if (!out_rgba || pitch < (int64_t)w * 4 || (pitch & 3) || out_capacity < pitch * (int64_t)(h - 1) + (int64_t)w * 4)
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (decode output buffer missing or too small)");
+  const bool out_host = out_mem_kind != STITCH_MEM_DEVICE;
+  if (out_host) {
+    const int64_t dpitch = ((int64_t)w * 4 + 15) & ~15LL;
+    st = ensure_stage(ctx, ln, 0, (size_t)(dpitch * h));
+    if (st != STITCH_OK) return st;
+    d.rgba = (uint8_t*)ln.in_stage[0];
+    d.pitch = dpitch;
+  } else {
+    d.rgba = (uint8_t*)out_rgba;
+    d.pitch = pitch;
+  }
+  st = decode_batch(ctx, ln, &d, 1);
+  if (st != STITCH_OK) return st;
+  if (out_host)
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
   return STITCH_OK;
 }

@@ -277,6 +277,16 @@ class StitchContext:
             _raise(st, self.handle)
         return out
 
+    def decode_jpeg(self, file_bytes: bytes) -> np.ndarray:
+        """loadImageFrom (utils/canvas.js:27-121) for a baseline JPEG file: RGBA8 [h, w, 4], decoded on the GPU."""
+        info = get_image_info(file_bytes)
+        out = np.empty((info["height"], info["width"], 4), dtype=np.uint8)
+        buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")
+        st = self.lib.stitch_decode_jpeg(self.handle, buf, len(file_bytes), out.ctypes.data, out.nbytes, 0, L.MEM_HOST, None)
+        if st != L.OK:
+            _raise(st, self.handle)
+        return out
+
     def build_job(self, images: Sequence[Dict[str, Any]], direction: str, mode: Optional[str], gap,
                   profile: L.StitchProfile, output: str, out_device: bool = False, out_rgba_ptr: int = 0,
                   out_yuv_ptr: int = 0, out_rgba_capacity: int = 0, out_yuv_capacity: int = 0, out_jpeg_ptr: int = 0,
@@ -287,7 +297,14 @@ class StitchContext:
         for i, img in enumerate(images):
             arr[i].desc = _desc(img)
             bmp = img.get("bitmap")
-            if isinstance(bmp, DeviceBitmap):
+            if bmp is None and img.get("file") is not None:      # a JPEG FILE: decoded on the GPU (loadImageFrom)
+                data = bytes(img["file"])
+                buf = (C.c_char * max(1, len(data))).from_buffer_copy(data or b"\0")
+                arr[i].data = C.cast(buf, C.c_void_p)
+                arr[i].pitch_bytes = len(data)
+                arr[i].mem_kind = L.MEM_HOST_JPEG
+                keep.append(buf)
+            elif isinstance(bmp, DeviceBitmap):
                 arr[i].data = bmp.ptr
                 arr[i].bmp_width, arr[i].bmp_height = bmp.width, bmp.height
                 arr[i].pitch_bytes = bmp.pitch

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 3
+#define STITCH_ABI_VERSION 4
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -122,7 +122,9 @@ int stitch_ctx_join(StitchCtx* ctx);
 typedef void (*StitchProgressFn)(void* user, int32_t percent);
 int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 
-typedef enum StitchMemKind { STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1 } StitchMemKind;
+/* STITCH_MEM_HOST_JPEG: `data` is a baseline JPEG FILE in host memory and pitch_bytes its length in bytes; the
+ * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
+typedef enum StitchMemKind { STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2 } StitchMemKind;
 typedef enum StitchOutputFlags { STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4 } StitchOutputFlags;
 
 /* A decoded bitmap (what loadImageFrom hands to drawWithOrientation, P:1445-1463,1532):
@@ -201,6 +203,16 @@ const char* stitch_type_name(int32_t type);
 /* The prepared record of P:724-739 from a probe result and the file size.  orientation is 1: the page
  * stores WeChat's orientation STRING, which drawWithOrientation's numeric switch (U:160-199) never matches. */
 int stitch_prepare_record(const StitchImageInfo* info, int64_t file_size, StitchImageDesc* out);
+
+/* ---- decode (loadImageFrom, U:27-121; P:1441-1520) ----
+ * Decodes one baseline JPEG file on the GPU into RGBA8 (alpha 255, EXIF orientation NOT applied -- the page
+ * hands the un-rotated bitmap to drawWithOrientation).  Huffman sequential DCT, 8 bit, gray or YCbCr with
+ * 4:4:4 / 4:2:2 / 4:2:0 sampling, restart markers; integer IDCT, triangle-filter chroma upsampling and
+ * fixed-point colour conversion as in libjpeg's default pipeline.  Other variants (progressive, arithmetic,
+ * CMYK) return STITCH_E_BAD_IMAGE: the page's answer to an undecodable file (P:1508-1513); there is no CPU
+ * fallback.  out_pitch 0 = packed.  `info` (optional) receives the probe result.  Synchronous. */
+int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                       int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
 
 /* ---- preview of the exported image on the page's <canvas> (P:1593-1603) ----
  * createHighResCanvas(node, size.width, size.height) (U:17-24) restores the canvas to floor(size * dpr)

@@ -1,0 +1,135 @@
+"""JPEG decode (utils/canvas.js:27-121 loadImageFrom, index.js:1441-1520).
+
+CPU: the oracle decoder (oracle/jpeg_dec_ref.c) is pinned byte-identical to libjpeg as shipped in PIL.
+GPU: stitch_decode_jpeg and STITCH_MEM_HOST_JPEG job inputs are byte-identical to the oracle decoder.
+"""
+import io
+
+import numpy as np
+import pytest
+from PIL import Image, ImageFile
+
+from oracle import jpeg_c as J
+from tests import util as U
+
+ImageFile.MAXBLOCK = 1 << 24
+
+
+def _picture(w, h, seed=0, noise=20):
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    a = np.stack([128 + 100 * np.sin(x / 17 + y / 29), 128 + 90 * np.cos(x / 23 - y / 13), (x * 3 + y * 5) % 256], -1)
+    a = a + rng.integers(-noise, noise + 1, a.shape)
+    return Image.fromarray(np.clip(a, 0, 255).astype(np.uint8))
+
+
+def _jpeg(w, h, seed=0, gray=False, **kw):
+    im = _picture(w, h, seed)
+    if gray:
+        im = im.convert("L")
+    b = io.BytesIO()
+    im.save(b, "JPEG", **kw)
+    return b.getvalue()
+
+
+def _pil(data):
+    return np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+
+
+SIZES = [(1, 1), (7, 5), (16, 16), (17, 33), (123, 77), (250, 131), (640, 481)]
+
+
+@pytest.mark.parametrize("size", SIZES, ids=[f"{w}x{h}" for w, h in SIZES])
+@pytest.mark.parametrize("subsampling", [0, 1, 2])
+def test_oracle_decoder_equals_libjpeg(size, subsampling):
+    for q, kw in ((50, {}), (90, {"optimize": True}), (100, {})):
+        data = _jpeg(*size, seed=q, quality=q, subsampling=subsampling, **kw)
+        got = J.decode(data)
+        assert (got[..., 3] == 255).all()
+        assert np.array_equal(got[..., :3], _pil(data)), f"{size} ss={subsampling} q={q}"
+
+
+def test_oracle_decoder_restart_markers_gray_and_own_files():
+    for kw in ({"restart_marker_blocks": 3}, {"restart_marker_rows": 1}, {"restart_marker_blocks": 1}):
+        for ss in (0, 2):
+            data = _jpeg(333, 211, quality=92, subsampling=ss, **kw)
+            assert b"\xff\xdd" in data
+            assert np.array_equal(J.decode(data)[..., :3], _pil(data))
+    data = _jpeg(100, 37, gray=True, quality=85)
+    assert np.array_equal(J.decode(data)[..., :3], _pil(data))
+    rng = np.random.default_rng(5)
+    y, cb, cr = (rng.integers(0, 256, s, dtype=np.uint8) for s in ((200, 333), (100, 167), (100, 167)))
+    data = J.encode_i420(y, cb, cr, 90, 8)                       # the product's own export format
+    assert np.array_equal(J.decode(data)[..., :3], _pil(data))
+
+
+def test_oracle_decoder_rejects_progressive():
+    data = _jpeg(64, 64, quality=80, progressive=True)
+    with pytest.raises(ValueError):
+        J.decode(data)
+
+
+# ---------------------------------------------------------------- GPU
+GPU_FILES = [
+    dict(w=1, h=1, quality=90, subsampling=2), dict(w=7, h=5, quality=75, subsampling=0),
+    dict(w=123, h=77, quality=90, subsampling=2), dict(w=250, h=131, quality=50, subsampling=1),
+    dict(w=640, h=481, quality=100, subsampling=2), dict(w=640, h=481, quality=95, subsampling=0, optimize=True),
+    dict(w=333, h=211, quality=92, subsampling=2, restart_marker_blocks=3),
+    dict(w=333, h=211, quality=92, subsampling=0, restart_marker_rows=1),
+    dict(w=100, h=37, quality=85, gray=True),
+    dict(w=2000, h=1500, quality=90, subsampling=2),             # ~ 0.5 MB of entropy data: thousands of subsequences
+    dict(w=1500, h=2000, quality=98, subsampling=1, optimize=True),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("spec", GPU_FILES, ids=[f"{s['w']}x{s['h']}-{i}" for i, s in enumerate(GPU_FILES)])
+def test_gpu_decoder_equals_oracle(spec):
+    from imagestitching_b200 import StitchContext
+    spec = dict(spec)
+    data = _jpeg(spec.pop("w"), spec.pop("h"), seed=3, **spec)
+    want = J.decode(data)
+    ctx = StitchContext(0)
+    got = ctx.decode_jpeg(data)
+    ctx.close()
+    assert got.shape == want.shape
+    assert np.array_equal(got, want), f"{np.count_nonzero(got != want)} bytes differ"
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_full_size_photo():
+    """A 12 MP file as the page's inputs are (BASELINE configs[1] shape)."""
+    from imagestitching_b200 import StitchContext
+    data = _jpeg(4032, 3024, seed=9, quality=90, subsampling=2)
+    want = J.decode(data)
+    ctx = StitchContext(0)
+    got = ctx.decode_jpeg(data)
+    ctx.close()
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_errors():
+    from imagestitching_b200 import StitchContext, StitchError
+    from imagestitching_b200 import _lib as L
+    ctx = StitchContext(0)
+    with pytest.raises(StitchError) as e:
+        ctx.decode_jpeg(_jpeg(64, 64, quality=80, progressive=True))
+    assert e.value.status == L.E_BAD_IMAGE and "解码异常" in e.value.message
+    ctx.close()
+
+
+@pytest.mark.gpu
+def test_job_with_jpeg_files_equals_job_with_decoded_bitmaps():
+    """index.js:1441-1554 end to end: files in -> decode on the GPU -> stitch; same canvas as stitching the
+    oracle-decoded bitmaps."""
+    from imagestitching_b200 import StitchContext, prepare_image
+    dims = [(806, 604), (604, 806), (1210, 908)]
+    files = [_jpeg(w, h, seed=20 + i, quality=92, subsampling=(2, 0, 1)[i]) for i, (w, h) in enumerate(dims)]
+    recs = [prepare_image(f) for f in files]
+    ctx = StitchContext(0)
+    a = ctx.run([dict(r, file=f) for r, f in zip(recs, files)], "vertical", mode="min", gap=3, platform="ios")
+    b = ctx.run([dict(r, bitmap=J.decode(f)) for r, f in zip(recs, files)], "vertical", mode="min", gap=3, platform="ios")
+    ctx.close()
+    assert a.width == b.width and a.height == b.height
+    assert np.array_equal(a.rgba, b.rgba)
