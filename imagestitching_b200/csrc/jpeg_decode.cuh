@@ -42,6 +42,8 @@ struct DecImage {
   uint4* state;               // [n_sub] end state {byte, bit | b << 8 | z << 16 | done << 24, blocks started, -}
   uint32_t* prefix;           // [n_sub] exclusive scan of blocks started
   int16_t* coef;              // [n_blocks][64] scan order, zig-zag order inside a block
+  int32_t* dcsum;             // [3][n_mcu] per-MCU DC sums, then their segmented scan
+  uint2* consumed;            // [blocks of the sync grid] predecessor state each block last started from
   uint8_t* plane[3];          // component planes, MCU-padded
   int32_t pw[3], ph[3];
   uint8_t* rgba;              // output bitmap
@@ -51,6 +53,7 @@ struct DecBatch {
   DecImage img[JDEC_MAX_IMAGES];
   int32_t n;
   uint32_t* changed;          // device flag raised by the sync kernel
+  int32_t round;              // sync round (0 = first)
 };
 
 // ---- Huffman tables in shared memory ----
@@ -329,15 +332,19 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
   const int t = threadIdx.x;
   uint4 mine = live ? I.state[i] : make_uint4(0, 0, 0, 0);
   sh_state[t + 1] = make_uint2(mine.x, mine.y);
-  sh_dirty[t + 1] = 1;   // first iteration: everybody re-decodes from the predecessor's state
+  // first round: everybody re-decodes from the predecessor's state; later rounds: only the chain that
+  // starts at a first thread whose input (the previous block's last end state) has moved since it was used
+  sh_dirty[t + 1] = B.round == 0 ? 1 : 0;
   if (t == 0) {
-    if (i == 0) {
-      sh_state[0] = make_uint2(0u, 0u);          // the scan starts at byte 0, bit 0, block 0, DC
-    } else {
+    uint2 in = make_uint2(0u, 0u);               // the scan starts at byte 0, bit 0, block 0, DC
+    if (i > 0) {
       const uint4 p = I.state[i - 1];
-      sh_state[0] = make_uint2(p.x, p.y);
+      in = make_uint2(p.x, p.y);
     }
-    sh_dirty[0] = 1;
+    sh_state[0] = in;
+    const uint2 was = I.consumed[blockIdx.x];
+    sh_dirty[0] = (B.round == 0 || was.x != in.x || was.y != in.y) ? 1 : 0;
+    I.consumed[blockIdx.x] = in;
   }
   __syncthreads();
   bool changed_ever = false, settled = false;
@@ -422,100 +429,90 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_write_kernel(const __grid_c
   decode_range<true>(I, T, s, (i + 1) * JDEC_SUB, &started, (int64_t)I.prefix[i]);
 }
 
-// D5: DC differences -> DC values.  One block per image walks the MCUs in chunks of 1024 with a running
-// carry per component; a restart interval boundary (MCU index multiple of ri) zeroes the predictors.
-__global__ void __launch_bounds__(1024) jdec_dc_kernel(const __grid_constant__ DecBatch B) {
-  __shared__ int wsum[3][32];
+// D5: DC differences -> DC values, in three steps: (a) per-MCU sums of the differences per component,
+// (b) one block per image: segmented inclusive scan of those sums over the MCUs (a restart interval
+// boundary -- MCU index multiple of ri -- zeroes the predictors), in place, (c) per MCU: predictor entering
+// it = scanned value minus its own sum; rewrite the DC slots of its blocks.
+__global__ void __launch_bounds__(256) jdec_dc_sum_kernel(const __grid_constant__ DecBatch B) {
+  const DecImage& I = B.img[blockIdx.y];
+  const int m = blockIdx.x * 256 + threadIdx.x, n_mcu = I.mcux * I.mcuy, ny = I.hs * I.vs;
+  if (m >= n_mcu) return;
+  const int16_t* blk = I.coef + (int64_t)m * I.bpm * 64;
+  int s0 = 0;
+  for (int b = 0; b < ny; ++b) s0 += blk[b * 64];
+  I.dcsum[m] = s0;
+  if (I.ncomp == 3) {
+    I.dcsum[n_mcu + m] = blk[ny * 64];
+    I.dcsum[2 * n_mcu + m] = blk[(ny + 1) * 64];
+  }
+}
+
+__global__ void __launch_bounds__(1024) jdec_dc_scan_kernel(const __grid_constant__ DecBatch B) {
+  __shared__ int wsum[32];
   __shared__ int wflag[32];
-  __shared__ int carry[3];
+  __shared__ int carry;
   const DecImage& I = B.img[blockIdx.x];
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-  const int n_mcu = I.mcux * I.mcuy, ny = I.hs * I.vs;
-  if (t < 3) carry[t] = 0;
+  const int n_mcu = I.mcux * I.mcuy;
+  int* v = I.dcsum + (int64_t)blockIdx.y * n_mcu;     // blockIdx.y = component
+  if ((int)blockIdx.y >= I.ncomp) return;
+  if (t == 0) carry = 0;
   __syncthreads();
   for (int base = 0; base < n_mcu; base += 1024) {
     const int m = base + t;
     const bool live = m < n_mcu;
-    int sum[3] = {0, 0, 0};
-    int16_t* blk = I.coef + (int64_t)m * I.bpm * 64;
-    if (live) {
-      for (int b = 0; b < ny; ++b) sum[0] += blk[b * 64];
-      if (I.ncomp == 3) { sum[1] = blk[ny * 64]; sum[2] = blk[(ny + 1) * 64]; }
-    }
-    // segmented inclusive scan over MCUs: flag = this MCU starts a restart interval
-    int flag = (live && I.ri > 0 && (m % I.ri) == 0) ? 1 : 0;
-    int x[3] = {sum[0], sum[1], sum[2]}, f = flag;
+    const int own = live ? v[m] : 0;
+    int x = own, f = (live && I.ri > 0 && (m % I.ri) == 0) ? 1 : 0;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const int f2 = __shfl_up_sync(0xffffffffu, f, d);
-      int y[3];
-#pragma unroll
-      for (int c = 0; c < 3; ++c) y[c] = __shfl_up_sync(0xffffffffu, x[c], d);
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
       if (lane >= d) {
-        if (!f) {
-#pragma unroll
-          for (int c = 0; c < 3; ++c) x[c] += y[c];
-        }
+        if (!f) x += y;
         f |= f2;
       }
     }
-    if (lane == 31) {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) wsum[c][w] = x[c];
-      wflag[w] = f;
-    }
+    if (lane == 31) { wsum[w] = x; wflag[w] = f; }
     __syncthreads();
     if (w == 0) {
-      int xs[3] = {wsum[0][lane], wsum[1][lane], wsum[2][lane]}, fs = wflag[lane];
+      int xs = wsum[lane], fs = wflag[lane];
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         const int f2 = __shfl_up_sync(0xffffffffu, fs, d);
-        int y[3];
-#pragma unroll
-        for (int c = 0; c < 3; ++c) y[c] = __shfl_up_sync(0xffffffffu, xs[c], d);
+        const int y = __shfl_up_sync(0xffffffffu, xs, d);
         if (lane >= d) {
-          if (!fs) {
-#pragma unroll
-            for (int c = 0; c < 3; ++c) xs[c] += y[c];
-          }
+          if (!fs) xs += y;
           fs |= f2;
         }
       }
-#pragma unroll
-      for (int c = 0; c < 3; ++c) wsum[c][lane] = xs[c];
+      wsum[lane] = xs;
       wflag[lane] = fs;
     }
     __syncthreads();
-    // prefix of everything before this MCU's warp + chunk carry, unless a flag intervened
-    int pre[3];
-    {
-      const bool cut_w = f != 0;                        // a restart inside my warp at or before me
-      const bool cut_b = w > 0 && wflag[w - 1] != 0;    // a restart in an earlier warp of this chunk
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        int v = x[c];                                   // inclusive within the warp (segmented)
-        if (!cut_w) {
-          if (w > 0) v += wsum[c][w - 1];
-          if (!cut_b) v += carry[c];
-        }
-        pre[c] = v - sum[c];                            // exclusive: predictor entering this MCU
-      }
+    int r = x;                                          // segmented inclusive value
+    if (!f) {                                           // no restart in my warp at or before me
+      if (w > 0) r += wsum[w - 1];
+      if (!(w > 0 && wflag[w - 1])) r += carry;         // nor in the earlier warps of this chunk
     }
-    if (live) {
-      if (flag) { pre[0] = pre[1] = pre[2] = 0; }
-      int p0 = pre[0];
-      for (int b = 0; b < ny; ++b) { p0 += blk[b * 64]; blk[b * 64] = (int16_t)p0; }
-      if (I.ncomp == 3) {
-        blk[ny * 64] = (int16_t)(pre[1] + sum[1]);
-        blk[(ny + 1) * 64] = (int16_t)(pre[2] + sum[2]);
-      }
-    }
+    if (live) v[m] = r;
     __syncthreads();
-    if (t == 1023) {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) carry[c] = pre[c] + sum[c];
-    }
+    if (t == 1023) carry = r;
     __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256) jdec_dc_apply_kernel(const __grid_constant__ DecBatch B) {
+  const DecImage& I = B.img[blockIdx.y];
+  const int m = blockIdx.x * 256 + threadIdx.x, n_mcu = I.mcux * I.mcuy, ny = I.hs * I.vs;
+  if (m >= n_mcu) return;
+  int16_t* blk = I.coef + (int64_t)m * I.bpm * 64;
+  int s0 = 0;
+  for (int b = 0; b < ny; ++b) s0 += blk[b * 64];
+  int p = I.dcsum[m] - s0;                              // luma predictor entering this MCU
+  for (int b = 0; b < ny; ++b) { p += blk[b * 64]; blk[b * 64] = (int16_t)p; }
+  if (I.ncomp == 3) {
+    blk[ny * 64] = (int16_t)I.dcsum[n_mcu + m];
+    blk[(ny + 1) * 64] = (int16_t)I.dcsum[2 * n_mcu + m];
   }
 }
 
@@ -621,53 +618,86 @@ __global__ void __launch_bounds__(128) jdec_idct_kernel(const __grid_constant__ 
 }
 
 // ---- D7: chroma upsampling (triangle filter, as libjpeg's "fancy" upsampling) + YCbCr -> RGB ----
+// One thread = 4 horizontally adjacent pixels (x0 = 4k): one 32-bit luma load, the chroma samples i-1 .. i+2
+// of the two rows involved, one 16-byte store.
+__device__ __forceinline__ uint32_t ycc_to_rgba(int yy, int cb, int cr) {
+  const int R = min(max(yy + ((91881 * cr + 32768) >> 16), 0), 255);
+  const int G = min(max(yy + ((-22554 * cb + 32768 - 46802 * cr) >> 16), 0), 255);
+  const int Bc = min(max(yy + ((116130 * cb + 32768) >> 16), 0), 255);
+  return (uint32_t)R | (uint32_t)G << 8 | (uint32_t)Bc << 16 | 0xff000000u;
+}
+
 __global__ void __launch_bounds__(256) jdec_colour_kernel(const __grid_constant__ DecBatch B) {
   const DecImage& I = B.img[blockIdx.z];
-  const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int x0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * 4;
   const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
-  if (x >= I.w || y >= I.h) return;
-  const int yy = I.plane[0][(int64_t)y * I.pw[0] + x];
-  uint32_t px;
+  if (x0 >= I.w || y >= I.h) return;
+  const uint32_t y4 = *reinterpret_cast<const uint32_t*>(I.plane[0] + (int64_t)y * I.pw[0] + x0);   // planes are padded to 8
+  uint32_t px[4];
   if (I.ncomp == 1) {
-    px = (uint32_t)yy * 0x010101u | 0xff000000u;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) px[k] = ((y4 >> (8 * k)) & 255u) * 0x010101u | 0xff000000u;
   } else {
     const int cw = (I.w + I.hs - 1) / I.hs, chh = (I.h + I.vs - 1) / I.vs;
     const bool fancy = I.hs == 2 && cw > 2;
-    int cv[2];
+    int cv[2][4];
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       const uint8_t* P = I.plane[c + 1];
       const int stride = I.pw[c + 1];
-      int val;
       if (I.hs == 1) {
-        val = P[(int64_t)y * stride + x];
-      } else if (I.vs == 1) {
-        const uint8_t* r0 = P + (int64_t)y * stride;
-        const int i = x >> 1;
-        if (!fancy) val = r0[i];
-        else if ((x & 1) == 0) val = i == 0 ? r0[0] : (r0[i] * 3 + r0[i - 1] + 1) >> 2;
-        else val = i == cw - 1 ? r0[i] : (r0[i] * 3 + r0[i + 1] + 2) >> 2;
+        const uint32_t v4 = *reinterpret_cast<const uint32_t*>(P + (int64_t)y * stride + x0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) cv[c][k] = (int)((v4 >> (8 * k)) & 255u);
       } else {
-        const int r = y >> 1, i = x >> 1;
-        if (!fancy) {
-          val = P[(int64_t)r * stride + i];
-        } else {
+        const int i0 = x0 >> 1;                         // chroma samples i0, i0 + 1 cover the 4 pixels
+        const int r = I.vs == 2 ? (y >> 1) : y;
+        const uint8_t* r0 = P + (int64_t)r * stride;
+        // horizontal neighbours i0 - 1 .. i0 + 2, clamped into the plane (the formulas below never use a clamped one)
+        const int il = max(i0 - 1, 0), ir = min(i0 + 2, stride - 1);
+        int s[4];                                       // column sums: 3 * near row + far row (h2v2) or the sample (h2v1)
+        if (I.vs == 2 && fancy) {
           const int rn = min(max((y & 1) ? r + 1 : r - 1, 0), chh - 1);
-          const uint8_t* r0 = P + (int64_t)r * stride;
           const uint8_t* r1 = P + (int64_t)rn * stride;
-          const int cur = r0[i] * 3 + r1[i];
-          if ((x & 1) == 0) val = i == 0 ? (cur * 4 + 8) >> 4 : (cur * 3 + (r0[i - 1] * 3 + r1[i - 1]) + 8) >> 4;
-          else val = i == cw - 1 ? (cur * 4 + 7) >> 4 : (cur * 3 + (r0[i + 1] * 3 + r1[i + 1]) + 7) >> 4;
+          s[0] = r0[il] * 3 + r1[il];
+          s[1] = r0[i0] * 3 + r1[i0];
+          s[2] = r0[i0 + 1] * 3 + r1[i0 + 1];
+          s[3] = r0[ir] * 3 + r1[ir];
+        } else {
+          s[0] = r0[il];
+          s[1] = r0[i0];
+          s[2] = r0[i0 + 1];
+          s[3] = r0[ir];
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {                   // chroma sample i = i0 + j -> pixels 2j, 2j + 1
+          const int i = i0 + j, cur = s[1 + j], left = s[j], right = s[2 + j];
+          int even, odd;
+          if (!fancy) {
+            even = odd = cur;
+          } else if (I.vs == 2) {
+            even = i == 0 ? (cur * 4 + 8) >> 4 : (cur * 3 + left + 8) >> 4;
+            odd = i == cw - 1 ? (cur * 4 + 7) >> 4 : (cur * 3 + right + 7) >> 4;
+          } else {
+            even = i == 0 ? cur : (cur * 3 + left + 1) >> 2;
+            odd = i == cw - 1 ? cur : (cur * 3 + right + 2) >> 2;
+          }
+          cv[c][2 * j] = even;
+          cv[c][2 * j + 1] = odd;
         }
       }
-      cv[c] = val - 128;
     }
-    const int R = min(max(yy + ((91881 * cv[1] + 32768) >> 16), 0), 255);
-    const int G = min(max(yy + ((-22554 * cv[0] + 32768 - 46802 * cv[1]) >> 16), 0), 255);
-    const int Bc = min(max(yy + ((116130 * cv[0] + 32768) >> 16), 0), 255);
-    px = (uint32_t)R | (uint32_t)G << 8 | (uint32_t)Bc << 16 | 0xff000000u;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) px[k] = ycc_to_rgba((int)((y4 >> (8 * k)) & 255u), cv[0][k] - 128, cv[1][k] - 128);
   }
-  *reinterpret_cast<uint32_t*>(I.rgba + (int64_t)y * I.pitch + (int64_t)x * 4) = px;
+  uint8_t* o = I.rgba + (int64_t)y * I.pitch + (int64_t)x0 * 4;
+  if (x0 + 3 < I.w && (((uintptr_t)o) & 15) == 0) {
+    *reinterpret_cast<uint4*>(o) = make_uint4(px[0], px[1], px[2], px[3]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      if (x0 + k < I.w) reinterpret_cast<uint32_t*>(o)[k] = px[k];
+  }
 }
 
 }  // namespace jpegdec

@@ -176,7 +176,8 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
   std::memset(&B, 0, sizeof B);
   B.n = n;
   size_t need = 256;  // the `changed` flag
-  struct Carve { size_t scan, tab, state, prefix, coef, plane[3]; } cv[JDEC_MAX_IMAGES];
+  struct Carve { size_t scan, tab, state, prefix, coef, plane[3], dcsum, consumed; } cv[JDEC_MAX_IMAGES];
+  int max_mcu = 0;
   int max_sub = 0, max_blocks = 0, max_w = 0, max_h = 0;
   for (int i = 0; i < n; ++i) {
     const jd::Header& H = items[i].hdr;
@@ -200,7 +201,10 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
     c.state = need; need += up((size_t)I.n_sub * 16);
     c.prefix = need; need += up((size_t)I.n_sub * 4);
     c.coef = need; need += up((size_t)I.n_blocks * 128);
-    for (int k = 0; k < 3; ++k) { c.plane[k] = need; need += up((size_t)I.pw[k] * I.ph[k]); }
+    for (int k = 0; k < 3; ++k) { c.plane[k] = need; need += up((size_t)I.pw[k] * I.ph[k] + 16); }
+    c.dcsum = need; need += up((size_t)H.mcux * H.mcuy * 3 * 4);
+    c.consumed = need; need += up((size_t)((I.n_sub + JDEC_THREADS - 1) / JDEC_THREADS) * 8);
+    max_mcu = std::max(max_mcu, H.mcux * H.mcuy);
     max_sub = std::max(max_sub, I.n_sub);
     max_blocks = std::max(max_blocks, I.n_blocks);
     max_w = std::max(max_w, H.w);
@@ -230,6 +234,8 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
     I.prefix = (uint32_t*)(A + c.prefix);
     I.coef = (int16_t*)(A + c.coef);
     for (int k = 0; k < 3; ++k) I.plane[k] = A + c.plane[k];
+    I.dcsum = (int32_t*)(A + c.dcsum);
+    I.consumed = (uint2*)(A + c.consumed);
     CUDA_TRY(ctx, cudaMemcpyAsync(A + c.scan, items[i].file + H.scan_off, H.scan_len, cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemcpyAsync(A + c.tab, &H.tab, sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemsetAsync(A + c.coef, 0, (size_t)I.n_blocks * 128, ln.stream));
@@ -240,6 +246,7 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
   for (;; ++rounds) {
     if (rounds > 4096) return fail(ctx, STITCH_E_BAD_IMAGE, "JPEG entropy decoder did not synchronise");
     CUDA_TRY(ctx, cudaMemsetAsync(B.changed, 0, 4, ln.stream));
+    B.round = rounds;
     jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
     ++launches;
     CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, B.changed, 4, cudaMemcpyDeviceToHost, ln.stream));
@@ -248,10 +255,12 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
   }
   jd::jdec_scan_kernel<<<n, 1024, 0, ln.stream>>>(B);
   jd::jdec_write_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
-  jd::jdec_dc_kernel<<<n, 1024, 0, ln.stream>>>(B);
+  jd::jdec_dc_sum_kernel<<<dim3((max_mcu + 255) / 256, n), 256, 0, ln.stream>>>(B);
+  jd::jdec_dc_scan_kernel<<<dim3(n, 3), 1024, 0, ln.stream>>>(B);
+  jd::jdec_dc_apply_kernel<<<dim3((max_mcu + 255) / 256, n), 256, 0, ln.stream>>>(B);
   jd::jdec_idct_kernel<<<dim3((max_blocks + 127) / 128, n), 128, 0, ln.stream>>>(B);
-  jd::jdec_colour_kernel<<<dim3((max_w + 31) / 32, (max_h + 7) / 8, n), 256, 0, ln.stream>>>(B);
-  launches += 5;
+  jd::jdec_colour_kernel<<<dim3((max_w + 127) / 128, (max_h + 7) / 8, n), 256, 0, ln.stream>>>(B);
+  launches += 7;
   CUDA_TRY(ctx, cudaGetLastError());
   ctx->launches += launches;
   return STITCH_OK;

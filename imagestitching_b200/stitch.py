@@ -298,12 +298,11 @@ class StitchContext:
             arr[i].desc = _desc(img)
             bmp = img.get("bitmap")
             if bmp is None and img.get("file") is not None:      # a JPEG FILE: decoded on the GPU (loadImageFrom)
-                data = bytes(img["file"])
-                buf = (C.c_char * max(1, len(data))).from_buffer_copy(data or b"\0")
-                arr[i].data = C.cast(buf, C.c_void_p)
+                data = img["file"] if isinstance(img["file"], bytes) else bytes(img["file"])
+                arr[i].data = C.cast(C.c_char_p(data), C.c_void_p)      # no copy: `data` is kept alive below
                 arr[i].pitch_bytes = len(data)
                 arr[i].mem_kind = L.MEM_HOST_JPEG
-                keep.append(buf)
+                keep.append(data)
             elif isinstance(bmp, DeviceBitmap):
                 arr[i].data = bmp.ptr
                 arr[i].bmp_width, arr[i].bmp_height = bmp.width, bmp.height
