@@ -112,6 +112,20 @@ __device__ __forceinline__ void rd_start(Reader& r, uint32_t byte, int bit) {
   (void)bit;
 }
 __device__ __forceinline__ void rd_fill(Reader& r) {
+  if (r.cnt > 32) return;                        // a symbol needs at most 16 + 11 bits
+  if (!r.mark && r.pos + 8 <= r.n) {
+    // fast path: four raw bytes at once (two aligned words, big-endian, funnel-shifted) when none is 0xFF
+    const uint32_t* p32 = reinterpret_cast<const uint32_t*>(r.p);
+    const uint32_t w0 = __byte_perm(p32[r.pos >> 2], 0, 0x0123), w1 = __byte_perm(p32[(r.pos >> 2) + 1], 0, 0x0123);
+    const uint32_t v = __funnelshift_l(w1, w0, 8 * (r.pos & 3));
+    const uint32_t t = ~v;
+    if (((t - 0x01010101u) & ~t & 0x80808080u) == 0) {
+      r.acc |= (uint64_t)v << (32 - r.cnt);
+      r.cnt += 32;
+      r.pos += 4;
+      return;
+    }
+  }
   while (r.cnt <= 56) {
     uint32_t v = 0;
     if (!r.mark) {
