@@ -146,3 +146,16 @@ export function computeLayout(images: ImageRecord[], direction: Direction, modeI
            superSample: ss, canvasW: cw, canvasH: ch, scaledGap, rects, natural: nat,
            progress: progressSequence(images.length) };
 }
+
+/** Preview geometry: createHighResCanvas (utils/canvas.js:17-24) + the fit-scale of index.js:1599-1603.
+ *  Twin of stitch_preview_layout in libstitch.so. */
+export interface PreviewLayout {
+  canvasW: number; canvasH: number; scaleFit: number; pvW: number; pvH: number; dx: number; dy: number; dpr: number;
+}
+export function previewLayout(exportW: number, exportH: number, viewW: number, viewH: number, pixelRatio?: number): PreviewLayout {
+  const dpr = pixelRatio || 1;                                                    // canvas.js:6,11
+  const scaleFit = Math.min(viewW / exportW, viewH / exportH);                    // :1600
+  const pvW = Math.round(exportW * scaleFit), pvH = Math.round(exportH * scaleFit); // :1601-1602
+  return { canvasW: Math.floor(viewW * dpr), canvasH: Math.floor(viewH * dpr), scaleFit, pvW, pvH,
+           dx: (viewW - pvW) / 2, dy: (viewH - pvH) / 2, dpr };                     // canvas.js:19-20, :1603
+}

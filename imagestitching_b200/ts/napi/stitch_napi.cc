@@ -147,10 +147,13 @@ napi_value Run(napi_env env, napi_callback_info info) {
     s.bmp_height = get_i32(env, im, "bmpHeight");
     s.pitch_bytes = get_i32(env, im, "pitchBytes");
     s.mem_kind = STITCH_MEM_HOST;
-    napi_get_named_property(env, im, "data", &data);
+    bool has_file = false;
+    napi_has_named_property(env, im, "file", &has_file);
+    napi_get_named_property(env, im, has_file ? "file" : "data", &data);
     napi_typedarray_type tt; size_t len = 0; void* ptr = nullptr; napi_value ab; size_t off = 0;
     if (napi_get_typedarray_info(env, data, &tt, &len, &ptr, &ab, &off) == napi_ok) {
       s.data = ptr;
+      if (has_file) { s.mem_kind = STITCH_MEM_HOST_JPEG; s.pitch_bytes = (int64_t)len; }   // the FILE: decoded on the GPU
       napi_ref ref; napi_create_reference(env, data, 1, &ref); d->keep.push_back(ref);
     }
   }
@@ -195,13 +198,61 @@ napi_value Run(napi_env env, napi_callback_info info) {
   return promise;
 }
 
+// probe(file) -> {width, height, type, orientation, orientationExif}   (stitch_probe_image; synchronous, CPU only)
+napi_value Probe(napi_env env, napi_callback_info info) {
+  size_t argc = 1; napi_value argv[1];
+  napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+  napi_typedarray_type tt; size_t len = 0; void* ptr = nullptr; napi_value ab; size_t off = 0;
+  if (argc < 1 || napi_get_typedarray_info(env, argv[0], &tt, &len, &ptr, &ab, &off) != napi_ok) {
+    napi_throw_type_error(env, nullptr, "probe(file: Uint8Array)");
+    return nullptr;
+  }
+  StitchImageInfo ii;
+  const int st = stitch_probe_image(ptr, len, &ii);
+  if (st != STITCH_OK) { napi_throw_error(env, nullptr, stitch_strerror(st)); return nullptr; }
+  napi_value out, v;
+  napi_create_object(env, &out);
+  napi_create_int32(env, ii.width, &v); napi_set_named_property(env, out, "width", v);
+  napi_create_int32(env, ii.height, &v); napi_set_named_property(env, out, "height", v);
+  napi_create_int32(env, ii.orientation_exif, &v); napi_set_named_property(env, out, "orientationExif", v);
+  napi_create_string_utf8(env, stitch_type_name(ii.type), NAPI_AUTO_LENGTH, &v); napi_set_named_property(env, out, "type", v);
+  napi_create_string_utf8(env, stitch_orientation_name(ii.orientation_exif), NAPI_AUTO_LENGTH, &v);
+  napi_set_named_property(env, out, "orientation", v);
+  return out;
+}
+
+// preview(ctx, rgba, exportW, exportH, viewW, viewH, dpr) -> Uint8Array   (stitch_preview; synchronous)
+napi_value Preview(napi_env env, napi_callback_info info) {
+  size_t argc = 7; napi_value argv[7];
+  napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+  void* p = nullptr;
+  napi_get_value_external(env, argv[0], &p);
+  napi_typedarray_type tt; size_t len = 0; void* src = nullptr; napi_value ab; size_t off = 0;
+  napi_get_typedarray_info(env, argv[1], &tt, &len, &src, &ab, &off);
+  int32_t ew = 0, eh = 0; double vw = 0, vh = 0, dpr = 1;
+  napi_get_value_int32(env, argv[2], &ew); napi_get_value_int32(env, argv[3], &eh);
+  napi_get_value_double(env, argv[4], &vw); napi_get_value_double(env, argv[5], &vh); napi_get_value_double(env, argv[6], &dpr);
+  StitchPreviewLayout pl;
+  int st = stitch_preview_layout(ew, eh, vw, vh, dpr, &pl);
+  if (st != STITCH_OK || (size_t)ew * eh * 4 > len) { napi_throw_error(env, nullptr, stitch_strerror(st ? st : STITCH_E_BAD_ARG)); return nullptr; }
+  const size_t bytes = (size_t)pl.canvas_w * pl.canvas_h * 4;
+  void* dst; napi_value out_ab, out;
+  napi_create_arraybuffer(env, bytes, &dst, &out_ab);
+  st = stitch_preview(static_cast<StitchCtx*>(p), src, STITCH_MEM_HOST, ew, eh, 0, vw, vh, dpr, dst, (int64_t)bytes, STITCH_MEM_HOST, &pl);
+  if (st != STITCH_OK) { napi_throw_error(env, nullptr, stitch_last_error(static_cast<StitchCtx*>(p))); return nullptr; }
+  napi_create_typedarray(env, napi_uint8_array, bytes, out_ab, 0, &out);
+  return out;
+}
+
 napi_value Init(napi_env env, napi_value exports) {
   napi_property_descriptor props[] = {
       {"createContext", nullptr, CreateContext, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"destroyContext", nullptr, DestroyContext, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"run", nullptr, Run, nullptr, nullptr, nullptr, napi_default, nullptr},
+      {"probe", nullptr, Probe, nullptr, nullptr, nullptr, napi_default, nullptr},
+      {"preview", nullptr, Preview, nullptr, nullptr, nullptr, napi_default, nullptr},
   };
-  napi_define_properties(env, exports, 3, props);
+  napi_define_properties(env, exports, 5, props);
   return exports;
 }
 

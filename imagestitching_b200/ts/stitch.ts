@@ -11,12 +11,16 @@ const native = require('./build/Release/stitch_napi.node') as {
   createContext(device: number): unknown;
   destroyContext(ctx: unknown): void;
   run(ctx: unknown, job: NativeJob, onProgress?: (pct: number) => void): Promise<NativeResult>;
+  probe(file: Uint8Array): { width: number; height: number; type: string; orientation: string; orientationExif: number };
+  preview(ctx: unknown, rgba: Uint8Array, exportW: number, exportH: number, viewW: number, viewH: number, dpr: number): Uint8Array;
 };
 
 export interface StitchImage extends ImageRecord {
-  /** decoded RGBA8 bitmap, straight alpha (what loadImageFrom hands to drawWithOrientation) */
-  data: Uint8Array;
-  bmpWidth: number; bmpHeight: number; pitchBytes?: number;
+  /** decoded RGBA8 bitmap, straight alpha (what loadImageFrom hands to drawWithOrientation) ... */
+  data?: Uint8Array;
+  bmpWidth?: number; bmpHeight?: number; pitchBytes?: number;
+  /** ... or the baseline JPEG FILE itself: decoded on the GPU (STITCH_MEM_HOST_JPEG, loadImageFrom canvas.js:27-121) */
+  file?: Uint8Array;
 }
 export interface StitchOptions {
   gap?: number; mode?: 'min' | 'max' | 'original' | string;
@@ -41,7 +45,18 @@ export class StitchError extends Error {
   constructor(public status: number, message: string) { super(message); }
 }
 
-export { computeLayout, fallbackProfile };
+export { computeLayout, fallbackProfile, previewLayout } from './layout';
+
+/** wx.getImageInfo for an in-memory file (stitch_probe_image): width, height, type and WeChat's orientation string. */
+export function getImageInfo(file: Uint8Array): { width: number; height: number; type: string; orientation: string; orientationExif: number } {
+  return native.probe(file);
+}
+/** The preview draw of index.js:1593-1603 (stitch_preview): straight-alpha RGBA8 of the fit-scaled export. */
+export function preview(rgba: Uint8Array, exportW: number, exportH: number, viewW: number, viewH: number, pixelRatio = 1, device = 0): Uint8Array {
+  let ctx = contexts.get(device);
+  if (!ctx) { ctx = native.createContext(device); contexts.set(device, ctx); }
+  return native.preview(ctx, rgba, exportW, exportH, viewW, viewH, pixelRatio);
+}
 
 /** onStitch(): resolves to undefined for an empty list (index.js:1189), rejects with the reference's messages. */
 export async function stitch(images: StitchImage[], direction: Direction, opts: StitchOptions = {}): Promise<StitchResult | undefined> {
