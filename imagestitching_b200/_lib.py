@@ -16,7 +16,7 @@ VERTICAL, HORIZONTAL = 0, 1
 MODE_MIN, MODE_MAX, MODE_ORIGINAL, MODE_OTHER = 0, 1, 2, 3
 IOS, ANDROID, OTHER = 0, 1, 2
 MEM_HOST, MEM_DEVICE, MEM_HOST_JPEG = 0, 1, 2
-OUT_RGBA, OUT_YUV420, OUT_JPEG = 1, 2, 4
+OUT_RGBA, OUT_YUV420, OUT_JPEG, OUT_PNG = 1, 2, 4, 8
 
 
 class StitchProfile(C.Structure):
@@ -54,13 +54,14 @@ class StitchJob(C.Structure):
                 ("output_flags", C.c_int32), ("out_mem_kind", C.c_int32), ("out_rgba", C.c_void_p),
                 ("out_rgba_pitch", C.c_int64), ("out_yuv", C.c_void_p), ("out_capacity_rgba", C.c_int64),
                 ("out_capacity_yuv", C.c_int64), ("out_jpeg", C.c_void_p), ("out_capacity_jpeg", C.c_int64),
-                ("jpeg_quality", C.c_int32), ("jpeg_restart_interval", C.c_int32)]
+                ("jpeg_quality", C.c_int32), ("jpeg_restart_interval", C.c_int32),
+                ("out_png", C.c_void_p), ("out_capacity_png", C.c_int64)]
 
 
 class StitchResult(C.Structure):
     _fields_ = [("layout", StitchLayout), ("canvas_w", C.c_int32), ("canvas_h", C.c_int32), ("rgba_bytes", C.c_int64),
                 ("yuv_bytes", C.c_int64), ("kernel_launches", C.c_int32), ("path_info", C.c_int32),
-                ("jpeg_bytes", C.c_int64)]
+                ("jpeg_bytes", C.c_int64), ("png_bytes", C.c_int64)]
 
 
 class StitchImageInfo(C.Structure):
@@ -87,6 +88,7 @@ SIGNATURES = {
     "stitch_set_progress_cb": (C.c_int, [C.c_void_p, PROGRESS_FN, C.c_void_p]),
     "stitch_output_size": (C.c_int, [C.POINTER(StitchLayout), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "stitch_jpeg_capacity": (C.c_int64, [C.POINTER(StitchLayout), C.c_int32]),
+    "stitch_png_capacity": (C.c_int64, [C.POINTER(StitchLayout)]),
     "stitch_run": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult)]),
     "stitch_submit": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult), C.POINTER(C.c_uint64)]),
     "stitch_wait": (C.c_int, [C.c_void_p, C.c_uint64]),

@@ -252,6 +252,13 @@ extern "C" int64_t stitch_jpeg_capacity(const StitchLayout* layout, int32_t rest
   return 1024 + mcus * 6 * 432 + segs * 4 + 2;
 }
 
+extern "C" int64_t stitch_png_capacity(const StitchLayout* layout) {
+  if (!layout) return 0;
+  const int64_t w = (int64_t)layout->canvas_w, h = (int64_t)layout->canvas_h;
+  const int64_t bands = (h + 7) / 8;
+  return 33 + 12 + bands * (12 + 160 + 8) + (h * (w * 4 + 1) * 15 + 7) / 8 + 64;
+}
+
 // Preview geometry: U:17-24 (createHighResCanvas) + P:1599-1603.
 extern "C" int stitch_preview_layout(int32_t export_w, int32_t export_h, double view_w, double view_h, double dpr,
                                      StitchPreviewLayout* out) {

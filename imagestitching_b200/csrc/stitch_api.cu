@@ -22,6 +22,7 @@
 #include "launch.cuh"
 #include "jpeg_kernels.cuh"
 #include "jpeg_decode.cuh"
+#include "png_kernels.cuh"
 #include "synth.cuh"
 
 struct PendingJob {
@@ -50,6 +51,9 @@ struct Lane {
   // JPEG decode: grow-only arena (scan bytes, tables, subsequence states, coefficients, component planes)
   void* dec_arena = nullptr;
   size_t dec_arena_cap = 0;
+  // PNG export: grow-only arena (RGBA canvas when the caller did not ask for it, code tables, coded bands, file)
+  void* png_arena = nullptr;
+  size_t png_arena_cap = 0;
 };
 
 struct StitchCtx {
@@ -150,6 +154,7 @@ void free_lane(Lane& ln) {
   if (ln.out_stage) cudaFree(ln.out_stage);
   if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
   if (ln.dec_arena) cudaFree(ln.dec_arena);
+  if (ln.png_arena) cudaFree(ln.png_arena);
   if (ln.jpeg_info_host) cudaFreeHost(ln.jpeg_info_host);
   stitch::free_scratch(ln.scratch);
   if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
@@ -307,7 +312,9 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
 
   int flags = job->output_flags ? job->output_flags : STITCH_OUT_RGBA;
   const bool want_rgba = (flags & STITCH_OUT_RGBA) != 0, want_yuv = (flags & STITCH_OUT_YUV420) != 0;
-  const bool want_jpeg = (flags & STITCH_OUT_JPEG) != 0;
+  const bool want_jpeg = (flags & STITCH_OUT_JPEG) != 0, want_png = (flags & STITCH_OUT_PNG) != 0;
+  if (want_png && (!job->out_png || job->out_capacity_png < 128))
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG output buffer missing or too small)");
   if (want_jpeg && (!job->out_jpeg || job->out_capacity_jpeg < 1024))
     return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer missing or too small)");
   if (want_jpeg && (cw > 65535 || ch > 65535)) return fail(ctx, STITCH_E_BAD_ARG, "JPEG export: canvas side above 65535");
@@ -468,7 +475,55 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     j_info = (uint64_t*)a; a += b_info;
     j_file = out_host ? a : (uint8_t*)job->out_jpeg;
   }
+  // PNG export: carve the lane's arena; the encoder reads the RGBA canvas of this launch (the caller's, or
+  // one inside the arena when RGBA was not requested).
+  stitch::png::Params PP;
+  std::memset(&PP, 0, sizeof PP);
+  if (want_png) {
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const int nb = (ch + PNG_BAND_ROWS - 1) / PNG_BAND_ROWS;
+    const int64_t band_raw = ((int64_t)cw * 4 + 1) * PNG_BAND_ROWS;
+    const int64_t band_cap = (int64_t)up((size_t)(band_raw * 2 + 1024));
+    const int64_t worst = stitch_png_capacity(&L);
+    const int64_t p_cap = job->out_capacity_png < worst ? job->out_capacity_png : worst;
+    const int64_t c_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
+    const size_t b_canvas = want_rgba ? 0 : up((size_t)(c_pitch * ch));
+    const size_t b_lens = up((size_t)nb * PNG_TAB_STRIDE), b_codes = up((size_t)nb * PNG_TAB_STRIDE * 2);
+    const size_t b_adler = up((size_t)nb * 8), b_scr = (size_t)nb * (size_t)band_cap;
+    const size_t b_blen = up((size_t)nb * 4), b_off = up((size_t)nb * 8), b_info = 256;
+    const size_t b_file = out_host ? up((size_t)p_cap) : 0;
+    const size_t need = b_canvas + b_lens + b_codes + b_adler + b_scr + b_blen + b_off + b_info + b_file;
+    if (ln.png_arena_cap < need) {
+      if (ln.png_arena) {
+        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+        CUDA_TRY(ctx, cudaFree(ln.png_arena));
+      }
+      ln.png_arena = nullptr;
+      ln.png_arena_cap = 0;
+      if (cudaMalloc(&ln.png_arena, need) != cudaSuccess)
+        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG work buffers allocation failed)");
+      ln.png_arena_cap = need;
+    }
+    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+    uint8_t* a = (uint8_t*)ln.png_arena;
+    if (!want_rgba) { d_rgba = a; d_rgba_pitch = c_pitch; }
+    a += b_canvas;
+    PP.lens = a; a += b_lens;
+    PP.codes = (uint16_t*)a; a += b_codes;
+    PP.adler = (uint32_t*)a; a += b_adler;
+    PP.scratch = a; a += b_scr;
+    PP.blen = (uint32_t*)a; a += b_blen;
+    PP.off = (uint64_t*)a; a += b_off;
+    PP.info = (uint64_t*)a; a += b_info;
+    PP.file = out_host ? a : (uint8_t*)job->out_png;
+    PP.cap = p_cap;
+    PP.band_cap = band_cap;
+    PP.w = cw; PP.h = ch; PP.nb = nb;
+    PP.rgba = d_rgba;
+    PP.pitch = d_rgba_pitch;
+  }
   const bool planes = want_yuv || want_jpeg;
+  const bool canvas = want_rgba || want_png;
   P.out_rgba = d_rgba;
   P.out_pitch = d_rgba_pitch;
   if (planes) {
@@ -480,7 +535,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   // [4] the draw loop (P:1439-1572) as fused launches
   int launches = 0;
   int path_info = 0;
-  st = stitch::launch_job(P, want_rgba, planes, ctx->sm_count, ln.scratch, ln.stream, &launches, &path_info);
+  st = stitch::launch_job(P, canvas, planes, ctx->sm_count, ln.scratch, ln.stream, &launches, &path_info);
   res->path_info = path_info;
   if (st != 0) return fail(ctx, STITCH_E_CUDA, std::string("kernel launch: ") + cudaGetErrorString((cudaError_t)st));
   ctx->launches += launches;
@@ -523,6 +578,55 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer too small; see jpeg_bytes)");
     if (out_host)
       CUDA_TRY(ctx, cudaMemcpyAsync(job->out_jpeg, j_file, (size_t)res->jpeg_bytes, cudaMemcpyDeviceToHost, ln.stream));
+  }
+  // [5c] export as the PNG file the page asks for (U:211-221 with fileType 'png', P:1579): histogram + code per
+  // band, encode, offsets, gather + CRC.  Like the JPEG export, complete when this function returns.
+  if (want_png) {
+    stitch::png::HeaderBytes hdr;
+    std::memset(&hdr, 0, sizeof hdr);
+    const uint8_t sig[16] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A, 0, 0, 0, 13, 'I', 'H', 'D', 'R'};
+    std::memcpy(hdr.b, sig, 16);
+    auto be32 = [](uint8_t* q, uint32_t v) { q[0] = v >> 24; q[1] = v >> 16; q[2] = v >> 8; q[3] = (uint8_t)v; };
+    be32(hdr.b + 16, (uint32_t)cw);
+    be32(hdr.b + 20, (uint32_t)ch);
+    hdr.b[24] = 8; hdr.b[25] = 6;   // 8 bit, colour type 6 (RGBA); compression 0, filter 0, no interlace
+    {
+      uint32_t c = 0xFFFFFFFFu;   // CRC-32 of 'IHDR' + 13 bytes
+      for (int i = 12; i < 29; ++i) {
+        c ^= hdr.b[i];
+        for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+      }
+      be32(hdr.b + 29, c ^ 0xFFFFFFFFu);
+    }
+    hdr.n = 33;
+    {
+      // x^(2^k) mod P, reflected: x2n[0] = x, each next one the square of the previous
+      auto mul = [](uint32_t a, uint32_t b) {
+        uint32_t m = 1u << 31, p = 0;
+        for (;;) {
+          if (a & m) { p ^= b; if ((a & (m - 1)) == 0) break; }
+          m >>= 1;
+          b = (b & 1u) ? (b >> 1) ^ 0xEDB88320u : b >> 1;
+        }
+        return p;
+      };
+      uint32_t p = 1u << 30;
+      PP.x2n[0] = p;
+      for (int k = 1; k < 32; ++k) { p = mul(p, p); PP.x2n[k] = p; }
+    }
+    stitch::png::png_hist_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
+    stitch::png::png_encode_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
+    stitch::png::png_offsets_kernel<<<1, 1024, 0, ln.stream>>>(PP, hdr);
+    stitch::png::png_gather_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches += 4;
+    res->kernel_launches += 4;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, PP.info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    res->png_bytes = (int64_t)ln.jpeg_info_host[0];
+    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG output buffer too small; see png_bytes)");
+    if (out_host)
+      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_png, PP.file, (size_t)res->png_bytes, cudaMemcpyDeviceToHost, ln.stream));
   }
   return STITCH_OK;
 }

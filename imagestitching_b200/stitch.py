@@ -62,6 +62,7 @@ class StitchOutput:
     cb: Any = None
     cr: Any = None
     jpeg: Optional[bytes] = None   # the exported JFIF file (output "...+jpeg" / "jpeg")
+    png: Optional[bytes] = None    # the exported PNG file (output "...+png" / "png"), what the page asks for
     kernel_launches: int = 0
     path_info: int = 0
     progress: List[int] = field(default_factory=list)
@@ -70,7 +71,8 @@ class StitchOutput:
 def _output_flags(output: str) -> int:
     flags = 0
     for part in output.split("+"):
-        flags |= {"rgba": L.OUT_RGBA, "yuv420": L.OUT_YUV420, "both": L.OUT_RGBA | L.OUT_YUV420, "jpeg": L.OUT_JPEG}[part]
+        flags |= {"rgba": L.OUT_RGBA, "yuv420": L.OUT_YUV420, "both": L.OUT_RGBA | L.OUT_YUV420, "jpeg": L.OUT_JPEG,
+                  "png": L.OUT_PNG}[part]
     return flags
 
 
@@ -340,7 +342,7 @@ class StitchContext:
             platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
             deviceMaxCanvasPixels: Optional[int] = None, output: str = "rgba",
             on_progress: Optional[Callable[[int], None]] = None, jpeg_quality: int = 0,
-            jpeg_restart_interval: int = 0, jpeg_capacity: int = 0) -> Optional[StitchOutput]:
+            jpeg_restart_interval: int = 0, jpeg_capacity: int = 0, png_capacity: int = 0) -> Optional[StitchOutput]:
         """Synchronous stitch with host outputs (numpy).  Returns None for an empty list (index.js:1189).
         `output`: "rgba" | "yuv420" | "both", optionally "+jpeg", or "jpeg" alone (the exported file)."""
         lib = self.lib
@@ -363,12 +365,15 @@ class StitchContext:
         jpg = None
         if flags & L.OUT_JPEG:
             jpg = np.empty(jpeg_capacity or int(lib.stitch_jpeg_capacity(C.byref(lay), jpeg_restart_interval)), dtype=np.uint8)
+        png = np.empty(png_capacity or int(lib.stitch_png_capacity(C.byref(lay))), dtype=np.uint8) if flags & L.OUT_PNG else None
         job, keep = self.build_job(images, direction, mode, gap, profile, output, False,
                                    rgba.ctypes.data if rgba is not None else 0,
                                    yuv.ctypes.data if yuv is not None else 0,
                                    rgba.nbytes if rgba is not None else 0, yuv.nbytes if yuv is not None else 0,
                                    jpg.ctypes.data if jpg is not None else 0, jpg.nbytes if jpg is not None else 0,
                                    jpeg_quality, jpeg_restart_interval)
+        if png is not None:
+            job.out_png, job.out_capacity_png = png.ctypes.data, png.nbytes
         progress: List[int] = []
 
         def _cb(_user, pct):
@@ -386,11 +391,15 @@ class StitchContext:
         if st != L.OK:
             if st == L.E_NO_SURFACE and res.jpeg_bytes:
                 raise StitchError(st, f"JPEG output buffer too small: {res.jpeg_bytes} bytes needed")
+            if st == L.E_NO_SURFACE and res.png_bytes:
+                raise StitchError(st, f"PNG output buffer too small: {res.png_bytes} bytes needed")
             _raise(st, self.handle)
         out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, path_info=res.path_info, progress=progress)
         out.rgba = rgba
         if jpg is not None:
             out.jpeg = jpg[: res.jpeg_bytes].tobytes()
+        if png is not None:
+            out.png = png[: res.png_bytes].tobytes()
         if yuv is not None:
             cwh, chh = (cw + 1) // 2, (ch + 1) // 2
             out.y = yuv[: cw * ch].reshape(ch, cw)

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 4
+#define STITCH_ABI_VERSION 5
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -125,7 +125,9 @@ int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 /* STITCH_MEM_HOST_JPEG: `data` is a baseline JPEG FILE in host memory and pitch_bytes its length in bytes; the
  * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
 typedef enum StitchMemKind { STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2 } StitchMemKind;
-typedef enum StitchOutputFlags { STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4 } StitchOutputFlags;
+typedef enum StitchOutputFlags {
+  STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4, STITCH_OUT_PNG = 8
+} StitchOutputFlags;
 
 /* A decoded bitmap (what loadImageFrom hands to drawWithOrientation, P:1445-1463,1532):
  * RGBA8, straight (non-premultiplied) alpha, row pitch in bytes (>= 4*bmp_width). */
@@ -154,6 +156,10 @@ typedef struct StitchJob {
   int64_t out_capacity_jpeg;      /* bytes available; stitch_jpeg_capacity() is always enough */
   int32_t jpeg_quality;           /* 1..100 (IJG scale); 0 = 100, the reference's `quality: 1` */
   int32_t jpeg_restart_interval;  /* MCUs between restart markers; 0 = default (8) */
+  /* STITCH_OUT_PNG: the export file the page actually asks for (fileType 'png', P:1577-1579): RGBA 8-bit PNG of
+   * the canvas, filtered and deflate-coded on the GPU; lossless, so decoding it returns the RGBA canvas exactly. */
+  void* out_png;
+  int64_t out_capacity_png;       /* bytes available; stitch_png_capacity() is always enough */
 } StitchJob;
 
 typedef struct StitchResult {
@@ -165,6 +171,7 @@ typedef struct StitchResult {
                                  regions of the fused compose launch; bit 24 = whole-canvas gather launch;
                                  bits 25-30 upscale regions */
   int64_t jpeg_bytes;         /* size of the JPEG file written to out_jpeg (or needed, on STITCH_E_NO_SURFACE) */
+  int64_t png_bytes;          /* size of the PNG file written to out_png (or needed, on STITCH_E_NO_SURFACE) */
 } StitchResult;
 
 /* Required output sizes for a layout (export region == whole canvas, U:206-209, P:1577-1579). */
@@ -173,6 +180,9 @@ int stitch_output_size(const StitchLayout* layout, int64_t* rgba_bytes, int64_t*
  * stuffed): a capacity that can never be too small.  Real files are a fraction of it; a smaller capacity
  * is accepted and reported through STITCH_E_NO_SURFACE + result.jpeg_bytes (the size needed) if exceeded. */
 int64_t stitch_jpeg_capacity(const StitchLayout* layout, int32_t restart_interval);
+
+/* Worst-case size of the PNG export of this layout (every byte coded with a 15-bit code). */
+int64_t stitch_png_capacity(const StitchLayout* layout);
 
 /* Synchronous onStitch(): layout -> draw all images -> export into the caller's buffer. (P:1186-1633) */
 int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);

@@ -26,7 +26,7 @@ def test_every_declared_symbol_is_exported_and_bound():
 
 def test_abi_version_and_strerror():
     lib = L.load()
-    assert lib.stitch_abi_version() == 4
+    assert lib.stitch_abi_version() == 5
     assert lib.stitch_strerror(L.E_BAD_DIMS).decode() == "图片尺寸不可用"
     assert lib.stitch_strerror(L.E_BAD_OUT).decode() == "输出尺寸计算失败"
     assert lib.stitch_strerror(L.E_NO_SURFACE).decode() == "无法获取绘图上下文"
@@ -40,10 +40,10 @@ def test_struct_sizes_match_header():
     assert C.sizeof(L.StitchRect) == 32
     assert C.sizeof(L.StitchLayout) == 8 + 11 * 8 + 9 * 32 + 2 * 36
     assert C.sizeof(L.StitchImage) == 32 + 8 + 8 + 8 + 8
-    assert C.sizeof(L.StitchJob) == 8 + 8 + 32 + 8 + 8 + 8 + 8 + 8 + 8 + 8 + 8 + 8
+    assert C.sizeof(L.StitchJob) == 8 + 8 + 32 + 8 + 8 + 8 + 8 + 8 + 8 + 8 + 8 + 8 + 16
     assert C.sizeof(L.StitchImageInfo) == 16
     assert C.sizeof(L.StitchPreviewLayout) == 16 + 4 * 8
-    assert C.sizeof(L.StitchResult) == C.sizeof(L.StitchLayout) + 8 + 16 + 8 + 8
+    assert C.sizeof(L.StitchResult) == C.sizeof(L.StitchLayout) + 8 + 16 + 8 + 8 + 8
 
 
 def test_no_cpu_fallback_without_gpu():

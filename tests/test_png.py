@@ -1,0 +1,79 @@
+"""PNG export (index.js:1577-1579 -> canvasToTempFilePath fileType 'png', utils/canvas.js:205-242).
+
+CPU: the oracle writer (oracle/png_ref.c) is pinned by decoding its files with libpng/zlib (PIL): lossless.
+GPU: STITCH_OUT_PNG files are byte-identical to the oracle writer's and decode to the RGBA canvas exactly.
+"""
+import io
+import zlib
+
+import numpy as np
+import pytest
+from PIL import Image
+
+from oracle import png_c as P
+from tests import util as U
+
+SIZES = [(1, 1), (3, 2), (17, 9), (64, 48), (123, 77), (333, 200), (700, 9)]
+
+
+def _back(data):
+    return np.asarray(Image.open(io.BytesIO(data)).convert("RGBA"))
+
+
+@pytest.mark.parametrize("size", SIZES, ids=[f"{w}x{h}" for w, h in SIZES])
+def test_oracle_png_roundtrip(size):
+    w, h = size
+    rng = np.random.default_rng(w * 1000 + h)
+    for a in (rng.integers(0, 256, (h, w, 4), dtype=np.uint8), np.full((h, w, 4), 255, np.uint8), U.synth_image(w, h, 5, 0)):
+        data = P.encode_rgba(a)
+        assert data[:8] == b"\x89PNG\r\n\x1a\n" and data[-12:] == b"\0\0\0\0IEND\xaeB`\x82"
+        assert np.array_equal(_back(data), a)
+
+
+def test_oracle_crc_and_length_limit():
+    for s in (b"", b"IEND", b"IDAT" + bytes(range(256)) * 7):
+        assert P.crc32(s) == zlib.crc32(s)
+    f = np.zeros(257, np.uint32)
+    f[:40] = [int(1.6 ** i) + 1 for i in range(40)]      # Fibonacci-like skew: plain Huffman would need > 15 bits
+    f[256] = 1
+    lens = P.code_lengths(f)
+    assert lens.max() == 15 and abs(sum(2.0 ** -int(x) for x in lens if x) - 1.0) < 1e-12
+    assert (lens[f == 0] == 0).all() and (lens[f > 0] > 0).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [
+    ([(806, 604), (604, 806), (806, 604)], "vertical", "min", 700, 0, "rgba+png"),
+    ([(320, 200), (100, 260)], "horizontal", "original", 0, 7, "png"),
+    ([(64, 48)], "vertical", "min", 0, 0, "rgba+png"),                   # one band
+    ([(1080, 1920), (1080, 1920)], "vertical", "min", 0, 0, "png"),      # cfg1: 2376 x 8448 canvas
+], ids=["three", "original-gap", "tiny", "cfg1"])
+def test_gpu_png_equals_oracle_and_is_lossless(case):
+    from imagestitching_b200 import StitchContext
+    dims, direction, mode, size, gap, output = case
+    bitmaps = [U.synth_image(w, h, 300 + i, 0) for i, (w, h) in enumerate(dims)]
+    ctx = StitchContext(0)
+    ref = ctx.run(U.page_images(dims, bitmaps), direction, mode=mode, gap=gap, platform="ios", deviceMaxCanvasSize=size or None)
+    got = ctx.run(U.page_images(dims, bitmaps), direction, mode=mode, gap=gap, platform="ios", deviceMaxCanvasSize=size or None,
+                  output=output)
+    ctx.close()
+    assert got.png is not None and got.kernel_launches == 5
+    back = _back(got.png)
+    assert np.array_equal(back, ref.rgba), "PNG does not decode to the canvas"
+    if got.rgba is not None:
+        assert np.array_equal(got.rgba, ref.rgba)
+    want = P.encode_rgba(ref.rgba)
+    assert len(got.png) == len(want) and got.png == want, "GPU PNG differs from the oracle writer"
+
+
+@pytest.mark.gpu
+def test_gpu_png_capacity_error():
+    from imagestitching_b200 import StitchContext, StitchError
+    from imagestitching_b200 import _lib as L
+    dims = [(320, 200), (320, 200)]
+    bitmaps = [U.synth_image(w, h, 1, 0) for w, h in dims]
+    ctx = StitchContext(0)
+    with pytest.raises(StitchError) as e:
+        ctx.run(U.page_images(dims, bitmaps), "vertical", output="png", png_capacity=4096)
+    assert e.value.status == L.E_NO_SURFACE and "bytes needed" in e.value.message
+    ctx.close()
