@@ -139,76 +139,90 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
     P.adler[2 * band + 1] = (uint32_t)(((unsigned long long)n + b) % 65521ull);
   }
   __syncthreads();
-  if (wp != 0) return;
-  // ---- warp 0: length-limited Huffman code of freq[0..256] ----
+  // ---- length-limited Huffman code of freq[0..256] ----
+  // Same tree as "merge the two smallest (weight, index) until one node is left": the leaves are ranked by
+  // (frequency, index) by counting, then one thread runs the two-queue merge (internal nodes are created in
+  // non-decreasing weight order, so the two queue heads are always the two smallest; on a tie the leaf -- lower
+  // index -- goes first), every thread walks its leaf up to the root for the depth, and the canonical code of a
+  // symbol is next[len] + the number of lower symbols of the same length.
   uint8_t* lens = P.lens + (int64_t)band * PNG_TAB_STRIDE;
   uint16_t* codes = P.codes + (int64_t)band * PNG_TAB_STRIDE;
+  __shared__ uint16_t order[PNG_NSYM];
+  __shared__ int s_nleaf, s_maxd;
+  __shared__ int bl_count[16], next_code[16];
   for (;;) {
-    int nn = PNG_NSYM;
-    for (int i = lane; i < 2 * PNG_NSYM; i += 32) { parent[i] = 0xffff; if (i >= PNG_NSYM) freq[i] = 0; }
-    __syncwarp();
-    // number of live leaves
-    int alive = 0;
-    for (int i = lane; i < PNG_NSYM; i += 32) alive += freq[i] > 0;
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) alive += __shfl_xor_sync(0xffffffffu, alive, d);
-    while (alive > 1) {
-      // the two smallest (weight, index) among nodes without a parent and with weight > 0
-      unsigned long long k1 = ~0ull, k2 = ~0ull;
-      for (int i = lane; i < nn; i += 32) {
-        if (parent[i] != 0xffff || freq[i] == 0) continue;
-        const unsigned long long key = (unsigned long long)freq[i] << 32 | (unsigned)i;
-        if (key < k1) { k2 = k1; k1 = key; }
-        else if (key < k2) k2 = key;
+    if (t == 0) { s_nleaf = 0; s_maxd = 0; }
+    for (int i = t; i < 2 * PNG_NSYM; i += PNG_THREADS) parent[i] = 0xffff;
+    __syncthreads();
+    for (int i = t; i < PNG_NSYM; i += PNG_THREADS) {
+      const uint32_t f = freq[i];
+      if (f == 0) continue;
+      int rank = 0;
+      for (int k = 0; k < PNG_NSYM; ++k) {
+        const uint32_t g = freq[k];
+        rank += (g != 0 && (g < f || (g == f && k < i))) ? 1 : 0;
       }
-      unsigned long long g1 = k1;
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, g1, d); g1 = o < g1 ? o : g1; }
-      unsigned long long g2 = (k1 == g1) ? k2 : k1;
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, g2, d); g2 = o < g2 ? o : g2; }
-      if (lane == 0) {
-        const int m1 = (int)(g1 & 0xffffffffu), m2 = (int)(g2 & 0xffffffffu);
-        freq[nn] = (uint32_t)(g1 >> 32) + (uint32_t)(g2 >> 32);
-        parent[m1] = (uint16_t)nn;
-        parent[m2] = (uint16_t)nn;
-      }
-      ++nn;
-      --alive;
-      __syncwarp();
+      order[rank] = (uint16_t)i;
+      atomicAdd(&s_nleaf, 1);
     }
-    int maxd = 0;
-    if (lane == 0) {
-      depth[nn - 1] = 0;
-      for (int i = nn - 2; i >= 0; --i) {
-        if (parent[i] == 0xffff) { depth[i] = 0; continue; }
-        depth[i] = (uint8_t)min((int)depth[parent[i]] + 1, 255);
-        if (i < PNG_NSYM && depth[i] > maxd) maxd = depth[i];
+    __syncthreads();
+    if (t == 0) {
+      const int nl = s_nleaf;
+      int qa = 0, qb = PNG_NSYM, nn = PNG_NSYM;     // heads of the leaf queue (order[]) and the internal-node queue
+      for (int m = 0; m < nl - 1; ++m) {
+        int pick[2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const bool has_a = qa < nl, has_b = qb < nn;
+          const uint32_t wa = has_a ? freq[order[qa]] : 0xffffffffu, wb = has_b ? freq[qb] : 0xffffffffu;
+          if (has_a && (!has_b || wa <= wb)) pick[e] = order[qa++];
+          else pick[e] = qb++;
+        }
+        freq[nn] = freq[pick[0]] + freq[pick[1]];
+        parent[pick[0]] = (uint16_t)nn;
+        parent[pick[1]] = (uint16_t)nn;
+        ++nn;
       }
     }
-    maxd = __shfl_sync(0xffffffffu, maxd, 0);
-    __syncwarp();
-    if (maxd <= 15) break;
-    for (int i = lane; i < PNG_NSYM; i += 32)
+    __syncthreads();
+    for (int i = t; i < PNG_NSYM; i += PNG_THREADS) {
+      int d = 0;
+      if (freq[i] != 0) {
+        int p = parent[i];
+        while (p != 0xffff) { ++d; p = parent[p]; }
+        if (s_nleaf == 1) d = 1;
+      }
+      depth[i] = (uint8_t)min(d, 255);
+      if (d > 15) atomicMax(&s_maxd, d);
+    }
+    __syncthreads();
+    if (s_maxd <= 15) break;
+    for (int i = t; i < PNG_NSYM; i += PNG_THREADS)
       if (freq[i] > 0) freq[i] = (freq[i] + 1) >> 1;
-    __syncwarp();
+    __syncthreads();
   }
-  for (int i = lane; i < PNG_NSYM; i += 32) lens[i] = freq[i] > 0 ? depth[i] : 0;
-  __syncwarp();
-  if (lane == 0) {  // canonical codes (RFC 1951 3.2.2), bit-reversed
-    int bl_count[16], next[16];
-    for (int b = 0; b < 16; ++b) bl_count[b] = 0;
-    for (int i = 0; i < PNG_NSYM; ++i) bl_count[lens[i]]++;
-    bl_count[0] = 0;
+  if (t < 16) bl_count[t] = 0;
+  __syncthreads();
+  for (int i = t; i < PNG_NSYM; i += PNG_THREADS) {
+    lens[i] = depth[i];
+    if (depth[i]) atomicAdd(&bl_count[depth[i]], 1);
+  }
+  __syncthreads();
+  if (t == 0) {   // RFC 1951 3.2.2
     int c = 0;
-    next[0] = 0;
-    for (int b = 1; b <= 15; ++b) { c = (c + bl_count[b - 1]) << 1; next[b] = c; }
-    for (int i = 0; i < PNG_NSYM; ++i) {
-      const int l = lens[i];
-      if (!l) { codes[i] = 0; continue; }
-      const uint32_t v = (uint32_t)next[l]++;
-      codes[i] = (uint16_t)(__brev(v) >> (32 - l));
+    next_code[0] = 0;
+    for (int bb = 1; bb <= 15; ++bb) { c = (c + (bb > 1 ? bl_count[bb - 1] : 0)) << 1; next_code[bb] = c; }
+  }
+  __syncthreads();
+  for (int i = t; i < PNG_NSYM; i += PNG_THREADS) {
+    const int l = depth[i];
+    uint32_t v = 0;
+    if (l) {
+      int lower = 0;
+      for (int k = 0; k < i; ++k) lower += depth[k] == l ? 1 : 0;
+      v = __brev((uint32_t)(next_code[l] + lower)) >> (32 - l);
     }
+    codes[i] = (uint16_t)v;
   }
 }
 
@@ -372,8 +386,24 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
 __global__ void __launch_bounds__(1024) png_offsets_kernel(const __grid_constant__ Params P, const __grid_constant__ HeaderBytes H) {
   __shared__ unsigned long long warp_sum[32];
   __shared__ unsigned long long carry_s;
+  __shared__ uint32_t s_ad[3][1024];            // per-thread Adler pair + length (mod 65521) of a slice of bands
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
   if (t == 0) carry_s = (unsigned long long)H.n;
+  {
+    const int per = (P.nb + 1023) / 1024;
+    unsigned long long a = 1, b = 0, nn = 0;
+    for (int k = t * per; k < min((t + 1) * per, P.nb); ++k) {
+      const int rows = min(PNG_BAND_ROWS, P.h - k * PNG_BAND_ROWS);
+      const unsigned long long n = (((unsigned long long)P.w * 4 + 1) * rows) % 65521ull;
+      const unsigned long long a2 = P.adler[2 * k], b2 = P.adler[2 * k + 1];
+      b = (b + b2 + n * ((a + 65520ull) % 65521ull)) % 65521ull;
+      a = (a + a2 + 65520ull) % 65521ull;
+      nn = (nn + n) % 65521ull;
+    }
+    s_ad[0][t] = (uint32_t)a;
+    s_ad[1][t] = (uint32_t)b;
+    s_ad[2][t] = (uint32_t)nn;
+  }
   __syncthreads();
   for (int base = 0; base < P.nb; base += 1024) {
     const int i = base + t;
@@ -407,14 +437,12 @@ __global__ void __launch_bounds__(1024) png_offsets_kernel(const __grid_constant
     const bool fits = total <= (unsigned long long)P.cap;
     P.info[0] = total;
     P.info[1] = fits ? 0ull : 1ull;
-    // Adler-32 of the whole stream from the per-band pairs
+    // Adler-32 of the whole stream: thread t combined its slice of bands above (s_ad); fold the slices in order
     unsigned long long a = 1, b = 0;
-    for (int k = 0; k < P.nb; ++k) {
-      const int rows = min(PNG_BAND_ROWS, P.h - k * PNG_BAND_ROWS);
-      const unsigned long long n = ((unsigned long long)P.w * 4 + 1) * rows;
-      const unsigned long long a2 = P.adler[2 * k], b2 = P.adler[2 * k + 1];
-      b = (b + b2 + (n % 65521ull) * ((a + 65520ull) % 65521ull)) % 65521ull;   // + n * (a - 1)
-      a = (a + a2 + 65520ull) % 65521ull;                                      // a + a2 - 1
+    for (int k = 0; k < 1024; ++k) {
+      const unsigned long long a2 = s_ad[0][k], b2 = s_ad[1][k], n2 = s_ad[2][k];
+      b = (b + b2 + n2 * ((a + 65520ull) % 65521ull)) % 65521ull;   // + n * (a - 1)
+      a = (a + a2 + 65520ull) % 65521ull;                          // a + a2 - 1
     }
     P.info[2] = (b << 16) | a;
     if (fits) {
@@ -484,9 +512,10 @@ __global__ void __launch_bounds__(PNG_THREADS) png_gather_kernel(const __grid_co
   __syncwarp();
   if (lane == 0) {
     uint32_t crc = part_crc[0];
+    const uint32_t xp = x_pow_8n(P, per);          // all slices but the last have `per` bytes
     for (int k = 1; k < 32; ++k) {
       if (part_len[k] == 0) continue;
-      crc = gf2_mul(x_pow_8n(P, part_len[k]), crc) ^ part_crc[k];
+      crc = gf2_mul(part_len[k] == per ? xp : x_pow_8n(P, part_len[k]), crc) ^ part_crc[k];
     }
     uint8_t* e = dst + 8 + dl;
     e[0] = (uint8_t)(crc >> 24); e[1] = (uint8_t)(crc >> 16); e[2] = (uint8_t)(crc >> 8); e[3] = (uint8_t)crc;

@@ -52,13 +52,15 @@ def main():
     for k in range(args.steps):
         ctx.decode_jpeg(files[k % 9])
     out["gpu_decode_ms_per_image_incl_d2h"] = round((time.perf_counter() - t) / args.steps * 1e3, 2)
-    for output in ("rgba", "jpeg"):
+    for output in ("rgba", "jpeg", "png"):
         kw = dict(jpeg_quality=90, jpeg_capacity=64 << 20) if output == "jpeg" else {}
         ctx.run(recs, "vertical", mode="min", platform="ios", output=output, **kw)
         l0 = ctx.kernel_launches
         t = time.perf_counter()
         for _ in range(args.steps):
             r = ctx.run(recs, "vertical", mode="min", platform="ios", output=output, **kw)
+        if output == "png":
+            out["png_MB"] = round(len(r.png) / 1e6, 2)
         ms = (time.perf_counter() - t) / args.steps * 1e3
         out[f"files_to_{output}_ms_per_job"] = round(ms, 2)
         out[f"files_to_{output}_MPps"] = round(r.width * r.height / 1e6 / (ms / 1e3), 1)
