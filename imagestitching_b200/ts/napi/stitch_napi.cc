@@ -21,7 +21,7 @@ struct RunData {
   std::vector<napi_ref> keep;          // the Uint8Arrays stay alive until completion
   StitchJob job{};
   StitchResult result{};
-  std::vector<uint8_t> rgba, yuv, jpeg;
+  std::vector<uint8_t> rgba, yuv, jpeg, png;
   int status = 0;
   std::string message;
   napi_deferred deferred = nullptr;
@@ -88,7 +88,9 @@ void complete(napi_env env, napi_status, void* p) {
   };
   if (d->status == STITCH_OK) { attach("rgba", d->rgba); attach("yuv", d->yuv);
     d->jpeg.resize((size_t)d->result.jpeg_bytes);   // the file is the first jpeg_bytes of the capacity buffer
-    attach("jpeg", d->jpeg); }
+    attach("jpeg", d->jpeg);
+    d->png.resize((size_t)d->result.png_bytes);
+    attach("png", d->png); }
   for (napi_ref r : d->keep) napi_delete_reference(env, r);
   if (d->tsfn) napi_release_threadsafe_function(d->tsfn, napi_tsfn_release);
   napi_resolve_deferred(env, d->deferred, out);
@@ -181,6 +183,11 @@ napi_value Run(napi_env env, napi_callback_info info) {
     d->jpeg.resize((size_t)stitch_jpeg_capacity(&lay, d->job.jpeg_restart_interval));
     d->job.out_jpeg = d->jpeg.data();
     d->job.out_capacity_jpeg = (int64_t)d->jpeg.size();
+  }
+  if (d->job.output_flags & STITCH_OUT_PNG) {
+    d->png.resize((size_t)stitch_png_capacity(&lay));
+    d->job.out_png = d->png.data();
+    d->job.out_capacity_png = (int64_t)d->png.size();
   }
   d->job.out_rgba = d->rgba.empty() ? nullptr : d->rgba.data();
   d->job.out_yuv = d->yuv.empty() ? nullptr : d->yuv.data();

@@ -25,17 +25,19 @@ export interface StitchImage extends ImageRecord {
 export interface StitchOptions {
   gap?: number; mode?: 'min' | 'max' | 'original' | string;
   platform?: Platform; deviceMaxCanvasSize?: number; deviceMaxCanvasPixels?: number;
-  output?: 'rgba' | 'yuv420' | 'both' | 'jpeg' | 'rgba+jpeg';
+  output?: 'rgba' | 'yuv420' | 'both' | 'jpeg' | 'rgba+jpeg' | 'png' | 'rgba+png';
   /** canvasToTempFilePath({fileType:'jpg', quality}) on the IJG 1..100 scale; the page passes quality 1 = 100 */
   jpegQuality?: number; jpegRestartInterval?: number; device?: number; onProgress?: (pct: number) => void;
 }
-export interface StitchResult { width: number; height: number; layout: Layout; rgba?: Uint8Array; yuv?: Uint8Array; jpeg?: Uint8Array; }
+export interface StitchResult { width: number; height: number; layout: Layout; rgba?: Uint8Array; yuv?: Uint8Array; jpeg?: Uint8Array;
+  /** the PNG file canvasToTempFilePath({fileType:'png'}) would write (index.js:1577-1579) */
+  png?: Uint8Array; }
 interface NativeJob {
   images: StitchImage[]; direction: number; mode: number; gap: number;
   platform: number; maxCanvasSize: number; maxCanvasPixels: number; output: number;
   jpegQuality: number; jpegRestartInterval: number;
 }
-interface NativeResult { width: number; height: number; rgba?: Uint8Array; yuv?: Uint8Array; jpeg?: Uint8Array; status: number; message: string; }
+interface NativeResult { width: number; height: number; rgba?: Uint8Array; yuv?: Uint8Array; jpeg?: Uint8Array; png?: Uint8Array; status: number; message: string; }
 
 const MODES: Record<string, number> = { min: 0, max: 1, original: 2 };
 const PLATFORMS: Record<string, number> = { ios: 0, android: 1 };
@@ -72,10 +74,10 @@ export async function stitch(images: StitchImage[], direction: Direction, opts: 
     images, direction: direction === 'vertical' ? 0 : 1, mode: mode in MODES ? MODES[mode] : 3, gap: opts.gap || 0,
     platform: platform in PLATFORMS ? PLATFORMS[platform] : 2,
     maxCanvasSize: profile.deviceMaxCanvasSize || 0, maxCanvasPixels: profile.deviceMaxCanvasPixels || 0,
-    output: { rgba: 1, yuv420: 2, both: 3, jpeg: 4, 'rgba+jpeg': 5 }[opts.output || 'rgba'],
+    output: { rgba: 1, yuv420: 2, both: 3, jpeg: 4, 'rgba+jpeg': 5, png: 8, 'rgba+png': 9 }[opts.output || 'rgba'],
     jpegQuality: opts.jpegQuality || 0, jpegRestartInterval: opts.jpegRestartInterval || 0,
   }, opts.onProgress);
   if (res.status !== 0) throw new StitchError(res.status, res.message);
   if (res.width !== layout.canvasW || res.height !== layout.canvasH) throw new StitchError(-1, 'layout twin mismatch');
-  return { width: res.width, height: res.height, layout, rgba: res.rgba, yuv: res.yuv, jpeg: res.jpeg };
+  return { width: res.width, height: res.height, layout, rgba: res.rgba, yuv: res.yuv, jpeg: res.jpeg, png: res.png };
 }
