@@ -267,7 +267,8 @@ __device__ __forceinline__ State decode_range(const DecImage& I, const SmemTable
     }
     if (r.cnt < r.fake) {
       // the symbol ran into a marker (it was padding) or past the end: drop it
-      const uint32_t mpos = r.pos;
+      uint32_t mpos = r.pos;
+      while (mpos + 2 < r.n && r.p[mpos + 1] == 0xFFu) ++mpos;   // fill bytes in front of the marker (T.81 B.1.1.2)
       const uint32_t m = (mpos + 1 < r.n) ? r.p[mpos + 1] : 0xD9u;
       if (mpos + 1 < r.n && m >= 0xD0u && m <= 0xD7u) {   // RSTn: byte-aligned restart, predictors and position reset
         b = 0;

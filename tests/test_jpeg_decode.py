@@ -96,6 +96,36 @@ def test_gpu_decoder_equals_oracle(spec):
     assert np.array_equal(got, want), f"{np.count_nonzero(got != want)} bytes differ"
 
 
+def _with_fill_bytes(data: bytes) -> bytes:
+    """Insert 0xFF fill bytes in front of every RSTn marker (legal: T.81 B.1.1.2)."""
+    sos = data.index(b"\xff\xda")
+    head, scan = data[:sos], bytearray(data[sos:])
+    out = bytearray()
+    i = 0
+    while i < len(scan):
+        if scan[i] == 0xFF and i + 1 < len(scan) and 0xD0 <= scan[i + 1] <= 0xD7:
+            out += b"\xff\xff"                         # two fill bytes, then the marker itself
+        out.append(scan[i])
+        i += 1
+    return head + bytes(out)
+
+
+def test_oracle_decoder_fill_bytes():
+    data = _with_fill_bytes(_jpeg(200, 120, quality=90, subsampling=2, restart_marker_blocks=2))
+    assert b"\xff\xff\xff\xd0" in data
+    assert np.array_equal(J.decode(data)[..., :3], _pil(data))
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_fill_bytes():
+    from imagestitching_b200 import StitchContext
+    data = _with_fill_bytes(_jpeg(640, 481, seed=4, quality=90, subsampling=2, restart_marker_blocks=5))
+    ctx = StitchContext(0)
+    got = ctx.decode_jpeg(data)
+    ctx.close()
+    assert np.array_equal(got, J.decode(data))
+
+
 @pytest.mark.gpu
 def test_gpu_decoder_full_size_photo():
     """A 12 MP file as the page's inputs are (BASELINE configs[1] shape)."""
