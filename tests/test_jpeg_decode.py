@@ -69,6 +69,29 @@ def test_oracle_decoder_rejects_progressive():
         J.decode(data)
 
 
+def _corrupt(data: bytes, seed: int, n_flips: int = 12, scan_only: bool = True) -> bytes:
+    rng = np.random.default_rng(seed)
+    b = bytearray(data)
+    lo = data.index(b"\xff\xda") + 14 if scan_only else 2
+    for pos in rng.integers(lo, len(b) - 2, n_flips):
+        b[pos] = int(rng.integers(0, 256))
+    return bytes(b)
+
+
+def test_oracle_decoder_survives_corruption():
+    """Damaged entropy data must give SOME bitmap of the right size (libjpeg behaves the same way); damaged
+    headers must give an error or a bitmap, never a crash."""
+    data = _jpeg(250, 131, quality=85, subsampling=2, restart_marker_blocks=4)
+    for seed in range(40):
+        out = J.decode(_corrupt(data, seed))
+        assert out.shape == (131, 250, 4)
+    for seed in range(40):
+        try:
+            J.decode(_corrupt(data, 1000 + seed, n_flips=3, scan_only=False))
+        except ValueError:
+            pass
+
+
 # ---------------------------------------------------------------- GPU
 GPU_FILES = [
     dict(w=1, h=1, quality=90, subsampling=2), dict(w=7, h=5, quality=75, subsampling=0),
@@ -136,6 +159,32 @@ def test_gpu_decoder_full_size_photo():
     got = ctx.decode_jpeg(data)
     ctx.close()
     assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(120)
+def test_gpu_decoder_survives_corruption():
+    """Damaged scans: the decoder terminates and returns a bitmap of the right size (the synchronisation loop is
+    bounded, block indices are range-checked).  Blocks are placed by COUNT, so damage that changes the number of
+    blocks of a restart interval displaces what follows (libjpeg would re-align at the next RSTn); the picture in
+    front of the damage is intact."""
+    from imagestitching_b200 import StitchContext
+    data = _jpeg(640, 481, seed=6, quality=90, subsampling=2, restart_marker_rows=1)
+    want = J.decode(data)
+    ctx = StitchContext(0)
+    for seed in range(6):
+        bad = _corrupt(data, seed, n_flips=4)
+        first = next(i for i, (x, y) in enumerate(zip(data, bad)) if x != y)
+        got = ctx.decode_jpeg(bad)
+        assert got.shape == want.shape
+        # rows wholly coded before the first damaged byte: a generous lower bound from the byte position
+        safe_rows = int(481 * (first - data.index(b"\xff\xda")) / len(data)) // 16 * 16 - 32
+        if safe_rows > 0:
+            assert np.array_equal(got[:safe_rows], want[:safe_rows])
+    plain = _jpeg(333, 211, seed=7, quality=90, subsampling=0)
+    for seed in range(4):
+        assert ctx.decode_jpeg(_corrupt(plain, 50 + seed, n_flips=2)).shape == (211, 333, 4)
+    ctx.close()
 
 
 @pytest.mark.gpu
