@@ -188,7 +188,9 @@ int64_t stitch_png_capacity(const StitchLayout* layout);
 int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
 
 /* Asynchronous form for job-level sharding: enqueue on the next lane, wait later.
- * Buffers must stay valid until stitch_wait(ticket) returns. */
+ * Buffers must stay valid until stitch_wait(ticket) returns.  Jobs with STITCH_MEM_HOST_JPEG inputs or
+ * STITCH_OUT_JPEG / STITCH_OUT_PNG outputs need host round trips (synchronisation rounds, file sizes) and are
+ * complete when stitch_submit returns; stitch_wait is then a no-op for them. */
 int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket);
 int stitch_wait(StitchCtx* ctx, uint64_t ticket);
 
