@@ -165,18 +165,10 @@ __device__ __forceinline__ void gather_unit(const JobParam& P, const Region& R, 
 //
 // MAXO = max over the job's streaming regions of ceil(4 / ratio_x); HOPS = max of ceil(ratio_x / 4)
 // (1, 2 or 4); MODE = STREAM_MODE_* (RGBA canvas, I420 planes, or both).
-template <int MAXO, int HOPS, int MODE>
-__global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
-compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
-  extern __shared__ __align__(128) uint8_t smem_raw[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  WarpSmem& ws = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
-  // Lanes that never copy (past the band) and padded rows read the ring as it is: give it defined,
-  // opaque contents once so the alpha check cannot trip on uninitialised shared memory.
-#pragma unroll
-  for (int s = 0; s < STREAM_NST; ++s)
-    *reinterpret_cast<uint4*>(&ws.ring[s][lane * 16]) = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
-  __syncwarp();
+// The persistent unit loop shared by both kernels.  STREAM = false compiles the streaming unit out.
+template <int MAXO, int HOPS, int MODE, bool STREAM>
+__device__ __forceinline__ void compose_loop(const JobParam& P, const Plan& plan, unsigned int* __restrict__ sched, WarpSmem* ws) {
+  const int lane = threadIdx.x & 31;
   // One ticket per unit, drawn when the previous unit is done.  (Drawing the next ticket ahead of a short
   // unit to hide the atomic's round trip was measured slower on every workload: a claimed unit waits.)
   for (;;) {
@@ -189,8 +181,8 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
     const Region& R = plan.r[ri];
     const int local = (int)unit - R.first_unit;
     const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
-    if (R.kind == REGION_STREAM) {
-      stream_unit<MAXO, HOPS, MODE>(P, R, tx, ty, ws, lane);
+    if (STREAM && R.kind == REGION_STREAM) {
+      stream_unit<MAXO, HOPS, MODE>(P, R, tx, ty, *ws, lane);
     } else if (R.kind == REGION_UPSCALE) {
       upscale_unit<MODE>(P, R, tx, ty, lane);
     } else if (R.kind == REGION_FILL) {
@@ -208,6 +200,32 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
       __threadfence();
     }
   }
+}
+
+template <int MAXO, int HOPS, int MODE>
+__global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
+compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  WarpSmem& ws = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
+  // Lanes that never copy (past the band) and padded rows read the ring as it is: give it defined,
+  // opaque contents once so the alpha check cannot trip on uninitialised shared memory.
+#pragma unroll
+  for (int s = 0; s < STREAM_NST; ++s)
+    *reinterpret_cast<uint4*>(&ws.ring[s][lane * 16]) = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+  __syncwarp();
+  compose_loop<MAXO, HOPS, MODE, true>(P, plan, sched, &ws);
+}
+
+// Jobs without a streaming region (every image enlarged, transposed or unaligned: BASELINE configs[0], previews):
+// no shared memory and a smaller register budget, so more warps are resident for the latency-bound units.
+#ifndef LIGHT_MINB
+#define LIGHT_MINB 4
+#endif
+template <int MODE>
+__global__ void __launch_bounds__(STREAM_WARPS * 32, LIGHT_MINB)
+compose_light_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
+  compose_loop<2, 1, MODE, false>(P, plan, sched, nullptr);
 }
 
 }  // namespace stitch

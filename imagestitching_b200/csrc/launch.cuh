@@ -311,6 +311,24 @@ struct ComposeLaunch {
   }
 };
 
+template <int MODE>
+struct LightLaunch {
+  static int ctas_per_sm(cudaError_t* err) {
+    static int value = -1;
+    if (value < 0) {
+      int n = 0;
+      const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_light_kernel<MODE>, STREAM_WARPS * 32, 0);
+      if (e != cudaSuccess) { *err = e; return 0; }
+      value = n < 1 ? 1 : n;
+    }
+    return value;
+  }
+  static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
+    compose_light_kernel<MODE><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan, sched);
+    return cudaGetLastError();
+  }
+};
+
 // The draw loop of one job as ONE launch.  path_info: streaming | gather << 8 | fill << 16 |
 // upscale << 25 region counts of the fused plan, or 1 << 24 when the whole canvas took the per-pixel gather kernel
 // (fractional device rects, overlapping images).
@@ -321,9 +339,11 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
   const int mode = want_yuv ? (want_rgba ? STREAM_MODE_BOTH : STREAM_MODE_YUV) : STREAM_MODE_RGBA;
   // kernel variant: decided by the images alone (before the unit grid is chosen)
   int maxo = 2, hops = 1;
+  bool any_stream = false;   // no streaming candidate at all -> the light kernel (no smem, more resident warps)
   for (int k = 0; k < P.n; ++k) {
     const ImgParam& im = P.img[k];
     if (!is_int(im.X0) || !is_int(im.Y0) || !is_int(im.W) || !is_int(im.H) || im.W < 1 || im.H < 1 || !stream_eligible(im)) continue;
+    any_stream = true;
     const int64_t dw = (int64_t)im.W;
     maxo = std::max(maxo, (int)std::min<int64_t>(4, (4 * dw + im.sx_len - 1) / im.sx_len));
     hops = std::max(hops, (int)((im.sx_len + 4 * dw - 1) / (4 * dw)));
@@ -341,7 +361,12 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
   STITCH_DISPATCH(2, 1, Md, expr) STITCH_DISPATCH(3, 1, Md, expr) STITCH_DISPATCH(4, 1, Md, expr) \
   STITCH_DISPATCH(2, 2, Md, expr) STITCH_DISPATCH(4, 4, Md, expr)
 #define STITCH_ALL(expr) STITCH_SHAPES(0, expr) STITCH_SHAPES(1, expr) STITCH_SHAPES(2, expr)
-  STITCH_ALL(per_sm = K::ctas_per_sm(&err))
+#define STITCH_LIGHT(expr)                                   \
+  if (mode == 0) { using K = LightLaunch<0>; expr; }          \
+  else if (mode == 1) { using K = LightLaunch<1>; expr; }     \
+  else { using K = LightLaunch<2>; expr; }
+  if (any_stream) { STITCH_ALL(per_sm = K::ctas_per_sm(&err)) }
+  else { STITCH_LIGHT(per_sm = K::ctas_per_sm(&err)) }
   if (err != cudaSuccess) return (int)err;
   const int resident_warps = sm_count * per_sm * STREAM_WARPS;
 
@@ -371,10 +396,12 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
     const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
     if (grid > need) grid = need;
     unsigned int* sched = (unsigned int*)scratch.p;
-    STITCH_ALL(err = K::launch(P, plan, grid, sched, stream))
+    if (any_stream) { STITCH_ALL(err = K::launch(P, plan, grid, sched, stream)) }
+    else { STITCH_LIGHT(err = K::launch(P, plan, grid, sched, stream)) }
     *launches = 1;
     return (int)err;
   }
+#undef STITCH_LIGHT
 #undef STITCH_ALL
 #undef STITCH_SHAPES
 #undef STITCH_DISPATCH
