@@ -150,6 +150,33 @@ def test_gpu_decoder_fill_bytes():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("seed", range(4))
+def test_gpu_decoder_randomized(seed):
+    """Random sizes, qualities, samplings, table optimisation and restart intervals: byte-identical to the oracle."""
+    from imagestitching_b200 import StitchContext
+    rng = np.random.default_rng(900 + seed)
+    ctx = StitchContext(0)
+    for _ in range(10):
+        w, h = int(rng.integers(1, 900)), int(rng.integers(1, 700))
+        kw = dict(quality=int(rng.integers(25, 101)), subsampling=int(rng.integers(0, 3)))
+        if rng.random() < 0.5:
+            kw["optimize"] = True
+        r = rng.random()
+        if r < 0.3:
+            kw["restart_marker_blocks"] = int(rng.integers(1, 40))
+        elif r < 0.45:
+            kw["restart_marker_rows"] = int(rng.integers(1, 4))
+        gray = rng.random() < 0.15
+        if gray:
+            kw.pop("subsampling")
+        data = _jpeg(w, h, seed=int(rng.integers(0, 1 << 30)), gray=gray, **kw)
+        want = J.decode(data)
+        got = ctx.decode_jpeg(data)
+        assert np.array_equal(got, want), f"{w}x{h} {kw} gray={gray}: {np.count_nonzero(got != want)} bytes differ"
+    ctx.close()
+
+
+@pytest.mark.gpu
 def test_gpu_decoder_full_size_photo():
     """A 12 MP file as the page's inputs are (BASELINE configs[1] shape)."""
     from imagestitching_b200 import StitchContext

@@ -67,6 +67,30 @@ def test_gpu_png_equals_oracle_and_is_lossless(case):
 
 
 @pytest.mark.gpu
+def test_gpu_png_randomized_and_flat_canvases():
+    """Random job shapes (band counts, widths, gaps -> white areas) and a canvas that is almost all white."""
+    from imagestitching_b200 import StitchContext
+    rng = np.random.default_rng(77)
+    ctx = StitchContext(0)
+    for k in range(8):
+        n = int(rng.integers(1, 5))
+        dims = [(int(rng.integers(8, 500)), int(rng.integers(8, 400))) for _ in range(n)]
+        bitmaps = [U.synth_image(w, h, 40 * k + i, int(rng.integers(0, 2))) for i, (w, h) in enumerate(dims)]
+        direction = "vertical" if rng.random() < 0.5 else "horizontal"
+        mode = ["min", "max", "original"][int(rng.integers(0, 3))]
+        got = ctx.run(U.page_images(dims, bitmaps), direction, mode=mode, gap=int(rng.integers(0, 21)), platform="ios",
+                      output="rgba+png")
+        assert np.array_equal(_back(got.png), got.rgba)
+        assert got.png == P.encode_rgba(got.rgba), f"job {k}: GPU PNG differs from the oracle writer"
+    # 'original' mode with one tiny and one wide image: the canvas is mostly background
+    dims = [(16, 16), (900, 20)]
+    bitmaps = [np.full((h, w, 4), 255, np.uint8) for w, h in dims]
+    got = ctx.run(U.page_images(dims, bitmaps), "vertical", mode="original", gap=20, platform="ios", output="rgba+png")
+    assert got.png == P.encode_rgba(got.rgba) and len(got.png) < got.rgba.nbytes // 5
+    ctx.close()
+
+
+@pytest.mark.gpu
 def test_gpu_png_capacity_error():
     from imagestitching_b200 import StitchContext, StitchError
     from imagestitching_b200 import _lib as L
