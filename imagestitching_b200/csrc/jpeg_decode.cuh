@@ -237,34 +237,25 @@ __device__ __forceinline__ State decode_range(const DecImage& I, const SmemTable
         }
       }
     }
-    // ---- one symbol ----
+    // ---- one symbol.  DC and AC symbols take the SAME instruction path (table, run and the state update are
+    // selected, not branched on): lanes of a warp sit at different places of their blocks, and a branch here
+    // would run both sides on almost every iteration. ----
     const int comp = b < ny ? 0 : b - ny + 1;
-    int value = 0, zpos = z;
-    bool block_done = false, is_dc = (z == 0);
-    if (is_dc) {
-      const int sz = huff_decode(T, I.td[comp], r) & 15;
-      if (sz) {
-        const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
-        rd_skip(r, sz);
-        value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
-      }
-      z = 1;
-    } else {
-      const int rs = huff_decode(T, 2 + I.ta[comp], r);
-      const int run = rs >> 4, sz = rs & 15;
-      if (sz == 0) {
-        if (run == 15) { z += 16; zpos = -1; if (z > 63) block_done = true; }
-        else { block_done = true; zpos = -1; }
-      } else {
-        z += run;
-        const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
-        rd_skip(r, sz);
-        value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
-        zpos = z;
-        z += 1;
-        if (z > 63) block_done = true;
-      }
+    const bool is_dc = (z == 0);
+    const int rs = huff_decode(T, is_dc ? I.td[comp] : 2 + I.ta[comp], r);
+    const int sz = rs & 15, run = is_dc ? 0 : rs >> 4;
+    int value = 0;
+    if (sz) {
+      const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
+      rd_skip(r, sz);
+      value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
     }
+    // AC with size 0: ZRL (run 15) skips 16 zeros, anything else ends the block; otherwise the coefficient
+    // lands at z + run and the next one is expected behind it
+    const bool coef = is_dc || sz != 0;
+    const int zpos = coef ? z + run : -1;
+    z = is_dc ? 1 : (sz != 0 ? z + run + 1 : (run == 15 ? z + 16 : 64));
+    const bool block_done = z > 63;
     if (r.cnt < r.fake) {
       // the symbol ran into a marker (it was padding) or past the end: drop it
       uint32_t mpos = r.pos;
