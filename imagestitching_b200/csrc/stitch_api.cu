@@ -281,6 +281,197 @@ int parse_jpeg(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::
   return fail(ctx, STITCH_E_BAD_IMAGE, buf);
 }
 
+
+// STITCH_OUT_JPEG (jpeg_kernels.cuh): carve() sizes and places the work buffers in the lane's arena before the
+// compose launch, run() encodes the I420 planes of that launch into the file and fetches its size.
+struct JpegExport {
+  int jpeg_ri = 8, jpeg_q = 100, mcu_x = 0, mcu_y = 0, n_mcu = 0, n_seg = 0;
+  int64_t seg_cap = 0, j_cap = 0;
+  bool out_host = true;
+  uint8_t* j_file = nullptr;
+  int16_t* j_coef = nullptr;
+  uint8_t* j_scratch = nullptr;
+  uint32_t* j_len = nullptr;
+  uint64_t *j_off = nullptr, *j_info = nullptr;
+
+  int carve(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, int cw, int ch, bool want_yuv, bool host,
+            uint8_t** d_yuv) {
+    out_host = host;
+    // JPEG export: carve the lane's arena.  The encoder reads the I420 planes of this launch: the caller's
+    // when STITCH_OUT_YUV420 is set too, planes inside the arena otherwise.
+    jpeg_ri = job->jpeg_restart_interval > 0 ? job->jpeg_restart_interval : 8;
+    jpeg_q = job->jpeg_quality > 0 ? (job->jpeg_quality > 100 ? 100 : job->jpeg_quality) : 100;
+    mcu_x = (cw + 15) / 16; mcu_y = (ch + 15) / 16; n_mcu = mcu_x * mcu_y;
+    n_seg = (n_mcu + jpeg_ri - 1) / jpeg_ri;
+    seg_cap = (int64_t)jpeg_ri * 6 * JPEG_BLOCK_MAX_BYTES + 16;
+    if (jpeg_ri > 65535) return fail(ctx, STITCH_E_BAD_ARG, "JPEG restart interval above 65535");
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const int64_t worst = 1024 + (int64_t)n_mcu * 6 * JPEG_BLOCK_MAX_BYTES + (int64_t)n_seg * 4 + 2;
+    j_cap = job->out_capacity_jpeg < worst ? job->out_capacity_jpeg : worst;
+    const size_t b_yuv = want_yuv ? 0 : up((size_t)res->yuv_bytes);
+    const size_t b_coef = up((size_t)n_mcu * 6 * 64 * sizeof(int16_t));
+    const size_t b_scr = up((size_t)n_seg * (size_t)seg_cap);
+    const size_t b_len = up((size_t)n_seg * 4), b_off = up((size_t)n_seg * 8), b_info = 256;
+    const size_t b_file = out_host ? up((size_t)j_cap) : 0;
+    const size_t need = b_yuv + b_coef + b_scr + b_len + b_off + b_info + b_file;
+    if (ln.jpeg_arena_cap < need) {
+      if (ln.jpeg_arena) {
+        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+        CUDA_TRY(ctx, cudaFree(ln.jpeg_arena));
+      }
+      ln.jpeg_arena = nullptr;
+      ln.jpeg_arena_cap = 0;
+      if (cudaMalloc(&ln.jpeg_arena, need) != cudaSuccess)
+        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG work buffers allocation failed)");
+      ln.jpeg_arena_cap = need;
+    }
+    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+    uint8_t* a = (uint8_t*)ln.jpeg_arena;
+    if (!want_yuv) *d_yuv = a;
+    a += b_yuv;
+    j_coef = (int16_t*)a; a += b_coef;
+    j_scratch = a; a += b_scr;
+    j_len = (uint32_t*)a; a += b_len;
+    j_off = (uint64_t*)a; a += b_off;
+    j_info = (uint64_t*)a; a += b_info;
+    j_file = out_host ? a : (uint8_t*)job->out_jpeg;
+    return STITCH_OK;
+  }
+
+  int run(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, const JobParam& P, int cw, int ch) {
+    stitch::jpeg::Tables tab;
+    stitch::jpeg::build_tables(jpeg_q, &tab);
+    stitch::jpeg::HeaderBytes hdr;
+    const std::vector<uint8_t> hv = stitch::jpeg::header(cw, ch, jpeg_q, jpeg_ri);
+    if (hv.size() > sizeof hdr.b) return fail(ctx, STITCH_E_BAD_ARG, "JPEG header too long");
+    std::memcpy(hdr.b, hv.data(), hv.size());
+    hdr.n = (int32_t)hv.size();
+    const int n_blocks = n_mcu * 6;
+    stitch::jpeg::jpeg_dct_kernel<<<(n_blocks + 127) / 128, 128, 0, ln.stream>>>(P.out_y, P.out_cb, P.out_cr, cw, ch, mcu_x,
+                                                                              mcu_y, tab, j_coef);
+    stitch::jpeg::jpeg_entropy_kernel<<<(n_seg + 3) / 4, 128, 0, ln.stream>>>(j_coef, n_mcu, jpeg_ri, n_seg, tab, j_scratch,
+                                                                             seg_cap, j_len);
+    stitch::jpeg::jpeg_offsets_kernel<<<1, 1024, 0, ln.stream>>>(j_len, n_seg, hdr, j_file, j_cap, j_off, j_info);
+    stitch::jpeg::jpeg_gather_kernel<<<(n_seg + 7) / 8, 256, 0, ln.stream>>>(j_scratch, seg_cap, j_len, j_off, n_seg, j_info,
+                                                                            j_file);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches += 4;
+    res->kernel_launches += 4;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, j_info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    res->jpeg_bytes = (int64_t)ln.jpeg_info_host[0];
+    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer too small; see jpeg_bytes)");
+    if (out_host)
+      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_jpeg, j_file, (size_t)res->jpeg_bytes, cudaMemcpyDeviceToHost, ln.stream));
+    return STITCH_OK;
+  }
+};
+
+// STITCH_OUT_PNG (png_kernels.cuh): same two steps for the PNG file; the encoder reads the RGBA canvas.
+struct PngExport {
+  stitch::png::Params PP;
+  bool out_host = true;
+
+  int carve(StitchCtx* ctx, Lane& ln, const StitchJob* job, const StitchLayout& L, int cw, int ch, bool want_rgba, bool host,
+            uint8_t** d_rgba, int64_t* d_rgba_pitch) {
+    out_host = host;
+    // PNG export: carve the lane's arena; the encoder reads the RGBA canvas of this launch (the caller's, or
+    // one inside the arena when RGBA was not requested).
+    std::memset(&PP, 0, sizeof PP);
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const int nb = (ch + PNG_BAND_ROWS - 1) / PNG_BAND_ROWS;
+    const int64_t band_raw = ((int64_t)cw * 4 + 1) * PNG_BAND_ROWS;
+    const int64_t band_cap = (int64_t)up((size_t)(band_raw * 2 + 1024));
+    const int64_t worst = stitch_png_capacity(&L);
+    const int64_t p_cap = job->out_capacity_png < worst ? job->out_capacity_png : worst;
+    const int64_t c_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
+    const size_t b_canvas = want_rgba ? 0 : up((size_t)(c_pitch * ch));
+    const size_t b_lens = up((size_t)nb * PNG_TAB_STRIDE), b_codes = up((size_t)nb * PNG_TAB_STRIDE * 2);
+    const size_t b_adler = up((size_t)nb * 8), b_scr = (size_t)nb * (size_t)band_cap;
+    const size_t b_blen = up((size_t)nb * 4), b_off = up((size_t)nb * 8), b_info = 256;
+    const size_t b_file = out_host ? up((size_t)p_cap) : 0;
+    const size_t need = b_canvas + b_lens + b_codes + b_adler + b_scr + b_blen + b_off + b_info + b_file;
+    if (ln.png_arena_cap < need) {
+      if (ln.png_arena) {
+        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+        CUDA_TRY(ctx, cudaFree(ln.png_arena));
+      }
+      ln.png_arena = nullptr;
+      ln.png_arena_cap = 0;
+      if (cudaMalloc(&ln.png_arena, need) != cudaSuccess)
+        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG work buffers allocation failed)");
+      ln.png_arena_cap = need;
+    }
+    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+    uint8_t* a = (uint8_t*)ln.png_arena;
+    if (!want_rgba) { *d_rgba = a; *d_rgba_pitch = c_pitch; }
+    a += b_canvas;
+    PP.lens = a; a += b_lens;
+    PP.codes = (uint16_t*)a; a += b_codes;
+    PP.adler = (uint32_t*)a; a += b_adler;
+    PP.scratch = a; a += b_scr;
+    PP.blen = (uint32_t*)a; a += b_blen;
+    PP.off = (uint64_t*)a; a += b_off;
+    PP.info = (uint64_t*)a; a += b_info;
+    PP.file = out_host ? a : (uint8_t*)job->out_png;
+    PP.cap = p_cap;
+    PP.band_cap = band_cap;
+    PP.w = cw; PP.h = ch; PP.nb = nb;
+    PP.rgba = *d_rgba;
+    PP.pitch = *d_rgba_pitch;
+    return STITCH_OK;
+  }
+
+  int run(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, int cw, int ch) {
+    stitch::png::HeaderBytes hdr;
+    std::memset(&hdr, 0, sizeof hdr);
+    const uint8_t sig[16] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A, 0, 0, 0, 13, 'I', 'H', 'D', 'R'};
+    std::memcpy(hdr.b, sig, 16);
+    auto be32 = [](uint8_t* q, uint32_t v) { q[0] = v >> 24; q[1] = v >> 16; q[2] = v >> 8; q[3] = (uint8_t)v; };
+    be32(hdr.b + 16, (uint32_t)cw);
+    be32(hdr.b + 20, (uint32_t)ch);
+    hdr.b[24] = 8; hdr.b[25] = 6;   // 8 bit, colour type 6 (RGBA); compression 0, filter 0, no interlace
+    {
+      uint32_t c = 0xFFFFFFFFu;   // CRC-32 of 'IHDR' + 13 bytes
+      for (int i = 12; i < 29; ++i) {
+        c ^= hdr.b[i];
+        for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+      }
+      be32(hdr.b + 29, c ^ 0xFFFFFFFFu);
+    }
+    hdr.n = 33;
+    {
+      // x^(2^k) mod P, reflected: x2n[0] = x, each next one the square of the previous
+      auto mul = [](uint32_t a, uint32_t b) {
+        uint32_t m = 1u << 31, p = 0;
+        for (;;) {
+          if (a & m) { p ^= b; if ((a & (m - 1)) == 0) break; }
+          m >>= 1;
+          b = (b & 1u) ? (b >> 1) ^ 0xEDB88320u : b >> 1;
+        }
+        return p;
+      };
+      uint32_t p = 1u << 30;
+      PP.x2n[0] = p;
+      for (int k = 1; k < 32; ++k) { p = mul(p, p); PP.x2n[k] = p; }
+    }
+    stitch::png::png_hist_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
+    stitch::png::png_encode_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
+    stitch::png::png_offsets_kernel<<<1, 1024, 0, ln.stream>>>(PP, hdr);
+    stitch::png::png_gather_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->launches += 4;
+    res->kernel_launches += 4;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, PP.info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    res->png_bytes = (int64_t)ln.jpeg_info_host[0];
+    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG output buffer too small; see png_bytes)");
+    if (out_host)
+      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_png, PP.file, (size_t)res->png_bytes, cudaMemcpyDeviceToHost, ln.stream));
+    return STITCH_OK;
+  }
+};
+
 int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res) {
   if (!ctx || !job || !res) return fail(ctx, STITCH_E_BAD_ARG, "null argument");
   if (job->n <= 0) return fail(ctx, STITCH_E_EMPTY, "empty image list");  // P:1189
@@ -428,99 +619,18 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     if (want_rgba) d_rgba = (uint8_t*)job->out_rgba;
     if (want_yuv) d_yuv = (uint8_t*)job->out_yuv;
   }
-  // JPEG export: carve the lane's arena.  The encoder reads the I420 planes of this launch: the caller's
-  // when STITCH_OUT_YUV420 is set too, planes inside the arena otherwise.
+  // JPEG / PNG exports carve their work buffers before the launch: the encoders read the I420 planes / the RGBA
+  // canvas of this launch -- the caller's when requested too, buffers inside the lane's arena otherwise.
   const int64_t cwh = (cw + 1) / 2, chh = (ch + 1) / 2;
-  const int jpeg_ri = job->jpeg_restart_interval > 0 ? job->jpeg_restart_interval : 8;
-  const int jpeg_q = job->jpeg_quality > 0 ? (job->jpeg_quality > 100 ? 100 : job->jpeg_quality) : 100;
-  const int mcu_x = (cw + 15) / 16, mcu_y = (ch + 15) / 16, n_mcu = mcu_x * mcu_y;
-  const int n_seg = (n_mcu + jpeg_ri - 1) / jpeg_ri;
-  const int64_t seg_cap = (int64_t)jpeg_ri * 6 * JPEG_BLOCK_MAX_BYTES + 16;
-  uint8_t* j_file = nullptr;
-  int16_t* j_coef = nullptr;
-  uint8_t* j_scratch = nullptr;
-  uint32_t* j_len = nullptr;
-  uint64_t *j_off = nullptr, *j_info = nullptr;
-  int64_t j_cap = 0;
+  JpegExport jx;
+  PngExport px;
   if (want_jpeg) {
-    if (jpeg_ri > 65535) return fail(ctx, STITCH_E_BAD_ARG, "JPEG restart interval above 65535");
-    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    const int64_t worst = 1024 + (int64_t)n_mcu * 6 * JPEG_BLOCK_MAX_BYTES + (int64_t)n_seg * 4 + 2;
-    j_cap = job->out_capacity_jpeg < worst ? job->out_capacity_jpeg : worst;
-    const size_t b_yuv = want_yuv ? 0 : up((size_t)res->yuv_bytes);
-    const size_t b_coef = up((size_t)n_mcu * 6 * 64 * sizeof(int16_t));
-    const size_t b_scr = up((size_t)n_seg * (size_t)seg_cap);
-    const size_t b_len = up((size_t)n_seg * 4), b_off = up((size_t)n_seg * 8), b_info = 256;
-    const size_t b_file = out_host ? up((size_t)j_cap) : 0;
-    const size_t need = b_yuv + b_coef + b_scr + b_len + b_off + b_info + b_file;
-    if (ln.jpeg_arena_cap < need) {
-      if (ln.jpeg_arena) {
-        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-        CUDA_TRY(ctx, cudaFree(ln.jpeg_arena));
-      }
-      ln.jpeg_arena = nullptr;
-      ln.jpeg_arena_cap = 0;
-      if (cudaMalloc(&ln.jpeg_arena, need) != cudaSuccess)
-        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG work buffers allocation failed)");
-      ln.jpeg_arena_cap = need;
-    }
-    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
-    uint8_t* a = (uint8_t*)ln.jpeg_arena;
-    if (!want_yuv) d_yuv = a;
-    a += b_yuv;
-    j_coef = (int16_t*)a; a += b_coef;
-    j_scratch = a; a += b_scr;
-    j_len = (uint32_t*)a; a += b_len;
-    j_off = (uint64_t*)a; a += b_off;
-    j_info = (uint64_t*)a; a += b_info;
-    j_file = out_host ? a : (uint8_t*)job->out_jpeg;
+    st = jx.carve(ctx, ln, job, res, cw, ch, want_yuv, out_host, &d_yuv);
+    if (st != STITCH_OK) return st;
   }
-  // PNG export: carve the lane's arena; the encoder reads the RGBA canvas of this launch (the caller's, or
-  // one inside the arena when RGBA was not requested).
-  stitch::png::Params PP;
-  std::memset(&PP, 0, sizeof PP);
   if (want_png) {
-    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    const int nb = (ch + PNG_BAND_ROWS - 1) / PNG_BAND_ROWS;
-    const int64_t band_raw = ((int64_t)cw * 4 + 1) * PNG_BAND_ROWS;
-    const int64_t band_cap = (int64_t)up((size_t)(band_raw * 2 + 1024));
-    const int64_t worst = stitch_png_capacity(&L);
-    const int64_t p_cap = job->out_capacity_png < worst ? job->out_capacity_png : worst;
-    const int64_t c_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
-    const size_t b_canvas = want_rgba ? 0 : up((size_t)(c_pitch * ch));
-    const size_t b_lens = up((size_t)nb * PNG_TAB_STRIDE), b_codes = up((size_t)nb * PNG_TAB_STRIDE * 2);
-    const size_t b_adler = up((size_t)nb * 8), b_scr = (size_t)nb * (size_t)band_cap;
-    const size_t b_blen = up((size_t)nb * 4), b_off = up((size_t)nb * 8), b_info = 256;
-    const size_t b_file = out_host ? up((size_t)p_cap) : 0;
-    const size_t need = b_canvas + b_lens + b_codes + b_adler + b_scr + b_blen + b_off + b_info + b_file;
-    if (ln.png_arena_cap < need) {
-      if (ln.png_arena) {
-        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-        CUDA_TRY(ctx, cudaFree(ln.png_arena));
-      }
-      ln.png_arena = nullptr;
-      ln.png_arena_cap = 0;
-      if (cudaMalloc(&ln.png_arena, need) != cudaSuccess)
-        return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG work buffers allocation failed)");
-      ln.png_arena_cap = need;
-    }
-    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
-    uint8_t* a = (uint8_t*)ln.png_arena;
-    if (!want_rgba) { d_rgba = a; d_rgba_pitch = c_pitch; }
-    a += b_canvas;
-    PP.lens = a; a += b_lens;
-    PP.codes = (uint16_t*)a; a += b_codes;
-    PP.adler = (uint32_t*)a; a += b_adler;
-    PP.scratch = a; a += b_scr;
-    PP.blen = (uint32_t*)a; a += b_blen;
-    PP.off = (uint64_t*)a; a += b_off;
-    PP.info = (uint64_t*)a; a += b_info;
-    PP.file = out_host ? a : (uint8_t*)job->out_png;
-    PP.cap = p_cap;
-    PP.band_cap = band_cap;
-    PP.w = cw; PP.h = ch; PP.nb = nb;
-    PP.rgba = d_rgba;
-    PP.pitch = d_rgba_pitch;
+    st = px.carve(ctx, ln, job, L, cw, ch, want_rgba, out_host, &d_rgba, &d_rgba_pitch);
+    if (st != STITCH_OK) return st;
   }
   const bool planes = want_yuv || want_jpeg;
   const bool canvas = want_rgba || want_png;
@@ -550,83 +660,15 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     if (want_yuv)
       CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ln.stream));
   }
-  // [5b] export as a JPEG file (U:211-221 with fileType 'jpg'): DCT + quantise, entropy-code one restart
-  // segment per warp, scan the segment sizes, gather.  The file size must reach the host before the call
-  // returns, so a JPEG job is complete when this function returns (also under stitch_submit).
+  // [5b] / [5c] export as a file (U:211-221): fileType 'jpg', or the 'png' the page asks for (P:1579).  The file
+  // size has to reach the host, so such a job is complete when this function returns (also under stitch_submit).
   if (want_jpeg) {
-    stitch::jpeg::Tables tab;
-    stitch::jpeg::build_tables(jpeg_q, &tab);
-    stitch::jpeg::HeaderBytes hdr;
-    const std::vector<uint8_t> hv = stitch::jpeg::header(cw, ch, jpeg_q, jpeg_ri);
-    if (hv.size() > sizeof hdr.b) return fail(ctx, STITCH_E_BAD_ARG, "JPEG header too long");
-    std::memcpy(hdr.b, hv.data(), hv.size());
-    hdr.n = (int32_t)hv.size();
-    const int n_blocks = n_mcu * 6;
-    stitch::jpeg::jpeg_dct_kernel<<<(n_blocks + 127) / 128, 128, 0, ln.stream>>>(P.out_y, P.out_cb, P.out_cr, cw, ch, mcu_x,
-                                                                              mcu_y, tab, j_coef);
-    stitch::jpeg::jpeg_entropy_kernel<<<(n_seg + 3) / 4, 128, 0, ln.stream>>>(j_coef, n_mcu, jpeg_ri, n_seg, tab, j_scratch,
-                                                                             seg_cap, j_len);
-    stitch::jpeg::jpeg_offsets_kernel<<<1, 1024, 0, ln.stream>>>(j_len, n_seg, hdr, j_file, j_cap, j_off, j_info);
-    stitch::jpeg::jpeg_gather_kernel<<<(n_seg + 7) / 8, 256, 0, ln.stream>>>(j_scratch, seg_cap, j_len, j_off, n_seg, j_info,
-                                                                            j_file);
-    CUDA_TRY(ctx, cudaGetLastError());
-    ctx->launches += 4;
-    res->kernel_launches += 4;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, j_info, 16, cudaMemcpyDeviceToHost, ln.stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-    res->jpeg_bytes = (int64_t)ln.jpeg_info_host[0];
-    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer too small; see jpeg_bytes)");
-    if (out_host)
-      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_jpeg, j_file, (size_t)res->jpeg_bytes, cudaMemcpyDeviceToHost, ln.stream));
+    st = jx.run(ctx, ln, job, res, P, cw, ch);
+    if (st != STITCH_OK) return st;
   }
-  // [5c] export as the PNG file the page asks for (U:211-221 with fileType 'png', P:1579): histogram + code per
-  // band, encode, offsets, gather + CRC.  Like the JPEG export, complete when this function returns.
   if (want_png) {
-    stitch::png::HeaderBytes hdr;
-    std::memset(&hdr, 0, sizeof hdr);
-    const uint8_t sig[16] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A, 0, 0, 0, 13, 'I', 'H', 'D', 'R'};
-    std::memcpy(hdr.b, sig, 16);
-    auto be32 = [](uint8_t* q, uint32_t v) { q[0] = v >> 24; q[1] = v >> 16; q[2] = v >> 8; q[3] = (uint8_t)v; };
-    be32(hdr.b + 16, (uint32_t)cw);
-    be32(hdr.b + 20, (uint32_t)ch);
-    hdr.b[24] = 8; hdr.b[25] = 6;   // 8 bit, colour type 6 (RGBA); compression 0, filter 0, no interlace
-    {
-      uint32_t c = 0xFFFFFFFFu;   // CRC-32 of 'IHDR' + 13 bytes
-      for (int i = 12; i < 29; ++i) {
-        c ^= hdr.b[i];
-        for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
-      }
-      be32(hdr.b + 29, c ^ 0xFFFFFFFFu);
-    }
-    hdr.n = 33;
-    {
-      // x^(2^k) mod P, reflected: x2n[0] = x, each next one the square of the previous
-      auto mul = [](uint32_t a, uint32_t b) {
-        uint32_t m = 1u << 31, p = 0;
-        for (;;) {
-          if (a & m) { p ^= b; if ((a & (m - 1)) == 0) break; }
-          m >>= 1;
-          b = (b & 1u) ? (b >> 1) ^ 0xEDB88320u : b >> 1;
-        }
-        return p;
-      };
-      uint32_t p = 1u << 30;
-      PP.x2n[0] = p;
-      for (int k = 1; k < 32; ++k) { p = mul(p, p); PP.x2n[k] = p; }
-    }
-    stitch::png::png_hist_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
-    stitch::png::png_encode_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
-    stitch::png::png_offsets_kernel<<<1, 1024, 0, ln.stream>>>(PP, hdr);
-    stitch::png::png_gather_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
-    CUDA_TRY(ctx, cudaGetLastError());
-    ctx->launches += 4;
-    res->kernel_launches += 4;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, PP.info, 16, cudaMemcpyDeviceToHost, ln.stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-    res->png_bytes = (int64_t)ln.jpeg_info_host[0];
-    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG output buffer too small; see png_bytes)");
-    if (out_host)
-      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_png, PP.file, (size_t)res->png_bytes, cudaMemcpyDeviceToHost, ln.stream));
+    st = px.run(ctx, ln, job, res, cw, ch);
+    if (st != STITCH_OK) return st;
   }
   return STITCH_OK;
 }
