@@ -323,64 +323,97 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_c
   I.state[i] = make_uint4(e.byte, pack_state(e), started, 0u);
 }
 
-// D2: one synchronisation round.  Inside a block the threads iterate until their chain is consistent with the
-// state their first thread got from the previous block (as it was when the kernel started); the host
-// relaunches until no end state changes any more.
+// D2: one synchronisation round.  Inside a block the subsequences iterate until their chain is consistent with
+// the state the first one got from the previous block (as it was when the kernel started); the host relaunches
+// until no block's last end state moves any more.  In every iteration the subsequences that have to be decoded
+// again (their input state moved) are COMPACTED onto the first threads, so a few stragglers cost a few warps,
+// not the whole block.
 __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_constant__ DecBatch B) {
   __shared__ SmemTables T;
-  __shared__ uint2 sh_state[JDEC_THREADS + 1];   // [t + 1] = end state of thread t; [0] = predecessor block's last
-  __shared__ int sh_dirty[JDEC_THREADS + 1];     // [t + 1]: thread t's end state changed in the last iteration
+  __shared__ uint2 sh_state[JDEC_THREADS + 1];   // [s + 1] = end state of subsequence s; [0] = predecessor block's last
+  __shared__ uint32_t sh_cnt[JDEC_THREADS];      // blocks started by subsequence s
+  __shared__ uint8_t sh_dirty[2][JDEC_THREADS + 1];   // [s]: the INPUT state of subsequence s moved
+  __shared__ uint16_t sh_list[JDEC_THREADS];
+  __shared__ int sh_warp_n[JDEC_THREADS / 32];
+  __shared__ int sh_last_moved;
   const DecImage& I = B.img[blockIdx.y];
   if (blockIdx.x * JDEC_THREADS >= (unsigned)I.n_sub) return;
   build_tables(I.tab, T);
-  const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
-  const bool live = i < (uint32_t)I.n_sub;
-  const int t = threadIdx.x;
-  uint4 mine = live ? I.state[i] : make_uint4(0, 0, 0, 0);
-  sh_state[t + 1] = make_uint2(mine.x, mine.y);
-  // first round: everybody re-decodes from the predecessor's state; later rounds: only the chain that
-  // starts at a first thread whose input (the previous block's last end state) has moved since it was used
-  sh_dirty[t + 1] = B.round == 0 ? 1 : 0;
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  const uint32_t base = blockIdx.x * JDEC_THREADS;
+  const int n_here = min(JDEC_THREADS, I.n_sub - (int)base);
+  {
+    const uint4 mine = t < n_here ? I.state[base + t] : make_uint4(0, 0, 0, 0);
+    sh_state[t + 1] = make_uint2(mine.x, mine.y);
+    sh_cnt[t] = mine.z;
+    // first round: everybody re-decodes from the predecessor's state; later rounds: only the chain that
+    // starts at a first subsequence whose input (the previous block's last end state) has moved since it was used
+    sh_dirty[0][t + 1] = (B.round == 0 && t + 1 < n_here) ? 1 : 0;
+    sh_dirty[1][t + 1] = 0;
+  }
   if (t == 0) {
     uint2 in = make_uint2(0u, 0u);               // the scan starts at byte 0, bit 0, block 0, DC
-    if (i > 0) {
-      const uint4 p = I.state[i - 1];
+    if (base > 0) {
+      const uint4 p = I.state[base - 1];
       in = make_uint2(p.x, p.y);
     }
     sh_state[0] = in;
     const uint2 was = I.consumed[blockIdx.x];
-    sh_dirty[0] = (B.round == 0 || was.x != in.x || was.y != in.y) ? 1 : 0;
+    sh_dirty[0][0] = (B.round == 0 || was.x != in.x || was.y != in.y) ? 1 : 0;
+    sh_dirty[1][0] = 0;
     I.consumed[blockIdx.x] = in;
+    sh_last_moved = 0;
   }
   __syncthreads();
-  bool changed_ever = false, settled = false;
+  int cur = 0;
+  bool settled = false;
   for (int iter = 0; iter < JDEC_THREADS + 1; ++iter) {
-    const bool work = live && sh_dirty[t] != 0;
-    uint2 mine_new = make_uint2(mine.x, mine.y);
-    uint32_t started = mine.z;
-    if (work) {
-      const uint2 ps = sh_state[t];
-      const State e = decode_range<false>(I, T, unpack_state(ps.x, ps.y), (i + 1) * JDEC_SUB, &started, 0);
-      mine_new = make_uint2(e.byte, pack_state(e));
+    // compact the dirty subsequences: warp ballots + a prefix over the 8 warps
+    const bool work = t < n_here && sh_dirty[cur][t] != 0;
+    const uint32_t m = __ballot_sync(0xffffffffu, work);
+    if (lane == 0) sh_warp_n[wp] = __popc(m);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < JDEC_THREADS / 32; ++k) {
+      const int c = sh_warp_n[k];
+      if (k < wp) before += c;
+      total += c;
+    }
+    if (total == 0) { settled = true; break; }
+    if (work) sh_list[before + __popc(m & ((1u << lane) - 1u))] = (uint16_t)t;
+    sh_dirty[cur ^ 1][t] = 0;
+    if (t == 0) sh_dirty[cur ^ 1][JDEC_THREADS] = 0;
+    __syncthreads();
+    uint2 fresh = make_uint2(0u, 0u);
+    uint32_t started = 0;
+    int s = -1;
+    if (t < total) {
+      s = sh_list[t];
+      const uint2 ps = sh_state[s];
+      const State e = decode_range<false>(I, T, unpack_state(ps.x, ps.y), (base + s + 1) * JDEC_SUB, &started, 0);
+      fresh = make_uint2(e.byte, pack_state(e));
     }
     __syncthreads();
-    const bool changed = work && (mine_new.x != mine.x || mine_new.y != mine.y);
-    if (work) {
-      mine.x = mine_new.x;
-      mine.y = mine_new.y;
-      mine.z = started;
-      sh_state[t + 1] = mine_new;
+    if (s >= 0) {
+      const uint2 old = sh_state[s + 1];
+      const bool moved = fresh.x != old.x || fresh.y != old.y;
+      sh_state[s + 1] = fresh;
+      sh_cnt[s] = started;
+      if (moved) {
+        sh_dirty[cur ^ 1][s + 1] = 1;
+        if (s == n_here - 1) sh_last_moved = 1;
+      }
     }
-    sh_dirty[t + 1] = changed ? 1 : 0;
-    if (t == 0) sh_dirty[0] = 0;
-    changed_ever |= changed;
-    if (!__syncthreads_or(changed ? 1 : 0)) { settled = true; break; }
+    __syncthreads();
+    cur ^= 1;
   }
-  if (live) I.state[i] = mine;
-  if (!settled && t == 0) atomicOr(B.changed, 1u);   // ran out of iterations with changes pending
-  // the LAST thread's end state feeds the next block: if it moved, another round is needed
-  if (live && changed_ever && (t == JDEC_THREADS - 1 || i == (uint32_t)I.n_sub - 1) && i + 1 < (uint32_t)I.n_sub)
-    atomicOr(B.changed, 1u);
+  if (t < n_here) {
+    const uint2 st = sh_state[t + 1];
+    I.state[base + t] = make_uint4(st.x, st.y, sh_cnt[t], 0u);
+  }
+  // the LAST subsequence's end state feeds the next block: if it moved, another round is needed
+  if (t == 0 && (sh_last_moved || !settled) && base + n_here < (uint32_t)I.n_sub) atomicOr(B.changed, 1u);
 }
 
 // D3: exclusive scan of the blocks-started counts (one block per image).
