@@ -256,7 +256,8 @@ extern "C" int64_t stitch_png_capacity(const StitchLayout* layout) {
   if (!layout) return 0;
   const int64_t w = (int64_t)layout->canvas_w, h = (int64_t)layout->canvas_h;
   const int64_t bands = (h + 7) / 8;
-  return 33 + 12 + bands * (12 + 160 + 8) + (h * (w * 4 + 1) * 15 + 7) / 8 + 64;
+  // per band: chunk framing 12, block header (1239 bits) + end of block + stored block or Adler + zlib header < 192
+  return 33 + 12 + bands * (12 + 192) + (h * (w * 4 + 1) * 15 + 7) / 8 + 64;
 }
 
 // Preview geometry: U:17-24 (createHighResCanvas) + P:1599-1603.

@@ -3,14 +3,15 @@
 // (RFC 1951).  The encoder's free choices are made for parallelism:
 //   * Paeth filter on every row (the predictor only looks at the canvas, never at compressed state);
 //   * the rows are cut into bands of PNG_BAND_ROWS rows, one CTA each; a band is ONE dynamic-Huffman block of
-//     literals (no LZ77 matches) + -- except for the last band -- an empty stored block that byte-aligns the
-//     stream, and is its own IDAT chunk, so bands are coded, CRC'd and placed independently;
+//     literals and run-length matches (distance 1; see round_tokens) + -- except for the last band -- an empty
+//     stored block that byte-aligns the stream, and is its own IDAT chunk, so bands are coded, CRC'd and placed
+//     independently;
 //   * the Adler-32 of the whole stream is combined from per-band sums.
-// P1 png_hist_kernel    filtered-byte histogram + Adler partial sums per band, then warp 0 builds the length-
+// P1 png_hist_kernel    filter + tokens (kept for P2), token histogram + Adler partial sums per band, then the length-
 //                       limited Huffman code (merge the two smallest (frequency, index); too deep -> halve the
 //                       frequencies and rebuild) and its canonical, bit-reversed codes
-// P2 png_encode_kernel  block header + codes: per chunk every thread codes 2 pixels into registers, a CTA scan of
-//                       the bit counts places them in a shared-memory bit window that is flushed as words
+// P2 png_encode_kernel  block header + codes: per round every thread codes the tokens of 2 pixels into registers, a
+//                       CTA scan of the bit counts places them in a shared-memory bit window flushed as words
 // P3 png_offsets_kernel scan of the band sizes, Adler combine, signature + IHDR + IEND
 // P4 png_gather_kernel  chunk length, 'IDAT', data, CRC-32 (32 lanes over 1/32 of the chunk each, combined
 //                       with x^(8n) mod P multiplications)
@@ -25,7 +26,8 @@ namespace stitch {
 namespace png {
 
 #define PNG_BAND_ROWS 8
-#define PNG_NSYM 257
+#define PNG_NSYM 286           // 256 literals + end of block + 29 length codes
+#define PNG_ROUND_PX 512        // pixels per tokenisation round (2 per thread); runs never cross a round
 #define PNG_THREADS 256
 #define PNG_TAB_STRIDE 320     // per-band stride of the length / code tables
 #define PNG_CRC_POLY 0xEDB88320u
@@ -42,6 +44,10 @@ struct Params {
   uint8_t* lens;               // [nb][PNG_TAB_STRIDE]
   uint16_t* codes;             // [nb][PNG_TAB_STRIDE]
   uint32_t* adler;             // [nb][2]: Adler pair of the band's bytes started from (1, 0)
+  uint32_t* nmatch;            // [nb] match tokens in the band (0: the distance alphabet is empty)
+  uint32_t* fpx;               // [h][w] filtered pixels (P1 -> P2)
+  uint64_t* desc;              // [nb][rounds][PNG_THREADS] token descriptors (P1 -> P2), see pack_tokens
+  int32_t rounds;              // rounds per band = ceil(PNG_BAND_ROWS * w / PNG_ROUND_PX)
   uint8_t* scratch;            // [nb][band_cap] coded bands
   int64_t band_cap;
   uint32_t* blen;              // [nb] bytes of zlib data per band (the last one includes the 4 Adler bytes)
@@ -79,6 +85,148 @@ __device__ __forceinline__ uint32_t filter_px(const Params& P, int j, int y) {
   return out;
 }
 
+
+// ---- run-length tokens of one round ----
+// LZ77 restricted to runs: inside a round (PNG_ROUND_PX pixels in raster order, the filter-type byte in front
+// of a row's first pixel) a maximal run of equal bytes is its first byte + matches of distance 1: chunks of up
+// to 258 bytes, a chunk shorter than 3 stays literal.  A token depends on its round only, so the histogram and
+// the encode kernel (and the sequential writer of the test tree) derive the same tokens independently.
+struct RoundSmem {
+  uint8_t bytes[PNG_ROUND_PX * 4 + PNG_ROUND_PX + 16];   // worst case: every pixel starts a row (w = 1)
+  int warp_a[PNG_THREADS / 32], warp_b[PNG_THREADS / 32];
+};
+struct ThreadTokens {
+  // Ten slots, statically indexed: slot 5e is the filter-type byte in front of pixel e (present when the pixel
+  // starts a row), slots 5e+1..5e+4 its four bytes.  `valid` marks the slots that exist.
+  uint32_t valid;
+  int off;            // index of the first valid slot's byte in the round
+  uint8_t v[10];      // byte values
+  int16_t tok[10];    // -1: covered by a match (or slot absent); 0..255: literal; 0x1000 | len: match of distance 1
+};
+
+__device__ __forceinline__ int multiples_before(int q, int w) { return (q + w - 1) / w; }   // multiples of w in [0, q)
+
+__device__ __forceinline__ void round_tokens(const Params& P, int y0, int npx, int base, RoundSmem& rs, ThreadTokens& tt) {
+  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+  const int q_end = min(base + PNG_ROUND_PX, npx);
+  const int n_round = 4 * (q_end - base) + multiples_before(q_end, P.w) - multiples_before(base, P.w);
+  const int q0 = base + 2 * t;
+  tt.valid = 0;
+  tt.off = q0 < q_end ? 4 * (q0 - base) + multiples_before(q0, P.w) - multiples_before(base, P.w) : n_round;
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    const int q = q0 + e;
+    uint32_t f = 0;
+    if (q < q_end) {
+      const int r = q / P.w, j = q - r * P.w;
+      tt.valid |= (j == 0 ? 0x1fu : 0x1eu) << (5 * e);
+      f = filter_px(P, j, y0 + r);
+    }
+    tt.v[5 * e] = 4;                                // the row's filter-type byte (Paeth)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) tt.v[5 * e + 1 + k] = (uint8_t)(f >> (8 * k));
+  }
+#pragma unroll
+  for (int i = 0; i < 10; ++i)
+    if (tt.valid >> i & 1u) rs.bytes[tt.off + __popc(tt.valid & ((1u << i) - 1u))] = tt.v[i];
+  __syncthreads();
+  // run starts inside my range; the last one at or before it and the first one behind it come from scans
+  int ls = -1, fs = 0x7fffffff;
+  uint32_t startmask = 0;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    if (tt.valid >> i & 1u) {
+      const int g = tt.off + __popc(tt.valid & ((1u << i) - 1u));
+      const bool st = g == 0 || tt.v[i] != rs.bytes[g - 1];
+      if (st) { startmask |= 1u << i; ls = g; fs = min(fs, g); }
+    }
+  }
+  int a = ls, b = fs;                               // inclusive scans: max from the left, min from the right
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int ya = __shfl_up_sync(0xffffffffu, a, d), yb = __shfl_down_sync(0xffffffffu, b, d);
+    if (lane >= d) a = max(a, ya);
+    if (lane + d < 32) b = min(b, yb);
+  }
+  if (lane == 31) rs.warp_a[wp] = a;
+  if (lane == 0) rs.warp_b[wp] = b;
+  __syncthreads();
+  int before = __shfl_up_sync(0xffffffffu, a, 1), after = __shfl_down_sync(0xffffffffu, b, 1);
+  if (lane == 0) before = -1;
+  if (lane == 31) after = 0x7fffffff;
+#pragma unroll
+  for (int k = 0; k < PNG_THREADS / 32; ++k) {
+    if (k < wp) before = max(before, rs.warp_a[k]);
+    if (k > wp) after = min(after, rs.warp_b[k]);
+  }
+  after = min(after, n_round);
+  // per byte: run start s (walking forward) and run end e (walking backward) -> token
+  int e_of[10];
+  {
+    int cur = after;
+#pragma unroll
+    for (int i = 9; i >= 0; --i) {
+      e_of[i] = cur;
+      if (startmask >> i & 1u) cur = tt.off + __popc(tt.valid & ((1u << i) - 1u));
+    }
+  }
+  int cur_s = before;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    int tk = -1;
+    if (tt.valid >> i & 1u) {
+      const int g = tt.off + __popc(tt.valid & ((1u << i) - 1u));
+      if (startmask >> i & 1u) cur_s = g;
+      const int k = g - cur_s, L = e_of[i] - cur_s;
+      tk = tt.v[i];
+      if (k >= 1) {
+        const int c = (k - 1) / 258, o = (k - 1) - 258 * c;
+        const int clen = min(258, (L - 1) - 258 * c);
+        if (clen >= 3) tk = (o == 0) ? (0x1000 | clen) : -1;
+      }
+    }
+    tt.tok[i] = (int16_t)tk;
+  }
+  __syncthreads();                                  // rs is reused by the next round
+}
+
+// length 3..258 -> literal/length symbol 257..285 and its extra bits (RFC 1951 3.2.5)
+__device__ __forceinline__ int len_symbol(int len, int* extra, int* nextra) {
+  int c, e = 0, ne = 0;
+  if (len < 11) c = 254 + len;
+  else if (len == 258) c = 285;
+  else {
+    const int n = len - 3;
+    ne = (31 - __clz(n)) - 2;
+    c = 257 + 4 * ne + (n >> ne);
+    e = n & ((1 << ne) - 1);
+  }
+  *extra = e;
+  *nextra = ne;
+  return c;
+}
+
+// A thread's tokens of one round in 44 bits, so that P2 neither filters nor tokenises again: slot i has class
+// (d >> 2i) & 3 -- 0 nothing to emit, 1 literal, 2 match -- and the k-th match of the thread (at most 3 in 10
+// bytes) has length 3 + ((d >> (20 + 8k)) & 255).
+__device__ __forceinline__ uint64_t pack_tokens(const ThreadTokens& tt) {
+  uint64_t d = 0;
+  int mi = 0;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const int tk = tt.tok[i];
+    if (tk < 0) continue;
+    if (tk & 0x1000) {
+      d |= 2ull << (2 * i);
+      d |= (uint64_t)((tk & 0xfff) - 3) << (20 + 8 * mi);
+      ++mi;
+    } else {
+      d |= 1ull << (2 * i);
+    }
+  }
+  return d;
+}
+
 // ---- P1 ----
 __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_constant__ Params P) {
   __shared__ uint32_t hist[PNG_THREADS / 32][PNG_NSYM + 3];
@@ -91,30 +239,45 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
   const int64_t rowlen = (int64_t)P.w * 4 + 1, n = rowlen * rows;
   for (int i = t; i < (PNG_THREADS / 32) * (PNG_NSYM + 3); i += PNG_THREADS) (&hist[0][0])[i] = 0;
   __syncthreads();
-  uint32_t zeros = 0;
+  __shared__ RoundSmem rs;
+  __shared__ uint32_t s_nmatch;
+  if (t == 0) s_nmatch = 0;
+  uint32_t zeros = 0, matches = 0;
   unsigned long long s1 = 0, s2 = 0;
   const int npx = rows * P.w;
-  int r = t / P.w, j = t - r * P.w;
-  for (int q = t; q < npx; q += PNG_THREADS) {
-    const uint32_t f = filter_px(P, j, y0 + r);
-    const int64_t pos = r * rowlen + 1 + (int64_t)j * 4;
+  for (int base = 0; base < npx; base += PNG_ROUND_PX) {
+    ThreadTokens tt;
+    round_tokens(P, y0, npx, base, rs, tt);
+    {
+      const int q0 = base + 2 * t;
+      uint32_t* fp = P.fpx + (int64_t)y0 * P.w + q0;
+      if (q0 < npx) fp[0] = (uint32_t)tt.v[1] | (uint32_t)tt.v[2] << 8 | (uint32_t)tt.v[3] << 16 | (uint32_t)tt.v[4] << 24;
+      if (q0 + 1 < npx) fp[1] = (uint32_t)tt.v[6] | (uint32_t)tt.v[7] << 8 | (uint32_t)tt.v[8] << 16 | (uint32_t)tt.v[9] << 24;
+      P.desc[((int64_t)band * P.rounds + base / PNG_ROUND_PX) * PNG_THREADS + t] = pack_tokens(tt);
+    }
+    const int64_t rpos = 4 * (int64_t)base + multiples_before(base, P.w);   // stream position of the round
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const uint32_t d = (f >> (8 * k)) & 255u;
-      if (d == 0) ++zeros;
-      else {
-        atomicAdd(&hist[wp][d], 1u);
+    for (int i = 0; i < 10; ++i) {
+      if (!(tt.valid >> i & 1u)) continue;
+      const uint32_t d = tt.v[i];
+      if (d) {
         s1 += d;
-        s2 += (unsigned long long)(n - (pos + k)) * d;
+        s2 += (unsigned long long)(n - (rpos + tt.off + __popc(tt.valid & ((1u << i) - 1u)))) * d;
+      }
+      const int tk = tt.tok[i];
+      if (tk < 0) continue;
+      if (tk & 0x1000) {
+        int ex, nex;
+        atomicAdd(&hist[wp][len_symbol(tk & 0xfff, &ex, &nex)], 1u);
+        ++matches;
+      } else if (tk == 0) {
+        ++zeros;
+      } else {
+        atomicAdd(&hist[wp][tk], 1u);
       }
     }
-    if (j == 0) {                               // the row's filter-type byte (4 = Paeth)
-      s1 += 4;
-      s2 += (unsigned long long)(n - r * rowlen) * 4;
-    }
-    j += PNG_THREADS;
-    while (j >= P.w) { j -= P.w; ++r; }
   }
+  if (matches) atomicAdd(&s_nmatch, matches);
   atomicAdd(&hist[wp][0], zeros);
   // block reduction of the Adler sums
 #pragma unroll
@@ -128,7 +291,6 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
     uint32_t v = 0;
 #pragma unroll
     for (int k = 0; k < PNG_THREADS / 32; ++k) v += hist[k][i];
-    if (i == 4) v += (uint32_t)rows;
     if (i == 256) v = 1;                        // end of block
     freq[i] = v;
   }
@@ -137,6 +299,7 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
     for (int k = 0; k < PNG_THREADS / 32; ++k) { a += red[0][k]; b += red[1][k]; }
     P.adler[2 * band] = (uint32_t)((1 + a) % 65521ull);
     P.adler[2 * band + 1] = (uint32_t)(((unsigned long long)n + b) % 65521ull);
+    P.nmatch[band] = s_nmatch;
   }
   __syncthreads();
   // ---- length-limited Huffman code of freq[0..256] ----
@@ -227,7 +390,8 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
 }
 
 // ---- P2 ----
-// A thread's bits for one chunk: up to 9 symbols of <= 15 bits (2 pixels + a filter byte) = 135 bits.
+// A thread's bits for one round: up to 10 literals of <= 15 bits (2 pixels, each possibly behind a filter byte;
+// a match token is <= 21 bits but covers >= 3 bytes) = 150 bits.
 struct LocalBits {
   uint32_t w[5];
   int n;
@@ -243,7 +407,7 @@ __device__ __forceinline__ void lb_put(LocalBits& b, uint32_t v, int len) {
   b.n += len;
 }
 
-#define PNG_WIN_WORDS 1152   // 256 threads x 135 bits = 1080 words + carry
+#define PNG_WIN_WORDS 1280   // 256 threads x 150 bits = 1200 words + carry
 
 __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_constant__ Params P) {
   __shared__ uint32_t win[PNG_WIN_WORDS];
@@ -264,7 +428,7 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
   int carry = 0;             // bits waiting at the start of the window
 
   // One round: every thread contributes `lb`; bits are placed in thread order after `carry`.
-  auto place = [&](const LocalBits& lb) {
+  auto place = [&](const LocalBits lb) {   // by value: the bits stay in registers
     int x = lb.n;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -305,8 +469,9 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
     carry = total & 31;
   };
 
-  // ---- zlib header (first band) + block header: BFINAL, BTYPE = 10, HLIT = 0, HDIST = 0, HCLEN = 15, the
-  // 19 code-length-code lengths (16, 17, 18 unused; 0..15 four bits each), then 258 lengths as 4-bit codes ----
+  // ---- zlib header (first band) + block header: BFINAL, BTYPE = 10, HLIT = 29, HDIST = 0, HCLEN = 15, the
+  // 19 code-length-code lengths (16, 17, 18 unused; 0..15 four bits each), then 286 literal/length code lengths
+  // and the single distance code length (1 when the band has a match) as 4-bit codes ----
   {
     LocalBits lb;
 #pragma unroll
@@ -316,46 +481,51 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
       if (band == 0) { lb_put(lb, 0x78u, 8); lb_put(lb, 0x01u, 8); }
       lb_put(lb, last ? 1u : 0u, 1);
       lb_put(lb, 2u, 2);
-      lb_put(lb, 0u, 5);
+      lb_put(lb, (uint32_t)(PNG_NSYM - 257), 5);
       lb_put(lb, 0u, 5);
       lb_put(lb, 15u, 4);
       lb_put(lb, 0u, 9);                          // 16, 17, 18: length 0
       for (int i = 0; i < 16; ++i) lb_put(lb, 4u, 3);
     }
     place(lb);
+    const int dist_len = P.nmatch[band] ? 1 : 0;
 #pragma unroll
-    for (int k = 0; k < 5; ++k) lb.w[k] = 0;
-    lb.n = 0;
-    {
-      const int s = t < PNG_NSYM ? s_len[t] : 0;
-      lb_put(lb, (uint32_t)(__brev((uint32_t)s) >> 28), 4);
-      if (t == PNG_THREADS - 1) {                 // symbol 256 and the single distance code (length 0)
-        const int s2 = s_len[256];
-        lb_put(lb, (uint32_t)(__brev((uint32_t)s2) >> 28), 4);
-        lb_put(lb, 0u, 4);
+    for (int part = 0; part < 2; ++part) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) lb.w[k] = 0;
+      lb.n = 0;
+      const int i = part * PNG_THREADS + t;
+      if (i <= PNG_NSYM) {
+        const int s = i < PNG_NSYM ? s_len[i] : dist_len;
+        lb_put(lb, (uint32_t)(__brev((uint32_t)s) >> 28), 4);
       }
+      place(lb);
     }
-    place(lb);
   }
-  // ---- the band's bytes: 2 pixels per thread and round ----
+  // ---- the band's tokens: 2 pixels per thread and round, as P1 left them ----
   const int npx = rows * P.w;
-  for (int base = 0; base < npx; base += 2 * PNG_THREADS) {
+  for (int base = 0; base < npx; base += PNG_ROUND_PX) {
+    const int q0 = base + 2 * t;
+    const uint64_t d = P.desc[((int64_t)band * P.rounds + base / PNG_ROUND_PX) * PNG_THREADS + t];
+    const uint32_t* fp = P.fpx + (int64_t)y0 * P.w + q0;
+    const uint32_t f0 = q0 < npx ? fp[0] : 0u, f1 = q0 + 1 < npx ? fp[1] : 0u;
     LocalBits lb;
 #pragma unroll
     for (int k = 0; k < 5; ++k) lb.w[k] = 0;
     lb.n = 0;
+    int mi = 0;
 #pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      const int q = base + 2 * t + e;
-      if (q < npx) {
-        const int r = q / P.w, j = q - r * P.w;
-        if (j == 0) lb_put(lb, s_code[4], s_len[4]);
-        const uint32_t f = filter_px(P, j, y0 + r);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const uint32_t d = (f >> (8 * k)) & 255u;
-          lb_put(lb, s_code[d], s_len[d]);
-        }
+    for (int i = 0; i < 10; ++i) {
+      const uint32_t cls = (uint32_t)(d >> (2 * i)) & 3u;
+      if (cls == 1u) {
+        const uint32_t v = (i % 5 == 0) ? 4u : ((i < 5 ? f0 : f1) >> (8 * ((i % 5) - 1))) & 255u;
+        lb_put(lb, s_code[v], s_len[v]);
+      } else if (cls == 2u) {
+        int ex, nex;
+        const int c = len_symbol(3 + (int)((d >> (20 + 8 * mi)) & 255ull), &ex, &nex);
+        ++mi;
+        // length code, its extra bits, then the 1-bit distance code (0): one field of <= 21 bits
+        lb_put(lb, (uint32_t)s_code[c] | ((uint32_t)ex << s_len[c]), s_len[c] + nex + 1);
       }
     }
     place(lb);

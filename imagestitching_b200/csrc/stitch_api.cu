@@ -387,10 +387,12 @@ struct PngExport {
     const int64_t c_pitch = ((int64_t)cw * 4 + 15) & ~15LL;
     const size_t b_canvas = want_rgba ? 0 : up((size_t)(c_pitch * ch));
     const size_t b_lens = up((size_t)nb * PNG_TAB_STRIDE), b_codes = up((size_t)nb * PNG_TAB_STRIDE * 2);
-    const size_t b_adler = up((size_t)nb * 8), b_scr = (size_t)nb * (size_t)band_cap;
+    const size_t b_adler = up((size_t)nb * 8), b_nm = up((size_t)nb * 4), b_scr = (size_t)nb * (size_t)band_cap;
+    const int rounds = (int)(((int64_t)PNG_BAND_ROWS * cw + PNG_ROUND_PX - 1) / PNG_ROUND_PX);
+    const size_t b_fpx = up((size_t)nb * PNG_BAND_ROWS * (size_t)cw * 4), b_desc = up((size_t)nb * rounds * PNG_THREADS * 8);
     const size_t b_blen = up((size_t)nb * 4), b_off = up((size_t)nb * 8), b_info = 256;
     const size_t b_file = out_host ? up((size_t)p_cap) : 0;
-    const size_t need = b_canvas + b_lens + b_codes + b_adler + b_scr + b_blen + b_off + b_info + b_file;
+    const size_t need = b_canvas + b_lens + b_codes + b_adler + b_nm + b_fpx + b_desc + b_scr + b_blen + b_off + b_info + b_file;
     if (ln.png_arena_cap < need) {
       if (ln.png_arena) {
         CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
@@ -409,6 +411,10 @@ struct PngExport {
     PP.lens = a; a += b_lens;
     PP.codes = (uint16_t*)a; a += b_codes;
     PP.adler = (uint32_t*)a; a += b_adler;
+    PP.nmatch = (uint32_t*)a; a += b_nm;
+    PP.fpx = (uint32_t*)a; a += b_fpx;
+    PP.desc = (uint64_t*)a; a += b_desc;
+    PP.rounds = rounds;
     PP.scratch = a; a += b_scr;
     PP.blen = (uint32_t*)a; a += b_blen;
     PP.off = (uint64_t*)a; a += b_off;

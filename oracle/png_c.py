@@ -41,7 +41,7 @@ def crc32(data: bytes) -> int:
 
 def code_lengths(freq) -> np.ndarray:
     f = np.ascontiguousarray(freq, dtype=np.uint32)
-    assert f.shape == (257,)
-    out = np.zeros(257, np.uint8)
+    assert f.shape == (286,)
+    out = np.zeros(286, np.uint8)
     _lib().png_ref_code_lengths(f.ctypes.data, out.ctypes.data)
     return out

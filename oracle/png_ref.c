@@ -9,17 +9,22 @@
  * files with libpng/zlib (PIL): the pixels must come back exactly.
  *
  * Encoder choices: Paeth filter (type 4) on every row; the rows are cut into bands of PNG_BAND_ROWS rows,
- * each band is ONE dynamic-Huffman block of literals only (no LZ77 matches) followed -- except for the last
- * band -- by an empty stored block that byte-aligns the stream, and is its own IDAT chunk.  Code lengths are
- * Huffman lengths limited to 15 bits by halving the frequencies until they fit; the code-length alphabet uses
- * a fixed 4-bit code for the lengths 0..15.
+ * each band is ONE dynamic-Huffman block followed -- except for the last band -- by an empty stored block that
+ * byte-aligns the stream, and is its own IDAT chunk.  LZ77 is restricted to RUNS: the band's bytes are taken in
+ * rounds of PNG_ROUND_PX pixels (with the filter-type byte in front of a row's first pixel); inside a round a
+ * maximal run of equal bytes is coded as its first byte + matches of distance 1 (chunks of up to 258 bytes; a
+ * chunk shorter than 3 stays literal).  That is what flat screenshot areas need -- after the Paeth filter they
+ * are runs of zeros -- and it keeps every token a function of its round only.  Code lengths are Huffman
+ * lengths limited to 15 bits by halving the frequencies until they fit; the code-length alphabet uses a fixed
+ * 4-bit code for the lengths 0..15; the distance alphabet has the single code "distance 1".
  */
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
 
 #define PNG_BAND_ROWS 8
-#define NSYM 257 /* 256 literals + end of block */
+#define PNG_ROUND_PX 512
+#define NSYM 286 /* 256 literals + end of block + 29 length codes */
 
 static uint32_t crc_table[256];
 static int crc_ready = 0;
@@ -110,6 +115,24 @@ void png_ref_codes(const uint8_t* len, uint16_t* code) {
   }
 }
 
+/* length 3..258 -> literal/length symbol 257..285 and its extra bits (RFC 1951 3.2.5) */
+static int len_code(int len, int* extra, int* nextra) {
+  int c, e = 0, ne = 0;
+  if (len < 11) c = 254 + len;
+  else if (len == 258) c = 285;
+  else {
+    const int n = len - 3;
+    int hb = 0;
+    while ((n >> (hb + 1)) != 0) ++hb;          /* floor(log2(n)), n >= 8 */
+    ne = hb - 2;
+    c = 257 + 4 * ne + (n >> ne);
+    e = n & ((1 << ne) - 1);
+  }
+  if (extra) *extra = e;
+  if (nextra) *nextra = ne;
+  return c;
+}
+
 typedef struct { uint8_t* p; size_t n, cap; uint64_t acc; int cnt; } BitW;
 static void put(BitW* b, uint32_t v, int n) {
   b->acc |= (uint64_t)v << b->cnt;
@@ -140,10 +163,12 @@ int png_ref_encode_rgba(const uint8_t* rgba, int w, int h, int64_t pitch, uint8_
   const size_t band_cap = (size_t)PNG_BAND_ROWS * (rowb + 1) * 2 + 1024;
   uint8_t* tmp = (uint8_t*)malloc(band_cap + 16);
   uint8_t* fb = (uint8_t*)malloc((size_t)PNG_BAND_ROWS * (rowb + 1));
-  if (!tmp || !fb) return -2;
+  int* tok = (int*)malloc(sizeof(int) * (size_t)PNG_BAND_ROWS * (rowb + 1));
+  if (!tmp || !fb || !tok) return -2;
   for (int band = 0; band < nb; ++band) {
     const int y0 = band * PNG_BAND_ROWS, y1 = y0 + PNG_BAND_ROWS < h ? y0 + PNG_BAND_ROWS : h;
-    /* filtered bytes of the band + histogram */
+    /* filtered bytes of the band, Adler, and the tokens: tok[i] = literal value (0..255), 0x1000 | length for a
+     * match of distance 1 (3..258), or -1 for a byte covered by a match */
     uint32_t freq[NSYM];
     memset(freq, 0, sizeof freq);
     size_t nf = 0;
@@ -154,9 +179,43 @@ int png_ref_encode_rgba(const uint8_t* rgba, int w, int h, int64_t pitch, uint8_
       for (int i = 0; i < rowb; ++i) fb[nf++] = filt(row, prev, i);
     }
     for (size_t i = 0; i < nf; ++i) {
-      freq[fb[i]]++;
       ad_a = (ad_a + fb[i]) % 65521u;
       ad_b = (ad_b + ad_a) % 65521u;
+    }
+    int n_match = 0;
+    {
+      const int npx = (y1 - y0) * w;
+      size_t pos = 0;                           /* stream position of the round's first byte */
+      for (int base = 0; base < npx; base += PNG_ROUND_PX) {
+        const int q1 = base + PNG_ROUND_PX < npx ? base + PNG_ROUND_PX : npx;
+        size_t n = 0;                           /* bytes of the round: 4 per pixel + 1 per row start */
+        for (int q = base; q < q1; ++q) n += 4 + ((q % w) == 0);
+        size_t i = 0;
+        while (i < n) {
+          size_t e = i + 1;
+          while (e < n && fb[pos + e] == fb[pos + i]) ++e;
+          const size_t L = e - i;               /* maximal run [i, e) */
+          tok[pos + i] = fb[pos + i];
+          for (size_t k = 1; k < L;) {
+            const size_t clen = L - k < 258 ? L - k : 258;
+            if (clen >= 3) {
+              tok[pos + i + k] = 0x1000 | (int)clen;
+              for (size_t m = 1; m < clen; ++m) tok[pos + i + k + m] = -1;
+              ++n_match;
+            } else {
+              for (size_t m = 0; m < clen; ++m) tok[pos + i + k + m] = fb[pos + i];
+            }
+            k += clen;
+          }
+          i = e;
+        }
+        pos += n;
+      }
+    }
+    for (size_t i = 0; i < nf; ++i) {
+      if (tok[i] < 0) continue;
+      if (tok[i] & 0x1000) freq[len_code(tok[i] & 0xfff, NULL, NULL)]++;
+      else freq[tok[i]]++;
     }
     freq[256] = 1;
     uint8_t len[NSYM];
@@ -170,17 +229,28 @@ int png_ref_encode_rgba(const uint8_t* rgba, int w, int h, int64_t pitch, uint8_
     if (band == 0) { put(&b, 0x78, 8); put(&b, 0x01, 8); }
     put(&b, (uint32_t)last, 1);
     put(&b, 2, 2);
-    put(&b, 0, 5);    /* HLIT: 257 codes */
-    put(&b, 0, 5);    /* HDIST: 1 code */
-    put(&b, 15, 4);   /* HCLEN: 19 code length codes */
+    put(&b, NSYM - 257, 5);  /* HLIT: 286 codes */
+    put(&b, 0, 5);           /* HDIST: 1 code */
+    put(&b, 15, 4);          /* HCLEN: 19 code length codes */
     static const int order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
     for (int i = 0; i < 19; ++i) put(&b, order[i] >= 16 ? 0 : 4, 3);
-    for (int i = 0; i <= NSYM; ++i) {  /* 257 literal/length code lengths + one distance code of length 0 */
-      const int s = i < NSYM ? len[i] : 0;
+    for (int i = 0; i <= NSYM; ++i) {  /* 286 literal/length code lengths + the distance code: 1 bit if any match */
+      const int s = i < NSYM ? len[i] : (n_match ? 1 : 0);
       const int r = ((s & 1) << 3) | ((s & 2) << 1) | ((s & 4) >> 1) | ((s & 8) >> 3);
       put(&b, (uint32_t)r, 4);
     }
-    for (size_t i = 0; i < nf; ++i) put(&b, code[fb[i]], len[fb[i]]);
+    for (size_t i = 0; i < nf; ++i) {
+      if (tok[i] < 0) continue;
+      if (tok[i] & 0x1000) {
+        int extra, nextra;
+        const int c = len_code(tok[i] & 0xfff, &extra, &nextra);
+        put(&b, code[c], len[c]);
+        if (nextra) put(&b, (uint32_t)extra, nextra);
+        put(&b, 0, 1);                          /* the single distance code (distance 1), canonical code 0 */
+      } else {
+        put(&b, code[tok[i]], len[tok[i]]);
+      }
+    }
     put(&b, code[256], len[256]);
     if (!last) {
       put(&b, 0, 3);  /* BFINAL = 0, BTYPE = 00 */
@@ -207,6 +277,7 @@ int png_ref_encode_rgba(const uint8_t* rgba, int w, int h, int64_t pitch, uint8_
   o += 12;
   free(tmp);
   free(fb);
+  free(tok);
   *need = o;
   return o <= cap ? 0 : -1;
 }

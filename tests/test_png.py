@@ -33,7 +33,7 @@ def test_oracle_png_roundtrip(size):
 def test_oracle_crc_and_length_limit():
     for s in (b"", b"IEND", b"IDAT" + bytes(range(256)) * 7):
         assert P.crc32(s) == zlib.crc32(s)
-    f = np.zeros(257, np.uint32)
+    f = np.zeros(286, np.uint32)
     f[:40] = [int(1.6 ** i) + 1 for i in range(40)]      # Fibonacci-like skew: plain Huffman would need > 15 bits
     f[256] = 1
     lens = P.code_lengths(f)
@@ -87,6 +87,45 @@ def test_gpu_png_randomized_and_flat_canvases():
     bitmaps = [np.full((h, w, 4), 255, np.uint8) for w, h in dims]
     got = ctx.run(U.page_images(dims, bitmaps), "vertical", mode="original", gap=20, platform="ios", output="rgba+png")
     assert got.png == P.encode_rgba(got.rgba) and len(got.png) < got.rgba.nbytes // 5
+    ctx.close()
+
+
+def _screenshot_like(w, h, seed):
+    """Flat colour blocks with a few noisy stripes: long runs of equal filtered bytes, ends at arbitrary offsets."""
+    rng = np.random.default_rng(seed)
+    img = np.empty((h, w, 4), np.uint8)
+    img[:] = rng.integers(0, 256, 4, dtype=np.uint8)
+    for _ in range(6):
+        x0, y0 = int(rng.integers(0, w)), int(rng.integers(0, h))
+        x1, y1 = int(rng.integers(x0, w)) + 1, int(rng.integers(y0, h)) + 1
+        img[y0:y1, x0:x1] = rng.integers(0, 256, 4, dtype=np.uint8)
+    if h > 4:
+        y = int(rng.integers(0, h - 2))
+        img[y:y + 2] = rng.integers(0, 256, (2, w, 4), dtype=np.uint8)
+    img[..., 3] = 255
+    return img
+
+
+def test_oracle_runs_roundtrip_and_shrink():
+    """Run-length tokens: flat content decodes exactly through libpng and is far smaller than literal coding."""
+    for k, (w, h) in enumerate([(1, 1), (1, 40), (2, 17), (3, 9), (129, 8), (512, 8), (513, 9), (700, 33), (1031, 20)]):
+        img = _screenshot_like(w, h, k)
+        data = P.encode_rgba(img)
+        assert np.array_equal(_back(data), img), (w, h)
+    white = np.full((200, 333, 4), 255, np.uint8)
+    assert len(P.encode_rgba(white)) < white.nbytes // 40
+
+
+@pytest.mark.gpu
+def test_gpu_png_run_tokens():
+    """Screenshot-like bitmaps (flat blocks -> long runs, ends anywhere in a round): the GPU file equals the writer's."""
+    from imagestitching_b200 import StitchContext
+    ctx = StitchContext(0)
+    for k, (w, h) in enumerate([(1, 1), (1, 40), (2, 17), (3, 9), (129, 8), (512, 8), (513, 9), (700, 33), (1031, 20), (1820, 64)]):
+        img = _screenshot_like(w, h, 100 + k)
+        got = ctx.run(U.page_images([(w, h)], [img]), "vertical", mode="original", gap=0, platform="ios", output="rgba+png")
+        assert got.png == P.encode_rgba(got.rgba), f"{w}x{h}: GPU PNG differs from the oracle writer"
+        assert np.array_equal(_back(got.png), got.rgba)
     ctx.close()
 
 
