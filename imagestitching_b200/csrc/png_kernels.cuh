@@ -56,6 +56,7 @@ struct Params {
   uint8_t* file;
   int64_t cap;
   uint32_t x2n[32];            // x^(2^k) mod P, reflected (CRC combine)
+  uint32_t xinv2n[32];         // x^(-2^k) mod P
 };
 
 __device__ __forceinline__ int paeth(int a, int b, int c) {
@@ -89,105 +90,160 @@ __device__ __forceinline__ uint32_t filter_px(const Params& P, int j, int y) {
 // ---- run-length tokens of one round ----
 // LZ77 restricted to runs: inside a round (PNG_ROUND_PX pixels in raster order, the filter-type byte in front
 // of a row's first pixel) a maximal run of equal bytes is its first byte + matches of distance 1: chunks of up
-// to 258 bytes, a chunk shorter than 3 stays literal.  A token depends on its round only, so the histogram and
-// the encode kernel (and the sequential writer of the test tree) derive the same tokens independently.
-struct RoundSmem {
-  uint8_t bytes[PNG_ROUND_PX * 4 + PNG_ROUND_PX + 16];   // worst case: every pixel starts a row (w = 1)
-  int warp_a[PNG_THREADS / 32], warp_b[PNG_THREADS / 32];
+// to 258 bytes, a chunk shorter than 3 stays literal.  A token depends on its round only; the sequential writer
+// of the test tree derives the same tokens.
+//
+// A thread owns 2 pixels = ten SLOTS, statically indexed: slot 5e is the filter-type byte in front of pixel e
+// (present when the pixel starts a row), slots 5e+1..5e+4 its four bytes; `valid` marks the slots that exist.
+// Almost every warp is PLAIN -- all 32 lanes have both pixels and no row start -- and runs the instantiation in
+// which `valid` is the constant 0x3de, so every validity test and position count folds away.
+#define PNG_PLAIN_VALID 0x3deu
+struct RoundSmem {   // per-warp partials, double-buffered by round parity (one barrier per round)
+  int warp_a[2][PNG_THREADS / 32];      // last run start inside the warp (its very first byte not counted), or -1
+  int warp_b[2][PNG_THREADS / 32];      // first run start inside the warp (same exclusion), or INT_MAX
+  int warp_g0[2][PNG_THREADS / 32];     // round index of the warp's first byte, -1: the warp has no bytes
+  uint8_t warp_first[2][PNG_THREADS / 32], warp_last[2][PNG_THREADS / 32];   // its first and last byte values
 };
 struct ThreadTokens {
-  // Ten slots, statically indexed: slot 5e is the filter-type byte in front of pixel e (present when the pixel
-  // starts a row), slots 5e+1..5e+4 its four bytes.  `valid` marks the slots that exist.
-  uint32_t valid;
-  int off;            // index of the first valid slot's byte in the round
-  uint8_t v[10];      // byte values
-  int16_t tok[10];    // -1: covered by a match (or slot absent); 0..255: literal; 0x1000 | len: match of distance 1
+  uint32_t f0, f1;    // the two filtered pixels (0 when absent)
+  uint32_t valid;     // slots that exist
+  int off;            // round index of the thread's first byte
+  uint32_t startmask; // slots that start a run
+  int a, b;           // warp scans (inclusive) of the thread's last (max, from the left) / first (min, from the right) start
+  uint32_t cls;       // 2 bits per slot: 0 nothing to emit, 1 literal, 2 match of distance 1
+  uint32_t lens;      // 8 bits per match, in slot order: length - 3
 };
 
 __device__ __forceinline__ int multiples_before(int q, int w) { return (q + w - 1) / w; }   // multiples of w in [0, q)
 
-__device__ __forceinline__ void round_tokens(const Params& P, int y0, int npx, int base, RoundSmem& rs, ThreadTokens& tt) {
-  const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
+__device__ __forceinline__ uint32_t slot_byte(const ThreadTokens& tt, int i) {
+  if (i == 0 || i == 5) return 4u;                  // the row's filter-type byte (Paeth)
+  return ((i < 5 ? tt.f0 : tt.f1) >> (8 * ((i % 5) - 1))) & 255u;
+}
+template <bool PLAIN>
+__device__ __forceinline__ int slot_pos(const ThreadTokens& tt, int i) {   // round index of slot i's byte
+  const uint32_t valid = PLAIN ? PNG_PLAIN_VALID : tt.valid;
+  return tt.off + __popc(valid & ((1u << i) - 1u));
+}
+
+// Pixels, slots and position of the thread in the round; returns whether the whole warp is PLAIN.
+__device__ __forceinline__ bool round_load(const Params& P, int y0, int npx, int base, int mb_base, ThreadTokens& tt) {
+  const int t = threadIdx.x;
   const int q_end = min(base + PNG_ROUND_PX, npx);
-  const int n_round = 4 * (q_end - base) + multiples_before(q_end, P.w) - multiples_before(base, P.w);
   const int q0 = base + 2 * t;
   tt.valid = 0;
-  tt.off = q0 < q_end ? 4 * (q0 - base) + multiples_before(q0, P.w) - multiples_before(base, P.w) : n_round;
-#pragma unroll
-  for (int e = 0; e < 2; ++e) {
-    const int q = q0 + e;
-    uint32_t f = 0;
-    if (q < q_end) {
-      const int r = q / P.w, j = q - r * P.w;
-      tt.valid |= (j == 0 ? 0x1fu : 0x1eu) << (5 * e);
-      f = filter_px(P, j, y0 + r);
+  tt.f0 = tt.f1 = 0;
+  tt.off = 4 * (min(q0, q_end) - base) + multiples_before(min(q0, q_end), P.w) - mb_base;
+  if (q0 < q_end) {
+    const int r = q0 / P.w, j = q0 - r * P.w;
+    tt.valid = j == 0 ? 0x1fu : 0x1eu;
+    tt.f0 = filter_px(P, j, y0 + r);
+    if (q0 + 1 < q_end) {
+      const bool wrap = j + 1 == P.w;
+      tt.valid |= wrap ? 0x3e0u : 0x3c0u;
+      tt.f1 = filter_px(P, wrap ? 0 : j + 1, y0 + r + (wrap ? 1 : 0));
     }
-    tt.v[5 * e] = 4;                                // the row's filter-type byte (Paeth)
-#pragma unroll
-    for (int k = 0; k < 4; ++k) tt.v[5 * e + 1 + k] = (uint8_t)(f >> (8 * k));
   }
-#pragma unroll
-  for (int i = 0; i < 10; ++i)
-    if (tt.valid >> i & 1u) rs.bytes[tt.off + __popc(tt.valid & ((1u << i) - 1u))] = tt.v[i];
-  __syncthreads();
-  // run starts inside my range; the last one at or before it and the first one behind it come from scans
-  int ls = -1, fs = 0x7fffffff;
-  uint32_t startmask = 0;
+  return __all_sync(0xffffffffu, tt.valid == PNG_PLAIN_VALID);
+}
+
+// Run starts of the thread (the first byte of lane 0 is left out: its predecessor lives in another warp), warp
+// scans, and the warp's partials for the other warps.
+template <bool PLAIN>
+__device__ __forceinline__ void round_starts(ThreadTokens& tt, RoundSmem& rs, int buf) {
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  const uint32_t valid = PLAIN ? PNG_PLAIN_VALID : tt.valid;
+  const uint32_t mylast = ((valid >> 6 & 1u) ? tt.f1 : tt.f0) >> 24;
+  uint32_t prev = __shfl_up_sync(0xffffffffu, mylast, 1);
+  bool have_prev = lane > 0;
+  uint32_t sm = 0;
 #pragma unroll
   for (int i = 0; i < 10; ++i) {
-    if (tt.valid >> i & 1u) {
-      const int g = tt.off + __popc(tt.valid & ((1u << i) - 1u));
-      const bool st = g == 0 || tt.v[i] != rs.bytes[g - 1];
-      if (st) { startmask |= 1u << i; ls = g; fs = min(fs, g); }
+    if (valid >> i & 1u) {
+      const uint32_t v = slot_byte(tt, i);
+      if (have_prev && v != prev) sm |= 1u << i;
+      prev = v;
+      have_prev = true;
     }
   }
-  int a = ls, b = fs;                               // inclusive scans: max from the left, min from the right
+  tt.startmask = sm;
+  int a = -1, b = 0x7fffffff;
+  if (sm) {
+    a = slot_pos<PLAIN>(tt, 31 - __clz(sm));
+    b = slot_pos<PLAIN>(tt, __ffs(sm) - 1);
+  }
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) {
     const int ya = __shfl_up_sync(0xffffffffu, a, d), yb = __shfl_down_sync(0xffffffffu, b, d);
     if (lane >= d) a = max(a, ya);
     if (lane + d < 32) b = min(b, yb);
   }
-  if (lane == 31) rs.warp_a[wp] = a;
-  if (lane == 0) rs.warp_b[wp] = b;
-  __syncthreads();
-  int before = __shfl_up_sync(0xffffffffu, a, 1), after = __shfl_down_sync(0xffffffffu, b, 1);
+  tt.a = a;
+  tt.b = b;
+  if (lane == 31) { rs.warp_a[buf][wp] = a; rs.warp_last[buf][wp] = (uint8_t)mylast; }
+  if (lane == 0) {
+    rs.warp_b[buf][wp] = b;
+    rs.warp_g0[buf][wp] = valid ? tt.off : -1;
+    rs.warp_first[buf][wp] = (uint8_t)((valid & 1u) ? 4u : (tt.f0 & 255u));
+  }
+}
+
+// After the barrier: the run around every byte of the thread -> cls / lens.
+template <bool PLAIN>
+__device__ __forceinline__ void round_finish(ThreadTokens& tt, const RoundSmem& rs, int buf, int n_round) {
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  const uint32_t valid = PLAIN ? PNG_PLAIN_VALID : tt.valid;
+  int before = __shfl_up_sync(0xffffffffu, tt.a, 1), after = __shfl_down_sync(0xffffffffu, tt.b, 1);
   if (lane == 0) before = -1;
   if (lane == 31) after = 0x7fffffff;
+  uint32_t sm = tt.startmask;
 #pragma unroll
   for (int k = 0; k < PNG_THREADS / 32; ++k) {
-    if (k < wp) before = max(before, rs.warp_a[k]);
-    if (k > wp) after = min(after, rs.warp_b[k]);
+    const int g0 = rs.warp_g0[buf][k];
+    // does warp k's first byte start a run?  (the round's first byte always does)
+    const bool real = g0 >= 0 && (k == 0 || rs.warp_first[buf][k] != rs.warp_last[buf][k > 0 ? k - 1 : 0]);
+    const int ak = max(rs.warp_a[buf][k], real ? g0 : -1);
+    const int bk = real ? g0 : rs.warp_b[buf][k];
+    if (k < wp) before = max(before, ak);
+    if (k > wp) after = min(after, bk);
+    if (k == wp && real) {
+      if (lane == 0) sm |= (valid & 1u) ? 1u : 2u;
+      else before = max(before, g0);
+    }
   }
   after = min(after, n_round);
-  // per byte: run start s (walking forward) and run end e (walking backward) -> token
   int e_of[10];
   {
     int cur = after;
 #pragma unroll
     for (int i = 9; i >= 0; --i) {
       e_of[i] = cur;
-      if (startmask >> i & 1u) cur = tt.off + __popc(tt.valid & ((1u << i) - 1u));
+      if (sm >> i & 1u) cur = slot_pos<PLAIN>(tt, i);
     }
   }
   int cur_s = before;
+  uint32_t cls = 0, lens = 0;
+  int mi = 0;
 #pragma unroll
   for (int i = 0; i < 10; ++i) {
-    int tk = -1;
-    if (tt.valid >> i & 1u) {
-      const int g = tt.off + __popc(tt.valid & ((1u << i) - 1u));
-      if (startmask >> i & 1u) cur_s = g;
+    if (valid >> i & 1u) {
+      const int g = slot_pos<PLAIN>(tt, i);
+      if (sm >> i & 1u) cur_s = g;
       const int k = g - cur_s, L = e_of[i] - cur_s;
-      tk = tt.v[i];
+      uint32_t c = 1u;
       if (k >= 1) {
-        const int c = (k - 1) / 258, o = (k - 1) - 258 * c;
-        const int clen = min(258, (L - 1) - 258 * c);
-        if (clen >= 3) tk = (o == 0) ? (0x1000 | clen) : -1;
+        const int ch = (k - 1) / 258, o = (k - 1) - 258 * ch;
+        const int clen = min(258, (L - 1) - 258 * ch);
+        if (clen >= 3) {
+          c = o == 0 ? 2u : 0u;
+          if (o == 0) { lens |= (uint32_t)(clen - 3) << (8 * mi); ++mi; }
+        }
       }
+      cls |= c << (2 * i);
     }
-    tt.tok[i] = (int16_t)tk;
   }
-  __syncthreads();                                  // rs is reused by the next round
+  tt.cls = cls;
+  tt.lens = lens;
 }
 
 // length 3..258 -> literal/length symbol 257..285 and its extra bits (RFC 1951 3.2.5)
@@ -206,25 +262,42 @@ __device__ __forceinline__ int len_symbol(int len, int* extra, int* nextra) {
   return c;
 }
 
-// A thread's tokens of one round in 44 bits, so that P2 neither filters nor tokenises again: slot i has class
-// (d >> 2i) & 3 -- 0 nothing to emit, 1 literal, 2 match -- and the k-th match of the thread (at most 3 in 10
-// bytes) has length 3 + ((d >> (20 + 8k)) & 255).
-__device__ __forceinline__ uint64_t pack_tokens(const ThreadTokens& tt) {
-  uint64_t d = 0;
+// P1 leaves a thread's tokens of a round to P2 as d = cls | lens << 20 (44 bits) next to the filtered pixels, so
+// that P2 neither filters nor tokenises again.
+
+// P1's share of a round after the barrier: tokens, their histogram, and the Adler sums of the thread's bytes
+// (s2 weights a byte by the number of stream bytes from it to the end of the band).
+template <bool PLAIN>
+__device__ __forceinline__ void hist_round(ThreadTokens& tt, const RoundSmem& rs, int buf, int n_round, int64_t left,
+                                           uint32_t* hist, uint32_t& zeros, uint32_t& matches,
+                                           unsigned long long& s1, unsigned long long& s2) {
+  round_finish<PLAIN>(tt, rs, buf, n_round);
+  const uint32_t valid = PLAIN ? PNG_PLAIN_VALID : tt.valid;
+  {
+    // a byte sits at round index (off - c0) + r: r = slot for slots 0..5, slot - c5 for the second pixel
+    const int c0 = (valid & 1u) ? 0 : 1, c5 = (valid >> 5 & 1u) ? 0 : 1;
+    const uint32_t sum0 = __dp4a(tt.f0, 0x01010101u, 0u), sum1 = __dp4a(tt.f1, 0x01010101u, 0u);
+    const uint32_t S = sum0 + sum1 + 4u * (uint32_t)((1 - c0) + (1 - c5));
+    const uint32_t W = __dp4a(tt.f0, 0x04030201u, 0u) + __dp4a(tt.f1, 0x09080706u, 0u) + (c5 ? 0u : 20u) - (uint32_t)c5 * sum1;
+    s1 += S;
+    s2 += (unsigned long long)(left - (tt.off - c0)) * S - W;
+  }
   int mi = 0;
 #pragma unroll
   for (int i = 0; i < 10; ++i) {
-    const int tk = tt.tok[i];
-    if (tk < 0) continue;
-    if (tk & 0x1000) {
-      d |= 2ull << (2 * i);
-      d |= (uint64_t)((tk & 0xfff) - 3) << (20 + 8 * mi);
+    if (!(valid >> i & 1u)) continue;
+    const uint32_t c = tt.cls >> (2 * i) & 3u;
+    if (c == 1u) {
+      const uint32_t v = slot_byte(tt, i);
+      if (v == 0) ++zeros;
+      else atomicAdd(&hist[v], 1u);
+    } else if (c == 2u) {
+      int ex, nex;
+      atomicAdd(&hist[len_symbol(3 + (int)(tt.lens >> (8 * mi) & 255u), &ex, &nex)], 1u);
       ++mi;
-    } else {
-      d |= 1ull << (2 * i);
+      ++matches;
     }
   }
-  return d;
 }
 
 // ---- P1 ----
@@ -245,36 +318,24 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
   uint32_t zeros = 0, matches = 0;
   unsigned long long s1 = 0, s2 = 0;
   const int npx = rows * P.w;
-  for (int base = 0; base < npx; base += PNG_ROUND_PX) {
+  for (int base = 0, round = 0; base < npx; base += PNG_ROUND_PX, ++round) {
     ThreadTokens tt;
-    round_tokens(P, y0, npx, base, rs, tt);
+    const int q_end = min(base + PNG_ROUND_PX, npx);
+    const int mb_base = multiples_before(base, P.w);
+    const int n_round = 4 * (q_end - base) + multiples_before(q_end, P.w) - mb_base;
+    const bool plain = round_load(P, y0, npx, base, mb_base, tt);
+    if (plain) round_starts<true>(tt, rs, round & 1);
+    else round_starts<false>(tt, rs, round & 1);
+    __syncthreads();
+    const int64_t left = n - (4 * (int64_t)base + mb_base);     // stream bytes from the round's first byte on
+    if (plain) hist_round<true>(tt, rs, round & 1, n_round, left, hist[wp], zeros, matches, s1, s2);
+    else hist_round<false>(tt, rs, round & 1, n_round, left, hist[wp], zeros, matches, s1, s2);
     {
       const int q0 = base + 2 * t;
       uint32_t* fp = P.fpx + (int64_t)y0 * P.w + q0;
-      if (q0 < npx) fp[0] = (uint32_t)tt.v[1] | (uint32_t)tt.v[2] << 8 | (uint32_t)tt.v[3] << 16 | (uint32_t)tt.v[4] << 24;
-      if (q0 + 1 < npx) fp[1] = (uint32_t)tt.v[6] | (uint32_t)tt.v[7] << 8 | (uint32_t)tt.v[8] << 16 | (uint32_t)tt.v[9] << 24;
-      P.desc[((int64_t)band * P.rounds + base / PNG_ROUND_PX) * PNG_THREADS + t] = pack_tokens(tt);
-    }
-    const int64_t rpos = 4 * (int64_t)base + multiples_before(base, P.w);   // stream position of the round
-#pragma unroll
-    for (int i = 0; i < 10; ++i) {
-      if (!(tt.valid >> i & 1u)) continue;
-      const uint32_t d = tt.v[i];
-      if (d) {
-        s1 += d;
-        s2 += (unsigned long long)(n - (rpos + tt.off + __popc(tt.valid & ((1u << i) - 1u)))) * d;
-      }
-      const int tk = tt.tok[i];
-      if (tk < 0) continue;
-      if (tk & 0x1000) {
-        int ex, nex;
-        atomicAdd(&hist[wp][len_symbol(tk & 0xfff, &ex, &nex)], 1u);
-        ++matches;
-      } else if (tk == 0) {
-        ++zeros;
-      } else {
-        atomicAdd(&hist[wp][tk], 1u);
-      }
+      if (q0 < npx) fp[0] = tt.f0;
+      if (q0 + 1 < npx) fp[1] = tt.f1;
+      P.desc[((int64_t)band * P.rounds + round) * PNG_THREADS + t] = (uint64_t)tt.cls | ((uint64_t)tt.lens << 20);
     }
   }
   if (matches) atomicAdd(&s_nmatch, matches);
@@ -423,7 +484,9 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
   }
   for (int i = t; i < PNG_WIN_WORDS; i += PNG_THREADS) win[i] = 0;
   __syncthreads();
-  uint32_t* out = reinterpret_cast<uint32_t*>(P.scratch + (int64_t)band * P.band_cap);
+  // scratch band = 'IDAT' + zlib data: exactly the bytes the chunk CRC covers
+  uint32_t* out = reinterpret_cast<uint32_t*>(P.scratch + (int64_t)band * P.band_cap) + 1;
+  if (t == 0) out[-1] = 0x54414449u;
   int64_t words_out = 0;     // words already flushed
   int carry = 0;             // bits waiting at the start of the window
 
@@ -602,19 +665,42 @@ __global__ void __launch_bounds__(1024) png_offsets_kernel(const __grid_constant
     if (t == 1023) carry_s = before + v;
     __syncthreads();
   }
+  // Adler-32 of the whole stream: thread t combined its slice of bands above; combine the slices in order with a
+  // butterfly (the operation is associative; (1, 0, 0) is its identity)
+  {
+    unsigned long long a = s_ad[0][t], b = s_ad[1][t], nn = s_ad[2][t];
+    auto level = [&](unsigned long long oa, unsigned long long ob, unsigned long long on, bool i_am_right) {
+      const unsigned long long la = i_am_right ? oa : a, lb = i_am_right ? ob : b, ln = i_am_right ? on : nn;
+      const unsigned long long ra = i_am_right ? a : oa, rb = i_am_right ? b : ob, rn = i_am_right ? nn : on;
+      b = (lb + rb + rn * ((la + 65520ull) % 65521ull)) % 65521ull;   // + n_right * (a_left - 1)
+      a = (la + ra + 65520ull) % 65521ull;                            // a_left + a_right - 1
+      nn = (ln + rn) % 65521ull;
+    };
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned long long oa = __shfl_xor_sync(0xffffffffu, a, d), ob = __shfl_xor_sync(0xffffffffu, b, d),
+                               on = __shfl_xor_sync(0xffffffffu, nn, d);
+      level(oa, ob, on, (lane & d) != 0);
+    }
+    __syncthreads();
+    if (lane == 0) { s_ad[0][w] = (uint32_t)a; s_ad[1][w] = (uint32_t)b; s_ad[2][w] = (uint32_t)nn; }
+    __syncthreads();
+    if (w == 0) {
+      a = s_ad[0][lane]; b = s_ad[1][lane]; nn = s_ad[2][lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long oa = __shfl_xor_sync(0xffffffffu, a, d), ob = __shfl_xor_sync(0xffffffffu, b, d),
+                                 on = __shfl_xor_sync(0xffffffffu, nn, d);
+        level(oa, ob, on, (lane & d) != 0);
+      }
+      if (lane == 0) P.info[2] = (b << 16) | a;
+    }
+  }
   if (t == 0) {
     const unsigned long long total = carry_s + 12ull;
     const bool fits = total <= (unsigned long long)P.cap;
     P.info[0] = total;
     P.info[1] = fits ? 0ull : 1ull;
-    // Adler-32 of the whole stream: thread t combined its slice of bands above (s_ad); fold the slices in order
-    unsigned long long a = 1, b = 0;
-    for (int k = 0; k < 1024; ++k) {
-      const unsigned long long a2 = s_ad[0][k], b2 = s_ad[1][k], n2 = s_ad[2][k];
-      b = (b + b2 + n2 * ((a + 65520ull) % 65521ull)) % 65521ull;   // + n * (a - 1)
-      a = (a + a2 + 65520ull) % 65521ull;                          // a + a2 - 1
-    }
-    P.info[2] = (b << 16) | a;
     if (fits) {
       for (int k = 0; k < H.n; ++k) P.file[k] = H.b[k];
       const uint8_t iend[12] = {0, 0, 0, 0, 'I', 'E', 'N', 'D', 0xAE, 0x42, 0x60, 0x82};
@@ -636,57 +722,106 @@ __device__ __forceinline__ uint32_t gf2_mul(uint32_t a, uint32_t b) {   // a * b
   }
   return p;
 }
-__device__ __forceinline__ uint32_t x_pow_8n(const Params& P, uint32_t nbytes) {  // x^(8 n) mod P
-  uint32_t p = 1u << 31;
-  uint32_t k = 3;
-  while (nbytes) {
-    if (nbytes & 1u) p = gf2_mul(P.x2n[k & 31], p);
-    nbytes >>= 1;
-    ++k;
-  }
-  return p;
-}
-
+// The chunk = length, then 'IDAT' + data (the band in scratch, contiguous), then the CRC-32 of those bytes.
+// Copy: aligned words of the file, each funnel-shifted from two scratch words.  CRC: the message is padded with
+// zero words at the END to whole tiles of PNG_THREADS x 16 words; per tile a thread runs slicing-by-4 over its 16
+// consecutive words (initial value 0), `acc = acc * x^(8 * tile bytes) + c` keeps its share of the tiles, a
+// butterfly over the threads (`left * x^(8 * 64 * 2^l) + right`) gives the CRC of the padded message with a zero
+// initial value, a multiplication by x^(-8 * pad) takes the padding back, and complementing the first four bytes
+// and the result stands for the 0xFFFFFFFF initial and final values.
 __global__ void __launch_bounds__(PNG_THREADS) png_gather_kernel(const __grid_constant__ Params P) {
-  __shared__ uint32_t tab[256];
-  __shared__ uint32_t part_crc[32], part_len[32];
+  __shared__ uint32_t tab[4][256];
+  __shared__ uint32_t s_part[PNG_THREADS / 32];
   if (P.info[1]) return;
-  const int band = blockIdx.x, t = threadIdx.x, lane = t & 31;
-  {
-    uint32_t c = (uint32_t)t;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) c = (c & 1u) ? PNG_CRC_POLY ^ (c >> 1) : c >> 1;
-    tab[t] = c;
-  }
+  const int band = blockIdx.x, t = threadIdx.x, lane = t & 31, wp = t >> 5;
   const uint32_t dl = P.blen[band];
-  const uint8_t* src = P.scratch + (int64_t)band * P.band_cap;
+  uint32_t* srcw = reinterpret_cast<uint32_t*>(P.scratch + (int64_t)band * P.band_cap);
   uint8_t* dst = P.file + P.off[band];
   const bool last = band == P.nb - 1;
-  const uint32_t copy_n = last ? dl - 4 : dl;
-  for (uint32_t i = t; i < copy_n; i += PNG_THREADS) dst[8 + i] = src[i];
-  if (t < 4) {
-    dst[t] = (uint8_t)(dl >> (24 - 8 * t));
-    dst[4 + t] = (uint8_t)("IDAT"[t]);
-    if (last) dst[8 + copy_n + t] = (uint8_t)(P.info[2] >> (24 - 8 * t));
+  const uint32_t total = dl + 4;                  // bytes under the CRC
+  const uint32_t nw = (total + 3) >> 2;
+  uint32_t c0 = (uint32_t)t;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) c0 = (c0 & 1u) ? PNG_CRC_POLY ^ (c0 >> 1) : c0 >> 1;
+  tab[0][t] = c0;
+  if (last && t == 0) {                           // the stream's Adler-32 closes the last band
+    uint8_t* sb = reinterpret_cast<uint8_t*>(srcw);
+    for (int k = 0; k < 4; ++k) sb[total - 4 + k] = (uint8_t)(P.info[2] >> (24 - 8 * k));
   }
   __syncthreads();
-  // CRC-32 over 'IDAT' + data = dst[4 .. 8 + dl): warp 0, each lane a contiguous slice, then combine in order
-  if (t >= 32) return;
-  const uint32_t total = dl + 4;
-  const uint32_t per = (total + 31) / 32;
-  const uint32_t b0 = min(lane * per, total), b1 = min(b0 + per, total);
-  uint32_t c = 0xFFFFFFFFu;
-  for (uint32_t i = b0; i < b1; ++i) c = tab[(c ^ dst[4 + i]) & 255u] ^ (c >> 8);
-  part_crc[lane] = c ^ 0xFFFFFFFFu;
-  part_len[lane] = b1 - b0;
-  __syncwarp();
-  if (lane == 0) {
-    uint32_t crc = part_crc[0];
-    const uint32_t xp = x_pow_8n(P, per);          // all slices but the last have `per` bytes
-    for (int k = 1; k < 32; ++k) {
-      if (part_len[k] == 0) continue;
-      crc = gf2_mul(part_len[k] == per ? xp : x_pow_8n(P, part_len[k]), crc) ^ part_crc[k];
+  {
+    uint32_t c = c0;
+#pragma unroll
+    for (int k = 1; k < 4; ++k) { c = tab[0][c & 255u] ^ (c >> 8); tab[k][t] = c; }
+  }
+  // ---- copy ----
+  if (t < 4) dst[t] = (uint8_t)(dl >> (24 - 8 * t));
+  {
+    uint8_t* D = dst + 4;
+    const uint8_t* sb = reinterpret_cast<const uint8_t*>(srcw);
+    const uint32_t h = min((uint32_t)((4 - (reinterpret_cast<uintptr_t>(D) & 3)) & 3), total);   // bytes before the first aligned word
+    const uint32_t nfw = (total - h) >> 2;
+    uint32_t* Dw = reinterpret_cast<uint32_t*>(D + h);
+    for (uint32_t j = t; j < nfw; j += PNG_THREADS) {
+      const uint32_t lo = srcw[j], hi = h ? srcw[j + 1] : 0u;
+      Dw[j] = __funnelshift_r(lo, hi, 8 * h);
     }
+    if ((uint32_t)t < h) D[t] = sb[t];
+    const uint32_t tail0 = h + 4 * nfw;
+    if (tail0 + t < total && t < 4) D[tail0 + t] = sb[tail0 + t];
+  }
+  __syncthreads();                                // tables ready
+  // ---- CRC ----
+  const uint32_t tile_words = PNG_THREADS * 16;
+  const uint32_t ntiles = (nw + tile_words - 1) / tile_words;
+  const uint32_t tail_mask = (total & 3u) ? (1u << (8 * (total & 3u))) - 1u : 0xFFFFFFFFu;
+  uint32_t acc = 0;
+  for (uint32_t tile = 0; tile < ntiles; ++tile) {
+    const uint32_t g0 = tile * tile_words + 16u * (uint32_t)t;
+    uint32_t c = 0;
+    if (g0 < nw) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (g0 + 4 * q < nw) v = *reinterpret_cast<const uint4*>(srcw + g0 + 4 * q);
+        const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const uint32_t g = g0 + 4 * q + r;
+          uint32_t x = g < nw ? wv[r] : 0u;
+          if (g == nw - 1) x &= tail_mask;
+          if (g == 0) x = ~x;
+          c ^= x;
+          c = tab[3][c & 255u] ^ tab[2][(c >> 8) & 255u] ^ tab[1][(c >> 16) & 255u] ^ tab[0][c >> 24];
+        }
+      }
+    }
+    acc = (tile ? gf2_mul(P.x2n[17], acc) : 0u) ^ c;      // tile = 2^14 bytes: x^(8 * 2^14) = x^(2^17)
+  }
+  // butterfly: thread groups of 2^l neighbours, 64 * 2^l bytes each: x^(8 * 64 * 2^l) = x^(2^(9 + l))
+#pragma unroll
+  for (int l = 0; l < 5; ++l) {
+    const uint32_t other = __shfl_xor_sync(0xffffffffu, acc, 1 << l);
+    const bool right = (lane >> l) & 1;
+    acc = gf2_mul(P.x2n[9 + l], right ? other : acc) ^ (right ? acc : other);
+  }
+  if (lane == 0) s_part[wp] = acc;
+  __syncthreads();
+  if (wp != 0) return;
+  acc = lane < PNG_THREADS / 32 ? s_part[lane] : 0u;
+#pragma unroll
+  for (int l = 0; l < 3; ++l) {
+    const uint32_t other = __shfl_xor_sync(0xffffffffu, acc, 1 << l);
+    const bool right = (lane >> l) & 1;
+    acc = gf2_mul(P.x2n[14 + l], right ? other : acc) ^ (right ? acc : other);
+  }
+  // x^(-8 * pad): one factor per bit of 8 * pad, multiplied up by a butterfly
+  const uint32_t pad_bits = 8u * (ntiles * tile_words * 4u - total);
+  uint32_t inv = (pad_bits >> lane & 1u) ? P.xinv2n[lane] : 0x80000000u;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) inv = gf2_mul(inv, __shfl_xor_sync(0xffffffffu, inv, d));
+  if (lane == 0) {
+    const uint32_t crc = gf2_mul(inv, acc) ^ 0xFFFFFFFFu;
     uint8_t* e = dst + 8 + dl;
     e[0] = (uint8_t)(crc >> 24); e[1] = (uint8_t)(crc >> 16); e[2] = (uint8_t)(crc >> 8); e[3] = (uint8_t)crc;
   }

@@ -460,6 +460,11 @@ struct PngExport {
       uint32_t p = 1u << 30;
       PP.x2n[0] = p;
       for (int k = 1; k < 32; ++k) { p = mul(p, p); PP.x2n[k] = p; }
+      // x^(-1) = x^(2^32 - 2) (x has order 2^32 - 1 modulo the CRC-32 polynomial), then its squares
+      uint32_t inv = 1u << 31;
+      for (int k = 1; k < 32; ++k) inv = mul(PP.x2n[k], inv);
+      PP.xinv2n[0] = inv;
+      for (int k = 1; k < 32; ++k) { inv = mul(inv, inv); PP.xinv2n[k] = inv; }
     }
     stitch::png::png_hist_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
     stitch::png::png_encode_kernel<<<PP.nb, PNG_THREADS, 0, ln.stream>>>(PP);
