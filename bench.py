@@ -60,6 +60,39 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def bind_near_gpu(cuda_index: int) -> dict:
+    """Host placement for the e2e leg: run this rank's submitting thread on the cores of the GPU's NUMA node and
+    prefer that node for new pages, so the pinned bitmaps / canvases (stitch_host_alloc) sit next to the GPU's
+    PCIe root.  With one rank per GPU every rank otherwise allocates wherever the launcher put it, and at N > 1
+    the uploads cross the socket link.  Best effort: returns what was done, never raises."""
+    info = {"node": None, "cpus": None, "mempolicy": None}
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(cuda_index)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return info
+        info["node"] = node
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        sel = cpus & os.sched_getaffinity(0)
+        if sel:
+            os.sched_setaffinity(0, sel)
+            info["cpus"] = len(sel)
+        # set_mempolicy(MPOL_PREFERRED, {node}): x86-64 syscall 238
+        libc = C.CDLL(None, use_errno=True)
+        mask = (C.c_ulong * 16)()
+        mask[node // 64] = 1 << (node % 64)
+        rc = libc.syscall(C.c_long(238), C.c_int(1), mask, C.c_ulong(16 * 64))
+        info["mempolicy"] = "preferred" if rc == 0 else f"errno {C.get_errno()}"
+    except Exception as e:   # no sysfs entry, no permission: stay where we are
+        info["error"] = str(e)[:80]
+    return info
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons through NVML while the timed region runs."""
 
@@ -167,6 +200,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (min(steps, 10))")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-numa", action="store_true", help="do not bind the rank to the GPU's NUMA node")
     ap.add_argument("--lanes", type=int, default=2,
                     help="job lanes of the StitchCtx the device-resident steps rotate over (1 = one job at a time)")
     ap.add_argument("--e2e-lanes", type=int, default=3, help="job lanes for the host-buffer (e2e) steps")
@@ -207,6 +241,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl ours needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    affinity0 = os.sched_getaffinity(0)
+    placement = bind_near_gpu(local_rank) if not args.no_numa else {"node": None}
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     stream = torch.cuda.Stream()
@@ -389,7 +425,8 @@ def main():
                    "inputs": "device-resident RGBA8, generated on device (seed 0x5717C4)",
                    "l2": f"{len(jobs)} job slots rotated; each job reads {src_bytes/1e6:.0f} MB (> 126 MB L2)",
                    "parallelism": f"{world} rank(s), jobs sharded, no collective",
-                   "lanes": f"{max(1, args.lanes)} job lane(s) per ctx for the device-resident steps, {e2e_lanes} for e2e"},
+                   "lanes": f"{max(1, args.lanes)} job lane(s) per ctx for the device-resident steps, {e2e_lanes} for e2e",
+                   "host_placement": placement},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_value, "unit": "MP/s", "h2d_bytes_per_step": src_bytes, "d2h_bytes_per_step": out_bytes,
@@ -407,6 +444,7 @@ def main():
             pass
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
+            os.sched_setaffinity(0, affinity0)   # the CPU leg uses every host core again
             val, ms, cores, _ = cpu_reference_run(args.workload, max(1, args.cpu_steps), 1)
             line["cpu_baseline"] = {"value": val, "unit": "MP/s", "cores": cores, "kind": "port",
                                     "sample": f"{max(1, args.cpu_steps)} full job(s), C restatement fp32 + OpenMP ({ms:.0f} ms/job)"}

@@ -7,10 +7,12 @@
 //
 //   J1 jpeg_dct_kernel      one thread per 8x8 block: level shift, integer LL&M forward DCT in registers,
 //                           quantise, zig-zag -> int16 coefficients in MCU order (Y00 Y01 Y10 Y11 Cb Cr)
-//   J2 jpeg_entropy_kernel  one WARP per restart segment: a lane owns two zig-zag positions of the block;
-//                           zero runs come from two ballots, code lengths from a warp prefix sum, the bits
-//                           are ORed into a per-warp shared-memory window and flushed as bytes with 0xFF
-//                           stuffing into the segment's slot of the scratch stream
+//   J2a jpeg_blockbits_kernel  one THREAD per block: Huffman-codes the block on its own (DC difference against
+//                           the previous block of its component, ffs walk over the nonzero AC positions) into
+//                           <= 53 words of a lane-interleaved scratch, and records the bit count
+//   J2b jpeg_pack_kernel    one WARP per restart segment, a lane per block: warp scan of the bit counts, the
+//                           lanes funnel-shift their words into a shared-memory window, which is flushed as
+//                           bytes with 0xFF stuffing into the segment's slot of the scratch stream
 //   J3 jpeg_offsets_kernel  exclusive scan of the segment lengths (+2 per restart marker) and the header
 //      jpeg_gather_kernel   one warp per segment copies it to its final place and appends RSTn / EOI
 //
@@ -33,8 +35,8 @@ struct HeaderBytes {
 // worst case of one entropy-coded block: DC 9 + 11 bits, 63 x (16 + 10) bits = 1658 bits = 208 bytes, every
 // byte stuffed
 #define JPEG_BLOCK_MAX_BYTES 432
-#define JPEG_WIN_WORDS 128      // per-warp bit window: 512 bytes
-#define JPEG_FLUSH_BITS 2048     // flush once this much is waiting: 2047 + 1665 (worst block) bits still fit
+#define JPEG_BLK_WORDS 64       // words a coded block may take in the block-bits scratch (worst case 1665 bits = 53)
+#define JPEG_WIN_WORDS 512      // per-warp bit window of the packer: 2 KB
 
 #define JDESCALE(x, n) (((x) + (1 << ((n)-1))) >> (n))
 
@@ -141,147 +143,185 @@ __global__ void __launch_bounds__(128) jpeg_dct_kernel(const uint8_t* __restrict
   for (int i = 0; i < 8; ++i) o[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
 }
 
-// ---- J2: entropy coding, one warp per restart segment ----
+// ---- J2: entropy coding in two steps: code every block on its own, then pack the segments ----
 
 __device__ __forceinline__ int hibit(uint32_t x) { return 31 - __clz(x); }  // -1 for x == 0
 
 // value bits of a coefficient / DC difference of magnitude category s (T.81 F.1.2.1)
 __device__ __forceinline__ uint32_t vbits(int v, int s) { return (uint32_t)(v < 0 ? v - 1 : v) & ((1u << s) - 1u); }
 
-// ORs the low `len` (<= 64) bits of `val`, MSB first, into the bit window at bit position `pos`.  The item
-// is left-aligned in 64 bits and lands in up to three words; neighbouring items share a word, hence the atomics.
-__device__ __forceinline__ void win_put(uint32_t* win, int pos, uint64_t val, int len) {
-  if (len == 0) return;
-  const uint64_t x = val << (64 - len);
-  const int wi = pos >> 5, bo = pos & 31;
-  const uint32_t w0 = (uint32_t)(x >> (32 + bo));
-  const uint32_t w1 = (uint32_t)(x >> bo);
-  const uint32_t w2 = bo ? (uint32_t)(x << (32 - bo)) : 0u;
-  if (w0) atomicOr(&win[wi], w0);
-  if (w1) atomicOr(&win[wi + 1], w1);
-  if (w2) atomicOr(&win[wi + 2], w2);
+// Word j of block `slot` in the block-bits scratch.  Blocks are grouped by 32 (one warp of J2a); inside a group
+// the words are interleaved -- word j of the 32 blocks is one 128-byte line -- so that both J2a (lane = block,
+// all lanes near the same j) and J2b (lane = block of a segment) touch whole lines.
+__device__ __forceinline__ size_t blockbits_index(int slot, int j) {
+  return ((size_t)(slot >> 5) * JPEG_BLK_WORDS + (size_t)j) * 32u + (size_t)(slot & 31);
 }
 
-// `seg_cap` bytes of scratch per segment; seg_len[s] receives the byte count (stuffing included).
-__global__ void __launch_bounds__(128) jpeg_entropy_kernel(const int16_t* __restrict__ coef, int n_mcu, int ri, int n_seg,
-                                                           const __grid_constant__ Tables tab, uint8_t* __restrict__ scratch,
-                                                           int64_t seg_cap, uint32_t* __restrict__ seg_len) {
+// J2a.  One THREAD per 8x8 block, blocks in MCU order (the order of `coef`).  The thread parks its 32 coefficient
+// words in its own shared-memory column (bank = lane: conflict-free for any index), walks the nonzero AC
+// positions with ffs over a 64-bit map, and shifts DC difference, (ZRL,) run/size codes + value bits and EOB
+// into a 64-bit register that is drained one 32-bit word at a time, MSB first.  blen[slot] = bits coded; the
+// unused low bits of the last word are zero.  The DC predictor is the previous block of the same component
+// (zero at the start of a restart segment), read from `coef`.
+__global__ void __launch_bounds__(128) jpeg_blockbits_kernel(const int16_t* __restrict__ coef, int n_blocks, int ri,
+                                                             const __grid_constant__ Tables tab, uint32_t* __restrict__ bits,
+                                                             uint32_t* __restrict__ blen) {
   __shared__ uint32_t s_huff[4][256];
+  __shared__ uint32_t s_c[32][128];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < 4 * 256; i += 128) s_huff[i >> 8][i & 255] = tab.huff[i >> 8][i & 255];
+  const int slot = blockIdx.x * 128 + tid;
+  const bool live = slot < n_blocks;
+  uint32_t nzlo = 0, nzhi = 0;   // nonzero maps of zig-zag positions 0..31 / 32..63
+  if (live) {
+    const uint4* src = reinterpret_cast<const uint4*>(coef + (size_t)slot * 64);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint4 v = src[i];
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int wi = 4 * i + k;   // holds positions 2*wi, 2*wi + 1
+        s_c[wi][tid] = w[k];
+        const uint32_t m = ((w[k] & 0xffffu) ? 1u : 0u) | ((w[k] >> 16) ? 2u : 0u);
+        if (wi < 16) nzlo |= m << (2 * wi);
+        else nzhi |= m << (2 * wi - 32);
+      }
+    }
+  }
+  __syncthreads();   // the code tables; s_c columns are private to their thread
+  if (!live) return;
+  const int b = slot % 6, m_idx = slot / 6;
+  const int comp = b < 4 ? 0 : b - 3;
+  const uint32_t* dc = s_huff[comp ? 1 : 0];
+  const uint32_t* ac = s_huff[comp ? 3 : 2];
+  uint32_t* out = bits + blockbits_index(slot, 0);
+  uint64_t acc = 0;
+  int nb = 0, nw = 0;
+  auto put = [&](uint32_t val, int len) {   // len <= 27, nb < 32 on entry
+    acc = (acc << len) | val;
+    nb += len;
+    if (nb >= 32) {
+      nb -= 32;
+      out[(size_t)nw * 32u] = (uint32_t)(acc >> nb);
+      ++nw;
+    }
+  };
+  {
+    int pred = 0;
+    const bool seg_first = (m_idx % ri) == 0;
+    if ((b >= 1 && b <= 3) || !seg_first) {
+      const int prev_slot = b == 0 ? slot - 3 : (b < 4 ? slot - 1 : slot - 6);
+      pred = coef[(size_t)prev_slot * 64];
+    }
+    const int diff = (int)(int16_t)(s_c[0][tid] & 0xffffu) - pred;
+    const int s = 32 - __clz((uint32_t)(diff < 0 ? -diff : diff));
+    const uint32_t e = dc[s];
+    put(((e & 0xffffu) << s) | vbits(diff, s), (int)(e >> 16) + s);
+  }
+  const uint32_t zrl = ac[0xf0];
+  int prev = 0;
+  nzlo &= ~1u;   // position 0 is the DC coefficient
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    uint32_t mask = half ? nzhi : nzlo;
+    while (mask) {
+      const int k = __ffs(mask) - 1 + 32 * half;
+      mask &= mask - 1;
+      const uint32_t w = s_c[k >> 1][tid];
+      const int v = (int)(int16_t)((k & 1) ? (w >> 16) : (w & 0xffffu));
+      int run = k - prev - 1;
+      prev = k;
+      while (run >= 16) {
+        put(zrl & 0xffffu, (int)(zrl >> 16));
+        run -= 16;
+      }
+      const int s = 32 - __clz((uint32_t)(v < 0 ? -v : v));
+      const uint32_t e = ac[(run << 4) | s];
+      put(((e & 0xffffu) << s) | vbits(v, s), (int)(e >> 16) + s);
+    }
+  }
+  if (prev != 63) {
+    const uint32_t e = ac[0];
+    put(e & 0xffffu, (int)(e >> 16));
+  }
+  if (nb) out[(size_t)nw * 32u] = (uint32_t)(acc << (32 - nb));
+  blen[slot] = (uint32_t)(nw * 32 + nb);
+}
+
+// J2b.  One WARP per restart segment: concatenates the segment's coded blocks and writes its bytes with 0xFF
+// stuffing into the segment's slot of the scratch stream; seg_len[s] = byte count (stuffing included).
+// Per round a lane takes one block: a warp scan of the bit lengths gives every block its bit offset, the
+// round takes as many blocks as fit the shared-memory window (at least one: the worst block is 1665 bits),
+// every lane funnel-shifts its block's words to the offset and ORs them into the window -- neighbouring
+// blocks share a word, hence the atomics -- and the complete bytes are flushed.
+__global__ void __launch_bounds__(128) jpeg_pack_kernel(const uint32_t* __restrict__ bits, const uint32_t* __restrict__ blen,
+                                                        int n_blocks, int ri, int n_seg, uint8_t* __restrict__ scratch,
+                                                        int64_t seg_cap, uint32_t* __restrict__ seg_len) {
   __shared__ uint32_t s_win[4][JPEG_WIN_WORDS + 4];
-  for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) s_huff[i >> 8][i & 255] = tab.huff[i >> 8][i & 255];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   uint32_t* win = s_win[warp];
   for (int i = lane; i < JPEG_WIN_WORDS + 4; i += 32) win[i] = 0;
-  __syncthreads();
+  __syncwarp();
   const int seg = blockIdx.x * 4 + warp;
   if (seg >= n_seg) return;
   uint8_t* out = scratch + (int64_t)seg * seg_cap;
   const uint32_t lt = (1u << lane) - 1u;
   int outpos = 0;   // bytes written to the segment so far
-  int carry = 0;    // bits waiting in the window (< JPEG_FLUSH_BITS between blocks)
-  int pred0 = 0, pred1 = 0, pred2 = 0;   // DC predictors of Y, Cb, Cr: zero at every restart
-  const int m0 = seg * ri, m1 = min(m0 + ri, n_mcu);
-  const uint32_t* cw = reinterpret_cast<const uint32_t*>(coef) + (size_t)m0 * 6 * 32;
-  uint32_t next = cw[lane];
-  for (int m = m0; m < m1; ++m) {
-    for (int b = 0; b < 6; ++b) {
-      const uint32_t word = next;
-      cw += 32;
-      if (!(m == m1 - 1 && b == 5)) next = cw[lane];   // prefetch the next block's coefficients
-      const int comp = b < 4 ? 0 : b - 3;
-      const uint32_t* dc = s_huff[comp ? 1 : 0];
-      const uint32_t* ac = s_huff[comp ? 3 : 2];
-      const int c0 = (int16_t)(word & 0xffffu), c1 = (int16_t)(word >> 16);   // zig-zag positions 2*lane, 2*lane+1
-      // nonzero maps; position 0 (DC) is the anchor the first run is counted from
-      const uint32_t nz0 = __ballot_sync(0xffffffffu, c0 != 0) | 1u;   // bit l <-> k = 2l
-      const uint32_t nz1 = __ballot_sync(0xffffffffu, c1 != 0);        // bit l <-> k = 2l + 1
-      uint64_t v0 = 0, v1 = 0, v2 = 0;
-      int l0 = 0, l1 = 0, l2 = 0;
-      const uint32_t zrl = ac[0xf0];
-      auto ac_item = [&](int k, int v, int prev, uint64_t& val, int& len) {
-        const int run = k - prev - 1;
-        const int s = 32 - __clz((uint32_t)(v < 0 ? -v : v));
-        const uint32_t e = ac[((run & 15) << 4) | s];
-        uint64_t x = 0;
-        int n = 0;
-        for (int z = run >> 4; z > 0; --z) {
-          x = (x << (zrl >> 16)) | (zrl & 0xffffu);
-          n += zrl >> 16;
-        }
-        x = (x << (e >> 16)) | (e & 0xffffu);
-        x = (x << s) | vbits(v, s);
-        val = x;
-        len = n + (int)(e >> 16) + s;
-      };
-      if (lane == 0) {   // DC difference
-        const int diff = c0 - (comp == 0 ? pred0 : comp == 1 ? pred1 : pred2);
-        const int s = 32 - __clz((uint32_t)(diff < 0 ? -diff : diff));
-        const uint32_t e = dc[s];
-        v0 = ((uint64_t)(e & 0xffffu) << s) | vbits(diff, s);
-        l0 = (int)(e >> 16) + s;
-      } else if (c0 != 0) {
-        const int prev = max(2 * hibit(nz0 & lt), 2 * hibit(nz1 & lt) + 1);
-        ac_item(2 * lane, c0, prev, v0, l0);
-      }
-      if (c1 != 0) {
-        const int prev = max(2 * hibit(nz0 & (lt | (1u << lane))), 2 * hibit(nz1 & lt) + 1);
-        ac_item(2 * lane + 1, c1, prev, v1, l1);
-      }
-      if (lane == 31) {   // end of block unless position 63 is coded
-        if (c1 == 0) {
-          const uint32_t e = ac[0];
-          v2 = e & 0xffffu;
-          l2 = (int)(e >> 16);
-        }
-      }
-      {
-        const int dcv = __shfl_sync(0xffffffffu, c0, 0);
-        if (comp == 0) pred0 = dcv; else if (comp == 1) pred1 = dcv; else pred2 = dcv;
-      }
-      // bit offsets: exclusive prefix sum of the lanes' lengths
-      const int mine = l0 + l1 + l2;
-      int incl = mine;
+  int carry = 0;    // bits of the last, incomplete byte waiting in win[0] (< 8)
+  int s0 = (int)min((int64_t)seg * ri * 6, (int64_t)n_blocks);
+  const int s1 = (int)min((int64_t)s0 + (int64_t)ri * 6, (int64_t)n_blocks);
+  while (s0 < s1) {
+    const int slot = s0 + lane;
+    int len = slot < s1 ? (int)blen[slot] : 0;
+    int incl = len;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int up = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += up;
-      }
-      const int total = carry + __shfl_sync(0xffffffffu, incl, 31);
-      int pos = carry + incl - mine;
-      win_put(win, pos, v0, l0);
-      pos += l0;
-      win_put(win, pos, v1, l1);
-      pos += l1;
-      win_put(win, pos, v2, l2);
-      __syncwarp();
-      carry = total;
-      // flush the complete bytes with 0xFF stuffing once enough of them wait (and at the segment's end)
-      if (total >= JPEG_FLUSH_BITS || (m == m1 - 1 && b == 5)) {
-        const int nbytes = total >> 3;
-        int extra = 0;
-        for (int j0 = 0; j0 < nbytes; j0 += 32) {
-          const int j = j0 + lane;
-          const bool valid = j < nbytes;
-          const uint32_t by = valid ? (win[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu : 0u;
-          const uint32_t ffm = __ballot_sync(0xffffffffu, valid && by == 0xffu);
-          if (valid) {
-            const int p = outpos + j + extra + __popc(ffm & lt);
-            out[p] = (uint8_t)by;
-            if (by == 0xffu) out[p + 1] = 0;
-          }
-          extra += __popc(ffm);
-        }
-        outpos += nbytes + extra;
-        // keep the partial byte, clear the rest of the window
-        carry = total & 7;
-        const uint32_t part = carry ? ((win[nbytes >> 2] >> (24 - 8 * (nbytes & 3))) & 0xffu) << 24 : 0u;
-        __syncwarp();
-        for (int i = lane; i <= (total >> 5) + 1; i += 32) win[i] = 0;
-        __syncwarp();
-        if (lane == 0) win[0] = part;
-        __syncwarp();
-      }
+    for (int d = 1; d < 32; d <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
     }
+    const bool fits = slot < s1 && carry + incl <= JPEG_WIN_WORDS * 32;
+    const int n_take = __popc(__ballot_sync(0xffffffffu, fits));   // a prefix of the lanes, >= 1
+    const int total = carry + __shfl_sync(0xffffffffu, incl, n_take - 1);
+    if (lane >= n_take) len = 0;
+    const int pos = carry + incl - len;
+    const int nw = (len + 31) >> 5;
+    const int maxw = __reduce_max_sync(0xffffffffu, nw);
+    const uint32_t* src = bits + blockbits_index(min(slot, n_blocks - 1), 0);
+    const int wi = pos >> 5, bo = pos & 31;
+    uint32_t prevw = 0;
+    for (int j = 0; j <= maxw; ++j) {
+      const uint32_t w = j < nw ? src[(size_t)j * 32u] : 0u;
+      const uint32_t piece = __funnelshift_r(w, prevw, bo);   // low word of (prevw:w) >> bo
+      if (j <= nw && piece) atomicOr(&win[wi + j], piece);
+      prevw = w;
+    }
+    __syncwarp();
+    s0 += n_take;
+    // flush the complete bytes with 0xFF stuffing
+    const int nbytes = total >> 3;
+    int extra = 0;
+    for (int j0 = 0; j0 < nbytes; j0 += 32) {
+      const int j = j0 + lane;
+      const bool valid = j < nbytes;
+      const uint32_t by = valid ? (win[j >> 2] >> (24 - 8 * (j & 3))) & 0xffu : 0u;
+      const uint32_t ffm = __ballot_sync(0xffffffffu, valid && by == 0xffu);
+      if (valid) {
+        const int p = outpos + j + extra + __popc(ffm & lt);
+        out[p] = (uint8_t)by;
+        if (by == 0xffu) out[p + 1] = 0;
+      }
+      extra += __popc(ffm);
+    }
+    outpos += nbytes + extra;
+    // keep the partial byte, clear the rest of the window
+    carry = total & 7;
+    const uint32_t part = carry ? ((win[nbytes >> 2] >> (24 - 8 * (nbytes & 3))) & 0xffu) << 24 : 0u;
+    __syncwarp();
+    for (int i = lane; i <= (total >> 5) + 1; i += 32) win[i] = 0;
+    __syncwarp();
+    if (lane == 0) win[0] = part;
+    __syncwarp();
   }
   // pad the last byte with 1-bits (stuffed like any other byte)
   if (lane == 0) {

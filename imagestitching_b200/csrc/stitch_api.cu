@@ -291,7 +291,7 @@ struct JpegExport {
   uint8_t* j_file = nullptr;
   int16_t* j_coef = nullptr;
   uint8_t* j_scratch = nullptr;
-  uint32_t* j_len = nullptr;
+  uint32_t *j_len = nullptr, *j_bits = nullptr, *j_blen = nullptr;
   uint64_t *j_off = nullptr, *j_info = nullptr;
 
   int carve(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, int cw, int ch, bool want_yuv, bool host,
@@ -313,7 +313,9 @@ struct JpegExport {
     const size_t b_scr = up((size_t)n_seg * (size_t)seg_cap);
     const size_t b_len = up((size_t)n_seg * 4), b_off = up((size_t)n_seg * 8), b_info = 256;
     const size_t b_file = out_host ? up((size_t)j_cap) : 0;
-    const size_t need = b_yuv + b_coef + b_scr + b_len + b_off + b_info + b_file;
+    const size_t n_blk = (size_t)n_mcu * 6;
+    const size_t b_bits = up((n_blk + 31) / 32 * JPEG_BLK_WORDS * 32 * sizeof(uint32_t)), b_blen = up(n_blk * 4);
+    const size_t need = b_yuv + b_coef + b_scr + b_len + b_off + b_info + b_file + b_bits + b_blen;
     if (ln.jpeg_arena_cap < need) {
       if (ln.jpeg_arena) {
         CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
@@ -334,6 +336,8 @@ struct JpegExport {
     j_len = (uint32_t*)a; a += b_len;
     j_off = (uint64_t*)a; a += b_off;
     j_info = (uint64_t*)a; a += b_info;
+    j_bits = (uint32_t*)a; a += b_bits;
+    j_blen = (uint32_t*)a; a += b_blen;
     j_file = out_host ? a : (uint8_t*)job->out_jpeg;
     return STITCH_OK;
   }
@@ -349,14 +353,16 @@ struct JpegExport {
     const int n_blocks = n_mcu * 6;
     stitch::jpeg::jpeg_dct_kernel<<<(n_blocks + 127) / 128, 128, 0, ln.stream>>>(P.out_y, P.out_cb, P.out_cr, cw, ch, mcu_x,
                                                                               mcu_y, tab, j_coef);
-    stitch::jpeg::jpeg_entropy_kernel<<<(n_seg + 3) / 4, 128, 0, ln.stream>>>(j_coef, n_mcu, jpeg_ri, n_seg, tab, j_scratch,
-                                                                             seg_cap, j_len);
+    stitch::jpeg::jpeg_blockbits_kernel<<<(n_blocks + 127) / 128, 128, 0, ln.stream>>>(j_coef, n_blocks, jpeg_ri, tab, j_bits,
+                                                                                    j_blen);
+    stitch::jpeg::jpeg_pack_kernel<<<(n_seg + 3) / 4, 128, 0, ln.stream>>>(j_bits, j_blen, n_blocks, jpeg_ri, n_seg, j_scratch,
+                                                                          seg_cap, j_len);
     stitch::jpeg::jpeg_offsets_kernel<<<1, 1024, 0, ln.stream>>>(j_len, n_seg, hdr, j_file, j_cap, j_off, j_info);
     stitch::jpeg::jpeg_gather_kernel<<<(n_seg + 7) / 8, 256, 0, ln.stream>>>(j_scratch, seg_cap, j_len, j_off, n_seg, j_info,
                                                                             j_file);
     CUDA_TRY(ctx, cudaGetLastError());
-    ctx->launches += 4;
-    res->kernel_launches += 4;
+    ctx->launches += 5;
+    res->kernel_launches += 5;
     CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, j_info, 16, cudaMemcpyDeviceToHost, ln.stream));
     CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
     res->jpeg_bytes = (int64_t)ln.jpeg_info_host[0];

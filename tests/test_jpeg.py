@@ -123,7 +123,7 @@ def test_gpu_jpeg_only_and_defaults(ctx):
     both = _gpu_case(ctx, dims, "vertical", 300, 0, 0)
     only = _gpu_case(ctx, dims, "vertical", 300, 0, 0, output="jpeg")
     assert only.rgba is None and only.y is None and only.jpeg == both.jpeg
-    assert only.kernel_launches == 5
+    assert only.kernel_launches == 6
     withrgba = _gpu_case(ctx, dims, "vertical", 300, 0, 0, output="rgba+jpeg")
     assert withrgba.jpeg == both.jpeg and (withrgba.rgba == both.rgba).all()
 
