@@ -343,38 +343,36 @@ __global__ void __launch_bounds__(1024) jpeg_offsets_kernel(const uint32_t* __re
                                                             const __grid_constant__ HeaderBytes hdr, uint8_t* __restrict__ out,
                                                             int64_t cap, uint64_t* __restrict__ seg_off, uint64_t* __restrict__ info) {
   __shared__ uint64_t s_warp[32];
-  __shared__ uint64_t s_carry;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_carry = (uint64_t)hdr.n;
+  // thread t owns the segments [t * per, t * per + per): its loads are independent, then ONE block scan
+  const int per = (n_seg + 1023) / 1024;
+  const int i0 = min(tid * per, n_seg), i1 = min(i0 + per, n_seg);
+  uint64_t mine = 0;
+  for (int i = i0; i < i1; ++i) mine += (uint64_t)seg_len[i] + (i + 1 < n_seg ? 2u : 0u);
+  uint64_t incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint64_t up = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += up;
+  }
+  if (lane == 31) s_warp[warp] = incl;
   __syncthreads();
-  for (int base = 0; base < n_seg; base += 1024) {
-    const int i = base + tid;
-    const uint64_t mine = i < n_seg ? (uint64_t)seg_len[i] + (i + 1 < n_seg ? 2u : 0u) : 0u;
-    uint64_t incl = mine;
+  if (warp == 0) {
+    uint64_t v = s_warp[lane];
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const uint64_t up = __shfl_up_sync(0xffffffffu, incl, d);
-      if (lane >= d) incl += up;
+      const uint64_t up = __shfl_up_sync(0xffffffffu, v, d);
+      if (lane >= d) v += up;
     }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    if (warp == 0) {
-      uint64_t v = s_warp[lane];
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint64_t up = __shfl_up_sync(0xffffffffu, v, d);
-        if (lane >= d) v += up;
-      }
-      s_warp[lane] = v;
-    }
-    __syncthreads();
-    const uint64_t before = s_carry + (warp ? s_warp[warp - 1] : 0) + incl - mine;
-    if (i < n_seg) seg_off[i] = before;
-    __syncthreads();
-    if (tid == 1023) s_carry = before + mine;
-    __syncthreads();
+    s_warp[lane] = v;
   }
-  const uint64_t total = s_carry + 2;   // EOI
+  __syncthreads();
+  uint64_t run = (uint64_t)hdr.n + (warp ? s_warp[warp - 1] : 0) + incl - mine;
+  for (int i = i0; i < i1; ++i) {
+    seg_off[i] = run;
+    run += (uint64_t)seg_len[i] + (i + 1 < n_seg ? 2u : 0u);
+  }
+  const uint64_t total = (uint64_t)hdr.n + s_warp[31] + 2;   // EOI
   if (tid == 0) {
     info[0] = total;
     info[1] = total > (uint64_t)cap ? 1u : 0u;
