@@ -128,10 +128,18 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
       fma2_s(v[k], v[k + 1], B[k], B[k + 1], tv);
     }
     if (RGBA) {
+      // quantise in register pairs (R0 G0)(B0 R1)(G1 B1)(R2 G2)(B2 R3)(G3 B3): a pair that holds a blue value takes
+      // the negated form -- pack_rgb reads only the low byte of red and green, which is the same in both forms
+      uint32_t q[12];
+      quant2(q[0], q[1], v[0], v[1]);
+      quant2_neg(q[2], q[3], v[2], v[3]);
+      quant2_neg(q[4], q[5], v[4], v[5]);
+      quant2(q[6], q[7], v[6], v[7]);
+      quant2_neg(q[8], q[9], v[8], v[9]);
+      quant2_neg(q[10], q[11], v[10], v[11]);
       uint32_t px[4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k)
-        px[k] = pack_rgb(quant_bits(v[k * 3]), quant_bits(v[k * 3 + 1]), quant_bits_neg(v[k * 3 + 2]));
+      for (int k = 0; k < 4; ++k) px[k] = pack_rgb(q[k * 3], q[k * 3 + 1], q[k * 3 + 2]);
       if (vec_ok) {
         *reinterpret_cast<uint4*>(orow) = make_uint4(px[0], px[1], px[2], px[3]);
       } else {
