@@ -222,6 +222,7 @@ __global__ void __launch_bounds__(128) jpeg_blockbits_kernel(const int16_t* __re
   const uint32_t zrl = ac[0xf0];
   int prev = 0;
   nzlo &= ~1u;   // position 0 is the DC coefficient
+  // (fetching the next nonzero position's word while the current one is coded was measured: 67 -> 70 us)
 #pragma unroll 1
   for (int half = 0; half < 2; ++half) {
     uint32_t mask = half ? nzhi : nzlo;

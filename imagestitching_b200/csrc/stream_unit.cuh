@@ -282,17 +282,13 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   float acc[12];
 #pragma unroll
   for (int k = 0; k < 12; ++k) acc[k] = 0.f;
-  uint32_t and_acc = 0xffffffffu;
+  uint32_t and_x = 0xffffffffu, and_y = 0xffffffffu, and_z = 0xffffffffu, and_w = 0xffffffffu;
   const uint32_t tab_s = smem_u32(ws.tab);
   uint32_t hoff = 0;  // byte offset of the ring part the current STREAM_UNR rows live in
 
   // One source row: vertical accumulate; when the row completes an output row (EMIT), the horizontal
   // pass runs in registers and the accumulators restart with the row's share of the next output row.
   auto row_step = [&](const uint4& px, const float wc, const float wn, const bool emit) {
-    and_acc &= px.x;
-    and_acc &= (px.y | m1);
-    and_acc &= (px.z | m2);
-    and_acc &= (px.w | m3);
     float f[12];
     f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x);
     f[3] = expand<0>(px.y); f[4] = expand<1>(px.y); f[5] = expand<2>(px.y);
@@ -427,6 +423,11 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
         cp_async16(ring_h + (u + 1) * STREAM_STAGE_BYTES, lbase + off);
         off = min(off + pitch, off_max);
         cp_async_commit();
+        // alpha check: per column and per row pair, one three-input LOP3 each; the edge masks come in at the end
+        and_x &= pa.x & pb.x;
+        and_y &= pa.y & pb.y;
+        and_z &= pa.z & pb.z;
+        and_w &= pa.w & pb.w;
         row_step(pa, t2.x, t2.y, (mask >> u) & 1u);
         row_step(pb, t2.z, t2.w, (mask >> (u + 1)) & 1u);
       }
@@ -436,6 +437,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   }
   // Translucent bitmaps (rare: photos are opaque): the unit is redone with the exact premultiplied
   // source-over evaluation.  Outside the hot loop so it costs the streaming path no registers.
+  const uint32_t and_acc = and_x & (and_y | m1) & (and_z | m2) & (and_w | m3);
   const bool need_fix = (and_acc >> 24) != 0xffu;
   if (__any_sync(0xffffffffu, need_fix)) {
     const int xf0 = __shfl_sync(0xffffffffu, Xfirst, 0), xf1 = __shfl_sync(0xffffffffu, Xfirst, STRIDE);

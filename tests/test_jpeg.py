@@ -89,8 +89,8 @@ def test_product_tables_equal_oracle_tables():
 BIG = 26 * 1024 * 1024
 
 
-def _gpu_case(ctx, dims, direction, size, q, ri, output="both+jpeg", mode="min"):
-    bitmaps = [U.synth_image(w, h, 321 + i, 0) for i, (w, h) in enumerate(dims)]
+def _gpu_case(ctx, dims, direction, size, q, ri, output="both+jpeg", mode="min", pattern=0):
+    bitmaps = [U.synth_image(w, h, 321 + i, pattern) for i, (w, h) in enumerate(dims)]
     fs = [BIG] + [0] * (len(dims) - 1)
     got = ctx.run(U.page_images(dims, bitmaps, None, fs), direction, mode=mode, platform="ios",
                   deviceMaxCanvasSize=size or None, output=output, jpeg_quality=q, jpeg_restart_interval=ri)
@@ -114,6 +114,27 @@ def test_gpu_file_is_byte_identical_to_oracle(ctx, dims, direction, size, q, ri)
     size_, ycc = _decode_ycc(got.jpeg)
     assert size_ == (got.width, got.height)
     assert _psnr(ycc[:, :, 0], got.y) >= (40.0 if q >= 95 else 36.0 if q >= 90 else 28.0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dims,q,ri,pattern", [
+    ([(256, 160)], 100, 8, 1),       # uniform noise copied 1:1, all-ones tables: ~60 long codes per block, so a
+    ([(256, 160)], 100, 64, 1),      # packer round takes fewer than 32 blocks and a segment needs many rounds
+    ([(333, 77)], 100, 65535, 1),    # one segment for the whole file
+    ([(320, 240)], 90, 8, 3),        # 1-px checkerboard: one extreme coefficient behind a long zero run (ZRL)
+    ([(64, 64)], 100, 1, 2),         # noise with translucent alpha over white, a segment per MCU
+])
+def test_gpu_worst_case_blocks(ctx, dims, q, ri, pattern):
+    """Blocks near the 1665-bit worst case: the block coder's word drain and the packer's window rounds."""
+    got = _gpu_case(ctx, dims, "vertical", 0, q, ri, pattern=pattern)
+    assert (got.width, got.height) == dims[0]
+    want = J.encode_i420(got.y, got.cb, got.cr, q, ri)
+    assert got.jpeg == want
+    size_, ycc = _decode_ycc(got.jpeg)
+    assert size_ == (got.width, got.height)
+    assert _psnr(ycc[:, :, 0], got.y) >= 36.0
+    if pattern == 1 and q == 100:
+        assert len(got.jpeg) > got.width * got.height   # > 8 bits per pixel: these blocks really are long
 
 
 @pytest.mark.gpu
