@@ -184,7 +184,10 @@ __device__ __forceinline__ void compose_loop(const JobParam& P, const Plan& plan
     if (STREAM && R.kind == REGION_STREAM) {
       stream_unit<MAXO, HOPS, MODE>(P, R, tx, ty, *ws, lane);
     } else if (R.kind == REGION_UPSCALE) {
-      upscale_unit<MODE>(P, R, tx, ty, lane);
+      // window of source pixels per lane and row (upscale_unit.cuh): launch.cuh picks 4 for scales >= 1.5; the
+      // kernel with streaming units compiles the general width only
+      if (!STREAM && R.g_base == 4) upscale_unit<MODE, 4>(P, R, tx, ty, lane);
+      else upscale_unit<MODE, 5>(P, R, tx, ty, lane);
     } else if (R.kind == REGION_FILL) {
       fill_unit<MODE>(P, R, tx, ty, lane);
     } else {

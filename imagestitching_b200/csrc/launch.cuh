@@ -44,6 +44,7 @@ inline bool stream_eligible(const ImgParam& im) {
 inline bool upscale_eligible(const ImgParam& im) {
   if (im.transpose) return false;
   if (!(im.W >= (double)im.sx_len && im.H >= (double)im.sy_len)) return false;
+  if (im.sx_len < 5) return false;   // a lane loads a window of up to 5 source pixels per row
   if (((uintptr_t)im.data & 3) || (im.pitch & 3)) return false;
   if (!(std::fabs(im.X0) < 1e8 && std::fabs(im.Y0) < 1e8 && im.W < 1e8 && im.H < 1e8)) return false;
   return true;
@@ -138,6 +139,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
     r.x0 = bx.ix0 * cs; r.x1 = bx.ix1 * cs; r.y0 = bx.iy0 * cs; r.y1 = bx.iy1 * cs;
     r.tile_w = UPSCALE_TILE_W;
     r.tile_h = UPSCALE_TILE_H;
+    r.g_base = (P.img[r.img].W / (double)P.img[r.img].sx_len >= 1.5) ? 4 : 5;   // source window per lane
     r.tiles_x = (r.x1 - (r.x0 & ~3) + UPSCALE_TILE_W - 1) / UPSCALE_TILE_W;
     regs.push_back(r);
   }
@@ -195,6 +197,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
   static const double body_frac = [] { const char* e = std::getenv("STITCH_BODY_FRAC"); return e ? atof(e) : 0.75; }();
   static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? atoi(e) : 32; }();
   static const double up_body_frac = [] { const char* e = std::getenv("STITCH_UP_BODY_FRAC"); return e ? atof(e) : 0.8; }();
+  static const int up_tail_h = [] { const char* e = std::getenv("STITCH_UP_TAIL_H"); return e ? std::min(32, std::max(2, atoi(e) & ~1)) : UPSCALE_TAIL_H; }();
   const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_UNR;
   auto tile_h_for = [&](const Region& r, int src_rows) {
     const ImgParam& im = P.img[r.img];
@@ -265,7 +268,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
       if (r.y0 + hb < r.y1) {
         Region t = r;
         t.y0 = r.y0 + hb;
-        t.tile_h = UPSCALE_TAIL_H;
+        t.tile_h = up_tail_h;
         tails.push_back(t);
       }
     }

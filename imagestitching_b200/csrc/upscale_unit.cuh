@@ -10,6 +10,12 @@
 // output-bound (one 16-byte store per lane and row); source pixels come through L1 with 32-bit loads:
 // a lane keeps, for the two source rows its output row blends, the horizontally interpolated values of
 // its 4 pixels in registers and reloads a row only when the output row moves on to the next one.
+//
+// Horizontal pass: the 8 column taps of a lane's 4 pixels lie inside a WINDOW of WIN consecutive source
+// pixels (WIN = 4 when the scale is >= 1.5, else 5: the upper taps of pixels x and x+3 are at most
+// ceil(3 / scale) apart).  The lane loads and expands the window once per source row (WIN loads, 3 WIN PRMT
+// instead of 8 loads and 24 PRMT for the taps one by one) and applies a per-lane 4 x WIN weight matrix that
+// holds (1 - t) and t at each pixel's two taps and zeros elsewhere.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -22,7 +28,7 @@ namespace stitch {
 
 #define UPSCALE_TILE_W 128
 #define UPSCALE_TILE_H 32
-#define UPSCALE_TAIL_H 8   // unit height at the end of the hand-out order (launch.cuh)
+#define UPSCALE_TAIL_H 16  // unit height at the end of the hand-out order (launch.cuh)
 
 // fp64 tap position of device pixel j on one axis, exactly as gather_kernel.cuh::axis_taps evaluates it
 // for a fully covered pixel: u = ((j + 0.5) - d0) / s - 0.5 with s = dlen / slen.
@@ -41,7 +47,7 @@ __device__ __forceinline__ void bilinear_tap(int j, double d0, double s, int sle
   *ib = i_b;
 }
 
-template <int MODE>
+template <int MODE, int WIN>
 __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R, int tx, int ty, int lane) {
   constexpr bool RGBA = MODE != STREAM_MODE_YUV, YUV = MODE != STREAM_MODE_RGBA;
   const ImgParam& im = P.img[R.img];
@@ -50,18 +56,31 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
   const int q = (R.x0 >> 2) + tx * 32 + lane;  // this lane's aligned quad of canvas pixels
   const int xq = 4 * q;
 
-  // ---- column taps of the lane's 4 pixels (byte offsets inside a bitmap row) ----
-  uint32_t offA[4], offB[4];
-  float tcol[4];
+  // ---- column taps of the lane's 4 pixels -> window start and weight matrix ----
+  // wt[c][j]: weight of window pixel j in output pixel c.  Stored so that (wt[0][j], wt[1][j]) and
+  // (wt[2][j], wt[3][j]) are register pairs: the blue channel is interpolated two pixels at a time.
+  float wt[4][WIN];
   bool ok[4];
+  uint32_t offW;
+  {
+    int ia[4], ib[4];
+    float tcol[4];
+    int wmin = 0x7fffffff;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int x = xq + k;
-    ok[k] = x >= R.x0 && x < R.x1;
-    int ia, ib;
-    bilinear_tap(min(max(x, R.x0), R.x1 - 1), im.X0, sx, im.sx_len, im.flip_x != 0, &ia, &ib, &tcol[k]);
-    offA[k] = (uint32_t)ia * 4u;
-    offB[k] = (uint32_t)ib * 4u;
+    for (int k = 0; k < 4; ++k) {
+      const int x = xq + k;
+      ok[k] = x >= R.x0 && x < R.x1;
+      bilinear_tap(min(max(x, R.x0), R.x1 - 1), im.X0, sx, im.sx_len, im.flip_x != 0, &ia[k], &ib[k], &tcol[k]);
+      wmin = min(wmin, min(ia[k], ib[k]));
+    }
+    wmin = max(min(wmin, im.sx_len - WIN), 0);   // the window stays inside the row (launch.cuh: sx_len >= 5)
+    offW = (uint32_t)wmin * 4u;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int ja = ia[k] - wmin, jb = ib[k] - wmin;
+#pragma unroll
+      for (int j = 0; j < WIN; ++j) wt[k][j] = (ja == j ? 1.f - tcol[k] : 0.f) + (jb == j ? tcol[k] : 0.f);
+    }
   }
   // ---- row taps: lane r evaluates output row y0 + r once, the row loop fetches them by shuffle.
   // k_r is the UNCLAMPED index of the upper tap (floor(u), may be -1); the device rect is at least as tall
@@ -84,23 +103,32 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
 
   uint32_t and_acc = 0xffffffffu;
   auto issue = [&](int k, uint32_t* raw) {
-    const uint8_t* base = im.data + (int64_t)src_row(k) * im.pitch;
-    asm("" : "+l"(base));  // keep ONE row pointer; otherwise the multiply is re-associated into every tap
+    const uint32_t* base = reinterpret_cast<const uint32_t*>(im.data + (int64_t)src_row(k) * im.pitch + (size_t)offW);
+    asm("" : "+l"(base));  // keep ONE row pointer; the loads take immediate offsets
 #pragma unroll
-    for (int c = 0; c < 4; ++c) {
-      raw[c] = __ldg(reinterpret_cast<const uint32_t*>(base + (size_t)offA[c]));
-      raw[4 + c] = __ldg(reinterpret_cast<const uint32_t*>(base + (size_t)offB[c]));
-    }
+    for (int j = 0; j < WIN; ++j) raw[j] = __ldg(base + j);
   };
-  auto convert = [&](const uint32_t* raw, float* h) {  // 1 + v * 2^-15 form, interpolated along x
+  // h layout: h[2c], h[2c+1] = red, green of pixel c; h[8 + c] = blue of pixel c (1 + v * 2^-15 form)
+  auto convert = [&](const uint32_t* raw, float* h) {
+    float fr[WIN], fg[WIN], fb[WIN];
+#pragma unroll
+    for (int j = 0; j < WIN; ++j) {
+      and_acc &= raw[j];
+      fr[j] = expand<0>(raw[j]);
+      fg[j] = expand<1>(raw[j]);
+      fb[j] = expand<2>(raw[j]);
+    }
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
-      const uint32_t pa = raw[c], pb = raw[4 + c];
-      and_acc &= pa & pb;
-      const float a0 = expand<0>(pa), a1 = expand<1>(pa), a2 = expand<2>(pa);
-      h[c * 3 + 0] = fmaf(tcol[c], expand<0>(pb) - a0, a0);
-      h[c * 3 + 1] = fmaf(tcol[c], expand<1>(pb) - a1, a1);
-      h[c * 3 + 2] = fmaf(tcol[c], expand<2>(pb) - a2, a2);
+      mul2_s(h[2 * c], h[2 * c + 1], fr[0], fg[0], wt[c][0]);
+#pragma unroll
+      for (int j = 1; j < WIN; ++j) fma2_s(h[2 * c], h[2 * c + 1], fr[j], fg[j], wt[c][j]);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c += 2) {
+      mul2_s(h[8 + c], h[9 + c], wt[c][0], wt[c + 1][0], fb[0]);
+#pragma unroll
+      for (int j = 1; j < WIN; ++j) fma2_s(h[8 + c], h[9 + c], wt[c][j], wt[c + 1][j], fb[j]);
     }
   };
 
@@ -128,18 +156,15 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
       fma2_s(v[k], v[k + 1], B[k], B[k + 1], tv);
     }
     if (RGBA) {
-      // quantise in register pairs (R0 G0)(B0 R1)(G1 B1)(R2 G2)(B2 R3)(G3 B3): a pair that holds a blue value takes
-      // the negated form -- pack_rgb reads only the low byte of red and green, which is the same in both forms
+      // red / green pairs in the plain form, the blue pairs in the negated one (pack_rgb takes alpha from its sign)
       uint32_t q[12];
-      quant2(q[0], q[1], v[0], v[1]);
-      quant2_neg(q[2], q[3], v[2], v[3]);
-      quant2_neg(q[4], q[5], v[4], v[5]);
-      quant2(q[6], q[7], v[6], v[7]);
+#pragma unroll
+      for (int k = 0; k < 8; k += 2) quant2(q[k], q[k + 1], v[k], v[k + 1]);
       quant2_neg(q[8], q[9], v[8], v[9]);
       quant2_neg(q[10], q[11], v[10], v[11]);
       uint32_t px[4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) px[k] = pack_rgb(q[k * 3], q[k * 3 + 1], q[k * 3 + 2]);
+      for (int k = 0; k < 4; ++k) px[k] = pack_rgb(q[2 * k], q[2 * k + 1], q[8 + k]);
       if (vec_ok) {
         *reinterpret_cast<uint4*>(orow) = make_uint4(px[0], px[1], px[2], px[3]);
       } else {
@@ -153,7 +178,7 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
       uint32_t yq[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const float R_ = v[k * 3], G_ = v[k * 3 + 1], B_ = v[k * 3 + 2];
+        const float R_ = v[2 * k], G_ = v[2 * k + 1], B_ = v[8 + k];
         yq[k] = quant_bits(fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_))) & 0xffu;
         ccb[k >> 1] += fmaf(-0.168736f, R_, fmaf(-0.331264f, G_, 0.5f * B_));
         ccr[k >> 1] += fmaf(0.5f, R_, fmaf(-0.418688f, G_, -0.081312f * B_));
@@ -184,14 +209,14 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
   };
 
   float hA[12], hB[12];
-  uint32_t raw[8];
+  uint32_t raw[WIN];
   int k = __shfl_sync(0xffffffffu, k_r, 0);
   // bit r: output row r starts a new source-row pair (k advances by exactly one there)
   const int k_prev = __shfl_up_sync(0xffffffffu, k_r, 1);
   const uint32_t step = __ballot_sync(0xffffffffu, lane > 0 && k_r != k_prev);
   const int nrows = y1 - y0;
   {
-    uint32_t raw2[8];
+    uint32_t raw2[WIN];
     issue(k, raw);
     issue(k + 1, raw2);
     convert(raw, hA);

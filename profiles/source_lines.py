@@ -21,7 +21,7 @@ for r in rows[hi + 1:]:
     except ValueError:
         continue
     cnt[r[0]] += n
-    smp[r[0]] += int(r[sm] or 0)
+    smp[r[0]] += int(r[sm]) if r[sm].strip().isdigit() else 0
     text[r[0]] = r[1]
 tot, stot = sum(cnt.values()), sum(smp.values())
 print(f"warp instructions {tot}, samples {stot}")
