@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- output MP/s of the 9x12MP vertical stitch (BASELINE.json configs[1]) on N B200s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg2_yuv|cfg1|cfg3]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg2_yuv|cfg2_jpeg|cfg2_png|cfg2_android|cfg1|cfg3|cfg3_min]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One "step" = one stitch job (layout + fused resample/compose of all 9 images into the
@@ -41,6 +41,10 @@ WORKLOADS = {
                   "9x 4032x3024 vertical stitch exported as a baseline JPEG file (quality 90, GPU encoder; SURVEY 8f rank 1)"),
     "cfg2_png": ([(4032, 3024)] * 9, "vertical", "min", "ios", "png",
                  "9x 4032x3024 vertical stitch exported as the PNG file the page asks for (GPU encoder; index.js:1579)"),
+    "cfg2_android": ([(4032, 3024)] * 9, "vertical", "min", "android", "rgba",
+                     "9x 4032x3024 RGBA vertical stitch, Android/other canvas clamp -> 606x4096 (6.65x downscale; SURVEY 8d)"),
+    "cfg3_min": (MIXED, "horizontal", "min", "ios", "rgba",
+                 "9 mixed-aspect images horizontal 'min' -> 7765x720 (all downscale; SURVEY 8d)"),
     "cfg1": ([(1080, 1920)] * 2, "vertical", "min", "ios", "rgba",
              "2x 1080x1920 vertical stitch, 2.2x supersampled canvas 2376x8448 (BASELINE configs[0])"),
     "cfg3": (MIXED, "horizontal", "max", "ios", "rgba",
@@ -295,10 +299,14 @@ def main():
         jobs.append((job, keep2, o_rgba, o_yuv, o_jpeg, o_png))
     res = L.StitchResult()
 
+    host_s = [0.0]
+
     def step(i):
         job = jobs[i % len(jobs)][0]
         t = C.c_uint64()
+        h0 = time.perf_counter()
         st = lib.stitch_submit(ctx.handle, C.byref(job), C.byref(res), C.byref(t))
+        host_s[0] += time.perf_counter() - h0
         if st != 0:
             raise RuntimeError(f"stitch_submit failed: {st} {lib.stitch_last_error(ctx.handle)}")
         return t.value
@@ -324,6 +332,7 @@ def main():
     torch.cuda.synchronize()
     sampler.start()
     ev0.record(stream)
+    host_s[0] = 0.0
     for i in range(args.steps):
         last = step(i)
     ctx.join()
@@ -428,6 +437,7 @@ def main():
                    "lanes": f"{max(1, args.lanes)} job lane(s) per ctx for the device-resident steps, {e2e_lanes} for e2e",
                    "host_placement": placement},
         "gpu_launches": int(launches),
+        "host_us_per_submit": round(host_s[0] / max(1, args.steps) * 1e6, 2),   # layout + plan + launch inside stitch_submit
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_value, "unit": "MP/s", "h2d_bytes_per_step": src_bytes, "d2h_bytes_per_step": out_bytes,
                 "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3, "single_job_latency_ms": e2e_single_ms},

@@ -313,6 +313,22 @@ def test_upscale_wide_and_tiny(ctx):
     _go_up(ctx, [(7, 5)], "horizontal", "min")
 
 
+@pytest.mark.parametrize("size,orientation", [(720, 1), (894, 2), (900, 3), (906, 4), (1000, 1), (1290, 2)])
+def test_upscale_window_widths(ctx, size, orientation):
+    """Scales 1.2 ... 2.15 around the 1.5 switch between the 5- and the 4-pixel source window of a lane."""
+    dims = [(400, 300), (400, 300)]
+    got, lay = _go_up(ctx, dims, "vertical", "min", size=size, orientations=[orientation, 1], outputs=("rgba", "both"))
+    assert abs(lay.superSample - size / 600.0) < 1e-9 and _n_up(got) == 2
+
+
+def test_upscale_narrow_sources(ctx):
+    """Bitmaps of 5 and 6 columns still take upscale units (window clamped to the row); 4 columns do not."""
+    got, _ = _go_up(ctx, [(40, 30), (5, 30), (6, 21)], "vertical", "max", outputs=("rgba",))
+    assert _n_up(got) == 3
+    got, _ = _go_up(ctx, [(40, 30), (4, 30)], "vertical", "max", outputs=("rgba",))
+    assert _n_up(got) == 1
+
+
 def test_upscale_translucent(ctx):
     dims = [(90, 60)] * 2
     bm = [U.synth_image(w, h, 5 + i, 2) for i, (w, h) in enumerate(dims)]
