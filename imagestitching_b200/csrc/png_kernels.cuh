@@ -41,6 +41,7 @@ struct Params {
   const uint8_t* rgba;
   int64_t pitch;
   int32_t w, h, nb;
+  uint32_t w_magic;            // ceil(2^32 / w) for 2 <= w <= 16384, else 0 (see div_w)
   uint8_t* lens;               // [nb][PNG_TAB_STRIDE]
   uint16_t* codes;             // [nb][PNG_TAB_STRIDE]
   uint32_t* adler;             // [nb][2]: Adler pair of the band's bytes started from (1, 0)
@@ -114,7 +115,10 @@ struct ThreadTokens {
   uint32_t lens;      // 8 bits per match, in slot order: length - 3
 };
 
-__device__ __forceinline__ int multiples_before(int q, int w) { return (q + w - 1) / w; }   // multiples of w in [0, q)
+// q / w for a pixel index q inside a band (q < (PNG_BAND_ROWS + 1) * w): one multiply-high.  Exact for 2 <= w <= 16384:
+// with m = ceil(2^32 / w), m * w - 2^32 < w and q * w < 9 * 16384^2 < 2^32.  Other widths: w_magic = 0, plain division.
+__device__ __forceinline__ int div_w(const Params& P, int q) { return P.w_magic ? (int)__umulhi((uint32_t)q, P.w_magic) : q / P.w; }
+__device__ __forceinline__ int multiples_before(const Params& P, int q) { return div_w(P, q + P.w - 1); }   // multiples of w in [0, q)
 
 __device__ __forceinline__ uint32_t slot_byte(const ThreadTokens& tt, int i) {
   if (i == 0 || i == 5) return 4u;                  // the row's filter-type byte (Paeth)
@@ -133,9 +137,9 @@ __device__ __forceinline__ bool round_load(const Params& P, int y0, int npx, int
   const int q0 = base + 2 * t;
   tt.valid = 0;
   tt.f0 = tt.f1 = 0;
-  tt.off = 4 * (min(q0, q_end) - base) + multiples_before(min(q0, q_end), P.w) - mb_base;
+  tt.off = 4 * (min(q0, q_end) - base) + multiples_before(P, min(q0, q_end)) - mb_base;
   if (q0 < q_end) {
-    const int r = q0 / P.w, j = q0 - r * P.w;
+    const int r = div_w(P, q0), j = q0 - r * P.w;
     tt.valid = j == 0 ? 0x1fu : 0x1eu;
     tt.f0 = filter_px(P, j, y0 + r);
     if (q0 + 1 < q_end) {
@@ -197,18 +201,23 @@ __device__ __forceinline__ void round_finish(ThreadTokens& tt, const RoundSmem& 
   if (lane == 0) before = -1;
   if (lane == 31) after = 0x7fffffff;
   uint32_t sm = tt.startmask;
-#pragma unroll
-  for (int k = 0; k < PNG_THREADS / 32; ++k) {
+  {
+    // the other warps' partials: lane k (k < 8) looks at warp k, two warp reductions give every lane the last run
+    // start before its warp and the first one after it (every thread walking all 8 entries was 12 % of P1)
+    static_assert(PNG_THREADS / 32 <= 32, "one lane per warp of the CTA");
+    const int k = lane < PNG_THREADS / 32 ? lane : 0;
     const int g0 = rs.warp_g0[buf][k];
     // does warp k's first byte start a run?  (the round's first byte always does)
     const bool real = g0 >= 0 && (k == 0 || rs.warp_first[buf][k] != rs.warp_last[buf][k > 0 ? k - 1 : 0]);
     const int ak = max(rs.warp_a[buf][k], real ? g0 : -1);
     const int bk = real ? g0 : rs.warp_b[buf][k];
-    if (k < wp) before = max(before, ak);
-    if (k > wp) after = min(after, bk);
-    if (k == wp && real) {
+    const bool mine = lane < PNG_THREADS / 32;
+    before = max(before, __reduce_max_sync(0xffffffffu, (mine && k < wp) ? ak : -1));
+    after = min(after, __reduce_min_sync(0xffffffffu, (mine && k > wp) ? bk : 0x7fffffff));
+    const int real_wp = __shfl_sync(0xffffffffu, real ? 1 : 0, wp), g0_wp = __shfl_sync(0xffffffffu, g0, wp);
+    if (real_wp) {
       if (lane == 0) sm |= (valid & 1u) ? 1u : 2u;
-      else before = max(before, g0);
+      else before = max(before, g0_wp);
     }
   }
   after = min(after, n_round);
@@ -321,8 +330,8 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
   for (int base = 0, round = 0; base < npx; base += PNG_ROUND_PX, ++round) {
     ThreadTokens tt;
     const int q_end = min(base + PNG_ROUND_PX, npx);
-    const int mb_base = multiples_before(base, P.w);
-    const int n_round = 4 * (q_end - base) + multiples_before(q_end, P.w) - mb_base;
+    const int mb_base = multiples_before(P, base);
+    const int n_round = 4 * (q_end - base) + multiples_before(P, q_end) - mb_base;
     const bool plain = round_load(P, y0, npx, base, mb_base, tt);
     if (plain) round_starts<true>(tt, rs, round & 1);
     else round_starts<false>(tt, rs, round & 1);
@@ -452,20 +461,32 @@ __global__ void __launch_bounds__(PNG_THREADS) png_hist_kernel(const __grid_cons
 
 // ---- P2 ----
 // A thread's bits for one round: up to 10 literals of <= 15 bits (2 pixels, each possibly behind a filter byte;
-// a match token is <= 21 bits but covers >= 3 bytes) = 150 bits.
+// a match token is <= 21 bits but covers >= 3 bytes) = 150 bits = 5 words.  Codes are shifted into a 64-bit
+// register, LSB first as deflate packs them, and drained one word at a time into the thread's own column of a
+// shared-memory staging array (bank = lane, no conflicts; the first version selected one of five registers
+// with predicates on every put: half of the kernel's instructions).
 struct LocalBits {
-  uint32_t w[5];
-  int n;
+  unsigned long long acc;
+  int nb;          // bits waiting in acc (< 32 between puts)
+  int nw;          // words drained
+  int n;           // bits of the round so far
+  uint32_t* col;   // word k of this thread at col[k * PNG_THREADS]
 };
-__device__ __forceinline__ void lb_put(LocalBits& b, uint32_t v, int len) {
-  const int wi = b.n >> 5, bo = b.n & 31;
-  // static indexing only: select the word with predicates
-#pragma unroll
-  for (int k = 0; k < 5; ++k) {
-    if (k == wi) b.w[k] |= v << bo;
-    if (k == wi + 1 && bo + len > 32) b.w[k] |= v >> (32 - bo);
-  }
+__device__ __forceinline__ void lb_reset(LocalBits& b, uint32_t* col) {
+  b.acc = 0;
+  b.nb = b.nw = b.n = 0;
+  b.col = col;
+}
+__device__ __forceinline__ void lb_put(LocalBits& b, uint32_t v, int len) {   // len <= 32
+  b.acc |= (unsigned long long)v << b.nb;
+  b.nb += len;
   b.n += len;
+  if (b.nb >= 32) {
+    b.col[b.nw * PNG_THREADS] = (uint32_t)b.acc;
+    b.acc >>= 32;
+    b.nb -= 32;
+    ++b.nw;
+  }
 }
 
 #define PNG_WIN_WORDS 1280   // 256 threads x 150 bits = 1200 words + carry
@@ -475,9 +496,11 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
   __shared__ uint16_t s_code[PNG_NSYM + 7];
   __shared__ uint8_t s_len[PNG_NSYM + 7];
   __shared__ int warp_bits[PNG_THREADS / 32];
+  __shared__ uint32_t s_lb[5][PNG_THREADS];
   const int band = blockIdx.x, t = threadIdx.x, lane = t & 31, wp = t >> 5;
   const int y0 = band * PNG_BAND_ROWS, rows = min(PNG_BAND_ROWS, P.h - y0);
   const bool last = band == P.nb - 1;
+  uint32_t* const col = &s_lb[0][t];
   for (int i = t; i < PNG_NSYM; i += PNG_THREADS) {
     s_code[i] = P.codes[(int64_t)band * PNG_TAB_STRIDE + i];
     s_len[i] = P.lens[(int64_t)band * PNG_TAB_STRIDE + i];
@@ -491,7 +514,8 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
   int carry = 0;             // bits waiting at the start of the window
 
   // One round: every thread contributes `lb`; bits are placed in thread order after `carry`.
-  auto place = [&](const LocalBits lb) {   // by value: the bits stay in registers
+  auto place = [&](const LocalBits& lb) {
+    if (lb.nb > 0) lb.col[lb.nw * PNG_THREADS] = (uint32_t)lb.acc;   // the partial last word
     int x = lb.n;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -510,12 +534,10 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
     if (lb.n > 0) {
       const int wi = before >> 5, bo = before & 31;
       const int nw = (lb.n + 31) >> 5;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        if (k < nw) {
-          atomicOr(&win[wi + k], lb.w[k] << bo);
-          if (bo) atomicOr(&win[wi + k + 1], lb.w[k] >> (32 - bo));
-        }
+      for (int k = 0; k < nw; ++k) {
+        const uint32_t w = lb.col[k * PNG_THREADS];
+        atomicOr(&win[wi + k], w << bo);
+        if (bo) atomicOr(&win[wi + k + 1], w >> (32 - bo));
       }
     }
     __syncthreads();
@@ -537,9 +559,7 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
   // and the single distance code length (1 when the band has a match) as 4-bit codes ----
   {
     LocalBits lb;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) lb.w[k] = 0;
-    lb.n = 0;
+    lb_reset(lb, col);
     if (t == 0) {
       if (band == 0) { lb_put(lb, 0x78u, 8); lb_put(lb, 0x01u, 8); }
       lb_put(lb, last ? 1u : 0u, 1);
@@ -554,9 +574,7 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
     const int dist_len = P.nmatch[band] ? 1 : 0;
 #pragma unroll
     for (int part = 0; part < 2; ++part) {
-#pragma unroll
-      for (int k = 0; k < 5; ++k) lb.w[k] = 0;
-      lb.n = 0;
+      lb_reset(lb, col);
       const int i = part * PNG_THREADS + t;
       if (i <= PNG_NSYM) {
         const int s = i < PNG_NSYM ? s_len[i] : dist_len;
@@ -573,9 +591,7 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
     const uint32_t* fp = P.fpx + (int64_t)y0 * P.w + q0;
     const uint32_t f0 = q0 < npx ? fp[0] : 0u, f1 = q0 + 1 < npx ? fp[1] : 0u;
     LocalBits lb;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) lb.w[k] = 0;
-    lb.n = 0;
+    lb_reset(lb, col);
     int mi = 0;
 #pragma unroll
     for (int i = 0; i < 10; ++i) {
@@ -596,9 +612,7 @@ __global__ void __launch_bounds__(PNG_THREADS) png_encode_kernel(const __grid_co
   // ---- end of block; byte alignment: empty stored block, or (last band) zero padding + room for the Adler-32 ----
   {
     LocalBits lb;
-#pragma unroll
-    for (int k = 0; k < 5; ++k) lb.w[k] = 0;
-    lb.n = 0;
+    lb_reset(lb, col);
     if (t == 0) {
       lb_put(lb, s_code[256], s_len[256]);
       if (!last) lb_put(lb, 0u, 3);

@@ -429,6 +429,7 @@ struct PngExport {
     PP.cap = p_cap;
     PP.band_cap = band_cap;
     PP.w = cw; PP.h = ch; PP.nb = nb;
+    PP.w_magic = (cw >= 2 && cw <= 16384) ? (uint32_t)(((1ull << 32) + (uint64_t)cw - 1) / (uint64_t)cw) : 0u;
     PP.rgba = *d_rgba;
     PP.pitch = *d_rgba_pitch;
     return STITCH_OK;
