@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- output MP/s of the 9x12MP vertical stitch (BASELINE.json configs[1]) on N B200s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg2_yuv|cfg2_jpeg|cfg2_png|cfg2_android|cfg1|cfg3|cfg3_min]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload cfg2|cfg2_yuv|cfg2_jpeg|cfg2_png|cfg2_android|cfg5|cfg1|cfg3|cfg3_min]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One "step" = one stitch job (layout + fused resample/compose of all 9 images into the
@@ -45,6 +45,9 @@ WORKLOADS = {
                      "9x 4032x3024 RGBA vertical stitch, Android/other canvas clamp -> 606x4096 (6.65x downscale; SURVEY 8d)"),
     "cfg3_min": (MIXED, "horizontal", "min", "ios", "rgba",
                  "9 mixed-aspect images horizontal 'min' -> 7765x720 (all downscale; SURVEY 8d)"),
+    "cfg5": ([(4032, 3024)] * 9, "vertical", "min", "ios", "rgba",
+             "batch of 10k independent 9x 4032x3024 stitch jobs sharded over the ranks, 32 resident job slots per GPU "
+             "(BASELINE configs[4]; sustained load: see clocks)"),
     "cfg1": ([(1080, 1920)] * 2, "vertical", "min", "ios", "rgba",
              "2x 1080x1920 vertical stitch, 2.2x supersampled canvas 2376x8448 (BASELINE configs[0])"),
     "cfg3": (MIXED, "horizontal", "max", "ios", "rgba",
@@ -196,11 +199,12 @@ def cpu_reference_run(workload: str, steps: int, warmup: int, threads: int | Non
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--steps", type=int, default=None, help="default 300; cfg5: 10000 // ranks (the batch is sharded)")
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
-    ap.add_argument("--slots", type=int, default=3, help="distinct resident job slots rotated between steps")
+    ap.add_argument("--slots", type=int, default=None,
+                    help="distinct resident job slots rotated between steps (default 3; cfg5: 32 = 14 GB of bitmaps per GPU)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (min(steps, 10))")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -214,6 +218,11 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     dims, direction, mode, platform, output, desc = WORKLOADS[args.workload]
+    batch = args.workload == "cfg5"
+    if args.steps is None:
+        args.steps = (10000 + world - 1) // world if batch and args.impl == "ours" else (3 if args.impl == "reference" else 300)
+    if args.slots is None:
+        args.slots = 32 if batch else 3
     W = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
     if args.impl == "reference":
@@ -426,7 +435,7 @@ def main():
     peak, peak_src = _peaks()
     achieved = algo_bytes / (ms_per_step * 1e-3) / 1e9   # one compose launch per step
     line = {
-        "metric": "output MP/s, 9x12MP vertical stitch" if args.workload.startswith("cfg2") else "output MP/s",
+        "metric": "output MP/s, 9x12MP vertical stitch" if args.workload.startswith("cfg2") or args.workload == "cfg5" else "output MP/s",
         "value": value, "unit": "MP/s", "n_gpus": world, "steps": args.steps, "warmup": W,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8 in/out, f32 accumulate", "data": "synthetic",
@@ -449,7 +458,7 @@ def main():
     prof_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof_path):
         try:
-            line["roofline"]["traffic"] = json.load(open(prof_path)).get(args.workload)
+            line["roofline"]["traffic"] = json.load(open(prof_path)).get("cfg2" if args.workload == "cfg5" else args.workload)
         except Exception:
             pass
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
