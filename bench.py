@@ -205,7 +205,7 @@ def main():
     ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
     ap.add_argument("--slots", type=int, default=None,
                     help="distinct resident job slots rotated between steps (default 3; cfg5: 32 = 14 GB of bitmaps per GPU)")
-    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (min(steps, 10))")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (min(steps, 40))")
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-numa", action="store_true", help="do not bind the rank to the GPU's NUMA node")
@@ -361,7 +361,7 @@ def main():
     ms_per_step = elapsed_ms / args.steps
 
     # ---- end-to-end through the C ABI with pinned host buffers ----
-    e2e_steps = args.e2e_steps or max(3, min(args.steps, 12))
+    e2e_steps = args.e2e_steps or max(3, min(args.steps, 40))   # long enough to amortise the last job's drain (1.7 ms)
     host_imgs, host_keep = [], []
     for i, (w, h) in enumerate(dims):
         p = C.c_void_p()

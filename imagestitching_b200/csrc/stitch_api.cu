@@ -600,8 +600,12 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       const int64_t dpitch = ((int64_t)im.bmp_width * 4 + 15) & ~15LL;
       st = ensure_stage(ctx, ln, i, (size_t)(dpitch * im.bmp_height));
       if (st != STITCH_OK) return st;
-      CUDA_TRY(ctx, cudaMemcpy2DAsync(ln.in_stage[i], dpitch, im.data, pitch, (size_t)im.bmp_width * 4, im.bmp_height,
-                                      cudaMemcpyHostToDevice, ln.stream));
+      if (pitch == dpitch && dpitch == (int64_t)im.bmp_width * 4)   // rows already contiguous: one linear DMA
+        CUDA_TRY(ctx, cudaMemcpyAsync(ln.in_stage[i], im.data, (size_t)(dpitch * im.bmp_height), cudaMemcpyHostToDevice,
+                                      ln.stream));
+      else
+        CUDA_TRY(ctx, cudaMemcpy2DAsync(ln.in_stage[i], dpitch, im.data, pitch, (size_t)im.bmp_width * 4, im.bmp_height,
+                                        cudaMemcpyHostToDevice, ln.stream));
       dptr = (const uint8_t*)ln.in_stage[i];
       pitch = dpitch;
     }
@@ -672,9 +676,13 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
 
   // [5] export (U:205-242): the canvas is copied out whole, unscaled (P:1577-1579)
   if (out_host) {
-    if (want_rgba)
-      CUDA_TRY(ctx, cudaMemcpy2DAsync(job->out_rgba, rgba_pitch, d_rgba, d_rgba_pitch, (size_t)cw * 4, ch,
-                                      cudaMemcpyDeviceToHost, ln.stream));
+    if (want_rgba) {
+      if ((int64_t)rgba_pitch == (int64_t)d_rgba_pitch && (int64_t)rgba_pitch == (int64_t)cw * 4)
+        CUDA_TRY(ctx, cudaMemcpyAsync(job->out_rgba, d_rgba, (size_t)cw * 4 * (size_t)ch, cudaMemcpyDeviceToHost, ln.stream));
+      else
+        CUDA_TRY(ctx, cudaMemcpy2DAsync(job->out_rgba, rgba_pitch, d_rgba, d_rgba_pitch, (size_t)cw * 4, ch,
+                                        cudaMemcpyDeviceToHost, ln.stream));
+    }
     if (want_yuv)
       CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ln.stream));
   }
