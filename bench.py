@@ -54,6 +54,7 @@ WORKLOADS = {
              "9 mixed-aspect images horizontal 'max' -> 12288x1139 (BASELINE configs[2])"),
 }
 SEED = 0x5717C4
+PREWARM_JOBS = 100   # untimed jobs in front of the warm-up steps (about 10 ms of GPU work)
 
 
 def _peaks():
@@ -330,6 +331,10 @@ def main():
     # that stream wait for the other lanes before ev1 is recorded.
     ctx.set_lanes(max(1, args.lanes))
     last = 0
+    # settle clocks / power state and every lane's lazily created buffers before the W warm-up steps: on a box that
+    # has just come up the first milliseconds of GPU work run slower (one N = 2 run measured 120 us/job over 50 steps)
+    for i in range(PREWARM_JOBS):
+        last = step(i)
     for i in range(W):
         last = step(i)
     lib.stitch_wait(ctx.handle, last)
@@ -444,7 +449,7 @@ def main():
                    "l2": f"{len(jobs)} job slots rotated; each job reads {src_bytes/1e6:.0f} MB (> 126 MB L2)",
                    "parallelism": f"{world} rank(s), jobs sharded, no collective",
                    "lanes": f"{max(1, args.lanes)} job lane(s) per ctx for the device-resident steps, {e2e_lanes} for e2e",
-                   "host_placement": placement},
+                   "host_placement": placement, "prewarm_jobs": PREWARM_JOBS},
         "gpu_launches": int(launches),
         "host_us_per_submit": round(host_s[0] / max(1, args.steps) * 1e6, 2),   # layout + plan + launch inside stitch_submit
         "clocks": sampler.summary(),
