@@ -5,6 +5,8 @@ Bar (BASELINE.json north_star): canvas size and rects bit-exact; pixels within
 """
 import itertools
 
+import os
+
 import numpy as np
 import pytest
 
@@ -224,7 +226,11 @@ def test_device_buffers_and_async(ctx):
         lib.stitch_device_free(ctx.handle, p)
 
 
-@pytest.mark.parametrize("seed", range(8))
+# STITCH_FUZZ_SEEDS / STITCH_FUZZ_BASE widen the sweep for a one-off fuzz run (e.g. 64 seeds from 100)
+_FUZZ_BASE = int(os.environ.get("STITCH_FUZZ_BASE", "0"))
+
+
+@pytest.mark.parametrize("seed", range(_FUZZ_BASE, _FUZZ_BASE + int(os.environ.get("STITCH_FUZZ_SEEDS", "8"))))
 def test_randomized_jobs(ctx, seed):
     """Random jobs (sizes, modes, gaps, clamps, EXIF, alpha, output formats): whatever mixture of stream / upscale /
     gather / fill units the plan chooses, layout is bit-exact and every plane is within the parity bar."""
