@@ -207,7 +207,7 @@ def main():
     ap.add_argument("--slots", type=int, default=None,
                     help="distinct resident job slots rotated between steps (default 3; cfg5: 32 = 14 GB of bitmaps per GPU)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 = auto (min(steps, 40))")
-    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--cpu-steps", type=int, default=10, help="jobs the CPU port is timed on (cpu_baseline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-numa", action="store_true", help="do not bind the rank to the GPU's NUMA node")
     ap.add_argument("--lanes", type=int, default=2,
