@@ -111,6 +111,11 @@ __device__ __forceinline__ uint32_t pack_rgb(uint32_t r, uint32_t g, uint32_t bn
 
 __device__ __forceinline__ uint32_t udiv_ceil(uint32_t n, uint32_t d) { return (n + d - 1) / d; }
 
+// byte store under a predicate: keeps the value's arithmetic outside of any branch
+__device__ __forceinline__ void st_u8_if(uint8_t* p, uint32_t v, bool ok) {
+  asm volatile("{.reg .pred q;\n setp.ne.u32 q, %2, 0;\n @q st.global.u8 [%0], %1;}" ::"l"(p), "r"(v), "r"((uint32_t)ok) : "memory");
+}
+
 // Builds the warp's row table for source rows [rs, rs + nrows): entry = (weight into the current
 // output row, weight into the next one or -1 when the row does not complete an output row).
 // Each lane fills a contiguous chunk, so it needs one division and then steps incrementally.
@@ -261,6 +266,18 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
       ccb[o] = ccr[o] = 0.f;
     }
   }
+  // MAXO == 2: two adjacent outputs have different parity, so a lane owns at most ONE chroma sample per block row.
+  // Which one, and where its horizontal partner lives, is fixed for the unit: the second-row step selects instead
+  // of branching per output (the per-output form cost two divergent regions per chroma row).
+  bool own1 = false, own_any = false, part_local = false;
+  uint8_t *cb_own = nullptr, *cr_own = nullptr;
+  if (YUV && MAXO == 2) {
+    own1 = c_own[MAXO - 1];
+    own_any = c_own[0] || c_own[MAXO - 1];
+    part_local = !own1 && pair_local[0];
+    cb_own = cbptr + (own1 ? c_off[MAXO - 1] : c_off[0]);
+    cr_own = crptr + (own1 ? c_off[MAXO - 1] : c_off[0]);
+  }
 
   // ---- ring prologue: each lane stages its own 16 B per row; rows travel in pairs (one commit group
   // per pair, STREAM_NST rows deep).  Rows are addressed by a 32-bit offset clamped to the unit's last
@@ -378,8 +395,16 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
           const float nb_cb = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccb[0], 1) : __shfl_sync(0xffffffffu, ccb[0], lane + nxt);
           const float nb_cr = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccr[0], 1) : __shfl_sync(0xffffffffu, ccr[0], lane + nxt);
           const float bias = 1.f + 128.f / 32768.f;
+          if (MAXO == 2) {
+            const float mcb = own1 ? ccb[MAXO - 1] : ccb[0], mcr = own1 ? ccr[MAXO - 1] : ccr[0];
+            const float qcb = part_local ? ccb[MAXO - 1] : nb_cb, qcr = part_local ? ccr[MAXO - 1] : nb_cr;
+            st_u8_if(cb_own, quant_bits(fmaf(0.25f, mcb + qcb, bias)), own_any);
+            st_u8_if(cr_own, quant_bits(fmaf(0.25f, mcr + qcr, bias)), own_any);
+            cb_own += cstep;
+            cr_own += cstep;
+          }
 #pragma unroll
-          for (int o = 0; o < MAXO; ++o) {
+          for (int o = 0; o < (MAXO == 2 ? 0 : MAXO); ++o) {
             float pcb = nb_cb, pcr = nb_cr;  // partner = output o+1
             if (o + 1 < MAXO) {
               pcb = pair_local[o] ? ccb[o + 1] : nb_cb;
@@ -394,8 +419,10 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
           }
 #pragma unroll
           for (int o = 0; o < MAXO; ++o) ccb[o] = ccr[o] = 0.f;
-          cbptr += cstep;
-          crptr += cstep;
+          if (MAXO != 2) {
+            cbptr += cstep;
+            crptr += cstep;
+          }
         }
         second = !second;
       }
