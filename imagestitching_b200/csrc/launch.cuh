@@ -351,10 +351,10 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
     maxo = std::max(maxo, (int)std::min<int64_t>(4, (4 * dw + im.sx_len - 1) / im.sx_len));
     hops = std::max(hops, (int)((im.sx_len + 4 * dw - 1) / (4 * dw)));
   }
-  // instantiated (MAXO, HOPS) shapes: (2|3|4, 1) for ratios <= 4, (2, 2) for 2 < ratio <= 8, (3, 2) for jobs that mix
-  // ratios from 4/3 up to 8 (mixed-aspect stitches to a common height: BASELINE configs[2] in 'min' mode), (4, 4) for the rest
+  // instantiated (MAXO, HOPS) shapes: (2|3|4, 1) for ratios <= 4, (2, 2) for 2 < ratio <= 8, (3, 2) / (4, 2) for jobs that mix
+  // ratios from 4/3 (or 1) up to 8 (mixed-aspect stitches to a common height: BASELINE configs[2] in 'min' mode), (4, 4) for the rest
   if (hops > 1) {
-    if (hops == 2 && maxo <= 3) { /* (2, 2) or (3, 2) */ }
+    if (hops == 2) { /* (2, 2), (3, 2) or (4, 2) */ }
     else { maxo = 4; hops = 4; }
   }
   cudaError_t err = cudaSuccess;
@@ -363,7 +363,8 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
   if (maxo == M && hops == H && mode == Md) { using K = ComposeLaunch<M, H, Md>; expr; }
 #define STITCH_SHAPES(Md, expr)                                                               \
   STITCH_DISPATCH(2, 1, Md, expr) STITCH_DISPATCH(3, 1, Md, expr) STITCH_DISPATCH(4, 1, Md, expr) \
-  STITCH_DISPATCH(2, 2, Md, expr) STITCH_DISPATCH(3, 2, Md, expr) STITCH_DISPATCH(4, 4, Md, expr)
+  STITCH_DISPATCH(2, 2, Md, expr) STITCH_DISPATCH(3, 2, Md, expr) STITCH_DISPATCH(4, 2, Md, expr) \
+  STITCH_DISPATCH(4, 4, Md, expr)
 #define STITCH_ALL(expr) STITCH_SHAPES(0, expr) STITCH_SHAPES(1, expr) STITCH_SHAPES(2, expr)
 #define STITCH_LIGHT(expr)                                   \
   if (mode == 0) { using K = LightLaunch<0>; expr; }          \

@@ -86,13 +86,24 @@ def test_ratio_above_16_uses_gather(ctx):
 
 def test_mixed_ratios_one_launch(ctx):
     """Ratios from 1.5 to 5.6 and an identity copy in one job (BASELINE configs[2] in 'min' mode, quartered):
-    the launch takes the most general kernel shape (MAXO 4, HOPS 4) for all streamed images."""
+    one launch, kernel shape (MAXO 3, HOPS 2) for all streamed images; (4, 4) under the Android-like clamp."""
     dims = [(w // 4, h // 4) for (w, h) in U.MIXED]
     got, lay = _go(ctx, dims, "horizontal", "min", 0)
     assert _n_stream(got) == 8 and _n_up(got) == 1
     _go_yuv(ctx, dims, "horizontal", "min", 0, min_stream=8)
     got, lay = _go(ctx, dims, "horizontal", "min", 1024)          # Android-like clamp: ratios 2.8 .. 10.5
     assert _n_stream(got) == 9
+
+
+def test_mixed_ratio_kernel_shapes(ctx):
+    """Jobs whose smallest / largest ratio pick the (MAXO, HOPS) shapes (3, 2) and (4, 2) (launch.cuh), RGBA and I420."""
+    for dims in ([(300, 108), (500, 432), (200, 72)],      # ratios 1.5, 6.0, identity    -> (3, 2)
+                 [(100, 86), (500, 432), (310, 144), (60, 72)],    # ratios 1.19, 6.0, 2.0, identity -> (4, 2)
+                 [(200, 151), (1000, 575), (90, 72)]):    # ratios 2.1, 7.99, identity   -> (2, 2)
+        for orient in (None, [2, 1, 4, 3][: len(dims)]):
+            got, lay = _go(ctx, dims, "horizontal", "min", 0, orientations=orient)
+            assert _n_stream(got) >= 2 and _n_up(got) == 1
+        _go_yuv(ctx, dims, "horizontal", "min", 0, min_stream=2)
 
 
 @pytest.mark.parametrize("orientation", [2, 3, 4])
