@@ -45,6 +45,29 @@ __global__ void k(float* out, const uint32_t* in, long long* cyc) {
       }
       p[4] &= p[0] & p[1]; p[4] &= p[2] & p[3];
       p[0] += 0x01010101u; p[1] ^= p[4]; p[2] += p[1]; p[3] ^= p[0];
+    } else if (MODE == 7) {  // 16 IDP2A (dp2a.lo / dp2a.hi alternating)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { p[i] = __dp2a_lo(p[(i + 1) & 7], p[(i + 2) & 7], p[i]); p[i] = __dp2a_hi(p[(i + 3) & 7], p[(i + 2) & 7], p[i]); }
+    } else if (MODE == 8) {  // 16 IDP4A
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { p[i] = __dp4a(p[(i + 1) & 7], p[(i + 2) & 7], p[i]); p[i] = __dp4a(p[(i + 3) & 7], p[(i + 2) & 7], p[i]); }
+    } else if (MODE == 9) {  // row-PAIR mix of the integer vertical pass for 4 pixels: 8 PRMT + 12 IDP2A + 4 LOP3
+      uint32_t acc[12];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) acc[i] = __float_as_uint(a[i]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t rg = __byte_perm(p[i], p[i + 4], 0x5140), ba = __byte_perm(p[i], p[i + 4], 0x7362);
+        acc[3 * i] = __dp2a_lo(p[(i + 1) & 3] | 0x10001u, rg, acc[3 * i]);
+        acc[3 * i + 1] = __dp2a_hi(p[(i + 1) & 3] | 0x10001u, rg, acc[3 * i + 1]);
+        acc[3 * i + 2] = __dp2a_lo(p[(i + 1) & 3] | 0x10001u, ba, acc[3 * i + 2]);
+      }
+      p[4] &= p[0] & p[1]; p[5] &= p[2] & p[3]; p[6] ^= p[4]; p[7] ^= p[5];
+#pragma unroll
+      for (int i = 0; i < 12; ++i) a[i] = __uint_as_float(acc[i]);
+    } else if (MODE == 10) {  // 8 IMAD (32-bit) for reference
+#pragma unroll
+      for (int i = 0; i < 8; ++i) { p[i] = p[(i + 1) & 7] * p[(i + 2) & 7] + p[i]; }
     }
   }
   long long t1 = clock64();
@@ -71,5 +94,6 @@ template <int MODE> void run(const char* name, int ninstr) {
 int main() {
   run<0>("16 FFMA", 16); run<1>("8 FFMA2", 8); run<5>("8 FFMA2 bcast", 8); run<2>("16 PRMT", 16);
   run<3>("8 PRMT + 8 FFMA", 16); run<4>("8 PRMT + 4 FFMA2", 12); run<6>("rowstep mix (12P+6F2+~8alu)", 26);
+  run<7>("16 IDP2A", 16); run<8>("16 IDP4A", 16); run<9>("int row-PAIR mix (8P+12IDP2A+4L)", 24); run<10>("8 IMAD", 8);
   printf("%s\n", cudaGetErrorString(cudaGetLastError()));
 }
