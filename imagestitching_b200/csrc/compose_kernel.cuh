@@ -167,8 +167,10 @@ __device__ __forceinline__ void gather_unit(const JobParam& P, const Region& R, 
 // (1, 2 or 4); MODE = STREAM_MODE_* (RGBA canvas, I420 planes, or both).
 // The persistent unit loop shared by both kernels.  STREAM = false compiles the streaming unit out.
 template <int MAXO, int HOPS, int MODE, bool STREAM>
-__device__ __forceinline__ void compose_loop(const JobParam& P, const Plan& plan, unsigned int* __restrict__ sched, WarpSmem* ws) {
+__device__ __forceinline__ void compose_loop(const JobParam& P, const Plan& plan, const TmaMaps* maps, unsigned int* __restrict__ sched,
+                                             WarpSmem* ws) {
   const int lane = threadIdx.x & 31;
+  WarpState wst;
   // One ticket per unit, drawn when the previous unit is done.  (Drawing the next ticket ahead of a short
   // unit to hide the atomic's round trip was measured slower on every workload: a claimed unit waits.)
   for (;;) {
@@ -182,7 +184,7 @@ __device__ __forceinline__ void compose_loop(const JobParam& P, const Plan& plan
     const int local = (int)unit - R.first_unit;
     const int ty = local / R.tiles_x, tx = local - ty * R.tiles_x;
     if (STREAM && R.kind == REGION_STREAM) {
-      stream_unit<MAXO, HOPS, MODE>(P, R, tx, ty, *ws, lane);
+      stream_unit<MAXO, HOPS, MODE>(P, *maps, R, tx, ty, *ws, wst, lane);
     } else if (R.kind == REGION_UPSCALE) {
       // window of source pixels per lane and row (upscale_unit.cuh): launch.cuh picks 4 for scales >= 1.5; the
       // kernel with streaming units compiles the general width only
@@ -207,17 +209,25 @@ __device__ __forceinline__ void compose_loop(const JobParam& P, const Plan& plan
 
 template <int MAXO, int HOPS, int MODE>
 __global__ void __launch_bounds__(STREAM_WARPS * 32, STREAM_MINB)
-compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
+compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, const __grid_constant__ TmaMaps maps,
+               unsigned int* __restrict__ sched) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   WarpSmem& ws = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
+#if STITCH_STREAM_TMA
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < STREAM_TMA_STAGES; ++s) mbar_init(smem_u32(&ws.full[s]), 1);
+    fence_proxy_async();   // the barriers are visible to the TMA unit before the first box is issued
+  }
+#endif
   // Lanes that never copy (past the band) and padded rows read the ring as it is: give it defined,
   // opaque contents once so the alpha check cannot trip on uninitialised shared memory.
 #pragma unroll
   for (int s = 0; s < STREAM_NST; ++s)
     *reinterpret_cast<uint4*>(&ws.ring[s][lane * 16]) = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
   __syncwarp();
-  compose_loop<MAXO, HOPS, MODE, true>(P, plan, sched, &ws);
+  compose_loop<MAXO, HOPS, MODE, true>(P, plan, &maps, sched, &ws);
 }
 
 // Jobs without a streaming region (every image enlarged, transposed or unaligned: BASELINE configs[0], previews):
@@ -228,7 +238,7 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
 template <int MODE>
 __global__ void __launch_bounds__(STREAM_WARPS * 32, LIGHT_MINB)
 compose_light_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan plan, unsigned int* __restrict__ sched) {
-  compose_loop<2, 1, MODE, false>(P, plan, sched, nullptr);
+  compose_loop<2, 1, MODE, false>(P, plan, nullptr, sched, nullptr);
 }
 
 }  // namespace stitch

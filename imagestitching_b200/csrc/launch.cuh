@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
@@ -11,12 +12,14 @@
 #include "compose_kernel.cuh"
 #include "gather_kernel.cuh"
 #include "stitch_plan.h"
+#include "tma_maps.h"
 
 namespace stitch {
 
 struct StreamScratch {
   void* p = nullptr;
   size_t cap = 0;
+  TmaCache tma;   // tensor maps of the bitmaps this lane has streamed
 };
 inline void free_scratch(StreamScratch& s) {
   if (s.p) cudaFree(s.p);
@@ -194,9 +197,10 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
   // most rows) followed by a TAIL of small units that even out the different speeds of the SMs
   // (near / far L2 and HBM); all tails are queued after all bodies.  With equal-sized units only,
   // ncu showed the SMs 14 % idle on average while the slowest ones finished.
-  static const double body_frac = [] { const char* e = std::getenv("STITCH_BODY_FRAC"); return e ? atof(e) : 0.75; }();
-  static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? atoi(e) : 32; }();
-  static const double up_body_frac = [] { const char* e = std::getenv("STITCH_UP_BODY_FRAC"); return e ? atof(e) : 0.8; }();
+  // tuning knobs (profiles/microbench sweeps); clamped so that no value can push a unit outside its region
+  static const double body_frac = [] { const char* e = std::getenv("STITCH_BODY_FRAC"); return e ? std::min(1.0, std::max(0.0, atof(e))) : 0.75; }();
+  static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? std::max(1, atoi(e)) : 32; }();
+  static const double up_body_frac = [] { const char* e = std::getenv("STITCH_UP_BODY_FRAC"); return e ? std::min(1.0, std::max(0.0, atof(e))) : 0.8; }();
   static const int up_tail_h = [] { const char* e = std::getenv("STITCH_UP_TAIL_H"); return e ? std::min(32, std::max(2, atoi(e) & ~1)) : UPSCALE_TAIL_H; }();
   const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_UNR;
   auto tile_h_for = [&](const Region& r, int src_rows) {
@@ -238,7 +242,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
       if (r0.kind != REGION_STREAM) { others.push_back(r0); continue; }
       const int th_b = tile_h_for(r0, body_src_rows);
       const int th_t = tile_h_for(r0, std::min(tail_rows, body_src_rows));
-      const int hb = (th_b > th_t) ? body_rows_of(r0, th_b) : 0;   // no point in a body of tail-sized units
+      const int hb = (th_b > th_t) ? std::min(body_rows_of(r0, th_b), r0.y1 - r0.y0) : 0;   // no point in a body of tail-sized units
       if (hb > 0) {
         Region b = r0;
         b.y1 = r0.y0 + hb;
@@ -259,7 +263,7 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
     // units over the rest, so the last round of units is short (configs[0]: 2.1 full units per warp)
     for (const Region& r : others) {
       if (r.kind != REGION_UPSCALE) continue;
-      const int hb = (int)((int64_t)(up_body_frac * (double)(r.y1 - r.y0)) / UPSCALE_TILE_H * UPSCALE_TILE_H);
+      const int hb = std::min(r.y1 - r.y0, (int)((int64_t)(up_body_frac * (double)(r.y1 - r.y0)) / UPSCALE_TILE_H * UPSCALE_TILE_H));
       if (hb > 0) {
         Region b = r;
         b.y1 = r.y0 + hb;
@@ -291,25 +295,33 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
   return unit > 0;
 }
 
+static constexpr int kMaxDevices = 64;
+
 template <int MAXO, int HOPS, int MODE>
 struct ComposeLaunch {
-  // resident CTAs per SM of this instantiation (queried once), 0 on error
+  // resident CTAs per SM of this instantiation, 0 on error.  Queried once PER DEVICE: the opt-in to more than 48 KB
+  // of dynamic shared memory is a per-device function attribute, and one process may hold contexts on several GPUs.
   static int ctas_per_sm(cudaError_t* err) {
-    static int value = -1;
-    if (value < 0) {
-      cudaError_t e = cudaFuncSetAttribute(compose_kernel<MAXO, HOPS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           kComposeSmemBytes);
+    static std::atomic<int> value[kMaxDevices];   // 0 = not queried yet
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) { *err = e != cudaSuccess ? e : cudaErrorInvalidDevice; return 0; }
+    int v = value[dev].load(std::memory_order_acquire);
+    if (v == 0) {
+      e = cudaFuncSetAttribute(compose_kernel<MAXO, HOPS, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kComposeSmemBytes);
       int n = 0;
       if (e == cudaSuccess)
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_kernel<MAXO, HOPS, MODE>, STREAM_WARPS * 32,
                                                           kComposeSmemBytes);
       if (e != cudaSuccess) { *err = e; return 0; }
-      value = n < 1 ? 1 : n;
+      v = n < 1 ? 1 : n;
+      value[dev].store(v, std::memory_order_release);
     }
-    return value;
+    return v;
   }
-  static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
-    compose_kernel<MAXO, HOPS, MODE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, sched);
+  static cudaError_t launch(const JobParam& P, const Plan& plan, const TmaMaps& maps, int grid, unsigned int* sched,
+                            cudaStream_t stream) {
+    compose_kernel<MAXO, HOPS, MODE><<<grid, STREAM_WARPS * 32, kComposeSmemBytes, stream>>>(P, plan, maps, sched);
     return cudaGetLastError();
   }
 };
@@ -317,16 +329,18 @@ struct ComposeLaunch {
 template <int MODE>
 struct LightLaunch {
   static int ctas_per_sm(cudaError_t* err) {
-    static int value = -1;
-    if (value < 0) {
+    static std::atomic<int> value{0};   // no per-device attribute involved: the occupancy is a property of the cubin
+    int v = value.load(std::memory_order_acquire);
+    if (v == 0) {
       int n = 0;
       const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, compose_light_kernel<MODE>, STREAM_WARPS * 32, 0);
       if (e != cudaSuccess) { *err = e; return 0; }
-      value = n < 1 ? 1 : n;
+      v = n < 1 ? 1 : n;
+      value.store(v, std::memory_order_release);
     }
-    return value;
+    return v;
   }
-  static cudaError_t launch(const JobParam& P, const Plan& plan, int grid, unsigned int* sched, cudaStream_t stream) {
+  static cudaError_t launch(const JobParam& P, const Plan& plan, const TmaMaps&, int grid, unsigned int* sched, cudaStream_t stream) {
     compose_light_kernel<MODE><<<grid, STREAM_WARPS * 32, 0, stream>>>(P, plan, sched);
     return cudaGetLastError();
   }
@@ -401,8 +415,21 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
     const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
     if (grid > need) grid = need;
     unsigned int* sched = (unsigned int*)scratch.p;
-    if (any_stream) { STITCH_ALL(err = K::launch(P, plan, grid, sched, stream)) }
-    else { STITCH_LIGHT(err = K::launch(P, plan, grid, sched, stream)) }
+    TmaMaps maps;
+#if STITCH_STREAM_TMA
+    // tensor maps of the bitmaps that have a streaming region (the other slots are never dereferenced)
+    uint32_t mapped = 0;
+    for (int i = 0; i < plan.n_regions; ++i) {
+      const Region& r = plan.r[i];
+      if (r.kind != REGION_STREAM || (mapped >> r.img & 1u)) continue;
+      mapped |= 1u << r.img;
+      const ImgParam& im = P.img[r.img];
+      const cudaError_t e = scratch.tma.get(im.data, im.pitch, im.bw, im.bh, &maps.box[r.img], &maps.row[r.img]);
+      if (e != cudaSuccess) return (int)e;
+    }
+#endif
+    if (any_stream) { STITCH_ALL(err = K::launch(P, plan, maps, grid, sched, stream)) }
+    else { STITCH_LIGHT(err = K::launch(P, plan, maps, grid, sched, stream)) }
     *launches = 1;
     return (int)err;
   }

@@ -13,11 +13,19 @@
 #include <cstdint>
 
 #include "stitch_plan.h"
+#include "tma_maps.h"
 
 namespace stitch {
 
+#if STITCH_STREAM_TMA
+// Staging by TMA: the warp's ring holds STREAM_TMA_STAGES stages of STREAM_TMA_ROWS source rows (512 B each); a stage is
+// filled by ONE cp.async.bulk.tensor.2d box (UTMALDG) that lane 0 issues when the warp has finished reading the
+// stage's previous contents, and completes on the stage's mbarrier (expect-tx bytes).
+#define STREAM_NST (STREAM_TMA_ROWS * STREAM_TMA_STAGES)
+#else
 #ifndef STREAM_NST
 #define STREAM_NST 8  // ring depth: source rows in flight per lane (power of two, multiple of STREAM_UNR)
+#endif
 #endif
 #define STREAM_UNR 4  // rows per iteration of the unrolled row loop
 #define STREAM_STAGE_BYTES 512
@@ -30,11 +38,23 @@ namespace stitch {
 // when chroma is produced, so that the chroma partner of the last stored output is complete too.
 #define STREAM_STRIDE_OF(MODE, HOPS) ((MODE) == STREAM_MODE_RGBA ? 32 - (HOPS) : 32 - 2 * (HOPS))
 
+#if STITCH_STREAM_TMA
+static_assert(STREAM_TMA_ROWS % STREAM_UNR == 0 && 32 % STREAM_TMA_ROWS == 0 && STREAM_UNR % 2 == 0, "ring layout");
+#else
 static_assert(STREAM_NST % STREAM_UNR == 0 && (STREAM_NST & (STREAM_NST - 1)) == 0 && STREAM_UNR % 2 == 0, "ring layout");
+#endif
 
 struct WarpSmem {
   alignas(128) uint8_t ring[STREAM_NST][STREAM_STAGE_BYTES];
   alignas(16) float2 tab[STREAM_TAB_MAX];
+#if STITCH_STREAM_TMA
+  alignas(8) uint64_t full[STREAM_TMA_STAGES];   // one mbarrier per stage: completes when the stage's bytes have landed
+#endif
+};
+// what a warp carries from unit to unit
+struct WarpState {
+  uint32_t slot = 0;     // ring slot the next stage goes to (slots are used round-robin across units)
+  uint32_t parity = 0;   // parity of that slot's next mbarrier completion: flips when the slot index wraps
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -61,6 +81,33 @@ __device__ __forceinline__ float4 lds128f(uint32_t addr) {
   asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
   return r;
 }
+
+#if STITCH_STREAM_TMA
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// Waits until the phase `parity` of the barrier has completed.  Every lane probes (try_wait suspends the thread for a
+// bounded time when the phase is still open) and the loop exits on a VOTE, so the exit is warp-uniform by construction:
+// with a per-lane exit branch the compiler has to assume the warp may have diverged and wraps every shuffle / vote of
+// the row loop in divergence checks (BSSY / BRA.DIV: +4 instructions per source row, measured).
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  } while (!__all_sync(0xffffffffu, ok != 0u));
+}
+// generic-proxy writes to shared memory (the ring scrub) ordered before later async-proxy (TMA) writes
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// One box of the tensor `map` at pixel column x, row y -> shared memory at dst; completes on `bar`.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int x, int y, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
+}
+#endif
 
 // ---- packed fp32x2 arithmetic (FFMA2 / FMUL2: two lanes of fp32 per issue slot) ----
 // (dx, dy) += (ax, ay) * s
@@ -165,7 +212,8 @@ __device__ __forceinline__ void build_row_table(float2* tab, int lane, uint32_t 
 // makes tile_h even, so every 2x2 chroma block lies inside one unit (launch.cuh).
 // All geometry is unsigned 32-bit; launch.cuh only admits images whose scaled coordinates fit.
 template <int MAXO, int HOPS, int MODE>
-__device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, int tx, int ty, WarpSmem& ws, int lane) {
+__device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& maps, const Region& R, int tx, int ty, WarpSmem& ws,
+                                            WarpState& wst, int lane) {
   const ImgParam& im = P.img[R.img];
   const uint32_t sw = (uint32_t)im.sx_len, sh = (uint32_t)im.sy_len;
   const uint32_t dw = (uint32_t)im.W, dh = (uint32_t)im.H;
@@ -178,11 +226,48 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   const uint32_t re = min(sh, udiv_ceil(oy1 * sh, dh));
   const int nrows = (int)(re - rs);
   const int nrows_pad = (nrows + STREAM_UNR - 1) / STREAM_UNR * STREAM_UNR;
-  __syncwarp();  // every lane is done reading the previous unit's table
+  constexpr int STRIDE = STREAM_STRIDE_OF(MODE, HOPS);
+  __syncwarp();  // every lane is done reading the previous unit's table and ring
+#if STITCH_STREAM_TMA
+  // ---- ring prologue, first thing in the unit: the first stages are in flight while the row table and the lane
+  // weights are set up.  A stage = ROWS source rows x the band's 128 pixels.  The ring slots are used round-robin
+  // across units (wst.slot), so the parity of a slot's mbarrier is one bit that flips when the slot index wraps.
+  // A full stage is ONE box; the last, partial stage of a unit is fetched row by row, so nothing is read beyond
+  // row re.  y_next / rows_left (the next stage to request) are kept by every lane so that the test stays uniform. ----
+  constexpr int ROWS = STREAM_TMA_ROWS, STAGES = STREAM_TMA_STAGES;
+  constexpr uint32_t SLOT_BYTES = ROWS * STREAM_STAGE_BYTES;
+  const int box_x = 4 * (R.g_base + tx * STRIDE);
+  const uint32_t ring_s = smem_u32(&ws.ring[0][0]), full_s = smem_u32(&ws.full[0]);
+  const CUtensorMap* const map_box = &maps.box[R.img];
+  int y_next = (int)rs, rows_left = nrows;
+  auto issue = [&](uint32_t slot_) {   // lane 0 only: request rows [y_next, y_next + min(ROWS, rows_left)) into slot_
+    const uint32_t bar = full_s + 8u * slot_, dst = ring_s + slot_ * SLOT_BYTES;
+    if (rows_left >= ROWS) {
+      mbar_expect_tx(bar, SLOT_BYTES);
+      tma_load_2d(dst, map_box, box_x, y_next, bar);
+    } else {
+      mbar_expect_tx(bar, (uint32_t)rows_left * STREAM_STAGE_BYTES);
+      const CUtensorMap* const map_row = map_box + STITCH_MAX_IMAGES;   // TmaMaps::row[img]
+#pragma unroll 1
+      for (int j = 0; j < rows_left; ++j) tma_load_2d(dst + j * STREAM_STAGE_BYTES, map_row, box_x, y_next + j, bar);
+    }
+  };
+  {
+    uint32_t ps = wst.slot;
+#pragma unroll
+    for (int s0 = 0; s0 < STAGES; ++s0) {
+      if (rows_left > 0) {
+        if (lane == 0) issue(ps);
+        y_next += ROWS;
+        rows_left -= ROWS;
+        ps = (ps + 1 == STAGES) ? 0u : ps + 1;
+      }
+    }
+  }
+#endif
   build_row_table(ws.tab, lane, rs, nrows, nrows_pad, sh, dh, oy0, inv_sh);
 
   // ---- horizontal: this lane's 4-pixel source group and the outputs that start in it ----
-  constexpr int STRIDE = STREAM_STRIDE_OF(MODE, HOPS);
   constexpr bool RGBA = MODE != STREAM_MODE_YUV, YUV = MODE != STREAM_MODE_RGBA;
   const uint32_t g = (uint32_t)(R.g_base + tx * STRIDE + lane);
   const uint32_t g_last = (sw + 3) / 4 - 1;
@@ -229,9 +314,14 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
     st_ok[o] = (lane < STRIDE) && (o < cnt) && (X >= R.x0) && (X < R.x1);
     last[o] = (o == cnt - 1) ? 1.f : 0.f;
   }
-  // columns past the bitmap edge (row padding) must not trip the alpha check
+  // columns past the bitmap edge (row padding; zero-filled by TMA) must not trip the alpha check
   const uint32_t m1 = (4 * g + 1 >= sw) ? 0xff000000u : 0u, m2 = (4 * g + 2 >= sw) ? 0xff000000u : 0u,
                  m3 = (4 * g + 3 >= sw) ? 0xff000000u : 0u;
+#if STITCH_STREAM_TMA
+  const uint32_t m0 = (4 * g >= sw) ? 0xff000000u : 0u;
+#else
+  const uint32_t m0 = 0u;   // lanes past the last group re-read it (clamped address)
+#endif
   // output pointers walk with the rows: device position of this lane's output 0, +-1 pixel per output
   const int xdir = im.flip_x ? -1 : 1;
   const int cx0 = X0 + (im.flip_x ? (int)dw - 1 - Xfirst : Xfirst);      // canvas x of output 0
@@ -279,6 +369,8 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
     cr_own = crptr + (own1 ? c_off[MAXO - 1] : c_off[0]);
   }
 
+  const uint32_t lring = smem_u32(&ws.ring[0][lane * 16]);
+#if !STITCH_STREAM_TMA
   // ---- ring prologue: each lane stages its own 16 B per row; rows travel in pairs (one commit group
   // per pair, STREAM_NST rows deep).  Rows are addressed by a 32-bit offset clamped to the unit's last
   // row, so the refills need no predicate: past the end (and in lanes past the bitmap's last group)
@@ -287,13 +379,13 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
   const uint8_t* lbase = im.data + (int64_t)rs * im.pitch + (int64_t)min(g, g_last) * 16;
   const uint32_t off_max = (uint32_t)(nrows - 1) * pitch;
   uint32_t off = 0;
-  const uint32_t lring = smem_u32(&ws.ring[0][lane * 16]);
 #pragma unroll
   for (int u = 0; u < STREAM_NST; ++u) {
     cp_async16(lring + u * STREAM_STAGE_BYTES, lbase + off);
     off = min(off + pitch, off_max);
     if (u & 1) cp_async_commit();
   }
+#endif
   __syncwarp();  // row table complete
 
   float acc[12];
@@ -431,6 +523,50 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
     }
   };
 
+#if STITCH_STREAM_TMA
+  uint32_t slot = wst.slot, parity = wst.parity;
+  for (int i0 = 0; i0 < nrows_pad; i0 += 32) {
+    // which of the next 32 rows complete an output row: one ballot, so the per-row branch below is on
+    // a warp-uniform mask and needs no reconvergence scaffolding around the shuffles
+    const bool fl = (i0 + lane < nrows_pad) && (ws.tab[i0 + lane].y >= 0.f);
+    uint32_t mask = __ballot_sync(0xffffffffu, fl);
+    const int i1 = min(i0 + 32, nrows_pad);
+#pragma unroll 1
+    for (int is = i0; is < i1; is += ROWS) {   // one stage (i1 - is is a multiple of STREAM_UNR)
+      mbar_wait(full_s + 8u * slot, parity);   // the stage's rows have landed
+      const uint32_t ring_h = lring + slot * SLOT_BYTES;
+      const uint32_t tab_h = tab_s + (uint32_t)is * 8u;
+#pragma unroll
+      for (int u = 0; u < ROWS; u += 2) {
+        if (u > 0 && (u % STREAM_UNR) == 0 && is + u >= i1) break;   // the unit's last stage may hold fewer rows
+        const float4 t2 = lds128f(tab_h + u * 8);  // table entries of rows is+u, is+u+1
+        const uint4 pa = lds128(ring_h + u * STREAM_STAGE_BYTES);
+        const uint4 pb = lds128(ring_h + (u + 1) * STREAM_STAGE_BYTES);
+        // alpha check: per column and per row pair, one three-input LOP3 each; the edge masks come in at the end
+        and_x &= pa.x & pb.x;
+        and_y &= pa.y & pb.y;
+        and_z &= pa.z & pb.z;
+        and_w &= pa.w & pb.w;
+        row_step(pa, t2.x, t2.y, (mask >> u) & 1u);
+        row_step(pb, t2.z, t2.w, (mask >> (u + 1)) & 1u);
+      }
+      mask >>= ROWS;
+      // every lane holds the stage's rows in registers: lane 0 re-arms the slot and requests the unit's next rows
+      __syncwarp();
+      if (rows_left > 0) {
+        if (lane == 0) issue(slot);
+        y_next += ROWS;
+        rows_left -= ROWS;
+      }
+      if (++slot == STAGES) {
+        slot = 0;
+        parity ^= 1u;
+      }
+    }
+  }
+  wst.slot = slot;
+  wst.parity = parity;
+#else
   for (int i0 = 0; i0 < nrows_pad; i0 += 32) {
     // which of the next 32 rows complete an output row: one ballot, so the per-row branch below is on
     // a warp-uniform mask and needs no reconvergence scaffolding around the shuffles
@@ -462,9 +598,10 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
       hoff = (hoff + STREAM_UNR * STREAM_STAGE_BYTES) & (STREAM_NST * STREAM_STAGE_BYTES - 1);
     }
   }
+#endif
   // Translucent bitmaps (rare: photos are opaque): the unit is redone with the exact premultiplied
   // source-over evaluation.  Outside the hot loop so it costs the streaming path no registers.
-  const uint32_t and_acc = and_x & (and_y | m1) & (and_z | m2) & (and_w | m3);
+  const uint32_t and_acc = (and_x | m0) & (and_y | m1) & (and_z | m2) & (and_w | m3);
   const bool need_fix = (and_acc >> 24) != 0xffu;
   if (__any_sync(0xffffffffu, need_fix)) {
     const int xf0 = __shfl_sync(0xffffffffu, Xfirst, 0), xf1 = __shfl_sync(0xffffffffu, Xfirst, STRIDE);
@@ -473,6 +610,20 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const Region& R, 
     const int ay = im.flip_y ? (int)(dh - oy1) : (int)oy0, by = im.flip_y ? (int)(dh - oy0) : (int)oy1;
     redo_rect<MODE>(P, X0 + ax, Y0 + ay, X0 + bx, Y0 + by, lane, im.flip_x ? 1 : 0);
   }
+#if STITCH_STREAM_TMA
+  // A lane whose group reaches past the bitmap edge received zero-filled (transparent) pixels: a later unit of this
+  // warp reads ring rows it has not fetched as padding (nrows_pad > nrows), and those must look opaque.  Rare
+  // (right-edge units of bitmaps whose width is no multiple of 128 px), outside the hot loop.  The branch is taken on
+  // a vote and the stores are predicated: a per-lane branch here leaves the compiler unable to prove that the warp
+  // is converged when the unit loop comes round, and it then guards every shuffle of the row loop (BRA.DIV).
+  if (__any_sync(0xffffffffu, m3 != 0u)) {
+#pragma unroll 1
+    for (int r = 0; r < STREAM_NST; ++r)
+      asm volatile("{\n .reg .pred q;\n setp.ne.u32 q, %2, 0;\n @q st.shared.v4.u32 [%0], {%1,%1,%1,%1};\n}"
+                   ::"r"(lring + r * STREAM_STAGE_BYTES), "r"(0xffffffffu), "r"(m3) : "memory");
+    fence_proxy_async();
+  }
+#endif
 }
 
 }  // namespace stitch
