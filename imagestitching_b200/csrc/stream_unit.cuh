@@ -17,17 +17,13 @@
 
 namespace stitch {
 
-#if STITCH_STREAM_TMA
 // Staging by TMA: the warp's ring holds STREAM_TMA_STAGES stages of STREAM_TMA_ROWS source rows (512 B each); a stage is
 // filled by ONE cp.async.bulk.tensor.2d box (UTMALDG) that lane 0 issues when the warp has finished reading the
-// stage's previous contents, and completes on the stage's mbarrier (expect-tx bytes).
+// stage's previous contents, and completes on the stage's mbarrier (expect-tx bytes).  (Round 1 staged with per-lane
+// cp.async / LDGSTS, 16 B per lane and row: 59.8 M warp instructions per 9x12 MP job against 57.3 M with the boxes,
+// 89.3 against 87.6 us on the same box; profiles/r2_compose_staging_ab.md.)
 #define STREAM_NST (STREAM_TMA_ROWS * STREAM_TMA_STAGES)
-#else
-#ifndef STREAM_NST
-#define STREAM_NST 8  // ring depth: source rows in flight per lane (power of two, multiple of STREAM_UNR)
-#endif
-#endif
-#define STREAM_UNR 4  // rows per iteration of the unrolled row loop
+#define STREAM_UNR 4  // rows between two possible ends of a unit's row range (nrows is padded to a multiple)
 #define STREAM_STAGE_BYTES 512
 // Output modes of the fused launch
 #define STREAM_MODE_RGBA 0  // RGBA8 canvas
@@ -38,18 +34,12 @@ namespace stitch {
 // when chroma is produced, so that the chroma partner of the last stored output is complete too.
 #define STREAM_STRIDE_OF(MODE, HOPS) ((MODE) == STREAM_MODE_RGBA ? 32 - (HOPS) : 32 - 2 * (HOPS))
 
-#if STITCH_STREAM_TMA
-static_assert(STREAM_TMA_ROWS % STREAM_UNR == 0 && 32 % STREAM_TMA_ROWS == 0 && STREAM_UNR % 2 == 0, "ring layout");
-#else
-static_assert(STREAM_NST % STREAM_UNR == 0 && (STREAM_NST & (STREAM_NST - 1)) == 0 && STREAM_UNR % 2 == 0, "ring layout");
-#endif
+static_assert(STREAM_TMA_ROWS == 8 && STREAM_UNR == 4, "the row loop is written for stages of 8 rows = 4 row pairs");
 
 struct WarpSmem {
   alignas(128) uint8_t ring[STREAM_NST][STREAM_STAGE_BYTES];
-  alignas(16) float2 tab[STREAM_TAB_MAX];
-#if STITCH_STREAM_TMA
+  alignas(16) uint4 tab[STREAM_TAB_MAX / 2];      // row-PAIR table (build_pair_table)
   alignas(8) uint64_t full[STREAM_TMA_STAGES];   // one mbarrier per stage: completes when the stage's bytes have landed
-#endif
 };
 // what a warp carries from unit to unit
 struct WarpState {
@@ -59,18 +49,6 @@ struct WarpState {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-// Per-lane 16-byte async copy global -> shared (LDGSTS), L1 bypassed.  A lane only ever refills the
-// slot it has itself just read with LDS; both go through the lane's LSU queue in program order and
-// the copy's shared-memory write lands a global-memory latency later, so no barrier is needed and
-// no other lane ever touches the slot.
-__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src) {
-  asm volatile("cp.async.cg.shared.global.L2::256B [%0], [%1], 16;" ::"r"(dst_smem), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
@@ -82,7 +60,6 @@ __device__ __forceinline__ float4 lds128f(uint32_t addr) {
   return r;
 }
 
-#if STITCH_STREAM_TMA
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
@@ -107,7 +84,6 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
   asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(bar) : "memory");
 }
-#endif
 
 // ---- packed fp32x2 arithmetic (FFMA2 / FMUL2: two lanes of fp32 per issue slot) ----
 // (dx, dy) += (ax, ay) * s
@@ -124,30 +100,53 @@ __device__ __forceinline__ void mul2_s(float& dx, float& dy, float ax, float ay,
       : "=f"(dx), "=f"(dy)
       : "f"(ax), "f"(ay), "f"(s));
 }
-// (dx, dy) = floor-quantise: see quant_bits
-__device__ __forceinline__ void quant2(uint32_t& qx, uint32_t& qy, float ax, float ay) {
+// ---- the "1 + b * 2^-15" number form (upscale_unit.cuh): a byte becomes a float with ONE PRMT ----
+// byte CH of px -> float 1 + b * 2^-15  (bit pattern 0x3F80bb00)
+template <int CH>
+__device__ __forceinline__ float expand(uint32_t px) {
+  return __uint_as_float(__byte_perm(px, 0x3F800000u, 0x7604u | (CH << 4)));
+}
+// (qx, qy) = 0x4B0000kk with kk = floor(v + 0.5) for x = 1 + v * 2^-15: x * 2^15 + (2^23 - 2^15 + 0.5), rounded down
+__device__ __forceinline__ void quant2_one(uint32_t& qx, uint32_t& qy, float ax, float ay) {
   asm("{.reg .b64 ra, rb, rc, rd;\n mov.b64 ra, {%2,%3};\n mov.b64 rb, {%4,%4};\n mov.b64 rc, {%5,%5};\n"
       " fma.rm.f32x2 rd, ra, rb, rc;\n mov.b64 {%0,%1}, rd;}"
       : "=r"(qx), "=r"(qy)
       : "f"(ax), "f"(ay), "f"(32768.f), "f"(8355840.5f));
 }
 // negated form, rounded towards +inf: bit pattern 0xCB0000kk, so byte 3 has its sign bit set
-__device__ __forceinline__ void quant2_neg(uint32_t& qx, uint32_t& qy, float ax, float ay) {
+__device__ __forceinline__ void quant2_neg_one(uint32_t& qx, uint32_t& qy, float ax, float ay) {
   asm("{.reg .b64 ra, rb, rc, rd;\n mov.b64 ra, {%2,%3};\n mov.b64 rb, {%4,%4};\n mov.b64 rc, {%5,%5};\n"
       " fma.rp.f32x2 rd, ra, rb, rc;\n mov.b64 {%0,%1}, rd;}"
       : "=r"(qx), "=r"(qy)
       : "f"(ax), "f"(ay), "f"(-32768.f), "f"(-8355840.5f));
 }
+__device__ __forceinline__ uint32_t quant_bits_one(float x) { return __float_as_uint(__fmaf_rd(x, 32768.f, 8355840.5f)); }
 
-// byte CH of px -> float 1 + b * 2^-15  (bit pattern 0x3F80bb00): one PRMT
-template <int CH>
-__device__ __forceinline__ float expand(uint32_t px) {
-  return __uint_as_float(__byte_perm(px, 0x3F800000u, 0x7604u | (CH << 4)));
+// ---- number form of the streaming unit ----
+// The vertical pass accumulates INTEGERS: pixel bytes times 15-bit row weights
+// that sum to exactly 2^15 per output row (IDP.2A, two rows per instruction), into registers that start at
+// 0x4B000000 -- so an accumulator is at the same time the bit pattern of the float 2^23 + s, s = v * 2^15 < 2^23 for
+// a channel value v in [0, 255], and the horizontal pass (float weights that sum to 1) works on it without any
+// conversion instruction.  Resolution 2^-15 LSB.
+#define STREAM_ACC_BASE 0x4B000000u
+// (qx, qy) = 0x4B0000kk with kk = floor(v + 0.5): one FFMA2.RM -- x * 2^-15 + (2^23 - 256 + 0.5) = 2^23 + v + 0.5, rounded down
+__device__ __forceinline__ void quant2(uint32_t& qx, uint32_t& qy, float ax, float ay) {
+  asm("{.reg .b64 ra, rb, rc, rd;\n mov.b64 ra, {%2,%3};\n mov.b64 rb, {%4,%4};\n mov.b64 rc, {%5,%5};\n"
+      " fma.rm.f32x2 rd, ra, rb, rc;\n mov.b64 {%0,%1}, rd;}"
+      : "=r"(qx), "=r"(qy)
+      : "f"(ax), "f"(ay), "f"(3.0517578125e-05f), "f"(8388352.5f));
 }
-// float 1 + v * 2^-15 (v in [0,255]) -> 0x4B0000kk with kk = floor(v + 0.5): one FFMA.RM
-__device__ __forceinline__ uint32_t quant_bits(float x) { return __float_as_uint(__fmaf_rd(x, 32768.f, 8355840.5f)); }
+// negated form, rounded towards +inf: bit pattern 0xCB0000kk, so byte 3 has its sign bit set
+__device__ __forceinline__ void quant2_neg(uint32_t& qx, uint32_t& qy, float ax, float ay) {
+  asm("{.reg .b64 ra, rb, rc, rd;\n mov.b64 ra, {%2,%3};\n mov.b64 rb, {%4,%4};\n mov.b64 rc, {%5,%5};\n"
+      " fma.rp.f32x2 rd, ra, rb, rc;\n mov.b64 {%0,%1}, rd;}"
+      : "=r"(qx), "=r"(qy)
+      : "f"(ax), "f"(ay), "f"(-3.0517578125e-05f), "f"(-8388352.5f));
+}
+// float 2^23 + v * 2^15 (v in [0,255]) -> 0x4B0000kk with kk = floor(v + 0.5): one FFMA.RM
+__device__ __forceinline__ uint32_t quant_bits(float x) { return __float_as_uint(__fmaf_rd(x, 3.0517578125e-05f, 8388352.5f)); }
 // same value negated (0xCB0000kk): FFMA.RP
-__device__ __forceinline__ uint32_t quant_bits_neg(float x) { return __float_as_uint(__fmaf_ru(x, -32768.f, -8355840.5f)); }
+__device__ __forceinline__ uint32_t quant_bits_neg(float x) { return __float_as_uint(__fmaf_ru(x, -3.0517578125e-05f, -8388352.5f)); }
 // (r, g, b quantised as above, b in the negated form) -> 0xFFbbggrr with two PRMT: the alpha byte is
 // the sign replication of b's top byte
 __device__ __forceinline__ uint32_t pack_rgb(uint32_t r, uint32_t g, uint32_t bneg) {
@@ -163,44 +162,60 @@ __device__ __forceinline__ void st_u8_if(uint8_t* p, uint32_t v, bool ok) {
   asm volatile("{.reg .pred q;\n setp.ne.u32 q, %2, 0;\n @q st.global.u8 [%0], %1;}" ::"l"(p), "r"(v), "r"((uint32_t)ok) : "memory");
 }
 
-// Builds the warp's row table for source rows [rs, rs + nrows): entry = (weight into the current
-// output row, weight into the next one or -1 when the row does not complete an output row).
+// Builds the warp's row-PAIR table for source rows [rs, rs + nrows), pair p = rows (2p, 2p+1) = (A, B).
+// Entry = {W1, W2, W3, flags}; a W packs two 15-bit weights (row A in the low half, row B in the high half) for one
+// IDP.2A per channel, and the pair is applied as
+//     acc += W1 . (A, B);   if (flags != 0) { EMIT; acc = W2 . (A, B); }   if (flags == 3) { EMIT; acc = W3 . (A, B); }
+// flags bit 0 / 1: row A / B completes an output row (its remainder, and every later row, belongs to the next one).
+// The weights of an output row are differences of F(t) = round(t * 2^15 / sh) at the row boundaries inside it, so they
+// sum to exactly 2^15 whatever the rounding does (a constant image stays exact), each within 2^-16 of the true area.
 // Each lane fills a contiguous chunk, so it needs one division and then steps incrementally.
-__device__ __forceinline__ void build_row_table(float2* tab, int lane, uint32_t rs, int nrows, int nrows_pad, uint32_t sh,
-                                                uint32_t dh, uint32_t oy0, float inv_sh) {
-  const int chunk = (nrows_pad + 31) >> 5;
-  int k = lane * chunk;
-  const int k_end = min(k + chunk, nrows_pad);
-  if (k >= k_end) return;
-  uint32_t lo = (rs + (uint32_t)k) * dh;  // start of row (rs+k) in source units scaled by dh
-  uint32_t Ya = lo / sh;                  // output row that contains it
-  uint32_t E = (Ya + 1) * sh;             // where that output row ends
-  const float wfull = (float)dh * inv_sh;
-  for (; k < k_end; ++k) {
-    float wc, wn;
-    if (k >= nrows) {  // padding up to a multiple of the unroll: contributes nothing
-      wc = 0.f;
-      wn = -1.f;
-    } else {
-      const uint32_t hi = lo + dh;
-      if (E >= hi) {  // row entirely inside output row Ya
-        wc = wfull;
-        wn = (E == hi) ? 0.f : -1.f;  // boundary exactly at the row end: emit, the next row starts clean
+__device__ __forceinline__ void build_pair_table(uint4* tab, int lane, uint32_t rs, int nrows, int npairs, uint32_t sh, uint32_t dh,
+                                                 uint32_t oy0, float q15) {
+  const int chunk = (npairs + 31) >> 5;
+  int p = lane * chunk;
+  const int p_end = min(p + chunk, npairs);
+  if (p >= p_end) return;
+  uint32_t lo = (rs + 2u * (uint32_t)p) * dh;  // start of row (rs + 2p) in source units scaled by dh
+  uint32_t Ya = lo / sh;                       // output row that contains it
+  uint32_t base = Ya * sh;                     // where that output row starts
+  auto F = [&](uint32_t t) { return (uint32_t)__float2int_rd(fmaf((float)t, q15, 0.5f)); };
+  int k = 2 * p;
+  auto row = [&](uint32_t& wc, uint32_t& wn, uint32_t& e) {
+    wc = 0u; wn = 0u; e = 0u;
+    if (k < nrows) {   // rows past the end are padding: no weight, no emit
+      const uint32_t hi = lo + dh, E = base + sh;
+      if (E >= hi) {   // row entirely inside output row Ya
+        wc = F(hi - base) - F(lo - base);
+        e = (E == hi) ? 1u : 0u;   // boundary exactly at the row end: emit, the next row starts clean
       } else {
-        wc = (float)(E - lo) * inv_sh;
-        wn = (float)(hi - E) * inv_sh;
+        wc = 32768u - F(lo - base);
+        wn = F(hi - E);
+        e = 1u;
       }
       if (Ya < oy0) {  // the part that belongs to the previous unit's output row is dropped
-        wc = (wn > 0.f) ? wn : 0.f;
-        wn = -1.f;
+        wc = wn;
+        wn = 0u;
+        e = 0u;
       }
       lo = hi;
-      if (E <= lo) {  // next row starts in the next output row
+      if (E <= lo) {   // next row starts in the next output row
         ++Ya;
-        E += sh;
+        base = E;
       }
     }
-    tab[k] = make_float2(wc, wn);
+    ++k;
+  };
+  for (; p < p_end; ++p) {
+    uint32_t ca, na, ea, cb, nb, eb;
+    row(ca, na, ea);
+    row(cb, nb, eb);
+    uint4 t;
+    t.x = ca | ((ea ? 0u : cb) << 16);
+    t.y = ea ? (na | (cb << 16)) : (nb << 16);
+    t.z = nb << 16;
+    t.w = ea | (eb << 1);
+    tab[p] = t;
   }
 }
 
@@ -219,7 +234,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
   const uint32_t dw = (uint32_t)im.W, dh = (uint32_t)im.H;
   const int X0 = (int)im.X0, Y0 = (int)im.Y0;
   const uint32_t oy0 = (uint32_t)(R.y0 + ty * R.tile_h), oy1 = min(oy0 + (uint32_t)R.tile_h, (uint32_t)R.y1);
-  const float inv_sw = __frcp_rn((float)sw), inv_sh = __frcp_rn((float)sh);
+  const float inv_sw = __frcp_rn((float)sw);
 
   // ---- vertical: source rows [rs, re) ----
   const uint32_t rs = (oy0 * sh) / dh;
@@ -228,7 +243,6 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
   const int nrows_pad = (nrows + STREAM_UNR - 1) / STREAM_UNR * STREAM_UNR;
   constexpr int STRIDE = STREAM_STRIDE_OF(MODE, HOPS);
   __syncwarp();  // every lane is done reading the previous unit's table and ring
-#if STITCH_STREAM_TMA
   // ---- ring prologue, first thing in the unit: the first stages are in flight while the row table and the lane
   // weights are set up.  A stage = ROWS source rows x the band's 128 pixels.  The ring slots are used round-robin
   // across units (wst.slot), so the parity of a slot's mbarrier is one bit that flips when the slot index wraps.
@@ -264,8 +278,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
       }
     }
   }
-#endif
-  build_row_table(ws.tab, lane, rs, nrows, nrows_pad, sh, dh, oy0, inv_sh);
+  build_pair_table(ws.tab, lane, rs, nrows, nrows_pad / 2, sh, dh, oy0, 32768.f * __frcp_rn((float)sh));
 
   // ---- horizontal: this lane's 4-pixel source group and the outputs that start in it ----
   constexpr bool RGBA = MODE != STREAM_MODE_YUV, YUV = MODE != STREAM_MODE_RGBA;
@@ -317,11 +330,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
   // columns past the bitmap edge (row padding; zero-filled by TMA) must not trip the alpha check
   const uint32_t m1 = (4 * g + 1 >= sw) ? 0xff000000u : 0u, m2 = (4 * g + 2 >= sw) ? 0xff000000u : 0u,
                  m3 = (4 * g + 3 >= sw) ? 0xff000000u : 0u;
-#if STITCH_STREAM_TMA
   const uint32_t m0 = (4 * g >= sw) ? 0xff000000u : 0u;
-#else
-  const uint32_t m0 = 0u;   // lanes past the last group re-read it (clamped address)
-#endif
   // output pointers walk with the rows: device position of this lane's output 0, +-1 pixel per output
   const int xdir = im.flip_x ? -1 : 1;
   const int cx0 = X0 + (im.flip_x ? (int)dw - 1 - Xfirst : Xfirst);      // canvas x of output 0
@@ -370,64 +379,40 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
   }
 
   const uint32_t lring = smem_u32(&ws.ring[0][lane * 16]);
-#if !STITCH_STREAM_TMA
-  // ---- ring prologue: each lane stages its own 16 B per row; rows travel in pairs (one commit group
-  // per pair, STREAM_NST rows deep).  Rows are addressed by a 32-bit offset clamped to the unit's last
-  // row, so the refills need no predicate: past the end (and in lanes past the bitmap's last group)
-  // they re-read bytes that are then weighted with zero. ----
-  const uint32_t pitch = (uint32_t)im.pitch;
-  const uint8_t* lbase = im.data + (int64_t)rs * im.pitch + (int64_t)min(g, g_last) * 16;
-  const uint32_t off_max = (uint32_t)(nrows - 1) * pitch;
-  uint32_t off = 0;
-#pragma unroll
-  for (int u = 0; u < STREAM_NST; ++u) {
-    cp_async16(lring + u * STREAM_STAGE_BYTES, lbase + off);
-    off = min(off + pitch, off_max);
-    if (u & 1) cp_async_commit();
-  }
-#endif
   __syncwarp();  // row table complete
 
-  float acc[12];
+  // vertical accumulators: 4 pixels x (r, g, b), integer sums that are float bit patterns (STREAM_ACC_BASE)
+  uint32_t acc[12];
 #pragma unroll
-  for (int k = 0; k < 12; ++k) acc[k] = 0.f;
+  for (int k = 0; k < 12; ++k) acc[k] = STREAM_ACC_BASE;
   uint32_t and_x = 0xffffffffu, and_y = 0xffffffffu, and_z = 0xffffffffu, and_w = 0xffffffffu;
   const uint32_t tab_s = smem_u32(ws.tab);
-  uint32_t hoff = 0;  // byte offset of the ring part the current STREAM_UNR rows live in
 
-  // One source row: vertical accumulate; when the row completes an output row (EMIT), the horizontal
-  // pass runs in registers and the accumulators restart with the row's share of the next output row.
-  auto row_step = [&](const uint4& px, const float wc, const float wn, const bool emit) {
-    float f[12];
-    f[0] = expand<0>(px.x); f[1] = expand<1>(px.x); f[2] = expand<2>(px.x);
-    f[3] = expand<0>(px.y); f[4] = expand<1>(px.y); f[5] = expand<2>(px.y);
-    f[6] = expand<0>(px.z); f[7] = expand<1>(px.z); f[8] = expand<2>(px.z);
-    f[9] = expand<0>(px.w); f[10] = expand<1>(px.w); f[11] = expand<2>(px.w);
-#pragma unroll
-    for (int k = 0; k < 12; k += 2) fma2_s(acc[k], acc[k + 1], f[k], f[k + 1], wc);
-    if (emit) {
-      float out[3][MAXO];  // un-rounded outputs, still in the 1 + v * 2^-15 form
+  // An output row is complete in acc: the horizontal pass runs in registers and the row is stored.
+  auto emit_row = [&]() {
+    {
+      float out[3][MAXO];  // un-rounded outputs, still in the 2^23 + v * 2^15 form
 #pragma unroll
       for (int ch = 0; ch < 3; ++ch) {
-        float prev = wprev[0] * acc[ch];
+        float prev = wprev[0] * __uint_as_float(acc[ch]);
 #pragma unroll
-        for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], acc[c * 3 + ch], prev);
+        for (int c = 1; c < 4; ++c) prev = fmaf(wprev[c], __uint_as_float(acc[c * 3 + ch]), prev);
         float rcv = __shfl_down_sync(0xffffffffu, prev, 1);
 #pragma unroll
         for (int k = 1; k < HOPS; ++k) rcv = fmaf(hop[k], __shfl_down_sync(0xffffffffu, prev, k + 1), rcv);
         // outputs in pairs: (out[o], out[o+1]) = sum_c (w[o][c], w[o+1][c]) * acc[c]
 #pragma unroll
         for (int o = 0; o + 1 < MAXO; o += 2) {
-          mul2_s(out[ch][o], out[ch][o + 1], w[o][0], w[o + 1][0], acc[ch]);
+          mul2_s(out[ch][o], out[ch][o + 1], w[o][0], w[o + 1][0], __uint_as_float(acc[ch]));
 #pragma unroll
-          for (int c = 1; c < 4; ++c) fma2_s(out[ch][o], out[ch][o + 1], w[o][c], w[o + 1][c], acc[c * 3 + ch]);
+          for (int c = 1; c < 4; ++c) fma2_s(out[ch][o], out[ch][o + 1], w[o][c], w[o + 1][c], __uint_as_float(acc[c * 3 + ch]));
           fma2_s(out[ch][o], out[ch][o + 1], last[o], last[o + 1], rcv);
         }
         if (MAXO & 1) {
           const int o = MAXO - 1;
-          out[ch][o] = w[o][0] * acc[ch];
+          out[ch][o] = w[o][0] * __uint_as_float(acc[ch]);
 #pragma unroll
-          for (int c = 1; c < 4; ++c) out[ch][o] = fmaf(w[o][c], acc[c * 3 + ch], out[ch][o]);
+          for (int c = 1; c < 4; ++c) out[ch][o] = fmaf(w[o][c], __uint_as_float(acc[c * 3 + ch]), out[ch][o]);
           out[ch][o] = fmaf(last[o], rcv, out[ch][o]);
         }
       }
@@ -486,7 +471,7 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
         if (__any_sync(0xffffffffu, second)) {   // warp-uniform by construction; the vote tells the compiler
           const float nb_cb = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccb[0], 1) : __shfl_sync(0xffffffffu, ccb[0], lane + nxt);
           const float nb_cr = (HOPS == 1) ? __shfl_down_sync(0xffffffffu, ccr[0], 1) : __shfl_sync(0xffffffffu, ccr[0], lane + nxt);
-          const float bias = 1.f + 128.f / 32768.f;
+          const float bias = 8388608.f + 128.f * 32768.f;   // 128 in the accumulator form
           if (MAXO == 2) {
             const float mcb = own1 ? ccb[MAXO - 1] : ccb[0], mcr = own1 ? ccr[MAXO - 1] : ccr[0];
             const float qcb = part_local ? ccb[MAXO - 1] : nb_cb, qcr = part_local ? ccr[MAXO - 1] : nb_cr;
@@ -518,39 +503,71 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
         }
         second = !second;
       }
+    }
+  };
+  // One row pair (A, B) of the lane's group: see build_pair_table.  e1: one of the rows completes an output row,
+  // e2: both do (ratio_y < 2).  Per pixel 2 PRMT interleave the two rows' bytes channel by channel and 3 IDP.2A
+  // apply both row weights at once (12 PRMT + 6 FFMA2 per ROW in the float form this replaces).
+  auto pair_step = [&](const uint4& pa, const uint4& pb, const uint4& t, const bool e1, const bool e2) {
+    uint32_t rg[4], ba[4];
+    rg[0] = __byte_perm(pa.x, pb.x, 0x5140); ba[0] = __byte_perm(pa.x, pb.x, 0x7362);
+    rg[1] = __byte_perm(pa.y, pb.y, 0x5140); ba[1] = __byte_perm(pa.y, pb.y, 0x7362);
+    rg[2] = __byte_perm(pa.z, pb.z, 0x5140); ba[2] = __byte_perm(pa.z, pb.z, 0x7362);
+    rg[3] = __byte_perm(pa.w, pb.w, 0x5140); ba[3] = __byte_perm(pa.w, pb.w, 0x7362);
 #pragma unroll
-      for (int k = 0; k < 12; k += 2) mul2_s(acc[k], acc[k + 1], f[k], f[k + 1], wn);
+    for (int c = 0; c < 4; ++c) {
+      acc[3 * c] = __dp2a_lo(t.x, rg[c], acc[3 * c]);
+      acc[3 * c + 1] = __dp2a_hi(t.x, rg[c], acc[3 * c + 1]);
+      acc[3 * c + 2] = __dp2a_lo(t.x, ba[c], acc[3 * c + 2]);
+    }
+    if (e1) {
+      emit_row();
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        acc[3 * c] = __dp2a_lo(t.y, rg[c], STREAM_ACC_BASE);
+        acc[3 * c + 1] = __dp2a_hi(t.y, rg[c], STREAM_ACC_BASE);
+        acc[3 * c + 2] = __dp2a_lo(t.y, ba[c], STREAM_ACC_BASE);
+      }
+      if (e2) {
+        emit_row();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          acc[3 * c] = __dp2a_lo(t.z, rg[c], STREAM_ACC_BASE);
+          acc[3 * c + 1] = __dp2a_hi(t.z, rg[c], STREAM_ACC_BASE);
+          acc[3 * c + 2] = __dp2a_lo(t.z, ba[c], STREAM_ACC_BASE);
+        }
+      }
     }
   };
 
-#if STITCH_STREAM_TMA
   uint32_t slot = wst.slot, parity = wst.parity;
-  for (int i0 = 0; i0 < nrows_pad; i0 += 32) {
-    // which of the next 32 rows complete an output row: one ballot, so the per-row branch below is on
-    // a warp-uniform mask and needs no reconvergence scaffolding around the shuffles
-    const bool fl = (i0 + lane < nrows_pad) && (ws.tab[i0 + lane].y >= 0.f);
-    uint32_t mask = __ballot_sync(0xffffffffu, fl);
-    const int i1 = min(i0 + 32, nrows_pad);
+  const int npairs = nrows_pad / 2;   // even: nrows_pad is a multiple of STREAM_UNR = 4
+  for (int p0 = 0; p0 < npairs; p0 += 32) {
+    // which of the next 32 row pairs complete output rows: two ballots over the table flags, so the branches in
+    // pair_step are on warp-uniform masks and need no reconvergence scaffolding around the shuffles
+    const uint32_t fl = (p0 + lane < npairs) ? ws.tab[p0 + lane].w : 0u;
+    uint32_t mask1 = __ballot_sync(0xffffffffu, fl != 0u), mask2 = __ballot_sync(0xffffffffu, fl == 3u);
+    const int p1 = min(p0 + 32, npairs);
 #pragma unroll 1
-    for (int is = i0; is < i1; is += ROWS) {   // one stage (i1 - is is a multiple of STREAM_UNR)
-      mbar_wait(full_s + 8u * slot, parity);   // the stage's rows have landed
+    for (int ps = p0; ps < p1; ps += ROWS / 2) {   // one stage = 4 row pairs (the unit's last one may hold 2)
+      mbar_wait(full_s + 8u * slot, parity);       // the stage's rows have landed
       const uint32_t ring_h = lring + slot * SLOT_BYTES;
-      const uint32_t tab_h = tab_s + (uint32_t)is * 8u;
+      const uint32_t tab_h = tab_s + (uint32_t)ps * 16u;
 #pragma unroll
-      for (int u = 0; u < ROWS; u += 2) {
-        if (u > 0 && (u % STREAM_UNR) == 0 && is + u >= i1) break;   // the unit's last stage may hold fewer rows
-        const float4 t2 = lds128f(tab_h + u * 8);  // table entries of rows is+u, is+u+1
-        const uint4 pa = lds128(ring_h + u * STREAM_STAGE_BYTES);
-        const uint4 pb = lds128(ring_h + (u + 1) * STREAM_STAGE_BYTES);
+      for (int u = 0; u < ROWS / 2; ++u) {
+        if (u == ROWS / 4 && ps + u >= p1) break;
+        const uint4 t = lds128(tab_h + u * 16);
+        const uint4 pa = lds128(ring_h + (2 * u) * STREAM_STAGE_BYTES);
+        const uint4 pb = lds128(ring_h + (2 * u + 1) * STREAM_STAGE_BYTES);
         // alpha check: per column and per row pair, one three-input LOP3 each; the edge masks come in at the end
         and_x &= pa.x & pb.x;
         and_y &= pa.y & pb.y;
         and_z &= pa.z & pb.z;
         and_w &= pa.w & pb.w;
-        row_step(pa, t2.x, t2.y, (mask >> u) & 1u);
-        row_step(pb, t2.z, t2.w, (mask >> (u + 1)) & 1u);
+        pair_step(pa, pb, t, (mask1 >> u) & 1u, (mask2 >> u) & 1u);
       }
-      mask >>= ROWS;
+      mask1 >>= ROWS / 2;
+      mask2 >>= ROWS / 2;
       // every lane holds the stage's rows in registers: lane 0 re-arms the slot and requests the unit's next rows
       __syncwarp();
       if (rows_left > 0) {
@@ -566,39 +583,6 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
   }
   wst.slot = slot;
   wst.parity = parity;
-#else
-  for (int i0 = 0; i0 < nrows_pad; i0 += 32) {
-    // which of the next 32 rows complete an output row: one ballot, so the per-row branch below is on
-    // a warp-uniform mask and needs no reconvergence scaffolding around the shuffles
-    const bool fl = (i0 + lane < nrows_pad) && (ws.tab[i0 + lane].y >= 0.f);
-    uint32_t mask = __ballot_sync(0xffffffffu, fl);
-    const int i1 = min(i0 + 32, nrows_pad);
-    for (int i = i0; i < i1; i += STREAM_UNR) {
-      const uint32_t ring_h = lring + hoff;
-#pragma unroll
-      for (int u = 0; u < STREAM_UNR; u += 2) {
-        const float4 t2 = lds128f(tab_s + (uint32_t)(i + u) * 8u);  // table entries of rows i+u, i+u+1
-        cp_async_wait<STREAM_NST / 2 - 1>();  // rows i+u, i+u+1 have landed (this lane's own copies)
-        const uint4 pa = lds128(ring_h + u * STREAM_STAGE_BYTES);
-        const uint4 pb = lds128(ring_h + (u + 1) * STREAM_STAGE_BYTES);
-        cp_async16(ring_h + u * STREAM_STAGE_BYTES, lbase + off);  // rows i+u+NST, i+u+1+NST
-        off = min(off + pitch, off_max);
-        cp_async16(ring_h + (u + 1) * STREAM_STAGE_BYTES, lbase + off);
-        off = min(off + pitch, off_max);
-        cp_async_commit();
-        // alpha check: per column and per row pair, one three-input LOP3 each; the edge masks come in at the end
-        and_x &= pa.x & pb.x;
-        and_y &= pa.y & pb.y;
-        and_z &= pa.z & pb.z;
-        and_w &= pa.w & pb.w;
-        row_step(pa, t2.x, t2.y, (mask >> u) & 1u);
-        row_step(pb, t2.z, t2.w, (mask >> (u + 1)) & 1u);
-      }
-      mask >>= STREAM_UNR;
-      hoff = (hoff + STREAM_UNR * STREAM_STAGE_BYTES) & (STREAM_NST * STREAM_STAGE_BYTES - 1);
-    }
-  }
-#endif
   // Translucent bitmaps (rare: photos are opaque): the unit is redone with the exact premultiplied
   // source-over evaluation.  Outside the hot loop so it costs the streaming path no registers.
   const uint32_t and_acc = (and_x | m0) & (and_y | m1) & (and_z | m2) & (and_w | m3);
@@ -610,7 +594,6 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
     const int ay = im.flip_y ? (int)(dh - oy1) : (int)oy0, by = im.flip_y ? (int)(dh - oy0) : (int)oy1;
     redo_rect<MODE>(P, X0 + ax, Y0 + ay, X0 + bx, Y0 + by, lane, im.flip_x ? 1 : 0);
   }
-#if STITCH_STREAM_TMA
   // A lane whose group reaches past the bitmap edge received zero-filled (transparent) pixels: a later unit of this
   // warp reads ring rows it has not fetched as padding (nrows_pad > nrows), and those must look opaque.  Rare
   // (right-edge units of bitmaps whose width is no multiple of 128 px), outside the hot loop.  The branch is taken on
@@ -623,7 +606,6 @@ __device__ __forceinline__ void stream_unit(const JobParam& P, const TmaMaps& ma
                    ::"r"(lring + r * STREAM_STAGE_BYTES), "r"(0xffffffffu), "r"(m3) : "memory");
     fence_proxy_async();
   }
-#endif
 }
 
 }  // namespace stitch

@@ -159,9 +159,9 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
       // red / green pairs in the plain form, the blue pairs in the negated one (pack_rgb takes alpha from its sign)
       uint32_t q[12];
 #pragma unroll
-      for (int k = 0; k < 8; k += 2) quant2(q[k], q[k + 1], v[k], v[k + 1]);
-      quant2_neg(q[8], q[9], v[8], v[9]);
-      quant2_neg(q[10], q[11], v[10], v[11]);
+      for (int k = 0; k < 8; k += 2) quant2_one(q[k], q[k + 1], v[k], v[k + 1]);
+      quant2_neg_one(q[8], q[9], v[8], v[9]);
+      quant2_neg_one(q[10], q[11], v[10], v[11]);
       uint32_t px[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) px[k] = pack_rgb(q[2 * k], q[2 * k + 1], q[8 + k]);
@@ -179,7 +179,7 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const float R_ = v[2 * k], G_ = v[2 * k + 1], B_ = v[8 + k];
-        yq[k] = quant_bits(fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_))) & 0xffu;
+        yq[k] = quant_bits_one(fmaf(0.299f, R_, fmaf(0.587f, G_, 0.114f * B_))) & 0xffu;
         ccb[k >> 1] += fmaf(-0.168736f, R_, fmaf(-0.331264f, G_, 0.5f * B_));
         ccr[k >> 1] += fmaf(0.5f, R_, fmaf(-0.418688f, G_, -0.081312f * B_));
       }
@@ -196,8 +196,8 @@ __device__ __forceinline__ void upscale_unit(const JobParam& P, const Region& R,
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           if (ok[2 * c]) {   // the region is even-aligned: a pair is inside or outside as a whole
-            cbp[c] = (uint8_t)quant_bits(fmaf(0.25f, ccb[c], bias));
-            crp[c] = (uint8_t)quant_bits(fmaf(0.25f, ccr[c], bias));
+            cbp[c] = (uint8_t)quant_bits_one(fmaf(0.25f, ccb[c], bias));
+            crp[c] = (uint8_t)quant_bits_one(fmaf(0.25f, ccr[c], bias));
           }
           ccb[c] = ccr[c] = 0.f;
         }
