@@ -193,13 +193,16 @@ inline bool build_plan(const JobParam& P, int mode, int hops, int resident_warps
 
   // Unit heights of the streaming regions -- a "guided" schedule.  Units are handed out in order to
   // `resident_warps` persistent warps.  Each image's rows are split into a BODY of large units
-  // (about one per warp, so the per-unit setup -- row table, lane weights -- is amortised over the
-  // most rows) followed by a TAIL of small units that even out the different speeds of the SMs
-  // (near / far L2 and HBM); all tails are queued after all bodies.  With equal-sized units only,
-  // ncu showed the SMs 14 % idle on average while the slowest ones finished.
+  // (about one per warp, so the per-unit setup -- row table, lane weights, the empty TMA ring -- is
+  // amortised over the most rows) followed by a TAIL of smaller units that even out the different
+  // speeds of the SMs (near / far L2 and HBM); all tails are queued after all bodies.
+  // Tail units are 128 source rows: with the TMA ring and the integer vertical pass a unit's fixed cost
+  // (~1.5 us until its first stage lands) weighs more than in round 1, when 32-row tails were best --
+  // 9x12 MP job, two job lanes: 89.5 us with 32-row tails, 81.2 with 96, 80.4 with 128, 79.4 with 216
+  // (profiles/r2_sched_sweep.md); one job at a time is 90 us either way.
   // tuning knobs (profiles/microbench sweeps); clamped so that no value can push a unit outside its region
   static const double body_frac = [] { const char* e = std::getenv("STITCH_BODY_FRAC"); return e ? std::min(1.0, std::max(0.0, atof(e))) : 0.75; }();
-  static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? std::max(1, atoi(e)) : 32; }();
+  static const int tail_rows = [] { const char* e = std::getenv("STITCH_TAIL_ROWS"); return e ? std::max(1, atoi(e)) : 128; }();
   static const double up_body_frac = [] { const char* e = std::getenv("STITCH_UP_BODY_FRAC"); return e ? std::min(1.0, std::max(0.0, atof(e))) : 0.8; }();
   static const int up_tail_h = [] { const char* e = std::getenv("STITCH_UP_TAIL_H"); return e ? std::min(32, std::max(2, atoi(e) & ~1)) : UPSCALE_TAIL_H; }();
   const int max_src_rows = STREAM_TAB_MAX - 4 - STREAM_UNR;

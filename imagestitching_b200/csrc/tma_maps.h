@@ -24,6 +24,9 @@
 #define STREAM_TMA_STAGES 3   // stages per warp ring
 #endif
 #define STREAM_TMA_BOX_PX 128  // 32 lanes x 4 pixels
+#ifndef STREAM_TMA_EVICT_FIRST
+#define STREAM_TMA_EVICT_FIRST 0
+#endif
 
 namespace stitch {
 
