@@ -1,5 +1,8 @@
 """Layout parity (no GPU): golden vectors vs the Python restatement vs the C++ twin in libstitch.so.
 
+The golden vectors are outputs of the reference's own lines, executed by oracle/jsmini.py (oracle/gen_golden.py);
+tests/test_jsmini.py re-runs them where /root/reference exists.  This file needs only the committed JSON.
+
 Bar: bit-exact doubles for canvas size, scaleDown, superSample and every rect (BASELINE north_star).
 """
 import json
