@@ -52,8 +52,10 @@ struct DecImage {
 struct DecBatch {
   DecImage img[JDEC_MAX_IMAGES];
   int32_t n;
-  uint32_t* changed;          // device flag raised by the sync kernel
+  uint32_t* changed;          // device flags: a sync round raises changed[flag_cur] when a block's last end state moved
   int32_t round;              // sync round (0 = first)
+  int32_t flag_cur;           // flag this round raises
+  int32_t flag_prev;          // flag of the round before (-1: none, the host decides whether to launch)
 };
 
 // ---- Huffman tables in shared memory ----
@@ -328,7 +330,12 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_c
 // until no block's last end state moves any more.  In every iteration the subsequences that have to be decoded
 // again (their input state moved) are COMPACTED onto the first threads, so a few stragglers cost a few warps,
 // not the whole block.
+//
+// Rounds are enqueued back to back without a host round trip: round r raises changed[r], and round r + 1 returns at
+// once when changed[r] is still zero (the chains have converged: 2 rounds for photos), so a fixed number of launches
+// costs a few empty grids; the host looks at the LAST flag when the job is waited for.
 __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_constant__ DecBatch B) {
+  if (B.flag_prev >= 0 && B.changed[B.flag_prev] == 0u) return;   // grid-uniform: converged in an earlier round
   __shared__ SmemTables T;
   __shared__ uint2 sh_state[JDEC_THREADS + 1];   // [s + 1] = end state of subsequence s; [0] = predecessor block's last
   __shared__ uint32_t sh_cnt[JDEC_THREADS];      // blocks started by subsequence s
@@ -413,7 +420,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
     I.state[base + t] = make_uint4(st.x, st.y, sh_cnt[t], 0u);
   }
   // the LAST subsequence's end state feeds the next block: if it moved, another round is needed
-  if (t == 0 && (sh_last_moved || !settled) && base + n_here < (uint32_t)I.n_sub) atomicOr(B.changed, 1u);
+  if (t == 0 && (sh_last_moved || !settled) && base + n_here < (uint32_t)I.n_sub) atomicOr(&B.changed[B.flag_cur], 1u);
 }
 
 // D3: exclusive scan of the blocks-started counts (one block per image).

@@ -25,11 +25,28 @@
 #include "png_kernels.cuh"
 #include "synth.cuh"
 
+// A submitted job.  Jobs that decode files and / or export a file are DEFERRED: everything is enqueued without a host
+// round trip at submit, and what needs the host (was the entropy decoder's fixed number of synchronisation rounds
+// enough?  how long is the file?  copy it out) happens in finalize_job -- at stitch_wait, or when the job's lane is
+// needed again.
 struct PendingJob {
-  uint64_t ticket;
-  cudaEvent_t done;
-  int32_t n;
+  uint64_t ticket = 0;
+  cudaEvent_t done = nullptr;
+  int32_t n = 0;
+  int32_t lane = 0;
+  bool deferred = false, finalized = false;
+  int status = STITCH_OK;
+  std::string error;
+  StitchResult* res = nullptr;
+  bool dec = false, jpeg = false, png = false, out_host = true;
+  const uint8_t* j_file = nullptr;   // device file staging (host outputs)
+  const uint8_t* p_file = nullptr;
+  StitchJob job;                     // for the synchronous redo when the decoder needed more rounds
+  std::vector<StitchImage> images;
 };
+
+// words of a lane's pinned info block
+enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_WORDS = 8 };
 
 // One job lane: a stream with its own unit-scheduler counters and its own staging, so that jobs
 // submitted to different lanes overlap -- the next job's blocks fill the SM slots the draining one
@@ -47,7 +64,8 @@ struct Lane {
   // segment scratch, lengths / offsets / info, file staging for host outputs) and a pinned info word pair
   void* jpeg_arena = nullptr;
   size_t jpeg_arena_cap = 0;
-  uint64_t* jpeg_info_host = nullptr;
+  uint64_t* info_host = nullptr;   // pinned, INFO_WORDS words: file sizes / overflow flags / decoder convergence
+  uint64_t busy_ticket = 0;        // deferred job that still owns this lane's arenas and info block (0 = none)
   // JPEG decode: grow-only arena (scan bytes, tables, subsequence states, coefficients, component planes)
   void* dec_arena = nullptr;
   size_t dec_arena_cap = 0;
@@ -130,6 +148,14 @@ void make_placement(const StitchRect& r, int orientation, double ss, int bw, int
   if (!(p->W > 0) || !(p->H > 0)) p->x_hi = p->x_lo;  // empty
 }
 
+int ensure_info(StitchCtx* ctx, Lane& ln) {
+  if (!ln.info_host) {
+    CUDA_TRY(ctx, cudaMallocHost((void**)&ln.info_host, INFO_WORDS * sizeof(uint64_t)));
+    std::memset(ln.info_host, 0, INFO_WORDS * sizeof(uint64_t));
+  }
+  return STITCH_OK;
+}
+
 int ensure_stage(StitchCtx* ctx, Lane& ln, size_t idx, size_t bytes) {
   if (ln.in_stage.size() <= idx) {
     ln.in_stage.resize(idx + 1, nullptr);
@@ -155,7 +181,7 @@ void free_lane(Lane& ln) {
   if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
   if (ln.dec_arena) cudaFree(ln.dec_arena);
   if (ln.png_arena) cudaFree(ln.png_arena);
-  if (ln.jpeg_info_host) cudaFreeHost(ln.jpeg_info_host);
+  if (ln.info_host) cudaFreeHost(ln.info_host);
   stitch::free_scratch(ln.scratch);
   if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
   ln = Lane();
@@ -170,9 +196,13 @@ struct DecodeItem {
   int64_t pitch;
 };
 
-// GPU decode of up to 9 files in one batch of launches on the lane's stream (jpeg_decode.cuh).  Synchronises
-// the stream: the number of synchronisation rounds is data dependent.
-int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
+// GPU decode of up to 9 files in one batch of launches on the lane's stream (jpeg_decode.cuh).
+// deferred = false: synchronises the stream after every synchronisation round (their number is data dependent).
+// deferred = true: enqueues kDecRounds rounds -- a round whose predecessor changed nothing returns at once -- and
+// copies the last round's flag into the lane's info block; the caller checks it when the job is finalised and
+// decodes again synchronously if the chains had not converged (no such file seen yet: photos take 2 rounds).
+constexpr int kDecRounds = 6;
+int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferred) {
   namespace jd = stitch::jpegdec;
   if (n <= 0) return STITCH_OK;
   if (n > JDEC_MAX_IMAGES) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
@@ -226,7 +256,10 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
       return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG decode buffers allocation failed)");
     ln.dec_arena_cap = need;
   }
-  if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+  {
+    const int st = ensure_info(ctx, ln);
+    if (st != STITCH_OK) return st;
+  }
   uint8_t* A = (uint8_t*)ln.dec_arena;
   B.changed = (uint32_t*)A;
   for (int i = 0; i < n; ++i) {
@@ -248,15 +281,31 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n) {
   const dim3 gsub((max_sub + JDEC_THREADS - 1) / JDEC_THREADS, n);
   jd::jdec_first_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
   int launches = 1, rounds = 0;
-  for (;; ++rounds) {
-    if (rounds > 4096) return fail(ctx, STITCH_E_BAD_IMAGE, "JPEG entropy decoder did not synchronise");
-    CUDA_TRY(ctx, cudaMemsetAsync(B.changed, 0, 4, ln.stream));
-    B.round = rounds;
-    jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
-    ++launches;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, B.changed, 4, cudaMemcpyDeviceToHost, ln.stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-    if (*(volatile uint32_t*)ln.jpeg_info_host == 0) break;
+  if (deferred) {
+    CUDA_TRY(ctx, cudaMemsetAsync(B.changed, 0, 4 * kDecRounds, ln.stream));
+    for (; rounds < kDecRounds; ++rounds) {
+      B.round = rounds;
+      B.flag_cur = rounds;
+      B.flag_prev = rounds - 1;
+      jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+      ++launches;
+    }
+    ln.info_host[INFO_DEC_CHANGED] = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_DEC_CHANGED], B.changed + (kDecRounds - 1), 4, cudaMemcpyDeviceToHost, ln.stream));
+  } else {
+    for (;; ++rounds) {
+      if (rounds > 4096) return fail(ctx, STITCH_E_BAD_IMAGE, "JPEG entropy decoder did not synchronise");
+      CUDA_TRY(ctx, cudaMemsetAsync(B.changed, 0, 4, ln.stream));
+      B.round = rounds;
+      B.flag_cur = 0;
+      B.flag_prev = -1;
+      jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+      ++launches;
+      ln.info_host[INFO_DEC_CHANGED] = 0;
+      CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_DEC_CHANGED], B.changed, 4, cudaMemcpyDeviceToHost, ln.stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+      if (*(volatile uint32_t*)&ln.info_host[INFO_DEC_CHANGED] == 0) break;
+    }
   }
   jd::jdec_scan_kernel<<<n, 1024, 0, ln.stream>>>(B);
   jd::jdec_write_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
@@ -327,7 +376,10 @@ struct JpegExport {
         return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG work buffers allocation failed)");
       ln.jpeg_arena_cap = need;
     }
-    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+    {
+      const int st = ensure_info(ctx, ln);
+      if (st != STITCH_OK) return st;
+    }
     uint8_t* a = (uint8_t*)ln.jpeg_arena;
     if (!want_yuv) *d_yuv = a;
     a += b_yuv;
@@ -342,7 +394,7 @@ struct JpegExport {
     return STITCH_OK;
   }
 
-  int run(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, const JobParam& P, int cw, int ch) {
+  int run(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, const JobParam& P, int cw, int ch, bool deferred) {
     stitch::jpeg::Tables tab;
     stitch::jpeg::build_tables(jpeg_q, &tab);
     stitch::jpeg::HeaderBytes hdr;
@@ -363,12 +415,21 @@ struct JpegExport {
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->launches += 5;
     res->kernel_launches += 5;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, j_info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_JPEG_BYTES], j_info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    if (deferred) return STITCH_OK;   // finish() runs when the job is finalised
     CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-    res->jpeg_bytes = (int64_t)ln.jpeg_info_host[0];
-    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer too small; see jpeg_bytes)");
-    if (out_host)
-      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_jpeg, j_file, (size_t)res->jpeg_bytes, cudaMemcpyDeviceToHost, ln.stream));
+    return finish(ctx, ln, res, out_host, j_file, job->out_jpeg);
+  }
+
+  // The file size has reached the host: report it, and copy the file out of the lane's staging for host outputs.
+  static int finish(StitchCtx* ctx, Lane& ln, StitchResult* res, bool out_host, const uint8_t* j_file, void* out_jpeg) {
+    res->jpeg_bytes = (int64_t)ln.info_host[INFO_JPEG_BYTES];
+    if (ln.info_host[INFO_JPEG_OVERFLOW])
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG output buffer too small; see jpeg_bytes)");
+    if (out_host) {
+      CUDA_TRY(ctx, cudaMemcpyAsync(out_jpeg, j_file, (size_t)res->jpeg_bytes, cudaMemcpyDeviceToHost, ln.stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    }
     return STITCH_OK;
   }
 };
@@ -410,7 +471,10 @@ struct PngExport {
         return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG work buffers allocation failed)");
       ln.png_arena_cap = need;
     }
-    if (!ln.jpeg_info_host) CUDA_TRY(ctx, cudaMallocHost((void**)&ln.jpeg_info_host, 16));
+    {
+      const int st = ensure_info(ctx, ln);
+      if (st != STITCH_OK) return st;
+    }
     uint8_t* a = (uint8_t*)ln.png_arena;
     if (!want_rgba) { *d_rgba = a; *d_rgba_pitch = c_pitch; }
     a += b_canvas;
@@ -435,7 +499,7 @@ struct PngExport {
     return STITCH_OK;
   }
 
-  int run(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, int cw, int ch) {
+  int run(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, int cw, int ch, bool deferred) {
     stitch::png::HeaderBytes hdr;
     std::memset(&hdr, 0, sizeof hdr);
     const uint8_t sig[16] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A, 0, 0, 0, 13, 'I', 'H', 'D', 'R'};
@@ -480,17 +544,27 @@ struct PngExport {
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->launches += 4;
     res->kernel_launches += 4;
-    CUDA_TRY(ctx, cudaMemcpyAsync(ln.jpeg_info_host, PP.info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_PNG_BYTES], PP.info, 16, cudaMemcpyDeviceToHost, ln.stream));
+    if (deferred) return STITCH_OK;   // finish() runs when the job is finalised
     CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
-    res->png_bytes = (int64_t)ln.jpeg_info_host[0];
-    if (ln.jpeg_info_host[1]) return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG output buffer too small; see png_bytes)");
-    if (out_host)
-      CUDA_TRY(ctx, cudaMemcpyAsync(job->out_png, PP.file, (size_t)res->png_bytes, cudaMemcpyDeviceToHost, ln.stream));
+    return finish(ctx, ln, res, out_host, PP.file, job->out_png);
+  }
+
+  static int finish(StitchCtx* ctx, Lane& ln, StitchResult* res, bool out_host, const uint8_t* p_file, void* out_png) {
+    res->png_bytes = (int64_t)ln.info_host[INFO_PNG_BYTES];
+    if (ln.info_host[INFO_PNG_OVERFLOW])
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG output buffer too small; see png_bytes)");
+    if (out_host) {
+      CUDA_TRY(ctx, cudaMemcpyAsync(out_png, p_file, (size_t)res->png_bytes, cudaMemcpyDeviceToHost, ln.stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+    }
     return STITCH_OK;
   }
 };
 
-int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res) {
+// defer == nullptr: everything that needs the host is done here (stitch_run).  Otherwise nothing waits for the GPU
+// and *defer says what finalize_job still owes (stitch_submit).
+int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, PendingJob* defer) {
   if (!ctx || !job || !res) return fail(ctx, STITCH_E_BAD_ARG, "null argument");
   if (job->n <= 0) return fail(ctx, STITCH_E_EMPTY, "empty image list");  // P:1189
   if (!job->images) return fail(ctx, STITCH_E_BAD_ARG, "images == NULL");
@@ -503,14 +577,41 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   int32_t seq[2 * STITCH_MAX_IMAGES + 4];
   stitch_progress_sequence(n, seq, 2 * STITCH_MAX_IMAGES + 4);
 
-  // [1] per-image prepare check (P:1225-1249): here only the record normalisation survives.
+  // [1] per-image prepare check (P:1225-1249).  A record without natural dims is re-probed by the page
+  // (_prepareSingleImage -> getImageInfo, P:1227-1231, 724-734): for a FILE input the header is right here.
   StitchImageDesc descs[STITCH_MAX_IMAGES];
+  int bw[STITCH_MAX_IMAGES], bh[STITCH_MAX_IMAGES];
+  DecodeItem dec[STITCH_MAX_IMAGES];
+  int n_dec = 0;
+  int st = STITCH_OK;
   for (int i = 0; i < n; ++i) {
-    descs[i] = job->images[i].desc;
+    const StitchImage& im = job->images[i];
+    descs[i] = im.desc;
+    bw[i] = im.bmp_width;
+    bh[i] = im.bmp_height;
+    if (im.mem_kind == STITCH_MEM_HOST_JPEG) {
+      if (!im.data || im.pitch_bytes <= 0) {
+        char buf[64];
+        std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
+        return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+      }
+      DecodeItem& d = dec[n_dec++];
+      d.file = (const uint8_t*)im.data;
+      d.bytes = (size_t)im.pitch_bytes;
+      st = parse_jpeg(ctx, im.data, d.bytes, i, &d.hdr);
+      if (st != STITCH_OK) return st;
+      bw[i] = d.hdr.w;
+      bh[i] = d.hdr.h;
+      if (descs[i].natural_width <= 0 || descs[i].natural_height <= 0) {
+        descs[i].natural_width = descs[i].width = d.hdr.w;      // P:729-732
+        descs[i].natural_height = descs[i].height = d.hdr.h;
+      }
+      if (descs[i].file_size <= 0) descs[i].file_size = im.pitch_bytes;   // P:733
+    }
     emit(ctx, seq[1 + i]);
   }
   // [2] layout (P:1251-1386)
-  int st = stitch_layout(descs, n, &job->params, &res->layout);
+  st = stitch_layout(descs, n, &job->params, &res->layout);
   if (st != STITCH_OK) return fail(ctx, st, stitch_strerror(st));
   emit(ctx, 30);  // P:1358
   const StitchLayout& L = res->layout;
@@ -540,28 +641,9 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   }
 
   // bitmaps (P:1512-1514); a STITCH_MEM_HOST_JPEG image is a FILE the GPU decodes (loadImageFrom, U:27-121)
-  int bw[STITCH_MAX_IMAGES], bh[STITCH_MAX_IMAGES];
-  DecodeItem dec[STITCH_MAX_IMAGES];
-  int n_dec = 0;
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
-    bw[i] = im.bmp_width;
-    bh[i] = im.bmp_height;
-    if (im.mem_kind == STITCH_MEM_HOST_JPEG) {
-      if (!im.data || im.pitch_bytes <= 0) {
-        char buf[64];
-        std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
-        return fail(ctx, STITCH_E_BAD_IMAGE, buf);
-      }
-      DecodeItem& d = dec[n_dec++];
-      d.file = (const uint8_t*)im.data;
-      d.bytes = (size_t)im.pitch_bytes;
-      st = parse_jpeg(ctx, im.data, d.bytes, i, &d.hdr);
-      if (st != STITCH_OK) return st;
-      bw[i] = d.hdr.w;
-      bh[i] = d.hdr.h;
-      continue;
-    }
+    if (im.mem_kind == STITCH_MEM_HOST_JPEG) continue;   // parsed above
     if (!im.data || im.bmp_width <= 0 || im.bmp_height <= 0) {
       char buf[64];
       std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -613,8 +695,9 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     P.img[i].pitch = pitch;
     make_placement(L.rects[i], im.desc.orientation, ss, bw[i], bh[i], cw, ch, &P.img[i]);
   }
+  const bool deferred = defer != nullptr;
   if (n_dec > 0) {
-    st = decode_batch(ctx, ln, dec, n_dec);
+    st = decode_batch(ctx, ln, dec, n_dec, deferred);
     if (st != STITCH_OK) return st;
   }
 
@@ -687,16 +770,67 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       CUDA_TRY(ctx, cudaMemcpyAsync(job->out_yuv, d_yuv, (size_t)res->yuv_bytes, cudaMemcpyDeviceToHost, ln.stream));
   }
   // [5b] / [5c] export as a file (U:211-221): fileType 'jpg', or the 'png' the page asks for (P:1579).  The file
-  // size has to reach the host, so such a job is complete when this function returns (also under stitch_submit).
+  // size has to reach the host: here for stitch_run, in finalize_job for a submitted job.
   if (want_jpeg) {
-    st = jx.run(ctx, ln, job, res, P, cw, ch);
+    st = jx.run(ctx, ln, job, res, P, cw, ch, deferred);
     if (st != STITCH_OK) return st;
   }
   if (want_png) {
-    st = px.run(ctx, ln, job, res, cw, ch);
+    st = px.run(ctx, ln, job, res, cw, ch, deferred);
     if (st != STITCH_OK) return st;
   }
+  if (deferred && (n_dec > 0 || want_jpeg || want_png)) {
+    defer->deferred = true;
+    defer->dec = n_dec > 0;
+    defer->jpeg = want_jpeg;
+    defer->png = want_png;
+    defer->out_host = out_host;
+    defer->j_file = want_jpeg ? jx.j_file : nullptr;
+    defer->p_file = want_png ? px.PP.file : nullptr;
+    defer->job = *job;
+    defer->images.assign(job->images, job->images + n);
+  }
   return STITCH_OK;
+}
+
+// What a deferred job still needs from the host; leaves pj.status / pj.error set.  Frees the job's lane.
+void finalize_job(StitchCtx* ctx, PendingJob& pj) {
+  if (pj.finalized) return;
+  pj.finalized = true;
+  Lane& ln = ctx->lanes[pj.lane];
+  cudaError_t e = cudaEventSynchronize(pj.done);
+  cudaEventDestroy(pj.done);
+  pj.done = nullptr;
+  if (ln.busy_ticket == pj.ticket) ln.busy_ticket = 0;
+  if (e != cudaSuccess) {
+    pj.status = fail(ctx, STITCH_E_CUDA, std::string("event sync: ") + cudaGetErrorString(e));
+  } else if (pj.deferred) {
+    if (pj.dec && (uint32_t)ln.info_host[INFO_DEC_CHANGED] != 0u) {
+      // the entropy decoder's chains had not converged after kDecRounds rounds: decode with as many as it takes
+      pj.job.images = pj.images.data();
+      StitchProgressFn keep = ctx->progress;
+      ctx->progress = nullptr;   // the values were emitted at submit
+      pj.status = enqueue_job(ctx, ln, &pj.job, pj.res, nullptr);
+      ctx->progress = keep;
+      if (pj.status == STITCH_OK && cudaStreamSynchronize(ln.stream) != cudaSuccess) pj.status = fail(ctx, STITCH_E_CUDA, "stream sync");
+    } else {
+      if (pj.jpeg) pj.status = JpegExport::finish(ctx, ln, pj.res, pj.out_host, pj.j_file, pj.job.out_jpeg);
+      if (pj.png && pj.status == STITCH_OK) pj.status = PngExport::finish(ctx, ln, pj.res, pj.out_host, pj.p_file, pj.job.out_png);
+    }
+  }
+  if (pj.status != STITCH_OK) pj.error = ctx->last_error;
+  if (pj.status == STITCH_OK) {
+    emit(ctx, 96);   // P:1581
+    emit(ctx, 100);  // P:1611
+  }
+}
+
+// A lane's arenas and info block belong to its unfinalised deferred job: finish that one before the lane is reused.
+void drain_lane(StitchCtx* ctx, Lane& ln) {
+  if (!ln.busy_ticket) return;
+  for (PendingJob& pj : ctx->pending)
+    if (pj.ticket == ln.busy_ticket) { finalize_job(ctx, pj); break; }
+  ln.busy_ticket = 0;
 }
 
 }  // namespace
@@ -731,7 +865,8 @@ extern "C" int stitch_ctx_destroy(StitchCtx* ctx) {
   cudaSetDevice(ctx->device);
   for (Lane& ln : ctx->lanes)
     if (ln.stream) cudaStreamSynchronize(ln.stream);
-  for (auto& p : ctx->pending) cudaEventDestroy(p.done);
+  for (auto& p : ctx->pending)
+    if (p.done) cudaEventDestroy(p.done);
   for (Lane& ln : ctx->lanes) free_lane(ln);
   delete ctx;
   return STITCH_OK;
@@ -780,7 +915,8 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
   if (!ctx) return STITCH_E_BAD_ARG;
   if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "stitch already in progress");  // P:772,781
   ctx->busy = true;
-  int st = enqueue_job(ctx, ctx->lanes[0], job, result);
+  drain_lane(ctx, ctx->lanes[0]);
+  int st = enqueue_job(ctx, ctx->lanes[0], job, result, nullptr);
   if (st == STITCH_OK) {
     cudaError_t e = cudaStreamSynchronize(ctx->lanes[0].stream);
     if (e != cudaSuccess) st = fail(ctx, STITCH_E_CUDA, std::string("stream sync: ") + cudaGetErrorString(e));
@@ -815,6 +951,7 @@ extern "C" int stitch_preview(StitchCtx* ctx, const void* src, int32_t src_mem_k
     return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (preview output buffer missing or too small)");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   Lane& ln = ctx->lanes[0];
+  drain_lane(ctx, ln);
 
   JobParam P;
   std::memset(&P, 0, sizeof P);
@@ -879,6 +1016,7 @@ extern "C" int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes
   if (!file) return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   Lane& ln = ctx->lanes[0];
+  drain_lane(ctx, ln);
   DecodeItem d;
   d.file = (const uint8_t*)file;
   d.bytes = bytes;
@@ -904,7 +1042,7 @@ extern "C" int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes
     d.rgba = (uint8_t*)out_rgba;
     d.pitch = pitch;
   }
-  st = decode_batch(ctx, ln, &d, 1);
+  st = decode_batch(ctx, ln, &d, 1, false);
   if (st != STITCH_OK) return st;
   if (out_host)
     CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
@@ -914,32 +1052,40 @@ extern "C" int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes
 
 extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {
   if (!ctx || !ticket) return STITCH_E_BAD_ARG;
-  Lane& ln = ctx->lanes[ctx->next_ticket % ctx->lanes.size()];  // jobs rotate over the lanes
-  int st = enqueue_job(ctx, ln, job, result);
-  if (st != STITCH_OK) return st;
+  const size_t li = ctx->next_ticket % ctx->lanes.size();   // jobs rotate over the lanes
+  Lane& ln = ctx->lanes[li];
+  drain_lane(ctx, ln);
   PendingJob pj;
+  int st = enqueue_job(ctx, ln, job, result, &pj);
+  if (st != STITCH_OK) return st;
   pj.ticket = ctx->next_ticket++;
   pj.n = job->n;
+  pj.lane = (int32_t)li;
+  pj.res = result;
   CUDA_TRY(ctx, cudaEventCreateWithFlags(&pj.done, cudaEventDisableTiming));
   CUDA_TRY(ctx, cudaEventRecord(pj.done, ln.stream));
-  ctx->pending.push_back(pj);
-  *ticket = pj.ticket;
+  if (pj.deferred) ln.busy_ticket = pj.ticket;
+  ctx->pending.push_back(std::move(pj));
+  *ticket = ctx->pending.back().ticket;
   return STITCH_OK;
 }
 
 extern "C" int stitch_wait(StitchCtx* ctx, uint64_t ticket) {
   if (!ctx) return STITCH_E_BAD_ARG;
-  // waiting for ticket T retires every earlier one too (tickets of one lane complete in order)
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  // waiting for ticket T retires every earlier one too (tickets of one lane complete in order); the first failure
+  // among them is what the call reports
+  int st = STITCH_OK;
   while (!ctx->pending.empty() && ctx->pending.front().ticket <= ticket) {
-    PendingJob pj = ctx->pending.front();
+    finalize_job(ctx, ctx->pending.front());
+    PendingJob& pj = ctx->pending.front();
+    if (st == STITCH_OK && pj.status != STITCH_OK) {
+      st = pj.status;
+      ctx->last_error = pj.error;
+    }
     ctx->pending.pop_front();
-    cudaError_t e = cudaEventSynchronize(pj.done);
-    cudaEventDestroy(pj.done);
-    if (e != cudaSuccess) return fail(ctx, STITCH_E_CUDA, std::string("event sync: ") + cudaGetErrorString(e));
-    emit(ctx, 96);
-    emit(ctx, 100);
   }
-  return STITCH_OK;
+  return st;
 }
 
 extern "C" int stitch_host_alloc(size_t bytes, void** out) {

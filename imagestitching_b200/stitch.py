@@ -338,19 +338,18 @@ class StitchContext:
         job.jpeg_restart_interval = jpeg_restart_interval
         return job, (arr, keep)
 
-    def run(self, images: Sequence[Dict[str, Any]], direction: str, *, mode: Optional[str] = "min", gap=0,
-            platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
-            deviceMaxCanvasPixels: Optional[int] = None, output: str = "rgba",
-            on_progress: Optional[Callable[[int], None]] = None, jpeg_quality: int = 0,
-            jpeg_restart_interval: int = 0, jpeg_capacity: int = 0, png_capacity: int = 0) -> Optional[StitchOutput]:
-        """Synchronous stitch with host outputs (numpy).  Returns None for an empty list (index.js:1189).
-        `output`: "rgba" | "yuv420" | "both", optionally "+jpeg", or "jpeg" alone (the exported file)."""
+    def _prepare(self, images, direction, mode, gap, platform, deviceMaxCanvasSize, deviceMaxCanvasPixels, output,
+                 jpeg_quality, jpeg_restart_interval, jpeg_capacity, png_capacity):
+        """Layout twin -> host output buffers -> StitchJob.  Everything a job needs to stay alive is in the returned dict."""
         lib = self.lib
-        if not images:
-            return None
         profile = _profile_struct(platform, deviceMaxCanvasSize, deviceMaxCanvasPixels)
-        # size the host output from the layout twin
         descs = (L.StitchImageDesc * len(images))(*[_desc(i) for i in images])
+        for d, img in zip(descs, images):   # a FILE without a prepared record: the library reads its header (P:1227-1231)
+            if img.get("file") is not None and not (d.natural_width and d.natural_height):
+                info = get_image_info(img["file"] if isinstance(img["file"], bytes) else bytes(img["file"]))
+                d.natural_width = d.width = info["width"]
+                d.natural_height = d.height = info["height"]
+                d.file_size = d.file_size or len(img["file"])
         prm = _params(direction, mode, gap, profile)
         lay = L.StitchLayout()
         st = lib.stitch_layout(descs, len(images), C.byref(prm), C.byref(lay))
@@ -374,7 +373,45 @@ class StitchContext:
                                    jpeg_quality, jpeg_restart_interval)
         if png is not None:
             job.out_png, job.out_capacity_png = png.ctypes.data, png.nbytes
-        progress: List[int] = []
+        return {"job": job, "keep": keep, "res": L.StitchResult(), "cw": cw, "ch": ch, "rgba": rgba, "yuv": yuv, "jpg": jpg,
+                "png": png, "progress": []}
+
+    def _collect(self, pj, st) -> StitchOutput:
+        res, cw, ch = pj["res"], pj["cw"], pj["ch"]
+        if st != L.OK:
+            if st == L.E_NO_SURFACE and res.jpeg_bytes:
+                raise StitchError(st, f"JPEG output buffer too small: {res.jpeg_bytes} bytes needed")
+            if st == L.E_NO_SURFACE and res.png_bytes:
+                raise StitchError(st, f"PNG output buffer too small: {res.png_bytes} bytes needed")
+            _raise(st, self.handle)
+        out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, path_info=res.path_info,
+                           progress=pj["progress"])
+        out.rgba = pj["rgba"]
+        if pj["jpg"] is not None:
+            out.jpeg = pj["jpg"][: res.jpeg_bytes].tobytes()
+        if pj["png"] is not None:
+            out.png = pj["png"][: res.png_bytes].tobytes()
+        yuv = pj["yuv"]
+        if yuv is not None:
+            cwh, chh = (cw + 1) // 2, (ch + 1) // 2
+            out.y = yuv[: cw * ch].reshape(ch, cw)
+            out.cb = yuv[cw * ch: cw * ch + cwh * chh].reshape(chh, cwh)
+            out.cr = yuv[cw * ch + cwh * chh:].reshape(chh, cwh)
+        return out
+
+    def run(self, images: Sequence[Dict[str, Any]], direction: str, *, mode: Optional[str] = "min", gap=0,
+            platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
+            deviceMaxCanvasPixels: Optional[int] = None, output: str = "rgba",
+            on_progress: Optional[Callable[[int], None]] = None, jpeg_quality: int = 0,
+            jpeg_restart_interval: int = 0, jpeg_capacity: int = 0, png_capacity: int = 0) -> Optional[StitchOutput]:
+        """Synchronous stitch with host outputs (numpy).  Returns None for an empty list (index.js:1189).
+        `output`: "rgba" | "yuv420" | "both", optionally "+jpeg" / "+png", or "jpeg" / "png" alone (the exported file)."""
+        lib = self.lib
+        if not images:
+            return None
+        pj = self._prepare(images, direction, mode, gap, platform, deviceMaxCanvasSize, deviceMaxCanvasPixels, output,
+                           jpeg_quality, jpeg_restart_interval, jpeg_capacity, png_capacity)
+        progress = pj["progress"]
 
         def _cb(_user, pct):
             progress.append(int(pct))
@@ -383,29 +420,30 @@ class StitchContext:
 
         cb = L.PROGRESS_FN(_cb)
         lib.stitch_set_progress_cb(self.handle, cb, None)
-        res = L.StitchResult()
         try:
-            st = lib.stitch_run(self.handle, C.byref(job), C.byref(res))
+            st = lib.stitch_run(self.handle, C.byref(pj["job"]), C.byref(pj["res"]))
         finally:
             lib.stitch_set_progress_cb(self.handle, C.cast(None, L.PROGRESS_FN), None)
+        return self._collect(pj, st)
+
+    def submit(self, images: Sequence[Dict[str, Any]], direction: str, *, mode: Optional[str] = "min", gap=0,
+               platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None, deviceMaxCanvasPixels: Optional[int] = None,
+               output: str = "rgba", jpeg_quality: int = 0, jpeg_restart_interval: int = 0, jpeg_capacity: int = 0,
+               png_capacity: int = 0):
+        """Asynchronous stitch (stitch_submit): the job is enqueued on the next lane and the call returns without waiting
+        for the GPU -- also for file inputs and file outputs.  Pass the returned handle to wait()."""
+        pj = self._prepare(images, direction, mode, gap, platform, deviceMaxCanvasSize, deviceMaxCanvasPixels, output,
+                           jpeg_quality, jpeg_restart_interval, jpeg_capacity, png_capacity)
+        ticket = C.c_uint64(0)
+        st = self.lib.stitch_submit(self.handle, C.byref(pj["job"]), C.byref(pj["res"]), C.byref(ticket))
         if st != L.OK:
-            if st == L.E_NO_SURFACE and res.jpeg_bytes:
-                raise StitchError(st, f"JPEG output buffer too small: {res.jpeg_bytes} bytes needed")
-            if st == L.E_NO_SURFACE and res.png_bytes:
-                raise StitchError(st, f"PNG output buffer too small: {res.png_bytes} bytes needed")
-            _raise(st, self.handle)
-        out = StitchOutput(cw, ch, _layout_dict(res.layout), kernel_launches=res.kernel_launches, path_info=res.path_info, progress=progress)
-        out.rgba = rgba
-        if jpg is not None:
-            out.jpeg = jpg[: res.jpeg_bytes].tobytes()
-        if png is not None:
-            out.png = png[: res.png_bytes].tobytes()
-        if yuv is not None:
-            cwh, chh = (cw + 1) // 2, (ch + 1) // 2
-            out.y = yuv[: cw * ch].reshape(ch, cw)
-            out.cb = yuv[cw * ch: cw * ch + cwh * chh].reshape(chh, cwh)
-            out.cr = yuv[cw * ch + cwh * chh:].reshape(chh, cwh)
-        return out
+            self._collect(pj, st)
+        pj["ticket"] = ticket.value
+        return pj
+
+    def wait(self, pj) -> StitchOutput:
+        """Completes a submitted job (and every job submitted before it) and returns its outputs."""
+        return self._collect(pj, self.lib.stitch_wait(self.handle, pj["ticket"]))
 
 
 _default_ctx: Dict[int, StitchContext] = {}
