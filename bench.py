@@ -197,6 +197,40 @@ def cpu_reference_run(workload: str, steps: int, warmup: int, threads: int | Non
     return mp * steps / dt, dt / steps * 1e3, cores, mp
 
 
+def cpu_files_run(files, direction, mode, platform, steps: int, out_kind: str = "png"):
+    """The file-in / file-out job on the host cores: oracle JPEG decoder (one thread per file), C raster (OpenMP),
+    oracle PNG / JPEG writer (sequential).  Returns (MP/s, ms per job, cores)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import jpeg_c as JC
+    from oracle import layout_ref as LR
+    from oracle import png_c as PC
+    from oracle import raster_c as RC
+    from tests import util as U
+
+    cores = len(os.sched_getaffinity(0)) or os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    pool = ThreadPoolExecutor(max_workers=min(cores, len(files)))
+
+    def one():
+        bitmaps = list(pool.map(JC.decode, files))            # ctypes releases the GIL
+        dims = [(b.shape[1], b.shape[0]) for b in bitmaps]
+        lay = LR.compute_layout(U.recs(dims), direction, mode, 0, U.profile_of(platform))
+        out = RC.render(lay, bitmaps, [1] * len(dims), want_rgba=out_kind == "png", want_yuv=out_kind == "jpeg", precision="f32")
+        if out_kind == "png":
+            return lay, len(PC.encode_rgba(out["rgba"]))
+        return lay, len(JC.encode_i420(out["y"], out["cb"], out["cr"], 90, 8))
+
+    lay, _ = one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = (time.perf_counter() - t0) / steps
+    pool.shutdown()
+    mp = lay.canvasW * lay.canvasH / 1e6
+    return mp / dt, dt * 1e3, cores
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -213,6 +247,9 @@ def main():
     ap.add_argument("--lanes", type=int, default=2,
                     help="job lanes of the StitchCtx the device-resident steps rotate over (1 = one job at a time)")
     ap.add_argument("--e2e-lanes", type=int, default=3, help="job lanes for the host-buffer (e2e) steps")
+    ap.add_argument("--files-steps", type=int, default=-1,
+                    help="e2e_files leg (JPEG files in host memory -> exported file in host memory): jobs per output kind; "
+                         "-1 = auto (24 for cfg2 / cfg5, 0 = skip for the other workloads)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -434,6 +471,89 @@ def main():
         e2e_s = float(t.item())
     e2e_value = mp * e2e_steps * world / e2e_s
 
+    # ---- end to end from FILES: 9 JPEG files in (pinned) host memory -> decode + stitch + encode on the GPU -> the
+    # exported file in host memory (what the page does between P:1441 and P:1581).  Uploads 14x fewer bytes than e2e.
+    files_steps = args.files_steps if args.files_steps >= 0 else (24 if args.workload in ("cfg2", "cfg5") else 0)
+    e2e_files = None
+    file_bytes_list = []
+    if files_steps > 0:
+        lib.stitch_wait(ctx.handle, last)
+        ctx.set_lanes(1)
+        fbufs = []
+        for i, (w, h) in enumerate(dims):   # the input files: each bitmap of slot 0 exported at its own size, quality 90
+            o = ctx.run([slots[0][0][i]], "vertical", platform="other", deviceMaxCanvasSize=max(w, h),
+                        deviceMaxCanvasPixels=w * h, output="jpeg", jpeg_quality=90)
+            assert (o.width, o.height) == (w, h), (o.width, o.height, w, h)
+            file_bytes_list.append(o.jpeg)
+            pf = C.c_void_p()
+            assert lib.stitch_host_alloc(len(o.jpeg), C.byref(pf)) == 0
+            C.memmove(pf, o.jpeg, len(o.jpeg))
+            fbufs.append((pf, len(o.jpeg)))
+            host_outs.append(pf)
+        in_bytes = sum(b for _, b in fbufs)
+        ctx.set_lanes(e2e_lanes)
+        e2e_files = {"unit": "MP/s", "steps": files_steps, "h2d_bytes_per_step": in_bytes, "lanes": e2e_lanes,
+                     "inputs": f"{len(dims)} baseline JPEG files, quality 90, 4:2:0 ({in_bytes / 1e6:.1f} MB), pinned host memory"}
+        for kind, flag in (("png", L.OUT_PNG), ("jpeg", L.OUT_JPEG)):
+            cap = rgba_bytes + (rgba_bytes >> 2) if kind == "png" else (64 << 20)
+            fjobs = []
+            for _ in range(e2e_lanes):
+                arr = (L.StitchImage * len(dims))()
+                for i, (w, h) in enumerate(dims):
+                    arr[i].desc.natural_width, arr[i].desc.natural_height = w, h
+                    arr[i].desc.width, arr[i].desc.height = w, h
+                    arr[i].desc.orientation = 1
+                    arr[i].desc.file_size = fbufs[i][1]
+                    arr[i].data = fbufs[i][0]
+                    arr[i].pitch_bytes = fbufs[i][1]
+                    arr[i].mem_kind = L.MEM_HOST_JPEG
+                po = C.c_void_p()
+                assert lib.stitch_host_alloc(cap, C.byref(po)) == 0
+                host_outs.append(po)
+                fj = L.StitchJob()
+                fj.images, fj.n = arr, len(dims)
+                fj.params = hjobs[0][0].params
+                fj.output_flags = flag
+                fj.out_mem_kind = L.MEM_HOST
+                if kind == "png":
+                    fj.out_png, fj.out_capacity_png = po.value, cap
+                else:
+                    fj.out_jpeg, fj.out_capacity_jpeg, fj.jpeg_quality = po.value, cap, 90
+                fjobs.append((fj, arr, L.StitchResult()))
+
+            def files_loop(nsteps):
+                tickets = []
+                for i in range(nsteps):
+                    fj, _, fr = fjobs[i % e2e_lanes]
+                    t = C.c_uint64()
+                    st = lib.stitch_submit(ctx.handle, C.byref(fj), C.byref(fr), C.byref(t))
+                    assert st == 0, lib.stitch_last_error(ctx.handle)
+                    tickets.append(t.value)
+                    if i >= e2e_lanes - 1:
+                        assert lib.stitch_wait(ctx.handle, tickets[i - (e2e_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
+                assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0, lib.stitch_last_error(ctx.handle)
+
+            files_loop(2 * e2e_lanes)
+            torch.cuda.synchronize()
+            barrier()
+            t0 = time.perf_counter()
+            files_loop(files_steps)
+            torch.cuda.synchronize()
+            fs = time.perf_counter() - t0
+            t1 = time.perf_counter()
+            for _ in range(3):
+                assert lib.stitch_run(ctx.handle, C.byref(fjobs[0][0]), C.byref(fjobs[0][2])) == 0
+            single_ms = (time.perf_counter() - t1) / 3 * 1e3
+            if world > 1:
+                t = torch.tensor([fs], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                fs = float(t.item())
+            fr = fjobs[0][2]
+            fbytes = int(fr.png_bytes if kind == "png" else fr.jpeg_bytes)
+            e2e_files[kind] = {"value": mp * files_steps * world / fs, "ms_per_step": fs / files_steps * 1e3,
+                               "d2h_bytes_per_step": fbytes, "single_job_latency_ms": single_ms}
+        e2e_files["value"] = e2e_files["png"]["value"]   # the page exports PNG (P:1579)
+
     if has_jpeg or has_png:
         out_bytes = int(hres.jpeg_bytes if has_jpeg else hres.png_bytes)   # d2h of the e2e step = the file
         algo_bytes = src_bytes + out_bytes
@@ -460,6 +580,8 @@ def main():
                      "frac_of_8TBps_nominal": achieved / 8000.0,
                      "launches_per_step": launches / max(1, args.steps)},
     }
+    if e2e_files is not None:
+        line["e2e_files"] = e2e_files
     prof_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof_path):
         try:
@@ -474,6 +596,14 @@ def main():
                                     "sample": f"{max(1, args.cpu_steps)} full job(s), C restatement fp32 + OpenMP ({ms:.0f} ms/job)"}
         except Exception as e:  # the baseline is a report, never a blocker
             line["cpu_baseline"] = {"value": None, "unit": "MP/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
+        if e2e_files is not None:
+            try:
+                v, ms, cores = cpu_files_run(file_bytes_list, direction, mode, platform, 1, "png")
+                e2e_files["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "ms_per_step": ms,
+                                             "sample": "1 job: oracle JPEG decoder (a thread per file) + C raster (OpenMP) + "
+                                                       "oracle PNG writer (sequential)"}
+            except Exception as e:
+                e2e_files["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
     if rank == 0:
         print(json.dumps(line))
     for p in host_keep + host_outs:
