@@ -109,6 +109,17 @@ SIGNATURES = {
     "stitch_memcpy_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "stitch_memcpy_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "stitch_generate_image": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_uint64, C.c_int32]),
+    "stitch_device_digest": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]),
+    "stitch_pool_create": (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "stitch_pool_destroy": (C.c_int, [C.c_void_p]),
+    "stitch_pool_device_count": (C.c_int32, [C.c_void_p]),
+    "stitch_pool_ctx": (C.c_void_p, [C.c_void_p, C.c_int32]),
+    "stitch_pool_submit": (C.c_int, [C.c_void_p, C.POINTER(StitchJob), C.POINTER(StitchResult), C.c_int32, C.POINTER(C.c_uint64)]),
+    "stitch_pool_digest": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "stitch_pool_wait": (C.c_int, [C.c_void_p, C.c_uint64, C.POINTER(C.c_int32)]),
+    "stitch_pool_wait_all": (C.c_int, [C.c_void_p]),
+    "stitch_pool_jobs_run": (C.c_int64, [C.c_void_p, C.c_int32]),
+    "stitch_pool_last_error": (C.c_char_p, [C.c_void_p]),
     "stitch_strerror": (C.c_char_p, [C.c_int]),
     "stitch_last_error": (C.c_char_p, [C.c_void_p]),
     "stitch_abi_version": (C.c_int, []),

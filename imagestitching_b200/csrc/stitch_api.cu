@@ -1130,5 +1130,28 @@ extern "C" int stitch_generate_image(StitchCtx* ctx, void* dev_dst, int32_t widt
   return STITCH_OK;
 }
 
+extern "C" int stitch_device_digest(StitchCtx* ctx, const void* dev_ptr, size_t bytes, uint64_t* out) {
+  if (!ctx || !dev_ptr || !out) return STITCH_E_BAD_ARG;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Lane& ln = ctx->lanes[0];
+  drain_lane(ctx, ln);
+  int st = ensure_info(ctx, ln);
+  if (st != STITCH_OK) return st;
+  if (!ln.scratch.p) {   // same 256-byte block as the unit scheduler counters: words 0-1 are the scheduler's, word 8.. ours
+    CUDA_TRY(ctx, cudaMalloc(&ln.scratch.p, 256));
+    ln.scratch.cap = 256;
+    CUDA_TRY(ctx, cudaMemsetAsync(ln.scratch.p, 0, 256, ln.stream));
+  }
+  unsigned long long* acc = (unsigned long long*)((uint8_t*)ln.scratch.p + 64);
+  CUDA_TRY(ctx, cudaMemsetAsync(acc, 0, 8, ln.stream));
+  stitch::digest_kernel<<<ctx->sm_count * 4, 256, 0, ln.stream>>>((const uint8_t*)dev_ptr, bytes, acc);
+  CUDA_TRY(ctx, cudaGetLastError());
+  ctx->launches += 1;
+  CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_WORDS - 1], acc, 8, cudaMemcpyDeviceToHost, ln.stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+  *out = ln.info_host[INFO_WORDS - 1];
+  return STITCH_OK;
+}
+
 extern "C" const char* stitch_last_error(StitchCtx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
 extern "C" int64_t stitch_kernel_launch_count(StitchCtx* ctx) { return ctx ? ctx->launches : 0; }

@@ -62,4 +62,34 @@ inline cudaError_t launch_generate(uint8_t* dst, int width, int height, int64_t 
   return cudaGetLastError();
 }
 
+// 64-bit digest of a device buffer: sum over its bytes' 32-bit words of splitmix64(word ^ position * K) -- order
+// independent, so any grid computes it; tests and the batch sweep compare digests of canvases produced on different
+// GPUs instead of copying 89 MB per job back.  CPU twin: tests/util.py::digest.
+__device__ __forceinline__ uint64_t digest_mix(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__global__ void __launch_bounds__(256) digest_kernel(const uint8_t* __restrict__ p, size_t bytes, unsigned long long* out) {
+  const size_t nw = bytes >> 2;
+  uint64_t acc = 0;
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(p);
+  const bool aligned = (reinterpret_cast<uintptr_t>(p) & 3) == 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nw; i += (size_t)gridDim.x * blockDim.x) {
+    uint32_t v;
+    if (aligned) v = w[i];
+    else v = p[4 * i] | (p[4 * i + 1] << 8) | (p[4 * i + 2] << 16) | ((uint32_t)p[4 * i + 3] << 24);
+    acc += digest_mix((uint64_t)v ^ ((uint64_t)i * 0xD6E8FEB86659FD93ull));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    uint32_t v = 0;
+    for (size_t k = nw * 4; k < bytes; ++k) v |= (uint32_t)p[k] << (8 * (k & 3));
+    acc += digest_mix((uint64_t)v ^ ((uint64_t)nw * 0xD6E8FEB86659FD93ull) ^ ((uint64_t)bytes << 32));
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, d);
+  if ((threadIdx.x & 31) == 0) atomicAdd(out, (unsigned long long)acc);
+}
+
 }  // namespace stitch

@@ -66,6 +66,7 @@ class StitchOutput:
     kernel_launches: int = 0
     path_info: int = 0
     progress: List[int] = field(default_factory=list)
+    device: int = -1               # StitchPool: index of the worker / GPU that ran the job
 
 
 def _output_flags(output: str) -> int:
@@ -444,6 +445,68 @@ class StitchContext:
     def wait(self, pj) -> StitchOutput:
         """Completes a submitted job (and every job submitted before it) and returns its outputs."""
         return self._collect(pj, self.lib.stitch_wait(self.handle, pj["ticket"]))
+
+
+class StitchPool:
+    """Every GPU of the box from one process (include/stitch.h: stitch_pool_*): one worker thread + ctx per GPU, a
+    shared job queue, no collective.  Jobs with host buffers go to whichever GPU has a free lane."""
+
+    def __init__(self, devices: Optional[Sequence[int]] = None, lanes_per_device: int = 2):
+        self.lib = L.load()
+        h = C.c_void_p()
+        arr = (C.c_int32 * len(devices))(*devices) if devices else None
+        st = self.lib.stitch_pool_create(arr, len(devices) if devices else 0, lanes_per_device, C.byref(h))
+        if st != L.OK:
+            _raise(st)
+        self.handle = h
+        self._jobs: Dict[int, Any] = {}
+        self._helper = StitchContext.__new__(StitchContext)   # build_job / _prepare / _collect need only .lib
+        self._helper.lib = self.lib
+        self._helper.handle = None
+
+    @property
+    def device_count(self) -> int:
+        return int(self.lib.stitch_pool_device_count(self.handle))
+
+    def ctx_handle(self, index: int):
+        return self.lib.stitch_pool_ctx(self.handle, index)
+
+    def jobs_run(self, index: int) -> int:
+        return int(self.lib.stitch_pool_jobs_run(self.handle, index))
+
+    def submit(self, images: Sequence[Dict[str, Any]], direction: str, *, device: int = -1, mode: Optional[str] = "min",
+               gap=0, platform: str = "ios", deviceMaxCanvasSize: Optional[int] = None,
+               deviceMaxCanvasPixels: Optional[int] = None, output: str = "rgba", jpeg_quality: int = 0,
+               jpeg_restart_interval: int = 0, jpeg_capacity: int = 0, png_capacity: int = 0):
+        pj = self._helper._prepare(images, direction, mode, gap, platform, deviceMaxCanvasSize, deviceMaxCanvasPixels,
+                                   output, jpeg_quality, jpeg_restart_interval, jpeg_capacity, png_capacity)
+        t = C.c_uint64(0)
+        st = self.lib.stitch_pool_submit(self.handle, C.byref(pj["job"]), C.byref(pj["res"]), device, C.byref(t))
+        if st != L.OK:
+            _raise(st)
+        pj["ticket"] = t.value
+        return pj
+
+    def wait(self, pj) -> StitchOutput:
+        dev = C.c_int32(-1)
+        st = self.lib.stitch_pool_wait(self.handle, pj["ticket"], C.byref(dev))
+        if st != L.OK:
+            msg = self.lib.stitch_pool_last_error(self.handle)
+            raise StitchError(st, (msg or b"").decode("utf-8", "replace") or self.lib.stitch_strerror(st).decode())
+        out = self._helper._collect(pj, st)
+        out.device = int(dev.value)
+        return out
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.stitch_pool_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 _default_ctx: Dict[int, StitchContext] = {}

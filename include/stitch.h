@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 5
+#define STITCH_ABI_VERSION 6
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -187,10 +187,13 @@ int64_t stitch_png_capacity(const StitchLayout* layout);
 /* Synchronous onStitch(): layout -> draw all images -> export into the caller's buffer. (P:1186-1633) */
 int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* result);
 
-/* Asynchronous form for job-level sharding: enqueue on the next lane, wait later.
- * Buffers must stay valid until stitch_wait(ticket) returns.  Jobs with STITCH_MEM_HOST_JPEG inputs or
- * STITCH_OUT_JPEG / STITCH_OUT_PNG outputs need host round trips (synchronisation rounds, file sizes) and are
- * complete when stitch_submit returns; stitch_wait is then a no-op for them. */
+/* Asynchronous form for job-level sharding: enqueue on the next lane, wait later.  Nothing in stitch_submit waits
+ * for the GPU -- also for STITCH_MEM_HOST_JPEG inputs (the entropy decoder runs a fixed number of synchronisation
+ * rounds gated on a device flag) and STITCH_OUT_JPEG / STITCH_OUT_PNG outputs (the file size is fetched, and a host
+ * file copied out, when the job is waited for -- or when its lane is needed by a later submit).
+ * Buffers AND *result must stay valid until stitch_wait(ticket) returns; result->jpeg_bytes / png_bytes and the
+ * "output buffer too small" error of a file job are delivered by stitch_wait, which returns the first failure among
+ * the jobs it retires (every job submitted before `ticket`). */
 int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket);
 int stitch_wait(StitchCtx* ctx, uint64_t ticket);
 
@@ -258,6 +261,34 @@ int stitch_memcpy_d2h(StitchCtx* ctx, void* dst, const void* src, size_t bytes);
 /* On-device synthetic bitmap generator (test/bench helper K0). */
 int stitch_generate_image(StitchCtx* ctx, void* dev_dst, int32_t width, int32_t height, int64_t pitch_bytes,
                           uint64_t seed, int32_t pattern);
+
+/* 64-bit digest of `bytes` bytes of device memory (order-independent sum of mixed 32-bit words): lets a batch sweep or a
+ * multi-GPU test compare canvases without copying them back.  Synchronous, lane 0. */
+int stitch_device_digest(StitchCtx* ctx, const void* dev_ptr, size_t bytes, uint64_t* out);
+
+/* ---- every GPU of a box from one process (north star: "independent stitch jobs are sharded across the 8 GPUs of one
+ * box with no NCCL") ----
+ * One host thread + one StitchCtx (with `lanes_per_device` job lanes) per GPU and a shared job queue: a worker takes the
+ * next job when one of its lanes is free, so uneven jobs balance themselves.  No collective, no peer
+ * access.  devices == NULL or n_devices <= 0: all GPUs.  A device may be listed more than once (one worker each).
+ * stitch_pool_submit copies the job descriptor and its image array; pixel buffers and *result must stay valid until the
+ * job has been waited for.  `device` = index into the pool's device list of the GPU that MUST run the job (its bitmaps or
+ * outputs are STITCH_MEM_DEVICE memory there), or -1: any GPU (host buffers only, else STITCH_E_BAD_ARG).
+ * stitch_pool_wait returns the job's status (text: stitch_pool_last_error) and which worker ran it.  Thread-safe. */
+typedef struct StitchPool StitchPool;
+int stitch_pool_create(const int32_t* devices, int32_t n_devices, int32_t lanes_per_device, StitchPool** out);
+int stitch_pool_destroy(StitchPool* pool); /* completes everything queued first */
+int32_t stitch_pool_device_count(StitchPool* pool);
+/* The worker's ctx, e.g. to allocate device buffers or generate bitmaps on that GPU BEFORE jobs are queued (a ctx is
+ * not thread-safe: do not use it while its worker has jobs). */
+StitchCtx* stitch_pool_ctx(StitchPool* pool, int32_t index);
+int stitch_pool_submit(StitchPool* pool, const StitchJob* job, StitchResult* result, int32_t device, uint64_t* ticket);
+/* stitch_device_digest on GPU `device`, ordered after every job that worker has taken so far. */
+int stitch_pool_digest(StitchPool* pool, int32_t device, const void* dev_ptr, size_t bytes, uint64_t* out, uint64_t* ticket);
+int stitch_pool_wait(StitchPool* pool, uint64_t ticket, int32_t* device_out /* may be NULL */);
+int stitch_pool_wait_all(StitchPool* pool);
+int64_t stitch_pool_jobs_run(StitchPool* pool, int32_t index);
+const char* stitch_pool_last_error(StitchPool* pool);
 
 const char* stitch_strerror(int status);
 const char* stitch_last_error(StitchCtx* ctx);

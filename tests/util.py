@@ -54,6 +54,21 @@ def synth_image(w: int, h: int, seed: int, pattern: int = 0) -> np.ndarray:
     return out
 
 
+def digest(buf) -> int:
+    """CPU twin of stitch_device_digest (synth.cuh::digest_kernel) for a bytes-like object."""
+    b = np.frombuffer(bytes(buf) if not isinstance(buf, np.ndarray) else np.ascontiguousarray(buf).tobytes(), np.uint8)
+    n, nw = b.size, b.size // 4
+    K = np.uint64(0xD6E8FEB86659FD93)
+    with np.errstate(over="ignore"):
+        w = b[: nw * 4].view("<u4").astype(np.uint64)
+        acc = np.add.reduce(splitmix64(w ^ (np.arange(nw, dtype=np.uint64) * K)), dtype=np.uint64) if nw else np.uint64(0)
+        v = np.uint64(0)
+        for k in range(nw * 4, n):
+            v |= np.uint64(int(b[k])) << np.uint64(8 * (k & 3))
+        acc = acc + splitmix64(v ^ (np.uint64(nw) * K) ^ (np.uint64(n) << np.uint64(32)))
+    return int(acc)
+
+
 def recs(dims, orientations=None, file_sizes=None):
     out = []
     for i, (w, h) in enumerate(dims):
