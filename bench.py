@@ -231,6 +231,98 @@ def cpu_files_run(files, direction, mode, platform, steps: int, out_kind: str = 
     return mp / dt, dt * 1e3, cores
 
 
+def pool_sweep(args):
+    """BASELINE configs[4] through the PRODUCT's multi-GPU entry: ONE process, stitch_pool_* (one worker thread + ctx per
+    GPU, include/stitch.h), 10 000 jobs with device-resident bitmaps, static assignment gpu = job_id % G.
+    Wall clock around submit-all + wait-all; digests of every GPU's K slot canvases must agree."""
+    from imagestitching_b200 import DeviceBitmap, StitchPool, compute_layout
+    from imagestitching_b200 import _lib as L
+    from imagestitching_b200.stitch import _profile_struct
+
+    dims, direction, mode, platform, output, desc = WORKLOADS[args.workload]
+    G = args.pool
+    pool = StitchPool(list(range(G)), lanes_per_device=max(1, args.lanes))
+    lib = pool.lib
+    K = args.slots or 32
+    n_jobs = args.steps or 10000
+    profile = _profile_struct(platform)
+    recs = [{"naturalWidth": w, "naturalHeight": h, "width": w, "height": h, "orientation": 1, "fileSize": 0} for (w, h) in dims]
+    lay = compute_layout(recs, direction, mode, 0, platform)
+    cw, ch = int(lay["canvasW"]), int(lay["canvasH"])
+    mp, rgba_bytes = cw * ch / 1e6, cw * ch * 4
+    src_bytes = sum(w * h * 4 for (w, h) in dims)
+    jobs, keep = [], []   # jobs[g][s]
+    for g in range(G):
+        h = pool.ctx_handle(g)
+        row = []
+        for s_ in range(K):
+            imgs = []
+            for i, (w, hh) in enumerate(dims):
+                pitch = (w * 4 + 15) & ~15
+                p = C.c_void_p()
+                assert lib.stitch_device_alloc(h, hh * pitch, C.byref(p)) == 0
+                assert lib.stitch_generate_image(h, p, w, hh, pitch, SEED + 16 * s_ + i, 0) == 0
+                imgs.append(dict(recs[i], bitmap=DeviceBitmap(p.value, w, hh, pitch, keepalive=p)))
+            out = C.c_void_p()
+            assert lib.stitch_device_alloc(h, rgba_bytes, C.byref(out)) == 0
+            job, k2 = pool._helper.build_job(imgs, direction, mode, 0, profile, "rgba", True, out.value, 0, rgba_bytes, 0)
+            row.append((job, out))
+            keep.append((imgs, k2))
+        assert lib.stitch_memcpy_h2d(h, row[0][1], (C.c_char * 16)(), 16) == 0   # drains the generator launches
+        jobs.append(row)
+    results = [[L.StitchResult() for _ in range(K)] for _ in range(G)]
+
+    def sweep(n):
+        t = C.c_uint64()
+        for j in range(n):
+            g, s_ = j % G, j % K
+            st = lib.stitch_pool_submit(pool.handle, C.byref(jobs[g][s_][0]), C.byref(results[g][s_]), g, C.byref(t))
+            assert st == 0, st
+        assert lib.stitch_pool_wait_all(pool.handle) == 0, lib.stitch_pool_last_error(pool.handle)
+
+    sweep(100 * G)   # warm-up: lanes' buffers, tensor-map caches, clocks
+    sampler = ClockSampler(0)
+    sampler.start()
+    t0 = time.perf_counter()
+    sweep(n_jobs)
+    dt = time.perf_counter() - t0
+    sampler.sample()
+    sampler.stop()
+    digs = []
+    for g in range(G):
+        row = []
+        for s_ in range(K):
+            d, t = C.c_uint64(0), C.c_uint64()
+            assert lib.stitch_pool_digest(pool.handle, g, jobs[g][s_][1], rgba_bytes, C.byref(d), C.byref(t)) == 0
+            assert lib.stitch_pool_wait(pool.handle, t.value, None) == 0
+            row.append(int(d.value))
+        digs.append(row)
+    ran = [pool.jobs_run(g) for g in range(G)]
+    pool.close()
+    peak, peak_src = _peaks()
+    per_gpu_us = dt / (n_jobs / G) * 1e6
+    achieved = (src_bytes + rgba_bytes) / (per_gpu_us * 1e-6) / 1e9
+    line = {
+        "metric": "output MP/s, 9x12MP vertical stitch", "value": mp * n_jobs / dt, "unit": "MP/s", "n_gpus": G, "steps": n_jobs,
+        "warmup": 100 * G, "ms_per_step": dt / n_jobs * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u8 in/out, i32 vertical / f32 horizontal accumulate", "data": "synthetic", "mode": "pool",
+        "config": {"workload": desc, "name": args.workload, "canvas": [cw, ch],
+                   "parallelism": f"1 process, StitchPool over {G} GPU(s): a worker thread + ctx per GPU, {max(1, args.lanes)} lanes each, "
+                                  f"job j -> GPU j % {G}, slot j % {K}; no collective",
+                   "timing": "host wall clock around submit-all + wait-all (the pool has no cross-device event)"},
+        "us_per_job_per_gpu": per_gpu_us, "gpu_launches": n_jobs,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "note": "per GPU, wall clock: includes host submission"},
+        "clocks": sampler.summary(),
+        "digests": {"slots": K, "gpus": G, "equal_across_gpus": all(r == digs[0] for r in digs), "distinct": len(set(digs[0])),
+                    "slot0": f"{digs[0][0]:016x}"},
+        "jobs_run_per_gpu": ran,
+    }
+    assert line["digests"]["equal_across_gpus"], "canvases differ between GPUs"
+    print(json.dumps(line))
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -250,7 +342,12 @@ def main():
     ap.add_argument("--files-steps", type=int, default=-1,
                     help="e2e_files leg (JPEG files in host memory -> exported file in host memory): jobs per output kind; "
                          "-1 = auto (24 for cfg2 / cfg5, 0 = skip for the other workloads)")
+    ap.add_argument("--pool", type=int, default=0,
+                    help="N > 0: run the batch sweep in ONE process through stitch_pool_* over N GPUs (no torchrun)")
     args = ap.parse_args()
+    if args.pool > 0:
+        args.workload = "cfg5" if args.workload == "cfg2" else args.workload
+        return pool_sweep(args)
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -310,7 +407,7 @@ def main():
             for i, (w, h) in enumerate(dims):
                 pitch = (w * 4 + 15) & ~15
                 t = torch.empty(h * pitch, dtype=torch.uint8, device="cuda")
-                st = lib.stitch_generate_image(ctx.handle, t.data_ptr(), w, h, pitch, SEED + 1000 * rank + 16 * s + i, 0)
+                st = lib.stitch_generate_image(ctx.handle, t.data_ptr(), w, h, pitch, SEED + 16 * s + i, 0)   # the same on every rank
                 assert st == 0
                 keep.append(t)
                 imgs.append({"naturalWidth": w, "naturalHeight": h, "width": w, "height": h, "orientation": 1,
@@ -348,8 +445,14 @@ def main():
 
     host_s = [0.0]
 
+    # BASELINE configs[4]: job ids 0..9999 are sharded round-robin over the ranks (shard.py: static gpu = job_id % G,
+    # SURVEY 8e); job j works on resident slot j % K, so every rank holds the same K slots and a job's canvas does
+    # not depend on which GPU ran it -- checked below with on-device digests.
+    from imagestitching_b200.shard import shard_jobs
+    my_jobs = shard_jobs(args.steps * world, rank, world) if batch else None
+
     def step(i):
-        job = jobs[i % len(jobs)][0]
+        job = jobs[(my_jobs[i % len(my_jobs)] if batch else i) % len(jobs)][0]
         t = C.c_uint64()
         h0 = time.perf_counter()
         st = lib.stitch_submit(ctx.handle, C.byref(job), C.byref(res), C.byref(t))
@@ -395,6 +498,21 @@ def main():
     barrier()
     elapsed_ms = ev0.elapsed_time(ev1)
     launches = ctx.kernel_launches - launches0
+    # digests of the canvases the sweep left in the K job slots, on the device; equal on every rank or the run is void
+    digests = None
+    if batch and output == "rgba":
+        mine = []
+        for (_, _, o_rgba, _, _, _) in jobs:
+            d = C.c_uint64(0)
+            assert lib.stitch_device_digest(ctx.handle, o_rgba.data_ptr(), rgba_bytes, C.byref(d)) == 0
+            mine.append(int(d.value))
+        allv = [mine]
+        if world > 1:
+            allv = [None] * world
+            dist.all_gather_object(allv, mine)
+        digests = {"slots": len(mine), "ranks": world, "equal_across_ranks": all(v == allv[0] for v in allv),
+                   "distinct": len(set(allv[0])), "slot0": f"{allv[0][0]:016x}"}
+        assert digests["equal_across_ranks"], "canvases differ between GPUs"
     if world > 1:
         t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -582,6 +700,8 @@ def main():
     }
     if e2e_files is not None:
         line["e2e_files"] = e2e_files
+    if digests is not None:
+        line["digests"] = digests
     prof_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof_path):
         try:

@@ -5,24 +5,24 @@
 // every region into warp-sized units; a persistent grid of warps pulls units from an atomic
 // counter (heavy units first) until none are left:
 //
-//   REGION_STREAM  integer-aligned area downscale (1 < ratio_x <= 4, ratio_y > 1), EXIF 1-4.
+//   REGION_STREAM  integer-aligned area downscale (1 < ratio_x <= 16, ratio_y > 1), EXIF 1-4.
 //       The bandwidth path (stream_unit.cuh).  A warp owns a band of <=32 source groups
-//       (4 px = 16 B per lane) and streams DOWN the source rows.  Each lane stages its own
-//       16 B per row into a per-warp shared-memory ring with cp.async (LDGSTS, L1 bypassed),
-//       STREAM_NST rows deep, so the bytes in flight cost no registers and no barrier.
-//       Vertical area weights are warp-uniform (row table in smem); the horizontal pass runs in
-//       registers when an output row completes: each lane reduces its 4 columns into the
-//       <=MAXO outputs that start in its group plus the tail of its left neighbour's last
-//       output, which travels by one shuffle.  Every source byte is fetched once per warp.
-//       Arithmetic: a byte b is expanded with ONE PRMT to the float 1 + b*2^-15 (0x3F80bb00);
-//       because the filter weights sum to 1 the accumulators stay in that form, and one
-//       FFMA.RM against 2^23 - 2^15 + 0.5 leaves floor(value + 0.5) in the low mantissa byte.
-//       Resolution of the form is 2^-8 LSB per rounding.  Alpha is not filtered: the pixels are
-//       ANDed together and a unit that saw any alpha != 255 is redone by the exact
-//       premultiplied gather path (photos are opaque, so this is the rare case).
-//       (A cp.async.bulk + mbarrier ring fed by one elected lane was measured too: 0.164 ms vs
-//       0.127 ms per 9x12MP job -- the elect/R2UR/UBLKCP sequence costs ~25 issue slots per
-//       512-byte row, and the kernel is issue-bound, not latency-bound.  See DESIGN.md.)
+//       (4 px = 16 B per lane) and streams DOWN the source rows.  The rows are staged by TMA:
+//       lane 0 requests one box of 128 px x 8 rows (cp.async.bulk.tensor.2d, one UTMALDG) per
+//       stage into a per-warp shared-memory ring of 3 stages, each completing on its own mbarrier
+//       (expect-tx); the warp that consumes a stage re-arms it, so no second warp and no block
+//       barrier is involved.  (Round 1 staged 16 B per lane and row with cp.async / LDGSTS; the
+//       first bulk attempt -- a 1-D cp.async.bulk per 512-byte row -- cost ~25 issue slots per row.)
+//       Vertical pass: INTEGER.  Two rows at a time: 2 PRMT interleave their bytes channel by
+//       channel, 3 IDP.2A apply both rows' 15-bit weights (a warp-uniform row-pair table in smem;
+//       the weights of an output row sum to exactly 2^15).  The accumulators start at 0x4B000000, so
+//       they are at the same time the floats 2^23 + v * 2^15 the horizontal pass works on.
+//       Horizontal pass, in registers when an output row completes: each lane reduces its 4 columns
+//       into the <=MAXO outputs that start in its group plus the tail of its left neighbour's last
+//       output, which travels by one shuffle; one FFMA.RM against 2^23 - 256 + 0.5 leaves
+//       floor(value + 0.5) in the low mantissa byte.  Every source byte is fetched once per warp.
+//       Alpha is not filtered: the pixels are ANDed together and a unit that saw any alpha != 255 is
+//       redone by the exact premultiplied gather path (photos are opaque, so this is the rare case).
 //   REGION_UPSCALE bilinear enlargement of the fully covered pixels of one image (upscale_unit.cuh):
 //       output-bound, 16-byte stores, source through L1.
 //   REGION_FILL    white.
@@ -214,13 +214,11 @@ compose_kernel(const __grid_constant__ JobParam P, const __grid_constant__ Plan 
   extern __shared__ __align__(128) uint8_t smem_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   WarpSmem& ws = reinterpret_cast<WarpSmem*>(smem_raw)[warp];
-#if STITCH_STREAM_TMA
   if (lane == 0) {
 #pragma unroll
     for (int s = 0; s < STREAM_TMA_STAGES; ++s) mbar_init(smem_u32(&ws.full[s]), 1);
     fence_proxy_async();   // the barriers are visible to the TMA unit before the first box is issued
   }
-#endif
   // Lanes that never copy (past the band) and padded rows read the ring as it is: give it defined,
   // opaque contents once so the alpha check cannot trip on uninitialised shared memory.
 #pragma unroll

@@ -419,7 +419,6 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
     if (grid > need) grid = need;
     unsigned int* sched = (unsigned int*)scratch.p;
     TmaMaps maps;
-#if STITCH_STREAM_TMA
     // tensor maps of the bitmaps that have a streaming region (the other slots are never dereferenced)
     uint32_t mapped = 0;
     for (int i = 0; i < plan.n_regions; ++i) {
@@ -430,7 +429,6 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
       const cudaError_t e = scratch.tma.get(im.data, im.pitch, im.bw, im.bh, &maps.box[r.img], &maps.row[r.img]);
       if (e != cudaSuccess) return (int)e;
     }
-#endif
     if (any_stream) { STITCH_ALL(err = K::launch(P, plan, maps, grid, sched, stream)) }
     else { STITCH_LIGHT(err = K::launch(P, plan, maps, grid, sched, stream)) }
     *launches = 1;

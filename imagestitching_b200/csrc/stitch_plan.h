@@ -51,16 +51,9 @@ struct Region {
 };
 
 #define STITCH_MAX_REGIONS 128
-#ifndef STITCH_STREAM_TMA
-#define STITCH_STREAM_TMA 1   // 0: per-lane cp.async (LDGSTS) staging, the round-1 form (kept for A/B runs)
-#endif
-// row-table entries per warp (= source rows of the tallest unit + padding).  With the TMA ring (24 rows x 512 B per
-// warp instead of 8) 224 entries keep two CTAs of 8 warps inside the SM's 228 KB of shared memory.
-#if STITCH_STREAM_TMA
+// row-table entries per warp (= source rows of the tallest unit + padding; one 16-byte entry per row PAIR).  With the
+// TMA ring (24 rows x 512 B per warp) 224 rows keep two CTAs of 8 warps inside the SM's 228 KB of shared memory.
 #define STREAM_TAB_MAX 224
-#else
-#define STREAM_TAB_MAX 288
-#endif
 #define STREAM_WARPS 8
 
 struct Plan {

@@ -10,13 +10,11 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <unordered_map>
 #include <vector>
 
 #include "stitch.h"
 
-#ifndef STITCH_STREAM_TMA
-#define STITCH_STREAM_TMA 1   // 0: per-lane cp.async (LDGSTS) staging, the round-1 form (kept for A/B runs)
-#endif
 #ifndef STREAM_TMA_ROWS
 #define STREAM_TMA_ROWS 8     // source rows per stage = per TMA box
 #endif
@@ -35,7 +33,6 @@ struct TmaMaps {
   CUtensorMap row[STITCH_MAX_IMAGES];
 };
 
-#if STITCH_STREAM_TMA
 typedef CUresult (*TmaEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                 const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -52,22 +49,33 @@ inline TmaEncodeFn tma_encode_fn() {
   return fn;
 }
 
-// Maps are a pure function of (address, pitch, size): a job that reuses its bitmap buffers (a lane's staging, a
-// resident job slot of the batch sweep) finds them here instead of encoding 18 descriptors per submit.
+// Maps are a pure function of (address, pitch, size): a job that reuses its bitmap buffers (a lane's staging, the
+// resident job slots of the batch sweep: 32 slots x 9 bitmaps) finds them here instead of encoding 18 descriptors per
+// submit (~60 us of host time per job when every lookup missed, against 80 us of GPU time).
 struct TmaCache {
-  struct Entry { const void* data; int64_t pitch; int32_t w, h; CUtensorMap box, row; };
-  std::vector<Entry> e;
-  size_t next = 0;
-  static constexpr size_t kCap = 64;
+  struct Key {
+    const void* data; int64_t pitch; int32_t w, h;
+    bool operator==(const Key& o) const { return data == o.data && pitch == o.pitch && w == o.w && h == o.h; }
+  };
+  struct KeyHash {
+    size_t operator()(const Key& k) const {
+      uint64_t x = (uint64_t)(uintptr_t)k.data ^ ((uint64_t)k.pitch * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uint32_t)k.w << 32) ^ (uint32_t)k.h;
+      x ^= x >> 29; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 32;
+      return (size_t)x;
+    }
+  };
+  struct Maps { CUtensorMap box, row; };
+  std::unordered_map<Key, Maps, KeyHash> e;
+  static constexpr size_t kCap = 8192;   // 2 MB of descriptors at most; cleared when full
 
   // cudaSuccess and the two maps, or an error (no driver entry point / encode refused)
   cudaError_t get(const void* data, int64_t pitch, int32_t w, int32_t h, CUtensorMap* box, CUtensorMap* row) {
-    for (const Entry& x : e)
-      if (x.data == data && x.pitch == pitch && x.w == w && x.h == h) { *box = x.box; *row = x.row; return cudaSuccess; }
+    const Key key{data, pitch, w, h};
+    auto it = e.find(key);
+    if (it != e.end()) { *box = it->second.box; *row = it->second.row; return cudaSuccess; }
     const TmaEncodeFn enc = tma_encode_fn();
     if (!enc) return cudaErrorNotSupported;
-    Entry n;
-    n.data = data; n.pitch = pitch; n.w = w; n.h = h;
+    Maps n;
     const cuuint64_t dims[2] = {(cuuint64_t)w, (cuuint64_t)h};
     const cuuint64_t strides[1] = {(cuuint64_t)pitch};
     const cuuint32_t es[2] = {1, 1};
@@ -77,14 +85,11 @@ struct TmaCache {
         enc(&n.row, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(data), dims, strides, b1, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return cudaErrorInvalidValue;
-    if (e.size() < kCap) e.push_back(n);
-    else { e[next] = n; next = (next + 1) % kCap; }
+    if (e.size() >= kCap) e.clear();
+    e.emplace(key, n);
     *box = n.box; *row = n.row;
     return cudaSuccess;
   }
 };
-#else
-struct TmaCache {};
-#endif
 
 }  // namespace stitch
