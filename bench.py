@@ -275,7 +275,7 @@ def pool_sweep(args):
     def sweep(n):
         t = C.c_uint64()
         for j in range(n):
-            g, s_ = j % G, j % K
+            g, s_ = j % G, (j // G) % K
             st = lib.stitch_pool_submit(pool.handle, C.byref(jobs[g][s_][0]), C.byref(results[g][s_]), g, C.byref(t))
             assert st == 0, st
         assert lib.stitch_pool_wait_all(pool.handle) == 0, lib.stitch_pool_last_error(pool.handle)
@@ -308,7 +308,7 @@ def pool_sweep(args):
         "dtype": "u8 in/out, i32 vertical / f32 horizontal accumulate", "data": "synthetic", "mode": "pool",
         "config": {"workload": desc, "name": args.workload, "canvas": [cw, ch],
                    "parallelism": f"1 process, StitchPool over {G} GPU(s): a worker thread + ctx per GPU, {max(1, args.lanes)} lanes each, "
-                                  f"job j -> GPU j % {G}, slot j % {K}; no collective",
+                                  f"job j -> GPU j % {G}, slot (j // {G}) % {K}; no collective",
                    "timing": "host wall clock around submit-all + wait-all (the pool has no cross-device event)"},
         "us_per_job_per_gpu": per_gpu_us, "gpu_launches": n_jobs,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
@@ -446,13 +446,13 @@ def main():
     host_s = [0.0]
 
     # BASELINE configs[4]: job ids 0..9999 are sharded round-robin over the ranks (shard.py: static gpu = job_id % G,
-    # SURVEY 8e); job j works on resident slot j % K, so every rank holds the same K slots and a job's canvas does
-    # not depend on which GPU ran it -- checked below with on-device digests.
+    # SURVEY 8e); job j works on resident slot (j // G) % K, so every rank cycles through the same K slots and a job's
+    # canvas does not depend on which GPU ran it -- checked below with on-device digests.
     from imagestitching_b200.shard import shard_jobs
     my_jobs = shard_jobs(args.steps * world, rank, world) if batch else None
 
     def step(i):
-        job = jobs[(my_jobs[i % len(my_jobs)] if batch else i) % len(jobs)][0]
+        job = jobs[(my_jobs[i % len(my_jobs)] // world if batch else i) % len(jobs)][0]
         t = C.c_uint64()
         h0 = time.perf_counter()
         st = lib.stitch_submit(ctx.handle, C.byref(job), C.byref(res), C.byref(t))
