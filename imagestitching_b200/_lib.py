@@ -17,6 +17,7 @@ MODE_MIN, MODE_MAX, MODE_ORIGINAL, MODE_OTHER = 0, 1, 2, 3
 IOS, ANDROID, OTHER = 0, 1, 2
 MEM_HOST, MEM_DEVICE, MEM_HOST_JPEG = 0, 1, 2
 OUT_RGBA, OUT_YUV420, OUT_JPEG, OUT_PNG = 1, 2, 4, 8
+NOALLOC_DIGEST_MAX_BYTES = 1 << 30
 
 
 class StitchProfile(C.Structure):
@@ -110,6 +111,7 @@ SIGNATURES = {
     "stitch_memcpy_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "stitch_generate_image": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int64, C.c_uint64, C.c_int32]),
     "stitch_device_digest": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]),
+    "stitch_device_digest_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_char_p, C.c_size_t]),
     "stitch_pool_create": (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
     "stitch_pool_destroy": (C.c_int, [C.c_void_p]),
     "stitch_pool_device_count": (C.c_int32, [C.c_void_p]),

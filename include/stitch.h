@@ -266,6 +266,22 @@ int stitch_generate_image(StitchCtx* ctx, void* dev_dst, int32_t width, int32_t 
  * multi-GPU test compare canvases without copying them back.  Synchronous, lane 0. */
 int stitch_device_digest(StitchCtx* ctx, const void* dev_ptr, size_t bytes, uint64_t* out);
 
+/* The same digest for callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Allocates nothing (no cudaMalloc / cudaMallocHost / cudaFree, no ctx): its scratch -- one partial sum per 256 KiB of
+ * input -- is a file-scope __device__ array of 32 KB that every GPU which loads the library holds until the process
+ * exits, which bounds the input at STITCH_NOALLOC_DIGEST_MAX_BYTES; a larger `bytes` is refused with STITCH_E_BAD_ARG
+ * and a message in `err` (optional, NUL-terminated, at most err_capacity bytes).  Two launches on `stream` (a
+ * cudaStream_t, NULL = the default stream) of GPU `device`; the 64-bit result is stored to `dev_out`, DEVICE memory of
+ * that GPU passed by the caller, when the stream reaches it -- the call does not synchronise.  Same value as
+ * stitch_device_digest.  All calls on one GPU share the scratch, which keeps the last call's contents (nothing in it
+ * has to start at zero: a call overwrites every slot it reads): calls that OVERLAP on that GPU -- two streams, two
+ * threads -- race; serialise them.  The first call per device looks the scratch's device address up
+ * (cudaGetSymbolAddress): make it once outside any graph capture. */
+#define STITCH_NOALLOC_DIGEST_MAX_BYTES (1ull << 30)
+int stitch_device_digest_noalloc(int32_t device, void* stream, const void* dev_ptr, size_t bytes, uint64_t* dev_out,
+                                 char* err, size_t err_capacity);
+
 /* ---- every GPU of a box from one process (north star: "independent stitch jobs are sharded across the 8 GPUs of one
  * box with no NCCL") ----
  * One host thread + one StitchCtx (with `lanes_per_device` job lanes) per GPU and a shared job queue: a worker takes the
