@@ -349,13 +349,32 @@ struct LightLaunch {
   }
 };
 
-// The draw loop of one job as ONE launch.  path_info: streaming | gather << 8 | fill << 16 |
-// upscale << 25 region counts of the fused plan, or 1 << 24 when the whole canvas took the per-pixel gather kernel
-// (fractional device rects, overlapping images).
-inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_count, StreamScratch& scratch,
-                      cudaStream_t stream, int* launches, int* path_info) {
-  *launches = 0;
-  *path_info = 1 << 24;
+#define STITCH_DISPATCH(M, H, Md, expr) \
+  if (maxo == M && hops == H && mode == Md) { using K = ComposeLaunch<M, H, Md>; expr; }
+#define STITCH_SHAPES(Md, expr)                                                               \
+  STITCH_DISPATCH(2, 1, Md, expr) STITCH_DISPATCH(3, 1, Md, expr) STITCH_DISPATCH(4, 1, Md, expr) \
+  STITCH_DISPATCH(2, 2, Md, expr) STITCH_DISPATCH(3, 2, Md, expr) STITCH_DISPATCH(4, 2, Md, expr) \
+  STITCH_DISPATCH(4, 4, Md, expr)
+#define STITCH_ALL(expr) STITCH_SHAPES(0, expr) STITCH_SHAPES(1, expr) STITCH_SHAPES(2, expr)
+#define STITCH_LIGHT(expr)                                   \
+  if (mode == 0) { using K = LightLaunch<0>; expr; }          \
+  else if (mode == 1) { using K = LightLaunch<1>; expr; }     \
+  else { using K = LightLaunch<2>; expr; }
+
+// Everything about a job's draw that is decided on the host: the kernel shape, the fused plan, the tensor maps.
+struct PreparedJob {
+  bool fused = false;        // false: no fast region at all, the whole-canvas gather kernel draws the job
+  int mode = 0, maxo = 2, hops = 1, per_sm = 0;
+  bool any_stream = false;
+  int path_info = 1 << 24;
+  Plan plan;
+  TmaMaps maps;
+};
+
+// path_info: streaming | gather << 8 | fill << 16 | upscale << 25 region counts of the fused plan, or 1 << 24 when the
+// whole canvas takes the per-pixel gather kernel (every image transposed, overlapped or unaligned).
+inline int prepare_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_count, StreamScratch& scratch, cudaStream_t stream,
+                       PreparedJob* J) {
   const int mode = want_yuv ? (want_rgba ? STREAM_MODE_BOTH : STREAM_MODE_YUV) : STREAM_MODE_RGBA;
   // kernel variant: decided by the images alone (before the unit grid is chosen)
   int maxo = 2, hops = 1;
@@ -370,74 +389,90 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
   }
   // instantiated (MAXO, HOPS) shapes: (2|3|4, 1) for ratios <= 4, (2, 2) for 2 < ratio <= 8, (3, 2) / (4, 2) for jobs that mix
   // ratios from 4/3 (or 1) up to 8 (mixed-aspect stitches to a common height: BASELINE configs[2] in 'min' mode), (4, 4) for the rest
-  if (hops > 1) {
-    if (hops == 2) { /* (2, 2), (3, 2) or (4, 2) */ }
-    else { maxo = 4; hops = 4; }
-  }
+  if (hops > 2) { maxo = 4; hops = 4; }
   cudaError_t err = cudaSuccess;
   int per_sm = 0;
-#define STITCH_DISPATCH(M, H, Md, expr) \
-  if (maxo == M && hops == H && mode == Md) { using K = ComposeLaunch<M, H, Md>; expr; }
-#define STITCH_SHAPES(Md, expr)                                                               \
-  STITCH_DISPATCH(2, 1, Md, expr) STITCH_DISPATCH(3, 1, Md, expr) STITCH_DISPATCH(4, 1, Md, expr) \
-  STITCH_DISPATCH(2, 2, Md, expr) STITCH_DISPATCH(3, 2, Md, expr) STITCH_DISPATCH(4, 2, Md, expr) \
-  STITCH_DISPATCH(4, 4, Md, expr)
-#define STITCH_ALL(expr) STITCH_SHAPES(0, expr) STITCH_SHAPES(1, expr) STITCH_SHAPES(2, expr)
-#define STITCH_LIGHT(expr)                                   \
-  if (mode == 0) { using K = LightLaunch<0>; expr; }          \
-  else if (mode == 1) { using K = LightLaunch<1>; expr; }     \
-  else { using K = LightLaunch<2>; expr; }
   if (any_stream) { STITCH_ALL(per_sm = K::ctas_per_sm(&err)) }
   else { STITCH_LIGHT(per_sm = K::ctas_per_sm(&err)) }
   if (err != cudaSuccess) return (int)err;
-  const int resident_warps = sm_count * per_sm * STREAM_WARPS;
-
-  Plan plan;
-  if (build_plan(P, mode, hops, resident_warps, &plan)) {
-    if (!scratch.p) {  // unit scheduler counters {next unit, warps retired}; the kernel leaves them at zero
-      cudaError_t e = cudaMalloc(&scratch.p, 256);
-      if (e != cudaSuccess) return (int)e;
-      scratch.cap = 256;
-      e = cudaMemsetAsync(scratch.p, 0, 256, stream);
-      if (e != cudaSuccess) return (int)e;
-    }
-    int cnt[4] = {0, 0, 0, 0};
-    uint32_t up_seen = 0;
-    for (int i = 0; i < plan.n_regions; ++i) {
-      const Region& r = plan.r[i];
-      if (r.kind == REGION_UPSCALE) {  // body + tail of one enlarged image count once
-        if (up_seen >> r.img & 1u) continue;
-        up_seen |= 1u << r.img;
-      }
-      cnt[r.kind]++;
-    }
-    *path_info = std::min(cnt[REGION_STREAM], 255) | (std::min(cnt[REGION_GATHER], 255) << 8) |
-                 (std::min(cnt[REGION_FILL], 255) << 16) | (std::min(cnt[REGION_UPSCALE], 63) << 25);
-    // persistent grid: every resident warp slot of the chip, capped by the number of units
-    int grid = sm_count * per_sm;
-    const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
-    if (grid > need) grid = need;
-    unsigned int* sched = (unsigned int*)scratch.p;
-    TmaMaps maps;
-    // tensor maps of the bitmaps that have a streaming region (the other slots are never dereferenced)
-    uint32_t mapped = 0;
-    for (int i = 0; i < plan.n_regions; ++i) {
-      const Region& r = plan.r[i];
-      if (r.kind != REGION_STREAM || (mapped >> r.img & 1u)) continue;
-      mapped |= 1u << r.img;
-      const ImgParam& im = P.img[r.img];
-      const cudaError_t e = scratch.tma.get(im.data, im.pitch, im.bw, im.bh, &maps.box[r.img], &maps.row[r.img]);
-      if (e != cudaSuccess) return (int)e;
-    }
-    if (any_stream) { STITCH_ALL(err = K::launch(P, plan, maps, grid, sched, stream)) }
-    else { STITCH_LIGHT(err = K::launch(P, plan, maps, grid, sched, stream)) }
-    *launches = 1;
-    return (int)err;
+  J->mode = mode; J->maxo = maxo; J->hops = hops; J->per_sm = per_sm; J->any_stream = any_stream;
+  J->path_info = 1 << 24;
+  J->fused = build_plan(P, mode, hops, sm_count * per_sm * STREAM_WARPS, &J->plan);
+  if (!J->fused) return 0;
+  if (!scratch.p) {  // unit scheduler counters {next unit, warps retired}; the kernel leaves them at zero
+    cudaError_t e = cudaMalloc(&scratch.p, 256);
+    if (e != cudaSuccess) return (int)e;
+    scratch.cap = 256;
+    e = cudaMemsetAsync(scratch.p, 0, 256, stream);
+    if (e != cudaSuccess) return (int)e;
   }
-#undef STITCH_LIGHT
-#undef STITCH_ALL
-#undef STITCH_SHAPES
-#undef STITCH_DISPATCH
+  const Plan& plan = J->plan;
+  int cnt[4] = {0, 0, 0, 0};
+  uint32_t up_seen = 0;
+  for (int i = 0; i < plan.n_regions; ++i) {
+    const Region& r = plan.r[i];
+    if (r.kind == REGION_UPSCALE) {  // body + tail of one enlarged image count once
+      if (up_seen >> r.img & 1u) continue;
+      up_seen |= 1u << r.img;
+    }
+    cnt[r.kind]++;
+  }
+  J->path_info = std::min(cnt[REGION_STREAM], 255) | (std::min(cnt[REGION_GATHER], 255) << 8) |
+                 (std::min(cnt[REGION_FILL], 255) << 16) | (std::min(cnt[REGION_UPSCALE], 63) << 25);
+  // tensor maps of the bitmaps that have a streaming region (the other slots are never dereferenced)
+  uint32_t mapped = 0;
+  for (int i = 0; i < plan.n_regions; ++i) {
+    const Region& r = plan.r[i];
+    if (r.kind != REGION_STREAM || (mapped >> r.img & 1u)) continue;
+    mapped |= 1u << r.img;
+    const ImgParam& im = P.img[r.img];
+    const cudaError_t e = scratch.tma.get(im.data, im.pitch, im.bw, im.bh, &J->maps.box[r.img], &J->maps.row[r.img]);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return 0;
+}
+
+// One compose launch over `plan`: the job's whole plan, or a subset of its regions (sub_plan below).
+inline int launch_plan(const JobParam& P, const PreparedJob& J, const Plan& plan, int sm_count, StreamScratch& scratch,
+                       cudaStream_t stream) {
+  const int mode = J.mode, maxo = J.maxo, hops = J.hops;
+  // persistent grid: every resident warp slot of the chip, capped by the number of units
+  int grid = sm_count * J.per_sm;
+  const int need = (plan.n_units + STREAM_WARPS - 1) / STREAM_WARPS;
+  if (grid > need) grid = need;
+  unsigned int* sched = (unsigned int*)scratch.p;
+  cudaError_t err = cudaSuccess;
+  if (J.any_stream) { STITCH_ALL(err = K::launch(P, plan, J.maps, grid, sched, stream)) }
+  else { STITCH_LIGHT(err = K::launch(P, plan, J.maps, grid, sched, stream)) }
+  return (int)err;
+}
+
+// The regions of `plan` that `take` accepts, renumbered: same units, same unit geometry -- so drawing a job as
+// several launches over disjoint subsets gives the same bytes as the one fused launch.
+template <class Pred>
+inline void sub_plan(const Plan& plan, Pred take, Plan* out) {
+  int unit = 0, n = 0;
+  for (int i = 0; i < plan.n_regions; ++i) {
+    if (!take(plan.r[i])) continue;
+    Region r = plan.r[i];
+    r.first_unit = unit;
+    unit += r.tiles_x * r.tiles_y;
+    out->r[n++] = r;
+  }
+  out->n_regions = n;
+  out->n_units = unit;
+}
+
+// The draw loop of one job as ONE launch.
+inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_count, StreamScratch& scratch,
+                      cudaStream_t stream, int* launches, int* path_info) {
+  *launches = 0;
+  PreparedJob J;
+  int st = prepare_job(P, want_rgba, want_yuv, sm_count, scratch, stream, &J);
+  *path_info = J.path_info;
+  if (st != 0) return st;
+  *launches = 1;
+  if (J.fused) return launch_plan(P, J, J.plan, sm_count, scratch, stream);
   if (want_yuv) {
     dim3 grid(((P.cw + 1) / 2 + 31) / 32, ((P.ch + 1) / 2 + 7) / 8);
     gather_yuv_kernel<<<grid, 256, 0, stream>>>(P);
@@ -445,7 +480,6 @@ inline int launch_job(const JobParam& P, bool want_rgba, bool want_yuv, int sm_c
     dim3 grid((P.cw + 31) / 32, (P.ch + 7) / 8);
     gather_rgba_kernel<<<grid, 256, 0, stream>>>(P);
   }
-  *launches = 1;
   return (int)cudaGetLastError();
 }
 
