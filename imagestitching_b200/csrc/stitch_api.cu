@@ -14,13 +14,16 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <atomic>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "gather_kernel.cuh"
 #include "stitch.h"
 #include "stitch_plan.h"
 #include "launch.cuh"
+#include "host_stage.h"
 #include "jpeg_kernels.cuh"
 #include "jpeg_decode.cuh"
 #include "png_kernels.cuh"
@@ -70,6 +73,14 @@ struct Lane {
   cudaEvent_t ev_draw[STITCH_MAX_IMAGES + 1] = {};
   cudaEvent_t ev_up[STITCH_MAX_IMAGES] = {};
   cudaEvent_t ev_dl = nullptr, ev_start = nullptr;
+  // pageable host buffers (host_stage.h): pinned upload ring, pinned copy of the canvas, events + counter of the
+  // copy-out tasks the pool still owes this lane
+  stitch::UploadRing* up_ring = nullptr;
+  uint8_t* host_canvas = nullptr;
+  size_t host_canvas_cap = 0;
+  std::vector<cudaEvent_t> dl_events;
+  size_t dl_events_used = 0;
+  std::atomic<int>* host_copies = nullptr;
   uint64_t* info_host = nullptr;   // pinned, INFO_WORDS words: file sizes / overflow flags / decoder convergence
   uint64_t busy_ticket = 0;        // deferred job that still owns this lane's arenas and info block (0 = none)
   // JPEG decode: grow-only arena (scan bytes, tables, subsequence states, coefficients, component planes)
@@ -196,6 +207,13 @@ void free_lane(Lane& ln) {
     if (e) cudaEventDestroy(e);
   if (ln.ev_dl) cudaEventDestroy(ln.ev_dl);
   if (ln.ev_start) cudaEventDestroy(ln.ev_start);
+  if (ln.host_copies) {
+    while (ln.host_copies->load(std::memory_order_acquire) > 0) std::this_thread::yield();
+    delete ln.host_copies;
+  }
+  if (ln.up_ring) { ln.up_ring->release(); delete ln.up_ring; }
+  if (ln.host_canvas) cudaFreeHost(ln.host_canvas);
+  for (cudaEvent_t e : ln.dl_events) cudaEventDestroy(e);
   stitch::free_scratch(ln.scratch);
   if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
   ln = Lane();
@@ -576,6 +594,71 @@ struct PngExport {
   }
 };
 
+// Uploads of PAGEABLE bitmaps through the lane's pinned ring (host_stage.h): the pool copies row chunks into ring slots,
+// this thread sends each slot as soon as it is full and keeps the pool kSlots chunks ahead -- across image boundaries.
+struct StagedUploads {
+  struct Chunk { int img, r0, r1; };
+  struct Src { uint8_t* dst; const uint8_t* src; int64_t dpitch, spitch; size_t row_bytes; };
+  std::vector<Chunk> chunks;
+  Src srcs[STITCH_MAX_IMAGES];
+  size_t submitted = 0, issued = 0;
+  stitch::UploadRing* ring = nullptr;
+  uint64_t base = 0;
+
+  void add(int img, void* dst, const void* src, int64_t dpitch, int64_t spitch, size_t row_bytes, int rows) {
+    srcs[img] = Src{(uint8_t*)dst, (const uint8_t*)src, dpitch, spitch, row_bytes};
+    const int per = (int)std::max<int64_t>(1, (int64_t)stitch::UploadRing::kChunk / dpitch);
+    for (int r = 0; r < rows; r += per) chunks.push_back(Chunk{img, r, std::min(rows, r + per)});
+  }
+  void submit_ahead() {
+    constexpr int K = stitch::UploadRing::kSlots;
+    while (submitted < chunks.size() && submitted < issued + K) {
+      const int slot = (int)((base + submitted) % K);
+      if (ring->used[slot]) cudaEventSynchronize(ring->sent[slot]);   // the slot's previous contents have left
+      ring->ready[slot].store(0, std::memory_order_relaxed);
+      const Chunk c = chunks[submitted];
+      const Src sr = srcs[c.img];
+      uint8_t* pinned = ring->base + (size_t)slot * stitch::UploadRing::kChunk;
+      std::atomic<int>* flag = &ring->ready[slot];
+      stitch::CopyPool::get().submit([=] {
+        stitch::copy_rows_in(pinned, sr.dpitch, sr.src, sr.spitch, sr.row_bytes, c.r0, c.r1);
+        flag->store(1, std::memory_order_release);
+      });
+      ++submitted;
+    }
+  }
+  // sends every chunk of `img` on stream `on`; returns when the last one has been handed to the DMA engine
+  cudaError_t upload_image(int img, cudaStream_t on) {
+    constexpr int K = stitch::UploadRing::kSlots;
+    while (issued < chunks.size() && chunks[issued].img == img) {
+      submit_ahead();
+      const int slot = (int)((base + issued) % K);
+      while (!ring->ready[slot].load(std::memory_order_acquire)) std::this_thread::yield();
+      const Chunk c = chunks[issued];
+      const Src& sr = srcs[c.img];
+      cudaError_t e = cudaMemcpyAsync(sr.dst + (int64_t)c.r0 * sr.dpitch, ring->base + (size_t)slot * stitch::UploadRing::kChunk,
+                                      (size_t)(c.r1 - c.r0) * (size_t)sr.dpitch, cudaMemcpyHostToDevice, on);
+      if (e == cudaSuccess) e = cudaEventRecord(ring->sent[slot], on);
+      if (e != cudaSuccess) return e;
+      ring->used[slot] = true;
+      ++issued;
+    }
+    submit_ahead();
+    return cudaSuccess;
+  }
+  // on every way out: no pool task may still be writing into the ring, and the ring's counter moves on
+  ~StagedUploads() {
+    if (!ring) return;
+    constexpr int K = stitch::UploadRing::kSlots;
+    for (size_t g = issued; g < submitted; ++g) {
+      const int slot = (int)((base + g) % K);
+      while (!ring->ready[slot].load(std::memory_order_acquire)) std::this_thread::yield();
+      ring->used[slot] = false;
+    }
+    ring->next = base + submitted;
+  }
+};
+
 // defer == nullptr: everything that needs the host is done here (stitch_run).  Otherwise nothing waits for the GPU
 // and *defer says what finalize_job still owes (stitch_submit).
 int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, PendingJob* defer) {
@@ -686,6 +769,12 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   };
   int k_dec = 0, n_host = 0;
   int64_t host_bytes = 0;
+  // pageable host memory is staged by the library itself, for the synchronous entry point (host_stage.h)
+  static const bool host_stage_on = [] { const char* e = std::getenv("STITCH_HOST_STAGE"); return !(e && e[0] == '0'); }();
+  const bool stage_ok = host_stage_on && defer == nullptr;
+  StagedUploads staged;
+  bool pend[STITCH_MAX_IMAGES] = {};
+  if (stage_ok) ln.dl_events_used = 0;
   // stitch_run's pipelined form (see [4] below) is decided here so that bitmap 0 is on its way before the plan is made
   static const bool pipeline_on = [] { const char* e = std::getenv("STITCH_PIPELINE"); return !(e && e[0] == '0'); }();
   bool early = pipeline_on && defer == nullptr && n >= 2 && job->out_mem_kind != STITCH_MEM_DEVICE && want_rgba && !want_yuv &&
@@ -734,11 +823,21 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
                           pitch == dpitch && dpitch == (int64_t)im.bmp_width * 4};
       has_upload[i] = true;
       ++n_host;
-      host_bytes += (int64_t)im.bmp_width * 4 * im.bmp_height;
+      const int64_t img_bytes = (int64_t)im.bmp_width * 4 * im.bmp_height;
+      host_bytes += img_bytes;
       if (early) {
         // the upload starts after whatever the lane's stream still holds for this buffer (a fresh staging's memset)
         CUDA_TRY(ctx, cudaEventRecord(ln.ev_start, ln.stream));
         CUDA_TRY(ctx, cudaStreamWaitEvent(ln.ul_stream, ln.ev_start, 0));
+      }
+      if (stage_ok && img_bytes >= (256 << 10) && stitch::is_pageable(im.data)) {
+        // pageable memory: through the lane's pinned ring, filled by the copy pool (host_stage.h); sent below
+        if (!ln.up_ring) ln.up_ring = new stitch::UploadRing();
+        CUDA_TRY(ctx, ln.up_ring->ensure());
+        if (!staged.ring) { staged.ring = ln.up_ring; staged.base = ln.up_ring->next; }
+        staged.add(i, ln.in_stage[i], im.data, dpitch, pitch, (size_t)im.bmp_width * 4, im.bmp_height);
+        pend[i] = true;
+      } else if (early) {
         CUDA_TRY(ctx, issue_upload(i, ln.ul_stream));
         CUDA_TRY(ctx, cudaEventRecord(ln.ev_up[i], ln.ul_stream));
       }
@@ -801,6 +900,56 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     P.out_cr = P.out_cb + cwh * chh;
   }
 
+  // A pageable RGBA output (host_stage.h): rects go to a pinned copy of the canvas, and the pool copies them on into
+  // the caller's memory behind a CUDA event -- in ~1 MB row slices, so a freshly allocated (never touched) output has its
+  // page faults taken by several cores.  stitch_run waits for the slices after the stream.
+  const bool out_pg = stage_ok && out_host && want_rgba && !want_png && (int64_t)cw * 4 * ch >= (256 << 10) &&
+                      stitch::is_pageable(job->out_rgba);
+  const int64_t hp = (int64_t)cw * 4;   // pitch of the pinned canvas
+  if (out_pg) {
+    const size_t need = (size_t)hp * (size_t)ch;
+    if (ln.host_canvas_cap < need) {
+      if (ln.host_canvas) CUDA_TRY(ctx, cudaFreeHost(ln.host_canvas));
+      ln.host_canvas = nullptr;
+      ln.host_canvas_cap = 0;
+      CUDA_TRY(ctx, cudaMallocHost((void**)&ln.host_canvas, need));
+      ln.host_canvas_cap = need;
+    }
+    if (!ln.host_copies) ln.host_copies = new std::atomic<int>(0);
+  }
+  auto download_staged = [&](int x0, int y0, int x1, int y1, cudaStream_t on) -> cudaError_t {
+    if (x1 <= x0 || y1 <= y0) return cudaSuccess;
+    const size_t wbytes = (size_t)(x1 - x0) * 4;
+    uint8_t* pinned = ln.host_canvas + (int64_t)y0 * hp + (int64_t)x0 * 4;
+    cudaError_t e = cudaMemcpy2DAsync(pinned, hp, d_rgba + (int64_t)y0 * d_rgba_pitch + (int64_t)x0 * 4, d_rgba_pitch, wbytes, y1 - y0,
+                                      cudaMemcpyDeviceToHost, on);
+    if (e != cudaSuccess) return e;
+    if (ln.dl_events_used == ln.dl_events.size()) {
+      cudaEvent_t ev;
+      e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+      if (e != cudaSuccess) return e;
+      ln.dl_events.push_back(ev);
+    }
+    const cudaEvent_t ev = ln.dl_events[ln.dl_events_used++];
+    e = cudaEventRecord(ev, on);
+    if (e != cudaSuccess) return e;
+    const int per = (int)std::max<size_t>(1, ((size_t)1 << 20) / wbytes);
+    uint8_t* user = (uint8_t*)job->out_rgba + (int64_t)y0 * rgba_pitch + (int64_t)x0 * 4;
+    std::atomic<int>* counter = ln.host_copies;
+    const int64_t up = rgba_pitch;
+    for (int r = 0; r < y1 - y0; r += per) {
+      const int r1 = std::min(y1 - y0, r + per);
+      counter->fetch_add(1, std::memory_order_relaxed);
+      stitch::CopyPool::get().submit([=] {
+        cudaEventSynchronize(ev);
+        if (up == hp && wbytes == (size_t)hp) std::memcpy(user + (int64_t)r * up, pinned + (int64_t)r * hp, (size_t)(r1 - r) * wbytes);
+        else for (int y = r; y < r1; ++y) std::memcpy(user + (int64_t)y * up, pinned + (int64_t)y * hp, wbytes);
+        counter->fetch_sub(1, std::memory_order_release);
+      });
+    }
+    return cudaSuccess;
+  };
+
   // [4] the draw loop (P:1439-1572)
   stitch::PreparedJob J;
   st = stitch::prepare_job(P, canvas, planes, ctx->sm_count, ln.scratch, ln.stream, &J);
@@ -817,8 +966,12 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   if (!pipelined) {
     for (int i = 0; i < n; ++i) {
       if (!has_upload[i]) continue;
+      if (pend[i]) {
+        CUDA_TRY(ctx, staged.upload_image(i, early ? ln.ul_stream : ln.stream));
+        if (early) CUDA_TRY(ctx, cudaEventRecord(ln.ev_up[i], ln.ul_stream));
+      }
       if (early) CUDA_TRY(ctx, cudaStreamWaitEvent(ln.stream, ln.ev_up[i], 0));   // already on its way (no fast region after all)
-      else CUDA_TRY(ctx, issue_upload(i, ln.stream));
+      else if (!pend[i]) CUDA_TRY(ctx, issue_upload(i, ln.stream));
     }
     if (J.fused) {
       st = stitch::launch_plan(P, J, J.plan, ctx->sm_count, ln.scratch, ln.stream);
@@ -840,7 +993,9 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
 
     // [5] export (U:205-242): the canvas is copied out whole, unscaled (P:1577-1579)
     if (out_host) {
-      if (want_rgba) {
+      if (want_rgba && out_pg) {
+        CUDA_TRY(ctx, download_staged(0, 0, cw, ch, ln.stream));
+      } else if (want_rgba) {
         if ((int64_t)rgba_pitch == (int64_t)d_rgba_pitch && (int64_t)rgba_pitch == (int64_t)cw * 4)
           CUDA_TRY(ctx, cudaMemcpyAsync(job->out_rgba, d_rgba, (size_t)cw * 4 * (size_t)ch, cudaMemcpyDeviceToHost, ln.stream));
         else
@@ -854,6 +1009,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     // one canvas rect home (device pixel coordinates), on the download stream
     auto download = [&](int x0, int y0, int x1, int y1) -> cudaError_t {
       if (x1 <= x0 || y1 <= y0) return cudaSuccess;
+      if (out_pg) return download_staged(x0, y0, x1, y1, ln.dl_stream);
       uint8_t* dst = (uint8_t*)job->out_rgba + (int64_t)y0 * rgba_pitch + (int64_t)x0 * 4;
       const uint8_t* src = d_rgba + (int64_t)y0 * d_rgba_pitch + (int64_t)x0 * 4;
       if (x0 == 0 && x1 == cw && rgba_pitch == d_rgba_pitch && rgba_pitch == (int64_t)cw * 4)   // whole rows: one linear DMA
@@ -863,6 +1019,10 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     bool own_launch[STITCH_MAX_IMAGES] = {};
     Plan sub;
     for (int k = 0; k < n; ++k) {
+      if (pend[k]) {
+        CUDA_TRY(ctx, staged.upload_image(k, ln.ul_stream));
+        CUDA_TRY(ctx, cudaEventRecord(ln.ev_up[k], ln.ul_stream));
+      }
       CUDA_TRY(ctx, cudaStreamWaitEvent(ln.stream, ln.ev_up[k], 0));
       stitch::sub_plan(J.plan, [&](const Region& r) { return (r.kind == REGION_STREAM || r.kind == REGION_UPSCALE) && r.img == k; }, &sub);
       if (sub.n_units == 0) continue;   // no fast region: drawn with the rest
@@ -1060,6 +1220,8 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
     cudaError_t e = cudaStreamSynchronize(ctx->lanes[0].stream);
     if (e != cudaSuccess) st = fail(ctx, STITCH_E_CUDA, std::string("stream sync: ") + cudaGetErrorString(e));
   }
+  if (std::atomic<int>* hc = ctx->lanes[0].host_copies)   // slices of a pageable canvas still on their way (host_stage.h)
+    while (hc->load(std::memory_order_acquire) > 0) std::this_thread::yield();
   if (st == STITCH_OK) {
     emit(ctx, 96);   // P:1581
     emit(ctx, 100);  // P:1611
