@@ -188,6 +188,7 @@ def cpu_reference_run(workload: str, steps: int, warmup: int, threads: int | Non
         RC.render(lay2, bitmaps, [1] * len(dims), want_rgba=not want_yuv or output == "both", want_yuv=want_yuv,
                   precision="f32")
 
+    RC.set_threads(cores)
     for _ in range(warmup):
         one()
     t0 = time.perf_counter()
@@ -195,6 +196,56 @@ def cpu_reference_run(workload: str, steps: int, warmup: int, threads: int | Non
         one()
     dt = time.perf_counter() - t0
     return mp * steps / dt, dt / steps * 1e3, cores, mp
+
+
+def cpu_sanity_baselines(workload: str):
+    """beside the all-cores port, (a) the same port on ONE thread and (b) a library sanity baseline,
+    cv2.resize (INTER_AREA when shrinking, INTER_LINEAR when enlarging) + numpy paste on all cores -- one job each."""
+    out = {}
+    try:
+        v, ms, _, _ = cpu_reference_run(workload, 1, 0, threads=1)
+        out["one_thread"] = {"value": v, "unit": "MP/s", "ms_per_step": ms, "cores": 1}
+    except Exception as e:
+        out["one_thread"] = {"value": None, "note": f"failed: {e}"}
+    try:
+        import cv2
+        import numpy as np
+
+        from oracle import layout_ref as LR
+        from tests import util as U
+        dims, direction, mode, platform, output, _ = WORKLOADS[workload]
+        cores = len(os.sched_getaffinity(0)) or 1
+        cv2.setNumThreads(cores)
+        bitmaps = {}
+        for i, (w, h) in enumerate(dims):
+            if (w, h) not in bitmaps:
+                bitmaps[(w, h)] = U.synth_image(w, h, SEED + i, 0)
+        lay = LR.compute_layout(U.recs(dims), direction, mode, 0, U.profile_of(platform))
+        ss = lay.superSample if lay.superSample != 1 else 1.0
+        cw, ch = int(lay.canvasW), int(lay.canvasH)
+
+        def one():
+            canvas = np.full((ch, cw, 4), 255, np.uint8)
+            for (dx, dy, dw, dh), (w, h) in zip(lay.rects, dims):
+                x0, y0 = int(round(dx * ss)), int(round(dy * ss))
+                tw, th = max(1, int(round(dw * ss))), max(1, int(round(dh * ss)))
+                interp = cv2.INTER_AREA if (tw < w or th < h) else cv2.INTER_LINEAR
+                r = cv2.resize(bitmaps[(w, h)], (tw, th), interpolation=interp)
+                xa, ya, xb, yb = max(0, x0), max(0, y0), min(cw, x0 + tw), min(ch, y0 + th)
+                if xb > xa and yb > ya:
+                    canvas[ya:yb, xa:xb] = r[ya - y0:yb - y0, xa - x0:xb - x0]
+            return canvas
+
+        one()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            one()
+        dt = (time.perf_counter() - t0) / 3
+        out["cv2"] = {"value": cw * ch / 1e6 / dt, "unit": "MP/s", "ms_per_step": dt * 1e3, "cores": cores,
+                      "what": "cv2.resize (INTER_AREA / INTER_LINEAR) + numpy paste, integer-rounded rects: a sanity figure, not the oracle"}
+    except Exception as e:
+        out["cv2"] = {"value": None, "note": f"failed: {e}"}
+    return out
 
 
 def cpu_files_run(files, direction, mode, platform, steps: int, out_kind: str = "png"):
@@ -729,7 +780,10 @@ def main():
             os.sched_setaffinity(0, affinity0)   # the CPU leg uses every host core again
             val, ms, cores, _ = cpu_reference_run(args.workload, max(1, args.cpu_steps), 1)
             line["cpu_baseline"] = {"value": val, "unit": "MP/s", "cores": cores, "kind": "port",
-                                    "sample": f"{max(1, args.cpu_steps)} full job(s), C restatement fp32 + OpenMP ({ms:.0f} ms/job)"}
+                                    "sample": f"{max(1, args.cpu_steps)} full job(s), C restatement fp32 + OpenMP ({ms:.0f} ms/job)",
+                                    "note": "a scalar, un-vectorised port with a float canvas round trip: a soft baseline, stated "
+                                            "and never the target -- the roofline fraction is what measures the kernel"}
+            line["cpu_baseline"].update(cpu_sanity_baselines(args.workload))
         except Exception as e:  # the baseline is a report, never a blocker
             line["cpu_baseline"] = {"value": None, "unit": "MP/s", "cores": 0, "kind": "port", "sample": f"failed: {e}"}
         if e2e_files is not None:

@@ -50,6 +50,11 @@ def load():
     return _lib
 
 
+def set_threads(n: int) -> None:
+    """OpenMP threads the C port uses from now on (bench.py: 1-thread and all-cores CPU baselines)."""
+    load().oracle_set_threads(int(n))
+
+
 def render_preview(bmp: np.ndarray, pl, precision: str = "f64") -> np.ndarray:
     """C twin of raster_ref.render_preview: straight-alpha RGBA8 [canvasH, canvasW, 4]."""
     from .layout_ref import preview_placement

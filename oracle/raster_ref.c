@@ -38,3 +38,13 @@ typedef struct {
 #undef NAME
 
 int oracle_abi(void) { return 1; }
+
+/* threads the OpenMP loops above use from now on (bench.py times the port on 1 thread and on all cores) */
+#ifdef _OPENMP
+#include <omp.h>
+void oracle_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int oracle_max_threads(void) { return omp_get_max_threads(); }
+#else
+void oracle_set_threads(int n) { (void)n; }
+int oracle_max_threads(void) { return 1; }
+#endif
