@@ -20,6 +20,9 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#if defined(__x86_64__) && defined(__GNUC__)
+#include <immintrin.h>
+#endif
 
 namespace stitch {
 
@@ -78,10 +81,41 @@ inline bool is_pageable(const void* p) {
   return a.type == cudaMemoryTypeUnregistered;
 }
 
+// memcpy with non-temporal stores for large blocks: the destination (a pinned ring chunk the DMA engine reads next, or a
+// caller's canvas nobody reads soon) should not be pulled into the cache first (read-for-ownership = a third of the
+// memory traffic of a plain copy).  Falls back to memcpy without AVX2 or for small blocks.
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target("avx2"))) inline void copy_stream_avx2(uint8_t* d, const uint8_t* s, size_t n) {
+  const size_t head = (32 - ((uintptr_t)d & 31)) & 31;
+  if (head) { std::memcpy(d, s, head); d += head; s += head; n -= head; }
+  size_t i = 0;
+  for (; i + 128 <= n; i += 128) {
+    const __m256i a = _mm256_loadu_si256((const __m256i*)(s + i)), b = _mm256_loadu_si256((const __m256i*)(s + i + 32));
+    const __m256i c = _mm256_loadu_si256((const __m256i*)(s + i + 64)), e = _mm256_loadu_si256((const __m256i*)(s + i + 96));
+    _mm256_stream_si256((__m256i*)(d + i), a);
+    _mm256_stream_si256((__m256i*)(d + i + 32), b);
+    _mm256_stream_si256((__m256i*)(d + i + 64), c);
+    _mm256_stream_si256((__m256i*)(d + i + 96), e);
+  }
+  _mm_sfence();
+  if (i < n) std::memcpy(d + i, s + i, n - i);
+}
+inline void copy_big(void* d, const void* s, size_t n) {
+  static const bool nt = [] {
+    const char* e = std::getenv("STITCH_COPY_NT");
+    return !(e && e[0] == '0') && __builtin_cpu_supports("avx2");
+  }();
+  if (nt && n >= (64u << 10)) copy_stream_avx2((uint8_t*)d, (const uint8_t*)s, n);
+  else std::memcpy(d, s, n);
+}
+#else
+inline void copy_big(void* d, const void* s, size_t n) { std::memcpy(d, s, n); }
+#endif
+
 // rows [r0, r1) of a pitched host image -> packed rows of `dpitch` bytes (pad bytes opaque)
 inline void copy_rows_in(uint8_t* dst, int64_t dpitch, const uint8_t* src, int64_t spitch, size_t row_bytes, int r0, int r1) {
   if (spitch == dpitch && (int64_t)row_bytes == dpitch) {
-    std::memcpy(dst, src + (int64_t)r0 * spitch, (size_t)(r1 - r0) * (size_t)dpitch);
+    copy_big(dst, src + (int64_t)r0 * spitch, (size_t)(r1 - r0) * (size_t)dpitch);
     return;
   }
   for (int r = r0; r < r1; ++r) {

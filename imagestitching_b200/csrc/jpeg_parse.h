@@ -39,6 +39,9 @@ inline ParseStatus parse(const uint8_t* p, size_t n, Header* H) {
   std::memset(&H->tab, 0, sizeof(H->tab));
   if (n < 4 || p[0] != 0xFF || p[1] != 0xD8) return kNotJpeg;
   bool have_sof = false, have_h[4] = {false, false, false, false}, have_q[4] = {false, false, false, false};
+  int comp_id[3] = {0, 0, 0};   // SOF component identifiers: the scan must name them in the same order
+  int adobe_transform = -1;     // Adobe APP14 colour transform: 0 = the three components are RGB, not YCbCr
+  bool saw_jfif = false;        // a JFIF APP0 marker settles it: YCbCr
   size_t o = 2;
   while (o + 4 <= n) {
     if (p[o] != 0xFF) return kCorrupt;
@@ -58,6 +61,10 @@ inline ParseStatus parse(const uint8_t* p, size_t n, Header* H) {
         have_q[t] = true;
         i += 65;
       }
+    } else if (m == 0xE0) {
+      if (sl >= 5 && std::memcmp(s, "JFIF", 5) == 0) saw_jfif = true;
+    } else if (m == 0xEE) {
+      if (sl >= 12 && std::memcmp(s, "Adobe", 5) == 0) adobe_transform = s[11];
     } else if (m == 0xC0 || m == 0xC1) {
       if (sl < 6) return kCorrupt;
       if (s[0] != 8) return kUnsupported;
@@ -69,6 +76,7 @@ inline ParseStatus parse(const uint8_t* p, size_t n, Header* H) {
       if (sl < (size_t)(6 + 3 * H->ncomp)) return kCorrupt;
       int hs[3] = {1, 1, 1}, vs[3] = {1, 1, 1};
       for (int c = 0; c < H->ncomp; ++c) {
+        comp_id[c] = s[6 + 3 * c];
         hs[c] = s[7 + 3 * c] >> 4;
         vs[c] = s[7 + 3 * c] & 15;
         H->tq[c] = s[8 + 3 * c];
@@ -108,7 +116,14 @@ inline ParseStatus parse(const uint8_t* p, size_t n, Header* H) {
       if (!have_sof) return kCorrupt;
       if (sl < 1 || s[0] != H->ncomp) return kUnsupported;  // non-interleaved scans
       if (sl < (size_t)(1 + 2 * H->ncomp + 3)) return kCorrupt;
+      // The decoder converts three components as YCbCr.  libjpeg (jdapimin.c default_decompress_parms) takes them as
+      // RGB when there is no JFIF marker and an Adobe marker says transform 0, or -- with neither marker -- when the
+      // component ids are 'R','G','B': such files are refused here rather than decoded to wrong colours.
+      if (H->ncomp == 3 && !saw_jfif &&
+          (adobe_transform == 0 || (adobe_transform < 0 && comp_id[0] == 'R' && comp_id[1] == 'G' && comp_id[2] == 'B')))
+        return kUnsupported;
       for (int c = 0; c < H->ncomp; ++c) {
+        if (s[1 + 2 * c] != comp_id[c]) return kUnsupported;   // scan components in another order than the frame's
         H->td[c] = s[2 + 2 * c] >> 4;
         H->ta[c] = s[2 + 2 * c] & 15;
         if (H->td[c] > 1 || H->ta[c] > 1) return kUnsupported;

@@ -942,7 +942,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       counter->fetch_add(1, std::memory_order_relaxed);
       stitch::CopyPool::get().submit([=] {
         cudaEventSynchronize(ev);
-        if (up == hp && wbytes == (size_t)hp) std::memcpy(user + (int64_t)r * up, pinned + (int64_t)r * hp, (size_t)(r1 - r) * wbytes);
+        if (up == hp && wbytes == (size_t)hp) stitch::copy_big(user + (int64_t)r * up, pinned + (int64_t)r * hp, (size_t)(r1 - r) * wbytes);
         else for (int y = r; y < r1; ++y) std::memcpy(user + (int64_t)y * up, pinned + (int64_t)y * hp, wbytes);
         counter->fetch_sub(1, std::memory_order_release);
       });
@@ -1194,11 +1194,10 @@ extern "C" int stitch_ctx_join(StitchCtx* ctx) {
   if (!ctx) return STITCH_E_BAD_ARG;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   for (size_t k = 1; k < ctx->lanes.size(); ++k) {
-    cudaEvent_t ev;
-    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-    CUDA_TRY(ctx, cudaEventRecord(ev, ctx->lanes[k].stream));
-    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lanes[0].stream, ev, 0));
-    CUDA_TRY(ctx, cudaEventDestroy(ev));
+    Lane& ln = ctx->lanes[k];
+    if (!ln.ev_start) CUDA_TRY(ctx, cudaEventCreateWithFlags(&ln.ev_start, cudaEventDisableTiming));   // the lane's own event, reused
+    CUDA_TRY(ctx, cudaEventRecord(ln.ev_start, ln.stream));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lanes[0].stream, ln.ev_start, 0));
   }
   return STITCH_OK;
 }

@@ -222,6 +222,25 @@ def test_gpu_decoder_errors():
     with pytest.raises(StitchError) as e:
         ctx.decode_jpeg(_jpeg(64, 64, quality=80, progressive=True))
     assert e.value.status == L.E_BAD_IMAGE and "解码异常" in e.value.message
+    # three components that are NOT YCbCr (libjpeg decodes these as RGB): refused, never decoded to wrong colours
+    base = _jpeg(64, 48, quality=85, subsampling=0)
+    app0 = base.index(b"\xff\xe0")          # drop the JFIF APP0 segment: with it libjpeg (and the parser) say YCbCr
+    assert base[app0 + 4:app0 + 9] == b"JFIF\0"
+    base = base[:app0] + base[app0 + 2 + ((base[app0 + 2] << 8) | base[app0 + 3]):]
+    sof = base.index(b"\xff\xc0")
+    sos = base.index(b"\xff\xda")
+    rgb_ids = bytearray(base)
+    for c, ch in enumerate(b"RGB"):            # component ids 'R','G','B' in the frame and the scan header
+        rgb_ids[sof + 4 + 6 + 3 * c] = ch
+        rgb_ids[sos + 4 + 1 + 2 * c] = ch
+    adobe = base[:2] + b"\xff\xee\x00\x0eAdobe\x00\x64\x00\x00\x00\x00\x00" + base[2:]     # APP14, transform = 0
+    swapped = bytearray(base)                  # scan names the components in another order than the frame
+    swapped[sos + 4 + 1], swapped[sos + 4 + 3] = base[sos + 4 + 3], base[sos + 4 + 1]
+    for bad in (bytes(rgb_ids), adobe, bytes(swapped)):
+        with pytest.raises(StitchError) as e:
+            ctx.decode_jpeg(bad)
+        assert e.value.status == L.E_BAD_IMAGE, bad[:4]
+    assert ctx.decode_jpeg(base).shape == (48, 64, 4)
     ctx.close()
 
 

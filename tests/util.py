@@ -21,7 +21,7 @@ def splitmix64(x):
 
 
 def synth_image(w: int, h: int, seed: int, pattern: int = 0) -> np.ndarray:
-    """CPU twin of the on-device generator (imagestitching_b200/csrc/stream_kernel.cuh synth_pixel)."""
+    """CPU twin of the on-device generator (imagestitching_b200/csrc/synth.cuh synth_pixel)."""
     with np.errstate(over="ignore"):
         ys, xs = np.meshgrid(np.arange(h, dtype=np.uint64), np.arange(w, dtype=np.uint64), indexing="ij")
         hsh = splitmix64(np.uint64(seed) ^ (ys * np.uint64(w) + xs))
