@@ -2,7 +2,7 @@
 // (U:27-121, P:1441-1520) so a job can take the FILES instead of 48.8 MB RGBA bitmaps per image.
 //
 // Huffman-coded data has no random access, so the entropy decoder is the self-synchronising one
-// (Klein & Wiseman 2003; Weissenberger & Schmidt 2018): the scan is cut into subsequences of JDEC_SUB raw
+// (Klein & Wiseman 2003; Weissenberger & Schmidt 2018): the scan is cut into subsequences of DecBatch::sub (128 ... 512) raw
 // bytes, one THREAD each.
 //   D1 first pass   every thread decodes its subsequence from its first bit as if a block started there and
 //                   records where it ended: (byte, bit, block-in-MCU, zig-zag index) -- the state the next
@@ -22,14 +22,31 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "jpeg_parse.h"
 
 namespace stitch {
 namespace jpegdec {
 
-#define JDEC_SUB 128          // raw bytes per subsequence
+// Raw bytes per subsequence (DecBatch::sub), chosen per batch by jdec_pick_sub: 512 when that still leaves >= 32 k
+// threads, else 256, else 128.  Long subsequences mean fewer links in the synchronisation chains (the sync kernel's
+// in-block iterations) and fewer wasted symbols after each guessed start: 9 x 12 MP files decode + stitch + export in
+// 3.2 ms/job with 512 against 4.0 with 128 (profiles/r2_decode_ab.md); a single small file keeps 128 for parallelism.
+#define JDEC_SUB_MIN 128
+#define JDEC_SUB_MAX 512
+inline uint32_t jdec_pick_sub(size_t total_scan_bytes) {
+  if (const char* e = std::getenv("STITCH_JDEC_SUB")) {   // tests force every size on small files
+    const int v = std::atoi(e);
+    if (v == 128 || v == 256 || v == 512) return (uint32_t)v;
+  }
+  for (uint32_t sub = JDEC_SUB_MAX; sub > JDEC_SUB_MIN; sub >>= 1)
+    if (total_scan_bytes / sub >= 32768) return sub;
+  return JDEC_SUB_MIN;
+}
+#ifndef JDEC_THREADS
 #define JDEC_THREADS 256
+#endif
 #define JDEC_MAX_IMAGES 9
 
 struct DecImage {
@@ -56,6 +73,7 @@ struct DecBatch {
   int32_t round;              // sync round (0 = first)
   int32_t flag_cur;           // flag this round raises
   int32_t flag_prev;          // flag of the round before (-1: none, the host decides whether to launch)
+  uint32_t sub;               // raw bytes per subsequence (jdec_pick_sub)
 };
 
 // ---- Huffman tables in shared memory ----
@@ -296,11 +314,11 @@ __device__ __forceinline__ State decode_range(const DecImage& I, const SmemTable
 }
 
 
-// Start state of subsequence i when nothing is known: the first data bit of raw byte i * JDEC_SUB, taken as
+// Start state of subsequence i when nothing is known: the first data bit of raw byte i * sub, taken as
 // the DC symbol of the first block of an MCU.  (A stuffed zero or the second byte of an RSTn is stepped over.)
-__device__ __forceinline__ State guess_state(const DecImage& I, uint32_t i) {
+__device__ __forceinline__ State guess_state(const DecImage& I, uint32_t i, uint32_t sub) {
   State s;
-  s.byte = i * JDEC_SUB;
+  s.byte = i * sub;
   s.bit = 0;
   s.b = 0;
   s.z = 0;
@@ -321,7 +339,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_c
   const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
   if (i >= (uint32_t)I.n_sub) return;
   uint32_t started = 0;
-  const State e = decode_range<false>(I, T, guess_state(I, i), (i + 1) * JDEC_SUB, &started, 0);
+  const State e = decode_range<false>(I, T, guess_state(I, i, B.sub), (i + 1) * B.sub, &started, 0);
   I.state[i] = make_uint4(e.byte, pack_state(e), started, 0u);
 }
 
@@ -398,7 +416,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
     if (t < total) {
       s = sh_list[t];
       const uint2 ps = sh_state[s];
-      const State e = decode_range<false>(I, T, unpack_state(ps.x, ps.y), (base + s + 1) * JDEC_SUB, &started, 0);
+      const State e = decode_range<false>(I, T, unpack_state(ps.x, ps.y), (base + s + 1) * B.sub, &started, 0);
       fresh = make_uint2(e.byte, pack_state(e));
     }
     __syncthreads();
@@ -472,7 +490,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_write_kernel(const __grid_c
   if (i == 0) { s.byte = 0; s.bit = 0; s.b = 0; s.z = 0; s.done = false; }
   else { const uint4 p = I.state[i - 1]; s = unpack_state(p.x, p.y); }
   uint32_t started = 0;
-  decode_range<true>(I, T, s, (i + 1) * JDEC_SUB, &started, (int64_t)I.prefix[i]);
+  decode_range<true>(I, T, s, (i + 1) * B.sub, &started, (int64_t)I.prefix[i]);
 }
 
 // D5: DC differences -> DC values, in three steps: (a) per-MCU sums of the differences per component,

@@ -246,6 +246,11 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferr
   struct Carve { size_t scan, tab, state, prefix, coef, plane[3], dcsum, consumed; } cv[JDEC_MAX_IMAGES];
   int max_mcu = 0;
   int max_sub = 0, max_blocks = 0, max_w = 0, max_h = 0;
+  {
+    size_t total_scan = 0;
+    for (int i = 0; i < n; ++i) total_scan += items[i].hdr.scan_len;
+    B.sub = jd::jdec_pick_sub(total_scan);
+  }
   for (int i = 0; i < n; ++i) {
     const jd::Header& H = items[i].hdr;
     jd::DecImage& I = B.img[i];
@@ -253,7 +258,7 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferr
     I.scan_len = (uint32_t)H.scan_len;
     I.w = H.w; I.h = H.h; I.ncomp = H.ncomp; I.hs = H.hs; I.vs = H.vs; I.mcux = H.mcux; I.mcuy = H.mcuy; I.ri = H.ri;
     I.bpm = H.ncomp == 1 ? 1 : H.hs * H.vs + 2;
-    I.n_sub = (int)((H.scan_len + JDEC_SUB - 1) / JDEC_SUB);
+    I.n_sub = (int)((H.scan_len + B.sub - 1) / B.sub);
     if (I.n_sub < 1) I.n_sub = 1;
     I.n_blocks = H.mcux * H.mcuy * I.bpm;
     for (int c = 0; c < 3; ++c) { I.td[c] = H.td[c]; I.ta[c] = H.ta[c]; I.tq[c] = H.tq[c]; }

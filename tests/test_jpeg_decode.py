@@ -215,6 +215,21 @@ def test_gpu_decoder_survives_corruption():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("sub", [128, 256, 512])
+def test_gpu_decoder_every_subsequence_size(sub, monkeypatch):
+    """The batch picks 128 / 256 / 512 raw bytes per subsequence by its size (jdec_pick_sub); every size must give the
+    oracle's bytes -- forced here on small files, restart markers and all three samplings included."""
+    from imagestitching_b200 import StitchContext
+    monkeypatch.setenv("STITCH_JDEC_SUB", str(sub))
+    ctx = StitchContext(0)
+    for i, (w, h) in enumerate([(1210, 908), (333, 200), (64, 48), (805, 1203)]):
+        f = _jpeg(w, h, seed=60 + i, quality=(92, 75, 98, 85)[i], subsampling=(2, 1, 0, 2)[i],
+                  **({"restart_marker_blocks": 3} if i == 3 else {}))
+        assert np.array_equal(ctx.decode_jpeg(f)[:, :, :3], J.decode(f)[:, :, :3]), (sub, w, h)
+    ctx.close()
+
+
+@pytest.mark.gpu
 def test_gpu_decoder_errors():
     from imagestitching_b200 import StitchContext, StitchError
     from imagestitching_b200 import _lib as L
