@@ -1,0 +1,733 @@
+// PNG inputs decoded on the GPU (VERDICT r1 "missing" 2): the bitmap decode of loadImageFrom
+// (U:27-121, P:1441-1463) for the other format real photo lists hold -- screenshots are PNG.
+//
+// A PNG's pixels are ONE zlib stream (the IDAT payloads), then a per-row prediction filter.  DEFLATE has no random
+// access: Huffman codes change per block at arbitrary bit positions and every match copies from the 32 KB before it.
+// The decoder here gets its parallelism from the BLOCKS of the stream for the entropy code (zlib closes a block every
+// 16 k-32 k symbols: a 12 MP photo has > 1000 of them, nine photos > 10 000) and from the BYTES for the copies:
+//   P0 gather    IDAT payloads -> one contiguous stream (the file is uploaded as it is).
+//   P1 find      EVERY bit offset is tested for a dynamic-Huffman block header: type bits, symbol counts and a
+//                COMPLETE code-length code (Kraft sum exactly 1) -- 0.1 % of the offsets of compressed data pass.
+//   P2 validate  a thread per survivor parses the whole header: the literal/length and distance code sets have to be
+//                complete and contain an end-of-block code (zlib's own acceptance rules).  What is left are the real
+//                blocks, and a false candidate per few hundred MB.
+//   P3 count     a thread per candidate decodes its block WITHOUT output: where it ends, how many bytes and matches.
+//   P4 walk      a thread per image follows the chain from the first block (end of one = start of the next), which
+//                drops false candidates; stored / fixed-Huffman blocks (no header to find) and anything P1 missed
+//                are decoded right there.  Output: the real blocks with their output and token offsets.
+//   P5 write     a thread per real block decodes again: literals to their bytes, every match to a token
+//                {position, length, distance} -- a thread alone must not copy 258 bytes per symbol.
+//   P6 expand    tokens -> src[i] = i - distance for every copied byte (short tokens by their lane, long ones by the warp).
+//   P7 resolve   pointer jumping over src[] until every copied byte points at a literal: rounds gated on a device
+//                flag, no host round trip (a run of one repeated byte is a chain as long as the run: log2 rounds).
+//   P8 bytes     every copied byte fetches its value.
+//   P9 transpose rows -> 16-byte chunks interleaved over the 32 rows of a group, so that "lane = row" reads coalesce.
+//   P10 unfilter the five PNG filters as a wavefront: lane = row, a row runs one pixel behind the row above it
+//                (shuffles inside a warp, a progress counter between the 32 warps of the image's CTA).
+//   P11 rgba     gray / RGB / palette / alpha, 1-16 bit -> RGBA8 (16-bit samples keep their high byte, tRNS applied).
+// Huffman tables are per thread, in shared memory (two levels, 10 + 7 first-level bits, interleaved over the CTA's threads).
+// Interlaced (Adam7) files are rejected by the parser.  There is no CPU fallback.
+#include "png_decode.h"
+
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "png_inflate_core.h"
+
+namespace stitch {
+namespace pngdec {
+
+using namespace stitch::pnginf;
+
+#ifndef PINF_THREADS
+#define PINF_THREADS 64          // decoding threads per CTA: 64 x 3520 B of tables = 220 KB of shared memory
+#endif
+constexpr int kJumpRounds = 32;  // >= log2(longest chain: < 2^31 bytes) + 1
+constexpr int kUnfWarps = 32;
+
+struct Img {
+  const uint8_t* file;
+  uint8_t* z;
+  uint32_t z_len, raw_len;
+  uint32_t* surv;
+  uint32_t surv_cap;
+  BlockRec* cand;
+  uint32_t cand_cap;
+  uint32_t* hkey;
+  uint32_t* hval;
+  uint32_t hmask;
+  uint4* chain;        // {bit position, output offset, token offset, -} of the real blocks, stream order
+  uint32_t chain_cap;
+  uint32_t* ctr;       // [0] survivors [1] candidates [2] real blocks [3] tokens
+  uint8_t* raw;        // inflated bytes: (filter byte + row) x h
+  uint32_t* src;
+  Token* tok;
+  uint32_t tok_cap;
+  uint32_t* rawT;      // filtered rows, transposed (t_word)
+  uint32_t* outT;      // unfiltered rows, same layout
+  uint32_t t_chunks;   // 16-byte chunks per row
+  uint32_t* progress;  // [ceil(h / 32)] pixels finished in the last row of each 32-row group
+  const uint32_t* palette;
+  int32_t w, h, depth, ctype, channels, bpp;
+  uint32_t row_bytes;
+  int32_t has_key;
+  uint32_t key[3];
+  uint8_t* rgba;
+  int64_t pitch;
+};
+struct Batch {
+  Img img[kMaxImages];
+  int32_t n;
+  uint32_t* status;    // error bits
+  uint32_t* flags;     // [kJumpRounds] "a pointer moved in round r"
+  uint16_t* slow;      // per decoding thread: kSlowWords uint16
+  const IdatPiece* pieces;
+  int32_t flag_cur, flag_prev;
+};
+
+// ---- P0 ----
+__global__ void __launch_bounds__(256) pinf_gather_kernel(Batch B) {
+  const IdatPiece pc = B.pieces[blockIdx.x];
+  const Img& I = B.img[pc.img];
+  const uint8_t* s = I.file + pc.file_off;
+  uint8_t* d = I.z + pc.dst_off;
+  for (uint32_t k = threadIdx.x; k < pc.len; k += 256) d[k] = s[k];
+}
+
+// ---- P1: one thread per stream byte, its 8 bit offsets ----
+__global__ void __launch_bounds__(256) pinf_find_kernel(Batch B) {
+  const Img& I = B.img[blockIdx.y];
+  const uint32_t byte = blockIdx.x * 256u + threadIdx.x;
+  const uint32_t z_bits = I.z_len * 8u;
+  const bool live = byte >= 2 && byte < I.z_len;
+  uint64_t b0 = 0, b1 = 0;
+  if (live) {
+    b0 = bits_at(I.z, byte * 8u);
+    b1 = bits_at(I.z, byte * 8u + 64u);
+  }
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll 1
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t p = byte * 8u + (uint32_t)j;
+    bool hit = false;
+    if (live && p + 32u <= z_bits) {
+      const uint64_t b = j ? (b0 >> j) | (b1 << (64 - j)) : b0;
+      hit = header_prefilter(b, b1 >> j);
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (m) {
+      uint32_t base = 0;
+      if (lane == 0) base = atomicAdd(&I.ctr[0], (uint32_t)__popc(m));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (hit) {
+        const uint32_t slot = base + (uint32_t)__popc(m & ((1u << lane) - 1u));
+        if (slot < I.surv_cap) I.surv[slot] = p;
+      }
+    }
+  }
+}
+
+// flattened work list over the images of a batch: item -> (image, index)
+struct Flat {
+  uint32_t start[kMaxImages + 1];
+  __device__ Flat(const Batch& B, int which) {
+    uint32_t t = 0;
+    for (int i = 0; i < kMaxImages; ++i) {
+      start[i] = t;
+      if (i < B.n) {
+        const Img& I = B.img[i];
+        const uint32_t c = I.ctr[which];
+        const uint32_t cap = which == 0 ? I.surv_cap : which == 1 ? I.cand_cap : which == 2 ? I.chain_cap : I.tok_cap;
+        t += c < cap ? c : cap;
+      }
+    }
+    start[kMaxImages] = t;
+  }
+  __device__ uint32_t total() const { return start[kMaxImages]; }
+  __device__ int image_of(uint32_t item) const {
+    int i = 0;
+#pragma unroll
+    for (int k = 1; k < kMaxImages; ++k) i += item >= start[k];
+    return i;
+  }
+};
+
+// ---- P2: full header parse of the survivors; the valid ones become candidates (+ hash entry by bit position) ----
+__global__ void __launch_bounds__(128) pinf_validate_kernel(Batch B) {
+  const Flat F(B, 0);
+  uint8_t lens[320];
+  for (uint32_t item = blockIdx.x * 128u + threadIdx.x; item < F.total(); item += gridDim.x * 128u) {
+    const int im = F.image_of(item);
+    const Img& I = B.img[im];
+    const uint32_t p = I.surv[item - F.start[im]];
+    BitReader br;
+    br.init(I.z, p);
+    br.skip(3);
+    int nlen, ndist;
+    if (!read_dynamic_lengths(br, lens, &nlen, &ndist, I.z_len * 8u)) continue;
+    const uint32_t idx = atomicAdd(&I.ctr[1], 1u);
+    if (idx >= I.cand_cap) continue;
+    I.cand[idx].bitpos = p;
+    I.cand[idx].flags = 0;
+    uint32_t slot = hash_pos(p) & I.hmask;
+    for (;;) {
+      const uint32_t old = atomicCAS(&I.hkey[slot], 0u, p + 1u);
+      if (old == 0u) break;
+      slot = (slot + 1u) & I.hmask;
+    }
+    I.hval[slot] = idx;
+  }
+}
+
+__device__ __forceinline__ HuffTables thread_tables(const Batch& B, uint16_t* smem) {
+  HuffTables T;
+  T.stride = blockDim.x;
+  T.lit = smem + threadIdx.x;
+  T.dist = smem + (size_t)blockDim.x * kLitEntries + threadIdx.x;
+  bind_slow(T, B.slow + (size_t)(blockIdx.x * blockDim.x + threadIdx.x) * kSlowWords);
+  return T;
+}
+
+// ---- P3: a thread per candidate, count mode.  The item loop and the symbol loop are warp-uniform (see DecState). ----
+__global__ void __launch_bounds__(PINF_THREADS) pinf_count_kernel(Batch B) {
+  extern __shared__ __align__(16) uint16_t pinf_smem[];
+  HuffTables T = thread_tables(B, pinf_smem);
+  const Flat F(B, 1);
+  uint8_t lens[320];
+  const uint32_t lane = threadIdx.x & 31;
+  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < F.total(); base += gridDim.x * blockDim.x) {
+    const uint32_t item = base + lane;
+    DecState st;
+    st.status = kDone;
+    BlockRec* rec = nullptr;
+    if (item < F.total()) {
+      const int im = F.image_of(item);
+      const Img& I = B.img[im];
+      rec = &I.cand[item - F.start[im]];
+      block_begin<false>(st, I.z, I.z_len, rec->bitpos, T, lens, 0, I.raw_len, nullptr);
+    }
+    while (__any_sync(0xffffffffu, st.status == kRunning))
+      if (st.status == kRunning) symbol_step<false>(st, T, nullptr, nullptr);
+    if (rec && st.status == kDone) block_end(st, rec);
+  }
+}
+
+// ---- P4: one thread per image walks the chain ----
+__global__ void __launch_bounds__(32) pinf_walk_kernel(Batch B) {
+  __shared__ uint16_t lut[kLitEntries + kDistEntries];
+  __shared__ uint16_t slow[kSlowWords];
+  __shared__ uint8_t lens[320];
+  if (threadIdx.x != 0) return;
+  const Img& I = B.img[blockIdx.x];
+  HuffTables T;
+  T.stride = 1;
+  T.lit = lut;
+  T.dist = lut + kLitEntries;
+  bind_slow(T, slow);
+  const uint32_t n_cand = I.ctr[1] < I.cand_cap ? I.ctr[1] : I.cand_cap;
+  uint32_t pos = 16, out = 0, nt = 0, nb = 0, err = 0;
+  for (;;) {
+    BlockRec rec;
+    rec.flags = 0;
+    if (n_cand) {
+      uint32_t slot = hash_pos(pos) & I.hmask;
+      for (;;) {
+        const uint32_t k = I.hkey[slot];
+        if (k == 0u) break;
+        if (k == pos + 1u) {
+          rec = I.cand[I.hval[slot]];
+          break;
+        }
+        slot = (slot + 1u) & I.hmask;
+      }
+    }
+    if (!(rec.flags & kRecValid) || rec.n_out > I.raw_len - out) {
+      if (decode_block<false>(I.z, I.z_len, pos, T, lens, &rec, 0, I.raw_len - out, nullptr, nullptr) != kBlockOk) {
+        err = kErrStream;
+        break;
+      }
+    }
+    if (nb >= I.chain_cap || rec.n_tok > I.tok_cap - nt) {
+      err = kErrCapacity;
+      break;
+    }
+    I.chain[nb++] = make_uint4(pos, out, nt, 0u);
+    out += rec.n_out;
+    nt += rec.n_tok;
+    pos = rec.end_bit;
+    if (rec.flags & kRecFinal) break;
+  }
+  if (!err && out != I.raw_len) err = kErrStream;   // libpng: "Not enough image data" / "Too much image data"
+  I.ctr[2] = err ? 0u : nb;
+  I.ctr[3] = err ? 0u : nt;
+  if (err) atomicOr(B.status, err);
+}
+
+// ---- P5: a thread per real block, write mode ----
+__global__ void __launch_bounds__(PINF_THREADS) pinf_write_kernel(Batch B) {
+  extern __shared__ __align__(16) uint16_t pinf_smem[];
+  HuffTables T = thread_tables(B, pinf_smem);
+  const Flat F(B, 2);
+  uint8_t lens[320];
+  const uint32_t lane = threadIdx.x & 31;
+  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < F.total(); base += gridDim.x * blockDim.x) {
+    const uint32_t item = base + lane;
+    DecState st;
+    st.status = kDone;
+    uint8_t* lit = nullptr;
+    Token* tok = nullptr;
+    if (item < F.total()) {
+      const int im = F.image_of(item);
+      const Img& I = B.img[im];
+      const uint4 blk = I.chain[item - F.start[im]];
+      lit = I.raw;
+      tok = I.tok + blk.z;
+      block_begin<true>(st, I.z, I.z_len, blk.x, T, lens, blk.y, I.raw_len, lit);
+    }
+    while (__any_sync(0xffffffffu, st.status == kRunning))
+      if (st.status == kRunning) symbol_step<true>(st, T, lit, tok);
+    if (st.status != kDone) atomicOr(B.status, (uint32_t)kErrStream);
+  }
+}
+
+// ---- P6: tokens -> src[].  A lane expands its own token when it is short; long ones are spread over the warp. ----
+__global__ void __launch_bounds__(256) pinf_expand_kernel(Batch B) {
+  const Flat F(B, 3);
+  const uint32_t total = F.total();
+  const unsigned lane = threadIdx.x & 31;
+  for (uint32_t base = (blockIdx.x * 256u + threadIdx.x) & ~31u; base < total; base += gridDim.x * 256u) {
+    const uint32_t item = base + lane;
+    uint32_t pos = 0, len = 0, dist = 1;
+    uint32_t* src = nullptr;
+    if (item < total) {
+      const int im = F.image_of(item);
+      const Img& I = B.img[im];
+      const Token t = I.tok[item - F.start[im]];
+      pos = t.pos;
+      len = t.len_dist >> 15;
+      dist = (t.len_dist & 0x7FFFu) + 1u;
+      src = I.src;
+    }
+    if (len <= 8) {
+      for (uint32_t k = 0; k < len; ++k) src[pos + k] = pos + k - dist;
+      len = 0;
+    }
+    unsigned m = __ballot_sync(0xffffffffu, len != 0);
+    while (m) {
+      const int l = __ffs(m) - 1;
+      m &= m - 1;
+      const uint32_t p = __shfl_sync(0xffffffffu, pos, l), n = __shfl_sync(0xffffffffu, len, l), d = __shfl_sync(0xffffffffu, dist, l);
+      uint32_t* s = reinterpret_cast<uint32_t*>(__shfl_sync(0xffffffffu, (unsigned long long)src, l));
+      for (uint32_t k = lane; k < n; k += 32) s[p + k] = p + k - d;
+    }
+  }
+}
+
+// ---- P7: one pointer-jumping round over src[] (4 entries per thread) ----
+__global__ void __launch_bounds__(256) pinf_jump_kernel(Batch B) {
+  if (B.flag_prev >= 0 && B.flags[B.flag_prev] == 0u) return;   // the round before moved nothing: converged
+  const Img& I = B.img[blockIdx.y];
+  const uint32_t i4 = blockIdx.x * 256u + threadIdx.x;
+  if ((uint64_t)i4 * 4u >= I.raw_len) return;
+  uint4 s = reinterpret_cast<uint4*>(I.src)[i4];
+  bool ch = false;
+  uint32_t* e = &s.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (e[k] != kRoot) {
+      const uint32_t s2 = I.src[e[k]];
+      if (s2 != kRoot) {
+        e[k] = s2;
+        ch = true;
+      }
+    }
+  }
+  if (ch) {
+    reinterpret_cast<uint4*>(I.src)[i4] = s;
+    B.flags[B.flag_cur] = 1u;
+  }
+}
+
+// ---- P8: copied bytes fetch their values ----
+__global__ void __launch_bounds__(256) pinf_bytes_kernel(Batch B) {
+  const Img& I = B.img[blockIdx.y];
+  const uint32_t i4 = blockIdx.x * 256u + threadIdx.x;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && B.flags[kJumpRounds - 1] != 0u) atomicOr(B.status, (uint32_t)kErrResolve);
+  if ((uint64_t)i4 * 4u >= I.raw_len) return;
+  const uint4 s = reinterpret_cast<const uint4*>(I.src)[i4];
+  const uint32_t* e = &s.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    if (e[k] != kRoot) I.raw[i4 * 4u + k] = I.raw[e[k]];   // the padding entries past raw_len are kRoot
+}
+
+// ---- P9: transpose.  Word j (4 bytes) of row y's payload lives at t_word(): the 16-byte chunks of the 32 rows of a
+// group are interleaved, so a warp whose lanes own the rows of a group reads / writes neighbouring chunks together.
+__device__ __forceinline__ size_t t_word(uint32_t chunks, int y, uint32_t j) {
+  return (((size_t)(y >> 5) * chunks + (j >> 2)) * 32 + (size_t)(y & 31)) * 4 + (j & 3);
+}
+__device__ __forceinline__ uint32_t t_byte(const uint32_t* t, uint32_t chunks, int y, uint32_t b) {
+  return reinterpret_cast<const uint8_t*>(t)[t_word(chunks, y, b >> 2) * 4 + (b & 3)];
+}
+
+__global__ void __launch_bounds__(256) png_transpose_kernel(Batch B) {
+  const Img& I = B.img[blockIdx.z];
+  const uint32_t j = blockIdx.x * 256u + threadIdx.x;
+  const int y = (int)blockIdx.y;
+  if (y >= I.h || j >= I.t_chunks * 4u) return;
+  const uint8_t* row = I.raw + (size_t)y * (I.row_bytes + 1u) + 1;
+  uint32_t w = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const uint32_t b = j * 4u + (uint32_t)k;
+    if (b < I.row_bytes) w |= (uint32_t)row[b] << (8 * k);
+  }
+  I.rawT[t_word(I.t_chunks, y, j)] = w;
+}
+
+// ---- P10: unfilter (PNG spec clause 9) ----
+__device__ __forceinline__ int paeth(int a, int b, int c) {
+  const int p = a + b - c;
+  const int pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+  return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+__device__ __forceinline__ uint32_t shfl_px(uint32_t v, int srcl) { return __shfl_sync(0xffffffffu, v, srcl); }
+__device__ __forceinline__ uint64_t shfl_px(uint64_t v, int srcl) { return __shfl_sync(0xffffffffu, (unsigned long long)v, srcl); }
+__device__ __forceinline__ uint32_t shfl_up_px(uint32_t v) { return __shfl_up_sync(0xffffffffu, v, 1); }
+__device__ __forceinline__ uint64_t shfl_up_px(uint64_t v) { return __shfl_up_sync(0xffffffffu, (unsigned long long)v, 1); }
+
+// One CTA per image.  Lane l of a warp owns row 32 g + l of the warp's current group g and works on pixel s - l at
+// step s, so the pixel above (lane l - 1, one step earlier) arrives by shuffle and left / upper-left are the lane's
+// own previous values.  Lane 0's upper row belongs to the group before -- another warp -- which publishes how far its
+// last row has got every 32 steps; its bytes are read back through L2.  Rows stream through two small byte queues
+// per lane (4-byte loads from rawT, 4-byte stores to outT).
+template <typename PX>
+__device__ void unfilter_image(const Batch& B, const Img& I) {
+  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  const int bpp = I.bpp;
+  const uint32_t chunks = I.t_chunks;
+  const int wp = (int)(I.row_bytes / (uint32_t)bpp);
+  const uint32_t n_words = (I.row_bytes + 3u) >> 2;
+  const int groups = (I.h + 31) / 32;
+  const uint64_t pmask = bpp >= 8 ? ~0ull : ((1ull << (8 * bpp)) - 1ull);
+  volatile uint32_t* progress = I.progress;
+  for (int g = wv; g < groups; g += kUnfWarps) {
+    const int y = g * 32 + lane;
+    const bool active = y < I.h;
+    const int yy = active ? y : g * 32;
+    int ft = active ? I.raw[(size_t)y * (I.row_bytes + 1u)] : 0;
+    if (ft > 4) {
+      atomicOr(B.status, (uint32_t)kErrFilter);
+      ft = 0;
+    }
+    PX left = 0, ul = 0, prev = 0, upbatch = 0;
+    uint64_t inbuf = 0, outbuf = 0;
+    int incnt = 0, outcnt = 0;
+    uint32_t inj = 0, outj = 0;
+    uint32_t pre = (active && n_words) ? I.rawT[t_word(chunks, yy, 0)] : 0u;   // always one word ahead
+    const int steps = wp + 31;
+    for (int s = 0; s < steps; ++s) {
+      if ((s & 31) == 0 && g && s < wp) {
+        const uint32_t need = (uint32_t)min(wp, s + 32);
+        while (progress[g - 1] < need) {
+        }
+        __threadfence();
+        const int px = s + lane;
+        PX v = 0;
+        if (px < wp) {
+#pragma unroll
+          for (int k = 0; k < (int)sizeof(PX); ++k)
+            if (k < bpp)
+              v |= (PX)__ldcg(reinterpret_cast<const uint8_t*>(I.outT) + t_word(chunks, g * 32 - 1, ((uint32_t)px * bpp + k) >> 2) * 4 +
+                              (((uint32_t)px * bpp + k) & 3)) << (8 * k);
+        }
+        upbatch = v;
+      }
+      const PX from_batch = shfl_px(upbatch, s & 31);
+      const PX from_below = shfl_up_px(prev);
+      const PX up = lane == 0 ? (g ? from_batch : (PX)0) : from_below;
+      const int x = s - lane;
+      const bool valid = active && x >= 0 && x < wp;
+      if (x == 0) {
+        left = 0;
+        ul = 0;
+      }
+      PX cur = 0;
+      if (valid) {
+        while (incnt < bpp) {
+          inbuf |= (uint64_t)pre << (8 * incnt);
+          incnt += 4;
+          ++inj;
+          pre = inj < n_words ? I.rawT[t_word(chunks, yy, inj)] : 0u;
+        }
+        const PX f = (PX)(inbuf & pmask);
+        inbuf = bpp >= 8 ? 0ull : inbuf >> (8 * bpp);
+        incnt -= bpp;
+#pragma unroll
+        for (int k = 0; k < (int)sizeof(PX); ++k) {
+          if (k < bpp) {
+            const int a = (int)((left >> (8 * k)) & 0xFF), b = (int)((up >> (8 * k)) & 0xFF), c = (int)((ul >> (8 * k)) & 0xFF);
+            const int pred = ft == 1 ? a : ft == 2 ? b : ft == 3 ? ((a + b) >> 1) : ft == 4 ? paeth(a, b, c) : 0;
+            cur |= (PX)((((int)((f >> (8 * k)) & 0xFF)) + pred) & 0xFF) << (8 * k);
+          }
+        }
+        outbuf |= (uint64_t)cur << (8 * outcnt);
+        outcnt += bpp;
+        while (outcnt >= 4) {
+          I.outT[t_word(chunks, yy, outj++)] = (uint32_t)outbuf;
+          outbuf >>= 32;
+          outcnt -= 4;
+        }
+        if (x == wp - 1 && outcnt > 0) {
+          I.outT[t_word(chunks, yy, outj++)] = (uint32_t)outbuf;
+          outcnt = 0;
+        }
+      }
+      left = cur;
+      ul = up;
+      prev = cur;
+      if ((s & 31) == 31 || s == steps - 1) {
+        __syncwarp();
+        if (lane == 31 && active) {
+          __threadfence();
+          const uint32_t done = s == steps - 1 ? (uint32_t)wp : (outj * 4u) / (uint32_t)bpp;
+          progress[g] = done;
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(32 * kUnfWarps) png_unfilter_kernel(Batch B) {
+  const Img& I = B.img[blockIdx.x];
+  if (*B.status) return;   // a damaged stream: the bitmap is not delivered
+  if (I.bpp <= 4) unfilter_image<uint32_t>(B, I);
+  else unfilter_image<uint64_t>(B, I);
+}
+
+// ---- P11: samples -> RGBA8 ----
+__global__ void __launch_bounds__(256) png_rgba_kernel(Batch B) {
+  const Img& I = B.img[blockIdx.z];
+  const int x = blockIdx.x * 64 + (threadIdx.x & 63);
+  const int y = blockIdx.y * 4 + (threadIdx.x >> 6);
+  if (x >= I.w || y >= I.h) return;
+  const uint32_t* T = I.outT;
+  const uint32_t ch = I.t_chunks;
+  uint32_t r, g, b, a = 255;
+  if (I.depth < 8) {
+    const uint32_t bit = (uint32_t)x * (uint32_t)I.depth;
+    const uint32_t v = (t_byte(T, ch, y, bit >> 3) >> (8 - I.depth - (int)(bit & 7))) & ((1u << I.depth) - 1u);
+    if (I.ctype == 3) {
+      const uint32_t p = I.palette[v];
+      r = p & 0xFF; g = (p >> 8) & 0xFF; b = (p >> 16) & 0xFF; a = p >> 24;
+    } else {
+      r = g = b = v * (255u / ((1u << I.depth) - 1u));
+      if (I.has_key && v == I.key[0]) a = 0;
+    }
+  } else {
+    const int sb = I.depth >> 3;   // bytes per sample
+    const uint32_t p0 = (uint32_t)x * (uint32_t)I.channels * (uint32_t)sb;
+    uint32_t smp[4], full[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      smp[c] = 0;
+      full[c] = 0;
+      if (c < I.channels) {
+        smp[c] = t_byte(T, ch, y, p0 + c * sb);   // 16-bit samples: the high byte (libpng's png_set_strip_16)
+        full[c] = sb == 2 ? (smp[c] << 8) | t_byte(T, ch, y, p0 + c * sb + 1) : smp[c];
+      }
+    }
+    switch (I.ctype) {
+      case 0:
+        r = g = b = smp[0];
+        if (I.has_key && full[0] == I.key[0]) a = 0;
+        break;
+      case 2:
+        r = smp[0]; g = smp[1]; b = smp[2];
+        if (I.has_key && full[0] == I.key[0] && full[1] == I.key[1] && full[2] == I.key[2]) a = 0;
+        break;
+      case 3: {
+        const uint32_t q = I.palette[smp[0]];
+        r = q & 0xFF; g = (q >> 8) & 0xFF; b = (q >> 16) & 0xFF; a = q >> 24;
+        break;
+      }
+      case 4:
+        r = g = b = smp[0];
+        a = smp[1];
+        break;
+      default:
+        r = smp[0]; g = smp[1]; b = smp[2]; a = smp[3];
+        break;
+    }
+  }
+  *reinterpret_cast<uint32_t*>(I.rgba + (size_t)y * I.pitch + (size_t)x * 4) = r | (g << 8) | (b << 16) | (a << 24);
+}
+
+// ---- host ----
+void free_arena(Arena& arena) {
+  if (arena.p) cudaFree(arena.p);
+  arena.p = nullptr;
+  arena.cap = 0;
+}
+
+#define PNG_TRY(x)                        \
+  do {                                    \
+    const cudaError_t e__ = (x);          \
+    if (e__ != cudaSuccess) return e__;   \
+  } while (0)
+
+cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStream_t stream, uint32_t* status_host, int sm_count, int* launches) {
+  if (n <= 0) return cudaSuccess;
+  if (n > kMaxImages) return cudaErrorInvalidValue;
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  const int dec_ctas = sm_count > 0 ? sm_count : 148;
+  const size_t dec_smem = (size_t)PINF_THREADS * (kLitEntries + kDistEntries) * sizeof(uint16_t);
+  static bool attr_done[64] = {};
+  {
+    int dev = 0;
+    PNG_TRY(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+      PNG_TRY(cudaFuncSetAttribute(pinf_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem));
+      PNG_TRY(cudaFuncSetAttribute(pinf_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem));
+      attr_done[dev] = true;
+    }
+  }
+  Batch B;
+  std::memset(&B, 0, sizeof B);
+  B.n = n;
+  // zeroed region first: status, flags, then per image counters / hash keys / progress
+  struct Carve { size_t ctr, hkey, progress, file, z, surv, cand, hval, chain, raw, src, tok, rawT, outT, palette; } cv[kMaxImages];
+  size_t need = 0;
+  const size_t o_status = need; need += 256;
+  const size_t o_flags = need; need += up(kJumpRounds * 4);
+  size_t n_pieces = 0;
+  uint32_t max_z = 0, max_raw = 0, max_chunks = 1;
+  int max_w = 0, max_h = 0;
+  for (int i = 0; i < n; ++i) {
+    const Header& H = items[i].hdr;
+    Img& I = B.img[i];
+    I.z_len = H.z_len;
+    I.raw_len = (uint32_t)H.raw_len;
+    I.surv_cap = H.z_len / 16 + 1024;
+    I.cand_cap = H.z_len / 128 + 256;
+    uint32_t hs = 1024;
+    while (hs < 2 * I.cand_cap) hs <<= 1;
+    I.hmask = hs - 1;
+    I.chain_cap = H.z_len / 8 + 64;
+    I.tok_cap = I.raw_len / 3 + 1;                       // a match makes at least 3 bytes
+    I.t_chunks = (H.row_bytes + 15) / 16;
+    I.w = H.w; I.h = H.h; I.depth = H.depth; I.ctype = H.ctype; I.channels = H.channels; I.bpp = H.bpp;
+    I.row_bytes = H.row_bytes;
+    I.has_key = H.has_key;
+    for (int c = 0; c < 3; ++c) I.key[c] = H.key[c];
+    I.rgba = items[i].rgba;
+    I.pitch = items[i].pitch;
+    Carve& c = cv[i];
+    c.ctr = need; need += 256;
+    c.hkey = need; need += up((size_t)hs * 4);
+    c.progress = need; need += up((size_t)((H.h + 31) / 32) * 4);
+    n_pieces += H.idat.size();
+    max_z = std::max(max_z, H.z_len);
+    max_raw = std::max(max_raw, I.raw_len);
+    max_chunks = std::max(max_chunks, I.t_chunks);
+    max_w = std::max(max_w, H.w);
+    max_h = std::max(max_h, H.h);
+  }
+  const size_t zero_bytes = need;
+  for (int i = 0; i < n; ++i) {
+    const Img& I = B.img[i];
+    Carve& c = cv[i];
+    c.file = need; need += up(items[i].bytes + 16);
+    c.z = need; need += up((size_t)I.z_len + 64);
+    c.surv = need; need += up((size_t)I.surv_cap * 4);
+    c.cand = need; need += up((size_t)I.cand_cap * sizeof(BlockRec));
+    c.hval = need; need += up((size_t)(I.hmask + 1) * 4);
+    c.chain = need; need += up((size_t)I.chain_cap * 16);
+    c.raw = need; need += up((size_t)I.raw_len + 16);
+    c.src = need; need += up(((size_t)I.raw_len + 15) / 16 * 16 * 4);
+    c.tok = need; need += up((size_t)I.tok_cap * sizeof(Token));
+    {
+      const size_t t_bytes = (size_t)((I.h + 31) / 32) * I.t_chunks * 32 * 16;
+      c.rawT = need; need += up(t_bytes);
+      c.outT = need; need += up(t_bytes);
+    }
+    c.palette = need; need += 1024;
+  }
+  const size_t o_slow = need; need += up((size_t)dec_ctas * PINF_THREADS * kSlowWords * 2);
+  const size_t o_pieces = need; need += up(n_pieces * sizeof(IdatPiece));
+  if (arena.cap < need) {
+    if (arena.p) {
+      PNG_TRY(cudaStreamSynchronize(stream));
+      PNG_TRY(cudaFree(arena.p));
+    }
+    arena.p = nullptr;
+    arena.cap = 0;
+    PNG_TRY(cudaMalloc(&arena.p, need));
+    arena.cap = need;
+  }
+  uint8_t* A = (uint8_t*)arena.p;
+  B.status = (uint32_t*)(A + o_status);
+  B.flags = (uint32_t*)(A + o_flags);
+  B.slow = (uint16_t*)(A + o_slow);
+  B.pieces = (const IdatPiece*)(A + o_pieces);
+  PNG_TRY(cudaMemsetAsync(A, 0, zero_bytes, stream));
+  std::vector<IdatPiece> pieces;
+  pieces.reserve(n_pieces);
+  for (int i = 0; i < n; ++i) {
+    Img& I = B.img[i];
+    const Carve& c = cv[i];
+    I.ctr = (uint32_t*)(A + c.ctr);
+    I.hkey = (uint32_t*)(A + c.hkey);
+    I.progress = (uint32_t*)(A + c.progress);
+    I.file = A + c.file;
+    I.z = A + c.z;
+    I.surv = (uint32_t*)(A + c.surv);
+    I.cand = (BlockRec*)(A + c.cand);
+    I.hval = (uint32_t*)(A + c.hval);
+    I.chain = (uint4*)(A + c.chain);
+    I.raw = A + c.raw;
+    I.src = (uint32_t*)(A + c.src);
+    I.tok = (Token*)(A + c.tok);
+    I.rawT = (uint32_t*)(A + c.rawT);
+    I.outT = (uint32_t*)(A + c.outT);
+    I.palette = (const uint32_t*)(A + c.palette);
+    PNG_TRY(cudaMemcpyAsync(A + c.file, items[i].file, items[i].bytes, cudaMemcpyHostToDevice, stream));
+    PNG_TRY(cudaMemcpyAsync(A + c.palette, items[i].hdr.palette, 1024, cudaMemcpyHostToDevice, stream));
+    PNG_TRY(cudaMemsetAsync(I.z + (I.z_len & ~3u), 0, 64, stream));   // the bit readers run a few words past the end
+    PNG_TRY(cudaMemsetAsync(I.src, 0xFF, ((size_t)I.raw_len + 15) / 16 * 16 * 4, stream));
+    for (IdatPiece pc : items[i].hdr.idat) {
+      pc.img = (uint32_t)i;
+      pieces.push_back(pc);
+    }
+  }
+  PNG_TRY(cudaMemcpyAsync(A + o_pieces, pieces.data(), pieces.size() * sizeof(IdatPiece), cudaMemcpyHostToDevice, stream));
+  int nl = 0;
+  pinf_gather_kernel<<<(unsigned)pieces.size(), 256, 0, stream>>>(B);
+  pinf_find_kernel<<<dim3((max_z + 255) / 256, n), 256, 0, stream>>>(B);
+  pinf_validate_kernel<<<dec_ctas * 8, 128, 0, stream>>>(B);
+  pinf_count_kernel<<<dec_ctas, PINF_THREADS, dec_smem, stream>>>(B);
+  pinf_walk_kernel<<<n, 32, 0, stream>>>(B);
+  pinf_write_kernel<<<dec_ctas, PINF_THREADS, dec_smem, stream>>>(B);
+  pinf_expand_kernel<<<dec_ctas * 8, 256, 0, stream>>>(B);
+  nl += 7;
+  const dim3 g4((max_raw / 4 + 256) / 256, n);
+  for (int r = 0; r < kJumpRounds; ++r) {
+    B.flag_cur = r;
+    B.flag_prev = r - 1;
+    pinf_jump_kernel<<<g4, 256, 0, stream>>>(B);
+    ++nl;
+  }
+  pinf_bytes_kernel<<<g4, 256, 0, stream>>>(B);
+  png_transpose_kernel<<<dim3((max_chunks * 4 + 255) / 256, max_h, n), 256, 0, stream>>>(B);
+  png_unfilter_kernel<<<n, 32 * kUnfWarps, 0, stream>>>(B);
+  png_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, stream>>>(B);
+  nl += 4;
+  PNG_TRY(cudaGetLastError());
+  if (status_host) PNG_TRY(cudaMemcpyAsync(status_host, B.status, 4, cudaMemcpyDeviceToHost, stream));
+  if (launches) *launches += nl;
+  return cudaSuccess;
+}
+
+}  // namespace pngdec
+}  // namespace stitch

@@ -26,6 +26,7 @@
 #include "host_stage.h"
 #include "jpeg_kernels.cuh"
 #include "jpeg_decode.cuh"
+#include "png_decode.h"
 #include "png_kernels.cuh"
 #include "synth.cuh"
 
@@ -42,7 +43,7 @@ struct PendingJob {
   int status = STITCH_OK;
   std::string error;
   StitchResult* res = nullptr;
-  bool dec = false, jpeg = false, png = false, out_host = true;
+  bool dec = false, pngdec = false, jpeg = false, png = false, out_host = true;
   const uint8_t* j_file = nullptr;   // device file staging (host outputs)
   const uint8_t* p_file = nullptr;
   StitchJob job;                     // for the synchronous redo when the decoder needed more rounds
@@ -50,7 +51,7 @@ struct PendingJob {
 };
 
 // words of a lane's pinned info block
-enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_WORDS = 8 };
+enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_PNGDEC_STATUS = 5, INFO_WORDS = 8 };
 
 // One job lane: a stream with its own unit-scheduler counters and its own staging, so that jobs
 // submitted to different lanes overlap -- the next job's blocks fill the SM slots the draining one
@@ -86,6 +87,8 @@ struct Lane {
   // JPEG decode: grow-only arena (scan bytes, tables, subsequence states, coefficients, component planes)
   void* dec_arena = nullptr;
   size_t dec_arena_cap = 0;
+  stitch::pngdec::Arena pngdec_arena;   // PNG-input decoder (png_decode.cu)
+  bool pngdec_active = false;        // the job on this lane decodes PNG files: check INFO_PNGDEC_STATUS when it is done
   // PNG export: grow-only arena (RGBA canvas when the caller did not ask for it, code tables, coded bands, file)
   void* png_arena = nullptr;
   size_t png_arena_cap = 0;
@@ -197,6 +200,7 @@ void free_lane(Lane& ln) {
   if (ln.out_stage) cudaFree(ln.out_stage);
   if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
   if (ln.dec_arena) cudaFree(ln.dec_arena);
+  stitch::pngdec::free_arena(ln.pngdec_arena);
   if (ln.png_arena) cudaFree(ln.png_arena);
   if (ln.info_host) cudaFreeHost(ln.info_host);
   if (ln.dl_stream) { cudaStreamSynchronize(ln.dl_stream); cudaStreamDestroy(ln.dl_stream); }
@@ -364,6 +368,47 @@ int parse_jpeg(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::
   std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
                 ps == stitch::jpegdec::kUnsupported ? "JPEG variant not supported: baseline Huffman, 4:4:4 / 4:2:2 / 4:2:0 / gray only"
                 : ps == stitch::jpegdec::kNotJpeg ? "not a JPEG file" : "corrupt JPEG headers");
+  return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+}
+
+int parse_png(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::pngdec::Header* H) {
+  const stitch::pngdec::ParseStatus ps = stitch::pngdec::parse((const uint8_t*)file, bytes, H);
+  if (ps == stitch::pngdec::kOk) return STITCH_OK;
+  char buf[128];
+  std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
+                ps == stitch::pngdec::kUnsupported ? "PNG variant not supported: interlaced, or larger than 2 GiB inflated"
+                : ps == stitch::pngdec::kNotPng ? "not a PNG file" : "corrupt PNG chunks");
+  return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+}
+
+// GPU decode of the PNG files of a job (png_decode.cu): all launches on the lane's stream, nothing waits; the
+// decoder's status word arrives in the lane's info block behind them.
+int decode_png_batch(StitchCtx* ctx, Lane& ln, stitch::pngdec::DecodeItem* items, int n) {
+  if (n <= 0) return STITCH_OK;
+  const int st = ensure_info(ctx, ln);
+  if (st != STITCH_OK) return st;
+  ln.info_host[INFO_PNGDEC_STATUS] = 0;
+  int launches = 0;
+  const cudaError_t e = stitch::pngdec::decode_batch(ln.pngdec_arena, items, n, ln.stream, (uint32_t*)&ln.info_host[INFO_PNGDEC_STATUS],
+                                                     ctx->sm_count, &launches);
+  if (e == cudaErrorMemoryAllocation) {
+    cudaGetLastError();
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (PNG decode buffers allocation failed)");
+  }
+  if (e != cudaSuccess) return fail(ctx, STITCH_E_CUDA, std::string("PNG decode: ") + cudaGetErrorString(e));
+  ctx->launches += launches;
+  ln.pngdec_active = true;
+  return STITCH_OK;
+}
+
+// After the lane's stream has drained: did the PNG decoder accept its streams?
+int check_png_status(StitchCtx* ctx, Lane& ln) {
+  if (!ln.pngdec_active) return STITCH_OK;
+  ln.pngdec_active = false;
+  const uint32_t bits = (uint32_t)ln.info_host[INFO_PNGDEC_STATUS];
+  if (!bits) return STITCH_OK;
+  char buf[96];
+  std::snprintf(buf, sizeof buf, "图片解码异常 (PNG data damaged: status 0x%x)", bits);
   return fail(ctx, STITCH_E_BAD_IMAGE, buf);
 }
 
@@ -684,7 +729,11 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   StitchImageDesc descs[STITCH_MAX_IMAGES];
   int bw[STITCH_MAX_IMAGES], bh[STITCH_MAX_IMAGES];
   DecodeItem dec[STITCH_MAX_IMAGES];
-  int n_dec = 0;
+  std::vector<stitch::pngdec::DecodeItem> pdec_store;
+  int n_dec = 0, n_pdec = 0;
+  for (int i = 0; i < n; ++i)
+    if (job->images[i].mem_kind == STITCH_MEM_HOST_PNG) { pdec_store.resize(STITCH_MAX_IMAGES); break; }
+  stitch::pngdec::DecodeItem* pdec = pdec_store.data();
   int st = STITCH_OK;
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
@@ -701,6 +750,24 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       d.file = (const uint8_t*)im.data;
       d.bytes = (size_t)im.pitch_bytes;
       st = parse_jpeg(ctx, im.data, d.bytes, i, &d.hdr);
+      if (st != STITCH_OK) return st;
+      bw[i] = d.hdr.w;
+      bh[i] = d.hdr.h;
+      if (descs[i].natural_width <= 0 || descs[i].natural_height <= 0) {
+        descs[i].natural_width = descs[i].width = d.hdr.w;      // P:729-732
+        descs[i].natural_height = descs[i].height = d.hdr.h;
+      }
+      if (descs[i].file_size <= 0) descs[i].file_size = im.pitch_bytes;   // P:733
+    } else if (im.mem_kind == STITCH_MEM_HOST_PNG) {
+      if (!im.data || im.pitch_bytes <= 0) {
+        char buf[64];
+        std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
+        return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+      }
+      stitch::pngdec::DecodeItem& d = pdec[n_pdec++];
+      d.file = (const uint8_t*)im.data;
+      d.bytes = (size_t)im.pitch_bytes;
+      st = parse_png(ctx, im.data, d.bytes, i, &d.hdr);
       if (st != STITCH_OK) return st;
       bw[i] = d.hdr.w;
       bh[i] = d.hdr.h;
@@ -745,7 +812,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   // bitmaps (P:1512-1514); a STITCH_MEM_HOST_JPEG image is a FILE the GPU decodes (loadImageFrom, U:27-121)
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
-    if (im.mem_kind == STITCH_MEM_HOST_JPEG) continue;   // parsed above
+    if (im.mem_kind == STITCH_MEM_HOST_JPEG || im.mem_kind == STITCH_MEM_HOST_PNG) continue;   // parsed above
     if (!im.data || im.bmp_width <= 0 || im.bmp_height <= 0) {
       char buf[64];
       std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -772,7 +839,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
     if (u.linear) return cudaMemcpyAsync(u.dst, u.src, (size_t)u.dpitch * u.rows, cudaMemcpyHostToDevice, on);
     return cudaMemcpy2DAsync(u.dst, u.dpitch, u.src, u.spitch, u.row_bytes, u.rows, cudaMemcpyHostToDevice, on);
   };
-  int k_dec = 0, n_host = 0;
+  int k_dec = 0, k_pdec = 0, n_host = 0;
   int64_t host_bytes = 0;
   // pageable host memory is staged by the library itself, for the synchronous entry point (host_stage.h)
   static const bool host_stage_on = [] { const char* e = std::getenv("STITCH_HOST_STAGE"); return !(e && e[0] == '0'); }();
@@ -816,6 +883,15 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       ++k_dec;
       dptr = (const uint8_t*)ln.in_stage[i];
       pitch = dpitch;
+    } else if (im.mem_kind == STITCH_MEM_HOST_PNG) {
+      const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
+      st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
+      if (st != STITCH_OK) return st;
+      pdec[k_pdec].rgba = (uint8_t*)ln.in_stage[i];
+      pdec[k_pdec].pitch = dpitch;
+      ++k_pdec;
+      dptr = (const uint8_t*)ln.in_stage[i];
+      pitch = dpitch;
     } else if (im.mem_kind == STITCH_MEM_DEVICE) {
       dptr = (const uint8_t*)im.data;
     } else {
@@ -856,6 +932,10 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   const bool deferred = defer != nullptr;
   if (n_dec > 0) {
     st = decode_batch(ctx, ln, dec, n_dec, deferred);
+    if (st != STITCH_OK) return st;
+  }
+  if (n_pdec > 0) {
+    st = decode_png_batch(ctx, ln, pdec, n_pdec);
     if (st != STITCH_OK) return st;
   }
 
@@ -1086,6 +1166,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
   if (deferred && (n_dec > 0 || want_jpeg || want_png)) {
     defer->deferred = true;
     defer->dec = n_dec > 0;
+    defer->pngdec = n_pdec > 0;
     defer->jpeg = want_jpeg;
     defer->png = want_png;
     defer->out_host = out_host;
@@ -1122,6 +1203,8 @@ void finalize_job(StitchCtx* ctx, PendingJob& pj) {
       if (pj.png && pj.status == STITCH_OK) pj.status = PngExport::finish(ctx, ln, pj.res, pj.out_host, pj.p_file, pj.job.out_png);
     }
   }
+  if (pj.status == STITCH_OK) pj.status = check_png_status(ctx, ln);
+  ln.pngdec_active = false;
   if (pj.status != STITCH_OK) pj.error = ctx->last_error;
   if (pj.status == STITCH_OK) {
     emit(ctx, 96);   // P:1581
@@ -1226,6 +1309,8 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
   }
   if (std::atomic<int>* hc = ctx->lanes[0].host_copies)   // slices of a pageable canvas still on their way (host_stage.h)
     while (hc->load(std::memory_order_acquire) > 0) std::this_thread::yield();
+  if (st == STITCH_OK) st = check_png_status(ctx, ctx->lanes[0]);
+  ctx->lanes[0].pngdec_active = false;
   if (st == STITCH_OK) {
     emit(ctx, 96);   // P:1581
     emit(ctx, 100);  // P:1611
@@ -1353,6 +1438,47 @@ extern "C" int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes
     CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
   return STITCH_OK;
+}
+
+extern "C" int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                                 int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "context is busy");
+  if (!file) return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Lane& ln = ctx->lanes[0];
+  drain_lane(ctx, ln);
+  stitch::pngdec::DecodeItem d;
+  d.file = (const uint8_t*)file;
+  d.bytes = bytes;
+  int st = parse_png(ctx, file, bytes, 0, &d.hdr);
+  if (info) {
+    std::memset(info, 0, sizeof(*info));
+    StitchImageInfo probe;
+    if (stitch_probe_image(file, bytes, &probe) == STITCH_OK) *info = probe;
+  }
+  if (st != STITCH_OK) return st;
+  const int w = d.hdr.w, h = d.hdr.h;
+  const int64_t pitch = out_pitch ? out_pitch : (int64_t)w * 4;
+  if (!out_rgba || pitch < (int64_t)w * 4 || (pitch & 3) || out_capacity < pitch * (int64_t)(h - 1) + (int64_t)w * 4)
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (decode output buffer missing or too small)");
+  const bool out_host = out_mem_kind != STITCH_MEM_DEVICE;
+  if (out_host) {
+    const int64_t dpitch = ((int64_t)w * 4 + 15) & ~15LL;
+    st = ensure_stage(ctx, ln, 0, (size_t)(dpitch * h));
+    if (st != STITCH_OK) return st;
+    d.rgba = (uint8_t*)ln.in_stage[0];
+    d.pitch = dpitch;
+  } else {
+    d.rgba = (uint8_t*)out_rgba;
+    d.pitch = pitch;
+  }
+  st = decode_png_batch(ctx, ln, &d, 1);
+  if (st != STITCH_OK) return st;
+  if (out_host)
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+  return check_png_status(ctx, ln);
 }
 
 extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {

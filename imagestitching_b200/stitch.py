@@ -290,6 +290,17 @@ class StitchContext:
             _raise(st, self.handle)
         return out
 
+    def decode_png(self, file_bytes: bytes) -> np.ndarray:
+        """loadImageFrom (utils/canvas.js:27-121) for a PNG file: RGBA8 [h, w, 4] with straight alpha, inflated,
+        unfiltered and converted on the GPU (png_decode.cu)."""
+        info = get_image_info(file_bytes)
+        out = np.empty((info["height"], info["width"], 4), dtype=np.uint8)
+        buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")
+        st = self.lib.stitch_decode_png(self.handle, buf, len(file_bytes), out.ctypes.data, out.nbytes, 0, L.MEM_HOST, None)
+        if st != L.OK:
+            _raise(st, self.handle)
+        return out
+
     def build_job(self, images: Sequence[Dict[str, Any]], direction: str, mode: Optional[str], gap,
                   profile: L.StitchProfile, output: str, out_device: bool = False, out_rgba_ptr: int = 0,
                   out_yuv_ptr: int = 0, out_rgba_capacity: int = 0, out_yuv_capacity: int = 0, out_jpeg_ptr: int = 0,
@@ -300,11 +311,11 @@ class StitchContext:
         for i, img in enumerate(images):
             arr[i].desc = _desc(img)
             bmp = img.get("bitmap")
-            if bmp is None and img.get("file") is not None:      # a JPEG FILE: decoded on the GPU (loadImageFrom)
+            if bmp is None and img.get("file") is not None:      # a JPEG / PNG FILE: decoded on the GPU (loadImageFrom)
                 data = img["file"] if isinstance(img["file"], bytes) else bytes(img["file"])
                 arr[i].data = C.cast(C.c_char_p(data), C.c_void_p)      # no copy: `data` is kept alive below
                 arr[i].pitch_bytes = len(data)
-                arr[i].mem_kind = L.MEM_HOST_JPEG
+                arr[i].mem_kind = L.MEM_HOST_PNG if data[:8] == b"\x89PNG\r\n\x1a\n" else L.MEM_HOST_JPEG
                 keep.append(data)
             elif isinstance(bmp, DeviceBitmap):
                 arr[i].data = bmp.ptr

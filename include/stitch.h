@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 6
+#define STITCH_ABI_VERSION 7
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -124,7 +124,10 @@ int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 
 /* STITCH_MEM_HOST_JPEG: `data` is a baseline JPEG FILE in host memory and pitch_bytes its length in bytes; the
  * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
-typedef enum StitchMemKind { STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2 } StitchMemKind;
+/* STITCH_MEM_HOST_PNG: the same for a PNG FILE (non-interlaced; gray / RGB / palette / alpha, 1-16 bit, tRNS). */
+typedef enum StitchMemKind {
+  STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2, STITCH_MEM_HOST_PNG = 3
+} StitchMemKind;
 typedef enum StitchOutputFlags {
   STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4, STITCH_OUT_PNG = 8
 } StitchOutputFlags;
@@ -228,6 +231,17 @@ int stitch_prepare_record(const StitchImageInfo* info, int64_t file_size, Stitch
  * fallback.  out_pitch 0 = packed.  `info` (optional) receives the probe result.  Synchronous. */
 int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
                        int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
+
+/* The same for a PNG file (the other format photo lists hold: screenshots).  The zlib stream of the IDAT chunks is
+ * inflated on the GPU -- every bit offset is tested for a deflate block header, the blocks are decoded in parallel
+ * and the matches that reach back across a block boundary are resolved by pointer jumping (png_decode.cu) -- then
+ * unfiltered as a wavefront over rows and converted to RGBA8 with straight alpha: gray / RGB / palette / gray+alpha
+ * / RGBA at 1-16 bit, tRNS (palette alpha or colour key) applied, 16-bit samples reduced to their high byte, gAMA /
+ * iCCP ignored -- what PIL's Image.convert("RGBA") returns.  Interlaced (Adam7) files, files that inflate to
+ * >= 2 GiB and damaged files return STITCH_E_BAD_IMAGE (P:1508-1513); critical-chunk CRCs are checked, IDAT CRCs and
+ * the Adler-32 are not.  There is no CPU fallback.  Synchronous. */
+int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                      int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
 
 /* ---- preview of the exported image on the page's <canvas> (P:1593-1603) ----
  * createHighResCanvas(node, size.width, size.height) (U:17-24) restores the canvas to floor(size * dpr)

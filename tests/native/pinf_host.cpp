@@ -1,0 +1,104 @@
+// CPU drive of imagestitching_b200/csrc/png_inflate_core.h: the same inline functions the GPU kernels of
+// png_decode.cu call, run one "thread" after another in the kernels' order (find -> validate -> count -> walk ->
+// write -> expand -> resolve -> bytes).  TEST CODE ONLY: tests/test_png_decode.py holds its output against zlib; nothing in
+// the library links it.
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <vector>
+
+#include "png_inflate_core.h"
+
+using namespace stitch::pnginf;
+
+namespace {
+struct Thread {
+  std::vector<uint16_t> lit, dist, slow;
+  HuffTables T;
+  uint8_t lens[320];
+  Thread() : lit(kLitEntries), dist(kDistEntries), slow(kSlowWords) {
+    T.lit = lit.data();
+    T.dist = dist.data();
+    T.stride = 1;
+    bind_slow(T, slow.data());
+  }
+};
+}  // namespace
+
+// stats: [0] prefilter survivors, [1] candidates, [2] chain blocks, [3] blocks the walker had to decode itself,
+//        [4] resolve rounds, [5] bytes that are copies
+extern "C" int pinf_host_inflate(const uint8_t* z_in, uint32_t z_len, uint32_t raw_len, uint8_t* out, uint32_t* stats) {
+  std::vector<uint8_t> zbuf((size_t)z_len + 32, 0);
+  std::memcpy(zbuf.data(), z_in, z_len);
+  const uint8_t* z = zbuf.data();
+  const uint32_t z_bits = z_len * 8u;
+  Thread th;
+  std::memset(stats, 0, 6 * sizeof(uint32_t));
+  // find + validate
+  std::vector<uint32_t> surv;
+  for (uint32_t p = 16; p + 32 <= z_bits; ++p)
+    if (header_prefilter(bits_at(z, p), bits_at(z, p + 64))) surv.push_back(p);
+  stats[0] = (uint32_t)surv.size();
+  std::map<uint32_t, BlockRec> cand;
+  for (uint32_t p : surv) {
+    BitReader br;
+    br.init(z, p);
+    br.take(3);
+    int nlen, ndist;
+    if (!read_dynamic_lengths(br, th.lens, &nlen, &ndist, z_bits)) continue;
+    // count
+    BlockRec rec;
+    if (decode_block<false>(z, z_len, p, th.T, th.lens, &rec, 0, raw_len, nullptr, nullptr) != kBlockOk) continue;
+    cand[p] = rec;
+  }
+  stats[1] = (uint32_t)cand.size();
+  // walk
+  struct Real { uint32_t bitpos, out, tok; };
+  std::vector<Real> chain;
+  uint32_t pos = 16, outp = 0, tokp = 0;
+  for (;;) {
+    BlockRec rec;
+    auto it = cand.find(pos);
+    if (it != cand.end()) {
+      rec = it->second;
+    } else {
+      if (decode_block<false>(z, z_len, pos, th.T, th.lens, &rec, 0, raw_len - outp, nullptr, nullptr) != kBlockOk) return 1;
+      stats[3]++;
+    }
+    if (rec.n_out > raw_len - outp) return 2;
+    chain.push_back(Real{pos, outp, tokp});
+    outp += rec.n_out;
+    tokp += rec.n_tok;
+    pos = rec.end_bit;
+    if (rec.flags & kRecFinal) break;
+  }
+  stats[2] = (uint32_t)chain.size();
+  if (outp != raw_len) return 3;
+  // write: literals + tokens
+  std::vector<uint32_t> src(raw_len, kRoot);
+  std::vector<Token> tok(tokp + 1);
+  for (const Real& b : chain)
+    if (decode_block<true>(z, z_len, b.bitpos, th.T, th.lens, nullptr, b.out, raw_len, out, tok.data() + b.tok) != kBlockOk) return 4;
+  // expand
+  for (uint32_t t = 0; t < tokp; ++t) {
+    const uint32_t len = tok[t].len_dist >> 15, dist = (tok[t].len_dist & 0x7FFFu) + 1u;
+    for (uint32_t k = 0; k < len; ++k) src[tok[t].pos + k] = tok[t].pos + k - dist;
+  }
+  for (uint32_t i = 0; i < raw_len; ++i) stats[5] += src[i] != kRoot;
+  // resolve
+  for (;;) {
+    bool changed = false;
+    for (uint32_t i = 0; i < raw_len; ++i) {
+      const uint32_t s = src[i];
+      if (s == kRoot) continue;
+      const uint32_t s2 = src[s];
+      if (s2 != kRoot) { src[i] = s2; changed = true; }
+    }
+    if (!changed) break;
+    if (++stats[4] > 64) return 5;
+  }
+  for (uint32_t i = 0; i < raw_len; ++i)
+    if (src[i] != kRoot) out[i] = out[src[i]];
+  return 0;
+}
