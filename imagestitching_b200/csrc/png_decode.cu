@@ -11,12 +11,17 @@
 //   P2 validate  a thread per survivor parses the whole header: the literal/length and distance code sets have to be
 //                complete and contain an end-of-block code (zlib's own acceptance rules).  What is left are the real
 //                blocks, and a false candidate per few hundred MB.
-//   P3 count     a thread per candidate decodes its block WITHOUT output: where it ends, how many bytes and matches.
+//   P3 count     a CTA per candidate decodes its block WITHOUT output: where it ends, how many bytes and matches.  Inside
+//                the block the code tables are known, so the block's bits are cut into subsequences of 512 bits, one
+//                thread each: a thread starts at its cut as if a symbol began there and runs to the first symbol
+//                boundary past the next cut; then every thread restarts from where its predecessor really ended until
+//                no start moves any more (Huffman streams re-synchronise after a few symbols: 2-3 rounds).  The exact
+//                start / end / output offset of every subsequence is kept for P5.
 //   P4 walk      a thread per image follows the chain from the first block (end of one = start of the next), which
 //                drops false candidates; stored / fixed-Huffman blocks (no header to find) and anything P1 missed
 //                are decoded right there.  Output: the real blocks with their output and token offsets.
-//   P5 write     a thread per real block decodes again: literals to their bytes, every match to a token
-//                {position, length, distance} -- a thread alone must not copy 258 bytes per symbol.
+//   P5 write     a CTA per real block, a thread per subsequence (now exact): literals to their bytes, every match to a
+//                token {position, length, distance} -- a thread alone must not copy 258 bytes per symbol.
 //   P6 expand    tokens -> src[i] = i - distance for every copied byte (short tokens by their lane, long ones by the warp).
 //   P7 resolve   pointer jumping over src[] until every copied byte points at a literal: rounds gated on a device
 //                flag, no host round trip (a run of one repeated byte is a chain as long as the run: log2 rounds).
@@ -25,11 +30,13 @@
 //   P10 unfilter the five PNG filters as a wavefront: lane = row, a row runs one pixel behind the row above it
 //                (shuffles inside a warp, a progress counter between the 32 warps of the image's CTA).
 //   P11 rgba     gray / RGB / palette / alpha, 1-16 bit -> RGBA8 (16-bit samples keep their high byte, tRNS applied).
-// Huffman tables are per thread, in shared memory (two levels, 10 + 7 first-level bits, interleaved over the CTA's threads).
+// Huffman tables: one set per CTA in shared memory (two levels, 10 + 7 first-level bits).
 // Interlaced (Adam7) files are rejected by the parser.  There is no CPU fallback.
 #include "png_decode.h"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -40,9 +47,8 @@ namespace pngdec {
 
 using namespace stitch::pnginf;
 
-#ifndef PINF_THREADS
-#define PINF_THREADS 64          // decoding threads per CTA: 64 x 3520 B of tables = 220 KB of shared memory
-#endif
+constexpr int kSubBits = 512;      // nominal length of a subsequence of a block's bits
+constexpr int kBlkThreads = 256;   // subsequences per window (one CTA pass over 16 KB of the block)
 constexpr int kJumpRounds = 32;  // >= log2(longest chain: < 2^31 bytes) + 1
 constexpr int kUnfWarps = 32;
 
@@ -57,9 +63,11 @@ struct Img {
   uint32_t* hkey;
   uint32_t* hval;
   uint32_t hmask;
-  uint4* chain;        // {bit position, output offset, token offset, -} of the real blocks, stream order
+  uint4* chain;        // {bit position, output offset, token offset, first window} of the real blocks, stream order
   uint32_t chain_cap;
-  uint32_t* ctr;       // [0] survivors [1] candidates [2] real blocks [3] tokens
+  uint4* sub;          // subsequence records, per window: {count, next window, -, -} then count x {start, end, out, tok}
+  uint32_t sub_cap;
+  uint32_t* ctr;       // [0] survivors [1] candidates [2] real blocks [3] tokens [4] subsequence records [5-7] statistics
   uint8_t* raw;        // inflated bytes: (filter byte + row) x h
   uint32_t* src;
   Token* tok;
@@ -81,7 +89,6 @@ struct Batch {
   int32_t n;
   uint32_t* status;    // error bits
   uint32_t* flags;     // [kJumpRounds] "a pointer moved in round r"
-  uint16_t* slow;      // per decoding thread: kSlowWords uint16
   const IdatPiece* pieces;
   int32_t flag_cur, flag_prev;
 };
@@ -180,36 +187,206 @@ __global__ void __launch_bounds__(128) pinf_validate_kernel(Batch B) {
   }
 }
 
-__device__ __forceinline__ HuffTables thread_tables(const Batch& B, uint16_t* smem) {
+// ---- P3 / P5: a CTA per block ----
+struct BlkSmem {
+  uint16_t lut[kLitEntries + kDistEntries];
+  uint16_t slow[kSlowWords];
+  uint8_t lens[320];
+  uint32_t s_end[kBlkThreads];
+  uint32_t s_flag[kBlkThreads];   // 0 ran through to its cut, 1 met the end-of-block code, 2 not a code / past the stream
+  uint32_t warp_a[kBlkThreads / 32], warp_b[kBlkThreads / 32];
+  uint32_t ok, p0, hdr, alloc;
+};
+
+__device__ __forceinline__ HuffTables cta_tables(BlkSmem& S) {
   HuffTables T;
-  T.stride = blockDim.x;
-  T.lit = smem + threadIdx.x;
-  T.dist = smem + (size_t)blockDim.x * kLitEntries + threadIdx.x;
-  bind_slow(T, B.slow + (size_t)(blockIdx.x * blockDim.x + threadIdx.x) * kSlowWords);
+  T.stride = 1;
+  T.lit = S.lut;
+  T.dist = S.lut + kLitEntries;
+  bind_slow(T, S.slow);
   return T;
 }
 
-// ---- P3: a thread per candidate, count mode.  The item loop and the symbol loop are warp-uniform (see DecState). ----
-__global__ void __launch_bounds__(PINF_THREADS) pinf_count_kernel(Batch B) {
-  extern __shared__ __align__(16) uint16_t pinf_smem[];
-  HuffTables T = thread_tables(B, pinf_smem);
-  const Flat F(B, 1);
-  uint8_t lens[320];
-  const uint32_t lane = threadIdx.x & 31;
-  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < F.total(); base += gridDim.x * blockDim.x) {
-    const uint32_t item = base + lane;
-    DecState st;
-    st.status = kDone;
-    BlockRec* rec = nullptr;
-    if (item < F.total()) {
-      const int im = F.image_of(item);
-      const Img& I = B.img[im];
-      rec = &I.cand[item - F.start[im]];
-      block_begin<false>(st, I.z, I.z_len, rec->bitpos, T, lens, 0, I.raw_len, nullptr);
+// Symbols from the state's position up to the first symbol boundary at or past stop_bit.  Every lane of the warp
+// calls this (go = false: nothing to do) so the symbol loop stays converged.
+template <bool WRITE>
+__device__ __forceinline__ void run_range(DecState& st, const HuffTables& T, uint32_t stop_bit, bool go, uint8_t* lit, Token* tok) {
+  bool running = go && st.status == kRunning && st.br.pos() < stop_bit;
+  while (__any_sync(0xffffffffu, running)) {
+    if (running) {
+      symbol_step<WRITE>(st, T, lit, tok);
+      running = st.status == kRunning && st.br.pos() < stop_bit;
     }
-    while (__any_sync(0xffffffffu, st.status == kRunning))
-      if (st.status == kRunning) symbol_step<false>(st, T, nullptr, nullptr);
-    if (rec && st.status == kDone) block_end(st, rec);
+  }
+}
+
+__device__ __forceinline__ void start_at(DecState& st, const uint8_t* z, uint32_t z_len, uint32_t bit, uint32_t out_pos, uint32_t out_limit) {
+  st.z_bits = z_len * 8u;
+  st.pos = st.out_start = out_pos;
+  st.out_limit = out_limit;
+  st.n_tok = 0;
+  st.bitpos = bit;
+  st.end_bit = 0;
+  st.hdr = 0;
+  st.status = bit < st.z_bits ? (uint32_t)kRunning : (uint32_t)kBad;
+  if (st.status == kRunning) st.br.init(z, bit);
+}
+
+// exclusive scan of two values over the CTA; totals returned to every thread
+__device__ __forceinline__ void cta_scan2(BlkSmem& S, uint32_t a, uint32_t b, uint32_t* ea, uint32_t* eb, uint32_t* ta, uint32_t* tb) {
+  const unsigned lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  uint32_t ia = a, ib = b;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t xa = __shfl_up_sync(0xffffffffu, ia, d), xb = __shfl_up_sync(0xffffffffu, ib, d);
+    if ((int)lane >= d) {
+      ia += xa;
+      ib += xb;
+    }
+  }
+  __syncthreads();
+  if (lane == 31) {
+    S.warp_a[wv] = ia;
+    S.warp_b[wv] = ib;
+  }
+  __syncthreads();
+  uint32_t oa = 0, ob = 0, sa = 0, sb = 0;
+#pragma unroll
+  for (int k = 0; k < kBlkThreads / 32; ++k) {
+    const uint32_t va = S.warp_a[k], vb = S.warp_b[k];
+    if (k < (int)wv) {
+      oa += va;
+      ob += vb;
+    }
+    sa += va;
+    sb += vb;
+  }
+  *ea = oa + ia - a;
+  *eb = ob + ib - b;
+  *ta = sa;
+  *tb = sb;
+}
+
+__global__ void __launch_bounds__(kBlkThreads, 2) pinf_count_kernel(Batch B) {
+  __shared__ BlkSmem S;
+  const Flat F(B, 1);
+  const HuffTables T = cta_tables(S);
+  const uint32_t tid = threadIdx.x;
+  for (uint32_t item = blockIdx.x; item < F.total(); item += gridDim.x) {
+    const int im = F.image_of(item);
+    const Img& I = B.img[im];
+    BlockRec* rec = &I.cand[item - F.start[im]];
+    const uint32_t z_bits = I.z_len * 8u;
+    __syncthreads();
+    if (tid == 0) {
+      DecState st;
+      HuffTables Tw = T;
+      block_begin<false>(st, I.z, I.z_len, rec->bitpos, Tw, S.lens, 0, I.raw_len, nullptr);
+      S.ok = st.status == kRunning;
+      S.p0 = S.ok ? st.br.pos() : 0u;
+      S.hdr = st.hdr;
+    }
+    __syncthreads();
+    if (!S.ok) continue;
+    uint32_t wstart = S.p0, tot_out = 0, tot_tok = 0, first_sub = kNoSub, prev_hdr = kNoSub, end_bit = 0;
+    bool fail = false, done = false;
+    while (!done && !fail) {
+      const uint32_t nominal_start = wstart + tid * (uint32_t)kSubBits, nominal_end = nominal_start + (uint32_t)kSubBits;
+      // Every thread keeps (and publishes) the result of its latest run; it runs again only when its predecessor ran
+      // through to an end that is not where this thread started.  A guessed run that meets a false end-of-block code
+      // therefore stalls its successors for a round or two instead of wiping their results.
+      uint32_t cached_start = kNoSub, my_end = 0, my_flag = 2, my_out = 0, my_tok = 0;
+      uint32_t first = kBlkThreads;   // first subsequence that did not run through: end-of-block code, or not a code
+      for (int round = 0;; ++round) {
+        uint32_t want = tid == 0 ? wstart : nominal_start;
+        bool need = round == 0;
+        if (round > 0 && tid > 0 && S.s_flag[tid - 1] == 0u) {
+          want = S.s_end[tid - 1];
+          need = want != cached_start;
+        }
+        DecState st;
+        st.status = kDone;
+        if (need) start_at(st, I.z, I.z_len, want, 0, I.raw_len);
+        run_range<false>(st, T, nominal_end, need, nullptr, nullptr);
+        bool changed = false;
+        if (need) {
+          const uint32_t f = st.status == kRunning ? 0u : st.status == kDone ? 1u : 2u;
+          const uint32_t e = st.status == kDone ? st.end_bit : st.status == kRunning ? st.br.pos() : 0u;
+          changed = f != my_flag || e != my_end || round == 0;
+          cached_start = want;
+          my_flag = f;
+          my_end = e;
+          my_out = st.pos;
+          my_tok = st.n_tok;
+        }
+        const unsigned stops = __ballot_sync(0xffffffffu, my_flag != 0u);
+        __syncthreads();   // every thread has read its predecessor
+        S.s_end[tid] = my_end;
+        S.s_flag[tid] = my_flag;
+        if ((tid & 31) == 0) S.warp_b[tid >> 5] = stops;
+        const bool any = __syncthreads_or(changed);
+        if (!any) {
+          first = kBlkThreads;
+#pragma unroll
+          for (int k = kBlkThreads / 32 - 1; k >= 0; --k) {
+            const uint32_t m = S.warp_b[k];
+            if (m) first = (uint32_t)k * 32u + (uint32_t)(__ffs(m) - 1);
+          }
+          if (tid == 0) {   // statistics (STITCH_PNG_DEBUG)
+            atomicAdd(&I.ctr[5], (uint32_t)round + 1u);
+            atomicMax(&I.ctr[6], (uint32_t)round + 1u);
+            atomicAdd(&I.ctr[7], 1u);
+          }
+          break;
+        }
+      }
+      uint32_t nvalid = kBlkThreads;
+      if (first < kBlkThreads) {
+        const uint32_t ff = S.s_flag[first];
+        if (ff == 1u) {
+          done = true;
+          nvalid = first + 1;
+          end_bit = S.s_end[first];
+        } else {
+          fail = true;   // not a code (or nothing left of the stream) before the end-of-block code
+        }
+      }
+      const uint32_t next_start = S.s_end[kBlkThreads - 1];
+      const bool mine = tid < nvalid;
+      uint32_t ex_out, ex_tok, sum_out, sum_tok;
+      cta_scan2(S, mine ? my_out : 0u, mine ? my_tok : 0u, &ex_out, &ex_tok, &sum_out, &sum_tok);
+      if (!fail) {
+        if (tid == 0) {
+          const uint32_t idx = atomicAdd(&I.ctr[4], nvalid + 1u);
+          S.alloc = idx + nvalid + 1u <= I.sub_cap ? idx : kNoSub;
+        }
+        __syncthreads();
+        const uint32_t idx = S.alloc;
+        if (idx == kNoSub || sum_out > I.raw_len - tot_out) {
+          fail = true;
+        } else {
+          if (tid == 0) {
+            I.sub[idx] = make_uint4(nvalid, kNoSub, 0u, 0u);
+            if (prev_hdr != kNoSub) I.sub[prev_hdr].y = idx;
+          }
+          if (mine) I.sub[idx + 1u + tid] = make_uint4(cached_start, my_end, tot_out + ex_out, tot_tok + ex_tok);
+          if (first_sub == kNoSub) first_sub = idx;
+          prev_hdr = idx;
+          tot_out += sum_out;
+          tot_tok += sum_tok;
+          wstart = next_start;
+        }
+      }
+      __syncthreads();
+    }
+    if (tid == 0 && !fail) {
+      rec->end_bit = end_bit;
+      rec->n_out = tot_out;
+      rec->n_tok = tot_tok;
+      rec->first_sub = first_sub;
+      __threadfence();
+      rec->flags = (S.hdr & 1u) | ((S.hdr >> 1) << 1) | kRecValid;
+    }
   }
 }
 
@@ -252,7 +429,7 @@ __global__ void __launch_bounds__(32) pinf_walk_kernel(Batch B) {
       err = kErrCapacity;
       break;
     }
-    I.chain[nb++] = make_uint4(pos, out, nt, 0u);
+    I.chain[nb++] = make_uint4(pos, out, nt, rec.first_sub);
     out += rec.n_out;
     nt += rec.n_tok;
     pos = rec.end_bit;
@@ -264,30 +441,51 @@ __global__ void __launch_bounds__(32) pinf_walk_kernel(Batch B) {
   if (err) atomicOr(B.status, err);
 }
 
-// ---- P5: a thread per real block, write mode ----
-__global__ void __launch_bounds__(PINF_THREADS) pinf_write_kernel(Batch B) {
-  extern __shared__ __align__(16) uint16_t pinf_smem[];
-  HuffTables T = thread_tables(B, pinf_smem);
+// ---- P5: a CTA per real block, a thread per subsequence ----
+__global__ void __launch_bounds__(kBlkThreads, 2) pinf_write_kernel(Batch B) {
+  __shared__ BlkSmem S;
   const Flat F(B, 2);
-  uint8_t lens[320];
-  const uint32_t lane = threadIdx.x & 31;
-  for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < F.total(); base += gridDim.x * blockDim.x) {
-    const uint32_t item = base + lane;
-    DecState st;
-    st.status = kDone;
-    uint8_t* lit = nullptr;
-    Token* tok = nullptr;
-    if (item < F.total()) {
-      const int im = F.image_of(item);
-      const Img& I = B.img[im];
-      const uint4 blk = I.chain[item - F.start[im]];
-      lit = I.raw;
-      tok = I.tok + blk.z;
-      block_begin<true>(st, I.z, I.z_len, blk.x, T, lens, blk.y, I.raw_len, lit);
+  const HuffTables T = cta_tables(S);
+  const uint32_t tid = threadIdx.x;
+  for (uint32_t item = blockIdx.x; item < F.total(); item += gridDim.x) {
+    const int im = F.image_of(item);
+    const Img& I = B.img[im];
+    const uint4 blk = I.chain[item - F.start[im]];
+    __syncthreads();
+    if (blk.w == kNoSub) {   // stored / fixed block, or one the finder missed: one thread, as the walker counted it
+      if (tid == 0) {
+        HuffTables Tw = T;
+        if (decode_block<true>(I.z, I.z_len, blk.x, Tw, S.lens, nullptr, blk.y, I.raw_len, I.raw, I.tok + blk.z) != kBlockOk)
+          atomicOr(B.status, (uint32_t)kErrStream);
+      }
+      continue;
     }
-    while (__any_sync(0xffffffffu, st.status == kRunning))
-      if (st.status == kRunning) symbol_step<true>(st, T, lit, tok);
-    if (st.status != kDone) atomicOr(B.status, (uint32_t)kErrStream);
+    if (tid == 0) {
+      DecState st;
+      HuffTables Tw = T;
+      block_begin<true>(st, I.z, I.z_len, blk.x, Tw, S.lens, blk.y, I.raw_len, I.raw);
+      S.ok = st.status == kRunning;
+    }
+    __syncthreads();
+    if (!S.ok) {
+      if (tid == 0) atomicOr(B.status, (uint32_t)kErrStream);
+      continue;
+    }
+    uint32_t w = blk.w;
+    bool bad = false;
+    while (w != kNoSub) {
+      const uint4 hdr = I.sub[w];
+      const bool go = tid < hdr.x;
+      uint4 r = make_uint4(0u, 0u, 0u, 0u);
+      if (go) r = I.sub[w + 1u + tid];
+      DecState st;
+      st.status = kDone;
+      if (go) start_at(st, I.z, I.z_len, r.x, blk.y + r.z, I.raw_len);
+      run_range<true>(st, T, r.y, go, I.raw, I.tok + blk.z + r.w);
+      if (go && (st.status == kBad || (st.status == kRunning ? st.br.pos() : st.end_bit) != r.y)) bad = true;
+      w = hdr.y;
+    }
+    if (bad) atomicOr(B.status, (uint32_t)kErrStream);
   }
 }
 
@@ -582,22 +780,11 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
   if (n > kMaxImages) return cudaErrorInvalidValue;
   auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
   const int dec_ctas = sm_count > 0 ? sm_count : 148;
-  const size_t dec_smem = (size_t)PINF_THREADS * (kLitEntries + kDistEntries) * sizeof(uint16_t);
-  static bool attr_done[64] = {};
-  {
-    int dev = 0;
-    PNG_TRY(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-      PNG_TRY(cudaFuncSetAttribute(pinf_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem));
-      PNG_TRY(cudaFuncSetAttribute(pinf_write_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dec_smem));
-      attr_done[dev] = true;
-    }
-  }
   Batch B;
   std::memset(&B, 0, sizeof B);
   B.n = n;
   // zeroed region first: status, flags, then per image counters / hash keys / progress
-  struct Carve { size_t ctr, hkey, progress, file, z, surv, cand, hval, chain, raw, src, tok, rawT, outT, palette; } cv[kMaxImages];
+  struct Carve { size_t ctr, hkey, progress, file, z, surv, cand, hval, chain, sub, raw, src, tok, rawT, outT, palette; } cv[kMaxImages];
   size_t need = 0;
   const size_t o_status = need; need += 256;
   const size_t o_flags = need; need += up(kJumpRounds * 4);
@@ -616,6 +803,7 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
     I.hmask = hs - 1;
     I.chain_cap = H.z_len / 8 + 64;
     I.tok_cap = I.raw_len / 3 + 1;                       // a match makes at least 3 bytes
+    I.sub_cap = 2 * (H.z_len * 8 / kSubBits) + 8 * I.cand_cap + 1024;
     I.t_chunks = (H.row_bytes + 15) / 16;
     I.w = H.w; I.h = H.h; I.depth = H.depth; I.ctype = H.ctype; I.channels = H.channels; I.bpp = H.bpp;
     I.row_bytes = H.row_bytes;
@@ -644,6 +832,7 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
     c.cand = need; need += up((size_t)I.cand_cap * sizeof(BlockRec));
     c.hval = need; need += up((size_t)(I.hmask + 1) * 4);
     c.chain = need; need += up((size_t)I.chain_cap * 16);
+    c.sub = need; need += up((size_t)I.sub_cap * 16);
     c.raw = need; need += up((size_t)I.raw_len + 16);
     c.src = need; need += up(((size_t)I.raw_len + 15) / 16 * 16 * 4);
     c.tok = need; need += up((size_t)I.tok_cap * sizeof(Token));
@@ -654,7 +843,6 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
     }
     c.palette = need; need += 1024;
   }
-  const size_t o_slow = need; need += up((size_t)dec_ctas * PINF_THREADS * kSlowWords * 2);
   const size_t o_pieces = need; need += up(n_pieces * sizeof(IdatPiece));
   if (arena.cap < need) {
     if (arena.p) {
@@ -669,7 +857,6 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
   uint8_t* A = (uint8_t*)arena.p;
   B.status = (uint32_t*)(A + o_status);
   B.flags = (uint32_t*)(A + o_flags);
-  B.slow = (uint16_t*)(A + o_slow);
   B.pieces = (const IdatPiece*)(A + o_pieces);
   PNG_TRY(cudaMemsetAsync(A, 0, zero_bytes, stream));
   std::vector<IdatPiece> pieces;
@@ -686,6 +873,7 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
     I.cand = (BlockRec*)(A + c.cand);
     I.hval = (uint32_t*)(A + c.hval);
     I.chain = (uint4*)(A + c.chain);
+    I.sub = (uint4*)(A + c.sub);
     I.raw = A + c.raw;
     I.src = (uint32_t*)(A + c.src);
     I.tok = (Token*)(A + c.tok);
@@ -706,9 +894,9 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
   pinf_gather_kernel<<<(unsigned)pieces.size(), 256, 0, stream>>>(B);
   pinf_find_kernel<<<dim3((max_z + 255) / 256, n), 256, 0, stream>>>(B);
   pinf_validate_kernel<<<dec_ctas * 8, 128, 0, stream>>>(B);
-  pinf_count_kernel<<<dec_ctas, PINF_THREADS, dec_smem, stream>>>(B);
+  pinf_count_kernel<<<dec_ctas * 2, kBlkThreads, 0, stream>>>(B);
   pinf_walk_kernel<<<n, 32, 0, stream>>>(B);
-  pinf_write_kernel<<<dec_ctas, PINF_THREADS, dec_smem, stream>>>(B);
+  pinf_write_kernel<<<dec_ctas * 2, kBlkThreads, 0, stream>>>(B);
   pinf_expand_kernel<<<dec_ctas * 8, 256, 0, stream>>>(B);
   nl += 7;
   const dim3 g4((max_raw / 4 + 256) / 256, n);
@@ -725,6 +913,16 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
   nl += 4;
   PNG_TRY(cudaGetLastError());
   if (status_host) PNG_TRY(cudaMemcpyAsync(status_host, B.status, 4, cudaMemcpyDeviceToHost, stream));
+  static const bool debug = [] { const char* e = std::getenv("STITCH_PNG_DEBUG"); return e && e[0] == '1'; }();
+  if (debug) {
+    PNG_TRY(cudaStreamSynchronize(stream));
+    for (int i = 0; i < n; ++i) {
+      uint32_t c[8];
+      PNG_TRY(cudaMemcpy(c, B.img[i].ctr, sizeof c, cudaMemcpyDeviceToHost));
+      std::fprintf(stderr, "png[%d] z=%u raw=%u survivors=%u candidates=%u blocks=%u tokens=%u subrecs=%u windows=%u rounds=%u (max %u)\n", i,
+                   B.img[i].z_len, B.img[i].raw_len, c[0], c[1], c[2], c[3], c[4], c[7], c[5], c[6]);
+    }
+  }
   if (launches) *launches += nl;
   return cudaSuccess;
 }

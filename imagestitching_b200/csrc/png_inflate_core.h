@@ -337,8 +337,9 @@ struct BlockRec {
   uint32_t n_out;     // bytes it produces
   uint32_t flags;     // bit 0: BFINAL, bits 1-2: type, bit 3: valid
   uint32_t n_tok;     // matches in it
+  uint32_t first_sub; // index of its first window of subsequence records (kNoSub: decoded by one thread)
 };
-constexpr uint32_t kRecFinal = 1, kRecValid = 8;
+constexpr uint32_t kRecFinal = 1, kRecValid = 8, kNoSub = 0xFFFFFFFFu;
 
 // A block being decoded by one thread.  The work is cut into block_begin / symbol_step / block_end so that a kernel can
 // run symbol_step under a warp-wide vote: 32 lanes that walk 32 different blocks stay converged, one symbol per lane
@@ -465,6 +466,7 @@ PINF_HD void block_end(const DecState& st, BlockRec* rec) {
   rec->n_out = st.pos - st.out_start;
   rec->flags = (st.hdr & 1) | ((st.hdr >> 1) << 1) | kRecValid;
   rec->n_tok = st.n_tok;
+  rec->first_sub = kNoSub;
 }
 
 // A whole block at `bitpos`, any type, by one thread on its own (the chain walker, the CPU drive of the tests).

@@ -102,3 +102,37 @@ extern "C" int pinf_host_inflate(const uint8_t* z_in, uint32_t z_len, uint32_t r
     if (src[i] != kRoot) out[i] = out[src[i]];
   return 0;
 }
+
+// Self-synchronisation statistics of the first Huffman block of a stream: subsequences of `sub_bits` bits are decoded
+// from their nominal (guessed) starts; out[0] = subsequences tried, out[1] = those whose end is a true symbol boundary.
+extern "C" int pinf_host_sync_stats(const uint8_t* z_in, uint32_t z_len, uint32_t sub_bits, uint32_t* out) {
+  std::vector<uint8_t> zbuf((size_t)z_len + 32, 0);
+  std::memcpy(zbuf.data(), z_in, z_len);
+  const uint8_t* z = zbuf.data();
+  Thread th;
+  DecState st;
+  block_begin<false>(st, z, z_len, 16, th.T, th.lens, 0, 0x7FFFFFFFu, nullptr);
+  out[0] = out[1] = 0;
+  if (st.status != kRunning) return 1;
+  const uint32_t p0 = st.br.pos();
+  std::vector<uint8_t> boundary((size_t)z_len * 8 + 64, 0);
+  while (st.status == kRunning) {
+    boundary[st.br.pos()] = 1;
+    symbol_step<false>(st, th.T, nullptr, nullptr);
+  }
+  if (st.status != kDone) return 2;
+  const uint32_t end = st.end_bit;
+  for (uint32_t s = p0 + sub_bits; s + sub_bits < end; s += sub_bits) {
+    DecState sp;
+    sp.z_bits = z_len * 8u;
+    sp.pos = sp.out_start = 0;
+    sp.out_limit = 0x7FFFFFFFu;
+    sp.n_tok = 0;
+    sp.status = kRunning;
+    sp.br.init(z, s);
+    while (sp.status == kRunning && sp.br.pos() < s + sub_bits) symbol_step<false>(sp, th.T, nullptr, nullptr);
+    out[0]++;
+    if (sp.status == kRunning && boundary[sp.br.pos()]) out[1]++;
+  }
+  return 0;
+}
