@@ -28,7 +28,8 @@
 //   P8 bytes     every copied byte fetches its value.
 //   P9 transpose rows -> 16-byte chunks interleaved over the 32 rows of a group, so that "lane = row" reads coalesce.
 //   P10 unfilter the five PNG filters as a wavefront: lane = row, a row runs one pixel behind the row above it
-//                (shuffles inside a warp, a progress counter between the 32 warps of the image's CTA).
+//                (shuffles inside a warp, a progress counter in global memory between the warps -- 96 per image,
+//                spread over 24 small CTAs so that a step costs its dependency chain, not a queue for one SM).
 //   P11 rgba     gray / RGB / palette / alpha, 1-16 bit -> RGBA8 (16-bit samples keep their high byte, tRNS applied).
 // Huffman tables: one set per CTA in shared memory (two levels, 10 + 7 first-level bits).
 // Interlaced (Adam7) files are rejected by the parser.  There is no CPU fallback.
@@ -50,7 +51,8 @@ using namespace stitch::pnginf;
 constexpr int kSubBits = 512;      // nominal length of a subsequence of a block's bits
 constexpr int kBlkThreads = 256;   // subsequences per window (one CTA pass over 16 KB of the block)
 constexpr int kJumpRounds = 32;  // >= log2(longest chain: < 2^31 bytes) + 1
-constexpr int kUnfWarps = 32;
+constexpr int kUnfWarps = 4;      // warps per CTA of the unfilter kernel
+constexpr int kUnfCtas = 24;      // CTAs per image: 96 row groups in flight (more would only wait for the wavefront)
 
 struct Img {
   const uint8_t* file;
@@ -276,7 +278,6 @@ __global__ void __launch_bounds__(kBlkThreads, 2) pinf_count_kernel(Batch B) {
     const int im = F.image_of(item);
     const Img& I = B.img[im];
     BlockRec* rec = &I.cand[item - F.start[im]];
-    const uint32_t z_bits = I.z_len * 8u;
     __syncthreads();
     if (tid == 0) {
       DecState st;
@@ -507,8 +508,13 @@ __global__ void __launch_bounds__(256) pinf_expand_kernel(Batch B) {
       dist = (t.len_dist & 0x7FFFu) + 1u;
       src = I.src;
     }
+    // a run (dist < len) repeats the dist bytes before it: every byte points straight at one of those, not at its
+    // neighbour dist back (a chain as long as the run)
     if (len <= 8) {
-      for (uint32_t k = 0; k < len; ++k) src[pos + k] = pos + k - dist;
+      for (uint32_t k = 0, m = 0; k < len; ++k) {
+        src[pos + k] = pos - dist + m;
+        if (++m == dist) m = 0;
+      }
       len = 0;
     }
     unsigned m = __ballot_sync(0xffffffffu, len != 0);
@@ -517,47 +523,54 @@ __global__ void __launch_bounds__(256) pinf_expand_kernel(Batch B) {
       m &= m - 1;
       const uint32_t p = __shfl_sync(0xffffffffu, pos, l), n = __shfl_sync(0xffffffffu, len, l), d = __shfl_sync(0xffffffffu, dist, l);
       uint32_t* s = reinterpret_cast<uint32_t*>(__shfl_sync(0xffffffffu, (unsigned long long)src, l));
-      for (uint32_t k = lane; k < n; k += 32) s[p + k] = p + k - d;
+      for (uint32_t k = lane; k < n; k += 32) s[p + k] = p - d + (d >= n ? k : k % d);
     }
   }
 }
 
-// ---- P7: one pointer-jumping round over src[] (4 entries per thread) ----
+// ---- P7: one pointer-jumping round over src[] (4 entries per thread and iteration; the grid is fixed so that a round
+// that has nothing to do -- the round before moved nothing -- costs one small launch) ----
 __global__ void __launch_bounds__(256) pinf_jump_kernel(Batch B) {
-  if (B.flag_prev >= 0 && B.flags[B.flag_prev] == 0u) return;   // the round before moved nothing: converged
+  if (B.flag_prev >= 0 && B.flags[B.flag_prev] == 0u) return;   // converged
   const Img& I = B.img[blockIdx.y];
-  const uint32_t i4 = blockIdx.x * 256u + threadIdx.x;
-  if ((uint64_t)i4 * 4u >= I.raw_len) return;
-  uint4 s = reinterpret_cast<uint4*>(I.src)[i4];
-  bool ch = false;
-  uint32_t* e = &s.x;
+  const uint32_t n4 = (I.raw_len + 3u) >> 2;
+  bool any = false;
+  for (uint32_t i4 = blockIdx.x * 256u + threadIdx.x; i4 < n4; i4 += gridDim.x * 256u) {
+    uint4 s = reinterpret_cast<uint4*>(I.src)[i4];
+    if ((s.x & s.y & s.z & s.w) == kRoot) continue;
+    bool ch = false;
+    uint32_t* e = &s.x;
+    uint32_t t[4];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    if (e[k] != kRoot) {
-      const uint32_t s2 = I.src[e[k]];
-      if (s2 != kRoot) {
-        e[k] = s2;
+    for (int k = 0; k < 4; ++k) t[k] = e[k] != kRoot ? I.src[e[k]] : kRoot;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (t[k] != kRoot) {
+        e[k] = t[k];
         ch = true;
       }
     }
+    if (ch) {
+      reinterpret_cast<uint4*>(I.src)[i4] = s;
+      any = true;
+    }
   }
-  if (ch) {
-    reinterpret_cast<uint4*>(I.src)[i4] = s;
-    B.flags[B.flag_cur] = 1u;
-  }
+  if (any) B.flags[B.flag_cur] = 1u;
 }
 
 // ---- P8: copied bytes fetch their values ----
 __global__ void __launch_bounds__(256) pinf_bytes_kernel(Batch B) {
   const Img& I = B.img[blockIdx.y];
-  const uint32_t i4 = blockIdx.x * 256u + threadIdx.x;
   if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && B.flags[kJumpRounds - 1] != 0u) atomicOr(B.status, (uint32_t)kErrResolve);
-  if ((uint64_t)i4 * 4u >= I.raw_len) return;
-  const uint4 s = reinterpret_cast<const uint4*>(I.src)[i4];
-  const uint32_t* e = &s.x;
+  const uint32_t n4 = (I.raw_len + 3u) >> 2;
+  for (uint32_t i4 = blockIdx.x * 256u + threadIdx.x; i4 < n4; i4 += gridDim.x * 256u) {
+    const uint4 s = reinterpret_cast<const uint4*>(I.src)[i4];
+    if ((s.x & s.y & s.z & s.w) == kRoot) continue;
+    const uint32_t* e = &s.x;
 #pragma unroll
-  for (int k = 0; k < 4; ++k)
-    if (e[k] != kRoot) I.raw[i4 * 4u + k] = I.raw[e[k]];   // the padding entries past raw_len are kRoot
+    for (int k = 0; k < 4; ++k)
+      if (e[k] != kRoot) I.raw[i4 * 4u + k] = I.raw[e[k]];   // the padding entries past raw_len are kRoot
+  }
 }
 
 // ---- P9: transpose.  Word j (4 bytes) of row y's payload lives at t_word(): the 16-byte chunks of the 32 rows of a
@@ -585,32 +598,42 @@ __global__ void __launch_bounds__(256) png_transpose_kernel(Batch B) {
 }
 
 // ---- P10: unfilter (PNG spec clause 9) ----
-__device__ __forceinline__ int paeth(int a, int b, int c) {
-  const int p = a + b - c;
-  const int pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
-  return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+// Four bytes at a time (the byte-wise SIMD intrinsics; |x - y| is one instruction, the compares a few).
+__device__ __forceinline__ uint32_t paeth4(uint32_t a, uint32_t b, uint32_t c) {
+  const uint32_t pa = __vabsdiffu4(b, c), pb = __vabsdiffu4(a, c);
+  // |a + b - 2c|: a - c and b - c of one sign -> pa + pb (saturated: it only has to stay >= pa, pb), else |pa - pb|
+  const uint32_t same = ~(__vcmpgeu4(a, c) ^ __vcmpgeu4(b, c));
+  const uint32_t pc = (same & __vaddus4(pa, pb)) | (~same & __vabsdiffu4(pa, pb));
+  const uint32_t use_a = __vcmpleu4(pa, pb) & __vcmpleu4(pa, pc), use_b = __vcmpleu4(pb, pc);
+  return (use_a & a) | (~use_a & ((use_b & b) | (~use_b & c)));
 }
-__device__ __forceinline__ uint32_t shfl_px(uint32_t v, int srcl) { return __shfl_sync(0xffffffffu, v, srcl); }
-__device__ __forceinline__ uint64_t shfl_px(uint64_t v, int srcl) { return __shfl_sync(0xffffffffu, (unsigned long long)v, srcl); }
-__device__ __forceinline__ uint32_t shfl_up_px(uint32_t v) { return __shfl_up_sync(0xffffffffu, v, 1); }
-__device__ __forceinline__ uint64_t shfl_up_px(uint64_t v) { return __shfl_up_sync(0xffffffffu, (unsigned long long)v, 1); }
+__device__ __forceinline__ uint32_t predict4(int ft, bool any_paeth, uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t p = ft == 1 ? a : ft == 2 ? b : ft == 3 ? __vhaddu4(a, b) : 0u;
+  if (any_paeth) {   // warp-uniform: groups without a Paeth row skip the arithmetic
+    const uint32_t q = paeth4(a, b, c);
+    p = ft == 4 ? q : p;
+  }
+  return p;
+}
 
-// One CTA per image.  Lane l of a warp owns row 32 g + l of the warp's current group g and works on pixel s - l at
-// step s, so the pixel above (lane l - 1, one step earlier) arrives by shuffle and left / upper-left are the lane's
-// own previous values.  Lane 0's upper row belongs to the group before -- another warp -- which publishes how far its
-// last row has got every 32 steps; its bytes are read back through L2.  Rows stream through two small byte queues
-// per lane (4-byte loads from rawT, 4-byte stores to outT).
-template <typename PX>
+constexpr int kUpBatch = 8;   // pixels of the row above that lane 0 fetches at a time
+
+// kUnfCtas CTAs per image, their warps take the row groups in turn.  Lane l of a warp owns row 32 g + l of the warp's
+// current group g and works on pixel s - l at step s, so the pixel above (lane l - 1, one step earlier) arrives by
+// shuffle and left / upper-left are the lane's own previous values.  Lane 0's upper row belongs to the group before --
+// another warp -- which publishes how far its last row has got every 8 steps; its bytes are read back through L2, 8
+// pixels at a time.  Rows stream through two small byte queues per lane (4-byte loads from rawT, 4-byte stores to
+// outT).  The time of this kernel is its dependency chain: (rows + width) steps of one pixel each.
+template <int BPP>
 __device__ void unfilter_image(const Batch& B, const Img& I) {
+  constexpr bool WIDE = BPP > 4;
   const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
-  const int bpp = I.bpp;
   const uint32_t chunks = I.t_chunks;
-  const int wp = (int)(I.row_bytes / (uint32_t)bpp);
+  const int wp = (int)(I.row_bytes / (uint32_t)BPP);
   const uint32_t n_words = (I.row_bytes + 3u) >> 2;
   const int groups = (I.h + 31) / 32;
-  const uint64_t pmask = bpp >= 8 ? ~0ull : ((1ull << (8 * bpp)) - 1ull);
   volatile uint32_t* progress = I.progress;
-  for (int g = wv; g < groups; g += kUnfWarps) {
+  for (int g = (int)blockIdx.x * kUnfWarps + wv; g < groups; g += (int)gridDim.x * kUnfWarps) {
     const int y = g * 32 + lane;
     const bool active = y < I.h;
     const int yy = active ? y : g * 32;
@@ -619,77 +642,97 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
       atomicOr(B.status, (uint32_t)kErrFilter);
       ft = 0;
     }
-    PX left = 0, ul = 0, prev = 0, upbatch = 0;
+    const bool any_paeth = __any_sync(0xffffffffu, ft == 4);
+    // word j of this lane's row: base + (j >> 2) * 128 + (j & 3)   (uint32 units, see t_word)
+    const uint32_t* in_row = I.rawT + t_word(chunks, yy, 0);
+    uint32_t* out_row = I.outT + t_word(chunks, yy, 0);
+    const uint8_t* above = g ? reinterpret_cast<const uint8_t*>(I.outT + t_word(chunks, g * 32 - 1, 0)) : nullptr;
+    uint32_t left0 = 0, left1 = 0, ul0 = 0, ul1 = 0, prev0 = 0, prev1 = 0, upb0 = 0, upb1 = 0;
     uint64_t inbuf = 0, outbuf = 0;
     int incnt = 0, outcnt = 0;
     uint32_t inj = 0, outj = 0;
-    uint32_t pre = (active && n_words) ? I.rawT[t_word(chunks, yy, 0)] : 0u;   // always one word ahead
+    uint32_t pre = (active && n_words) ? in_row[0] : 0u;   // always one word ahead
+    uint32_t seen = 0;                                      // progress of the group above, as last read
     const int steps = wp + 31;
     for (int s = 0; s < steps; ++s) {
-      if ((s & 31) == 0 && g && s < wp) {
-        const uint32_t need = (uint32_t)min(wp, s + 32);
-        while (progress[g - 1] < need) {
+      if ((s & (kUpBatch - 1)) == 0 && g && s < wp) {
+        const uint32_t need = (uint32_t)min(wp, s + kUpBatch);
+        if (seen < need) {
+          while ((seen = progress[g - 1]) < need) {
+          }
+          __threadfence();
         }
-        __threadfence();
         const int px = s + lane;
-        PX v = 0;
-        if (px < wp) {
+        uint32_t v0 = 0, v1 = 0;
+        if (lane < kUpBatch && px < wp) {
 #pragma unroll
-          for (int k = 0; k < (int)sizeof(PX); ++k)
-            if (k < bpp)
-              v |= (PX)__ldcg(reinterpret_cast<const uint8_t*>(I.outT) + t_word(chunks, g * 32 - 1, ((uint32_t)px * bpp + k) >> 2) * 4 +
-                              (((uint32_t)px * bpp + k) & 3)) << (8 * k);
+          for (int k = 0; k < BPP; ++k) {
+            const uint32_t bo = (uint32_t)px * BPP + k;
+            const uint32_t byte = __ldcg(above + ((size_t)(bo >> 4) * 128 + ((bo >> 2) & 3)) * 4 + (bo & 3));
+            if (k < 4) v0 |= byte << (8 * k);
+            else v1 |= byte << (8 * (k - 4));
+          }
         }
-        upbatch = v;
+        upb0 = v0;
+        upb1 = v1;
       }
-      const PX from_batch = shfl_px(upbatch, s & 31);
-      const PX from_below = shfl_up_px(prev);
-      const PX up = lane == 0 ? (g ? from_batch : (PX)0) : from_below;
+      uint32_t up0 = __shfl_sync(0xffffffffu, upb0, s & (kUpBatch - 1)), up1 = 0;
+      const uint32_t below0 = __shfl_up_sync(0xffffffffu, prev0, 1);
+      up0 = lane == 0 ? (g ? up0 : 0u) : below0;
+      if (WIDE) {
+        up1 = __shfl_sync(0xffffffffu, upb1, s & (kUpBatch - 1));
+        const uint32_t below1 = __shfl_up_sync(0xffffffffu, prev1, 1);
+        up1 = lane == 0 ? (g ? up1 : 0u) : below1;
+      }
       const int x = s - lane;
       const bool valid = active && x >= 0 && x < wp;
       if (x == 0) {
-        left = 0;
-        ul = 0;
+        left0 = left1 = 0;
+        ul0 = ul1 = 0;
       }
-      PX cur = 0;
+      uint32_t cur0 = 0, cur1 = 0;
       if (valid) {
-        while (incnt < bpp) {
+        while (incnt < BPP) {
           inbuf |= (uint64_t)pre << (8 * incnt);
           incnt += 4;
           ++inj;
-          pre = inj < n_words ? I.rawT[t_word(chunks, yy, inj)] : 0u;
+          pre = inj < n_words ? in_row[(inj >> 2) * 128u + (inj & 3u)] : 0u;
         }
-        const PX f = (PX)(inbuf & pmask);
-        inbuf = bpp >= 8 ? 0ull : inbuf >> (8 * bpp);
-        incnt -= bpp;
-#pragma unroll
-        for (int k = 0; k < (int)sizeof(PX); ++k) {
-          if (k < bpp) {
-            const int a = (int)((left >> (8 * k)) & 0xFF), b = (int)((up >> (8 * k)) & 0xFF), c = (int)((ul >> (8 * k)) & 0xFF);
-            const int pred = ft == 1 ? a : ft == 2 ? b : ft == 3 ? ((a + b) >> 1) : ft == 4 ? paeth(a, b, c) : 0;
-            cur |= (PX)((((int)((f >> (8 * k)) & 0xFF)) + pred) & 0xFF) << (8 * k);
-          }
+        const uint32_t f0 = (uint32_t)inbuf & (BPP >= 4 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u);
+        const uint32_t f1 = WIDE ? (uint32_t)(inbuf >> 32) & (BPP >= 8 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u) : 0u;
+        inbuf = BPP >= 8 ? 0ull : inbuf >> (8 * (BPP & 7));
+        incnt -= BPP;
+        cur0 = __vadd4(f0, predict4(ft, any_paeth, left0, up0, ul0));
+        if (BPP < 4) cur0 &= (1u << (8 * (BPP & 3))) - 1u;
+        if (WIDE) {
+          cur1 = __vadd4(f1, predict4(ft, any_paeth, left1, up1, ul1));
+          if (BPP < 8) cur1 &= (1u << (8 * (BPP & 3))) - 1u;
         }
-        outbuf |= (uint64_t)cur << (8 * outcnt);
-        outcnt += bpp;
+        outbuf |= (WIDE ? ((uint64_t)cur1 << 32) | cur0 : (uint64_t)cur0) << (8 * outcnt);
+        outcnt += BPP;
         while (outcnt >= 4) {
-          I.outT[t_word(chunks, yy, outj++)] = (uint32_t)outbuf;
+          out_row[(outj >> 2) * 128u + (outj & 3u)] = (uint32_t)outbuf;
+          ++outj;
           outbuf >>= 32;
           outcnt -= 4;
         }
         if (x == wp - 1 && outcnt > 0) {
-          I.outT[t_word(chunks, yy, outj++)] = (uint32_t)outbuf;
+          out_row[(outj >> 2) * 128u + (outj & 3u)] = (uint32_t)outbuf;
+          ++outj;
           outcnt = 0;
         }
       }
-      left = cur;
-      ul = up;
-      prev = cur;
-      if ((s & 31) == 31 || s == steps - 1) {
+      left0 = cur0;
+      left1 = cur1;
+      ul0 = up0;
+      ul1 = up1;
+      prev0 = cur0;
+      prev1 = cur1;
+      if ((s & 7) == 7 || s == steps - 1) {
         __syncwarp();
         if (lane == 31 && active) {
           __threadfence();
-          const uint32_t done = s == steps - 1 ? (uint32_t)wp : (outj * 4u) / (uint32_t)bpp;
+          const uint32_t done = s == steps - 1 ? (uint32_t)wp : (outj * 4u) / (uint32_t)BPP;
           progress[g] = done;
         }
       }
@@ -698,10 +741,16 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
 }
 
 __global__ void __launch_bounds__(32 * kUnfWarps) png_unfilter_kernel(Batch B) {
-  const Img& I = B.img[blockIdx.x];
+  const Img& I = B.img[blockIdx.y];
   if (*B.status) return;   // a damaged stream: the bitmap is not delivered
-  if (I.bpp <= 4) unfilter_image<uint32_t>(B, I);
-  else unfilter_image<uint64_t>(B, I);
+  switch (I.bpp) {
+    case 1: unfilter_image<1>(B, I); break;
+    case 2: unfilter_image<2>(B, I); break;
+    case 3: unfilter_image<3>(B, I); break;
+    case 4: unfilter_image<4>(B, I); break;
+    case 6: unfilter_image<6>(B, I); break;
+    default: unfilter_image<8>(B, I); break;
+  }
 }
 
 // ---- P11: samples -> RGBA8 ----
@@ -899,7 +948,7 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
   pinf_write_kernel<<<dec_ctas * 2, kBlkThreads, 0, stream>>>(B);
   pinf_expand_kernel<<<dec_ctas * 8, 256, 0, stream>>>(B);
   nl += 7;
-  const dim3 g4((max_raw / 4 + 256) / 256, n);
+  const dim3 g4((unsigned)std::min<uint32_t>((max_raw / 4 + 256) / 256, (uint32_t)dec_ctas * 8u), n);
   for (int r = 0; r < kJumpRounds; ++r) {
     B.flag_cur = r;
     B.flag_prev = r - 1;
@@ -908,7 +957,7 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
   }
   pinf_bytes_kernel<<<g4, 256, 0, stream>>>(B);
   png_transpose_kernel<<<dim3((max_chunks * 4 + 255) / 256, max_h, n), 256, 0, stream>>>(B);
-  png_unfilter_kernel<<<n, 32 * kUnfWarps, 0, stream>>>(B);
+  png_unfilter_kernel<<<dim3(kUnfCtas, n), 32 * kUnfWarps, 0, stream>>>(B);   // 216 small CTAs at most: all resident, so the waits are safe
   png_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, stream>>>(B);
   nl += 4;
   PNG_TRY(cudaGetLastError());

@@ -33,6 +33,9 @@ def main():
     t = time.perf_counter(); ctx.decode_png(fs[0]); print("first decode_png (allocations): %.1f ms" % ((time.perf_counter() - t) * 1e3))
     for _ in range(3):
         t = time.perf_counter(); ctx.decode_png(fs[0]); print("decode_png one file: %.2f ms" % ((time.perf_counter() - t) * 1e3))
+    if jobs == 0:
+        ctx.close()
+        return
     imgs = [{"file": f} for f in fs]
     for output in ("rgba", "png"):
         ctx.set_lanes(1)

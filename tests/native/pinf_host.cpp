@@ -83,7 +83,7 @@ extern "C" int pinf_host_inflate(const uint8_t* z_in, uint32_t z_len, uint32_t r
   // expand
   for (uint32_t t = 0; t < tokp; ++t) {
     const uint32_t len = tok[t].len_dist >> 15, dist = (tok[t].len_dist & 0x7FFFu) + 1u;
-    for (uint32_t k = 0; k < len; ++k) src[tok[t].pos + k] = tok[t].pos + k - dist;
+    for (uint32_t k = 0; k < len; ++k) src[tok[t].pos + k] = tok[t].pos - dist + (dist >= len ? k : k % dist);   // as pinf_expand_kernel
   }
   for (uint32_t i = 0; i < raw_len; ++i) stats[5] += src[i] != kRoot;
   // resolve
