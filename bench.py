@@ -248,6 +248,60 @@ def cpu_sanity_baselines(workload: str):
     return out
 
 
+def synth_screenshot_png(w: int, h: int, seed: int = 0) -> bytes:
+    """A phone-screenshot-like RGBA PNG file: a coloured title bar, white ground, blocks of text-like speckle, a gradient
+    card.  Encoded by PIL (libpng filter heuristics, zlib level 6) -- the encoder real screenshots come from."""
+    import io
+
+    import numpy as np
+    from PIL import Image
+
+    rng = np.random.default_rng(seed)
+    a = np.full((h, w, 4), 255, np.uint8)
+    a[: h // 10] = (32, 120, 240, 255)
+    for _ in range(60):
+        y0 = int(rng.integers(h // 10, h - 40))
+        x0 = int(rng.integers(0, w - 400))
+        ww = int(rng.integers(100, 400))
+        a[y0:y0 + 28, x0:x0 + ww, :3] = rng.integers(0, 2, (28, ww, 1)) * 220
+    a[h // 2: h // 2 + h // 8, w // 10: w - w // 10, 0] = np.linspace(0, 255, w - 2 * (w // 10)).astype(np.uint8)
+    b = io.BytesIO()
+    Image.fromarray(a, "RGBA").save(b, "PNG")
+    return b.getvalue()
+
+
+def cpu_png_files_run(files, direction, mode, platform, steps: int):
+    """The PNG-in / PNG-out job on the host cores: oracle PNG decoder (one thread per file), C raster (OpenMP), oracle PNG
+    writer.  Returns (MP/s, ms per job, cores)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    from oracle import layout_ref as LR
+    from oracle import png_c as PC
+    from oracle import png_dec_c as PD
+    from oracle import raster_c as RC
+    from tests import util as U
+
+    cores = len(os.sched_getaffinity(0)) or os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(cores)
+    pool = ThreadPoolExecutor(max_workers=min(cores, len(files)))
+
+    def one():
+        bitmaps = list(pool.map(PD.decode, files))
+        dims = [(b.shape[1], b.shape[0]) for b in bitmaps]
+        lay = LR.compute_layout(U.recs(dims), direction, mode, 0, U.profile_of(platform))
+        out = RC.render(lay, bitmaps, [1] * len(dims), want_rgba=True, want_yuv=False, precision="f32")
+        return lay, len(PC.encode_rgba(out["rgba"]))
+
+    lay, _ = one()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    dt = (time.perf_counter() - t0) / steps
+    pool.shutdown()
+    mp = lay.canvasW * lay.canvasH / 1e6
+    return mp / dt, dt * 1e3, cores
+
+
 def cpu_files_run(files, direction, mode, platform, steps: int, out_kind: str = "png"):
     """The file-in / file-out job on the host cores: oracle JPEG decoder (one thread per file), C raster (OpenMP),
     oracle PNG / JPEG writer (sequential).  Returns (MP/s, ms per job, cores)."""
@@ -659,6 +713,7 @@ def main():
     # exported file in host memory (what the page does between P:1441 and P:1581).  Uploads 14x fewer bytes than e2e.
     files_steps = args.files_steps if args.files_steps >= 0 else (24 if args.workload in ("cfg2", "cfg5") else 0)
     e2e_files = None
+    shot_files = None
     file_bytes_list = []
     if files_steps > 0:
         lib.stitch_wait(ctx.handle, last)
@@ -738,6 +793,83 @@ def main():
                                "d2h_bytes_per_step": fbytes, "single_job_latency_ms": single_ms}
         e2e_files["value"] = e2e_files["png"]["value"]   # the page exports PNG (P:1579)
 
+        # PNG inputs: nine phone screenshots (1290 x 2796 RGBA PNG files, what a long-screenshot stitch is fed) -> PNG file
+        try:
+            shots = [synth_screenshot_png(1290, 2796, seed=i) for i in range(3)]
+            shots = [shots[i % 3] for i in range(9)]
+            sbufs = []
+            for f in shots:
+                pf = C.c_void_p()
+                assert lib.stitch_host_alloc(len(f), C.byref(pf)) == 0
+                C.memmove(pf, f, len(f))
+                sbufs.append((pf, len(f)))
+                host_outs.append(pf)
+            sjobs = []
+            s_cap = 0
+            for _ in range(e2e_lanes):
+                arr = (L.StitchImage * 9)()
+                for i in range(9):
+                    arr[i].desc.natural_width, arr[i].desc.natural_height = 1290, 2796
+                    arr[i].desc.width, arr[i].desc.height = 1290, 2796
+                    arr[i].desc.orientation = 1
+                    arr[i].desc.file_size = sbufs[i][1]
+                    arr[i].data = sbufs[i][0]
+                    arr[i].pitch_bytes = sbufs[i][1]
+                    arr[i].mem_kind = L.MEM_HOST_PNG
+                sj = L.StitchJob()
+                sj.images, sj.n = arr, 9
+                sj.params = hjobs[0][0].params
+                sj.output_flags = L.OUT_PNG
+                sj.out_mem_kind = L.MEM_HOST
+                if not s_cap:
+                    lay = L.StitchLayout()
+                    descs = (L.StitchImageDesc * 9)(*[arr[i].desc for i in range(9)])
+                    assert lib.stitch_layout(descs, 9, C.byref(sj.params), C.byref(lay)) == 0
+                    s_cap = int(lib.stitch_png_capacity(C.byref(lay)))
+                    s_mp = lay.canvas_w * lay.canvas_h / 1e6
+                po = C.c_void_p()
+                assert lib.stitch_host_alloc(s_cap, C.byref(po)) == 0
+                host_outs.append(po)
+                sj.out_png, sj.out_capacity_png = po.value, s_cap
+                sjobs.append((sj, arr, L.StitchResult()))
+
+            def shots_loop(nsteps):
+                tickets = []
+                for i in range(nsteps):
+                    sj, _, sr = sjobs[i % e2e_lanes]
+                    t = C.c_uint64()
+                    st = lib.stitch_submit(ctx.handle, C.byref(sj), C.byref(sr), C.byref(t))
+                    assert st == 0, lib.stitch_last_error(ctx.handle)
+                    tickets.append(t.value)
+                    if i >= e2e_lanes - 1:
+                        assert lib.stitch_wait(ctx.handle, tickets[i - (e2e_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
+                assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0, lib.stitch_last_error(ctx.handle)
+
+            shots_loop(2 * e2e_lanes)
+            torch.cuda.synchronize()
+            barrier()
+            t0 = time.perf_counter()
+            shots_loop(files_steps)
+            torch.cuda.synchronize()
+            ss = time.perf_counter() - t0
+            t1 = time.perf_counter()
+            for _ in range(3):
+                assert lib.stitch_run(ctx.handle, C.byref(sjobs[0][0]), C.byref(sjobs[0][2])) == 0
+            s_single = (time.perf_counter() - t1) / 3 * 1e3
+            if world > 1:
+                t = torch.tensor([ss], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ss = float(t.item())
+            e2e_files["png_in"] = {"value": s_mp * files_steps * world / ss, "unit": "MP/s", "ms_per_step": ss / files_steps * 1e3,
+                                   "single_job_latency_ms": s_single, "output_mp_per_step": s_mp,
+                                   "h2d_bytes_per_step": sum(b for _, b in sbufs), "d2h_bytes_per_step": int(sjobs[0][2].png_bytes),
+                                   "inputs": "9 screenshot-like PNG files, 1290x2796 RGBA, written by PIL (zlib level 6), pinned host memory; "
+                                             "inflated, unfiltered, stitched and re-encoded as one PNG on the GPU"}
+            shot_files = shots
+        except Exception as e:  # PIL missing on the box, or the leg failed: report, do not hide the other figures
+            e2e_files["png_in"] = {"value": None, "note": f"failed: {e}"}
+            shot_files = None
+
     if has_jpeg or has_png:
         out_bytes = int(hres.jpeg_bytes if has_jpeg else hres.png_bytes)   # d2h of the e2e step = the file
         algo_bytes = src_bytes + out_bytes
@@ -794,6 +926,14 @@ def main():
                                                        "oracle PNG writer (sequential)"}
             except Exception as e:
                 e2e_files["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
+            if isinstance(e2e_files.get("png_in"), dict) and e2e_files["png_in"].get("value") and shot_files:
+                try:
+                    v, ms, cores = cpu_png_files_run(shot_files, direction, mode, platform, 1)
+                    e2e_files["png_in"]["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "ms_per_step": ms,
+                                                           "sample": "1 job: oracle PNG decoder (a thread per file) + C raster (OpenMP) + "
+                                                                     "oracle PNG writer (sequential)"}
+                except Exception as e:
+                    e2e_files["png_in"]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
     if rank == 0:
         print(json.dumps(line))
     for p in host_keep + host_outs:
