@@ -492,6 +492,7 @@ __global__ void __launch_bounds__(kBlkThreads, 2) pinf_write_kernel(Batch B) {
 
 // ---- P6: tokens -> src[].  A lane expands its own token when it is short; long ones are spread over the warp. ----
 __global__ void __launch_bounds__(256) pinf_expand_kernel(Batch B) {
+  if (*B.status) return;   // a block failed in P5: its token slots were never written
   const Flat F(B, 3);
   const uint32_t total = F.total();
   const unsigned lane = threadIdx.x & 31;
@@ -507,6 +508,7 @@ __global__ void __launch_bounds__(256) pinf_expand_kernel(Batch B) {
       len = t.len_dist >> 15;
       dist = (t.len_dist & 0x7FFFu) + 1u;
       src = I.src;
+      if (dist > pos || len > I.raw_len - pos) len = 0;   // cannot happen for tokens P5 wrote; never write out of bounds
     }
     // a run (dist < len) repeats the dist bytes before it: every byte points straight at one of those, not at its
     // neighbour dist back (a chain as long as the run)

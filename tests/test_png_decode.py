@@ -364,3 +364,75 @@ def test_gpu_decoder_errors(ctx):
         assert ei.value.status == L.E_BAD_IMAGE, name
     # the context still works afterwards
     assert np.array_equal(ctx.decode_png(good), P.decode(good))
+
+
+@pytest.mark.gpu
+def test_gpu_decoder_survives_damaged_streams(ctx):
+    """Bit flips inside the deflate stream (chunk framing and CRCs repaired, so only the inflater can notice): the GPU
+    decoder and the oracle agree on accept / reject, on the bytes when both accept, and the context keeps working."""
+    from imagestitching_b200 import StitchError
+    rng = np.random.default_rng(11)
+    seeds = [_png(_picture(160, 120, 3, seed=21), "RGB"), _png(_screenshot(200, 300, seed=22), "RGBA"),
+             _png(_picture(97, 61, 4, seed=23), "RGBA", compress_level=1)]
+    rejected = accepted = 0
+    for base in seeds:
+        at = base.index(b"IDAT")
+        (n,) = struct.unpack(">I", base[at - 4: at])
+        for trial in range(14):
+            body = bytearray(base[at + 4: at + 4 + n])
+            for _ in range(int(rng.integers(1, 4))):
+                body[int(rng.integers(2, n))] ^= 1 << int(rng.integers(0, 8))
+            if trial == 13:
+                body = body[: n // 3]            # the stream simply stops
+            data = base[: at - 4] + _chunk(b"IDAT", bytes(body)) + base[at + 8 + n:]
+            try:
+                want = P.decode(data)
+            except P.PngError:
+                want = None
+            try:
+                got = ctx.decode_png(data)
+            except StitchError as e:
+                assert e.status == L.E_BAD_IMAGE
+                got = None
+            assert (got is None) == (want is None), (trial, "GPU and oracle disagree on whether the stream is valid")
+            if want is None:
+                rejected += 1
+            else:
+                accepted += 1
+                assert np.array_equal(got, want), trial
+    assert rejected >= 10 and accepted + rejected == 42
+    good = seeds[0]
+    assert np.array_equal(ctx.decode_png(good), P.decode(good))
+
+
+@pytest.mark.gpu
+def test_gpu_png_async_error_and_batch_of_unequal_files(ctx):
+    """A damaged PNG among good ones fails the job at stitch_wait with the page's message; the next job on that lane is
+    clean.  Nine files of nine different shapes and colour types in one job."""
+    from imagestitching_b200 import StitchError
+    good = _png(_picture(200, 120, 3, seed=4), "RGB")
+    at = good.index(b"IDAT")
+    (n,) = struct.unpack(">I", good[at - 4: at])
+    body = bytearray(good[at + 4: at + 4 + n])
+    for k in range(40, min(len(body), 400), 7):
+        body[k] ^= 0x5A
+    bad = good[: at - 4] + _chunk(b"IDAT", bytes(body)) + good[at + 8 + n:]
+    ctx.set_lanes(2)
+    try:
+        t_bad = ctx.submit([{"file": good}, {"file": bad}], "vertical")
+        t_ok = ctx.submit([{"file": good}, {"file": good}], "vertical")
+        with pytest.raises(StitchError) as ei:
+            ctx.wait(t_bad)
+        assert ei.value.status == L.E_BAD_IMAGE and "解码异常" in ei.value.message
+        ok = ctx.wait(t_ok)
+        again = ctx.wait(ctx.submit([{"file": good}, {"file": good}], "vertical"))
+        assert np.array_equal(ok.rgba, again.rgba)
+    finally:
+        ctx.set_lanes(1)
+    files = [data for name, data in matrix() if name in ("pil_RGB", "pil_RGBA", "pil_L", "pil_LA", "pil_palette", "gray1", "palette4",
+                                                         "ct6_d16", "fixed")]
+    assert len(files) == 9
+    bitmaps = [P.decode(f) for f in files]
+    want = ctx.run([{"naturalWidth": b.shape[1], "naturalHeight": b.shape[0], "bitmap": b} for b in bitmaps], "horizontal")
+    got = ctx.run([{"file": f} for f in files], "horizontal")
+    assert np.array_equal(got.rgba, want.rgba)
