@@ -635,7 +635,14 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
   const uint32_t n_words = (I.row_bytes + 3u) >> 2;
   const int groups = (I.h + 31) / 32;
   volatile uint32_t* progress = I.progress;
-  for (int g = (int)blockIdx.x * kUnfWarps + wv; g < groups; g += (int)gridDim.x * kUnfWarps) {
+  (void)wv;
+  for (;;) {
+    // groups are handed out in order: a group is only ever started by a warp that is running, after every group
+    // before it has been started -- so the waits below cannot depend on a CTA that has not been scheduled yet
+    int g = 0;
+    if (lane == 0) g = (int)atomicAdd(&I.ctr[8], 1u);
+    g = __shfl_sync(0xffffffffu, g, 0);
+    if (g >= groups) break;
     const int y = g * 32 + lane;
     const bool active = y < I.h;
     const int yy = active ? y : g * 32;
@@ -645,6 +652,23 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
       ft = 0;
     }
     const bool any_paeth = __any_sync(0xffffffffu, ft == 4);
+    // No Average / Paeth row in the group: nothing looks diagonally, so the 32 rows can work on the SAME pixel in a
+    // step -- Sub adds the lane's own previous pixel, a run of Up rows is a prefix sum down the lanes (a segmented
+    // scan by shuffles) -- and the next group may follow 8 pixels behind instead of 31 + 16.
+    const bool flat = !__any_sync(0xffffffffu, ft >= 3);
+    const int skew = flat ? 0 : lane;
+    uint32_t take = 0;   // bit k: this lane adds the value 2^k lanes below it in scan step k
+    if (flat) {
+      bool head = lane == 0 || ft != 2;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const bool below = __shfl_up_sync(0xffffffffu, head, 1 << k);
+        if (lane >= (1 << k)) {
+          if (!head) take |= 1u << k;
+          head = head || below;
+        }
+      }
+    }
     // word j of this lane's row: base + (j >> 2) * 128 + (j & 3)   (uint32 units, see t_word)
     const uint32_t* in_row = I.rawT + t_word(chunks, yy, 0);
     uint32_t* out_row = I.outT + t_word(chunks, yy, 0);
@@ -655,7 +679,7 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
     uint32_t inj = 0, outj = 0;
     uint32_t pre = (active && n_words) ? in_row[0] : 0u;   // always one word ahead
     uint32_t seen = 0;                                      // progress of the group above, as last read
-    const int steps = wp + 31;
+    const int steps = wp + (flat ? 0 : 31);
     for (int s = 0; s < steps; ++s) {
       if ((s & (kUpBatch - 1)) == 0 && g && s < wp) {
         const uint32_t need = (uint32_t)min(wp, s + kUpBatch);
@@ -686,7 +710,7 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
         const uint32_t below1 = __shfl_up_sync(0xffffffffu, prev1, 1);
         up1 = lane == 0 ? (g ? up1 : 0u) : below1;
       }
-      const int x = s - lane;
+      const int x = s - skew;
       const bool valid = active && x >= 0 && x < wp;
       if (x == 0) {
         left0 = left1 = 0;
@@ -704,12 +728,28 @@ __device__ void unfilter_image(const Batch& B, const Img& I) {
         const uint32_t f1 = WIDE ? (uint32_t)(inbuf >> 32) & (BPP >= 8 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u) : 0u;
         inbuf = BPP >= 8 ? 0ull : inbuf >> (8 * (BPP & 7));
         incnt -= BPP;
-        cur0 = __vadd4(f0, predict4(ft, any_paeth, left0, up0, ul0));
-        if (BPP < 4) cur0 &= (1u << (8 * (BPP & 3))) - 1u;
-        if (WIDE) {
-          cur1 = __vadd4(f1, predict4(ft, any_paeth, left1, up1, ul1));
-          if (BPP < 8) cur1 &= (1u << (8 * (BPP & 3))) - 1u;
+        if (flat) {   // Sub here; Up is the scan below (lane 0 takes the row above directly)
+          cur0 = __vadd4(f0, ft == 1 ? left0 : (lane == 0 && ft == 2) ? up0 : 0u);
+          if (WIDE) cur1 = __vadd4(f1, ft == 1 ? left1 : (lane == 0 && ft == 2) ? up1 : 0u);
+        } else {
+          cur0 = __vadd4(f0, predict4(ft, any_paeth, left0, up0, ul0));
+          if (WIDE) cur1 = __vadd4(f1, predict4(ft, any_paeth, left1, up1, ul1));
         }
+      }
+      if (flat) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+          const uint32_t t0 = __shfl_up_sync(0xffffffffu, cur0, 1 << k);
+          if (take & (1u << k)) cur0 = __vadd4(cur0, t0);
+          if (WIDE) {
+            const uint32_t t1 = __shfl_up_sync(0xffffffffu, cur1, 1 << k);
+            if (take & (1u << k)) cur1 = __vadd4(cur1, t1);
+          }
+        }
+      }
+      if (valid) {
+        if (BPP < 4) cur0 &= (1u << (8 * (BPP & 3))) - 1u;
+        if (WIDE && BPP < 8) cur1 &= (1u << (8 * (BPP & 3))) - 1u;
         outbuf |= (WIDE ? ((uint64_t)cur1 << 32) | cur0 : (uint64_t)cur0) << (8 * outcnt);
         outcnt += BPP;
         while (outcnt >= 4) {
