@@ -230,6 +230,8 @@ __device__ __forceinline__ void start_at(DecState& st, const uint8_t* z, uint32_
   st.bitpos = bit;
   st.end_bit = 0;
   st.hdr = 0;
+  st.rep_nbits = 0;
+  st.rep_bits = st.rep_len_dist = st.rep_len = 0;
   st.status = bit < st.z_bits ? (uint32_t)kRunning : (uint32_t)kBad;
   if (st.status == kRunning) st.br.init(z, bit);
 }

