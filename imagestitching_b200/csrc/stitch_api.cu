@@ -711,7 +711,27 @@ struct StagedUploads {
 
 // defer == nullptr: everything that needs the host is done here (stitch_run).  Otherwise nothing waits for the GPU
 // and *defer says what finalize_job still owes (stitch_submit).
+int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, PendingJob* defer);
+
+// A job that fails half-way may already have copies in flight that read the caller's bitmaps or write the caller's
+// canvas: the error is only returned once the lane's streams (and the host copy threads) are done with them.
 int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, PendingJob* defer) {
+  const int st = enqueue_job_impl(ctx, ln, job, res, defer);
+  if (st != STITCH_OK && ctx && st != STITCH_E_BAD_ARG && st != STITCH_E_EMPTY && st != STITCH_E_TOO_MANY) {
+    const std::string keep = ctx->last_error;
+    if (ln.ul_stream) cudaStreamSynchronize(ln.ul_stream);
+    if (ln.stream) cudaStreamSynchronize(ln.stream);
+    if (ln.dl_stream) cudaStreamSynchronize(ln.dl_stream);
+    if (ln.host_copies)
+      while (ln.host_copies->load(std::memory_order_acquire) > 0) std::this_thread::yield();
+    cudaGetLastError();
+    ln.pngdec_active = false;
+    ctx->last_error = keep;
+  }
+  return st;
+}
+
+int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* res, PendingJob* defer) {
   if (!ctx || !job || !res) return fail(ctx, STITCH_E_BAD_ARG, "null argument");
   if (job->n <= 0) return fail(ctx, STITCH_E_EMPTY, "empty image list");  // P:1189
   if (!job->images) return fail(ctx, STITCH_E_BAD_ARG, "images == NULL");
