@@ -50,7 +50,11 @@ using namespace stitch::pnginf;
 
 constexpr int kSubBits = 512;      // nominal length of a subsequence of a block's bits
 constexpr int kBlkThreads = 256;   // subsequences per window (one CTA pass over 16 KB of the block)
-constexpr int kJumpRounds = 32;  // >= log2(longest chain: < 2^31 bytes) + 1
+constexpr int kJumpRounds = 16;  // a round shortens every chain to <= 1 / (kHops + 1) of its length: 5^14 > 2^31, + 1 to see that nothing moves
+#ifndef PINF_HOPS
+#define PINF_HOPS 4
+#endif
+constexpr int kHops = PINF_HOPS;  // links followed per round and entry
 constexpr int kUnfWarps = 4;      // warps per CTA of the unfilter kernel
 constexpr int kUnfCtas = 24;      // CTAs per image: 96 row groups in flight (more would only wait for the wavefront)
 
@@ -544,15 +548,24 @@ __global__ void __launch_bounds__(256) pinf_jump_kernel(Batch B) {
     if ((s.x & s.y & s.z & s.w) == kRoot) continue;
     bool ch = false;
     uint32_t* e = &s.x;
-    uint32_t t[4];
+    // up to kHops links per round (the entries read may have been shortened already by other threads: any value on
+    // the chain is a valid one): the chain of a byte shrinks by more than kHops + 1 per round, and the 4 bytes of
+    // src per image byte are streamed a third as often as with one link per round
+#pragma unroll 1
+    for (int hop = 0; hop < kHops; ++hop) {
+      uint32_t t[4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) t[k] = e[k] != kRoot ? I.src[e[k]] : kRoot;
+      for (int k = 0; k < 4; ++k) t[k] = e[k] != kRoot ? I.src[e[k]] : kRoot;
+      bool moved = false;
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      if (t[k] != kRoot) {
-        e[k] = t[k];
-        ch = true;
+      for (int k = 0; k < 4; ++k) {
+        if (t[k] != kRoot) {
+          e[k] = t[k];
+          moved = true;
+        }
       }
+      if (!moved) break;
+      ch = true;
     }
     if (ch) {
       reinterpret_cast<uint4*>(I.src)[i4] = s;
