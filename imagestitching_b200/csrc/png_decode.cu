@@ -109,7 +109,12 @@ __global__ void __launch_bounds__(256) pinf_gather_kernel(Batch B) {
 }
 
 // ---- P1: one thread per stream byte, its 8 bit offsets ----
+// header_prefilter (png_inflate_core.h) with the Kraft sum of the code-length code taken three 3-bit lengths at a time
+// from a 512-entry table in shared memory: 7 look-ups instead of a 19-step loop (this kernel is pure instruction count).
 __global__ void __launch_bounds__(256) pinf_find_kernel(Batch B) {
+  __shared__ uint8_t kraft3[512];
+  for (int e = threadIdx.x; e < 512; e += 256) kraft3[e] = kraft3_entry(e);
+  __syncthreads();
   const Img& I = B.img[blockIdx.y];
   const uint32_t byte = blockIdx.x * 256u + threadIdx.x;
   const uint32_t z_bits = I.z_len * 8u;
@@ -126,7 +131,7 @@ __global__ void __launch_bounds__(256) pinf_find_kernel(Batch B) {
     bool hit = false;
     if (live && p + 32u <= z_bits) {
       const uint64_t b = j ? (b0 >> j) | (b1 << (64 - j)) : b0;
-      hit = header_prefilter(b, b1 >> j);
+      hit = header_prefilter_tab(b, b1 >> j, kraft3);
     }
     const unsigned m = __ballot_sync(0xffffffffu, hit);
     if (m) {
@@ -391,6 +396,18 @@ __global__ void __launch_bounds__(kBlkThreads, 2) pinf_count_kernel(Batch B) {
       rec->n_out = tot_out;
       rec->n_tok = tot_tok;
       rec->first_sub = first_sub;
+      // the candidate that starts where this block ends, looked up here -- 1000 blocks at once -- so that the chain
+      // walk is one dependent load per block instead of three
+      uint32_t nx = kNoSub;
+      for (uint32_t slot = hash_pos(end_bit) & I.hmask;; slot = (slot + 1u) & I.hmask) {
+        const uint32_t k = I.hkey[slot];
+        if (k == 0u) break;
+        if (k == end_bit + 1u) {
+          nx = I.hval[slot];
+          break;
+        }
+      }
+      rec->next = nx;
       __threadfence();
       rec->flags = (S.hdr & 1u) | ((S.hdr >> 1) << 1) | kRecValid;
     }
@@ -411,10 +428,14 @@ __global__ void __launch_bounds__(32) pinf_walk_kernel(Batch B) {
   bind_slow(T, slow);
   const uint32_t n_cand = I.ctr[1] < I.cand_cap ? I.ctr[1] : I.cand_cap;
   uint32_t pos = 16, out = 0, nt = 0, nb = 0, err = 0;
+  uint32_t hint = kNoSub;   // the previous block's `next`
   for (;;) {
     BlockRec rec;
     rec.flags = 0;
-    if (n_cand) {
+    if (hint != kNoSub) {
+      rec = I.cand[hint];
+      if (rec.bitpos != pos) rec.flags = 0;
+    } else if (n_cand) {
       uint32_t slot = hash_pos(pos) & I.hmask;
       for (;;) {
         const uint32_t k = I.hkey[slot];
@@ -437,6 +458,7 @@ __global__ void __launch_bounds__(32) pinf_walk_kernel(Batch B) {
       break;
     }
     I.chain[nb++] = make_uint4(pos, out, nt, rec.first_sub);
+    hint = (rec.flags & kRecValid) ? rec.next : kNoSub;
     out += rec.n_out;
     nt += rec.n_tok;
     pos = rec.end_bit;
@@ -641,159 +663,172 @@ constexpr int kUpBatch = 8;   // pixels of the row above that lane 0 fetches at 
 // another warp -- which publishes how far its last row has got every 8 steps; its bytes are read back through L2, 8
 // pixels at a time.  Rows stream through two small byte queues per lane (4-byte loads from rawT, 4-byte stores to
 // outT).  The time of this kernel is its dependency chain: (rows + width) steps of one pixel each.
-template <int BPP>
-__device__ void unfilter_image(const Batch& B, const Img& I) {
+//
+// FLAT: no Average / Paeth row in the group -- nothing looks diagonally, so the 32 rows work on the SAME pixel in a
+// step (Sub adds the lane's own previous pixel, a run of Up rows is a prefix sum down the lanes: a segmented scan by
+// shuffles) and the next group may follow 8 pixels behind instead of 31 + 16.
+template <int BPP, bool FLAT>
+__device__ __forceinline__ void unfilter_group(const Batch& B, const Img& I, int g, int ft, bool active, bool any_paeth, int lane) {
   constexpr bool WIDE = BPP > 4;
-  const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+  constexpr uint32_t kMask0 = BPP >= 4 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u;
+  constexpr uint32_t kMask1 = BPP >= 8 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u;
   const uint32_t chunks = I.t_chunks;
   const int wp = (int)(I.row_bytes / (uint32_t)BPP);
   const uint32_t n_words = (I.row_bytes + 3u) >> 2;
-  const int groups = (I.h + 31) / 32;
   volatile uint32_t* progress = I.progress;
-  (void)wv;
+  const int yy = active ? g * 32 + lane : g * 32;
+  const int skew = FLAT ? 0 : lane;
+  uint32_t take = 0;   // FLAT: bit k = this lane adds the value 2^k lanes below it in scan step k
+  if (FLAT) {
+    bool head = lane == 0 || ft != 2;
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      const bool below = __shfl_up_sync(0xffffffffu, head, 1 << k);
+      if (lane >= (1 << k)) {
+        if (!head) take |= 1u << k;
+        head = head || below;
+      }
+    }
+  }
+  // word j of this lane's row: base + (j >> 2) * 128 + (j & 3)   (uint32 units, see t_word)
+  const uint32_t* in_row = I.rawT + t_word(chunks, yy, 0);
+  uint32_t* out_row = I.outT + t_word(chunks, yy, 0);
+  const uint8_t* above = g ? reinterpret_cast<const uint8_t*>(I.outT + t_word(chunks, g * 32 - 1, 0)) : nullptr;
+  uint32_t left0 = 0, left1 = 0, ul0 = 0, ul1 = 0, prev0 = 0, prev1 = 0, upb0 = 0, upb1 = 0;
+  uint64_t inbuf = 0, outbuf = 0;
+  int incnt = 0, outcnt = 0;
+  uint32_t inj = 0, outj = 0;
+  uint32_t pre = (active && n_words) ? in_row[0] : 0u;   // always one word ahead
+  uint32_t seen = 0;                                      // progress of the group above, as last read
+  auto pull = [&]() {   // one more word into the input queue, the next one requested
+    inbuf |= (uint64_t)pre << (8 * incnt);
+    incnt += 4;
+    ++inj;
+    pre = inj < n_words ? in_row[(inj >> 2) * 128u + (inj & 3u)] : 0u;
+  };
+  auto push = [&]() {   // one word out of the output queue
+    out_row[(outj >> 2) * 128u + (outj & 3u)] = (uint32_t)outbuf;
+    ++outj;
+    outbuf >>= 32;
+    outcnt -= 4;
+  };
+  const int steps = wp + (FLAT ? 0 : 31);
+  for (int s = 0; s < steps; ++s) {
+    if ((s & (kUpBatch - 1)) == 0 && g && s < wp) {
+      const uint32_t need = (uint32_t)min(wp, s + kUpBatch);
+      if (seen < need) {
+        while ((seen = progress[g - 1]) < need) {
+        }
+        __threadfence();
+      }
+      const int px = s + lane;
+      uint32_t v0 = 0, v1 = 0;
+      if (lane < kUpBatch && px < wp) {
+#pragma unroll
+        for (int k = 0; k < BPP; ++k) {
+          const uint32_t bo = (uint32_t)px * BPP + k;
+          const uint32_t byte = __ldcg(above + ((size_t)(bo >> 4) * 128 + ((bo >> 2) & 3)) * 4 + (bo & 3));
+          if (k < 4) v0 |= byte << (8 * k);
+          else v1 |= byte << (8 * (k - 4));
+        }
+      }
+      upb0 = v0;
+      upb1 = v1;
+    }
+    uint32_t up0 = __shfl_sync(0xffffffffu, upb0, s & (kUpBatch - 1)), up1 = 0;
+    if (WIDE) up1 = __shfl_sync(0xffffffffu, upb1, s & (kUpBatch - 1));
+    if (!g) up0 = up1 = 0;
+    if (!FLAT) {
+      const uint32_t below0 = __shfl_up_sync(0xffffffffu, prev0, 1);
+      up0 = lane == 0 ? up0 : below0;
+      if (WIDE) {
+        const uint32_t below1 = __shfl_up_sync(0xffffffffu, prev1, 1);
+        up1 = lane == 0 ? up1 : below1;
+      }
+    }
+    const int x = s - skew;
+    const bool valid = active && x >= 0 && x < wp;
+    if (x == 0) {
+      left0 = left1 = 0;
+      ul0 = ul1 = 0;
+    }
+    uint32_t cur0 = 0, cur1 = 0;
+    if (valid) {
+      if (incnt < BPP) pull();
+      if (BPP > 4 && incnt < BPP) pull();
+      const uint32_t f0 = (uint32_t)inbuf & kMask0;
+      const uint32_t f1 = WIDE ? (uint32_t)(inbuf >> 32) & kMask1 : 0u;
+      inbuf = BPP >= 8 ? 0ull : inbuf >> (8 * (BPP & 7));
+      incnt -= BPP;
+      if (FLAT) {   // Sub here; Up is the scan below (lane 0 takes the row above directly)
+        cur0 = __vadd4(f0, ft == 1 ? left0 : (lane == 0 && ft == 2) ? up0 : 0u);
+        if (WIDE) cur1 = __vadd4(f1, ft == 1 ? left1 : (lane == 0 && ft == 2) ? up1 : 0u);
+      } else {
+        cur0 = __vadd4(f0, predict4(ft, any_paeth, left0, up0, ul0));
+        if (WIDE) cur1 = __vadd4(f1, predict4(ft, any_paeth, left1, up1, ul1));
+      }
+    }
+    if (FLAT) {
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const uint32_t t0 = __shfl_up_sync(0xffffffffu, cur0, 1 << k);
+        if (take & (1u << k)) cur0 = __vadd4(cur0, t0);
+        if (WIDE) {
+          const uint32_t t1 = __shfl_up_sync(0xffffffffu, cur1, 1 << k);
+          if (take & (1u << k)) cur1 = __vadd4(cur1, t1);
+        }
+      }
+    }
+    if (valid) {
+      cur0 &= kMask0;
+      if (WIDE) cur1 &= kMask1;
+      outbuf |= (WIDE ? ((uint64_t)cur1 << 32) | cur0 : (uint64_t)cur0) << (8 * outcnt);
+      outcnt += BPP;
+      if (outcnt >= 4) push();
+      if (BPP > 4 && outcnt >= 4) push();
+      if (x == wp - 1 && outcnt > 0) {
+        push();
+        outcnt = 0;
+      }
+    }
+    left0 = cur0;
+    left1 = cur1;
+    ul0 = up0;
+    ul1 = up1;
+    prev0 = cur0;
+    prev1 = cur1;
+    if ((s & 7) == 7 || s == steps - 1) {
+      __syncwarp();
+      if (lane == 31 && active) {
+        __threadfence();
+        const uint32_t done = s == steps - 1 ? (uint32_t)wp : (outj * 4u) / (uint32_t)BPP;
+        progress[g] = done;
+      }
+    }
+  }
+}
+
+template <int BPP>
+__device__ void unfilter_image(const Batch& B, const Img& I) {
+  const int lane = threadIdx.x & 31;
+  const int groups = (I.h + 31) / 32;
   for (;;) {
     // groups are handed out in order: a group is only ever started by a warp that is running, after every group
-    // before it has been started -- so the waits below cannot depend on a CTA that has not been scheduled yet
+    // before it has been started -- so the waits cannot depend on a CTA that has not been scheduled yet
     int g = 0;
     if (lane == 0) g = (int)atomicAdd(&I.ctr[8], 1u);
     g = __shfl_sync(0xffffffffu, g, 0);
     if (g >= groups) break;
     const int y = g * 32 + lane;
     const bool active = y < I.h;
-    const int yy = active ? y : g * 32;
     int ft = active ? I.raw[(size_t)y * (I.row_bytes + 1u)] : 0;
     if (ft > 4) {
       atomicOr(B.status, (uint32_t)kErrFilter);
       ft = 0;
     }
     const bool any_paeth = __any_sync(0xffffffffu, ft == 4);
-    // No Average / Paeth row in the group: nothing looks diagonally, so the 32 rows can work on the SAME pixel in a
-    // step -- Sub adds the lane's own previous pixel, a run of Up rows is a prefix sum down the lanes (a segmented
-    // scan by shuffles) -- and the next group may follow 8 pixels behind instead of 31 + 16.
-    const bool flat = !__any_sync(0xffffffffu, ft >= 3);
-    const int skew = flat ? 0 : lane;
-    uint32_t take = 0;   // bit k: this lane adds the value 2^k lanes below it in scan step k
-    if (flat) {
-      bool head = lane == 0 || ft != 2;
-#pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const bool below = __shfl_up_sync(0xffffffffu, head, 1 << k);
-        if (lane >= (1 << k)) {
-          if (!head) take |= 1u << k;
-          head = head || below;
-        }
-      }
-    }
-    // word j of this lane's row: base + (j >> 2) * 128 + (j & 3)   (uint32 units, see t_word)
-    const uint32_t* in_row = I.rawT + t_word(chunks, yy, 0);
-    uint32_t* out_row = I.outT + t_word(chunks, yy, 0);
-    const uint8_t* above = g ? reinterpret_cast<const uint8_t*>(I.outT + t_word(chunks, g * 32 - 1, 0)) : nullptr;
-    uint32_t left0 = 0, left1 = 0, ul0 = 0, ul1 = 0, prev0 = 0, prev1 = 0, upb0 = 0, upb1 = 0;
-    uint64_t inbuf = 0, outbuf = 0;
-    int incnt = 0, outcnt = 0;
-    uint32_t inj = 0, outj = 0;
-    uint32_t pre = (active && n_words) ? in_row[0] : 0u;   // always one word ahead
-    uint32_t seen = 0;                                      // progress of the group above, as last read
-    const int steps = wp + (flat ? 0 : 31);
-    for (int s = 0; s < steps; ++s) {
-      if ((s & (kUpBatch - 1)) == 0 && g && s < wp) {
-        const uint32_t need = (uint32_t)min(wp, s + kUpBatch);
-        if (seen < need) {
-          while ((seen = progress[g - 1]) < need) {
-          }
-          __threadfence();
-        }
-        const int px = s + lane;
-        uint32_t v0 = 0, v1 = 0;
-        if (lane < kUpBatch && px < wp) {
-#pragma unroll
-          for (int k = 0; k < BPP; ++k) {
-            const uint32_t bo = (uint32_t)px * BPP + k;
-            const uint32_t byte = __ldcg(above + ((size_t)(bo >> 4) * 128 + ((bo >> 2) & 3)) * 4 + (bo & 3));
-            if (k < 4) v0 |= byte << (8 * k);
-            else v1 |= byte << (8 * (k - 4));
-          }
-        }
-        upb0 = v0;
-        upb1 = v1;
-      }
-      uint32_t up0 = __shfl_sync(0xffffffffu, upb0, s & (kUpBatch - 1)), up1 = 0;
-      const uint32_t below0 = __shfl_up_sync(0xffffffffu, prev0, 1);
-      up0 = lane == 0 ? (g ? up0 : 0u) : below0;
-      if (WIDE) {
-        up1 = __shfl_sync(0xffffffffu, upb1, s & (kUpBatch - 1));
-        const uint32_t below1 = __shfl_up_sync(0xffffffffu, prev1, 1);
-        up1 = lane == 0 ? (g ? up1 : 0u) : below1;
-      }
-      const int x = s - skew;
-      const bool valid = active && x >= 0 && x < wp;
-      if (x == 0) {
-        left0 = left1 = 0;
-        ul0 = ul1 = 0;
-      }
-      uint32_t cur0 = 0, cur1 = 0;
-      if (valid) {
-        while (incnt < BPP) {
-          inbuf |= (uint64_t)pre << (8 * incnt);
-          incnt += 4;
-          ++inj;
-          pre = inj < n_words ? in_row[(inj >> 2) * 128u + (inj & 3u)] : 0u;
-        }
-        const uint32_t f0 = (uint32_t)inbuf & (BPP >= 4 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u);
-        const uint32_t f1 = WIDE ? (uint32_t)(inbuf >> 32) & (BPP >= 8 ? 0xFFFFFFFFu : (1u << (8 * (BPP & 3))) - 1u) : 0u;
-        inbuf = BPP >= 8 ? 0ull : inbuf >> (8 * (BPP & 7));
-        incnt -= BPP;
-        if (flat) {   // Sub here; Up is the scan below (lane 0 takes the row above directly)
-          cur0 = __vadd4(f0, ft == 1 ? left0 : (lane == 0 && ft == 2) ? up0 : 0u);
-          if (WIDE) cur1 = __vadd4(f1, ft == 1 ? left1 : (lane == 0 && ft == 2) ? up1 : 0u);
-        } else {
-          cur0 = __vadd4(f0, predict4(ft, any_paeth, left0, up0, ul0));
-          if (WIDE) cur1 = __vadd4(f1, predict4(ft, any_paeth, left1, up1, ul1));
-        }
-      }
-      if (flat) {
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-          const uint32_t t0 = __shfl_up_sync(0xffffffffu, cur0, 1 << k);
-          if (take & (1u << k)) cur0 = __vadd4(cur0, t0);
-          if (WIDE) {
-            const uint32_t t1 = __shfl_up_sync(0xffffffffu, cur1, 1 << k);
-            if (take & (1u << k)) cur1 = __vadd4(cur1, t1);
-          }
-        }
-      }
-      if (valid) {
-        if (BPP < 4) cur0 &= (1u << (8 * (BPP & 3))) - 1u;
-        if (WIDE && BPP < 8) cur1 &= (1u << (8 * (BPP & 3))) - 1u;
-        outbuf |= (WIDE ? ((uint64_t)cur1 << 32) | cur0 : (uint64_t)cur0) << (8 * outcnt);
-        outcnt += BPP;
-        while (outcnt >= 4) {
-          out_row[(outj >> 2) * 128u + (outj & 3u)] = (uint32_t)outbuf;
-          ++outj;
-          outbuf >>= 32;
-          outcnt -= 4;
-        }
-        if (x == wp - 1 && outcnt > 0) {
-          out_row[(outj >> 2) * 128u + (outj & 3u)] = (uint32_t)outbuf;
-          ++outj;
-          outcnt = 0;
-        }
-      }
-      left0 = cur0;
-      left1 = cur1;
-      ul0 = up0;
-      ul1 = up1;
-      prev0 = cur0;
-      prev1 = cur1;
-      if ((s & 7) == 7 || s == steps - 1) {
-        __syncwarp();
-        if (lane == 31 && active) {
-          __threadfence();
-          const uint32_t done = s == steps - 1 ? (uint32_t)wp : (outj * 4u) / (uint32_t)BPP;
-          progress[g] = done;
-        }
-      }
-    }
+    if (__any_sync(0xffffffffu, ft >= 3)) unfilter_group<BPP, false>(B, I, g, ft, active, any_paeth, lane);
+    else unfilter_group<BPP, true>(B, I, g, ft, active, false, lane);
   }
 }
 

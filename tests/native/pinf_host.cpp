@@ -137,3 +137,30 @@ extern "C" int pinf_host_sync_stats(const uint8_t* z_in, uint32_t z_len, uint32_
   }
   return 0;
 }
+
+// header_prefilter_tab (what the finder kernel runs) against header_prefilter on n pseudo-random 128-bit windows and on
+// every bit offset of a stream; returns the number of disagreements, *hits = windows that pass.
+extern "C" uint32_t pinf_host_prefilter_check(const uint8_t* z_in, uint32_t z_len, uint32_t n_random, uint32_t* hits) {
+  uint8_t tab[512];
+  for (int e = 0; e < 512; ++e) tab[e] = kraft3_entry(e);
+  uint32_t bad = 0, h = 0;
+  uint64_t x = 0x9E3779B97F4A7C15ull;
+  auto next = [&]() { x ^= x << 13; x ^= x >> 7; x ^= x << 17; return x; };
+  for (uint32_t i = 0; i < n_random; ++i) {
+    uint64_t b = next(), b2 = next();
+    if (i & 1) b = (b & ~6ull) | 4ull;   // half of them with block type 2, so the interesting path is taken often
+    const bool a = header_prefilter(b, b2), t = header_prefilter_tab(b, b2, tab);
+    bad += a != t;
+    h += a;
+  }
+  std::vector<uint8_t> zbuf((size_t)z_len + 32, 0);
+  std::memcpy(zbuf.data(), z_in, z_len);
+  for (uint32_t p = 16; p + 32 <= z_len * 8u; ++p) {
+    const uint64_t b = bits_at(zbuf.data(), p), b2 = bits_at(zbuf.data(), p + 64);
+    const bool a = header_prefilter(b, b2), t = header_prefilter_tab(b, b2, tab);
+    bad += a != t;
+    h += a;
+  }
+  *hits = h;
+  return bad;
+}

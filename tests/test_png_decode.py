@@ -278,6 +278,18 @@ def test_kernel_pieces_on_the_cpu_equal_zlib():
     assert _host_inflate(lib, z, len(walk) + 1)[0] != 0
 
 
+def test_finder_table_test_equals_the_loop():
+    """The block finder's table-driven header test == the plain one, on 2 M random windows and every offset of a stream."""
+    lib = _host_lib()
+    lib.pinf_host_prefilter_check.restype = ctypes.c_uint32
+    lib.pinf_host_prefilter_check.argtypes = [ctypes.c_char_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p]
+    rng = np.random.default_rng(2)
+    z = zlib.compress((np.cumsum(rng.integers(-3, 4, 300000)) % 256).astype(np.uint8).tobytes(), 6)
+    hits = ctypes.c_uint32(0)
+    assert lib.pinf_host_prefilter_check(z, len(z), 2_000_000, ctypes.byref(hits)) == 0
+    assert hits.value > 1000
+
+
 # ---------------- GPU ----------------
 @pytest.mark.gpu
 def test_gpu_decoder_equals_oracle_on_the_matrix(ctx):
