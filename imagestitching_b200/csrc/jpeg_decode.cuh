@@ -74,16 +74,10 @@ struct DecBatch {
   int32_t flag_cur;           // flag this round raises
   int32_t flag_prev;          // flag of the round before (-1: none, the host decides whether to launch)
   uint32_t sub;               // raw bytes per subsequence (jdec_pick_sub)
+  __device__ __forceinline__ const DecImage& item(int i) const { return img[i]; }
 };
 
-// ---- Huffman tables in shared memory ----
-struct SmemTables {
-  uint16_t lut[4][256];       // first 8 bits -> (length << 8 | symbol), 0 = longer than 8 bits
-  int32_t maxcode[4][17];     // per length 1..16, -1 = no codes
-  int32_t mincode[4][17];
-  int32_t valptr[4][17];
-  uint8_t vals[4][256];
-};
+// ---- Huffman tables in shared memory (SmemTables: jpeg_parse.h) ----
 
 __device__ __forceinline__ void build_tables(const Tables* __restrict__ g, SmemTables& s) {
   for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) {
@@ -359,6 +353,12 @@ __device__ __forceinline__ State guess_state(const DecImage& I, uint32_t i, uint
   return s;
 }
 
+// What the shared synchronisation / prefix kernels ask of a batch item (progressive scans answer in jpeg_prog.cuh).
+__device__ __forceinline__ State decode_nowrite(const DecImage& I, const SmemTables& T, State s, uint32_t end_byte, uint32_t* started) {
+  return decode_range<false>(I, T, s, end_byte, started, 0);
+}
+__device__ __forceinline__ uint32_t scan_start_word(const DecImage&) { return 0u; }   // packed state at byte 0: block 0, DC
+
 // D1: first pass from guessed states.
 __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_constant__ DecBatch B) {
   __shared__ SmemTables T;
@@ -381,7 +381,8 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_c
 // Rounds are enqueued back to back without a host round trip: round r raises changed[r], and round r + 1 returns at
 // once when changed[r] is still zero (the chains have converged: 2 rounds for photos), so a fixed number of launches
 // costs a few empty grids; the host looks at the LAST flag when the job is waited for.
-__global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_constant__ DecBatch B) {
+template <class BATCH>
+__global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_constant__ BATCH B) {
   if (B.flag_prev >= 0 && B.changed[B.flag_prev] == 0u) return;   // grid-uniform: converged in an earlier round
   __shared__ SmemTables T;
   __shared__ uint2 sh_state[JDEC_THREADS + 1];   // [s + 1] = end state of subsequence s; [0] = predecessor block's last
@@ -390,7 +391,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
   __shared__ uint16_t sh_list[JDEC_THREADS];
   __shared__ int sh_warp_n[JDEC_THREADS / 32];
   __shared__ int sh_last_moved;
-  const DecImage& I = B.img[blockIdx.y];
+  const auto& I = B.item(blockIdx.y);
   if (blockIdx.x * JDEC_THREADS >= (unsigned)I.n_sub) return;
   build_tables(I.tab, T);
   const int t = threadIdx.x, lane = t & 31, wp = t >> 5;
@@ -406,7 +407,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
     sh_dirty[1][t + 1] = 0;
   }
   if (t == 0) {
-    uint2 in = make_uint2(0u, 0u);               // the scan starts at byte 0, bit 0, block 0, DC
+    uint2 in = make_uint2(0u, scan_start_word(I));   // the scan starts at byte 0, bit 0, block 0, DC
     if (base > 0) {
       const uint4 p = I.state[base - 1];
       in = make_uint2(p.x, p.y);
@@ -445,7 +446,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
     if (t < total) {
       s = sh_list[t];
       const uint2 ps = sh_state[s];
-      const State e = decode_range<false>(I, T, unpack_state(ps.x, ps.y), (base + s + 1) * B.sub, &started, 0);
+      const State e = decode_nowrite(I, T, unpack_state(ps.x, ps.y), (base + s + 1) * B.sub, &started);
       fresh = make_uint2(e.byte, pack_state(e));
     }
     __syncthreads();
@@ -471,10 +472,11 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
 }
 
 // D3: exclusive scan of the blocks-started counts (one block per image).
-__global__ void __launch_bounds__(1024) jdec_scan_kernel(const __grid_constant__ DecBatch B) {
+template <class BATCH>
+__global__ void __launch_bounds__(1024) jdec_scan_kernel(const __grid_constant__ BATCH B) {
   __shared__ uint32_t warp_sum[32];
   __shared__ uint32_t carry_s;
-  const DecImage& I = B.img[blockIdx.x];
+  const auto& I = B.item(blockIdx.x);
   const int t = threadIdx.x, lane = t & 31, w = t >> 5;
   if (t == 0) carry_s = 0;
   __syncthreads();

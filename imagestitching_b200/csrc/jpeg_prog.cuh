@@ -1,0 +1,249 @@
+// Progressive JPEG (SOF2) decoding on the GPU: the entropy kernels.  The back end (dequantise + IDCT, chroma
+// upsampling + colour) is the baseline decoder's (jpeg_decode.cuh D6, D7) over the same coefficient buffer.
+//
+// A progressive file is a list of scans, each coding one spectral band of one component (or the DC terms of all of
+// them) at one precision (T.81 Annex G).  Which of them can run side by side follows from what they touch:
+//   * FIRST scans (Ah = 0) of a band touch coefficients nothing else has written, and their symbols do not depend on
+//     the coefficients: all first scans of all files of a job go through the self-synchronising decoder of the
+//     baseline path in ONE set of launches -- a scan is a batch item like a baseline file is.  State per subsequence:
+//     (bit position, block-in-MCU) for DC scans, (bit position, zig-zag index) for AC scans; an EOB run of n blocks is
+//     one symbol that completes n blocks, so the block index of a subsequence is again a prefix sum (of blocks
+//     COMPLETED).  DC differences are written in scan order and turned into values by a segmented scan per component.
+//   * REFINEMENT scans (Ah > 0) read one correction bit per coefficient that is ALREADY non-zero in the block they are
+//     in, so a thread that guesses its start cannot even parse: they are decoded by one thread per scan
+//     (pscan_sequential, jpeg_prog_core.h).  Scans that touch disjoint (component, band) sets share a launch: the host
+//     orders them in dependency levels (Y / Cb / Cr refinements of the usual script run side by side).
+#pragma once
+#include "jpeg_decode.cuh"
+#include "jpeg_prog_core.h"
+
+namespace stitch {
+namespace jpegdec {
+
+struct PBatch {
+  const PScan* scans;         // device array: the first scans of every file of the job
+  uint32_t* changed;
+  int32_t round, flag_cur, flag_prev;
+  uint32_t sub;
+  __device__ __forceinline__ const PScan& item(int i) const { return scans[i]; }
+};
+
+// Decodes the symbols of a FIRST scan whose first bit lies in raw bytes [.., end_byte), starting from `s`
+// (s.b = block in the MCU for DC scans, s.z = zig-zag index for AC scans).  Returns the state after the last of them
+// and the number of blocks COMPLETED.  WRITE: blk is the scan-order index of the block in progress.
+template <bool WRITE>
+__device__ __forceinline__ State pdecode_range(const PScan& S, const SmemTables& T, State s, uint32_t end_byte,
+                                               uint32_t* completed, int64_t blk) {
+  Reader r;
+  r.p = S.data;
+  r.n = S.len;
+  rd_start(r, s.byte, s.bit);
+  uint32_t count = 0;
+  bool first = true;
+  int b = s.b, z = s.z;
+  State out = s;
+  if (s.done) { *completed = 0; return s; }
+  const bool dc = S.mode == PSCAN_DC_FIRST;
+  const int ny = S.ns > 1 ? S.hs * S.vs : 1;
+  const int z0 = dc ? 0 : S.ss;
+  const int tac = 2 + S.ta;
+  for (;;) {
+    rd_fill(r);
+    if (first) { rd_skip(r, s.bit); first = false; }
+    {
+      const int real = r.cnt - r.fake;
+      const uint32_t nb = (uint32_t)((real + 7) >> 3);
+      if (r.pos - nb >= end_byte) {
+        uint32_t c;
+        int cbit;
+        rd_where(r, &c, &cbit);
+        if (c >= end_byte) {
+          out.byte = c; out.bit = cbit; out.b = b; out.z = z; out.done = false;
+          break;
+        }
+      }
+    }
+    int nblk = 0, zpos = -1, value = 0, nb2 = b, nz = z;
+    if (dc) {
+      const int ci = S.ns == 1 ? 0 : (b < ny ? 0 : b - ny + 1);
+      const int sz = huff_decode(T, S.td[ci], r) & 15;
+      if (sz) {
+        const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
+        rd_skip(r, sz);
+        value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
+      }
+      nblk = 1;
+      nb2 = (b + 1 == S.bpm) ? 0 : b + 1;
+    } else {
+      const int rs = huff_decode(T, tac, r);
+      const int run = rs >> 4, sz = rs & 15;
+      if (sz) {
+        const uint32_t bits = (uint32_t)(r.acc >> (64 - sz));
+        rd_skip(r, sz);
+        value = (bits < (1u << (sz - 1))) ? (int)bits - (1 << sz) + 1 : (int)bits;
+        zpos = z + run;
+        nz = zpos + 1;
+      } else if (run == 15) {
+        nz = z + 16;
+      } else {                                   // EOBn: this block and (1 << run) + bits - 1 more end here
+        nblk = 1 << run;
+        if (run) {
+          nblk += (int)(uint32_t)(r.acc >> (64 - run));
+          rd_skip(r, run);
+        }
+        nz = S.ss;
+      }
+      if (nz > S.se && nblk == 0) { nblk = 1; nz = S.ss; }
+    }
+    if (r.cnt < r.fake) {
+      // the symbol ran into a marker (it was padding) or past the end: drop it
+      uint32_t mpos = r.pos;
+      while (mpos + 2 < r.n && r.p[mpos + 1] == 0xFFu) ++mpos;
+      const uint32_t m = (mpos + 1 < r.n) ? r.p[mpos + 1] : 0xD9u;
+      if (mpos + 1 < r.n && m >= 0xD0u && m <= 0xD7u) {
+        b = 0;
+        z = z0;
+        rd_start(r, mpos + 2, 0);
+        if (mpos + 2 >= end_byte) {
+          out.byte = mpos + 2; out.bit = 0; out.b = 0; out.z = z0; out.done = false;
+          break;
+        }
+        continue;
+      }
+      out.byte = r.n; out.bit = 0; out.b = 0; out.z = z0; out.done = true;
+      break;
+    }
+    if (WRITE && blk >= 0 && blk < S.n_blk) {
+      if (dc) S.dcdiff[blk] = value;
+      else if (zpos >= 0 && zpos < 64) S.coef[pscan_block(S, (int)blk) * 64 + zpos] = (int16_t)(value * (1 << S.al));
+    }
+    blk += nblk;
+    count += (uint32_t)nblk;
+    b = nb2;
+    z = nz;
+  }
+  *completed = count;
+  return out;
+}
+
+__device__ __forceinline__ State decode_nowrite(const PScan& S, const SmemTables& T, State s, uint32_t end_byte, uint32_t* completed) {
+  return pdecode_range<false>(S, T, s, end_byte, completed, 0);
+}
+__device__ __forceinline__ uint32_t scan_start_word(const PScan& S) {
+  return S.mode == PSCAN_AC_FIRST ? (uint32_t)S.ss << 16 : 0u;
+}
+
+__device__ __forceinline__ State pguess_state(const PScan& S, uint32_t i, uint32_t sub) {
+  State s;
+  s.byte = i * sub;
+  s.bit = 0;
+  s.b = 0;
+  s.z = S.mode == PSCAN_AC_FIRST ? S.ss : 0;
+  s.done = false;
+  if (i > 0 && s.byte < S.len && S.data[s.byte - 1] == 0xFFu) {
+    const uint32_t v = S.data[s.byte];
+    if (v == 0 || (v >= 0xD0u && v <= 0xD7u)) s.byte += 1;
+  }
+  return s;
+}
+
+// PD1: first pass from guessed states (the synchronisation rounds and the prefix sums are jdec_sync_kernel<PBatch> and
+// jdec_scan_kernel<PBatch>).
+__global__ void __launch_bounds__(JDEC_THREADS) jprog_first_kernel(const __grid_constant__ PBatch B) {
+  __shared__ SmemTables T;
+  const PScan& S = B.item(blockIdx.y);
+  if (blockIdx.x * JDEC_THREADS >= (unsigned)S.n_sub) return;
+  build_tables(S.tab, T);
+  const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
+  if (i >= (uint32_t)S.n_sub) return;
+  uint32_t completed = 0;
+  const State e = pdecode_range<false>(S, T, pguess_state(S, i, B.sub), (i + 1) * B.sub, &completed, 0);
+  S.state[i] = make_uint4(e.byte, pack_state(e), completed, 0u);
+}
+
+// PD4: write pass from the synchronised states.
+__global__ void __launch_bounds__(JDEC_THREADS) jprog_write_kernel(const __grid_constant__ PBatch B) {
+  __shared__ SmemTables T;
+  const PScan& S = B.item(blockIdx.y);
+  if (blockIdx.x * JDEC_THREADS >= (unsigned)S.n_sub) return;
+  build_tables(S.tab, T);
+  const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
+  if (i >= (uint32_t)S.n_sub) return;
+  State s;
+  if (i == 0) { s = unpack_state(0u, scan_start_word(S)); }
+  else { const uint4 p = S.state[i - 1]; s = unpack_state(p.x, p.y); }
+  uint32_t completed = 0;
+  pdecode_range<true>(S, T, s, (i + 1) * B.sub, &completed, (int64_t)S.prefix[i]);
+}
+
+// PD5: DC differences (scan order) -> values << Al in the coefficient buffer.  One CTA per (scan, component in the
+// scan): segmented inclusive scan over the component's blocks in scan order, a restart interval boundary zeroes the
+// predictor.  grid = (first scans, 3); scans that are not DC scans return.
+__global__ void __launch_bounds__(1024) jprog_dc_kernel(const PScan* __restrict__ scans) {
+  __shared__ int wsum[32];
+  __shared__ int wflag[32];
+  __shared__ int carry;
+  const PScan& S = scans[blockIdx.x];
+  if (S.mode != PSCAN_DC_FIRST || (int)blockIdx.y >= S.ns) return;
+  const int ci = blockIdx.y;
+  const int ny = S.ns > 1 ? S.hs * S.vs : 1;
+  const int nb = ci == 0 ? ny : 1, off = ci == 0 ? 0 : ny + ci - 1;
+  const int n_el = (S.n_blk / S.bpm) * nb;
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  if (t == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n_el; base += 1024) {
+    const int j = base + t;
+    const bool live = j < n_el;
+    const int mcu = j / nb, within = j - mcu * nb;
+    const int blk = mcu * S.bpm + off + within;
+    const int own = live ? S.dcdiff[blk] : 0;
+    int x = own, f = (live && S.ri > 0 && within == 0 && (mcu % S.ri) == 0) ? 1 : 0;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int f2 = __shfl_up_sync(0xffffffffu, f, d);
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) {
+        if (!f) x += y;
+        f |= f2;
+      }
+    }
+    if (lane == 31) { wsum[w] = x; wflag[w] = f; }
+    __syncthreads();
+    if (w == 0) {
+      int xs = wsum[lane], fs = wflag[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int f2 = __shfl_up_sync(0xffffffffu, fs, d);
+        const int y = __shfl_up_sync(0xffffffffu, xs, d);
+        if (lane >= d) {
+          if (!fs) xs += y;
+          fs |= f2;
+        }
+      }
+      wsum[lane] = xs;
+      wflag[lane] = fs;
+    }
+    __syncthreads();
+    int r = x;
+    if (!f) {
+      if (w > 0) r += wsum[w - 1];
+      if (!(w > 0 && wflag[w - 1])) r += carry;
+    }
+    if (live) S.coef[pscan_block(S, blk) * 64] = (int16_t)(r * (1 << S.al));
+    __syncthreads();
+    if (t == 1023) carry = r;
+    __syncthreads();
+  }
+}
+
+// Scans of one dependency level, one CTA each: the warp builds the tables, its first thread decodes the scan.
+__global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__ scans) {
+  __shared__ SmemTables T;
+  const PScan S = scans[blockIdx.x];      // a private copy: the decoder's stores cannot alias it
+  build_tables(S.tab, T);
+  if (threadIdx.x == 0) pscan_sequential(S, T);
+}
+
+}  // namespace jpegdec
+}  // namespace stitch

@@ -26,6 +26,7 @@
 #include "host_stage.h"
 #include "jpeg_kernels.cuh"
 #include "jpeg_decode.cuh"
+#include "jpeg_prog.cuh"
 #include "png_decode.h"
 #include "png_kernels.cuh"
 #include "synth.cuh"
@@ -51,7 +52,7 @@ struct PendingJob {
 };
 
 // words of a lane's pinned info block
-enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_PNGDEC_STATUS = 5, INFO_WORDS = 8 };
+enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_PNGDEC_STATUS = 5, INFO_PDEC_CHANGED = 6, INFO_WORDS = 8 };
 
 // One job lane: a stream with its own unit-scheduler counters and its own staging, so that jobs
 // submitted to different lanes overlap -- the next job's blocks fill the SM slots the draining one
@@ -87,6 +88,8 @@ struct Lane {
   // JPEG decode: grow-only arena (scan bytes, tables, subsequence states, coefficients, component planes)
   void* dec_arena = nullptr;
   size_t dec_arena_cap = 0;
+  void* prog_arena = nullptr;        // progressive files of the job (jpeg_prog.cuh): their own arena, same rules
+  size_t prog_arena_cap = 0;
   stitch::pngdec::Arena pngdec_arena;   // PNG-input decoder (png_decode.cu)
   bool pngdec_active = false;        // the job on this lane decodes PNG files: check INFO_PNGDEC_STATUS when it is done
   // PNG export: grow-only arena (RGBA canvas when the caller did not ask for it, code tables, coded bands, file)
@@ -200,6 +203,7 @@ void free_lane(Lane& ln) {
   if (ln.out_stage) cudaFree(ln.out_stage);
   if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
   if (ln.dec_arena) cudaFree(ln.dec_arena);
+  if (ln.prog_arena) cudaFree(ln.prog_arena);
   stitch::pngdec::free_arena(ln.pngdec_arena);
   if (ln.png_arena) cudaFree(ln.png_arena);
   if (ln.info_host) cudaFreeHost(ln.info_host);
@@ -238,7 +242,7 @@ struct DecodeItem {
 // copies the last round's flag into the lane's info block; the caller checks it when the job is finalised and
 // decodes again synchronously if the chains had not converged (no such file seen yet: photos take 2 rounds).
 constexpr int kDecRounds = 6;
-int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferred) {
+int decode_baseline_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferred) {
   namespace jd = stitch::jpegdec;
   if (n <= 0) return STITCH_OK;
   if (n > JDEC_MAX_IMAGES) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
@@ -328,7 +332,7 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferr
       B.round = rounds;
       B.flag_cur = rounds;
       B.flag_prev = rounds - 1;
-      jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+      jd::jdec_sync_kernel<jd::DecBatch><<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
       ++launches;
     }
     ln.info_host[INFO_DEC_CHANGED] = 0;
@@ -340,7 +344,7 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferr
       B.round = rounds;
       B.flag_cur = 0;
       B.flag_prev = -1;
-      jd::jdec_sync_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
+      jd::jdec_sync_kernel<jd::DecBatch><<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
       ++launches;
       ln.info_host[INFO_DEC_CHANGED] = 0;
       CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_DEC_CHANGED], B.changed, 4, cudaMemcpyDeviceToHost, ln.stream));
@@ -348,7 +352,7 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferr
       if (*(volatile uint32_t*)&ln.info_host[INFO_DEC_CHANGED] == 0) break;
     }
   }
-  jd::jdec_scan_kernel<<<n, 1024, 0, ln.stream>>>(B);
+  jd::jdec_scan_kernel<jd::DecBatch><<<n, 1024, 0, ln.stream>>>(B);
   jd::jdec_write_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(B);
   jd::jdec_dc_sum_kernel<<<dim3((max_mcu + 255) / 256, n), 256, 0, ln.stream>>>(B);
   jd::jdec_dc_scan_kernel<<<dim3(n, 3), 1024, 0, ln.stream>>>(B);
@@ -361,12 +365,218 @@ int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferr
   return STITCH_OK;
 }
 
+// GPU decode of the PROGRESSIVE files of a job (jpeg_prog.cuh) on the lane's stream.  First scans (Ah = 0) of all
+// files go through the self-synchronising decoder as one batch; the other scans follow in dependency levels, one
+// thread per scan; then the shared dequantise / IDCT / colour kernels.  `deferred` as in decode_baseline_batch (the
+// flag lands in INFO_PDEC_CHANGED).  STITCH_JPROG_SEQ=1 sends every scan down the one-thread path (tests).
+int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferred) {
+  namespace jd = stitch::jpegdec;
+  if (n <= 0) return STITCH_OK;
+  if (n > JDEC_MAX_IMAGES) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
+  const char* seq_env = std::getenv("STITCH_JPROG_SEQ");
+  const bool all_seq = seq_env && seq_env[0] == '1';
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  struct ScanRef { int img, scan, level; bool par; size_t data, state, prefix, consumed, dcdiff; jd::PScan ps; };
+  struct ImgCarve { size_t tabs, qtab, coef, plane[3]; };
+  std::vector<ScanRef> refs;
+  ImgCarve cv[JDEC_MAX_IMAGES];
+  jd::DecBatch B;   // back end (IDCT + colour) only
+  std::memset(&B, 0, sizeof B);
+  B.n = n;
+  size_t need = 256;   // `changed` flags
+  size_t par_bytes = 0;
+  int max_blocks = 0, max_w = 0, max_h = 0, max_level = 0;
+  for (int i = 0; i < n; ++i) {
+    const jd::Header& H = items[i].hdr;
+    jd::DecImage& I = B.img[i];
+    I.w = H.w; I.h = H.h; I.ncomp = H.ncomp; I.hs = H.hs; I.vs = H.vs; I.mcux = H.mcux; I.mcuy = H.mcuy; I.ri = 0;
+    I.bpm = H.ncomp == 1 ? 1 : H.hs * H.vs + 2;
+    I.n_blocks = H.mcux * H.mcuy * I.bpm;
+    for (int c = 0; c < 3; ++c) I.tq[c] = H.tq[c];
+    I.pw[0] = H.mcux * H.hs * 8; I.ph[0] = H.mcuy * H.vs * 8;
+    I.pw[1] = I.pw[2] = H.ncomp == 3 ? H.mcux * 8 : 0;
+    I.ph[1] = I.ph[2] = H.ncomp == 3 ? H.mcuy * 8 : 0;
+    I.rgba = items[i].rgba;
+    I.pitch = items[i].pitch;
+    ImgCarve& c = cv[i];
+    c.tabs = need; need += up(H.scan_tabs.size() * sizeof(jd::Tables));
+    c.qtab = need; need += up(sizeof(jd::Tables));
+    c.coef = need; need += up((size_t)I.n_blocks * 128);
+    for (int k = 0; k < 3; ++k) { c.plane[k] = need; need += up((size_t)I.pw[k] * I.ph[k] + 16); }
+    max_blocks = std::max(max_blocks, I.n_blocks);
+    max_w = std::max(max_w, H.w);
+    max_h = std::max(max_h, H.h);
+    // dependency levels: a scan waits for every earlier scan that shares a component and overlaps its band
+    const size_t first_ref = refs.size();
+    for (size_t k = 0; k < H.scans.size(); ++k) {
+      const jd::ProgScan& ps = H.scans[k];
+      ScanRef r;
+      std::memset(&r.ps, 0, sizeof r.ps);
+      r.img = i;
+      r.scan = (int)k;
+      r.level = 0;
+      for (size_t j = 0; j < k; ++j) {
+        const jd::ProgScan& q = H.scans[j];
+        const bool shares = ps.ns > 1 || q.ns > 1 || ps.comp == q.comp;
+        if (shares && ps.ss <= q.se && q.ss <= ps.se) r.level = std::max(r.level, refs[first_ref + j].level + 1);
+      }
+      r.par = !all_seq && ps.ah == 0 && r.level == 0;
+      jd::pscan_describe(H, ps, &r.ps);
+      r.data = need; need += up(ps.len + 16);
+      r.state = r.prefix = r.consumed = r.dcdiff = 0;
+      if (r.par) par_bytes += ps.len;
+      refs.push_back(r);
+    }
+  }
+  const uint32_t sub = jd::jdec_pick_sub(par_bytes);
+  int n_par = 0, max_sub = 0;
+  for (ScanRef& r : refs) {
+    if (!r.par) { max_level = std::max(max_level, r.level); continue; }
+    ++n_par;
+    r.ps.n_sub = std::max(1, (int)((r.ps.len + sub - 1) / sub));
+    max_sub = std::max(max_sub, r.ps.n_sub);
+    r.state = need; need += up((size_t)r.ps.n_sub * 16);
+    r.prefix = need; need += up((size_t)r.ps.n_sub * 4);
+    r.consumed = need; need += up((size_t)((r.ps.n_sub + JDEC_THREADS - 1) / JDEC_THREADS) * 8);
+    if (r.ps.mode == jd::PSCAN_DC_FIRST) { r.dcdiff = need; need += up((size_t)r.ps.n_blk * 4); }
+  }
+  // device copies of the scan records: the first scans in front, the others sorted by level behind them
+  std::vector<int> order;
+  for (size_t k = 0; k < refs.size(); ++k) if (refs[k].par) order.push_back((int)k);
+  std::vector<int> level_off(max_level + 2, 0);
+  for (int lv = 0; lv <= max_level; ++lv) {
+    level_off[lv] = (int)order.size();
+    for (size_t k = 0; k < refs.size(); ++k) if (!refs[k].par && refs[k].level == lv) order.push_back((int)k);
+  }
+  level_off[max_level + 1] = (int)order.size();
+  const size_t recs = need;
+  need += up(order.size() * sizeof(jd::PScan));
+  if (ln.prog_arena_cap < need) {
+    if (ln.prog_arena) {
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+      CUDA_TRY(ctx, cudaFree(ln.prog_arena));
+    }
+    ln.prog_arena = nullptr;
+    ln.prog_arena_cap = 0;
+    if (cudaMalloc(&ln.prog_arena, need) != cudaSuccess)
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (JPEG decode buffers allocation failed)");
+    ln.prog_arena_cap = need;
+  }
+  {
+    const int st = ensure_info(ctx, ln);
+    if (st != STITCH_OK) return st;
+  }
+  uint8_t* A = (uint8_t*)ln.prog_arena;
+  for (int i = 0; i < n; ++i) {
+    const jd::Header& H = items[i].hdr;
+    jd::DecImage& I = B.img[i];
+    const ImgCarve& c = cv[i];
+    I.tab = (const jd::Tables*)(A + c.qtab);
+    I.coef = (int16_t*)(A + c.coef);
+    for (int k = 0; k < 3; ++k) I.plane[k] = A + c.plane[k];
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + c.tabs, H.scan_tabs.data(), H.scan_tabs.size() * sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + c.qtab, &H.tab, sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(A + c.coef, 0, (size_t)I.n_blocks * 128, ln.stream));
+  }
+  std::vector<jd::PScan> host_recs(order.size());
+  for (size_t k = 0; k < order.size(); ++k) {
+    ScanRef& r = refs[order[k]];
+    const jd::Header& H = items[r.img].hdr;
+    const jd::ProgScan& ps = H.scans[r.scan];
+    r.ps.data = A + r.data;
+    r.ps.tab = (const jd::Tables*)(A + cv[r.img].tabs) + ps.tab;
+    r.ps.coef = (int16_t*)(A + cv[r.img].coef);
+    if (r.par) {
+      r.ps.state = (uint4*)(A + r.state);
+      r.ps.prefix = (uint32_t*)(A + r.prefix);
+      r.ps.consumed = (uint2*)(A + r.consumed);
+      r.ps.dcdiff = r.dcdiff ? (int32_t*)(A + r.dcdiff) : nullptr;
+    }
+    if (ps.len) CUDA_TRY(ctx, cudaMemcpyAsync(A + r.data, items[r.img].file + ps.off, ps.len, cudaMemcpyHostToDevice, ln.stream));
+    host_recs[k] = r.ps;
+  }
+  jd::PScan* d_recs = (jd::PScan*)(A + recs);
+  if (!host_recs.empty())
+    CUDA_TRY(ctx, cudaMemcpyAsync(d_recs, host_recs.data(), host_recs.size() * sizeof(jd::PScan), cudaMemcpyHostToDevice, ln.stream));
+  int launches = 0;
+  ln.info_host[INFO_PDEC_CHANGED] = 0;
+  if (n_par > 0) {
+    jd::PBatch P;
+    std::memset(&P, 0, sizeof P);
+    P.scans = d_recs;
+    P.changed = (uint32_t*)A;
+    P.sub = sub;
+    const dim3 gsub((max_sub + JDEC_THREADS - 1) / JDEC_THREADS, n_par);
+    jd::jprog_first_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(P);
+    ++launches;
+    int rounds = 0;
+    if (deferred) {
+      CUDA_TRY(ctx, cudaMemsetAsync(P.changed, 0, 4 * kDecRounds, ln.stream));
+      for (; rounds < kDecRounds; ++rounds) {
+        P.round = rounds;
+        P.flag_cur = rounds;
+        P.flag_prev = rounds - 1;
+        jd::jdec_sync_kernel<jd::PBatch><<<gsub, JDEC_THREADS, 0, ln.stream>>>(P);
+        ++launches;
+      }
+      CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_PDEC_CHANGED], P.changed + (kDecRounds - 1), 4, cudaMemcpyDeviceToHost, ln.stream));
+    } else {
+      for (;; ++rounds) {
+        if (rounds > 4096) return fail(ctx, STITCH_E_BAD_IMAGE, "JPEG entropy decoder did not synchronise");
+        CUDA_TRY(ctx, cudaMemsetAsync(P.changed, 0, 4, ln.stream));
+        P.round = rounds;
+        P.flag_cur = 0;
+        P.flag_prev = -1;
+        jd::jdec_sync_kernel<jd::PBatch><<<gsub, JDEC_THREADS, 0, ln.stream>>>(P);
+        ++launches;
+        ln.info_host[INFO_PDEC_CHANGED] = 0;
+        CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_PDEC_CHANGED], P.changed, 4, cudaMemcpyDeviceToHost, ln.stream));
+        CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+        if (*(volatile uint32_t*)&ln.info_host[INFO_PDEC_CHANGED] == 0) break;
+      }
+    }
+    jd::jdec_scan_kernel<jd::PBatch><<<n_par, 1024, 0, ln.stream>>>(P);
+    jd::jprog_write_kernel<<<gsub, JDEC_THREADS, 0, ln.stream>>>(P);
+    jd::jprog_dc_kernel<<<dim3(n_par, 3), 1024, 0, ln.stream>>>(d_recs);
+    launches += 3;
+  }
+  for (int lv = 0; lv <= max_level; ++lv) {
+    const int cnt = level_off[lv + 1] - level_off[lv];
+    if (cnt <= 0) continue;
+    jd::jprog_seq_kernel<<<cnt, 32, 0, ln.stream>>>(d_recs + level_off[lv]);
+    ++launches;
+  }
+  jd::jdec_idct_kernel<<<dim3((max_blocks + 127) / 128, n), 128, 0, ln.stream>>>(B);
+  jd::jdec_colour_kernel<<<dim3((max_w + 127) / 128, (max_h + 7) / 8, n), 256, 0, ln.stream>>>(B);
+  launches += 2;
+  CUDA_TRY(ctx, cudaGetLastError());
+  ctx->launches += launches;
+  return STITCH_OK;
+}
+
+// The JPEG files of a job: baseline ones and progressive ones are two batches on the same stream.
+int decode_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool deferred) {
+  if (n <= 0) return STITCH_OK;
+  if (n > JDEC_MAX_IMAGES) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
+  {
+    const int st = ensure_info(ctx, ln);
+    if (st != STITCH_OK) return st;
+  }
+  ln.info_host[INFO_DEC_CHANGED] = 0;
+  ln.info_host[INFO_PDEC_CHANGED] = 0;
+  std::vector<DecodeItem> base, prog;
+  for (int i = 0; i < n; ++i) (items[i].hdr.progressive ? prog : base).push_back(items[i]);
+  int st = decode_baseline_batch(ctx, ln, base.data(), (int)base.size(), deferred);
+  if (st == STITCH_OK) st = decode_prog_batch(ctx, ln, prog.data(), (int)prog.size(), deferred);
+  return st;
+}
+
 int parse_jpeg(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::jpegdec::Header* H) {
   const stitch::jpegdec::ParseStatus ps = stitch::jpegdec::parse((const uint8_t*)file, bytes, H);
   if (ps == stitch::jpegdec::kOk) return STITCH_OK;
   char buf[96];
   std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
-                ps == stitch::jpegdec::kUnsupported ? "JPEG variant not supported: baseline Huffman, 4:4:4 / 4:2:2 / 4:2:0 / gray only"
+                ps == stitch::jpegdec::kUnsupported ? "JPEG variant not supported: Huffman-coded baseline or progressive, 4:4:4 / 4:2:2 / 4:2:0 / gray only"
                 : ps == stitch::jpegdec::kNotJpeg ? "not a JPEG file" : "corrupt JPEG headers");
   return fail(ctx, STITCH_E_BAD_IMAGE, buf);
 }
@@ -1210,7 +1420,7 @@ void finalize_job(StitchCtx* ctx, PendingJob& pj) {
   if (e != cudaSuccess) {
     pj.status = fail(ctx, STITCH_E_CUDA, std::string("event sync: ") + cudaGetErrorString(e));
   } else if (pj.deferred) {
-    if (pj.dec && (uint32_t)ln.info_host[INFO_DEC_CHANGED] != 0u) {
+    if (pj.dec && ((uint32_t)ln.info_host[INFO_DEC_CHANGED] | (uint32_t)ln.info_host[INFO_PDEC_CHANGED]) != 0u) {
       // the entropy decoder's chains had not converged after kDecRounds rounds: decode with as many as it takes
       pj.job.images = pj.images.data();
       StitchProgressFn keep = ctx->progress;

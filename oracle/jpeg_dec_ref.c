@@ -8,8 +8,11 @@
  * fixed-point YCbCr->RGB conversion of JFIF.  PINNED: tests/test_jpeg_decode.py holds it byte-identical to
  * libjpeg(-turbo) as shipped in PIL for 4:4:4, 4:2:2, 4:2:0 and grayscale files.
  *
- * Supported: baseline / extended sequential Huffman (SOF0, SOF1), 8-bit, 1 or 3 components, one interleaved
- * scan, luma sampling 1x1, 2x1 or 2x2 with 1x1 chroma, restart intervals.  Anything else returns < 0.
+ * Supported: baseline / extended sequential Huffman (SOF0, SOF1) with one interleaved scan, and progressive Huffman
+ * (SOF2, T.81 Annex G: spectral selection + successive approximation, interleaved DC scans, single-component scans,
+ * EOB runs, tables redefined between scans); 8-bit, 1 or 3 components, luma sampling 1x1, 2x1 or 2x2 with 1x1
+ * chroma, restart intervals.  A complete progressive file is decoded without libjpeg's inter-block smoothing (that only
+ * acts on files whose AC scans are missing).  Anything else returns < 0.
  */
 #include <stdint.h>
 #include <stdlib.h>
@@ -28,6 +31,10 @@ typedef struct {
   int32_t mincode[4][17], maxcode[4][18], valptr[4][17];
   const uint8_t* scan;
   size_t scan_len;
+  int progressive;              /* SOF2 */
+  int comp_id[3];
+  const uint8_t* file;          /* progressive: the marker walk restarts at first_sos for every decode */
+  size_t file_len, first_sos;
 } JDec;
 
 static void build_huff(JDec* d, int t) {
@@ -65,13 +72,15 @@ static int parse(JDec* d, const uint8_t* p, size_t n) {
         for (int k = 0; k < 64; ++k) d->q[tq][JZIGZAG[k]] = s[i + 1 + k];
         i += 65;
       }
-    } else if (m == 0xC0 || m == 0xC1) {  /* SOF0 / SOF1 */
+    } else if (m == 0xC0 || m == 0xC1 || m == 0xC2) {  /* SOF0 / SOF1 / SOF2 */
       if (sl < 6 || s[0] != 8) return -5;
+      d->progressive = (m == 0xC2);
       d->h = (s[1] << 8) | s[2];
       d->w = (s[3] << 8) | s[4];
       d->ncomp = s[5];
       if ((d->ncomp != 1 && d->ncomp != 3) || sl < (size_t)(6 + 3 * d->ncomp) || d->w == 0 || d->h == 0) return -6;
       for (int c = 0; c < d->ncomp; ++c) {
+        d->comp_id[c] = s[6 + 3 * c];
         d->hs[c] = s[7 + 3 * c] >> 4;
         d->vs[c] = s[7 + 3 * c] & 15;
         d->tq[c] = s[8 + 3 * c];
@@ -88,8 +97,8 @@ static int parse(JDec* d, const uint8_t* p, size_t n) {
       d->mcux = (d->w + 8 * d->hmax - 1) / (8 * d->hmax);
       d->mcuy = (d->h + 8 * d->vmax - 1) / (8 * d->vmax);
       have_sof = 1;
-    } else if (m >= 0xC2 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
-      return -8;  /* progressive, lossless, arithmetic: not baseline */
+    } else if (m >= 0xC3 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
+      return -8;  /* lossless, hierarchical, arithmetic */
     } else if (m == 0xC4) {  /* DHT */
       size_t i = 0;
       while (i < sl) {
@@ -107,6 +116,11 @@ static int parse(JDec* d, const uint8_t* p, size_t n) {
     } else if (m == 0xDD) {
       if (sl < 2) return -10;
       d->ri = (s[0] << 8) | s[1];
+    } else if (m == 0xDA && have_sof && d->progressive) {  /* first SOS of a progressive file: scans are walked later */
+      d->file = p;
+      d->file_len = n;
+      d->first_sos = o;
+      return 0;
     } else if (m == 0xDA) {  /* SOS */
       if (!have_sof || sl < 1 || s[0] != d->ncomp || sl < (size_t)(1 + 2 * d->ncomp + 3)) return -11;
       for (int c = 0; c < d->ncomp; ++c) {
@@ -229,6 +243,212 @@ static int decode_scan(const JDec* d, int16_t* coef[3]) {
   return 0;
 }
 
+
+/* ---- progressive scans (T.81 Annex G; the same steps as libjpeg's jdphuff.c) ---- */
+static inline int getbit(Bits* b) { return getbits(b, 1); }
+
+/* End of the entropy-coded data that starts at o: the first marker that is neither a stuffed zero nor RSTn. */
+static size_t scan_end(const uint8_t* p, size_t n, size_t o) {
+  while (o + 1 < n) {
+    if (p[o] == 0xFF && p[o + 1] != 0 && p[o + 1] != 0xFF && !(p[o + 1] >= 0xD0 && p[o + 1] <= 0xD7)) return o;
+    ++o;
+  }
+  return n;
+}
+
+static void restart(Bits* b, int* rst_next) {
+  b->acc = 0;
+  b->cnt = 0;
+  if (!b->marker) {
+    while (b->o + 1 < b->n && !(b->p[b->o] == 0xFF && b->p[b->o + 1] >= 0xD0 && b->p[b->o + 1] <= 0xD7)) b->o++;
+    if (b->o + 1 < b->n) { b->marker = b->p[b->o + 1]; b->o += 2; }
+  }
+  if (b->marker == 0xD0 + *rst_next) b->marker = 0;
+  *rst_next = (*rst_next + 1) & 7;
+}
+
+static int16_t* block_at(const JDec* d, int16_t* coef[3], int c, int bx, int by) {
+  return coef[c] + ((size_t)by * (d->mcux * d->hs[c]) + bx) * 64;
+}
+
+/* One scan: ns components cs[] (frame indices), band ss..se, successive approximation ah/al. */
+static int decode_prog_scan(JDec* d, int16_t* coef[3], const uint8_t* data, size_t len, int ns, const int* cs, const int* td,
+                            const int* ta, int ss, int se, int ah, int al) {
+  Bits b;
+  memset(&b, 0, sizeof b);
+  b.p = data;
+  b.n = len;
+  int pred[3] = {0, 0, 0};
+  int rst_left = d->ri, rst_next = 0;
+  unsigned eobrun = 0;
+  if (ss == 0) {                       /* DC scan: may interleave components */
+    if (se != 0) return -31;
+    int nmx, nmy;
+    if (ns == 1) {
+      const int c = cs[0];
+      nmx = ((d->w * d->hs[c] + d->hmax - 1) / d->hmax + 7) / 8;
+      nmy = ((d->h * d->vs[c] + d->vmax - 1) / d->vmax + 7) / 8;
+    } else {
+      nmx = d->mcux;
+      nmy = d->mcuy;
+    }
+    for (int m = 0; m < nmx * nmy; ++m) {
+      if (d->ri && rst_left == 0) { restart(&b, &rst_next); pred[0] = pred[1] = pred[2] = 0; rst_left = d->ri; }
+      const int mx = m % nmx, my = m / nmx;
+      for (int j = 0; j < ns; ++j) {
+        const int c = cs[j];
+        const int nh = ns == 1 ? 1 : d->hs[c], nv = ns == 1 ? 1 : d->vs[c];
+        for (int v = 0; v < nv; ++v)
+          for (int h = 0; h < nh; ++h) {
+            int16_t* blk = block_at(d, coef, c, mx * nh + h, my * nv + v);
+            if (ah == 0) {
+              const int s = decode_sym(d, td[j], &b);
+              const int diff = s ? extend(getbits(&b, s & 15), s & 15) : 0;
+              pred[c] += diff;
+              blk[0] = (int16_t)(pred[c] * (1 << al));
+            } else if (getbit(&b)) {
+              blk[0] |= (int16_t)(1 << al);
+            }
+          }
+      }
+      if (d->ri) rst_left--;
+    }
+    return 0;
+  }
+  /* AC scan: one component, blocks of the component's own (unpadded) size in raster order */
+  if (ns != 1 || se > 63 || ss > se) return -32;
+  const int c = cs[0];
+  const int nbx = ((d->w * d->hs[c] + d->hmax - 1) / d->hmax + 7) / 8;
+  const int nby = ((d->h * d->vs[c] + d->vmax - 1) / d->vmax + 7) / 8;
+  const int p1 = 1 << al, m1 = -(1 << al);
+  const int t = 2 + ta[0];
+  for (int m = 0; m < nbx * nby; ++m) {
+    if (d->ri && rst_left == 0) { restart(&b, &rst_next); eobrun = 0; rst_left = d->ri; }
+    int16_t* blk = block_at(d, coef, c, m % nbx, m / nbx);
+    if (ah == 0) {
+      if (eobrun > 0) {
+        eobrun--;
+      } else {
+        for (int k = ss; k <= se; ++k) {
+          const int rs = decode_sym(d, t, &b);
+          const int r = rs >> 4, s = rs & 15;
+          if (s) {
+            k += r;
+            const int v = extend(getbits(&b, s), s);
+            if (k <= 63) blk[JZIGZAG[k]] = (int16_t)(v * (1 << al));
+          } else if (r == 15) {
+            k += 15;
+          } else {
+            eobrun = 1u << r;
+            if (r) eobrun += (unsigned)getbits(&b, r);
+            eobrun--;
+            break;
+          }
+        }
+      }
+    } else {
+      int k = ss;
+      if (eobrun == 0) {
+        for (; k <= se; ++k) {
+          const int rs = decode_sym(d, t, &b);
+          int r = rs >> 4, s = rs & 15;
+          if (s) {
+            s = getbit(&b) ? p1 : m1;       /* size must be 1: a newly non-zero coefficient */
+          } else if (r != 15) {
+            eobrun = 1u << r;
+            if (r) eobrun += (unsigned)getbits(&b, r);
+            break;
+          }
+          do {
+            int16_t* cf = blk + JZIGZAG[k];
+            if (*cf != 0) {
+              if (getbit(&b) && (*cf & p1) == 0) *cf = (int16_t)(*cf + (*cf >= 0 ? p1 : m1));
+            } else if (--r < 0) {
+              break;
+            }
+            ++k;
+          } while (k <= se);
+          if (s && k <= 63) blk[JZIGZAG[k]] = (int16_t)s;
+        }
+      }
+      if (eobrun > 0) {
+        for (; k <= se; ++k) {
+          int16_t* cf = blk + JZIGZAG[k];
+          if (*cf != 0 && getbit(&b) && (*cf & p1) == 0) *cf = (int16_t)(*cf + (*cf >= 0 ? p1 : m1));
+        }
+        eobrun--;
+      }
+    }
+    if (d->ri) rst_left--;
+  }
+  return 0;
+}
+
+/* Walks the marker segments from the first SOS to EOI: DHT / DRI between scans take effect for the scans after them. */
+static int decode_progressive(JDec* d, int16_t* coef[3]) {
+  const uint8_t* p = d->file;
+  const size_t n = d->file_len;
+  size_t o = d->first_sos;
+  int scans = 0;
+  while (o + 4 <= n) {
+    if (p[o] != 0xFF) return -33;
+    const int m = p[o + 1];
+    if (m == 0xFF) { ++o; continue; }
+    if (m == 0xD9) break;
+    if (m == 0x01 || (m >= 0xD0 && m <= 0xD7)) { o += 2; continue; }
+    const size_t len = ((size_t)p[o + 2] << 8) | p[o + 3];
+    if (len < 2 || o + 2 + len > n) return -34;
+    const uint8_t* s = p + o + 4;
+    const size_t sl = len - 2;
+    if (m == 0xC4) {
+      size_t i = 0;
+      while (i < sl) {
+        const int tc = s[i] >> 4, th = s[i] & 15;
+        if (tc > 1 || th > 1 || i + 17 > sl) return -9;
+        const int t = tc * 2 + th;
+        int cnt = 0;
+        for (int l = 1; l <= 16; ++l) { d->bits[t][l] = s[i + l]; cnt += s[i + l]; }
+        if (cnt > 256 || i + 17 + cnt > sl) return -9;
+        memset(d->vals[t], 0, 256);
+        memcpy(d->vals[t], s + i + 17, cnt);
+        build_huff(d, t);
+        d->have_h[t] = 1;
+        i += 17 + cnt;
+      }
+    } else if (m == 0xDD) {
+      if (sl < 2) return -10;
+      d->ri = (s[0] << 8) | s[1];
+    } else if (m == 0xDA) {
+      if (sl < 1) return -11;
+      const int ns = s[0];
+      if (ns < 1 || ns > 3 || sl < (size_t)(1 + 2 * ns + 3)) return -11;
+      if (ns != 1 && ns != d->ncomp) return -35;          /* partial interleaves: not produced by any common encoder */
+      int cs[3], td[3], ta[3];
+      for (int j = 0; j < ns; ++j) {
+        cs[j] = -1;
+        for (int c = 0; c < d->ncomp; ++c)
+          if (d->comp_id[c] == s[1 + 2 * j]) cs[j] = c;
+        if (cs[j] < 0 || (ns > 1 && cs[j] != j)) return -35;
+        td[j] = s[2 + 2 * j] >> 4;
+        ta[j] = s[2 + 2 * j] & 15;
+        if (td[j] > 1 || ta[j] > 1) return -11;
+      }
+      const int ss = s[1 + 2 * ns], se = s[2 + 2 * ns], ah = s[3 + 2 * ns] >> 4, al = s[3 + 2 * ns] & 15;
+      if (al > 13) return -36;
+      for (int j = 0; j < ns; ++j)
+        if ((ss == 0 && ah == 0 && !d->have_h[td[j]]) || (ss > 0 && !d->have_h[2 + ta[j]])) return -11;
+      const size_t start = o + 2 + len, end = scan_end(p, n, start);
+      const int rc = decode_prog_scan(d, coef, p + start, end - start, ns, cs, td, ta, ss, se, ah, al);
+      if (rc) return rc;
+      ++scans;
+      o = end;
+      continue;
+    }
+    o += 2 + len;
+  }
+  return scans ? 0 : -37;
+}
+
 /* ---- inverse DCT, "islow": LL&M with 13-bit constants, two passes ---- */
 #define CB 13
 #define P1 2
@@ -310,7 +530,12 @@ int jpeg_ref_decode(const uint8_t* file, size_t n, uint8_t* rgba, int64_t pitch)
     plane[c] = (uint8_t*)malloc((size_t)pw[c] * ph[c]);
     if (!coef[c] || !plane[c]) return -20;
   }
-  rc = decode_scan(&d, coef);
+  if (d.progressive) {
+    for (int c = 0; c < d.ncomp; ++c) memset(coef[c], 0, (size_t)pw[c] * ph[c] * sizeof(int16_t));
+    rc = decode_progressive(&d, coef);
+  } else {
+    rc = decode_scan(&d, coef);
+  }
   for (int c = 0; c < d.ncomp && !rc; ++c) {
     const int bw = pw[c] / 8, bh = ph[c] / 8;
 #pragma omp parallel for schedule(static)
@@ -385,5 +610,5 @@ int jpeg_ref_coefficients(const uint8_t* file, size_t n, int16_t* c0, int16_t* c
   int rc = parse(&d, file, n);
   if (rc) return rc;
   int16_t* coef[3] = {c0, c1, c2};
-  return decode_scan(&d, coef);
+  return d.progressive ? decode_progressive(&d, coef) : decode_scan(&d, coef);   /* progressive: caller zeroes the planes */
 }

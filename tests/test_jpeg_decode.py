@@ -63,10 +63,15 @@ def test_oracle_decoder_restart_markers_gray_and_own_files():
     assert np.array_equal(J.decode(data)[..., :3], _pil(data))
 
 
-def test_oracle_decoder_rejects_progressive():
-    data = _jpeg(64, 64, quality=80, progressive=True)
+def _as_arithmetic(data: bytes) -> bytes:
+    """The same file with its SOF marker turned into SOF9 (arithmetic coding): what no decoder here accepts."""
+    sof = data.index(b"\xff\xc0")
+    return data[:sof + 1] + b"\xc9" + data[sof + 2:]
+
+
+def test_oracle_decoder_rejects_arithmetic_coding():
     with pytest.raises(ValueError):
-        J.decode(data)
+        J.decode(_as_arithmetic(_jpeg(64, 64, quality=80)))
 
 
 def _corrupt(data: bytes, seed: int, n_flips: int = 12, scan_only: bool = True) -> bytes:
@@ -235,7 +240,7 @@ def test_gpu_decoder_errors():
     from imagestitching_b200 import _lib as L
     ctx = StitchContext(0)
     with pytest.raises(StitchError) as e:
-        ctx.decode_jpeg(_jpeg(64, 64, quality=80, progressive=True))
+        ctx.decode_jpeg(_as_arithmetic(_jpeg(64, 64, quality=80)))
     assert e.value.status == L.E_BAD_IMAGE and "解码异常" in e.value.message
     # three components that are NOT YCbCr (libjpeg decodes these as RGB): refused, never decoded to wrong colours
     base = _jpeg(64, 48, quality=85, subsampling=0)
