@@ -237,12 +237,94 @@ __global__ void __launch_bounds__(1024) jprog_dc_kernel(const PScan* __restrict_
   }
 }
 
-// Scans of one dependency level, one CTA each: the warp builds the tables, its first thread decodes the scan.
+// ---- refinement scans: one WARP per scan ----
+// The bit stream has to be parsed by one thread (see the head of this file), but the rest of the warp keeps it fed:
+// the scan's blocks stream through a ring of JPROG_STAGES shared-memory slots (cp.async, 4 bytes per lane = one
+// coalesced 128-byte request per block, issued JPROG_STAGES blocks ahead, so the L2 latency of the coefficient
+// buffer -- what made a coefficient-by-coefficient loop over global memory take 2.3 s for a 12 MP file -- is hidden),
+// two ballots give lane 0 the block's non-zero mask, lane 0 runs pj_refine_block on the slot, and the warp writes the
+// scan's band of the block back only when a coefficient changed.
+#define JPROG_STAGES 8
+
+__device__ __forceinline__ int br_sym(const SmemTables& T, int t, Reader& r) {
+  rd_fill(r);
+  return huff_decode(T, t, r);
+}
+__device__ __forceinline__ int br_bits(Reader& r, int nbits) {
+  if (nbits == 0) return 0;
+  rd_fill(r);
+  const int v = (int)(r.acc >> (64 - nbits));
+  rd_skip(r, nbits);
+  return v;
+}
+// Byte-aligned restart: drop the bits in hand, continue behind the next RSTn marker (zeros when there is none).
+__device__ __forceinline__ void br_restart(Reader& r, int* rst_next) {
+  uint32_t o = r.pos;
+  while (o + 1 < r.n && !(r.p[o] == 0xFFu && r.p[o + 1] >= 0xD0u && r.p[o + 1] <= 0xD7u)) ++o;
+  rd_start(r, o + 1 < r.n ? o + 2 : r.n, 0);
+  *rst_next = (*rst_next + 1) & 7;
+}
+
+// Scans of one dependency level, one CTA (one warp) each.
 __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__ scans) {
   __shared__ SmemTables T;
+  __shared__ __align__(16) int16_t ring[JPROG_STAGES][64];
   const PScan S = scans[blockIdx.x];      // a private copy: the decoder's stores cannot alias it
   build_tables(S.tab, T);
-  if (threadIdx.x == 0) pscan_sequential(S, T);
+  const int lane = threadIdx.x;
+  if (S.mode != PSCAN_AC_REFINE && S.mode != PSCAN_DC_REFINE) {
+    // a first scan that could not join the parallel batch (a file that codes a band twice; STITCH_JPROG_SEQ)
+    if (lane == 0) pscan_sequential(S, T);
+    return;
+  }
+  auto issue = [&](int blk) {
+    if (blk < S.n_blk) {
+      const int16_t* src = S.coef + pscan_block(S, blk) * 64 + 2 * lane;
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&ring[blk % JPROG_STAGES][2 * lane]);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  for (int s = 0; s < JPROG_STAGES; ++s) issue(s);
+  Reader r;
+  r.p = S.data;
+  r.n = S.len;
+  rd_start(r, 0, 0);
+  int rst_left = S.ri, rst_next = 0, b_in_mcu = 0;
+  uint32_t eobrun = 0;
+  const int p1 = 1 << S.al, tac = 2 + S.ta;
+  for (int blk = 0; blk < S.n_blk; ++blk) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(JPROG_STAGES - 1) : "memory");
+    __syncwarp();
+    int16_t* c = ring[blk % JPROG_STAGES];
+    const uint32_t lo = __ballot_sync(0xffffffffu, c[lane] != 0), hi = __ballot_sync(0xffffffffu, c[lane + 32] != 0);
+    int dirty = 0;
+    if (lane == 0) {
+      if (b_in_mcu == 0 && S.ri) {
+        if (rst_left == 0) { br_restart(r, &rst_next); eobrun = 0; rst_left = S.ri; }
+        rst_left--;
+      }
+      if (S.mode == PSCAN_DC_REFINE) {
+        if (br_bits(r, 1)) { c[0] = (int16_t)(c[0] | p1); dirty = 1; }
+      } else {
+        dirty = pj_refine_block(r, T, tac, c, (uint64_t)lo | (uint64_t)hi << 32, S.ss, S.se, p1, &eobrun) ? 1 : 0;
+      }
+      b_in_mcu = (b_in_mcu + 1 == S.bpm) ? 0 : b_in_mcu + 1;
+    }
+    dirty = __shfl_sync(0xffffffffu, dirty, 0);
+    __syncwarp();
+    if (dirty) {
+      // only the scan's own band goes back: scans of the same level share blocks (DC refinement beside an AC one)
+      int16_t* dst = S.coef + pscan_block(S, blk) * 64;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int k = 2 * lane + j;
+        if (k >= S.ss && k <= S.se) dst[k] = c[k];
+      }
+    }
+    __syncwarp();
+    issue(blk + JPROG_STAGES);
+  }
 }
 
 }  // namespace jpegdec

@@ -15,7 +15,7 @@
 
 #if defined(__CUDACC__)
 #include <cuda_runtime.h>
-#define PJ_HD __host__ __device__ __forceinline__
+#define PJ_HD __device__ __forceinline__   /* under nvcc only kernels call these; the host build is the tests' CPU drive */
 #else
 #define PJ_HD inline
 struct uint4 { uint32_t x, y, z, w; };   // plain-C++ build (the CPU drive of the tests): layout only
@@ -187,6 +187,77 @@ PJ_HD void sb_restart(SeqBits& b, int* rst_next) {
 PJ_HD void pj_correct(int16_t* cf, int p1) {
   const int v = *cf;
   if ((v & p1) == 0) *cf = (int16_t)(v >= 0 ? v + p1 : v - p1);
+}
+
+// Bit-reader interface of the refinement code below: SeqBits here, the word-wise Reader of jpeg_decode.cuh on the GPU.
+PJ_HD int br_sym(const SmemTables& T, int t, SeqBits& b) { return sb_sym(T, t, b); }
+PJ_HD int br_bits(SeqBits& b, int nbits) { return sb_bits(b, nbits); }
+PJ_HD void br_restart(SeqBits& b, int* rst_next) { sb_restart(b, rst_next); }
+
+#if defined(__CUDACC__)
+#define PJ_CTZ64(x) (__ffsll((long long)(x)) - 1)
+#define PJ_POPC64(x) __popcll(x)
+#else
+#define PJ_CTZ64(x) __builtin_ctzll(x)
+#define PJ_POPC64(x) __builtin_popcountll(x)
+#endif
+
+// Correction bits for the coefficients of mask m (zig-zag positions, ascending), one bit each.  True when one changed.
+template <class BR>
+PJ_HD bool pj_corrections(BR& b, int16_t* c, uint64_t m, int p1) {
+  bool dirty = false;
+  while (m) {
+    int n = PJ_POPC64(m);
+    if (n > 16) n = 16;
+    const int bits = br_bits(b, n);                 // the next n correction bits, first one on top
+    for (int j = n - 1; j >= 0; --j) {
+      const int k = PJ_CTZ64(m);
+      m &= m - 1;
+      if ((bits >> j) & 1) {
+        const int v = c[k];
+        if ((v & p1) == 0) { c[k] = (int16_t)(v >= 0 ? v + p1 : v - p1); dirty = true; }
+      }
+    }
+  }
+  return dirty;
+}
+
+// One block of an AC refinement scan (G.1.2.3, Figure G.7) with the block's non-zero history as a bit mask: the zero
+// coefficients a run skips are found by bit operations (drop r set bits of the zero mask, take the next), the
+// corrections of the non-zero ones it passes are read as one group.  c = the block (zig-zag order), nz = bit k set
+// when c[k] != 0 on entry.  Same result as the coefficient-by-coefficient loop of pscan_sequential.
+template <class BR>
+PJ_HD bool pj_refine_block(BR& b, const SmemTables& T, int tac, int16_t* c, uint64_t nz, int ss, int se, int p1, uint32_t* eobrun) {
+  bool dirty = false;
+  const uint64_t band = (se >= 63 ? ~0ull : ((1ull << (se + 1)) - 1)) & ~((1ull << ss) - 1);
+  int k = ss;
+  if (*eobrun == 0) {
+    while (k <= se) {
+      const int rs = br_sym(T, tac, b);
+      const int r = rs >> 4, s = rs & 15;
+      int newval = 0;
+      if (s) {
+        newval = br_bits(b, 1) ? p1 : -p1;
+      } else if (r != 15) {
+        *eobrun = 1u << r;
+        if (r) *eobrun += (uint32_t)br_bits(b, r);
+        break;
+      }
+      const uint64_t from = band & ~((1ull << k) - 1);          // positions k .. se
+      uint64_t zeros = ~nz & from;
+      for (int i = 0; i < r && zeros; ++i) zeros &= zeros - 1;    // the run's r zero-history coefficients
+      const int stop = zeros ? PJ_CTZ64(zeros) : se + 1;          // the next one takes the new value (or ends a ZRL)
+      const uint64_t below = stop > 63 ? ~0ull : ((1ull << stop) - 1);
+      dirty |= pj_corrections(b, c, nz & from & below, p1);
+      if (s && stop <= 63) { c[stop] = (int16_t)newval; dirty = true; }
+      k = stop + 1;
+    }
+  }
+  if (*eobrun > 0) {
+    if (k <= 63) dirty |= pj_corrections(b, c, nz & band & ~((1ull << k) - 1), p1);
+    --*eobrun;
+  }
+  return dirty;
 }
 
 // The whole scan, block after block (all four kinds).  The steps are those of T.81 G.1.2 / Figures G.3 - G.7.

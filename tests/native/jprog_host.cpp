@@ -24,6 +24,37 @@ extern "C" int jprog_host_info(const uint8_t* file, size_t n, int32_t* info) {
 
 // coef: [blocks][64] int16, buffer order (interleaved MCU order, zig-zag inside a block), zeroed here.
 // scan_desc (optional): per scan {mode, ns, comp, ss, se, ah, al, n_blk}.
+// AC / DC refinement scans the way the GPU's warp kernel runs them (jprog_seq_kernel): block by block through
+// pj_refine_block with the block's non-zero mask.
+static void refine_by_mask(const PScan& S, const SmemTables& T) {
+  SeqBits b;
+  std::memset(&b, 0, sizeof b);
+  b.p = S.data;
+  b.n = S.len;
+  int rst_left = S.ri, rst_next = 0;
+  uint32_t eobrun = 0;
+  const int p1 = 1 << S.al;
+  int b_in_mcu = 0;
+  for (int blk = 0; blk < S.n_blk; ++blk) {
+    if (b_in_mcu == 0 && S.ri) {
+      if (rst_left == 0) { br_restart(b, &rst_next); eobrun = 0; rst_left = S.ri; }
+      rst_left--;
+    }
+    int16_t* c = S.coef + pscan_block(S, blk) * 64;
+    if (S.mode == PSCAN_DC_REFINE) {
+      if (br_bits(b, 1)) c[0] = (int16_t)(c[0] | p1);
+    } else {
+      uint64_t nz = 0;
+      for (int k = 0; k < 64; ++k) nz |= (uint64_t)(c[k] != 0) << k;
+      pj_refine_block(b, T, 2 + S.ta, c, nz, S.ss, S.se, p1, &eobrun);
+    }
+    b_in_mcu = (b_in_mcu + 1 == S.bpm) ? 0 : b_in_mcu + 1;
+  }
+}
+
+static bool g_by_mask = false;
+extern "C" void jprog_host_set_mask_path(int on) { g_by_mask = on != 0; }
+
 extern "C" int jprog_host_decode(const uint8_t* file, size_t n, int16_t* coef, int32_t* scan_desc) {
   Header H;
   const ParseStatus st = parse(file, n, &H);
@@ -44,7 +75,8 @@ extern "C" int jprog_host_decode(const uint8_t* file, size_t n, int16_t* coef, i
     S.coef = coef;
     SmemTables T;
     build_tables_seq(S.tab, T);
-    pscan_sequential(S, T);
+    if (g_by_mask && (S.mode == PSCAN_AC_REFINE || S.mode == PSCAN_DC_REFINE)) refine_by_mask(S, T);
+    else pscan_sequential(S, T);
     if (scan_desc) {
       int32_t* d = scan_desc + 8 * i;
       d[0] = S.mode; d[1] = S.ns; d[2] = S.comp; d[3] = S.ss; d[4] = S.se; d[5] = ps.ah; d[6] = S.al; d[7] = S.n_blk;
