@@ -270,6 +270,24 @@ def synth_screenshot_png(w: int, h: int, seed: int = 0) -> bytes:
     return b.getvalue()
 
 
+def synth_progressive_jpeg(w: int, h: int, seed: int = 0) -> bytes:
+    """A progressive JPEG file (SOF2, libjpeg's standard 10-scan script, quality 90, 4:2:0) of a smooth picture with mild
+    noise, written by PIL / libjpeg-turbo -- the encoder such files come from."""
+    import io
+
+    import numpy as np
+    from PIL import Image, ImageFile
+
+    ImageFile.MAXBLOCK = 1 << 26
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    a = np.stack([128 + 100 * np.sin(x / 17 + y / 29), 128 + 90 * np.cos(x / 23 - y / 13), (x * 3 + y * 5) % 256], -1)
+    a = np.clip(a + rng.integers(-4, 5, a.shape), 0, 255).astype(np.uint8)
+    b = io.BytesIO()
+    Image.fromarray(a).save(b, "JPEG", quality=90, subsampling=2, progressive=True)
+    return b.getvalue()
+
+
 def cpu_png_files_run(files, direction, mode, platform, steps: int):
     """The PNG-in / PNG-out job on the host cores: oracle PNG decoder (one thread per file), C raster (OpenMP), oracle PNG
     writer.  Returns (MP/s, ms per job, cores)."""
@@ -714,6 +732,7 @@ def main():
     files_steps = args.files_steps if args.files_steps >= 0 else (24 if args.workload in ("cfg2", "cfg5") else 0)
     e2e_files = None
     shot_files = None
+    prog_files = None
     file_bytes_list = []
     if files_steps > 0:
         lib.stitch_wait(ctx.handle, last)
@@ -870,6 +889,86 @@ def main():
             e2e_files["png_in"] = {"value": None, "note": f"failed: {e}"}
             shot_files = None
 
+        # progressive JPEG inputs: nine 1600 x 1200 files (web-sized: cameras write baseline files) -> stitched JPEG file.
+        # The refinement scans of a file are decoded by ONE warp each (jpeg_prog.cuh), so a job's latency is that of its
+        # longest scan chain; few steps, the leg is slow by construction.
+        try:
+            pw_, ph_ = 1600, 1200
+            progs = [synth_progressive_jpeg(pw_, ph_, seed=i) for i in range(3)]
+            progs = [progs[i % 3] for i in range(9)]
+            pbufs = []
+            for f in progs:
+                pf = C.c_void_p()
+                assert lib.stitch_host_alloc(len(f), C.byref(pf)) == 0
+                C.memmove(pf, f, len(f))
+                pbufs.append((pf, len(f)))
+                host_outs.append(pf)
+            pjobs = []
+            p_mp = 0.0
+            for _ in range(e2e_lanes):
+                arr = (L.StitchImage * 9)()
+                for i in range(9):
+                    arr[i].desc.natural_width, arr[i].desc.natural_height = pw_, ph_
+                    arr[i].desc.width, arr[i].desc.height = pw_, ph_
+                    arr[i].desc.orientation = 1
+                    arr[i].desc.file_size = pbufs[i][1]
+                    arr[i].data = pbufs[i][0]
+                    arr[i].pitch_bytes = pbufs[i][1]
+                    arr[i].mem_kind = L.MEM_HOST_JPEG
+                pj_ = L.StitchJob()
+                pj_.images, pj_.n = arr, 9
+                pj_.params = hjobs[0][0].params
+                pj_.output_flags = L.OUT_JPEG
+                pj_.out_mem_kind = L.MEM_HOST
+                if not p_mp:
+                    lay = L.StitchLayout()
+                    descs = (L.StitchImageDesc * 9)(*[arr[i].desc for i in range(9)])
+                    assert lib.stitch_layout(descs, 9, C.byref(pj_.params), C.byref(lay)) == 0
+                    p_mp = lay.canvas_w * lay.canvas_h / 1e6
+                po = C.c_void_p()
+                assert lib.stitch_host_alloc(32 << 20, C.byref(po)) == 0
+                host_outs.append(po)
+                pj_.out_jpeg, pj_.out_capacity_jpeg, pj_.jpeg_quality = po.value, 32 << 20, 90
+                pjobs.append((pj_, arr, L.StitchResult()))
+
+            def prog_loop(nsteps):
+                tickets = []
+                for i in range(nsteps):
+                    pj_, _, pr = pjobs[i % e2e_lanes]
+                    t = C.c_uint64()
+                    st = lib.stitch_submit(ctx.handle, C.byref(pj_), C.byref(pr), C.byref(t))
+                    assert st == 0, lib.stitch_last_error(ctx.handle)
+                    tickets.append(t.value)
+                    if i >= e2e_lanes - 1:
+                        assert lib.stitch_wait(ctx.handle, tickets[i - (e2e_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
+                assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0, lib.stitch_last_error(ctx.handle)
+
+            p_steps = min(files_steps, 2 * e2e_lanes)
+            prog_loop(e2e_lanes)
+            torch.cuda.synchronize()
+            barrier()
+            t0 = time.perf_counter()
+            prog_loop(p_steps)
+            torch.cuda.synchronize()
+            ps_ = time.perf_counter() - t0
+            t1 = time.perf_counter()
+            assert lib.stitch_run(ctx.handle, C.byref(pjobs[0][0]), C.byref(pjobs[0][2])) == 0
+            p_single = (time.perf_counter() - t1) * 1e3
+            if world > 1:
+                t = torch.tensor([ps_], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ps_ = float(t.item())
+            e2e_files["prog_in"] = {"value": p_mp * p_steps * world / ps_, "unit": "MP/s", "steps": p_steps,
+                                    "ms_per_step": ps_ / p_steps * 1e3, "single_job_latency_ms": p_single, "output_mp_per_step": p_mp,
+                                    "h2d_bytes_per_step": sum(b for _, b in pbufs), "d2h_bytes_per_step": int(pjobs[0][2].jpeg_bytes),
+                                    "inputs": "9 progressive JPEG files (SOF2, libjpeg's 10-scan script), 1600x1200, quality 90, 4:2:0, "
+                                              "written by PIL, pinned host memory; first scans decoded in parallel, refinement "
+                                              "scans one warp each (latency-bound by construction), stitched, JPEG file out"}
+            prog_files = progs
+        except Exception as e:
+            e2e_files["prog_in"] = {"value": None, "note": f"failed: {e}"}
+            prog_files = None
+
     if has_jpeg or has_png:
         out_bytes = int(hres.jpeg_bytes if has_jpeg else hres.png_bytes)   # d2h of the e2e step = the file
         algo_bytes = src_bytes + out_bytes
@@ -934,6 +1033,14 @@ def main():
                                                                      "oracle PNG writer (sequential)"}
                 except Exception as e:
                     e2e_files["png_in"]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
+            if isinstance(e2e_files.get("prog_in"), dict) and e2e_files["prog_in"].get("value") and prog_files:
+                try:
+                    v, ms, cores = cpu_files_run(prog_files, direction, mode, platform, 1, "jpeg")
+                    e2e_files["prog_in"]["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "ms_per_step": ms,
+                                                            "sample": "1 job: oracle progressive JPEG decoder (a thread per file) + C raster "
+                                                                      "(OpenMP) + oracle JPEG writer (sequential)"}
+                except Exception as e:
+                    e2e_files["prog_in"]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
     if rank == 0:
         print(json.dumps(line))
     for p in host_keep + host_outs:

@@ -238,22 +238,30 @@ __global__ void __launch_bounds__(1024) jprog_dc_kernel(const PScan* __restrict_
 }
 
 // ---- refinement scans: one WARP per scan ----
-// The bit stream has to be parsed by one thread (see the head of this file), but the rest of the warp keeps it fed:
-// the scan's blocks stream through a ring of JPROG_STAGES shared-memory slots (cp.async, 4 bytes per lane = one
-// coalesced 128-byte request per block, issued JPROG_STAGES blocks ahead, so the L2 latency of the coefficient
-// buffer -- what made a coefficient-by-coefficient loop over global memory take 2.3 s for a 12 MP file -- is hidden),
-// two ballots give lane 0 the block's non-zero mask, lane 0 runs pj_refine_block on the slot, and the warp writes the
-// scan's band of the block back only when a coefficient changed.
+// The bit stream has to be parsed by one thread (see the head of this file); a single GPU thread issues a dependent
+// instruction every ~4 cycles, so everything that is not parsing is taken off it:
+//   * bytes: the warp copies the scan's bytes into a shared-memory ring WITHOUT the stuffed zeros (32 words per step,
+//     keep flags + a warp prefix sum), so lane 0 refills 32 bits with one aligned LDS and no 0xFF test;
+//   * blocks: they stream through a ring of JPROG_STAGES shared-memory slots (cp.async, one coalesced 128-byte request
+//     per block, issued JPROG_STAGES blocks ahead: the L2 latency of the coefficient buffer -- what made a
+//     coefficient-by-coefficient loop over global memory take 2.3 s for a 12 MP file -- is hidden), and two ballots
+//     give lane 0 the block's non-zero mask;
+//   * lane 0 runs pj_refine_parse: mask algebra per symbol, results as four 64-bit words;
+//   * every lane applies them to its two coefficients (pj_refine_apply) and stores the ones that changed.
+// DC refinement scans (one bit per block) need no parser at all: lane i of a step takes block 32 * step + i.
+// Scans with restart intervals, and first scans that could not join the parallel batch, take the plain one-thread
+// route (pscan_sequential / pj_refine on the word-wise Reader).
 #define JPROG_STAGES 8
+#define JPROG_RING 1024            // bytes of unstuffed scan data in shared memory (power of two)
 
 __device__ __forceinline__ int br_sym(const SmemTables& T, int t, Reader& r) {
   rd_fill(r);
   return huff_decode(T, t, r);
 }
-__device__ __forceinline__ int br_bits(Reader& r, int nbits) {
+__device__ __forceinline__ int br_bits(Reader& r, int nbits) {   // nbits <= 32
   if (nbits == 0) return 0;
   rd_fill(r);
-  const int v = (int)(r.acc >> (64 - nbits));
+  const int v = (int)(uint32_t)(r.acc >> (64 - nbits));
   rd_skip(r, nbits);
   return v;
 }
@@ -265,18 +273,59 @@ __device__ __forceinline__ void br_restart(Reader& r, int* rst_next) {
   *rst_next = (*rst_next + 1) & 7;
 }
 
-// Scans of one dependency level, one CTA (one warp) each.
-__global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__ scans) {
-  __shared__ SmemTables T;
-  __shared__ __align__(16) int16_t ring[JPROG_STAGES][64];
-  const PScan S = scans[blockIdx.x];      // a private copy: the decoder's stores cannot alias it
-  build_tables(S.tab, T);
-  const int lane = threadIdx.x;
-  if (S.mode != PSCAN_AC_REFINE && S.mode != PSCAN_DC_REFINE) {
-    // a first scan that could not join the parallel batch (a file that codes a band twice; STITCH_JPROG_SEQ)
-    if (lane == 0) pscan_sequential(S, T);
-    return;
+// Lane 0's reader over the ring of unstuffed bytes: rd / wr count bytes since the start of the scan.
+struct RingBits {
+  const uint8_t* ring;
+  uint32_t rd, wr;
+  uint64_t acc;
+  int cnt;
+};
+__device__ __forceinline__ void rb_fill(RingBits& b) {
+  if (b.cnt > 32) return;
+  uint32_t w;
+  if (b.rd + 4 <= b.wr) {
+    w = __byte_perm(*reinterpret_cast<const uint32_t*>(b.ring + (b.rd & (JPROG_RING - 1))), 0, 0x0123);
+  } else {                                        // the last bytes of the scan, zeros behind them
+    w = 0;
+    for (uint32_t j = 0; j < 4; ++j)
+      if (b.rd + j < b.wr) w |= (uint32_t)b.ring[(b.rd + j) & (JPROG_RING - 1)] << (24 - 8 * j);
   }
+  b.rd += 4;
+  b.acc |= (uint64_t)w << (32 - b.cnt);
+  b.cnt += 32;
+}
+__device__ __forceinline__ int br_sym(const SmemTables& T, int t, RingBits& b) {
+  rb_fill(b);
+  const uint32_t v = (uint32_t)(b.acc >> 48);
+  const uint32_t e = T.lut[t][v >> 8];
+  int len = (int)(e >> 8), sym = (int)(e & 255u);
+  if (!e) {
+    len = 16;
+    sym = 0;
+    for (int l = 9; l <= 16; ++l) {
+      const int code = (int)(v >> (16 - l));
+      if (code <= T.maxcode[t][l] && code >= T.mincode[t][l]) {
+        len = l;
+        sym = T.vals[t][(T.valptr[t][l] + code - T.mincode[t][l]) & 255];
+        break;
+      }
+    }
+  }
+  b.acc <<= len;
+  b.cnt -= len;
+  return sym;
+}
+__device__ __forceinline__ int br_bits(RingBits& b, int nbits) {   // nbits <= 32
+  if (nbits == 0) return 0;
+  rb_fill(b);
+  const int v = (int)(uint32_t)(b.acc >> (64 - nbits));
+  b.acc <<= nbits;
+  b.cnt -= nbits;
+  return v;
+}
+
+// The plain route: one thread, coefficient blocks through the cp.async ring, word-wise Reader with restart markers.
+__device__ __forceinline__ void jprog_refine_plain(const PScan& S, const SmemTables& T, int16_t (*ring)[64], int lane) {
   auto issue = [&](int blk) {
     if (blk < S.n_blk) {
       const int16_t* src = S.coef + pscan_block(S, blk) * 64 + 2 * lane;
@@ -293,34 +342,156 @@ __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__
   int rst_left = S.ri, rst_next = 0, b_in_mcu = 0;
   uint32_t eobrun = 0;
   const int p1 = 1 << S.al, tac = 2 + S.ta;
+  const uint64_t band = (S.se >= 63 ? ~0ull : ((1ull << (S.se + 1)) - 1)) & ~((1ull << S.ss) - 1);
   for (int blk = 0; blk < S.n_blk; ++blk) {
     asm volatile("cp.async.wait_group %0;" ::"n"(JPROG_STAGES - 1) : "memory");
     __syncwarp();
     int16_t* c = ring[blk % JPROG_STAGES];
-    const uint32_t lo = __ballot_sync(0xffffffffu, c[lane] != 0), hi = __ballot_sync(0xffffffffu, c[lane + 32] != 0);
-    int dirty = 0;
+    const int v0 = c[lane], v1 = c[lane + 32];
+    const uint32_t lo = __ballot_sync(0xffffffffu, v0 != 0), hi = __ballot_sync(0xffffffffu, v1 != 0);
+    RefineOut o;
+    o.corrmask = o.corrbits = o.newmask = o.negmask = 0;
     if (lane == 0) {
       if (b_in_mcu == 0 && S.ri) {
         if (rst_left == 0) { br_restart(r, &rst_next); eobrun = 0; rst_left = S.ri; }
         rst_left--;
       }
       if (S.mode == PSCAN_DC_REFINE) {
-        if (br_bits(r, 1)) { c[0] = (int16_t)(c[0] | p1); dirty = 1; }
+        if (br_bits(r, 1)) { o.corrmask = 1; o.corrbits = 1; }     // "correct" coefficient 0 ...
       } else {
-        dirty = pj_refine_block(r, T, tac, c, (uint64_t)lo | (uint64_t)hi << 32, S.ss, S.se, p1, &eobrun) ? 1 : 0;
+        pj_refine_parse(r, T, tac, (uint64_t)lo | (uint64_t)hi << 32, band, &eobrun, &o);
       }
       b_in_mcu = (b_in_mcu + 1 == S.bpm) ? 0 : b_in_mcu + 1;
     }
-    dirty = __shfl_sync(0xffffffffu, dirty, 0);
+    o.corrmask = __shfl_sync(0xffffffffu, o.corrmask, 0);
+    o.corrbits = __shfl_sync(0xffffffffu, o.corrbits, 0);
+    o.newmask = __shfl_sync(0xffffffffu, o.newmask, 0);
+    o.negmask = __shfl_sync(0xffffffffu, o.negmask, 0);
+    int16_t* dst = S.coef + pscan_block(S, blk) * 64;
+    if (S.mode == PSCAN_DC_REFINE) {
+      if (lane == 0 && o.corrmask) dst[0] = (int16_t)(v0 | p1);     // ... which for the DC term is a plain OR
+    } else {
+      const int n0 = pj_refine_apply(v0, lane, p1, o), n1 = pj_refine_apply(v1, lane + 32, p1, o);
+      if (n0 != v0) dst[lane] = (int16_t)n0;
+      if (n1 != v1) dst[lane + 32] = (int16_t)n1;
+    }
     __syncwarp();
-    if (dirty) {
-      // only the scan's own band goes back: scans of the same level share blocks (DC refinement beside an AC one)
-      int16_t* dst = S.coef + pscan_block(S, blk) * 64;
+    issue(blk + JPROG_STAGES);
+  }
+}
+
+// Scans of one dependency level, one CTA (one warp) each.
+__global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__ scans) {
+  __shared__ SmemTables T;
+  __shared__ __align__(16) int16_t ring[JPROG_STAGES][64];
+  __shared__ __align__(16) uint8_t bytes[JPROG_RING];
+  const PScan S = scans[blockIdx.x];      // a private copy: the decoder's stores cannot alias it
+  build_tables(S.tab, T);
+  const int lane = threadIdx.x;
+  if (S.mode != PSCAN_AC_REFINE && S.mode != PSCAN_DC_REFINE) {
+    // a first scan that could not join the parallel batch (a file that codes a band twice; STITCH_JPROG_SEQ)
+    if (lane == 0) pscan_sequential(S, T);
+    return;
+  }
+  if (S.ri != 0) { jprog_refine_plain(S, T, ring, lane); return; }
+
+  // ---- the byte ring: 32 words of the scan per step, stuffed zeros dropped ----
+  uint32_t raw_pos = 0, wr = 0, prev_last = 0;    // warp-uniform
+  const uint32_t* data32 = reinterpret_cast<const uint32_t*>(S.data);
+  auto stage = [&]() {
+    const uint32_t base = raw_pos + 4 * lane;
+    const uint32_t w = base < S.len ? data32[base >> 2] : 0u;
+    const int valid = base < S.len ? min(4, (int)(S.len - base)) : 0;
+    const uint32_t up = __shfl_up_sync(0xffffffffu, w, 1);
+    uint32_t pb = lane ? up >> 24 : prev_last;
+    uint32_t keep = 0;                            // bit j: byte j of the word is data
+    int n = 0;
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const int k = 2 * lane + j;
-        if (k >= S.ss && k <= S.se) dst[k] = c[k];
+    for (int j = 0; j < 4; ++j) {
+      const uint32_t bj = (w >> (8 * j)) & 255u;
+      if (j < valid && !(bj == 0u && pb == 0xFFu)) { keep |= 1u << j; ++n; }
+      pb = bj;
+    }
+    int x = n;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    uint32_t at = wr + (uint32_t)(x - n);
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (keep & (1u << j)) bytes[at++ & (JPROG_RING - 1)] = (uint8_t)(w >> (8 * j));
+    wr += (uint32_t)__shfl_sync(0xffffffffu, x, 31);
+    prev_last = __shfl_sync(0xffffffffu, w, 31) >> 24;
+    raw_pos += 128;
+  };
+  // at least `need` bytes ahead of the reader (or all that is left); never overwrites unread bytes (need <= 512)
+  auto ensure = [&](uint32_t rd, uint32_t need) {
+    while (wr - rd < need && raw_pos < S.len) stage();
+    __syncwarp();
+  };
+  const int p1 = 1 << S.al;
+
+  if (S.mode == PSCAN_DC_REFINE) {
+    // one bit per block, in block order: a step is 32 blocks = 4 bytes of the ring
+    uint32_t rd = 0;
+    for (int g = 0; g < S.n_blk; g += 32) {
+      ensure(rd, 64);
+      const int blk = g + lane;
+      const uint32_t at = rd + (lane >> 3);
+      const uint32_t byte = at < wr ? bytes[at & (JPROG_RING - 1)] : 0u;
+      if (blk < S.n_blk && ((byte >> (7 - (lane & 7))) & 1u)) {
+        int16_t* dc = S.coef + pscan_block(S, blk) * 64;
+        *dc = (int16_t)(*dc | p1);
       }
+      rd += 4;
+      __syncwarp();
+    }
+    return;
+  }
+
+  auto issue = [&](int blk) {
+    if (blk < S.n_blk) {
+      const int16_t* src = S.coef + pscan_block(S, blk) * 64 + 2 * lane;
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&ring[blk % JPROG_STAGES][2 * lane]);
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  for (int s = 0; s < JPROG_STAGES; ++s) issue(s);
+  RingBits b;
+  b.ring = bytes;
+  b.rd = 0;
+  b.wr = 0;
+  b.acc = 0;
+  b.cnt = 0;
+  uint32_t eobrun = 0;
+  const int tac = 2 + S.ta;
+  const uint64_t band = (S.se >= 63 ? ~0ull : ((1ull << (S.se + 1)) - 1)) & ~((1ull << S.ss) - 1);
+  for (int blk = 0; blk < S.n_blk; ++blk) {
+    // a block takes at most 63 x (16 + 1 + 1) + 30 bits = 146 bytes, the reader holds up to 8 more
+    ensure(__shfl_sync(0xffffffffu, b.rd, 0), 256);
+    asm volatile("cp.async.wait_group %0;" ::"n"(JPROG_STAGES - 1) : "memory");
+    __syncwarp();
+    const int16_t* c = ring[blk % JPROG_STAGES];
+    const int v0 = c[lane], v1 = c[lane + 32];
+    const uint32_t lo = __ballot_sync(0xffffffffu, v0 != 0), hi = __ballot_sync(0xffffffffu, v1 != 0);
+    RefineOut o;
+    o.corrmask = o.corrbits = o.newmask = o.negmask = 0;
+    if (lane == 0) {
+      b.wr = wr;
+      pj_refine_parse(b, T, tac, (uint64_t)lo | (uint64_t)hi << 32, band, &eobrun, &o);
+    }
+    o.corrmask = __shfl_sync(0xffffffffu, o.corrmask, 0);
+    o.corrbits = __shfl_sync(0xffffffffu, o.corrbits, 0);
+    o.newmask = __shfl_sync(0xffffffffu, o.newmask, 0);
+    o.negmask = __shfl_sync(0xffffffffu, o.negmask, 0);
+    if (o.corrmask | o.newmask) {
+      int16_t* dst = S.coef + pscan_block(S, blk) * 64;
+      const int n0 = pj_refine_apply(v0, lane, p1, o), n1 = pj_refine_apply(v1, lane + 32, p1, o);
+      if (n0 != v0) dst[lane] = (int16_t)n0;
+      if (n1 != v1) dst[lane + 32] = (int16_t)n1;
     }
     __syncwarp();
     issue(blk + JPROG_STAGES);

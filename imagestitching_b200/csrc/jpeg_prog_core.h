@@ -202,62 +202,75 @@ PJ_HD void br_restart(SeqBits& b, int* rst_next) { sb_restart(b, rst_next); }
 #define PJ_POPC64(x) __builtin_popcountll(x)
 #endif
 
-// Correction bits for the coefficients of mask m (zig-zag positions, ascending), one bit each.  True when one changed.
+// ---- AC refinement, block by block, with the block's history as a bit mask (G.1.2.3, Figure G.7) ----
+// The bit stream can only be parsed by ONE thread (jpeg_prog.cuh), so that thread does nothing but parse: given the
+// mask nz of coefficients that are non-zero on entry (zig-zag bit k), it walks the symbols with mask algebra -- a run
+// of r zero-history coefficients drops r set bits from the zero mask, the lowest remaining one takes the new value,
+// the non-zero ones passed on the way each own one correction bit -- and RECORDS what to do: the coefficients that
+// get a correction bit (corrmask) with their bits in stream order (corrbits, first bit on top), the newly non-zero
+// ones (newmask) and their signs (negmask).  pj_refine_apply then updates one coefficient; on the GPU every lane of
+// the warp applies two.
+struct RefineOut {
+  uint64_t corrmask, corrbits, newmask, negmask;
+};
+
 template <class BR>
-PJ_HD bool pj_corrections(BR& b, int16_t* c, uint64_t m, int p1) {
-  bool dirty = false;
-  while (m) {
-    int n = PJ_POPC64(m);
-    if (n > 16) n = 16;
-    const int bits = br_bits(b, n);                 // the next n correction bits, first one on top
-    for (int j = n - 1; j >= 0; --j) {
-      const int k = PJ_CTZ64(m);
-      m &= m - 1;
-      if ((bits >> j) & 1) {
-        const int v = c[k];
-        if ((v & p1) == 0) { c[k] = (int16_t)(v >= 0 ? v + p1 : v - p1); dirty = true; }
-      }
-    }
+PJ_HD void pj_refine_take(BR& b, uint64_t m, RefineOut* o) {
+  int n = PJ_POPC64(m);
+  if (n == 0) return;
+  o->corrmask |= m;
+  if (n > 32) {                                   // br_bits hands out at most 32 bits
+    o->corrbits = (o->corrbits << 32) | (uint32_t)br_bits(b, 32);
+    n -= 32;
   }
-  return dirty;
+  o->corrbits = (o->corrbits << n) | (uint32_t)br_bits(b, n);
 }
 
-// One block of an AC refinement scan (G.1.2.3, Figure G.7) with the block's non-zero history as a bit mask: the zero
-// coefficients a run skips are found by bit operations (drop r set bits of the zero mask, take the next), the
-// corrections of the non-zero ones it passes are read as one group.  c = the block (zig-zag order), nz = bit k set
-// when c[k] != 0 on entry.  Same result as the coefficient-by-coefficient loop of pscan_sequential.
+// band = bits ss..se.  Same effect on the block as the coefficient-by-coefficient loop of pscan_sequential.
 template <class BR>
-PJ_HD bool pj_refine_block(BR& b, const SmemTables& T, int tac, int16_t* c, uint64_t nz, int ss, int se, int p1, uint32_t* eobrun) {
-  bool dirty = false;
-  const uint64_t band = (se >= 63 ? ~0ull : ((1ull << (se + 1)) - 1)) & ~((1ull << ss) - 1);
-  int k = ss;
+PJ_HD void pj_refine_parse(BR& b, const SmemTables& T, int tac, uint64_t nz, uint64_t band, uint32_t* eobrun, RefineOut* o) {
+  o->corrmask = o->corrbits = o->newmask = o->negmask = 0;
+  uint64_t from = band;                           // positions of the band not yet passed
   if (*eobrun == 0) {
-    while (k <= se) {
+    while (from) {
       const int rs = br_sym(T, tac, b);
       const int r = rs >> 4, s = rs & 15;
-      int newval = 0;
+      bool neg = false;
       if (s) {
-        newval = br_bits(b, 1) ? p1 : -p1;
+        neg = br_bits(b, 1) == 0;
       } else if (r != 15) {
         *eobrun = 1u << r;
         if (r) *eobrun += (uint32_t)br_bits(b, r);
         break;
       }
-      const uint64_t from = band & ~((1ull << k) - 1);          // positions k .. se
       uint64_t zeros = ~nz & from;
       for (int i = 0; i < r && zeros; ++i) zeros &= zeros - 1;    // the run's r zero-history coefficients
-      const int stop = zeros ? PJ_CTZ64(zeros) : se + 1;          // the next one takes the new value (or ends a ZRL)
-      const uint64_t below = stop > 63 ? ~0ull : ((1ull << stop) - 1);
-      dirty |= pj_corrections(b, c, nz & from & below, p1);
-      if (s && stop <= 63) { c[stop] = (int16_t)newval; dirty = true; }
-      k = stop + 1;
+      const uint64_t low = zeros & (0 - zeros);                   // the next one: takes the new value (or ends a ZRL)
+      const uint64_t upto = zeros ? low - 1 : ~0ull;              // everything in front of it
+      pj_refine_take(b, nz & from & upto, o);
+      if (s && zeros) {
+        o->newmask |= low;
+        if (neg) o->negmask |= low;
+      }
+      from = zeros ? from & ~(upto | low) : 0;
     }
   }
   if (*eobrun > 0) {
-    if (k <= 63) dirty |= pj_corrections(b, c, nz & band & ~((1ull << k) - 1), p1);
+    pj_refine_take(b, nz & from, o);
     --*eobrun;
   }
-  return dirty;
+}
+
+// Coefficient k of the block after the scan (v = its value before).
+PJ_HD int pj_refine_apply(int v, int k, int p1, const RefineOut& o) {
+  const uint64_t bit = 1ull << k;
+  if (o.corrmask & bit) {
+    const int rank = PJ_POPC64(o.corrmask & (bit - 1)), total = PJ_POPC64(o.corrmask);
+    if (((o.corrbits >> (total - 1 - rank)) & 1) && (v & p1) == 0) v = v >= 0 ? v + p1 : v - p1;
+  } else if (o.newmask & bit) {
+    v = (o.negmask & bit) ? -p1 : p1;
+  }
+  return v;
 }
 
 // The whole scan, block after block (all four kinds).  The steps are those of T.81 G.1.2 / Figures G.3 - G.7.

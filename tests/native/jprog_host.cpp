@@ -25,7 +25,7 @@ extern "C" int jprog_host_info(const uint8_t* file, size_t n, int32_t* info) {
 // coef: [blocks][64] int16, buffer order (interleaved MCU order, zig-zag inside a block), zeroed here.
 // scan_desc (optional): per scan {mode, ns, comp, ss, se, ah, al, n_blk}.
 // AC / DC refinement scans the way the GPU's warp kernel runs them (jprog_seq_kernel): block by block through
-// pj_refine_block with the block's non-zero mask.
+// pj_refine_parse (one thread) + pj_refine_apply (every coefficient) with the block's non-zero mask.
 static void refine_by_mask(const PScan& S, const SmemTables& T) {
   SeqBits b;
   std::memset(&b, 0, sizeof b);
@@ -46,7 +46,10 @@ static void refine_by_mask(const PScan& S, const SmemTables& T) {
     } else {
       uint64_t nz = 0;
       for (int k = 0; k < 64; ++k) nz |= (uint64_t)(c[k] != 0) << k;
-      pj_refine_block(b, T, 2 + S.ta, c, nz, S.ss, S.se, p1, &eobrun);
+      const uint64_t band = (S.se >= 63 ? ~0ull : ((1ull << (S.se + 1)) - 1)) & ~((1ull << S.ss) - 1);
+      RefineOut o;
+      pj_refine_parse(b, T, 2 + S.ta, nz, band, &eobrun, &o);
+      for (int k = 0; k < 64; ++k) c[k] = (int16_t)pj_refine_apply(c[k], k, p1, o);      // on the GPU: two per lane
     }
     b_in_mcu = (b_in_mcu + 1 == S.bpm) ? 0 : b_in_mcu + 1;
   }

@@ -109,7 +109,66 @@ def test_parser_lists_the_scans_of_libjpegs_script():
     assert desc[9].tolist()[:7] == [3, 1, 0, 1, 63, 1, 0]
 
 
+# ---------------------------------------------------------------- scan scripts PIL never writes
+def _script_files(sizes=((123, 77), (64, 48), (17, 9)), restarts=(0, 5)):
+    """(label, file) for every script of tests/jprog_encode.py x sampling x restart interval, re-coded from PIL baselines."""
+    from tests import jprog_encode as E
+    for size in sizes:
+        for ss, gray in ((0, False), (1, False), (2, False), (None, True)):
+            base = _jpeg(*size, seed=5, quality=88, gray=gray, **({} if gray else {"subsampling": ss}))
+            assert E.component_ids_from_one(base)
+            for name, make in E.SCRIPTS.items():
+                for ri in restarts:
+                    yield f"{size} ss={ss} {name} ri={ri}", base, E.encode_progressive(base, make(1 if gray else 3), ri)
+
+
+def test_oracle_and_scan_decoder_on_other_scripts():
+    """DC scans per component, spectral selection alone, three refinement passes, restart intervals in AC scans: the
+    re-coded file must give PIL the pixels of its source (the test encoder is sound), the oracle PIL's pixels, and both
+    CPU-driven forms of the GPU's scan decoder the oracle's coefficients."""
+    lib = _host_lib()
+    lib.jprog_host_set_mask_path.argtypes = [ctypes.c_int]
+    n = 0
+    for label, base, f in _script_files():
+        assert np.array_equal(_pil(f), _pil(base)), label
+        assert np.array_equal(J.decode(f)[..., :3], _pil(f)), label
+        for by_mask in (0, 1):
+            lib.jprog_host_set_mask_path(by_mask)
+            coef, info, _ = _host_coefficients(lib, f)
+            assert np.array_equal(coef, _buffer_order(J.coefficients(f), int(info[3]), int(info[4]))), (label, by_mask)
+        n += 1
+    lib.jprog_host_set_mask_path(0)
+    assert n == 96
+
+
+def test_mask_path_of_the_scan_decoder_equals_oracle_coefficients():
+    """pj_refine_parse + pj_refine_apply (what the warp kernel runs) on PIL's files."""
+    lib = _host_lib()
+    lib.jprog_host_set_mask_path.argtypes = [ctypes.c_int]
+    lib.jprog_host_set_mask_path(1)
+    try:
+        for size in SIZES + [(800, 600)]:
+            for ss in (0, 1, 2):
+                for q, kw in ((20, {}), (90, {"restart_marker_blocks": 3}), (100, {})):
+                    data = _jpeg(*size, seed=q, quality=q, subsampling=ss, progressive=True, **kw)
+                    coef, info, _ = _host_coefficients(lib, data)
+                    assert np.array_equal(coef, _buffer_order(J.coefficients(data), int(info[3]), int(info[4]))), (size, ss, q)
+    finally:
+        lib.jprog_host_set_mask_path(0)
+
+
 # ---------------------------------------------------------------- GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("seq", [0, 1], ids=["parallel-first-scans", "one-thread-per-scan"])
+def test_gpu_other_scripts_equal_oracle(seq, monkeypatch):
+    from imagestitching_b200 import StitchContext
+    monkeypatch.setenv("STITCH_JPROG_SEQ", str(seq))
+    ctx = StitchContext(0)
+    for label, _, f in _script_files(sizes=((123, 77), (333, 211)), restarts=(0, 7)):
+        assert np.array_equal(ctx.decode_jpeg(f), J.decode(f)), label
+    ctx.close()
+
+
 GPU_FILES = [
     dict(w=1, h=1, quality=90, subsampling=2), dict(w=7, h=5, quality=75, subsampling=0),
     dict(w=123, h=77, quality=90, subsampling=2), dict(w=250, h=131, quality=50, subsampling=1),
