@@ -246,7 +246,9 @@ __global__ void __launch_bounds__(1024) jprog_dc_kernel(const PScan* __restrict_
 //     per block, issued JPROG_STAGES blocks ahead: the L2 latency of the coefficient buffer -- what made a
 //     coefficient-by-coefficient loop over global memory take 2.3 s for a 12 MP file -- is hidden), and two ballots
 //     give lane 0 the block's non-zero mask;
-//   * lane 0 runs pj_refine_parse: mask algebra per symbol, results as four 64-bit words;
+//   * the lanes list the positions of the block's zero-history coefficients (one popc each), so that a zero run is one
+//     table read for the parser, pj_refine_parse_z: results as four 64-bit words.  All 32 lanes run the parser on the
+//     same bits (same cost as one lane in SIMT; no divergence, no broadcast of the results);
 //   * every lane applies them to its two coefficients (pj_refine_apply) and stores the ones that changed.
 // DC refinement scans (one bit per block) need no parser at all: lane i of a step takes block 32 * step + i.
 // Scans with restart intervals, and first scans that could not join the parallel batch, take the plain one-thread
@@ -324,8 +326,52 @@ __device__ __forceinline__ int br_bits(RingBits& b, int nbits) {   // nbits <= 3
   return v;
 }
 
+// ---- scans of one launch that depend on each other: progress words ----
+// A refinement pass may touch block i as soon as the pass before it (same component, same block order) is done with
+// block i: the producer publishes its block count every few blocks (fence + release store), the consumer polls it
+// (acquire load, bounded: a corrupt job must not hang the GPU) before it requests a block.  All CTAs of the launch are
+// resident (one warp each, at most a few dozen), and producers have the lower CTA indices.
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Warp-wide: returns once every dependency has published at least `need` blocks; `seen` caches the smallest count read.
+// Every lane runs the same loop on lane 0's reading: a poll inside `if (lane == 0)` left the warp split in two behind
+// it (the compiler kept separate copies of the code that follows), and everything warp-wide then ran twice per block
+// -- 340 ms instead of 230 for a 3 MP file.
+__device__ __forceinline__ void wait_deps(const PScan& S, uint32_t need, uint32_t& seen, int lane) {
+  if (S.ndep == 0 || seen >= need) return;
+  uint32_t low = 0xffffffffu;
+  for (int d = 0; d < S.ndep; ++d) {
+    uint32_t v = __shfl_sync(0xffffffffu, ld_acquire_u32(S.dep[d]), 0), spins = 0;
+    while (v < need && ++spins < (1u << 24)) {
+      __nanosleep(200);
+      v = __shfl_sync(0xffffffffu, ld_acquire_u32(S.dep[d]), 0);
+    }
+    low = min(low, max(v, need));                 // gave up: carry on (the job's output is garbage, the GPU is free)
+  }
+  seen = low;
+  (void)lane;
+}
+// Warp-wide: this scan's blocks [0, n) are final.
+__device__ __forceinline__ void publish(const PScan& S, uint32_t n, int lane) {
+  if (!S.progress) return;
+  __syncwarp();                                   // the lanes' stores happen before lane 0's release (cumulative)
+  if (lane == 0) st_release_u32(S.progress, n);
+#ifdef JPROG_TRACE
+  if (lane == 0 && (n <= 16 || (n & 8191) == 0)) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    printf("  publish %u at %llu us (word %p)\n", n, t / 1000 % 100000000ull, (void*)S.progress); }
+#endif
+}
+
 // The plain route: one thread, coefficient blocks through the cp.async ring, word-wise Reader with restart markers.
 __device__ __forceinline__ void jprog_refine_plain(const PScan& S, const SmemTables& T, int16_t (*ring)[64], int lane) {
+  uint32_t seen = 0;
+  wait_deps(S, (uint32_t)S.n_blk, seen, lane);
   auto issue = [&](int blk) {
     if (blk < S.n_blk) {
       const int16_t* src = S.coef + pscan_block(S, blk) * 64 + 2 * lane;
@@ -378,19 +424,37 @@ __device__ __forceinline__ void jprog_refine_plain(const PScan& S, const SmemTab
     __syncwarp();
     issue(blk + JPROG_STAGES);
   }
+  publish(S, (uint32_t)S.n_blk, lane);
 }
 
-// Scans of one dependency level, one CTA (one warp) each.
+// Scans decoded by one warp each: one CTA per scan.
 __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__ scans) {
   __shared__ SmemTables T;
   __shared__ __align__(16) int16_t ring[JPROG_STAGES][64];
   __shared__ __align__(16) uint8_t bytes[JPROG_RING];
+  __shared__ uint8_t zpos[64];             // positions of the block's zero-history coefficients inside the band
+#ifdef JPROG_REVERSE
+  const PScan S = scans[gridDim.x - 1 - blockIdx.x];
+#else
   const PScan S = scans[blockIdx.x];      // a private copy: the decoder's stores cannot alias it
+#endif
   build_tables(S.tab, T);
   const int lane = threadIdx.x;
+#ifdef JPROG_TRACE
+  struct Trace { int cta, mode, comp, al, ndep; unsigned smid; unsigned long long t0;
+    __device__ ~Trace() { unsigned long long t1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (threadIdx.x == 0) printf("cta %d mode %d comp %d al %d ndep %d sm %u: start %llu us, end %llu us\n", cta, mode, comp, al, ndep, smid, t0 / 1000 % 100000000ull, t1 / 1000 % 100000000ull); } } trace;
+  trace.cta = blockIdx.x; trace.mode = S.mode; trace.comp = S.comp; trace.al = S.al; trace.ndep = S.ndep;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(trace.smid));
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(trace.t0));
+#endif
   if (S.mode != PSCAN_AC_REFINE && S.mode != PSCAN_DC_REFINE) {
     // a first scan that could not join the parallel batch (a file that codes a band twice; STITCH_JPROG_SEQ)
+    uint32_t seen = 0;
+    wait_deps(S, (uint32_t)S.n_blk, seen, lane);
     if (lane == 0) pscan_sequential(S, T);
+    __syncwarp();
+    publish(S, (uint32_t)S.n_blk, lane);
     return;
   }
   if (S.ri != 0) { jprog_refine_plain(S, T, ring, lane); return; }
@@ -435,8 +499,9 @@ __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__
 
   if (S.mode == PSCAN_DC_REFINE) {
     // one bit per block, in block order: a step is 32 blocks = 4 bytes of the ring
-    uint32_t rd = 0;
+    uint32_t rd = 0, seen = 0;
     for (int g = 0; g < S.n_blk; g += 32) {
+      wait_deps(S, (uint32_t)min(S.n_blk, g + 32), seen, lane);
       ensure(rd, 64);
       const int blk = g + lane;
       const uint32_t at = rd + (lane >> 3);
@@ -448,14 +513,24 @@ __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__
       rd += 4;
       __syncwarp();
     }
+    publish(S, (uint32_t)S.n_blk, lane);
     return;
   }
 
-  auto issue = [&](int blk) {
+  uint32_t seen = 0;
+  BlockWalk ahead, cur;                    // the block being requested / the block being decoded
+  walk_start(S, 0, &ahead);
+  walk_start(S, 0, &cur);
+  auto issue = [&](int blk) {               // blocks are requested in order: `ahead` is at blk
     if (blk < S.n_blk) {
-      const int16_t* src = S.coef + pscan_block(S, blk) * 64 + 2 * lane;
-      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&ring[blk % JPROG_STAGES][2 * lane]);
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+      wait_deps(S, (uint32_t)blk + 1u, seen, lane);
+      // L2 loads (cp.async.cg, 16 bytes from 8 lanes): another SM may have written the block a moment ago
+      if (lane < 8) {
+        const int16_t* src = S.coef + walk_index(S, ahead, blk) * 64 + 8 * lane;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&ring[blk % JPROG_STAGES][8 * lane]);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+      }
+      walk_next(S, &ahead);
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
@@ -471,28 +546,31 @@ __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__
   const uint64_t band = (S.se >= 63 ? ~0ull : ((1ull << (S.se + 1)) - 1)) & ~((1ull << S.ss) - 1);
   for (int blk = 0; blk < S.n_blk; ++blk) {
     // a block takes at most 63 x (16 + 1 + 1) + 30 bits = 146 bytes, the reader holds up to 8 more
-    ensure(__shfl_sync(0xffffffffu, b.rd, 0), 256);
+    ensure(b.rd, 256);
     asm volatile("cp.async.wait_group %0;" ::"n"(JPROG_STAGES - 1) : "memory");
     __syncwarp();
     const int16_t* c = ring[blk % JPROG_STAGES];
     const int v0 = c[lane], v1 = c[lane + 32];
     const uint32_t lo = __ballot_sync(0xffffffffu, v0 != 0), hi = __ballot_sync(0xffffffffu, v1 != 0);
+    // the list of zero-history positions: every lane ranks its two coefficients with one popc each
+    const uint32_t zlo = ~lo & (uint32_t)band, zhi = ~hi & (uint32_t)(band >> 32);
+    const int nzl = __popc(zlo);
+    if ((zlo >> lane) & 1u) zpos[__popc(zlo & ((1u << lane) - 1u))] = (uint8_t)lane;
+    if ((zhi >> lane) & 1u) zpos[nzl + __popc(zhi & ((1u << lane) - 1u))] = (uint8_t)(32 + lane);
+    __syncwarp();
+    // EVERY lane parses (the same bits, the same tables: shared-memory broadcasts): in SIMT that costs what one lane
+    // costs, the warp never splits, and every lane ends up holding the results
     RefineOut o;
-    o.corrmask = o.corrbits = o.newmask = o.negmask = 0;
-    if (lane == 0) {
-      b.wr = wr;
-      pj_refine_parse(b, T, tac, (uint64_t)lo | (uint64_t)hi << 32, band, &eobrun, &o);
-    }
-    o.corrmask = __shfl_sync(0xffffffffu, o.corrmask, 0);
-    o.corrbits = __shfl_sync(0xffffffffu, o.corrbits, 0);
-    o.newmask = __shfl_sync(0xffffffffu, o.newmask, 0);
-    o.negmask = __shfl_sync(0xffffffffu, o.negmask, 0);
+    b.wr = wr;
+    pj_refine_parse_z(b, T, tac, (uint64_t)lo | (uint64_t)hi << 32, band, zpos, nzl + __popc(zhi), S.ss, S.se, &eobrun, &o);
     if (o.corrmask | o.newmask) {
-      int16_t* dst = S.coef + pscan_block(S, blk) * 64;
+      int16_t* dst = S.coef + walk_index(S, cur, blk) * 64;
       const int n0 = pj_refine_apply(v0, lane, p1, o), n1 = pj_refine_apply(v1, lane + 32, p1, o);
       if (n0 != v0) dst[lane] = (int16_t)n0;
       if (n1 != v1) dst[lane + 32] = (int16_t)n1;
     }
+    walk_next(S, &cur);
+    if ((blk & 31) == 31 || blk == S.n_blk - 1) publish(S, (uint32_t)blk + 1u, lane);
     __syncwarp();
     issue(blk + JPROG_STAGES);
   }

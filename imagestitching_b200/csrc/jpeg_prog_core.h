@@ -44,6 +44,11 @@ struct PScan {
   int32_t ss, se, al, ri;
   int32_t bpm;                // blocks per MCU of THIS scan
   int32_t hs, vs, mcux, img_bpm, ncomp, bw;   // image geometry; bw = block columns of a single-component scan
+  // scans decoded by one warp each, all in ONE launch (jprog_seq_kernel): block i may be touched once every scan
+  // listed in dep[] -- earlier scans of the same blocks in the same order -- has published progress > i
+  uint32_t* progress;         // blocks of this scan that are final (device word, zeroed before the launch)
+  const uint32_t* dep[4];
+  int32_t ndep;
 };
 
 // Scan-order block index -> block index in the coefficient buffer.
@@ -59,6 +64,26 @@ PJ_HD int64_t pscan_block(const PScan& S, int blk) {
     b = S.hs * S.vs + S.comp - 1;
   }
   return (int64_t)m * S.img_bpm + b;
+}
+
+// The same map for a walk over consecutive blocks: no divisions (luma sampling factors are 1 or 2).
+struct BlockWalk {
+  int bx, by;
+};
+PJ_HD void walk_start(const PScan& S, int blk, BlockWalk* w) {
+  w->bx = blk % S.bw;
+  w->by = blk / S.bw;
+}
+PJ_HD int64_t walk_index(const PScan& S, const BlockWalk& w, int blk) {
+  if (S.ns > 1 || S.ncomp == 1) return blk;
+  if (S.comp == 0) {
+    const int sx = S.hs - 1, sy = S.vs - 1;     // shift and mask at once: factors are 1 or 2
+    return (int64_t)((w.by >> sy) * S.mcux + (w.bx >> sx)) * S.img_bpm + ((w.by & sy) << sx) + (w.bx & sx);
+  }
+  return (int64_t)(w.by * S.mcux + w.bx) * S.img_bpm + S.hs * S.vs + S.comp - 1;
+}
+PJ_HD void walk_next(const PScan& S, BlockWalk* w) {
+  if (++w->bx == S.bw) { w->bx = 0; ++w->by; }
 }
 
 // Geometry and parameters of scan `ps` of file `H` (pointers are left to the caller).
@@ -259,6 +284,62 @@ PJ_HD void pj_refine_parse(BR& b, const SmemTables& T, int tac, uint64_t nz, uin
     pj_refine_take(b, nz & from, o);
     --*eobrun;
   }
+}
+
+// The same parse with the positions of the band's zero-history coefficients listed (zpos[0 .. nz0), ascending -- on
+// the GPU the lanes write that list, one popc each): a run then costs one table read instead of a bit loop, and the
+// number of correction bits in front of the stop is (stop - k - r), no mask needed.  This is the form the warp kernel
+// runs; ~65 instructions per symbol on the parsing thread instead of ~115.
+template <class BR>
+PJ_HD void pj_refine_parse_z(BR& b, const SmemTables& T, int tac, uint64_t nz, uint64_t band, const uint8_t* zpos, int nz0,
+                             int ss, int se, uint32_t* eobrun, RefineOut* o) {
+  uint64_t corrbits = 0, newmask = 0, negmask = 0;
+  int k = ss, zi = 0;
+  auto take = [&](int n) {
+    if (n > 32) {
+      corrbits = (corrbits << 32) | (uint32_t)br_bits(b, 32);
+      n -= 32;
+    }
+    if (n > 0) corrbits = (corrbits << n) | (uint32_t)br_bits(b, n);
+  };
+  if (*eobrun == 0) {
+    while (k <= se) {
+      const int rs = br_sym(T, tac, b);
+      const int r = rs >> 4, s = rs & 15;
+      bool neg = false;
+      if (s) {
+        neg = br_bits(b, 1) == 0;
+      } else if (r != 15) {
+        *eobrun = 1u << r;
+        if (r) *eobrun += (uint32_t)br_bits(b, r);
+        break;
+      }
+      const int t = zi + r;                        // index of the zero-history coefficient the run stops at
+      if (t < nz0) {
+        const int stop = zpos[t];
+        take(stop - k - r);
+        if (s) {
+          newmask |= 1ull << stop;
+          if (neg) negmask |= 1ull << stop;
+        }
+        zi = t + 1;
+        k = stop + 1;
+      } else {                                     // fewer zeros left than the run asks for: to the end of the band
+        take((se + 1 - k) - (nz0 - zi));
+        zi = nz0;
+        k = se + 1;
+      }
+    }
+  }
+  if (*eobrun > 0) {
+    if (k <= se) take((se + 1 - k) - (nz0 - zi));
+    k = se + 1;
+    --*eobrun;
+  }
+  o->corrbits = corrbits;
+  o->newmask = newmask;
+  o->negmask = negmask;
+  o->corrmask = nz & band & (k > 63 ? ~0ull : ((1ull << k) - 1));   // every non-zero coefficient in front of k was passed
 }
 
 // Coefficient k of the block after the scan (v = its value before).

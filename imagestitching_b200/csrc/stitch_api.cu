@@ -376,7 +376,8 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
   const char* seq_env = std::getenv("STITCH_JPROG_SEQ");
   const bool all_seq = seq_env && seq_env[0] == '1';
   auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-  struct ScanRef { int img, scan, level; bool par; size_t data, state, prefix, consumed, dcdiff; jd::PScan ps; };
+  struct ScanRef { int img, scan, level; bool par; size_t data, state, prefix, consumed, dcdiff; jd::PScan ps;
+                   int deps[4]; int ndeps; bool deps_ok; };
   struct ImgCarve { size_t tabs, qtab, coef, plane[3]; };
   std::vector<ScanRef> refs;
   ImgCarve cv[JDEC_MAX_IMAGES];
@@ -415,10 +416,21 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
       r.img = i;
       r.scan = (int)k;
       r.level = 0;
+      r.ndeps = 0;
+      r.deps_ok = true;
       for (size_t j = 0; j < k; ++j) {
         const jd::ProgScan& q = H.scans[j];
         const bool shares = ps.ns > 1 || q.ns > 1 || ps.comp == q.comp;
-        if (shares && ps.ss <= q.se && q.ss <= ps.se) r.level = std::max(r.level, refs[first_ref + j].level + 1);
+        if (shares && ps.ss <= q.se && q.ss <= ps.se) {
+          r.level = std::max(r.level, refs[first_ref + j].level + 1);
+          // a predecessor that is itself a one-warp scan (those of the parallel batch are finished before that launch):
+          // chained through a progress word when both walk the same blocks in the same order
+          if (!refs[first_ref + j].par) {
+            const bool same_order = ps.ns == q.ns && (ps.ns > 1 || ps.comp == q.comp);
+            if (!same_order || r.ndeps == 4) r.deps_ok = false;
+            else r.deps[r.ndeps++] = (int)(first_ref + j);
+          }
+        }
       }
       r.par = !all_seq && ps.ah == 0 && r.level == 0;
       jd::pscan_describe(H, ps, &r.ps);
@@ -451,6 +463,14 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
   level_off[max_level + 1] = (int)order.size();
   const size_t recs = need;
   need += up(order.size() * sizeof(jd::PScan));
+  const size_t prog_words = need;
+  need += up(refs.size() * 4);
+  // One launch for all one-warp scans when every dependency among them is between scans of the same block order (they
+  // are then chained through progress words); STITCH_JPROG_LEVELS=1 keeps a launch per dependency level.
+  const char* lv_env = std::getenv("STITCH_JPROG_LEVELS");
+  bool one_launch = !(lv_env && lv_env[0] == '1') && (int)order.size() - n_par <= 128;
+  for (const ScanRef& r : refs)
+    if (!r.par && !r.deps_ok) one_launch = false;
   if (ln.prog_arena_cap < need) {
     if (ln.prog_arena) {
       CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
@@ -493,8 +513,15 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
       r.ps.dcdiff = r.dcdiff ? (int32_t*)(A + r.dcdiff) : nullptr;
     }
     if (ps.len) CUDA_TRY(ctx, cudaMemcpyAsync(A + r.data, items[r.img].file + ps.off, ps.len, cudaMemcpyHostToDevice, ln.stream));
+    r.ps.progress = nullptr;
+    r.ps.ndep = 0;
+    if (!r.par && one_launch) {
+      r.ps.progress = (uint32_t*)(A + prog_words) + order[k];
+      for (int d = 0; d < r.ndeps; ++d) r.ps.dep[r.ps.ndep++] = (const uint32_t*)(A + prog_words) + r.deps[d];
+    }
     host_recs[k] = r.ps;
   }
+  if (one_launch) CUDA_TRY(ctx, cudaMemsetAsync(A + prog_words, 0, refs.size() * 4, ln.stream));
   jd::PScan* d_recs = (jd::PScan*)(A + recs);
   if (!host_recs.empty())
     CUDA_TRY(ctx, cudaMemcpyAsync(d_recs, host_recs.data(), host_recs.size() * sizeof(jd::PScan), cudaMemcpyHostToDevice, ln.stream));
@@ -540,11 +567,26 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
     jd::jprog_dc_kernel<<<dim3(n_par, 3), 1024, 0, ln.stream>>>(d_recs);
     launches += 3;
   }
-  for (int lv = 0; lv <= max_level; ++lv) {
-    const int cnt = level_off[lv + 1] - level_off[lv];
-    if (cnt <= 0) continue;
-    jd::jprog_seq_kernel<<<cnt, 32, 0, ln.stream>>>(d_recs + level_off[lv]);
-    ++launches;
+  if (one_launch) {
+    const int cnt = (int)order.size() - n_par;       // sorted by level: producers get the lower CTA indices
+    if (cnt > 0) {
+      // EXPERIMENT: STITCH_JPROG_SPREAD=1 asks for 120 KB of dynamic shared memory per CTA, so that no two scans share an SM
+      static const bool spread = [] { const char* e = std::getenv("STITCH_JPROG_SPREAD"); return e && e[0] == '1'; }();
+      size_t dyn = 0;
+      if (spread) {
+        dyn = 120 * 1024;
+        cudaFuncSetAttribute(jd::jprog_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+      }
+      jd::jprog_seq_kernel<<<cnt, 32, dyn, ln.stream>>>(d_recs + n_par);
+      ++launches;
+    }
+  } else {
+    for (int lv = 0; lv <= max_level; ++lv) {
+      const int cnt = level_off[lv + 1] - level_off[lv];
+      if (cnt <= 0) continue;
+      jd::jprog_seq_kernel<<<cnt, 32, 0, ln.stream>>>(d_recs + level_off[lv]);
+      ++launches;
+    }
   }
   jd::jdec_idct_kernel<<<dim3((max_blocks + 127) / 128, n), 128, 0, ln.stream>>>(B);
   jd::jdec_colour_kernel<<<dim3((max_w + 127) / 128, (max_h + 7) / 8, n), 256, 0, ln.stream>>>(B);

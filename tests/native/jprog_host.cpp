@@ -24,6 +24,8 @@ extern "C" int jprog_host_info(const uint8_t* file, size_t n, int32_t* info) {
 
 // coef: [blocks][64] int16, buffer order (interleaved MCU order, zig-zag inside a block), zeroed here.
 // scan_desc (optional): per scan {mode, ns, comp, ss, se, ah, al, n_blk}.
+static int g_by_mask = 0;   // 0: coefficient by coefficient, 1: pj_refine_parse, 2: pj_refine_parse_z
+
 // AC / DC refinement scans the way the GPU's warp kernel runs them (jprog_seq_kernel): block by block through
 // pj_refine_parse (one thread) + pj_refine_apply (every coefficient) with the block's non-zero mask.
 static void refine_by_mask(const PScan& S, const SmemTables& T) {
@@ -48,15 +50,22 @@ static void refine_by_mask(const PScan& S, const SmemTables& T) {
       for (int k = 0; k < 64; ++k) nz |= (uint64_t)(c[k] != 0) << k;
       const uint64_t band = (S.se >= 63 ? ~0ull : ((1ull << (S.se + 1)) - 1)) & ~((1ull << S.ss) - 1);
       RefineOut o;
-      pj_refine_parse(b, T, 2 + S.ta, nz, band, &eobrun, &o);
+      if (g_by_mask == 2) {
+        uint8_t zpos[64];
+        int nz0 = 0;
+        for (int k = S.ss; k <= S.se; ++k)
+          if (!((nz >> k) & 1)) zpos[nz0++] = (uint8_t)k;
+        pj_refine_parse_z(b, T, 2 + S.ta, nz, band, zpos, nz0, S.ss, S.se, &eobrun, &o);
+      } else {
+        pj_refine_parse(b, T, 2 + S.ta, nz, band, &eobrun, &o);
+      }
       for (int k = 0; k < 64; ++k) c[k] = (int16_t)pj_refine_apply(c[k], k, p1, o);      // on the GPU: two per lane
     }
     b_in_mcu = (b_in_mcu + 1 == S.bpm) ? 0 : b_in_mcu + 1;
   }
 }
 
-static bool g_by_mask = false;
-extern "C" void jprog_host_set_mask_path(int on) { g_by_mask = on != 0; }
+extern "C" void jprog_host_set_mask_path(int on) { g_by_mask = on; }
 
 extern "C" int jprog_host_decode(const uint8_t* file, size_t n, int16_t* coef, int32_t* scan_desc) {
   Header H;
@@ -83,6 +92,24 @@ extern "C" int jprog_host_decode(const uint8_t* file, size_t n, int16_t* coef, i
     if (scan_desc) {
       int32_t* d = scan_desc + 8 * i;
       d[0] = S.mode; d[1] = S.ns; d[2] = S.comp; d[3] = S.ss; d[4] = S.se; d[5] = ps.ah; d[6] = S.al; d[7] = S.n_blk;
+    }
+  }
+  return 0;
+}
+
+// walk_index (the division-free block map of the warp kernel) against pscan_block, every block of every scan.
+extern "C" int jprog_host_walk_check(const uint8_t* file, size_t n) {
+  Header H;
+  if (parse(file, n, &H) != kOk || !H.progressive) return -1;
+  for (const ProgScan& ps : H.scans) {
+    PScan S;
+    std::memset(&S, 0, sizeof S);
+    pscan_describe(H, ps, &S);
+    BlockWalk w;
+    walk_start(S, 0, &w);
+    for (int blk = 0; blk < S.n_blk; ++blk) {
+      if (walk_index(S, w, blk) != pscan_block(S, blk)) return blk + 1;
+      walk_next(S, &w);
     }
   }
   return 0;

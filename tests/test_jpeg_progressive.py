@@ -94,6 +94,14 @@ def test_sequential_scan_decoder_equals_oracle_coefficients():
         assert np.array_equal(coef, _buffer_order(J.coefficients(data), 1, 1))
 
 
+def test_block_walk_equals_block_map():
+    lib = _host_lib()
+    for size in SIZES + [(333, 211)]:
+        for kw in ({"subsampling": 0}, {"subsampling": 1}, {"subsampling": 2}, {"gray": True}):
+            data = _jpeg(*size, quality=80, progressive=True, **kw)
+            assert lib.jprog_host_walk_check(data, len(data)) == 0, (size, kw)
+
+
 def test_parser_lists_the_scans_of_libjpegs_script():
     """jpeg_simple_progression for YCbCr: DC (all components, Al 1), Y 1-5 Al 2, Cr 1-63 Al 1, Cb 1-63 Al 1, Y 6-63 Al 2,
     Y 1-63 refine to 1, DC refine, Cr / Cb refine, Y refine to 0."""
@@ -132,7 +140,7 @@ def test_oracle_and_scan_decoder_on_other_scripts():
     for label, base, f in _script_files():
         assert np.array_equal(_pil(f), _pil(base)), label
         assert np.array_equal(J.decode(f)[..., :3], _pil(f)), label
-        for by_mask in (0, 1):
+        for by_mask in (0, 1, 2):
             lib.jprog_host_set_mask_path(by_mask)
             coef, info, _ = _host_coefficients(lib, f)
             assert np.array_equal(coef, _buffer_order(J.coefficients(f), int(info[3]), int(info[4]))), (label, by_mask)
@@ -142,17 +150,19 @@ def test_oracle_and_scan_decoder_on_other_scripts():
 
 
 def test_mask_path_of_the_scan_decoder_equals_oracle_coefficients():
-    """pj_refine_parse + pj_refine_apply (what the warp kernel runs) on PIL's files."""
+    """pj_refine_parse / pj_refine_parse_z + pj_refine_apply (what the warp kernels run) on PIL's files."""
     lib = _host_lib()
     lib.jprog_host_set_mask_path.argtypes = [ctypes.c_int]
-    lib.jprog_host_set_mask_path(1)
     try:
         for size in SIZES + [(800, 600)]:
             for ss in (0, 1, 2):
                 for q, kw in ((20, {}), (90, {"restart_marker_blocks": 3}), (100, {})):
                     data = _jpeg(*size, seed=q, quality=q, subsampling=ss, progressive=True, **kw)
-                    coef, info, _ = _host_coefficients(lib, data)
-                    assert np.array_equal(coef, _buffer_order(J.coefficients(data), int(info[3]), int(info[4]))), (size, ss, q)
+                    want = _buffer_order(J.coefficients(data), 2 if ss else 1, 2 if ss == 2 else 1)
+                    for path in (1, 2):
+                        lib.jprog_host_set_mask_path(path)
+                        coef, info, _ = _host_coefficients(lib, data)
+                        assert np.array_equal(coef, want), (size, ss, q, path)
     finally:
         lib.jprog_host_set_mask_path(0)
 
@@ -196,6 +206,24 @@ def test_gpu_progressive_equals_oracle(spec, seq, monkeypatch):
     ctx.close()
     assert got.shape == want.shape
     assert np.array_equal(got, want), f"{np.count_nonzero(got != want)} bytes differ"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seq", [0, 1])
+def test_gpu_progressive_launch_per_level(seq, monkeypatch):
+    """STITCH_JPROG_LEVELS=1: the one-warp scans in a launch per dependency level instead of one launch chained through
+    progress words (the form a file with order-incompatible dependencies falls back to)."""
+    from imagestitching_b200 import StitchContext
+    monkeypatch.setenv("STITCH_JPROG_LEVELS", "1")
+    monkeypatch.setenv("STITCH_JPROG_SEQ", str(seq))
+    ctx = StitchContext(0)
+    for spec in (GPU_FILES[2], GPU_FILES[6], GPU_FILES[8], GPU_FILES[10]):
+        spec = dict(spec)
+        data = _jpeg(spec.pop("w"), spec.pop("h"), seed=3, progressive=True, **spec)
+        assert np.array_equal(ctx.decode_jpeg(data), J.decode(data)), spec
+    for label, _, f in _script_files(sizes=((123, 77),), restarts=(0, 7)):
+        assert np.array_equal(ctx.decode_jpeg(f), J.decode(f)), label
+    ctx.close()
 
 
 @pytest.mark.gpu
