@@ -281,7 +281,7 @@ class StitchContext:
         return out
 
     def decode_jpeg(self, file_bytes: bytes) -> np.ndarray:
-        """loadImageFrom (utils/canvas.js:27-121) for a baseline JPEG file: RGBA8 [h, w, 4], decoded on the GPU."""
+        """loadImageFrom (utils/canvas.js:27-121) for a JPEG file (baseline or progressive): RGBA8 [h, w, 4], decoded on the GPU."""
         info = get_image_info(file_bytes)
         out = np.empty((info["height"], info["width"], 4), dtype=np.uint8)
         buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")

@@ -223,12 +223,14 @@ const char* stitch_type_name(int32_t type);
 int stitch_prepare_record(const StitchImageInfo* info, int64_t file_size, StitchImageDesc* out);
 
 /* ---- decode (loadImageFrom, U:27-121; P:1441-1520) ----
- * Decodes one baseline JPEG file on the GPU into RGBA8 (alpha 255, EXIF orientation NOT applied -- the page
- * hands the un-rotated bitmap to drawWithOrientation).  Huffman sequential DCT, 8 bit, gray or YCbCr with
- * 4:4:4 / 4:2:2 / 4:2:0 sampling, restart markers; integer IDCT, triangle-filter chroma upsampling and
- * fixed-point colour conversion as in libjpeg's default pipeline.  Other variants (progressive, arithmetic,
- * CMYK) return STITCH_E_BAD_IMAGE: the page's answer to an undecodable file (P:1508-1513); there is no CPU
- * fallback.  out_pitch 0 = packed.  `info` (optional) receives the probe result.  Synchronous. */
+ * Decodes one JPEG file on the GPU into RGBA8 (alpha 255, EXIF orientation NOT applied -- the page hands the
+ * un-rotated bitmap to drawWithOrientation).  Huffman-coded sequential (SOF0 / SOF1) and progressive (SOF2: any
+ * script of interleaved DC scans and single-component scans) DCT, 8 bit, gray or YCbCr with 4:4:4 / 4:2:2 / 4:2:0
+ * sampling, restart markers; integer IDCT, triangle-filter chroma upsampling and fixed-point colour conversion as
+ * in libjpeg's default pipeline.  A progressive file's refinement scans are decoded by one warp each (a 12 MP
+ * file takes 0.3 - 0.7 s against 3 ms for a baseline one).  Other variants (arithmetic coding, lossless, CMYK)
+ * return STITCH_E_BAD_IMAGE: the page's answer to an undecodable file (P:1508-1513); there is no CPU fallback.
+ * out_pitch 0 = packed.  `info` (optional) receives the probe result.  Synchronous. */
 int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
                        int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
 
