@@ -89,6 +89,7 @@ struct Img {
   uint32_t key[3];
   uint8_t* rgba;
   int64_t pitch;
+  int32_t ox, oy, sx, sy;   // where pixel (x, y) of this (pass of an) image lands: (ox + x sx, oy + y sy); 0, 0, 1, 1 when not interlaced
 };
 struct Batch {
   Img img[kMaxImages];
@@ -900,7 +901,7 @@ __global__ void __launch_bounds__(256) png_rgba_kernel(Batch B) {
         break;
     }
   }
-  *reinterpret_cast<uint32_t*>(I.rgba + (size_t)y * I.pitch + (size_t)x * 4) = r | (g << 8) | (b << 16) | (a << 24);
+  *reinterpret_cast<uint32_t*>(I.rgba + (size_t)(I.oy + y * I.sy) * I.pitch + (size_t)(I.ox + x * I.sx) * 4) = r | (g << 8) | (b << 16) | (a << 24);
 }
 
 // ---- host ----
@@ -952,6 +953,8 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
     for (int c = 0; c < 3; ++c) I.key[c] = H.key[c];
     I.rgba = items[i].rgba;
     I.pitch = items[i].pitch;
+    I.ox = I.oy = 0;
+    I.sx = I.sy = 1;
     Carve& c = cv[i];
     c.ctr = need; need += 256;
     c.hkey = need; need += up((size_t)hs * 4);
@@ -1048,10 +1051,53 @@ cudaError_t decode_batch(Arena& arena, const DecodeItem* items, int n, cudaStrea
     ++nl;
   }
   pinf_bytes_kernel<<<g4, 256, 0, stream>>>(B);
-  png_transpose_kernel<<<dim3((max_chunks * 4 + 255) / 256, max_h, n), 256, 0, stream>>>(B);
-  png_unfilter_kernel<<<dim3(kUnfCtas, n), 32 * kUnfWarps, 0, stream>>>(B);   // 216 small CTAs at most: all resident, so the waits are safe
-  png_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, stream>>>(B);
-  nl += 4;
+  ++nl;
+  bool any_laced = false;
+  for (int i = 0; i < n; ++i) any_laced = any_laced || items[i].hdr.interlace != 0;
+  if (!any_laced) {
+    png_transpose_kernel<<<dim3((max_chunks * 4 + 255) / 256, max_h, n), 256, 0, stream>>>(B);
+    png_unfilter_kernel<<<dim3(kUnfCtas, n), 32 * kUnfWarps, 0, stream>>>(B);   // 216 small CTAs at most: all resident, so the waits are safe
+    png_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, stream>>>(B);
+    nl += 3;
+  } else {
+    // Adam7 files: every pass is a small image of its own in the inflated stream -- its own rows, filtered on its own
+    // (ISO 15948 8.2) -- so the three kernels run once per pass over a batch whose records describe that pass (plain
+    // files of the batch take part in the first round only), and the conversion scatters the pixels to their places.
+    AdamPass ps[kMaxImages][7];
+    int np[kMaxImages];
+    int rounds = 1;
+    for (int i = 0; i < n; ++i) {
+      const Header& H = items[i].hdr;
+      np[i] = H.interlace ? adam7_passes(H.w, H.h, H.channels * H.depth, ps[i]) : 1;
+      rounds = std::max(rounds, np[i]);
+    }
+    size_t raw_off[kMaxImages] = {};
+    for (int r = 0; r < rounds; ++r) {
+      Batch P = B;
+      for (int i = 0; i < n; ++i) {
+        Img& I = P.img[i];
+        if (r >= np[i]) { I.w = 0; I.h = 0; continue; }
+        if (!items[i].hdr.interlace) continue;
+        const AdamPass& a = ps[i][r];
+        I.raw = B.img[i].raw + raw_off[i];
+        raw_off[i] += ((size_t)a.row_bytes + 1) * (size_t)a.h;
+        I.w = a.w; I.h = a.h;
+        I.row_bytes = a.row_bytes;
+        I.t_chunks = (a.row_bytes + 15) / 16;
+        I.ox = a.x0; I.oy = a.y0; I.sx = a.dx; I.sy = a.dy;
+      }
+      if (r > 0)   // the unfilter kernel's row-group tickets and progress words start from zero
+        for (int i = 0; i < n; ++i) {
+          if (r >= np[i]) continue;
+          PNG_TRY(cudaMemsetAsync(B.img[i].ctr + 8, 0, 4, stream));
+          PNG_TRY(cudaMemsetAsync(B.img[i].progress, 0, (size_t)((items[i].hdr.h + 31) / 32) * 4, stream));
+        }
+      png_transpose_kernel<<<dim3((max_chunks * 4 + 255) / 256, max_h, n), 256, 0, stream>>>(P);
+      png_unfilter_kernel<<<dim3(kUnfCtas, n), 32 * kUnfWarps, 0, stream>>>(P);
+      png_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, stream>>>(P);
+      nl += 3;
+    }
+  }
   PNG_TRY(cudaGetLastError());
   if (status_host) PNG_TRY(cudaMemcpyAsync(status_host, B.status, 4, cudaMemcpyDeviceToHost, stream));
   static const bool debug = [] { const char* e = std::getenv("STITCH_PNG_DEBUG"); return e && e[0] == '1'; }();

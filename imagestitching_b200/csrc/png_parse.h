@@ -54,6 +54,23 @@ inline uint32_t crc32_update(uint32_t c, const uint8_t* p, size_t n) {
   return c;
 }
 
+// Adam7 (ISO 15948 clause 8.2): pass p holds the pixels (x0 + i dx, y0 + j dy).  Fills ps[] with the passes that hold
+// pixels, in stream order; returns their number.
+struct AdamPass {
+  int32_t x0, y0, dx, dy, w, h;
+  uint32_t row_bytes;
+};
+inline int adam7_passes(int32_t w, int32_t h, int bits, AdamPass* ps) {
+  static const int8_t t[7][4] = {{0, 0, 8, 8}, {4, 0, 8, 8}, {0, 4, 4, 8}, {2, 0, 4, 4}, {0, 2, 2, 4}, {1, 0, 2, 2}, {0, 1, 1, 2}};
+  int n = 0;
+  for (int p = 0; p < 7; ++p) {
+    const int64_t pw = ((int64_t)w - t[p][0] + t[p][2] - 1) / t[p][2], ph = ((int64_t)h - t[p][1] + t[p][3] - 1) / t[p][3];
+    if (pw <= 0 || ph <= 0) continue;
+    ps[n++] = AdamPass{t[p][0], t[p][1], t[p][2], t[p][3], (int32_t)pw, (int32_t)ph, (uint32_t)((pw * bits + 7) / 8)};
+  }
+  return n;
+}
+
 inline ParseStatus parse(const uint8_t* f, size_t n, Header* H) {
   static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', '\r', '\n', 0x1A, '\n'};
   if (n < 8 || std::memcmp(f, sig, 8) != 0) return kNotPng;
@@ -158,7 +175,12 @@ inline ParseStatus parse(const uint8_t* f, size_t n, Header* H) {
       for (uint32_t k = 0; k < pc.len && got < 2; ++k) zh[got++] = f[pc.file_off + k];
     if ((zh[0] & 0x0F) != 8 || (zh[0] >> 4) > 7 || ((zh[0] << 8) | zh[1]) % 31 != 0 || (zh[1] & 0x20)) return kCorrupt;
   }
-  if (H->interlace) return kUnsupported;
+  if (H->interlace) {   // Adam7: the stream holds the passes one after the other, each with its own (shorter) rows
+    AdamPass ps[7];
+    const int np = adam7_passes(H->w, H->h, H->channels * H->depth, ps);
+    H->raw_len = 0;
+    for (int k = 0; k < np; ++k) H->raw_len += ((uint64_t)ps[k].row_bytes + 1) * (uint64_t)ps[k].h;
+  }
   if (H->raw_len >= ((uint64_t)1 << 31)) return kUnsupported;
   return kOk;
 }

@@ -628,7 +628,7 @@ int parse_png(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::p
   if (ps == stitch::pngdec::kOk) return STITCH_OK;
   char buf[128];
   std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
-                ps == stitch::pngdec::kUnsupported ? "PNG variant not supported: interlaced, or larger than 2 GiB inflated"
+                ps == stitch::pngdec::kUnsupported ? "PNG variant not supported: larger than 2 GiB inflated"
                 : ps == stitch::pngdec::kNotPng ? "not a PNG file" : "corrupt PNG chunks");
   return fail(ctx, STITCH_E_BAD_IMAGE, buf);
 }

@@ -124,7 +124,7 @@ int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 
 /* STITCH_MEM_HOST_JPEG: `data` is a baseline JPEG FILE in host memory and pitch_bytes its length in bytes; the
  * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
-/* STITCH_MEM_HOST_PNG: the same for a PNG FILE (non-interlaced; gray / RGB / palette / alpha, 1-16 bit, tRNS). */
+/* STITCH_MEM_HOST_PNG: the same for a PNG FILE (plain or Adam7-interlaced; gray / RGB / palette / alpha, 1-16 bit, tRNS). */
 typedef enum StitchMemKind {
   STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2, STITCH_MEM_HOST_PNG = 3
 } StitchMemKind;
@@ -239,7 +239,8 @@ int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes, void* out
  * and the matches that reach back across a block boundary are resolved by pointer jumping (png_decode.cu) -- then
  * unfiltered as a wavefront over rows and converted to RGBA8 with straight alpha: gray / RGB / palette / gray+alpha
  * / RGBA at 1-16 bit, tRNS (palette alpha or colour key) applied, 16-bit samples reduced to their high byte, gAMA /
- * iCCP ignored -- what PIL's Image.convert("RGBA") returns.  Interlaced (Adam7) files, files that inflate to
+ * iCCP ignored -- what PIL's Image.convert("RGBA") returns.  Adam7-interlaced files take the unfilter and
+ * conversion kernels once per pass.  Files that inflate to
  * >= 2 GiB and damaged files return STITCH_E_BAD_IMAGE (P:1508-1513); critical-chunk CRCs are checked, IDAT CRCs and
  * the Adler-32 are not.  There is no CPU fallback.  Synchronous. */
 int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,

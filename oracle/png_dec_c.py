@@ -76,11 +76,25 @@ def inflate(z: bytes, out_len: int) -> np.ndarray:
     return out
 
 
+# Adam7 (ISO 15948 clause 8.2): pass -> (x0, y0, dx, dy); a pass holds the pixels (x0 + i dx, y0 + j dy)
+ADAM7 = ((0, 0, 8, 8), (4, 0, 8, 8), (0, 4, 4, 8), (2, 0, 4, 4), (0, 2, 2, 4), (1, 0, 2, 2), (0, 1, 1, 2))
+
+
+def adam7_passes(w: int, h: int, bits: int):
+    """(x0, y0, dx, dy, pass width, pass height, row bytes) of the passes that hold pixels, in stream order."""
+    out = []
+    for x0, y0, dx, dy in ADAM7:
+        pw, ph = (w - x0 + dx - 1) // dx, (h - y0 + dy - 1) // dy
+        if pw > 0 and ph > 0:
+            out.append((x0, y0, dx, dy, pw, ph, (pw * bits + 7) // 8))
+    return out
+
+
 def decode(data: bytes, use_zlib: bool = False) -> np.ndarray:
     """RGBA8 [h, w, 4], straight alpha.  use_zlib=True swaps the oracle's inflater for Python's zlib (the pin)."""
     H = header(data)
-    if H["interlace"]:
-        raise PngError("interlaced")
+    if H["interlace"] > 1:
+        raise PngError("unknown interlace method")
     palette = np.zeros((256, 4), np.uint8)
     palette[:, 3] = 255
     key = np.zeros(3, np.uint16)
@@ -100,7 +114,9 @@ def decode(data: bytes, use_zlib: bool = False) -> np.ndarray:
         elif typ == b"IDAT":
             idat.append(body)
     z = b"".join(idat)
-    raw_len = (H["row_bytes"] + 1) * H["h"]
+    bits = CHANNELS[H["ctype"]] * H["depth"]
+    passes = adam7_passes(H["w"], H["h"], bits) if H["interlace"] else [(0, 0, 1, 1, H["w"], H["h"], H["row_bytes"])]
+    raw_len = sum((rb + 1) * ph for *_, ph, rb in passes)
     if use_zlib:
         raw = np.frombuffer(zlib.decompress(z), np.uint8).copy()
         if raw.size != raw_len:
@@ -108,9 +124,15 @@ def decode(data: bytes, use_zlib: bool = False) -> np.ndarray:
     else:
         raw = inflate(z, raw_len)
     lib = _lib()
-    if lib.png_dec_ref_unfilter(raw.ctypes.data, H["h"], H["row_bytes"], H["bpp"]):
-        raise PngError("bad filter type")
     out = np.empty((H["h"], H["w"], 4), np.uint8)
-    lib.png_dec_ref_to_rgba(raw.ctypes.data, H["w"], H["h"], H["row_bytes"], H["depth"], H["ctype"], palette.ctypes.data, has_key,
-                            key.ctypes.data, out.ctypes.data)
+    off = 0
+    for x0, y0, dx, dy, pw, ph, rb in passes:        # every pass is a small image of its own: filtered and unfiltered alone
+        part = raw[off:off + (rb + 1) * ph]
+        off += (rb + 1) * ph
+        if lib.png_dec_ref_unfilter(part.ctypes.data, ph, rb, H["bpp"]):
+            raise PngError("bad filter type")
+        px = np.empty((ph, pw, 4), np.uint8)
+        lib.png_dec_ref_to_rgba(part.ctypes.data, pw, ph, rb, H["depth"], H["ctype"], palette.ctypes.data, has_key,
+                                key.ctypes.data, px.ctypes.data)
+        out[y0::dy, x0::dx] = px
     return out

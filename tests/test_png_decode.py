@@ -99,6 +99,71 @@ def _raw_png(w, h, depth, ctype, rows, filters=None, extra=(), level=6, idat_spl
     return body + _chunk(b"IEND", b"")
 
 
+def _adam7_png(w, h, depth, ctype, rows, extra=(), level=6):
+    """The interlaced (Adam7) form of the picture whose packed rows are `rows`: the pixels of every pass re-packed into
+    that pass's own rows, each pass filtered on its own (filter types in turn), one zlib stream."""
+    bits = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype] * depth
+    bpp = max(1, bits // 8)
+    px = np.stack([np.unpackbits(np.frombuffer(bytes(r), np.uint8))[: w * bits].reshape(w, bits) for r in rows])   # [h, w, bits]
+    out = bytearray()
+    for x0, y0, dx, dy, pw, ph, rb in P.adam7_passes(w, h, bits):
+        sub = px[y0::dy, x0::dx].reshape(ph, pw * bits)
+        prev = np.zeros(rb, np.int32)
+        for y in range(ph):
+            cur = np.packbits(sub[y]).astype(np.int32)
+            assert cur.size == rb
+            ft = (y + x0) % 5
+            left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]]) if rb > bpp else np.zeros(rb, np.int32)
+            ul = np.concatenate([np.zeros(bpp, np.int32), prev[:-bpp]]) if rb > bpp else np.zeros(rb, np.int32)
+            if ft == 0:
+                pred = np.zeros(rb, np.int32)
+            elif ft == 1:
+                pred = left
+            elif ft == 2:
+                pred = prev
+            elif ft == 3:
+                pred = (left + prev) >> 1
+            else:
+                p = left + prev - ul
+                pa, pb, pc = abs(p - left), abs(p - prev), abs(p - ul)
+                pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, prev, ul))
+            out.append(ft)
+            out += ((cur - pred) & 0xFF).astype(np.uint8).tobytes()
+            prev = cur
+    body = b"\x89PNG\r\n\x1a\n" + _chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, ctype, 0, 0, 1))
+    for typ, data in extra:
+        body += _chunk(typ, data)
+    return body + _chunk(b"IDAT", zlib.compress(bytes(out), level)) + _chunk(b"IEND", b"")
+
+
+def _interlaced_matrix():
+    """(name, interlaced file, the same picture not interlaced) over colour types, depths and awkward sizes."""
+    rng = np.random.default_rng(17)
+    files = []
+    for (w, h) in ((67, 41), (1, 1), (3, 2), (8, 8), (9, 17), (5, 1), (1, 9)):
+        for depth, ctype in ((1, 0), (2, 0), (4, 3), (8, 0), (8, 2), (8, 3), (8, 4), (8, 6), (16, 2), (16, 6)):
+            if (w, h) != (67, 41) and (depth, ctype) not in ((1, 0), (4, 3), (8, 2), (8, 6)):
+                continue
+            ch = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+            rb = (w * ch * depth + 7) // 8
+            rows = [rng.integers(0, 256, rb, dtype=np.uint8) for _ in range(h)]
+            extra = []
+            if ctype == 3:
+                n_pal = min(1 << depth, 200)
+                if depth == 8:
+                    rows = [r % n_pal for r in rows]
+                extra = [(b"PLTE", rng.integers(0, 256, n_pal * 3, dtype=np.uint8).tobytes()),
+                         (b"tRNS", rng.integers(0, 256, max(1, n_pal // 2), dtype=np.uint8).tobytes())]
+            files.append((f"{w}x{h}_ct{ctype}_d{depth}", _adam7_png(w, h, depth, ctype, rows, extra), _raw_png(w, h, depth, ctype, rows, extra=extra)))
+    a = _picture(333, 211, 4, seed=21)
+    rows = [a[y].tobytes() for y in range(211)]
+    files.append(("photo_rgba", _adam7_png(333, 211, 8, 6, rows), _raw_png(333, 211, 8, 6, rows)))
+    s = _screenshot(390, 300)
+    rows = [s[y].tobytes() for y in range(300)]
+    files.append(("screenshot", _adam7_png(390, 300, 8, 6, rows), _raw_png(390, 300, 8, 6, rows)))
+    return files
+
+
 def _file_matrix():
     """(name, file bytes) over colour types, depths, filters, tRNS, chunking and deflate strategies."""
     rng = np.random.default_rng(7)
@@ -187,6 +252,16 @@ def test_oracle_equals_pil_and_zlib():
             assert np.array_equal(got[..., :3], want[..., :3]), name
         else:
             assert np.array_equal(got, want), name
+
+
+def test_oracle_interlaced_equals_plain_and_pil():
+    """Adam7: the interlaced file decodes to the pixels of the plain file of the same picture -- in PIL / libpng (so the
+    test's interlacer is sound) and in the oracle, whose own inflater agrees with zlib on it."""
+    for name, laced, plain in _interlaced_matrix():
+        assert np.array_equal(_pil_rgba(laced), _pil_rgba(plain)), name
+        got = P.decode(laced)
+        assert np.array_equal(got, P.decode(plain)), name
+        assert np.array_equal(got, P.decode(laced, use_zlib=True)), name
 
 
 def test_oracle_low_depth_gray_and_16_bit_values():
@@ -299,6 +374,19 @@ def test_gpu_decoder_equals_oracle_on_the_matrix(ctx):
 
 
 @pytest.mark.gpu
+def test_gpu_decoder_interlaced(ctx):
+    """Adam7 files: seven passes through transpose / unfilter / conversion, scattered into the bitmap."""
+    for name, laced, plain in _interlaced_matrix():
+        assert np.array_equal(ctx.decode_png(laced), P.decode(laced)), name
+    # a job that mixes an interlaced and a plain file
+    from tests import util as U
+    _, laced, plain = _interlaced_matrix()[-2]
+    a = ctx.run([{"file": laced}, {"file": plain}], "vertical", platform="ios")
+    b = ctx.run([{"file": plain}, {"file": plain}], "vertical", platform="ios")
+    assert np.array_equal(a.rgba, b.rgba)
+
+
+@pytest.mark.gpu
 def test_gpu_decoder_sizes_and_shapes(ctx):
     for i, (w, h) in enumerate([(1, 1), (2, 1), (1, 70), (33, 31), (32, 32), (640, 481), (1, 4000), (5000, 3), (1290, 2796)]):
         for c, mode in ((3, "RGB"), (4, "RGBA")):
@@ -354,7 +442,7 @@ def test_gpu_png_job_inputs_equal_bitmap_job(ctx):
 def test_gpu_decoder_errors(ctx):
     from imagestitching_b200 import StitchError
     good = _png(_picture(200, 120, 3, seed=4), "RGB")
-    # interlaced: stated as unsupported
+    # the interlace flag set on a stream that is not interlaced: the inflated data has the wrong length
     lace = bytearray(good)
     lace[28] = 1
     lace[29:33] = struct.pack(">I", zlib.crc32(bytes(lace[12:29])) & 0xFFFFFFFF)
