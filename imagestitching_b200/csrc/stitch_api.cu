@@ -28,6 +28,7 @@
 #include "jpeg_decode.cuh"
 #include "jpeg_prog.cuh"
 #include "png_decode.h"
+#include "bmp_decode.cuh"
 #include "png_kernels.cuh"
 #include "synth.cuh"
 
@@ -90,6 +91,8 @@ struct Lane {
   size_t dec_arena_cap = 0;
   void* prog_arena = nullptr;        // progressive files of the job (jpeg_prog.cuh): their own arena, same rules
   size_t prog_arena_cap = 0;
+  void* bmp_arena = nullptr;         // BMP files of the job (bmp_decode.cuh): device copies of the files + palettes
+  size_t bmp_arena_cap = 0;
   stitch::pngdec::Arena pngdec_arena;   // PNG-input decoder (png_decode.cu)
   bool pngdec_active = false;        // the job on this lane decodes PNG files: check INFO_PNGDEC_STATUS when it is done
   // PNG export: grow-only arena (RGBA canvas when the caller did not ask for it, code tables, coded bands, file)
@@ -204,6 +207,7 @@ void free_lane(Lane& ln) {
   if (ln.jpeg_arena) cudaFree(ln.jpeg_arena);
   if (ln.dec_arena) cudaFree(ln.dec_arena);
   if (ln.prog_arena) cudaFree(ln.prog_arena);
+  if (ln.bmp_arena) cudaFree(ln.bmp_arena);
   stitch::pngdec::free_arena(ln.pngdec_arena);
   if (ln.png_arena) cudaFree(ln.png_arena);
   if (ln.info_host) cudaFreeHost(ln.info_host);
@@ -623,6 +627,86 @@ int parse_jpeg(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::
   return fail(ctx, STITCH_E_BAD_IMAGE, buf);
 }
 
+// One BMP file to convert into a device bitmap.
+struct BmpItem {
+  const uint8_t* file;
+  size_t bytes;
+  stitch::bmpdec::Header hdr;
+  uint8_t* rgba;
+  int64_t pitch;
+};
+
+int parse_bmp(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::bmpdec::Header* H) {
+  const stitch::bmpdec::ParseStatus ps = stitch::bmpdec::parse((const uint8_t*)file, bytes, H);
+  if (ps == stitch::bmpdec::kOk) return STITCH_OK;
+  char buf[112];
+  std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
+                ps == stitch::bmpdec::kUnsupported ? "BMP variant not supported: RLE, embedded JPEG / PNG, odd bit fields"
+                : ps == stitch::bmpdec::kNotBmp ? "not a BMP file" : "corrupt BMP headers");
+  return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+}
+
+// The BMP files of a job: uploads + one kernel on the lane's stream, nothing waits.
+int decode_bmp_batch(StitchCtx* ctx, Lane& ln, BmpItem* items, int n) {
+  namespace bd = stitch::bmpdec;
+  if (n <= 0) return STITCH_OK;
+  if (n > bd::kMaxImages) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  size_t need = 0, off_file[bd::kMaxImages], off_pal[bd::kMaxImages];
+  for (int i = 0; i < n; ++i) {
+    off_file[i] = need; need += up(items[i].bytes + 16);
+    off_pal[i] = need; need += 1024;
+  }
+  if (ln.bmp_arena_cap < need) {
+    if (ln.bmp_arena) {
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+      CUDA_TRY(ctx, cudaFree(ln.bmp_arena));
+    }
+    ln.bmp_arena = nullptr;
+    ln.bmp_arena_cap = 0;
+    if (cudaMalloc(&ln.bmp_arena, need) != cudaSuccess)
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (BMP decode buffers allocation failed)");
+    ln.bmp_arena_cap = need;
+  }
+  uint8_t* A = (uint8_t*)ln.bmp_arena;
+  bd::Batch B;
+  std::memset(&B, 0, sizeof B);
+  B.n = n;
+  int max_w = 0, max_h = 0;
+  for (int i = 0; i < n; ++i) {
+    const bd::Header& H = items[i].hdr;
+    bd::Img& I = B.img[i];
+    I.file = A + off_file[i];
+    I.palette = (const uint32_t*)(A + off_pal[i]);
+    I.rgba = items[i].rgba;
+    I.pitch = items[i].pitch;
+    I.w = H.w; I.h = H.h; I.bpp = H.bpp; I.top_down = H.top_down ? 1 : 0;
+    I.data_off = H.data_off;
+    I.row_stride = H.row_stride;
+    for (int k = 0; k < 4; ++k) { I.shift[k] = H.shift[k]; I.bits[k] = H.bits[k]; }
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + off_file[i], items[i].file, items[i].bytes, cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + off_pal[i], H.palette, 1024, cudaMemcpyHostToDevice, ln.stream));
+    max_w = std::max(max_w, H.w);
+    max_h = std::max(max_h, H.h);
+  }
+  bd::bmp_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, ln.stream>>>(B);
+  CUDA_TRY(ctx, cudaGetLastError());
+  ctx->launches += 1;
+  return STITCH_OK;
+}
+
+// What kind of file an input is: the caller's word, or -- STITCH_MEM_HOST_FILE -- the file's signature.
+int file_kind_of(const StitchImage& im) {
+  if (im.mem_kind != STITCH_MEM_HOST_FILE) return im.mem_kind;
+  const uint8_t* f = (const uint8_t*)im.data;
+  const int64_t n = im.pitch_bytes;
+  if (!f || n < 8) return -1;
+  if (f[0] == 0xFF && f[1] == 0xD8) return STITCH_MEM_HOST_JPEG;
+  if (std::memcmp(f, "\x89PNG\r\n\x1a\n", 8) == 0) return STITCH_MEM_HOST_PNG;
+  if (f[0] == 'B' && f[1] == 'M') return STITCH_MEM_HOST_BMP;
+  return -1;   // GIF, WebP and the rest: probed, not decoded
+}
+
 int parse_png(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::pngdec::Header* H) {
   const stitch::pngdec::ParseStatus ps = stitch::pngdec::parse((const uint8_t*)file, bytes, H);
   if (ps == stitch::pngdec::kOk) return STITCH_OK;
@@ -1002,17 +1086,46 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
   int bw[STITCH_MAX_IMAGES], bh[STITCH_MAX_IMAGES];
   DecodeItem dec[STITCH_MAX_IMAGES];
   std::vector<stitch::pngdec::DecodeItem> pdec_store;
-  int n_dec = 0, n_pdec = 0;
-  for (int i = 0; i < n; ++i)
-    if (job->images[i].mem_kind == STITCH_MEM_HOST_PNG) { pdec_store.resize(STITCH_MAX_IMAGES); break; }
+  std::vector<BmpItem> bdec_store;
+  int n_dec = 0, n_pdec = 0, n_bdec = 0;
+  int kind[STITCH_MAX_IMAGES];
+  for (int i = 0; i < n; ++i) {
+    kind[i] = file_kind_of(job->images[i]);
+    if (kind[i] < 0) {
+      char buf[96];
+      std::snprintf(buf, sizeof buf, "图片%d解码异常 (file type not decoded: JPEG, PNG and BMP are)", i);
+      return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+    }
+    if (kind[i] == STITCH_MEM_HOST_PNG && pdec_store.empty()) pdec_store.resize(STITCH_MAX_IMAGES);
+    if (kind[i] == STITCH_MEM_HOST_BMP && bdec_store.empty()) bdec_store.resize(STITCH_MAX_IMAGES);
+  }
   stitch::pngdec::DecodeItem* pdec = pdec_store.data();
+  BmpItem* bdec = bdec_store.data();
   int st = STITCH_OK;
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
     descs[i] = im.desc;
     bw[i] = im.bmp_width;
     bh[i] = im.bmp_height;
-    if (im.mem_kind == STITCH_MEM_HOST_JPEG) {
+    if (kind[i] == STITCH_MEM_HOST_BMP) {
+      if (!im.data || im.pitch_bytes <= 0) {
+        char buf[64];
+        std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
+        return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+      }
+      BmpItem& d = bdec[n_bdec++];
+      d.file = (const uint8_t*)im.data;
+      d.bytes = (size_t)im.pitch_bytes;
+      st = parse_bmp(ctx, im.data, d.bytes, i, &d.hdr);
+      if (st != STITCH_OK) return st;
+      bw[i] = d.hdr.w;
+      bh[i] = d.hdr.h;
+      if (descs[i].natural_width <= 0 || descs[i].natural_height <= 0) {
+        descs[i].natural_width = descs[i].width = d.hdr.w;      // P:729-732
+        descs[i].natural_height = descs[i].height = d.hdr.h;
+      }
+      if (descs[i].file_size <= 0) descs[i].file_size = im.pitch_bytes;   // P:733
+    } else if (kind[i] == STITCH_MEM_HOST_JPEG) {
       if (!im.data || im.pitch_bytes <= 0) {
         char buf[64];
         std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -1030,7 +1143,7 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
         descs[i].natural_height = descs[i].height = d.hdr.h;
       }
       if (descs[i].file_size <= 0) descs[i].file_size = im.pitch_bytes;   // P:733
-    } else if (im.mem_kind == STITCH_MEM_HOST_PNG) {
+    } else if (kind[i] == STITCH_MEM_HOST_PNG) {
       if (!im.data || im.pitch_bytes <= 0) {
         char buf[64];
         std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -1084,7 +1197,7 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
   // bitmaps (P:1512-1514); a STITCH_MEM_HOST_JPEG image is a FILE the GPU decodes (loadImageFrom, U:27-121)
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
-    if (im.mem_kind == STITCH_MEM_HOST_JPEG || im.mem_kind == STITCH_MEM_HOST_PNG) continue;   // parsed above
+    if (kind[i] == STITCH_MEM_HOST_JPEG || kind[i] == STITCH_MEM_HOST_PNG || kind[i] == STITCH_MEM_HOST_BMP) continue;   // parsed above
     if (!im.data || im.bmp_width <= 0 || im.bmp_height <= 0) {
       char buf[64];
       std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -1111,7 +1224,7 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
     if (u.linear) return cudaMemcpyAsync(u.dst, u.src, (size_t)u.dpitch * u.rows, cudaMemcpyHostToDevice, on);
     return cudaMemcpy2DAsync(u.dst, u.dpitch, u.src, u.spitch, u.row_bytes, u.rows, cudaMemcpyHostToDevice, on);
   };
-  int k_dec = 0, k_pdec = 0, n_host = 0;
+  int k_dec = 0, k_pdec = 0, k_bdec = 0, n_host = 0;
   int64_t host_bytes = 0;
   // pageable host memory is staged by the library itself, for the synchronous entry point (host_stage.h)
   static const bool host_stage_on = [] { const char* e = std::getenv("STITCH_HOST_STAGE"); return !(e && e[0] == '0'); }();
@@ -1146,7 +1259,16 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
     const StitchImage& im = job->images[i];
     int64_t pitch = im.pitch_bytes ? im.pitch_bytes : (int64_t)im.bmp_width * 4;
     const uint8_t* dptr = nullptr;
-    if (im.mem_kind == STITCH_MEM_HOST_JPEG) {
+    if (kind[i] == STITCH_MEM_HOST_BMP) {
+      const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
+      st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
+      if (st != STITCH_OK) return st;
+      bdec[k_bdec].rgba = (uint8_t*)ln.in_stage[i];
+      bdec[k_bdec].pitch = dpitch;
+      ++k_bdec;
+      dptr = (const uint8_t*)ln.in_stage[i];
+      pitch = dpitch;
+    } else if (kind[i] == STITCH_MEM_HOST_JPEG) {
       const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
       st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
       if (st != STITCH_OK) return st;
@@ -1155,7 +1277,7 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
       ++k_dec;
       dptr = (const uint8_t*)ln.in_stage[i];
       pitch = dpitch;
-    } else if (im.mem_kind == STITCH_MEM_HOST_PNG) {
+    } else if (kind[i] == STITCH_MEM_HOST_PNG) {
       const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
       st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
       if (st != STITCH_OK) return st;
@@ -1208,6 +1330,10 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
   }
   if (n_pdec > 0) {
     st = decode_png_batch(ctx, ln, pdec, n_pdec);
+    if (st != STITCH_OK) return st;
+  }
+  if (n_bdec > 0) {
+    st = decode_bmp_batch(ctx, ln, bdec, n_bdec);
     if (st != STITCH_OK) return st;
   }
 
@@ -1751,6 +1877,69 @@ extern "C" int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes,
     CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
   return check_png_status(ctx, ln);
+}
+
+extern "C" int stitch_decode_bmp(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                                 int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "context is busy");
+  if (!file) return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Lane& ln = ctx->lanes[0];
+  drain_lane(ctx, ln);
+  BmpItem d;
+  d.file = (const uint8_t*)file;
+  d.bytes = bytes;
+  int st = parse_bmp(ctx, file, bytes, 0, &d.hdr);
+  if (info) {
+    std::memset(info, 0, sizeof(*info));
+    StitchImageInfo probe;
+    if (stitch_probe_image(file, bytes, &probe) == STITCH_OK) *info = probe;
+  }
+  if (st != STITCH_OK) return st;
+  const int w = d.hdr.w, h = d.hdr.h;
+  const int64_t pitch = out_pitch ? out_pitch : (int64_t)w * 4;
+  if (!out_rgba || pitch < (int64_t)w * 4 || (pitch & 3) || out_capacity < pitch * (int64_t)(h - 1) + (int64_t)w * 4)
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (decode output buffer missing or too small)");
+  const bool out_host = out_mem_kind != STITCH_MEM_DEVICE;
+  if (out_host) {
+    const int64_t dpitch = ((int64_t)w * 4 + 15) & ~15LL;
+    st = ensure_stage(ctx, ln, 0, (size_t)(dpitch * h));
+    if (st != STITCH_OK) return st;
+    d.rgba = (uint8_t*)ln.in_stage[0];
+    d.pitch = dpitch;
+  } else {
+    d.rgba = (uint8_t*)out_rgba;
+    d.pitch = pitch;
+  }
+  st = decode_bmp_batch(ctx, ln, &d, 1);
+  if (st != STITCH_OK) return st;
+  if (out_host)
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+  return STITCH_OK;
+}
+
+extern "C" int stitch_decode_image(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                                   int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  StitchImage im;
+  std::memset(&im, 0, sizeof im);
+  im.data = file;
+  im.pitch_bytes = (int64_t)bytes;
+  im.mem_kind = STITCH_MEM_HOST_FILE;
+  switch (file_kind_of(im)) {
+    case STITCH_MEM_HOST_JPEG: return stitch_decode_jpeg(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
+    case STITCH_MEM_HOST_PNG: return stitch_decode_png(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
+    case STITCH_MEM_HOST_BMP: return stitch_decode_bmp(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
+    default: break;
+  }
+  if (info) {
+    std::memset(info, 0, sizeof(*info));
+    StitchImageInfo probe;
+    if (file && stitch_probe_image(file, bytes, &probe) == STITCH_OK) *info = probe;
+  }
+  return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常 (file type not decoded: JPEG, PNG and BMP are)");
 }
 
 extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {

@@ -155,10 +155,8 @@ napi_value Run(napi_env env, napi_callback_info info) {
     napi_typedarray_type tt; size_t len = 0; void* ptr = nullptr; napi_value ab; size_t off = 0;
     if (napi_get_typedarray_info(env, data, &tt, &len, &ptr, &ab, &off) == napi_ok) {
       s.data = ptr;
-      if (has_file) {   // the FILE (JPEG, or PNG by its signature): decoded on the GPU
-        const uint8_t* fb = (const uint8_t*)ptr;
-        const bool png = len >= 8 && fb[0] == 0x89 && fb[1] == 'P' && fb[2] == 'N' && fb[3] == 'G';
-        s.mem_kind = png ? STITCH_MEM_HOST_PNG : STITCH_MEM_HOST_JPEG;
+      if (has_file) {   // the FILE (JPEG, PNG or BMP: the library looks at its signature): decoded on the GPU
+        s.mem_kind = STITCH_MEM_HOST_FILE;
         s.pitch_bytes = (int64_t)len;
       }
       napi_ref ref; napi_create_reference(env, data, 1, &ref); d->keep.push_back(ref);

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define STITCH_ABI_VERSION 7
+#define STITCH_ABI_VERSION 8
 #define STITCH_MAX_IMAGES 9 /* P:311  MAX_IMAGES: 9 */
 
 /* ---- status codes: one per reference throw site (P:1618-1624 is the catch) ---- */
@@ -125,8 +125,12 @@ int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 /* STITCH_MEM_HOST_JPEG: `data` is a baseline JPEG FILE in host memory and pitch_bytes its length in bytes; the
  * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
 /* STITCH_MEM_HOST_PNG: the same for a PNG FILE (plain or Adam7-interlaced; gray / RGB / palette / alpha, 1-16 bit, tRNS). */
+/* STITCH_MEM_HOST_BMP: the same for a BMP FILE (1 / 4 / 8 bit palettised, 16 / 24 / 32 bit, bit fields; no RLE). */
+/* STITCH_MEM_HOST_FILE: an image FILE of any of these types: the library looks at its signature (what the page does
+ * with a picked path: SUPPORTED_IMAGE_TYPES, P:4). */
 typedef enum StitchMemKind {
-  STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2, STITCH_MEM_HOST_PNG = 3
+  STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2, STITCH_MEM_HOST_PNG = 3, STITCH_MEM_HOST_BMP = 4,
+  STITCH_MEM_HOST_FILE = 5
 } StitchMemKind;
 typedef enum StitchOutputFlags {
   STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4, STITCH_OUT_PNG = 8
@@ -245,6 +249,18 @@ int stitch_decode_jpeg(StitchCtx* ctx, const void* file, size_t bytes, void* out
  * the Adler-32 are not.  There is no CPU fallback.  Synchronous. */
 int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
                       int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
+
+/* The same for a BMP file (P:4 lists 'bmp'): header and palette are read on the host, one kernel converts the pixel
+ * array -- bottom-up or top-down rows, 1 / 4 / 8 bit palettised, 16 bit (5-5-5, or the bit fields the file names),
+ * 24 bit, 32 bit (alpha only where a V3+ header's mask says so; a plain 32-bit file is opaque, as in PIL and the
+ * browsers).  RLE4 / RLE8 files return STITCH_E_BAD_IMAGE. */
+int stitch_decode_bmp(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                      int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
+
+/* loadImageFrom for a file of whatever type (U:27-121): looks at the signature and calls the decoder above that takes
+ * it; GIF and WebP files (probed by stitch_probe_image, not decoded) and anything else return STITCH_E_BAD_IMAGE. */
+int stitch_decode_image(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                        int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
 
 /* ---- preview of the exported image on the page's <canvas> (P:1593-1603) ----
  * createHighResCanvas(node, size.width, size.height) (U:17-24) restores the canvas to floor(size * dpr)

@@ -26,7 +26,7 @@ def test_every_declared_symbol_is_exported_and_bound():
 
 def test_abi_version_and_strerror():
     lib = L.load()
-    assert lib.stitch_abi_version() == 7
+    assert lib.stitch_abi_version() == 8
     assert lib.stitch_strerror(L.E_BAD_DIMS).decode() == "图片尺寸不可用"
     assert lib.stitch_strerror(L.E_BAD_OUT).decode() == "输出尺寸计算失败"
     assert lib.stitch_strerror(L.E_NO_SURFACE).decode() == "无法获取绘图上下文"
