@@ -15,7 +15,7 @@ STITCH_MAX_IMAGES = 9
 VERTICAL, HORIZONTAL = 0, 1
 MODE_MIN, MODE_MAX, MODE_ORIGINAL, MODE_OTHER = 0, 1, 2, 3
 IOS, ANDROID, OTHER = 0, 1, 2
-MEM_HOST, MEM_DEVICE, MEM_HOST_JPEG, MEM_HOST_PNG, MEM_HOST_BMP, MEM_HOST_FILE = 0, 1, 2, 3, 4, 5
+MEM_HOST, MEM_DEVICE, MEM_HOST_JPEG, MEM_HOST_PNG, MEM_HOST_BMP, MEM_HOST_FILE, MEM_HOST_GIF = 0, 1, 2, 3, 4, 5, 6
 OUT_RGBA, OUT_YUV420, OUT_JPEG, OUT_PNG = 1, 2, 4, 8
 NOALLOC_DIGEST_MAX_BYTES = 1 << 30
 
@@ -102,6 +102,8 @@ SIGNATURES = {
     "stitch_decode_png": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
                                     C.POINTER(StitchImageInfo)]),
     "stitch_decode_bmp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
+                                    C.POINTER(StitchImageInfo)]),
+    "stitch_decode_gif": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
                                     C.POINTER(StitchImageInfo)]),
     "stitch_decode_image": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_int64, C.c_int32,
                                     C.POINTER(StitchImageInfo)]),

@@ -29,6 +29,7 @@
 #include "jpeg_prog.cuh"
 #include "png_decode.h"
 #include "bmp_decode.cuh"
+#include "gif_decode.cuh"
 #include "png_kernels.cuh"
 #include "synth.cuh"
 
@@ -53,7 +54,7 @@ struct PendingJob {
 };
 
 // words of a lane's pinned info block
-enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_PNGDEC_STATUS = 5, INFO_PDEC_CHANGED = 6, INFO_WORDS = 8 };
+enum { INFO_JPEG_BYTES = 0, INFO_JPEG_OVERFLOW = 1, INFO_PNG_BYTES = 2, INFO_PNG_OVERFLOW = 3, INFO_DEC_CHANGED = 4, INFO_PNGDEC_STATUS = 5, INFO_PDEC_CHANGED = 6, INFO_GIFDEC_STATUS = 7, INFO_WORDS = 8 };
 
 // One job lane: a stream with its own unit-scheduler counters and its own staging, so that jobs
 // submitted to different lanes overlap -- the next job's blocks fill the SM slots the draining one
@@ -93,6 +94,9 @@ struct Lane {
   size_t prog_arena_cap = 0;
   void* bmp_arena = nullptr;         // BMP files of the job (bmp_decode.cuh): device copies of the files + palettes
   size_t bmp_arena_cap = 0;
+  void* gif_arena = nullptr;         // GIF files of the job (gif_decode.cuh): files, LZW streams, index buffers
+  size_t gif_arena_cap = 0;
+  bool gifdec_active = false;        // the job on this lane decodes GIF files: check INFO_GIFDEC_STATUS when it is done
   stitch::pngdec::Arena pngdec_arena;   // PNG-input decoder (png_decode.cu)
   bool pngdec_active = false;        // the job on this lane decodes PNG files: check INFO_PNGDEC_STATUS when it is done
   // PNG export: grow-only arena (RGBA canvas when the caller did not ask for it, code tables, coded bands, file)
@@ -208,6 +212,7 @@ void free_lane(Lane& ln) {
   if (ln.dec_arena) cudaFree(ln.dec_arena);
   if (ln.prog_arena) cudaFree(ln.prog_arena);
   if (ln.bmp_arena) cudaFree(ln.bmp_arena);
+  if (ln.gif_arena) cudaFree(ln.gif_arena);
   stitch::pngdec::free_arena(ln.pngdec_arena);
   if (ln.png_arena) cudaFree(ln.png_arena);
   if (ln.info_host) cudaFreeHost(ln.info_host);
@@ -695,6 +700,103 @@ int decode_bmp_batch(StitchCtx* ctx, Lane& ln, BmpItem* items, int n) {
   return STITCH_OK;
 }
 
+// One GIF file (first frame) to decode into a device bitmap.
+struct GifItem {
+  const uint8_t* file;
+  size_t bytes;
+  stitch::gifdec::Header hdr;
+  uint8_t* rgba;
+  int64_t pitch;
+};
+
+int parse_gif(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::gifdec::Header* H) {
+  const stitch::gifdec::ParseStatus ps = stitch::gifdec::parse((const uint8_t*)file, bytes, H);
+  if (ps == stitch::gifdec::kOk) return STITCH_OK;
+  char buf[112];
+  std::snprintf(buf, sizeof buf, "图片%d解码异常 (%s)", idx,
+                ps == stitch::gifdec::kUnsupported ? "GIF variant not supported: first frame smaller than the screen"
+                : ps == stitch::gifdec::kNotGif ? "not a GIF file" : "corrupt GIF blocks");
+  return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+}
+
+// The GIF files of a job: uploads + three kernels on the lane's stream; the status word follows them into the lane's
+// info block (read when the job is waited for).
+int decode_gif_batch(StitchCtx* ctx, Lane& ln, GifItem* items, int n) {
+  namespace gd = stitch::gifdec;
+  if (n <= 0) return STITCH_OK;
+  if (n > gd::kMaxImages) return fail(ctx, STITCH_E_TOO_MANY, "more than 9 images");
+  {
+    const int st = ensure_info(ctx, ln);
+    if (st != STITCH_OK) return st;
+  }
+  auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+  size_t need = 256, off_file[gd::kMaxImages], off_stream[gd::kMaxImages], off_idx[gd::kMaxImages], off_pal[gd::kMaxImages];
+  size_t n_pieces = 0;
+  for (int i = 0; i < n; ++i) {
+    const gd::Header& H = items[i].hdr;
+    off_file[i] = need; need += up(items[i].bytes + 16);
+    off_stream[i] = need; need += up((size_t)H.stream_len + 16);
+    off_idx[i] = need; need += up((size_t)gd::kPrelude + (size_t)H.w * H.h + 16);
+    off_pal[i] = need; need += 1024;
+    n_pieces += H.pieces.size();
+  }
+  const size_t off_pieces = need; need += up(n_pieces * sizeof(gd::Piece));
+  const size_t off_pimg = need; need += up(n_pieces);
+  if (ln.gif_arena_cap < need) {
+    if (ln.gif_arena) {
+      CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+      CUDA_TRY(ctx, cudaFree(ln.gif_arena));
+    }
+    ln.gif_arena = nullptr;
+    ln.gif_arena_cap = 0;
+    if (cudaMalloc(&ln.gif_arena, need) != cudaSuccess)
+      return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (GIF decode buffers allocation failed)");
+    ln.gif_arena_cap = need;
+  }
+  uint8_t* A = (uint8_t*)ln.gif_arena;
+  gd::Batch B;
+  std::memset(&B, 0, sizeof B);
+  B.n = n;
+  B.status = (uint32_t*)A;
+  B.pieces = (const gd::Piece*)(A + off_pieces);
+  B.piece_img = A + off_pimg;
+  CUDA_TRY(ctx, cudaMemsetAsync(A, 0, 256, ln.stream));
+  std::vector<gd::Piece> pieces;
+  std::vector<uint8_t> pimg;
+  pieces.reserve(n_pieces);
+  pimg.reserve(n_pieces);
+  int max_w = 0, max_h = 0;
+  for (int i = 0; i < n; ++i) {
+    const gd::Header& H = items[i].hdr;
+    gd::Img& I = B.img[i];
+    I.file = A + off_file[i];
+    I.stream = A + off_stream[i];
+    I.idx = A + off_idx[i];
+    I.palette = (const uint32_t*)(A + off_pal[i]);
+    I.rgba = items[i].rgba;
+    I.pitch = items[i].pitch;
+    I.stream_len = H.stream_len;
+    I.w = H.w; I.h = H.h; I.interlaced = H.interlaced ? 1 : 0; I.min_code = H.min_code;
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + off_file[i], items[i].file, items[i].bytes, cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + off_pal[i], H.palette, 1024, cudaMemcpyHostToDevice, ln.stream));
+    CUDA_TRY(ctx, cudaMemsetAsync(A + off_stream[i] + (H.stream_len & ~(size_t)3), 0, 16, ln.stream));   // the bit reader fetches whole words
+    for (const gd::Piece& pc : H.pieces) { pieces.push_back(pc); pimg.push_back((uint8_t)i); }
+    max_w = std::max(max_w, H.w);
+    max_h = std::max(max_h, H.h);
+  }
+  CUDA_TRY(ctx, cudaMemcpyAsync(A + off_pieces, pieces.data(), pieces.size() * sizeof(gd::Piece), cudaMemcpyHostToDevice, ln.stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(A + off_pimg, pimg.data(), pimg.size(), cudaMemcpyHostToDevice, ln.stream));
+  gd::gif_gather_kernel<<<(unsigned)pieces.size(), 64, 0, ln.stream>>>(B);
+  gd::gif_lzw_kernel<<<n, 32, 0, ln.stream>>>(B);
+  gd::gif_rgba_kernel<<<dim3((max_w + 63) / 64, (max_h + 3) / 4, n), 256, 0, ln.stream>>>(B);
+  CUDA_TRY(ctx, cudaGetLastError());
+  ln.info_host[INFO_GIFDEC_STATUS] = 0;
+  CUDA_TRY(ctx, cudaMemcpyAsync(&ln.info_host[INFO_GIFDEC_STATUS], B.status, 4, cudaMemcpyDeviceToHost, ln.stream));
+  ln.gifdec_active = true;
+  ctx->launches += 3;
+  return STITCH_OK;
+}
+
 // What kind of file an input is: the caller's word, or -- STITCH_MEM_HOST_FILE -- the file's signature.
 int file_kind_of(const StitchImage& im) {
   if (im.mem_kind != STITCH_MEM_HOST_FILE) return im.mem_kind;
@@ -704,7 +806,8 @@ int file_kind_of(const StitchImage& im) {
   if (f[0] == 0xFF && f[1] == 0xD8) return STITCH_MEM_HOST_JPEG;
   if (std::memcmp(f, "\x89PNG\r\n\x1a\n", 8) == 0) return STITCH_MEM_HOST_PNG;
   if (f[0] == 'B' && f[1] == 'M') return STITCH_MEM_HOST_BMP;
-  return -1;   // GIF, WebP and the rest: probed, not decoded
+  if (std::memcmp(f, "GIF8", 4) == 0) return STITCH_MEM_HOST_GIF;
+  return -1;   // WebP and the rest: probed, not decoded
 }
 
 int parse_png(StitchCtx* ctx, const void* file, size_t bytes, int idx, stitch::pngdec::Header* H) {
@@ -739,6 +842,13 @@ int decode_png_batch(StitchCtx* ctx, Lane& ln, stitch::pngdec::DecodeItem* items
 
 // After the lane's stream has drained: did the PNG decoder accept its streams?
 int check_png_status(StitchCtx* ctx, Lane& ln) {
+  if (ln.gifdec_active) {
+    ln.gifdec_active = false;
+    if ((uint32_t)ln.info_host[INFO_GIFDEC_STATUS]) {
+      ln.pngdec_active = false;
+      return fail(ctx, STITCH_E_BAD_IMAGE, "图片解码异常 (GIF data damaged: a code outside the dictionary)");
+    }
+  }
   if (!ln.pngdec_active) return STITCH_OK;
   ln.pngdec_active = false;
   const uint32_t bits = (uint32_t)ln.info_host[INFO_PNGDEC_STATUS];
@@ -1087,27 +1197,48 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
   DecodeItem dec[STITCH_MAX_IMAGES];
   std::vector<stitch::pngdec::DecodeItem> pdec_store;
   std::vector<BmpItem> bdec_store;
-  int n_dec = 0, n_pdec = 0, n_bdec = 0;
+  std::vector<GifItem> gdec_store;
+  int n_dec = 0, n_pdec = 0, n_bdec = 0, n_gdec = 0;
   int kind[STITCH_MAX_IMAGES];
   for (int i = 0; i < n; ++i) {
     kind[i] = file_kind_of(job->images[i]);
     if (kind[i] < 0) {
       char buf[96];
-      std::snprintf(buf, sizeof buf, "图片%d解码异常 (file type not decoded: JPEG, PNG and BMP are)", i);
+      std::snprintf(buf, sizeof buf, "图片%d解码异常 (file type not decoded: JPEG, PNG, BMP and GIF are)", i);
       return fail(ctx, STITCH_E_BAD_IMAGE, buf);
     }
     if (kind[i] == STITCH_MEM_HOST_PNG && pdec_store.empty()) pdec_store.resize(STITCH_MAX_IMAGES);
     if (kind[i] == STITCH_MEM_HOST_BMP && bdec_store.empty()) bdec_store.resize(STITCH_MAX_IMAGES);
+    if (kind[i] == STITCH_MEM_HOST_GIF && gdec_store.empty()) gdec_store.resize(STITCH_MAX_IMAGES);
   }
   stitch::pngdec::DecodeItem* pdec = pdec_store.data();
   BmpItem* bdec = bdec_store.data();
+  GifItem* gdec = gdec_store.data();
   int st = STITCH_OK;
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
     descs[i] = im.desc;
     bw[i] = im.bmp_width;
     bh[i] = im.bmp_height;
-    if (kind[i] == STITCH_MEM_HOST_BMP) {
+    if (kind[i] == STITCH_MEM_HOST_GIF) {
+      if (!im.data || im.pitch_bytes <= 0) {
+        char buf[64];
+        std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
+        return fail(ctx, STITCH_E_BAD_IMAGE, buf);
+      }
+      GifItem& d = gdec[n_gdec++];
+      d.file = (const uint8_t*)im.data;
+      d.bytes = (size_t)im.pitch_bytes;
+      st = parse_gif(ctx, im.data, d.bytes, i, &d.hdr);
+      if (st != STITCH_OK) return st;
+      bw[i] = d.hdr.w;
+      bh[i] = d.hdr.h;
+      if (descs[i].natural_width <= 0 || descs[i].natural_height <= 0) {
+        descs[i].natural_width = descs[i].width = d.hdr.w;      // P:729-732
+        descs[i].natural_height = descs[i].height = d.hdr.h;
+      }
+      if (descs[i].file_size <= 0) descs[i].file_size = im.pitch_bytes;   // P:733
+    } else if (kind[i] == STITCH_MEM_HOST_BMP) {
       if (!im.data || im.pitch_bytes <= 0) {
         char buf[64];
         std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -1197,7 +1328,8 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
   // bitmaps (P:1512-1514); a STITCH_MEM_HOST_JPEG image is a FILE the GPU decodes (loadImageFrom, U:27-121)
   for (int i = 0; i < n; ++i) {
     const StitchImage& im = job->images[i];
-    if (kind[i] == STITCH_MEM_HOST_JPEG || kind[i] == STITCH_MEM_HOST_PNG || kind[i] == STITCH_MEM_HOST_BMP) continue;   // parsed above
+    if (kind[i] == STITCH_MEM_HOST_JPEG || kind[i] == STITCH_MEM_HOST_PNG || kind[i] == STITCH_MEM_HOST_BMP ||
+        kind[i] == STITCH_MEM_HOST_GIF) continue;   // parsed above
     if (!im.data || im.bmp_width <= 0 || im.bmp_height <= 0) {
       char buf[64];
       std::snprintf(buf, sizeof buf, "图片%d解码异常", i);
@@ -1224,7 +1356,7 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
     if (u.linear) return cudaMemcpyAsync(u.dst, u.src, (size_t)u.dpitch * u.rows, cudaMemcpyHostToDevice, on);
     return cudaMemcpy2DAsync(u.dst, u.dpitch, u.src, u.spitch, u.row_bytes, u.rows, cudaMemcpyHostToDevice, on);
   };
-  int k_dec = 0, k_pdec = 0, k_bdec = 0, n_host = 0;
+  int k_dec = 0, k_pdec = 0, k_bdec = 0, k_gdec = 0, n_host = 0;
   int64_t host_bytes = 0;
   // pageable host memory is staged by the library itself, for the synchronous entry point (host_stage.h)
   static const bool host_stage_on = [] { const char* e = std::getenv("STITCH_HOST_STAGE"); return !(e && e[0] == '0'); }();
@@ -1259,7 +1391,16 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
     const StitchImage& im = job->images[i];
     int64_t pitch = im.pitch_bytes ? im.pitch_bytes : (int64_t)im.bmp_width * 4;
     const uint8_t* dptr = nullptr;
-    if (kind[i] == STITCH_MEM_HOST_BMP) {
+    if (kind[i] == STITCH_MEM_HOST_GIF) {
+      const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
+      st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
+      if (st != STITCH_OK) return st;
+      gdec[k_gdec].rgba = (uint8_t*)ln.in_stage[i];
+      gdec[k_gdec].pitch = dpitch;
+      ++k_gdec;
+      dptr = (const uint8_t*)ln.in_stage[i];
+      pitch = dpitch;
+    } else if (kind[i] == STITCH_MEM_HOST_BMP) {
       const int64_t dpitch = ((int64_t)bw[i] * 4 + 15) & ~15LL;
       st = ensure_stage(ctx, ln, i, (size_t)(dpitch * bh[i]));
       if (st != STITCH_OK) return st;
@@ -1334,6 +1475,10 @@ int enqueue_job_impl(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResul
   }
   if (n_bdec > 0) {
     st = decode_bmp_batch(ctx, ln, bdec, n_bdec);
+    if (st != STITCH_OK) return st;
+  }
+  if (n_gdec > 0) {
+    st = decode_gif_batch(ctx, ln, gdec, n_gdec);
     if (st != STITCH_OK) return st;
   }
 
@@ -1920,6 +2065,47 @@ extern "C" int stitch_decode_bmp(StitchCtx* ctx, const void* file, size_t bytes,
   return STITCH_OK;
 }
 
+extern "C" int stitch_decode_gif(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                                 int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info) {
+  if (!ctx) return STITCH_E_BAD_ARG;
+  if (ctx->busy) return fail(ctx, STITCH_E_BUSY, "context is busy");
+  if (!file) return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Lane& ln = ctx->lanes[0];
+  drain_lane(ctx, ln);
+  GifItem d;
+  d.file = (const uint8_t*)file;
+  d.bytes = bytes;
+  int st = parse_gif(ctx, file, bytes, 0, &d.hdr);
+  if (info) {
+    std::memset(info, 0, sizeof(*info));
+    StitchImageInfo probe;
+    if (stitch_probe_image(file, bytes, &probe) == STITCH_OK) *info = probe;
+  }
+  if (st != STITCH_OK) return st;
+  const int w = d.hdr.w, h = d.hdr.h;
+  const int64_t pitch = out_pitch ? out_pitch : (int64_t)w * 4;
+  if (!out_rgba || pitch < (int64_t)w * 4 || (pitch & 3) || out_capacity < pitch * (int64_t)(h - 1) + (int64_t)w * 4)
+    return fail(ctx, STITCH_E_NO_SURFACE, "无法获取绘图上下文 (decode output buffer missing or too small)");
+  const bool out_host = out_mem_kind != STITCH_MEM_DEVICE;
+  if (out_host) {
+    const int64_t dpitch = ((int64_t)w * 4 + 15) & ~15LL;
+    st = ensure_stage(ctx, ln, 0, (size_t)(dpitch * h));
+    if (st != STITCH_OK) return st;
+    d.rgba = (uint8_t*)ln.in_stage[0];
+    d.pitch = dpitch;
+  } else {
+    d.rgba = (uint8_t*)out_rgba;
+    d.pitch = pitch;
+  }
+  st = decode_gif_batch(ctx, ln, &d, 1);
+  if (st != STITCH_OK) return st;
+  if (out_host)
+    CUDA_TRY(ctx, cudaMemcpy2DAsync(out_rgba, pitch, d.rgba, d.pitch, (size_t)w * 4, h, cudaMemcpyDeviceToHost, ln.stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ln.stream));
+  return check_png_status(ctx, ln);
+}
+
 extern "C" int stitch_decode_image(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
                                    int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info) {
   if (!ctx) return STITCH_E_BAD_ARG;
@@ -1932,6 +2118,7 @@ extern "C" int stitch_decode_image(StitchCtx* ctx, const void* file, size_t byte
     case STITCH_MEM_HOST_JPEG: return stitch_decode_jpeg(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
     case STITCH_MEM_HOST_PNG: return stitch_decode_png(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
     case STITCH_MEM_HOST_BMP: return stitch_decode_bmp(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
+    case STITCH_MEM_HOST_GIF: return stitch_decode_gif(ctx, file, bytes, out_rgba, out_capacity, out_pitch, out_mem_kind, info);
     default: break;
   }
   if (info) {
@@ -1939,7 +2126,7 @@ extern "C" int stitch_decode_image(StitchCtx* ctx, const void* file, size_t byte
     StitchImageInfo probe;
     if (file && stitch_probe_image(file, bytes, &probe) == STITCH_OK) *info = probe;
   }
-  return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常 (file type not decoded: JPEG, PNG and BMP are)");
+  return fail(ctx, STITCH_E_BAD_IMAGE, "图片0解码异常 (file type not decoded: JPEG, PNG, BMP and GIF are)");
 }
 
 extern "C" int stitch_submit(StitchCtx* ctx, const StitchJob* job, StitchResult* result, uint64_t* ticket) {

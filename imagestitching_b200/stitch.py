@@ -291,11 +291,21 @@ class StitchContext:
         return out
 
     def decode_image(self, file_bytes: bytes) -> np.ndarray:
-        """loadImageFrom (utils/canvas.js:27-121) for a file of any decodable type (JPEG, PNG, BMP: by its signature)."""
+        """loadImageFrom (utils/canvas.js:27-121) for a file of any decodable type (JPEG, PNG, BMP, GIF: by its signature)."""
         info = get_image_info(file_bytes)
         out = np.empty((max(1, info["height"]), max(1, info["width"]), 4), dtype=np.uint8)
         buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")
         st = self.lib.stitch_decode_image(self.handle, buf, len(file_bytes), out.ctypes.data, out.nbytes, 0, L.MEM_HOST, None)
+        if st != L.OK:
+            _raise(st, self.handle)
+        return out
+
+    def decode_gif(self, file_bytes: bytes) -> np.ndarray:
+        """loadImageFrom for a GIF file: RGBA8 [h, w, 4] of its first frame (gif_decode.cuh)."""
+        info = get_image_info(file_bytes)
+        out = np.empty((info["height"], info["width"], 4), dtype=np.uint8)
+        buf = (C.c_char * max(1, len(file_bytes))).from_buffer_copy(file_bytes or b"\0")
+        st = self.lib.stitch_decode_gif(self.handle, buf, len(file_bytes), out.ctypes.data, out.nbytes, 0, L.MEM_HOST, None)
         if st != L.OK:
             _raise(st, self.handle)
         return out
@@ -335,7 +345,7 @@ class StitchContext:
                 data = img["file"] if isinstance(img["file"], bytes) else bytes(img["file"])
                 arr[i].data = C.cast(C.c_char_p(data), C.c_void_p)      # no copy: `data` is kept alive below
                 arr[i].pitch_bytes = len(data)
-                arr[i].mem_kind = L.MEM_HOST_FILE      # the library looks at the signature: JPEG, PNG or BMP
+                arr[i].mem_kind = L.MEM_HOST_FILE      # the library looks at the signature: JPEG, PNG, BMP or GIF
                 keep.append(data)
             elif isinstance(bmp, DeviceBitmap):
                 arr[i].data = bmp.ptr

@@ -155,7 +155,7 @@ napi_value Run(napi_env env, napi_callback_info info) {
     napi_typedarray_type tt; size_t len = 0; void* ptr = nullptr; napi_value ab; size_t off = 0;
     if (napi_get_typedarray_info(env, data, &tt, &len, &ptr, &ab, &off) == napi_ok) {
       s.data = ptr;
-      if (has_file) {   // the FILE (JPEG, PNG or BMP: the library looks at its signature): decoded on the GPU
+      if (has_file) {   // the FILE (JPEG, PNG, BMP or GIF: the library looks at its signature): decoded on the GPU
         s.mem_kind = STITCH_MEM_HOST_FILE;
         s.pitch_bytes = (int64_t)len;
       }

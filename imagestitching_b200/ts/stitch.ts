@@ -19,7 +19,7 @@ export interface StitchImage extends ImageRecord {
   /** decoded RGBA8 bitmap, straight alpha (what loadImageFrom hands to drawWithOrientation) ... */
   data?: Uint8Array;
   bmpWidth?: number; bmpHeight?: number; pitchBytes?: number;
-  /** ... or the FILE itself -- JPEG (baseline or progressive), PNG or BMP: decoded on the GPU (STITCH_MEM_HOST_FILE, loadImageFrom canvas.js:27-121) */
+  /** ... or the FILE itself -- JPEG (baseline or progressive), PNG, BMP or GIF (first frame): decoded on the GPU (STITCH_MEM_HOST_FILE, loadImageFrom canvas.js:27-121) */
   file?: Uint8Array;
 }
 export interface StitchOptions {

@@ -126,11 +126,12 @@ int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
  * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
 /* STITCH_MEM_HOST_PNG: the same for a PNG FILE (plain or Adam7-interlaced; gray / RGB / palette / alpha, 1-16 bit, tRNS). */
 /* STITCH_MEM_HOST_BMP: the same for a BMP FILE (1 / 4 / 8 bit palettised, 16 / 24 / 32 bit, bit fields; no RLE). */
+/* STITCH_MEM_HOST_GIF: the same for a GIF FILE: its first frame (what createImage + drawImage paint). */
 /* STITCH_MEM_HOST_FILE: an image FILE of any of these types: the library looks at its signature (what the page does
  * with a picked path: SUPPORTED_IMAGE_TYPES, P:4). */
 typedef enum StitchMemKind {
   STITCH_MEM_HOST = 0, STITCH_MEM_DEVICE = 1, STITCH_MEM_HOST_JPEG = 2, STITCH_MEM_HOST_PNG = 3, STITCH_MEM_HOST_BMP = 4,
-  STITCH_MEM_HOST_FILE = 5
+  STITCH_MEM_HOST_FILE = 5, STITCH_MEM_HOST_GIF = 6
 } StitchMemKind;
 typedef enum StitchOutputFlags {
   STITCH_OUT_RGBA = 1, STITCH_OUT_YUV420 = 2, STITCH_OUT_JPEG = 4, STITCH_OUT_PNG = 8
@@ -257,8 +258,16 @@ int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes, void* out_
 int stitch_decode_bmp(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
                       int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
 
+/* The same for a GIF file (P:4 lists 'gif'): the FIRST frame, which is what createImage + drawImage paint.  The
+ * container is walked on the host; the LZW stream is decoded by one warp (every dictionary string is a substring of the
+ * output already written: a code is a copy), indices go through the colour table, the transparent index of a graphic
+ * control extension gets alpha 0, interlaced rows are put in place.  A first frame smaller than the logical screen and a
+ * damaged stream return STITCH_E_BAD_IMAGE. */
+int stitch_decode_gif(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
+                      int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
+
 /* loadImageFrom for a file of whatever type (U:27-121): looks at the signature and calls the decoder above that takes
- * it; GIF and WebP files (probed by stitch_probe_image, not decoded) and anything else return STITCH_E_BAD_IMAGE. */
+ * it; WebP files (probed by stitch_probe_image, not decoded) and anything else return STITCH_E_BAD_IMAGE. */
 int stitch_decode_image(StitchCtx* ctx, const void* file, size_t bytes, void* out_rgba, int64_t out_capacity,
                         int64_t out_pitch, int32_t out_mem_kind, StitchImageInfo* info);
 

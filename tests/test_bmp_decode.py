@@ -129,11 +129,10 @@ def test_gpu_decode_image_dispatches_and_refuses(ctx):
     Image.fromarray(a).save(pb, "PNG")
     assert np.array_equal(ctx.decode_image(jb.getvalue()), J.decode(jb.getvalue()))
     assert np.array_equal(ctx.decode_image(pb.getvalue()), P.decode(pb.getvalue()))
-    gb = io.BytesIO()
-    Image.fromarray(a).save(gb, "GIF")
+    webp = b"RIFF" + struct.pack("<I", 30) + b"WEBPVP8 " + struct.pack("<I", 18) + bytes(18)     # probed, never decoded
     good = _pil_bmp(a, "RGB")
     rle = good[:30] + struct.pack("<I", 1) + good[34:]
-    for bad in (gb.getvalue(), rle, good[:60]):
+    for bad in (webp, rle, good[:60]):
         with pytest.raises(StitchError) as e:
             ctx.decode_image(bad)
         assert e.value.status == L.E_BAD_IMAGE
@@ -142,7 +141,7 @@ def test_gpu_decode_image_dispatches_and_refuses(ctx):
 @pytest.mark.gpu
 def test_gpu_job_with_bmp_jpeg_and_png_files(ctx):
     """Files of three types in one job (the library looks at their signatures) == the job over the decoded bitmaps;
-    a GIF file in the list is the page's decode error."""
+    a WebP file in the list is the page's decode error."""
     from imagestitching_b200 import StitchError
     from oracle import jpeg_c as J
     from oracle import png_dec_c as P
@@ -161,8 +160,7 @@ def test_gpu_job_with_bmp_jpeg_and_png_files(ctx):
     tickets = [ctx.submit([{"file": f} for f in files_], "vertical", platform="ios") for _ in range(3)]
     for t in tickets:
         assert np.array_equal(ctx.wait(t).rgba, want.rgba)
-    gb = io.BytesIO()
-    Image.fromarray(_picture(50, 40, 3)).save(gb, "GIF")
+    webp = b"RIFF" + struct.pack("<I", 30) + b"WEBPVP8 " + struct.pack("<I", 18) + bytes(18)
     with pytest.raises(StitchError) as e:
-        ctx.run([{"file": bmp}, {"file": gb.getvalue()}], "vertical", platform="ios")
+        ctx.run([{"file": bmp}, {"file": webp, "naturalWidth": 50, "naturalHeight": 40, "width": 50, "height": 40}], "vertical", platform="ios")
     assert e.value.status == L.E_BAD_IMAGE and "图片1解码异常" in e.value.message

@@ -1,0 +1,127 @@
+"""GIF inputs (P:4 SUPPORTED_IMAGE_TYPES 'gif'; utils/canvas.js:27-121 loadImageFrom): the first frame.
+
+CPU: the oracle (oracle/gif_ref.py: classic table-of-strings LZW) is pinned to PIL's GifImagePlugin, frame 0.
+GPU: stitch_decode_gif / stitch_decode_image and GIF job inputs equal the oracle.
+"""
+import io
+
+import numpy as np
+import pytest
+from PIL import Image
+
+from imagestitching_b200 import _lib as L
+from oracle import gif_ref as G
+
+
+def _picture(w, h, seed=0, noise=8):
+    y, x = np.mgrid[0:h, 0:w]
+    a = np.stack([128 + 100 * np.sin(x / 17 + y / 29), 128 + 90 * np.cos(x / 23 - y / 13), (x * 3 + y * 5) % 256], -1)
+    return np.clip(a + np.random.default_rng(seed).integers(-noise, noise + 1, a.shape), 0, 255).astype(np.uint8)
+
+
+def _gif(im, **kw):
+    b = io.BytesIO()
+    im.save(b, "GIF", **kw)
+    return b.getvalue()
+
+
+def _pil_rgba(data):
+    return np.asarray(Image.open(io.BytesIO(data)).convert("RGBA"))
+
+
+def files():
+    rng = np.random.default_rng(1)
+    out = []
+    for (w, h) in ((1, 1), (7, 5), (64, 48), (123, 77), (250, 131)):
+        for kw in ({}, {"interlace": 1}, {"transparency": 3}, {"interlace": 1, "transparency": 0}):
+            for colours in (2, 16, 256):
+                out.append((f"{w}x{h}_{colours}_{sorted(kw)}", _gif(Image.fromarray(_picture(w, h, colours)).quantize(colours), **kw)))
+    g = np.zeros((300, 400), np.uint8)        # a flat graphic: long strings, the dictionary fills up and is cleared
+    g[50:200, 80:300] = 7
+    g[::17] = 3
+    im = Image.fromarray(g, "P")
+    im.putpalette([int(v) for v in rng.integers(0, 256, 768)])
+    out.append(("graphic", _gif(im)))
+    out.append(("gray", _gif(Image.fromarray(_picture(200, 150)[..., 0], "L"))))
+    out.append(("photo_800x600", _gif(Image.fromarray(_picture(800, 600, 5)).quantize(256))))
+    # two frames: only the first is painted
+    a, b = Image.fromarray(_picture(90, 60, 1)).quantize(64), Image.fromarray(_picture(90, 60, 2)).quantize(64)
+    buf = io.BytesIO()
+    a.save(buf, "GIF", save_all=True, append_images=[b], duration=100)
+    out.append(("animated", buf.getvalue()))
+    return out
+
+
+def test_oracle_equals_pil():
+    for name, data in files():
+        assert np.array_equal(G.decode(data), _pil_rgba(data)), name
+
+
+def test_oracle_rejects():
+    good = _gif(Image.fromarray(_picture(20, 10)).quantize(16))
+    with pytest.raises(G.GifError):
+        G.decode(b"BM" + bytes(40))
+    lsd = bytearray(good)
+    lsd[6] = 30                                   # the logical screen is wider than the frame
+    with pytest.raises(G.GifError):
+        G.decode(bytes(lsd))
+
+
+@pytest.fixture()
+def ctx():
+    from imagestitching_b200 import StitchContext
+    c = StitchContext(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.gpu
+def test_gpu_gif_equals_oracle(ctx):
+    for name, data in files():
+        want = G.decode(data)
+        assert np.array_equal(ctx.decode_gif(data), want), name
+        assert np.array_equal(ctx.decode_image(data), want), name
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(120)
+def test_gpu_gif_errors_and_damage(ctx):
+    from imagestitching_b200 import StitchError
+    good = _gif(Image.fromarray(_picture(120, 80)).quantize(64))
+    lsd = bytearray(good)
+    lsd[6] = 200
+    with pytest.raises(StitchError) as e:
+        ctx.decode_gif(bytes(lsd))
+    assert e.value.status == L.E_BAD_IMAGE
+    rng = np.random.default_rng(4)
+    start = good.index(b"\x2c") + 11
+    for seed in range(8):                          # damaged LZW data: a bitmap, or the decode error -- never a hang
+        bad = bytearray(good)
+        for pos in rng.integers(start + 2, len(bad) - 4, 5):
+            if pos % 256 != (start % 256):         # keep clear of most sub-block length bytes
+                bad[pos] ^= int(rng.integers(1, 256))
+        try:
+            assert ctx.decode_gif(bytes(bad)).shape == (80, 120, 4)
+        except StitchError as e2:
+            assert e2.status == L.E_BAD_IMAGE
+    assert np.array_equal(ctx.decode_gif(good), G.decode(good))
+    cut = good[: len(good) // 2]                   # cut short: what the data delivers, index 0 behind it (or refused)
+    try:
+        assert ctx.decode_gif(cut).shape == (80, 120, 4)
+    except StitchError as e3:
+        assert e3.status == L.E_BAD_IMAGE
+
+
+@pytest.mark.gpu
+def test_gpu_job_with_gif_files(ctx):
+    from tests import util as U
+    dims = [(123, 77), (250, 131)]
+    fs = [_gif(Image.fromarray(_picture(*dims[0], 3)).quantize(256), transparency=5), _gif(Image.fromarray(_picture(*dims[1], 4)).quantize(32), interlace=1)]
+    bitmaps = [G.decode(f) for f in fs]
+    want = ctx.run(U.page_images(dims, bitmaps), "vertical", platform="ios")
+    got = ctx.run([{"file": f} for f in fs], "vertical", platform="ios")
+    assert np.array_equal(got.rgba, want.rgba)
+    ctx.set_lanes(2)
+    tickets = [ctx.submit([{"file": f} for f in fs], "vertical", platform="ios") for _ in range(3)]
+    for t in tickets:
+        assert np.array_equal(ctx.wait(t).rgba, want.rgba)
