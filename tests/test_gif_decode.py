@@ -44,6 +44,13 @@ def files():
     out.append(("graphic", _gif(im)))
     out.append(("gray", _gif(Image.fromarray(_picture(200, 150)[..., 0], "L"))))
     out.append(("photo_800x600", _gif(Image.fromarray(_picture(800, 600, 5)).quantize(256))))
+    # strings longer than the decoder's shared-memory window of recent output, and sources behind it
+    big = np.zeros((900, 1600), np.uint8)
+    big[100:800, 200:1400] = 1
+    big[::97, ::3] = 2
+    im = Image.fromarray(big, "P")
+    im.putpalette([int(v) for v in rng.integers(0, 256, 768)])
+    out.append(("flat_1600x900", _gif(im)))
     # two frames: only the first is painted
     a, b = Image.fromarray(_picture(90, 60, 1)).quantize(64), Image.fromarray(_picture(90, 60, 2)).quantize(64)
     buf = io.BytesIO()
