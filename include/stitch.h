@@ -122,7 +122,7 @@ int stitch_ctx_join(StitchCtx* ctx);
 typedef void (*StitchProgressFn)(void* user, int32_t percent);
 int stitch_set_progress_cb(StitchCtx* ctx, StitchProgressFn fn, void* user);
 
-/* STITCH_MEM_HOST_JPEG: `data` is a baseline JPEG FILE in host memory and pitch_bytes its length in bytes; the
+/* STITCH_MEM_HOST_JPEG: `data` is a JPEG FILE (baseline or progressive) in host memory and pitch_bytes its length in bytes; the
  * library decodes it on the GPU (loadImageFrom, U:27-121) -- bmp_width / bmp_height are read from the file. */
 /* STITCH_MEM_HOST_PNG: the same for a PNG FILE (plain or Adam7-interlaced; gray / RGB / palette / alpha, 1-16 bit, tRNS). */
 /* STITCH_MEM_HOST_BMP: the same for a BMP FILE (1 / 4 / 8 bit palettised, 16 / 24 / 32 bit, bit fields; no RLE). */
