@@ -48,6 +48,7 @@ inline uint32_t jdec_pick_sub(size_t total_scan_bytes) {
 #define JDEC_THREADS 256
 #endif
 #define JDEC_MAX_IMAGES 9
+#define JDEC_SEG 128          // bytes between the checkpoints inside a subsequence (see redecode)
 
 struct DecImage {
   const uint8_t* scan;        // entropy-coded segment (device)
@@ -61,6 +62,8 @@ struct DecImage {
   int16_t* coef;              // [n_blocks][64] scan order, zig-zag order inside a block
   int32_t* dcsum;             // [3][n_mcu] per-MCU DC sums, then their segmented scan
   uint2* consumed;            // [blocks of the sync grid] predecessor state each block last started from
+  uint4* cp;                  // [n_sub][nseg] checkpoints: {byte, packed state, blocks started} at the end of every 128-byte
+                              // segment of a subsequence, as its LAST decode saw them (nullptr: no checkpoints)
   uint8_t* plane[3];          // component planes, MCU-padded
   int32_t pw[3], ph[3];
   uint8_t* rgba;              // output bitmap
@@ -74,6 +77,7 @@ struct DecBatch {
   int32_t flag_cur;           // flag this round raises
   int32_t flag_prev;          // flag of the round before (-1: none, the host decides whether to launch)
   uint32_t sub;               // raw bytes per subsequence (jdec_pick_sub)
+  uint32_t nseg;              // checkpointed segments per subsequence (sub / JDEC_SEG; 1 = none)
   __device__ __forceinline__ const DecImage& item(int i) const { return img[i]; }
 };
 
@@ -359,6 +363,38 @@ __device__ __forceinline__ State decode_nowrite(const DecImage& I, const SmemTab
 }
 __device__ __forceinline__ uint32_t scan_start_word(const DecImage&) { return 0u; }   // packed state at byte 0: block 0, DC
 
+// A subsequence decoded again from a new entry state.  With checkpoints (I.cp) the decode stops at the first segment
+// boundary where it arrives in the state the PREVIOUS decode of this subsequence had there: from that point on the two
+// are the same decode, so the old end state and the old block counts of the remaining segments stand.  Entry states
+// that differ only re-synchronise a few symbols in (that is what the whole scheme rests on), so a re-decode costs one
+// segment or two instead of the subsequence -- and the synchronisation rounds are chains of re-decodes.
+// EARLY = false (the first pass): nothing to compare with yet, the checkpoints are only written.
+template <bool EARLY, class BATCH>
+__device__ __forceinline__ State redecode(const BATCH& B, const DecImage& I, const SmemTables& T, uint32_t idx, State in, uint32_t* started) {
+  const uint32_t nseg = B.nseg;
+  if (!I.cp || nseg <= 1) return decode_nowrite(I, T, in, (idx + 1) * B.sub, started);
+  uint4* cp = I.cp + (size_t)idx * nseg;
+  uint32_t total = 0;
+  State cur = in;
+  for (uint32_t c = 0; c < nseg; ++c) {
+    uint32_t n = 0;
+    const State e = decode_nowrite(I, T, cur, idx * B.sub + (c + 1) * JDEC_SEG, &n);
+    const uint32_t pk = pack_state(e);
+    const uint4 old = cp[c];
+    cp[c] = make_uint4(e.byte, pk, n, 0u);
+    total += n;
+    cur = e;
+    if (EARLY && c + 1 < nseg && old.x == e.byte && old.y == pk) {
+      for (uint32_t k = c + 1; k < nseg; ++k) total += cp[k].z;
+      const uint4 last = cp[nseg - 1];
+      cur = unpack_state(last.x, last.y);
+      break;
+    }
+  }
+  *started = total;
+  return cur;
+}
+
 // D1: first pass from guessed states.
 __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_constant__ DecBatch B) {
   __shared__ SmemTables T;
@@ -368,7 +404,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_first_kernel(const __grid_c
   const uint32_t i = blockIdx.x * JDEC_THREADS + threadIdx.x;
   if (i >= (uint32_t)I.n_sub) return;
   uint32_t started = 0;
-  const State e = decode_range<false>(I, T, guess_state(I, i, B.sub), (i + 1) * B.sub, &started, 0);
+  const State e = redecode<false>(B, I, T, i, guess_state(I, i, B.sub), &started);
   I.state[i] = make_uint4(e.byte, pack_state(e), started, 0u);
 }
 
@@ -446,7 +482,7 @@ __global__ void __launch_bounds__(JDEC_THREADS) jdec_sync_kernel(const __grid_co
     if (t < total) {
       s = sh_list[t];
       const uint2 ps = sh_state[s];
-      const State e = decode_nowrite(I, T, unpack_state(ps.x, ps.y), (base + s + 1) * B.sub, &started);
+      const State e = redecode<true>(B, I, T, base + s, unpack_state(ps.x, ps.y), &started);
       fresh = make_uint2(e.byte, pack_state(e));
     }
     __syncthreads();

@@ -129,6 +129,10 @@ __device__ __forceinline__ State pdecode_range(const PScan& S, const SmemTables&
 __device__ __forceinline__ State decode_nowrite(const PScan& S, const SmemTables& T, State s, uint32_t end_byte, uint32_t* completed) {
   return pdecode_range<false>(S, T, s, end_byte, completed, 0);
 }
+template <bool EARLY, class BATCH>
+__device__ __forceinline__ State redecode(const BATCH& B, const PScan& S, const SmemTables& T, uint32_t idx, State in, uint32_t* completed) {
+  return pdecode_range<false>(S, T, in, (idx + 1) * B.sub, completed, 0);   // no checkpoints for the scans of progressive files
+}
 __device__ __forceinline__ uint32_t scan_start_word(const PScan& S) {
   return S.mode == PSCAN_AC_FIRST ? (uint32_t)S.ss << 16 : 0u;
 }

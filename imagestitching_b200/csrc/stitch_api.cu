@@ -260,13 +260,15 @@ int decode_baseline_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bo
   std::memset(&B, 0, sizeof B);
   B.n = n;
   size_t need = 256;  // the `changed` flag
-  struct Carve { size_t scan, tab, state, prefix, coef, plane[3], dcsum, consumed; } cv[JDEC_MAX_IMAGES];
+  struct Carve { size_t scan, tab, state, prefix, coef, plane[3], dcsum, consumed, cp; } cv[JDEC_MAX_IMAGES];
   int max_mcu = 0;
   int max_sub = 0, max_blocks = 0, max_w = 0, max_h = 0;
   {
     size_t total_scan = 0;
     for (int i = 0; i < n; ++i) total_scan += items[i].hdr.scan_len;
     B.sub = jd::jdec_pick_sub(total_scan);
+    static const bool cp_off = [] { const char* e = std::getenv("STITCH_JDEC_CP"); return e && e[0] == '0'; }();
+    B.nseg = cp_off ? 1u : B.sub / JDEC_SEG;
   }
   for (int i = 0; i < n; ++i) {
     const jd::Header& H = items[i].hdr;
@@ -293,6 +295,7 @@ int decode_baseline_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bo
     for (int k = 0; k < 3; ++k) { c.plane[k] = need; need += up((size_t)I.pw[k] * I.ph[k] + 16); }
     c.dcsum = need; need += up((size_t)H.mcux * H.mcuy * 3 * 4);
     c.consumed = need; need += up((size_t)((I.n_sub + JDEC_THREADS - 1) / JDEC_THREADS) * 8);
+    c.cp = need; need += up((size_t)I.n_sub * B.nseg * 16);
     max_mcu = std::max(max_mcu, H.mcux * H.mcuy);
     max_sub = std::max(max_sub, I.n_sub);
     max_blocks = std::max(max_blocks, I.n_blocks);
@@ -328,6 +331,7 @@ int decode_baseline_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bo
     for (int k = 0; k < 3; ++k) I.plane[k] = A + c.plane[k];
     I.dcsum = (int32_t*)(A + c.dcsum);
     I.consumed = (uint2*)(A + c.consumed);
+    I.cp = B.nseg > 1 ? (uint4*)(A + c.cp) : nullptr;
     CUDA_TRY(ctx, cudaMemcpyAsync(A + c.scan, items[i].file + H.scan_off, H.scan_len, cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemcpyAsync(A + c.tab, &H.tab, sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemsetAsync(A + c.coef, 0, (size_t)I.n_blocks * 128, ln.stream));
