@@ -1176,6 +1176,7 @@ int enqueue_job(StitchCtx* ctx, Lane& ln, const StitchJob* job, StitchResult* re
       while (ln.host_copies->load(std::memory_order_acquire) > 0) std::this_thread::yield();
     cudaGetLastError();
     ln.pngdec_active = false;
+    ln.gifdec_active = false;
     ctx->last_error = keep;
   }
   return st;
@@ -1752,6 +1753,7 @@ void finalize_job(StitchCtx* ctx, PendingJob& pj) {
   }
   if (pj.status == STITCH_OK) pj.status = check_png_status(ctx, ln);
   ln.pngdec_active = false;
+  ln.gifdec_active = false;
   if (pj.status != STITCH_OK) pj.error = ctx->last_error;
   if (pj.status == STITCH_OK) {
     emit(ctx, 96);   // P:1581
@@ -1858,6 +1860,7 @@ extern "C" int stitch_run(StitchCtx* ctx, const StitchJob* job, StitchResult* re
     while (hc->load(std::memory_order_acquire) > 0) std::this_thread::yield();
   if (st == STITCH_OK) st = check_png_status(ctx, ctx->lanes[0]);
   ctx->lanes[0].pngdec_active = false;
+  ctx->lanes[0].gifdec_active = false;
   if (st == STITCH_OK) {
     emit(ctx, 96);   // P:1581
     emit(ctx, 100);  // P:1611
@@ -1995,6 +1998,7 @@ extern "C" int stitch_decode_png(StitchCtx* ctx, const void* file, size_t bytes,
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   Lane& ln = ctx->lanes[0];
   drain_lane(ctx, ln);
+  ln.gifdec_active = ln.pngdec_active = false;   // nothing of an earlier, failed call is left to check
   stitch::pngdec::DecodeItem d;
   d.file = (const uint8_t*)file;
   d.bytes = bytes;
@@ -2077,6 +2081,7 @@ extern "C" int stitch_decode_gif(StitchCtx* ctx, const void* file, size_t bytes,
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   Lane& ln = ctx->lanes[0];
   drain_lane(ctx, ln);
+  ln.gifdec_active = ln.pngdec_active = false;   // nothing of an earlier, failed call is left to check
   GifItem d;
   d.file = (const uint8_t*)file;
   d.bytes = bytes;

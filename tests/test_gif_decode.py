@@ -112,6 +112,17 @@ def test_gpu_gif_errors_and_damage(ctx):
         except StitchError as e2:
             assert e2.status == L.E_BAD_IMAGE
     assert np.array_equal(ctx.decode_gif(good), G.decode(good))
+    # a job with a damaged GIF fails; the next job on the same context -- no GIF in it -- is not blamed for it
+    from tests import util as U
+    worst = bytearray(good)
+    worst[start + 3: start + 40] = bytes([0xFF]) * 37
+    bmpish = G.decode(good)
+    try:
+        ctx.run([{"file": bytes(worst)}, {"file": good}], "vertical", platform="ios")
+    except StitchError as e4:
+        assert e4.status == L.E_BAD_IMAGE
+    ok = ctx.run(U.page_images([(120, 80)] * 2, [bmpish, bmpish]), "vertical", platform="ios")
+    assert ok.rgba.shape[1] > 0
     cut = good[: len(good) // 2]                   # cut short: what the data delivers, index 0 behind it (or refused)
     try:
         assert ctx.decode_gif(cut).shape == (80, 120, 4)
