@@ -7,7 +7,7 @@
 // is the initial value of the accumulator, so no separate fill pass exists.
 //
 // Coordinates are evaluated in fp64 exactly as the oracle does; colour is
-// accumulated in fp32.  The streaming kernel (stream_kernel.cuh) takes over the
+// accumulated in fp32.  The streaming unit (stream_unit.cuh) takes over the
 // bandwidth-critical integer-aligned downscale case.
 #pragma once
 #include <cstdint>
