@@ -903,9 +903,13 @@ def main():
                 C.memmove(pf, f, len(f))
                 pbufs.append((pf, len(f)))
                 host_outs.append(pf)
+            # a job keeps 45 warps busy (one per refinement scan) for tens of milliseconds: more jobs in flight than the
+            # other legs use cost nothing, so this leg takes every lane a context has
+            p_lanes = 8
+            ctx.set_lanes(p_lanes)
             pjobs = []
             p_mp = 0.0
-            for _ in range(e2e_lanes):
+            for _ in range(p_lanes):
                 arr = (L.StitchImage * 9)()
                 for i in range(9):
                     arr[i].desc.natural_width, arr[i].desc.natural_height = pw_, ph_
@@ -934,17 +938,18 @@ def main():
             def prog_loop(nsteps):
                 tickets = []
                 for i in range(nsteps):
-                    pj_, _, pr = pjobs[i % e2e_lanes]
+                    pj_, _, pr = pjobs[i % p_lanes]
                     t = C.c_uint64()
                     st = lib.stitch_submit(ctx.handle, C.byref(pj_), C.byref(pr), C.byref(t))
                     assert st == 0, lib.stitch_last_error(ctx.handle)
                     tickets.append(t.value)
-                    if i >= e2e_lanes - 1:
-                        assert lib.stitch_wait(ctx.handle, tickets[i - (e2e_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
-                assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0, lib.stitch_last_error(ctx.handle)
+                    if i >= p_lanes - 1:
+                        assert lib.stitch_wait(ctx.handle, tickets[i - (p_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
+                for t_ in tickets[-(p_lanes - 1):]:
+                    assert lib.stitch_wait(ctx.handle, t_) == 0, lib.stitch_last_error(ctx.handle)
 
-            p_steps = min(files_steps, 2 * e2e_lanes)
-            prog_loop(e2e_lanes)
+            p_steps = min(files_steps, 3 * p_lanes)
+            prog_loop(p_lanes)
             torch.cuda.synchronize()
             barrier()
             t0 = time.perf_counter()
@@ -958,7 +963,8 @@ def main():
                 t = torch.tensor([ps_], dtype=torch.float64, device="cuda")
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 ps_ = float(t.item())
-            e2e_files["prog_in"] = {"value": p_mp * p_steps * world / ps_, "unit": "MP/s", "steps": p_steps,
+            ctx.set_lanes(e2e_lanes)
+            e2e_files["prog_in"] = {"value": p_mp * p_steps * world / ps_, "unit": "MP/s", "steps": p_steps, "lanes": p_lanes,
                                     "ms_per_step": ps_ / p_steps * 1e3, "single_job_latency_ms": p_single, "output_mp_per_step": p_mp,
                                     "h2d_bytes_per_step": sum(b for _, b in pbufs), "d2h_bytes_per_step": int(pjobs[0][2].jpeg_bytes),
                                     "inputs": "9 progressive JPEG files (SOF2, libjpeg's 10-scan script), 1600x1200, quality 90, 4:2:0, "
@@ -968,6 +974,10 @@ def main():
         except Exception as e:
             e2e_files["prog_in"] = {"value": None, "note": f"failed: {e}"}
             prog_files = None
+            try:
+                ctx.set_lanes(e2e_lanes)
+            except Exception:
+                pass
 
     if has_jpeg or has_png:
         out_bytes = int(hres.jpeg_bytes if has_jpeg else hres.png_bytes)   # d2h of the e2e step = the file
