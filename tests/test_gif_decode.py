@@ -64,6 +64,58 @@ def test_oracle_equals_pil():
         assert np.array_equal(G.decode(data), _pil_rgba(data)), name
 
 
+def _lzw_as_copies(stream: bytes, min_code: int, n_out: int) -> np.ndarray:
+    """The GPU kernel's form of LZW (gif_decode.cuh G1), restated: the dictionary holds (start, length) into the output
+    already written, a 256-byte prelude in front of the output holds the roots, a code is a copy."""
+    clear, eoi = 1 << min_code, (1 << min_code) + 1
+    out = bytearray(range(256))
+    start, length = list(range(clear)) + [0, 0], [1] * clear + [0, 0]
+    size, nxt, prev, prev_pos = min_code + 1, clear + 2, -1, 0
+    acc = cnt = 0
+    it = iter(stream)
+    total = 256 + n_out
+    while len(out) < total:
+        while cnt < size:
+            b = next(it, None)
+            if b is None:
+                return np.frombuffer(bytes(out[256:]).ljust(n_out, b"\0"), np.uint8)
+            acc |= b << cnt
+            cnt += 8
+        code = acc & ((1 << size) - 1)
+        acc >>= size
+        cnt -= size
+        if code == clear:
+            start, length = start[:clear + 2], length[:clear + 2]
+            size, nxt, prev = min_code + 1, clear + 2, -1
+            continue
+        if code == eoi:
+            break
+        pos = len(out)
+        if code < nxt and (code < clear or code > eoi):
+            src, n = start[code], length[code]
+        else:
+            assert code == nxt and prev >= 0
+            src, n = prev_pos, length[prev] + 1
+        for j in range(n):                       # the lanes' copy: the last byte of the second case is the copy's own first
+            s = src + j
+            out.append(out[s if s < pos else src])
+        if prev >= 0 and nxt < 4096:
+            start.append(prev_pos)
+            length.append(length[prev] + 1)
+            nxt += 1
+            if nxt == (1 << size) and size < 12:
+                size += 1
+        prev, prev_pos = code, pos
+    return np.frombuffer(bytes(out[256:total]).ljust(n_out, b"\0"), np.uint8)
+
+
+def test_lzw_as_copies_equals_table_of_strings():
+    """The kernel's dictionary-as-substrings form against the oracle's classic one, on the streams of real files."""
+    for name, data in files():
+        if len(data) < 200000:
+            assert np.array_equal(G.decode(data, lzw_fn=_lzw_as_copies), G.decode(data)), name
+
+
 def test_oracle_rejects():
     good = _gif(Image.fromarray(_picture(20, 10)).quantize(16))
     with pytest.raises(G.GifError):
