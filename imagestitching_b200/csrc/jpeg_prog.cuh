@@ -437,11 +437,7 @@ __global__ void __launch_bounds__(32) jprog_seq_kernel(const PScan* __restrict__
   __shared__ __align__(16) int16_t ring[JPROG_STAGES][64];
   __shared__ __align__(16) uint8_t bytes[JPROG_RING];
   __shared__ uint8_t zpos[64];             // positions of the block's zero-history coefficients inside the band
-#ifdef JPROG_REVERSE
-  const PScan S = scans[gridDim.x - 1 - blockIdx.x];
-#else
   const PScan S = scans[blockIdx.x];      // a private copy: the decoder's stores cannot alias it
-#endif
   build_tables(S.tab, T);
   const int lane = threadIdx.x;
 #ifdef JPROG_TRACE

@@ -583,14 +583,7 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
   if (one_launch) {
     const int cnt = (int)order.size() - n_par;       // sorted by level: producers get the lower CTA indices
     if (cnt > 0) {
-      // EXPERIMENT: STITCH_JPROG_SPREAD=1 asks for 120 KB of dynamic shared memory per CTA, so that no two scans share an SM
-      static const bool spread = [] { const char* e = std::getenv("STITCH_JPROG_SPREAD"); return e && e[0] == '1'; }();
-      size_t dyn = 0;
-      if (spread) {
-        dyn = 120 * 1024;
-        cudaFuncSetAttribute(jd::jprog_seq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-      }
-      jd::jprog_seq_kernel<<<cnt, 32, dyn, ln.stream>>>(d_recs + n_par);
+      jd::jprog_seq_kernel<<<cnt, 32, 0, ln.stream>>>(d_recs + n_par);
       ++launches;
     }
   } else {
