@@ -21,6 +21,10 @@ import argparse
 import ctypes as C
 import json
 import os
+
+# the library's job lanes are streams of their own; more of them than hardware queues (default 8) makes kernels of one
+# job wait behind another job's (stitch_ctx_create sets the same default when it is the first to touch CUDA; here torch is)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 import threading
 import time

@@ -136,6 +136,7 @@ SIGNATURES = {
     "stitch_kernel_launch_count": (C.c_int64, [C.c_void_p]),
 }
 
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # see stitch_ctx_create (must precede CUDA's initialisation)
 LIB_PATH = os.environ.get("STITCH_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libstitch.so")
 _lib = None
 

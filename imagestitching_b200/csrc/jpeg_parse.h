@@ -64,7 +64,10 @@ enum ParseStatus { kOk = 0, kNotJpeg = 1, kCorrupt = 2, kUnsupported = 3 };
 // End of the entropy-coded data that starts at o: the first marker that is neither a stuffed zero nor RSTn.
 inline size_t scan_end(const uint8_t* p, size_t n, size_t o) {
   while (o + 1 < n) {
-    if (p[o] == 0xFF && p[o + 1] != 0 && p[o + 1] != 0xFF && !(p[o + 1] >= 0xD0 && p[o + 1] <= 0xD7)) return o;
+    const uint8_t* ff = (const uint8_t*)std::memchr(p + o, 0xFF, n - 1 - o);   // entropy-coded data holds few 0xFF bytes
+    if (!ff) return n;
+    o = (size_t)(ff - p);
+    if (p[o + 1] != 0 && p[o + 1] != 0xFF && !(p[o + 1] >= 0xD0 && p[o + 1] <= 0xD7)) return o;
     ++o;
   }
   return n;

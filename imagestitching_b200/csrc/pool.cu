@@ -132,6 +132,7 @@ int enqueue(StitchPool* P, std::unique_ptr<PoolJob> pj, uint64_t* ticket) {
 extern "C" int stitch_pool_create(const int32_t* devices, int32_t n_devices, int32_t lanes_per_device, StitchPool** out) {
   if (!out) return STITCH_E_BAD_ARG;
   *out = nullptr;
+  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);   // see stitch_ctx_create
   int count = 0;
   if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return STITCH_E_CUDA;
   std::unique_ptr<StitchPool> P(new StitchPool());

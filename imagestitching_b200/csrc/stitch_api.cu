@@ -391,7 +391,7 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
   auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
   struct ScanRef { int img, scan, level; bool par; size_t data, state, prefix, consumed, dcdiff; jd::PScan ps;
                    int deps[4]; int ndeps; bool deps_ok; };
-  struct ImgCarve { size_t tabs, qtab, coef, plane[3]; };
+  struct ImgCarve { size_t tabs, qtab, coef, plane[3], file; };
   std::vector<ScanRef> refs;
   ImgCarve cv[JDEC_MAX_IMAGES];
   jd::DecBatch B;   // back end (IDCT + colour) only
@@ -413,6 +413,7 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
     I.rgba = items[i].rgba;
     I.pitch = items[i].pitch;
     ImgCarve& c = cv[i];
+    c.file = need; need += up(items[i].bytes + 16);
     c.tabs = need; need += up(H.scan_tabs.size() * sizeof(jd::Tables));
     c.qtab = need; need += up(sizeof(jd::Tables));
     c.coef = need; need += up((size_t)I.n_blocks * 128);
@@ -478,6 +479,8 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
   need += up(order.size() * sizeof(jd::PScan));
   const size_t prog_words = need;
   need += up(refs.size() * 4);
+  const size_t piece_recs = need;
+  need += up(refs.size() * sizeof(jd::ScanPiece));
   // One launch for all one-warp scans when every dependency among them is between scans of the same block order (they
   // are then chained through progress words); STITCH_JPROG_LEVELS=1 keeps a launch per dependency level.
   const char* lv_env = std::getenv("STITCH_JPROG_LEVELS");
@@ -507,11 +510,15 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
     I.tab = (const jd::Tables*)(A + c.qtab);
     I.coef = (int16_t*)(A + c.coef);
     for (int k = 0; k < 3; ++k) I.plane[k] = A + c.plane[k];
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + c.file, items[i].file, items[i].bytes, cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemcpyAsync(A + c.tabs, H.scan_tabs.data(), H.scan_tabs.size() * sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemcpyAsync(A + c.qtab, &H.tab, sizeof(jd::Tables), cudaMemcpyHostToDevice, ln.stream));
     CUDA_TRY(ctx, cudaMemsetAsync(A + c.coef, 0, (size_t)I.n_blocks * 128, ln.stream));
   }
   std::vector<jd::PScan> host_recs(order.size());
+  std::vector<jd::ScanPiece> host_pieces;
+  host_pieces.reserve(order.size());
+  uint32_t max_piece = 0;
   for (size_t k = 0; k < order.size(); ++k) {
     ScanRef& r = refs[order[k]];
     const jd::Header& H = items[r.img].hdr;
@@ -525,7 +532,10 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
       r.ps.consumed = (uint2*)(A + r.consumed);
       r.ps.dcdiff = r.dcdiff ? (int32_t*)(A + r.dcdiff) : nullptr;
     }
-    if (ps.len) CUDA_TRY(ctx, cudaMemcpyAsync(A + r.data, items[r.img].file + ps.off, ps.len, cudaMemcpyHostToDevice, ln.stream));
+    if (ps.len) {
+      host_pieces.push_back(jd::ScanPiece{A + cv[r.img].file + ps.off, A + r.data, (uint32_t)ps.len});
+      max_piece = std::max(max_piece, (uint32_t)ps.len);
+    }
     r.ps.progress = nullptr;
     r.ps.ndep = 0;
     if (!r.par && one_launch) {
@@ -535,10 +545,16 @@ int decode_prog_batch(StitchCtx* ctx, Lane& ln, DecodeItem* items, int n, bool d
     host_recs[k] = r.ps;
   }
   if (one_launch) CUDA_TRY(ctx, cudaMemsetAsync(A + prog_words, 0, refs.size() * 4, ln.stream));
+  int launches = 0;
+  if (!host_pieces.empty()) {
+    CUDA_TRY(ctx, cudaMemcpyAsync(A + piece_recs, host_pieces.data(), host_pieces.size() * sizeof(jd::ScanPiece), cudaMemcpyHostToDevice, ln.stream));
+    const unsigned gy = std::min<unsigned>(64u, (max_piece + 4095u) / 4096u);
+    jd::jprog_gather_kernel<<<dim3((unsigned)host_pieces.size(), std::max(1u, gy)), 256, 0, ln.stream>>>((const jd::ScanPiece*)(A + piece_recs));
+    ++launches;
+  }
   jd::PScan* d_recs = (jd::PScan*)(A + recs);
   if (!host_recs.empty())
     CUDA_TRY(ctx, cudaMemcpyAsync(d_recs, host_recs.data(), host_recs.size() * sizeof(jd::PScan), cudaMemcpyHostToDevice, ln.stream));
-  int launches = 0;
   ln.info_host[INFO_PDEC_CHANGED] = 0;
   if (n_par > 0) {
     jd::PBatch P;
@@ -1767,6 +1783,11 @@ void drain_lane(StitchCtx* ctx, Lane& ln) {
 extern "C" int stitch_ctx_create(int32_t device, void* stream, StitchCtx** out) {
   if (!out) return STITCH_E_BAD_ARG;
   *out = nullptr;
+  // A context drives up to STITCH_MAX_LANES job streams (+ upload / download streams); with the default of 8 hardware
+  // queues they alias, and a short kernel of one job waits behind another job's long one (progressive-JPEG jobs: 18
+  // instead of 10 ms/job with eight in flight).  Takes effect when CUDA has not been initialised in the process yet;
+  // a value the caller has set is left alone.
+  setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
   int count = 0;
   cudaError_t e = cudaGetDeviceCount(&count);
   if (e != cudaSuccess || device < 0 || device >= count) return STITCH_E_CUDA;
