@@ -466,6 +466,7 @@ def main():
     ap.add_argument("--lanes", type=int, default=2,
                     help="job lanes of the StitchCtx the device-resident steps rotate over (1 = one job at a time)")
     ap.add_argument("--e2e-lanes", type=int, default=3, help="job lanes for the host-buffer (e2e) steps")
+    ap.add_argument("--files-lanes", type=int, default=6, help="job lanes for the file-in / file-out (e2e_files) legs")
     ap.add_argument("--files-steps", type=int, default=-1,
                     help="e2e_files leg (JPEG files in host memory -> exported file in host memory): jobs per output kind; "
                          "-1 = auto (24 for cfg2 / cfg5, 0 = skip for the other workloads)")
@@ -733,7 +734,8 @@ def main():
 
     # ---- end to end from FILES: 9 JPEG files in (pinned) host memory -> decode + stitch + encode on the GPU -> the
     # exported file in host memory (what the page does between P:1441 and P:1581).  Uploads 14x fewer bytes than e2e.
-    files_steps = args.files_steps if args.files_steps >= 0 else (24 if args.workload in ("cfg2", "cfg5") else 0)
+    files_steps = args.files_steps if args.files_steps >= 0 else (36 if args.workload in ("cfg2", "cfg5") else 0)
+    f_lanes = max(1, min(8, args.files_lanes))   # file jobs are GPU-bound, not PCIe-bound: more of them in flight fill the gaps
     e2e_files = None
     shot_files = None
     prog_files = None
@@ -753,13 +755,13 @@ def main():
             fbufs.append((pf, len(o.jpeg)))
             host_outs.append(pf)
         in_bytes = sum(b for _, b in fbufs)
-        ctx.set_lanes(e2e_lanes)
-        e2e_files = {"unit": "MP/s", "steps": files_steps, "h2d_bytes_per_step": in_bytes, "lanes": e2e_lanes,
+        ctx.set_lanes(f_lanes)
+        e2e_files = {"unit": "MP/s", "steps": files_steps, "h2d_bytes_per_step": in_bytes, "lanes": f_lanes,
                      "inputs": f"{len(dims)} baseline JPEG files, quality 90, 4:2:0 ({in_bytes / 1e6:.1f} MB), pinned host memory"}
         for kind, flag in (("png", L.OUT_PNG), ("jpeg", L.OUT_JPEG)):
             cap = rgba_bytes + (rgba_bytes >> 2) if kind == "png" else (64 << 20)
             fjobs = []
-            for _ in range(e2e_lanes):
+            for _ in range(f_lanes):
                 arr = (L.StitchImage * len(dims))()
                 for i, (w, h) in enumerate(dims):
                     arr[i].desc.natural_width, arr[i].desc.natural_height = w, h
@@ -786,16 +788,16 @@ def main():
             def files_loop(nsteps):
                 tickets = []
                 for i in range(nsteps):
-                    fj, _, fr = fjobs[i % e2e_lanes]
+                    fj, _, fr = fjobs[i % f_lanes]
                     t = C.c_uint64()
                     st = lib.stitch_submit(ctx.handle, C.byref(fj), C.byref(fr), C.byref(t))
                     assert st == 0, lib.stitch_last_error(ctx.handle)
                     tickets.append(t.value)
-                    if i >= e2e_lanes - 1:
-                        assert lib.stitch_wait(ctx.handle, tickets[i - (e2e_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
+                    if i >= f_lanes - 1:
+                        assert lib.stitch_wait(ctx.handle, tickets[i - (f_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
                 assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0, lib.stitch_last_error(ctx.handle)
 
-            files_loop(2 * e2e_lanes)
+            files_loop(2 * f_lanes)
             torch.cuda.synchronize()
             barrier()
             t0 = time.perf_counter()
@@ -829,7 +831,7 @@ def main():
                 host_outs.append(pf)
             sjobs = []
             s_cap = 0
-            for _ in range(e2e_lanes):
+            for _ in range(f_lanes):
                 arr = (L.StitchImage * 9)()
                 for i in range(9):
                     arr[i].desc.natural_width, arr[i].desc.natural_height = 1290, 2796
@@ -859,16 +861,16 @@ def main():
             def shots_loop(nsteps):
                 tickets = []
                 for i in range(nsteps):
-                    sj, _, sr = sjobs[i % e2e_lanes]
+                    sj, _, sr = sjobs[i % f_lanes]
                     t = C.c_uint64()
                     st = lib.stitch_submit(ctx.handle, C.byref(sj), C.byref(sr), C.byref(t))
                     assert st == 0, lib.stitch_last_error(ctx.handle)
                     tickets.append(t.value)
-                    if i >= e2e_lanes - 1:
-                        assert lib.stitch_wait(ctx.handle, tickets[i - (e2e_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
+                    if i >= f_lanes - 1:
+                        assert lib.stitch_wait(ctx.handle, tickets[i - (f_lanes - 1)]) == 0, lib.stitch_last_error(ctx.handle)
                 assert lib.stitch_wait(ctx.handle, tickets[-1]) == 0, lib.stitch_last_error(ctx.handle)
 
-            shots_loop(2 * e2e_lanes)
+            shots_loop(2 * f_lanes)
             torch.cuda.synchronize()
             barrier()
             t0 = time.perf_counter()
@@ -967,7 +969,7 @@ def main():
                 t = torch.tensor([ps_], dtype=torch.float64, device="cuda")
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 ps_ = float(t.item())
-            ctx.set_lanes(e2e_lanes)
+            ctx.set_lanes(f_lanes)
             e2e_files["prog_in"] = {"value": p_mp * p_steps * world / ps_, "unit": "MP/s", "steps": p_steps, "lanes": p_lanes,
                                     "ms_per_step": ps_ / p_steps * 1e3, "single_job_latency_ms": p_single, "output_mp_per_step": p_mp,
                                     "h2d_bytes_per_step": sum(b for _, b in pbufs), "d2h_bytes_per_step": int(pjobs[0][2].jpeg_bytes),
@@ -979,7 +981,7 @@ def main():
             e2e_files["prog_in"] = {"value": None, "note": f"failed: {e}"}
             prog_files = None
             try:
-                ctx.set_lanes(e2e_lanes)
+                ctx.set_lanes(f_lanes)
             except Exception:
                 pass
 
@@ -997,7 +999,7 @@ def main():
                    "inputs": "device-resident RGBA8, generated on device (seed 0x5717C4)",
                    "l2": f"{len(jobs)} job slots rotated; each job reads {src_bytes/1e6:.0f} MB (> 126 MB L2)",
                    "parallelism": f"{world} rank(s), jobs sharded, no collective",
-                   "lanes": f"{max(1, args.lanes)} job lane(s) per ctx for the device-resident steps, {e2e_lanes} for e2e",
+                   "lanes": f"{max(1, args.lanes)} job lane(s) per ctx for the device-resident steps, {e2e_lanes} for e2e, {max(1, min(8, args.files_lanes))} for e2e_files",
                    "host_placement": placement, "prewarm_jobs": PREWARM_JOBS},
         "gpu_launches": int(launches),
         "host_us_per_submit": round(host_s[0] / max(1, args.steps) * 1e6, 2),   # layout + plan + launch inside stitch_submit
