@@ -49,3 +49,29 @@ extern "C" int parse_fuzz_one(int kind, const uint8_t* data, size_t n) {
   std::free(f);
   return st;
 }
+
+// What the parsers read from an intact file: out = {status, width, height, a, b, c, d, e}
+//   JPEG: a = components, b = luma h-sampling, c = luma v-sampling, d = progressive, e = scans
+//   PNG:  a = bit depth, b = colour type, c = interlace, d = row bytes
+//   BMP:  a = bits per pixel, b = top-down, c = row stride, d = offset of the pixel array
+//   GIF:  a = interlaced, b = LZW minimum code size, c = transparent index (-1: none), d = bytes of LZW data
+extern "C" void parse_fields(int kind, const uint8_t* f, size_t n, int64_t* out) {
+  for (int i = 0; i < 8; ++i) out[i] = 0;
+  if (kind == 0) {
+    stitch::jpegdec::Header H;
+    out[0] = (int)stitch::jpegdec::parse(f, n, &H);
+    out[1] = H.w; out[2] = H.h; out[3] = H.ncomp; out[4] = H.hs; out[5] = H.vs; out[6] = H.progressive; out[7] = (int64_t)H.scans.size();
+  } else if (kind == 1) {
+    stitch::pngdec::Header H;
+    out[0] = (int)stitch::pngdec::parse(f, n, &H);
+    out[1] = H.w; out[2] = H.h; out[3] = H.depth; out[4] = H.ctype; out[5] = H.interlace; out[6] = H.row_bytes;
+  } else if (kind == 2) {
+    stitch::bmpdec::Header H;
+    out[0] = (int)stitch::bmpdec::parse(f, n, &H);
+    out[1] = H.w; out[2] = H.h; out[3] = H.bpp; out[4] = H.top_down; out[5] = H.row_stride; out[6] = H.data_off;
+  } else {
+    stitch::gifdec::Header H;
+    out[0] = (int)stitch::gifdec::parse(f, n, &H);
+    out[1] = H.w; out[2] = H.h; out[3] = H.interlaced; out[4] = H.min_code; out[5] = H.transparent; out[6] = H.stream_len;
+  }
+}

@@ -33,17 +33,19 @@ def files():
     rng = np.random.default_rng(1)
     out = []
     for (w, h) in ((1, 1), (7, 5), (64, 48), (123, 77), (250, 131)):
-        for kw in ({}, {"interlace": 1}, {"transparency": 3}, {"interlace": 1, "transparency": 0}):
+        # PIL interlaces by default (pictures of 16 px and more): interlace=0 asks for rows in order
+        for kw in ({"interlace": 0}, {"interlace": 1}, {"transparency": 3, "interlace": 0}, {"interlace": 1, "transparency": 0}):
             for colours in (2, 16, 256):
-                out.append((f"{w}x{h}_{colours}_{sorted(kw)}", _gif(Image.fromarray(_picture(w, h, colours)).quantize(colours), **kw)))
+                out.append((f"{w}x{h}_{colours}_{kw}", _gif(Image.fromarray(_picture(w, h, colours)).quantize(colours), **kw)))
     g = np.zeros((300, 400), np.uint8)        # a flat graphic: long strings, the dictionary fills up and is cleared
     g[50:200, 80:300] = 7
     g[::17] = 3
     im = Image.fromarray(g, "P")
     im.putpalette([int(v) for v in rng.integers(0, 256, 768)])
     out.append(("graphic", _gif(im)))
+    out.append(("graphic_rows_in_order", _gif(im, interlace=0)))
     out.append(("gray", _gif(Image.fromarray(_picture(200, 150)[..., 0], "L"))))
-    out.append(("photo_800x600", _gif(Image.fromarray(_picture(800, 600, 5)).quantize(256))))
+    out.append(("photo_800x600", _gif(Image.fromarray(_picture(800, 600, 5)).quantize(256), interlace=0)))
     # strings longer than the decoder's shared-memory window of recent output, and sources behind it
     big = np.zeros((900, 1600), np.uint8)
     big[100:800, 200:1400] = 1

@@ -96,3 +96,59 @@ def test_parsers_survive_damaged_files(tmp_path):
     for kind, path in _files(str(tmp_path)):
         r = subprocess.run([sys.executable, "-c", DRIVER, lib, str(kind), path, "600"], env=env, capture_output=True, text=True, timeout=300)
         assert r.returncode == 0, f"{path}:\n{r.stdout[-500:]}\n{r.stderr[-3000:]}"
+
+
+def _plain_lib():
+    """The same source without the sanitizers (loads into this process)."""
+    out = os.path.join(ROOT, "tests", "_build", "libparse_plain.so")
+    src = os.path.join(ROOT, "tests", "native", "parse_fuzz.cpp")
+    inc = os.path.join(ROOT, "imagestitching_b200", "csrc")
+    deps = [src] + [os.path.join(inc, f) for f in ("jpeg_parse.h", "png_parse.h", "bmp_parse.h", "gif_parse.h")]
+    if not os.path.exists(out) or any(os.path.getmtime(d) > os.path.getmtime(out) for d in deps):
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-I" + inc, "-o", out, src])
+    import ctypes
+    lib = ctypes.CDLL(out)
+    lib.parse_fields.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
+    return lib
+
+
+def _fields(lib, kind, data):
+    out = np.zeros(8, np.int64)
+    lib.parse_fields(kind, data, len(data), out.ctypes.data)
+    return out.tolist()
+
+
+def test_parsers_read_what_the_files_say():
+    """Header fields of the library's host-side parsers against what PIL and the test writers put into the files."""
+    from tests import test_bmp_decode as TB
+    from tests import test_gif_decode as TG
+    from tests.test_jpeg_decode import _jpeg
+    lib = _plain_lib()
+    for name, data in TB.files():
+        im = Image.open(io.BytesIO(data))
+        st, w, h, bpp, top_down, stride, off, _ = _fields(lib, 2, data)
+        assert st == 0 and (w, h) == im.size, name
+        assert stride == (w * bpp + 31) // 32 * 4 and off + stride * h <= len(data), name
+        if name != "pal8_os2":                       # (that entry of the BMP test list repeats the top-down file)
+            assert top_down == ("topdown" in name), name
+    for name, data in TG.files():
+        im = Image.open(io.BytesIO(data))
+        st, w, h, laced, min_code, transparent, stream_len, _ = _fields(lib, 3, data)
+        assert st == 0 and (w, h) == im.size, name
+        assert transparent == im.info.get("transparency", -1), name
+        if "'interlace': 0" in name or "rows_in_order" in name:
+            assert laced == 0, name
+        elif "'interlace': 1" in name:
+            assert laced == (min(w, h) >= 16), name      # PIL does not interlace pictures under 16 px
+        assert 2 <= min_code <= 8 and 0 < stream_len < len(data), name
+    for kw, want in (({"subsampling": 0}, (3, 1, 1, 0, 0)), ({"subsampling": 1}, (3, 2, 1, 0, 0)), ({"subsampling": 2}, (3, 2, 2, 0, 0)),
+                     ({"gray": True}, (1, 1, 1, 0, 0)), ({"subsampling": 2, "progressive": True}, (3, 2, 2, 1, 10)),
+                     ({"gray": True, "progressive": True}, (1, 1, 1, 1, 6))):
+        data = _jpeg(123, 77, quality=80, **kw)
+        f = _fields(lib, 0, data)
+        assert f[0] == 0 and f[1:3] == [123, 77] and tuple(f[3:8]) == want, (kw, f)
+    b = io.BytesIO()
+    _picture(50, 31).save(b, "PNG")
+    f = _fields(lib, 1, b.getvalue())
+    assert f[:7] == [0, 50, 31, 8, 2, 0, 150], f
