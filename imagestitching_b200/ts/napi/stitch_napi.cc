@@ -254,6 +254,34 @@ napi_value Preview(napi_env env, napi_callback_info info) {
   return out;
 }
 
+// decodeImage(ctx, file) -> { width, height, data: Uint8Array }   (stitch_decode_image; synchronous): loadImageFrom
+// (canvas.js:27-121) for a JPEG / PNG / BMP / GIF file, decoded on the GPU into straight-alpha RGBA8
+napi_value DecodeImage(napi_env env, napi_callback_info info) {
+  size_t argc = 2; napi_value argv[2];
+  napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+  void* p = nullptr;
+  napi_get_value_external(env, argv[0], &p);
+  napi_typedarray_type tt; size_t len = 0; void* src = nullptr; napi_value ab; size_t off = 0;
+  if (napi_get_typedarray_info(env, argv[1], &tt, &len, &src, &ab, &off) != napi_ok) {
+    napi_throw_type_error(env, nullptr, "decodeImage: file must be a Uint8Array");
+    return nullptr;
+  }
+  StitchImageInfo pi;
+  int st = stitch_probe_image(src, len, &pi);
+  if (st != STITCH_OK || pi.width <= 0 || pi.height <= 0) { napi_throw_error(env, nullptr, stitch_strerror(st ? st : STITCH_E_BAD_IMAGE)); return nullptr; }
+  const size_t bytes = (size_t)pi.width * (size_t)pi.height * 4;
+  void* dst; napi_value out_ab, data, out, v;
+  napi_create_arraybuffer(env, bytes, &dst, &out_ab);
+  st = stitch_decode_image(static_cast<StitchCtx*>(p), src, len, dst, (int64_t)bytes, 0, STITCH_MEM_HOST, nullptr);
+  if (st != STITCH_OK) { napi_throw_error(env, nullptr, stitch_last_error(static_cast<StitchCtx*>(p))); return nullptr; }
+  napi_create_typedarray(env, napi_uint8_array, bytes, out_ab, 0, &data);
+  napi_create_object(env, &out);
+  napi_create_int32(env, pi.width, &v); napi_set_named_property(env, out, "width", v);
+  napi_create_int32(env, pi.height, &v); napi_set_named_property(env, out, "height", v);
+  napi_set_named_property(env, out, "data", data);
+  return out;
+}
+
 napi_value Init(napi_env env, napi_value exports) {
   napi_property_descriptor props[] = {
       {"createContext", nullptr, CreateContext, nullptr, nullptr, nullptr, napi_default, nullptr},
@@ -261,8 +289,9 @@ napi_value Init(napi_env env, napi_value exports) {
       {"run", nullptr, Run, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"probe", nullptr, Probe, nullptr, nullptr, nullptr, napi_default, nullptr},
       {"preview", nullptr, Preview, nullptr, nullptr, nullptr, napi_default, nullptr},
+      {"decodeImage", nullptr, DecodeImage, nullptr, nullptr, nullptr, napi_default, nullptr},
   };
-  napi_define_properties(env, exports, 5, props);
+  napi_define_properties(env, exports, 6, props);
   return exports;
 }
 

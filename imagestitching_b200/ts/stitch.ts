@@ -13,6 +13,7 @@ const native = require('./build/Release/stitch_napi.node') as {
   run(ctx: unknown, job: NativeJob, onProgress?: (pct: number) => void): Promise<NativeResult>;
   probe(file: Uint8Array): { width: number; height: number; type: string; orientation: string; orientationExif: number };
   preview(ctx: unknown, rgba: Uint8Array, exportW: number, exportH: number, viewW: number, viewH: number, dpr: number): Uint8Array;
+  decodeImage(ctx: unknown, file: Uint8Array): { width: number; height: number; data: Uint8Array };
 };
 
 export interface StitchImage extends ImageRecord {
@@ -58,6 +59,14 @@ export function preview(rgba: Uint8Array, exportW: number, exportH: number, view
   let ctx = contexts.get(device);
   if (!ctx) { ctx = native.createContext(device); contexts.set(device, ctx); }
   return native.preview(ctx, rgba, exportW, exportH, viewW, viewH, pixelRatio);
+}
+
+/** loadImageFrom (canvas.js:27-121) for an in-memory file -- JPEG (baseline or progressive), PNG, BMP, GIF (first frame):
+ *  decoded on the GPU (stitch_decode_image) into straight-alpha RGBA8; rejects like the page's 图片解码异常. */
+export function decodeImage(file: Uint8Array, device = 0): { width: number; height: number; data: Uint8Array } {
+  let ctx = contexts.get(device);
+  if (!ctx) { ctx = native.createContext(device); contexts.set(device, ctx); }
+  return native.decodeImage(ctx, file);
 }
 
 /** onStitch(): resolves to undefined for an empty list (index.js:1189), rejects with the reference's messages. */
